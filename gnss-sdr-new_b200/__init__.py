@@ -1,0 +1,362 @@
+"""gnss-sdr-new_b200 — B200-native GNSS correlation engine (PCPS acquisition + tracking multicorrelator).
+
+Python is only the test / bench driver: this module is a thin ctypes layer over the C-ABI of
+libgnss_b200.so (include/gnss_b200.h). All arithmetic runs in hand-written sm_100a CUDA kernels; there is
+no CPU fallback and this package never imports anything from oracle/.
+"""
+import ctypes as C
+import math
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgnss_b200.so")
+
+c_u32 = C.c_uint32
+c_i32 = C.c_int32
+_fp = C.POINTER(C.c_float)
+_u32p = C.POINTER(c_u32)
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+class AcqCfg(C.Structure):
+    _fields_ = [
+        ("fft_size", c_u32), ("consumed_samples", c_u32), ("bit_transition", c_u32), ("doppler_max", c_i32),
+        ("doppler_step", c_u32), ("fs", C.c_double), ("samples_per_chip", c_u32), ("use_cfar", c_u32),
+        ("keep_grid", c_u32), ("max_slots", c_u32), ("device", c_i32), ("row_begin", c_u32), ("row_end", c_u32),
+    ]
+
+
+class AcqResult(C.Structure):
+    _fields_ = [
+        ("test_statistic", C.c_float), ("peak", C.c_float), ("input_power", C.c_float), ("second_peak", C.c_float),
+        ("code_phase", c_u32), ("doppler_index", c_u32), ("doppler_hz", c_i32), ("dwell_count", c_u32),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class AcqRow(C.Structure):
+    _fields_ = [("max_val", C.c_float), ("max_idx", c_u32), ("row_sum", C.c_float), ("valid", c_u32)]
+
+
+ACQ_ROW_DTYPE = np.dtype([("max_val", np.float32), ("max_idx", np.uint32), ("row_sum", np.float32), ("valid", np.uint32)])
+ACQ_RESULT_DTYPE = np.dtype([("test_statistic", np.float32), ("peak", np.float32), ("input_power", np.float32),
+                             ("second_peak", np.float32), ("code_phase", np.uint32), ("doppler_index", np.uint32),
+                             ("doppler_hz", np.int32), ("dwell_count", np.uint32)])
+
+
+class McArgs(C.Structure):
+    _fields_ = [
+        ("sig_in_c64", C.c_void_p), ("stream_offset", C.c_uint64), ("n_samples", c_u32),
+        ("rem_carr_phase_rad", C.c_float), ("carr_step_rad", C.c_float), ("carr_rate_rad", C.c_float),
+        ("rem_code_phase_chips", C.c_float), ("code_step_chips", C.c_float), ("code_rate_chips", C.c_float),
+    ]
+
+
+MC_HIGH_DYN = 1
+MC_SIX_ARG = 2
+
+# every symbol include/gnss_b200.h declares (tests check the library exports all of them)
+EXPORTS = [
+    "gnss_b200_last_error", "gnss_b200_version", "gnss_b200_device_count", "gnss_b200_host_register",
+    "gnss_b200_host_unregister", "gnss_b200_acq_create", "gnss_b200_acq_destroy", "gnss_b200_acq_num_doppler_bins",
+    "gnss_b200_acq_set_local_code", "gnss_b200_acq_set_local_codes", "gnss_b200_acq_set_doppler_center",
+    "gnss_b200_acq_reset", "gnss_b200_acq_dwell", "gnss_b200_acq_dwell_device_async", "gnss_b200_acq_sync",
+    "gnss_b200_acq_read_grid", "gnss_b200_acq_read_rows", "gnss_b200_acq_finalize_rows", "gnss_b200_acq_threshold",
+    "gnss_b200_acq_stream", "gnss_b200_acq_launch_count", "gnss_b200_mc_create", "gnss_b200_mc_destroy",
+    "gnss_b200_mc_set_code", "gnss_b200_mc_set_stream", "gnss_b200_mc_correlate_batch",
+    "gnss_b200_mc_correlate_device_async", "gnss_b200_mc_sync", "gnss_b200_mc_chip_indices", "gnss_b200_mc_stream",
+    "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan",
+]
+
+_lib = None
+
+
+def lib():
+    """Load libgnss_b200.so. Fails loudly if it was not built (python gnss-sdr-new_b200/build.py)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B200Error(f"{LIB_PATH} is missing: build it with `python gnss-sdr-new_b200/build.py` (needs nvcc). "
+                        "There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    L.gnss_b200_last_error.restype = C.c_char_p
+    L.gnss_b200_version.restype = C.c_char_p
+    L.gnss_b200_acq_create.argtypes = [C.POINTER(AcqCfg), C.POINTER(C.c_void_p)]
+    L.gnss_b200_acq_destroy.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_num_doppler_bins.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_num_doppler_bins.restype = c_u32
+    L.gnss_b200_acq_set_local_code.argtypes = [C.c_void_p, c_u32, _fp]
+    L.gnss_b200_acq_set_local_codes.argtypes = [C.c_void_p, c_u32, _u32p, _fp]
+    L.gnss_b200_acq_set_doppler_center.argtypes = [C.c_void_p, c_u32, c_i32, c_i32]
+    L.gnss_b200_acq_reset.argtypes = [C.c_void_p, c_u32]
+    L.gnss_b200_acq_dwell.argtypes = [C.c_void_p, C.c_void_p, C.c_int, c_u32, _u32p, C.c_void_p]
+    L.gnss_b200_acq_dwell_device_async.argtypes = [C.c_void_p, C.c_void_p, c_u32, _u32p]
+    L.gnss_b200_acq_sync.argtypes = [C.c_void_p, c_u32, C.c_void_p]
+    L.gnss_b200_acq_read_grid.argtypes = [C.c_void_p, c_u32, _fp]
+    L.gnss_b200_acq_read_rows.argtypes = [C.c_void_p, c_u32, C.c_void_p]
+    L.gnss_b200_acq_finalize_rows.argtypes = [C.c_void_p, c_u32, c_u32, c_i32, c_u32, c_i32, c_u32, C.c_void_p]
+    L.gnss_b200_acq_threshold.argtypes = [C.c_float, c_u32, c_u32, c_u32, C.c_int]
+    L.gnss_b200_acq_threshold.restype = C.c_float
+    L.gnss_b200_acq_stream.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_stream.restype = C.c_void_p
+    L.gnss_b200_acq_launch_count.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_launch_count.restype = C.c_uint64
+    L.gnss_b200_host_register.argtypes = [C.c_void_p, C.c_size_t]
+    L.gnss_b200_host_unregister.argtypes = [C.c_void_p]
+    L.gnss_b200_mc_create.argtypes = [c_u32, c_u32, c_u32, c_i32, C.POINTER(C.c_void_p)]
+    L.gnss_b200_mc_destroy.argtypes = [C.c_void_p]
+    L.gnss_b200_mc_set_code.argtypes = [C.c_void_p, c_u32, c_u32, _fp, C.c_int]
+    L.gnss_b200_mc_set_stream.argtypes = [C.c_void_p, _fp, C.c_uint64]
+    L.gnss_b200_mc_correlate_batch.argtypes = [C.c_void_p, c_u32, _u32p, C.POINTER(McArgs), _fp, c_u32, c_u32, _fp]
+    L.gnss_b200_mc_correlate_device_async.argtypes = [C.c_void_p, c_u32, _u32p, C.POINTER(McArgs), _fp, c_u32, c_u32,
+                                                      C.c_void_p, C.c_uint64]
+    L.gnss_b200_mc_sync.argtypes = [C.c_void_p, c_u32, c_u32, _fp]
+    L.gnss_b200_mc_chip_indices.argtypes = [C.c_void_p, c_u32, C.POINTER(McArgs), _fp, c_u32, c_u32, C.POINTER(c_i32)]
+    L.gnss_b200_mc_stream.argtypes = [C.c_void_p]
+    L.gnss_b200_mc_stream.restype = C.c_void_p
+    L.gnss_b200_mc_launch_count.argtypes = [C.c_void_p]
+    L.gnss_b200_mc_launch_count.restype = C.c_uint64
+    L.gnss_b200_debug_wipeoff_phase.argtypes = [c_i32, C.c_double, c_u32, _fp, _u32p]
+    L.gnss_b200_debug_fft_plan.argtypes = [c_u32, _u32p, _u32p, _u32p, _u32p]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise B200Error(f"gnss_b200 status {rc}: {lib().gnss_b200_last_error().decode(errors='replace')}")
+
+
+def _f32p(a):
+    return a.ctypes.data_as(_fp)
+
+
+def _u32a(x):
+    return np.ascontiguousarray(x, dtype=np.uint32)
+
+
+# --------------------------------------------------------------------------------------------------
+# Acquisition geometry: what Acq_Conf::SetFromConfiguration / SetDerivedParams (acq_conf.cc:24-119) and the
+# pcps_acquisition constructor (pcps_acquisition.cc:68-92) derive from the configuration keys.
+# --------------------------------------------------------------------------------------------------
+def acq_geometry(fs, chip_rate, ms_per_code, sampled_ms, bit_transition=False):
+    samples_per_ms = np.float32(np.float32(fs) * np.float32(0.001))
+    samples_per_chip = int(math.ceil(float(np.float32(fs) / np.float32(chip_rate))))
+    samples_per_code = float(np.float32(samples_per_ms * np.float32(ms_per_code)))
+    consumed = int(sampled_ms * float(samples_per_ms) * (2.0 if bit_transition else 1.0))
+    fft_size = consumed if sampled_ms == ms_per_code else consumed * 2
+    return dict(fft_size=fft_size, consumed_samples=consumed, samples_per_chip=samples_per_chip,
+                samples_per_code=samples_per_code, effective_size=fft_size // 2 if bit_transition else fft_size)
+
+
+class PcpsAcquisitionB200:
+    """A batch of reference `pcps_acquisition` block instances ("slots") sharing one sample stream.
+
+    Method names follow the reference block / AcquisitionInterface (set_local_code, set_doppler_center,
+    reset, ...); `dwell` is one `acquisition_core` pass for a list of slots.
+    """
+
+    def __init__(self, fft_size, consumed_samples, doppler_max, doppler_step, fs, samples_per_chip, max_slots,
+                 use_cfar=True, bit_transition=False, keep_grid=False, device=0, row_begin=0, row_end=0):
+        self.L = lib()
+        self.cfg = AcqCfg(fft_size, consumed_samples, int(bit_transition), int(doppler_max), int(doppler_step), float(fs),
+                          int(samples_per_chip), int(use_cfar), int(keep_grid), int(max_slots), int(device),
+                          int(row_begin), int(row_end))
+        self.h = C.c_void_p()
+        _check(self.L.gnss_b200_acq_create(C.byref(self.cfg), C.byref(self.h)))
+        self.fft_size = fft_size
+        self.consumed = consumed_samples
+        self.eff = fft_size // 2 if bit_transition else fft_size
+        self.n_doppler = self.L.gnss_b200_acq_num_doppler_bins(self.h)
+        self.n_doppler_local = (row_end - row_begin) if row_end > row_begin else self.n_doppler
+        self.max_slots = max_slots
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.gnss_b200_acq_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_local_codes(self, slots, codes):
+        slots = _u32a(slots)
+        codes = np.ascontiguousarray(codes, dtype=np.complex64).reshape(slots.size, -1)
+        if codes.shape[1] != self.consumed:
+            raise B200Error(f"set_local_codes: each code needs consumed_samples={self.consumed} items, got {codes.shape[1]}")
+        _check(self.L.gnss_b200_acq_set_local_codes(self.h, slots.size, slots.ctypes.data_as(_u32p), _f32p(codes.view(np.float32))))
+
+    def set_local_code(self, slot, code):
+        self.set_local_codes([slot], np.asarray(code)[None, :])
+
+    def set_doppler_center(self, slot, center_hz, bias_hz=0):
+        _check(self.L.gnss_b200_acq_set_doppler_center(self.h, slot, int(center_hz), int(bias_hz)))
+
+    def reset(self, slot):
+        _check(self.L.gnss_b200_acq_reset(self.h, slot))
+
+    def dwell(self, samples, slots):
+        slots = _u32a(slots)
+        samples = np.ascontiguousarray(samples)
+        if samples.dtype == np.int16:
+            is_cshort = 1
+            if samples.size < 2 * self.consumed:
+                raise B200Error("dwell: not enough cshort samples")
+        else:
+            is_cshort = 0
+            samples = samples.astype(np.complex64, copy=False)
+            if samples.size < self.consumed:
+                raise B200Error("dwell: not enough samples")
+        res = np.zeros(slots.size, dtype=ACQ_RESULT_DTYPE)
+        _check(self.L.gnss_b200_acq_dwell(self.h, samples.ctypes.data_as(C.c_void_p), is_cshort, slots.size,
+                                          slots.ctypes.data_as(_u32p), res.ctypes.data_as(C.c_void_p)))
+        return res
+
+    def dwell_device_async(self, d_samples_ptr, slots):
+        slots = _u32a(slots)
+        _check(self.L.gnss_b200_acq_dwell_device_async(self.h, C.c_void_p(d_samples_ptr), slots.size, slots.ctypes.data_as(_u32p)))
+
+    def sync(self, n_slots):
+        res = np.zeros(n_slots, dtype=ACQ_RESULT_DTYPE)
+        _check(self.L.gnss_b200_acq_sync(self.h, n_slots, res.ctypes.data_as(C.c_void_p)))
+        return res
+
+    def read_grid(self, slot):
+        out = np.zeros((self.n_doppler_local, self.eff), dtype=np.float32)
+        _check(self.L.gnss_b200_acq_read_grid(self.h, slot, _f32p(out)))
+        return out
+
+    def read_rows(self, slot):
+        rows = np.zeros(self.n_doppler, dtype=ACQ_ROW_DTYPE)
+        _check(self.L.gnss_b200_acq_read_rows(self.h, slot, rows.ctypes.data_as(C.c_void_p)))
+        return rows
+
+    def stream(self):
+        return self.L.gnss_b200_acq_stream(self.h)
+
+    def launch_count(self):
+        return int(self.L.gnss_b200_acq_launch_count(self.h))
+
+
+def finalize_rows(rows, effective_size, doppler_max, doppler_step, doppler_center, dwell_count):
+    rows = np.ascontiguousarray(rows, dtype=ACQ_ROW_DTYPE)
+    res = np.zeros(1, dtype=ACQ_RESULT_DTYPE)
+    _check(lib().gnss_b200_acq_finalize_rows(rows.ctypes.data_as(C.c_void_p), rows.size, effective_size, doppler_max,
+                                             doppler_step, doppler_center, dwell_count, res.ctypes.data_as(C.c_void_p)))
+    return res[0]
+
+
+def acq_threshold(pfa, effective_size, n_doppler, max_dwells=1, bit_transition=False):
+    return float(lib().gnss_b200_acq_threshold(pfa, effective_size, n_doppler, max_dwells, int(bit_transition)))
+
+
+def debug_wipeoff_phase(doppler_hz, fs, n):
+    out = np.zeros(n, dtype=np.float32)
+    npc = c_u32(0)
+    _check(lib().gnss_b200_debug_wipeoff_phase(int(doppler_hz), float(fs), n, _f32p(out), C.byref(npc)))
+    return out, npc.value
+
+
+def debug_fft_plan(n):
+    ns, nr = c_u32(0), c_u32(0)
+    rad = np.zeros(32, dtype=np.uint32)
+    perm = np.zeros(n, dtype=np.uint32)
+    _check(lib().gnss_b200_debug_fft_plan(n, C.byref(ns), rad.ctypes.data_as(_u32p), C.byref(nr), perm.ctypes.data_as(_u32p)))
+    return ns.value, rad[:nr.value].tolist(), perm
+
+
+class MulticorrelatorB200:
+    """`max_channels` reference correlator objects (Cpu_Multicorrelator_Real_Codes / Cpu_Multicorrelator) in one engine."""
+
+    def __init__(self, max_channels, max_samples, max_taps, device=0):
+        self.L = lib()
+        self.h = C.c_void_p()
+        _check(self.L.gnss_b200_mc_create(max_channels, max_samples, max_taps, device, C.byref(self.h)))
+        self.max_channels, self.max_samples, self.max_taps = max_channels, max_samples, max_taps
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.gnss_b200_mc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_local_code(self, ch, code):
+        code = np.ascontiguousarray(code)
+        if np.iscomplexobj(code):
+            code = code.astype(np.complex64, copy=False)
+            _check(self.L.gnss_b200_mc_set_code(self.h, ch, code.size, _f32p(code.view(np.float32)), 1))
+        else:
+            code = code.astype(np.float32, copy=False)
+            _check(self.L.gnss_b200_mc_set_code(self.h, ch, code.size, _f32p(code), 0))
+
+    def set_stream(self, samples):
+        samples = np.ascontiguousarray(samples, dtype=np.complex64)
+        self._keep = [samples]
+        _check(self.L.gnss_b200_mc_set_stream(self.h, _f32p(samples.view(np.float32)), samples.size))
+
+    @staticmethod
+    def make_args(n_ch, n_samples, rem_carr, carr_step, carr_rate, rem_code, code_step, code_rate, sig_ptrs=None, stream_offsets=None):
+        arr = (McArgs * n_ch)()
+        bc = lambda v: np.broadcast_to(np.asarray(v), (n_ch,))  # noqa: E731
+        ns, rc, cs, cr, rk, ks, kr = map(bc, (n_samples, rem_carr, carr_step, carr_rate, rem_code, code_step, code_rate))
+        for i in range(n_ch):
+            arr[i].sig_in_c64 = None if sig_ptrs is None else int(sig_ptrs[i])
+            arr[i].stream_offset = 0 if stream_offsets is None else int(stream_offsets[i])
+            arr[i].n_samples = int(ns[i])
+            arr[i].rem_carr_phase_rad = float(rc[i])
+            arr[i].carr_step_rad = float(cs[i])
+            arr[i].carr_rate_rad = float(cr[i])
+            arr[i].rem_code_phase_chips = float(rk[i])
+            arr[i].code_step_chips = float(ks[i])
+            arr[i].code_rate_chips = float(kr[i])
+        return arr
+
+    def correlate_batch(self, channels, args, shifts, flags=0):
+        channels = _u32a(channels)
+        shifts = np.ascontiguousarray(shifts, dtype=np.float32).reshape(channels.size, -1)
+        n_taps = shifts.shape[1]
+        out = np.zeros((channels.size, n_taps), dtype=np.complex64)
+        _check(self.L.gnss_b200_mc_correlate_batch(self.h, channels.size, channels.ctypes.data_as(_u32p), args, _f32p(shifts),
+                                                   n_taps, flags, _f32p(out.view(np.float32))))
+        return out
+
+    def correlate_device_async(self, channels, args, shifts, d_sig_ptr, ch_stride_samples, flags=0):
+        channels = _u32a(channels)
+        shifts = np.ascontiguousarray(shifts, dtype=np.float32).reshape(channels.size, -1)
+        _check(self.L.gnss_b200_mc_correlate_device_async(self.h, channels.size, channels.ctypes.data_as(_u32p), args, _f32p(shifts),
+                                                          shifts.shape[1], flags, C.c_void_p(d_sig_ptr), ch_stride_samples))
+
+    def sync(self, n_ch, n_taps):
+        out = np.zeros((n_ch, n_taps), dtype=np.complex64)
+        _check(self.L.gnss_b200_mc_sync(self.h, n_ch, n_taps, _f32p(out.view(np.float32))))
+        return out
+
+    def chip_indices(self, ch, args_one, shifts, flags=0):
+        shifts = np.ascontiguousarray(shifts, dtype=np.float32)
+        n = args_one[0].n_samples
+        out = np.zeros((shifts.size, n), dtype=np.int32)
+        _check(self.L.gnss_b200_mc_chip_indices(self.h, ch, args_one, _f32p(shifts), shifts.size, flags, out.ctypes.data_as(C.POINTER(c_i32))))
+        return out
+
+    def stream(self):
+        return self.L.gnss_b200_mc_stream(self.h)
+
+    def launch_count(self):
+        return int(self.L.gnss_b200_mc_launch_count(self.h))

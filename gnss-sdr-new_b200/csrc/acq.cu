@@ -1,0 +1,613 @@
+// Host side of the PCPS acquisition engine: handle, buffers, launch sequencing, C-ABI.
+// Reference for every entry point: include/gnss_b200.h.
+#include "acq_kernels.cuh"
+#include "wipeoff_pieces.h"
+#include <algorithm>
+#include <cmath>
+#include <map>
+#include <vector>
+
+using namespace b200;
+
+namespace
+{
+constexpr uint32_t kMaxSingleStagePoints = 24576;  // 192 KiB of complex64 in one CTA's shared memory
+constexpr size_t kScratchBudgetBytes = 48ull << 20;  // two-stage intermediate kept L2-resident by chunking rows
+constexpr uint32_t kMaxCachedGroups = 64;
+
+struct CallMeta  // uploaded once per dwell call
+{
+    std::vector<uint32_t> slots, slot_group, dwell_after, group_piece_base;
+    std::vector<int32_t> center;
+};
+}  // namespace
+
+struct gnss_b200_acq
+{
+    std::mutex mu;
+    gnss_b200_acq_cfg cfg{};
+    uint32_t N = 0, consumed = 0, eff = 0, nD = 0, nD_local = 0, row_begin = 0;
+    uint32_t code_len = 0, code_off = 0, mag_offset = 0;
+    FftPlan plan;
+    cudaStream_t stream = nullptr;
+    uint64_t launches = 0;
+
+    DevBuf d_W, d_cbuf, d_xbuf, d_samples, d_codes_td, d_scratch;
+    DevBuf d_pieces, d_npieces;  // per cached group: nD_local tables
+    std::map<int64_t, uint32_t> group_cache;  // (center + bias) -> cached group ordinal
+    DevBuf d_meta;
+    PinBuf h_meta;
+    DevBuf d_partials, d_partials2, d_rows, d_results, d_bestk, d_grid, d_rowbuf;
+    PinBuf h_results, h_samples;
+
+    std::vector<int32_t> center, bias;
+    std::vector<uint8_t> has_code;
+    std::vector<uint32_t> dwell;
+    uint32_t last_n_slots = 0;
+};
+
+namespace
+{
+template <int LOAD, int STORE, bool INV>
+int launch_stage(gnss_b200_acq* h, const StageArgs& a, uint32_t n_transforms)
+{
+    if (n_transforms == 0) return GNSS_B200_OK;
+    const size_t smem = (size_t)a.st.tile_points * sizeof(float2);
+    static thread_local size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured)
+        {
+            B200_CUDA(cudaFuncSetAttribute(stage_kernel<LOAD, STORE, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            configured = 227 * 1024;
+        }
+    const dim3 grid(n_transforms, a.st.tiles);
+    stage_kernel<LOAD, STORE, INV><<<grid, a.st.threads, smem, h->stream>>>(a);
+    h->launches++;
+    B200_CUDA(cudaGetLastError());
+    return GNSS_B200_OK;
+}
+
+StageArgs base_args(const gnss_b200_acq* h, int stage)
+{
+    StageArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.st = h->plan.stage[stage];
+    a.W = h->d_W.as<float2>();
+    a.N = h->N;
+    a.nD_local = h->nD_local;
+    a.eff = h->eff;
+    a.mag_offset = h->mag_offset;
+    a.consumed = h->consumed;
+    return a;
+}
+
+// Forward transform of `n` zero-padded local codes (time domain in d_codes_td) into conj spectra at cbuf[slots[i]].
+int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
+{
+    if (h->plan.n_stages == 1)
+        {
+            StageArgs a = base_args(h, 0);
+            a.codes_td = h->d_codes_td.as<float2>();
+            a.code_len = h->code_len;
+            a.code_off = h->code_off;
+            a.slots = d_slots;
+            a.out_buf = h->d_cbuf.as<float2>();
+            a.out_by_slot = 1;
+            return launch_stage<LOAD_CODE, STORE_CONJ, false>(h, a, n);
+        }
+    // two stages through the scratch buffer, in chunks that fit it
+    const uint32_t chunk = (uint32_t)std::max<size_t>(1, h->d_scratch.cap / ((size_t)h->N * 8));
+    for (uint32_t y0 = 0; y0 < n; y0 += chunk)
+        {
+            const uint32_t cnt = std::min(chunk, n - y0);
+            StageArgs a = base_args(h, 0);
+            a.codes_td = h->d_codes_td.as<float2>();
+            a.code_len = h->code_len;
+            a.code_off = h->code_off;
+            a.y0 = y0;
+            a.out_buf = h->d_scratch.as<float2>();
+            a.out_y0 = y0;
+            int rc = launch_stage<LOAD_CODE, STORE_BUF, false>(h, a, cnt);
+            if (rc) return rc;
+            StageArgs b = base_args(h, 1);
+            b.in_buf = h->d_scratch.as<float2>();
+            b.in_y0 = y0;
+            b.y0 = y0;
+            b.slots = d_slots;
+            b.out_buf = h->d_cbuf.as<float2>();
+            b.out_by_slot = 1;
+            rc = launch_stage<LOAD_BUF, STORE_CONJ, false>(h, b, cnt);
+            if (rc) return rc;
+        }
+    return GNSS_B200_OK;
+}
+
+int ensure_group(gnss_b200_acq* h, int64_t key, uint32_t* ordinal)
+{
+    auto it = h->group_cache.find(key);
+    if (it != h->group_cache.end())
+        {
+            *ordinal = it->second;
+            return GNSS_B200_OK;
+        }
+    if (h->group_cache.size() >= kMaxCachedGroups) h->group_cache.clear();
+    const uint32_t ord = (uint32_t)h->group_cache.size();
+    // host: one piece table per local Doppler bin (the reference's update_grid_doppler_wipeoffs, :298-305)
+    std::vector<WipePiece> tab((size_t)h->nD_local * kMaxPieces);
+    std::vector<uint32_t> cnt(h->nD_local);
+    std::vector<WipePieceHost> pc;
+    for (uint32_t kk = 0; kk < h->nD_local; kk++)
+        {
+            const uint32_t k = h->row_begin + kk;
+            const int32_t doppler = -h->cfg.doppler_max + (int32_t)(h->cfg.doppler_step * k);  // + center + bias = key
+            const float inc = wipeoff_phase_inc((int32_t)(key + doppler), h->cfg.fs);
+            build_wipeoff_pieces(inc, h->N, &pc);
+            B200_REQUIRE(pc.size() <= (size_t)kMaxPieces, GNSS_B200_ERR_UNSUPPORTED, "carrier phase table needs %zu pieces (> %d)", pc.size(), kMaxPieces);
+            cnt[kk] = (uint32_t)pc.size();
+            for (size_t i = 0; i < pc.size(); i++) tab[(size_t)kk * kMaxPieces + i] = WipePiece{pc[i].start, pc[i].phi0, pc[i].step};
+        }
+    const size_t tb = sizeof(WipePiece) * tab.size(), cb = sizeof(uint32_t) * cnt.size();
+    B200_CUDA(cudaStreamSynchronize(h->stream));
+    B200_CUDA(cudaMemcpy(h->d_pieces.as<char>() + (size_t)ord * tb, tab.data(), tb, cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(h->d_npieces.as<char>() + (size_t)ord * cb, cnt.data(), cb, cudaMemcpyHostToDevice));
+    h->group_cache[key] = ord;
+    *ordinal = ord;
+    return GNSS_B200_OK;
+}
+
+// Everything of one dwell after the samples are on the device.
+int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32_t n_slots, const uint32_t* slots)
+{
+    B200_REQUIRE(n_slots > 0 && n_slots <= h->cfg.max_slots, GNSS_B200_ERR_INVALID, "dwell: n_slots=%u out of range", n_slots);
+    // ---- per-call metadata: slots, Doppler groups, dwell counters ----
+    CallMeta m;
+    std::vector<int64_t> call_keys;
+    for (uint32_t i = 0; i < n_slots; i++)
+        {
+            const uint32_t s = slots[i];
+            B200_REQUIRE(s < h->cfg.max_slots, GNSS_B200_ERR_INVALID, "dwell: slot %u out of range", s);
+            B200_REQUIRE(h->has_code[s], GNSS_B200_ERR_STATE, "dwell: slot %u has no local code (call gnss_b200_acq_set_local_code)", s);
+            const int64_t key = (int64_t)h->center[s] + (int64_t)h->bias[s];
+            uint32_t g = 0;
+            for (; g < call_keys.size(); g++)
+                if (call_keys[g] == key) break;
+            if (g == call_keys.size()) call_keys.push_back(key);
+            m.slots.push_back(s);
+            m.slot_group.push_back(g);
+            m.center.push_back(h->center[s]);
+        }
+    B200_REQUIRE(call_keys.size() <= kMaxCachedGroups, GNSS_B200_ERR_UNSUPPORTED, "dwell: more than %u distinct Doppler centres in one call", kMaxCachedGroups);
+    for (int64_t key : call_keys)
+        {
+            if (h->group_cache.size() >= kMaxCachedGroups && !h->group_cache.count(key)) h->group_cache.clear();
+        }
+    for (int64_t key : call_keys)
+        {
+            uint32_t ord;
+            int rc = ensure_group(h, key, &ord);
+            if (rc) return rc;
+            m.group_piece_base.push_back(ord * h->nD_local);
+        }
+    for (uint32_t i = 0; i < n_slots; i++) m.dwell_after.push_back(++h->dwell[slots[i]]);  // :638
+    const uint32_t n_groups = (uint32_t)call_keys.size();
+
+    const size_t meta_words = (size_t)n_slots * 4 + n_groups;
+    B200_CUDA(h->h_meta.reserve(meta_words * 4));
+    B200_CUDA(h->d_meta.reserve(meta_words * 4));
+    uint32_t* hm = h->h_meta.as<uint32_t>();
+    std::memcpy(hm, m.slots.data(), n_slots * 4);
+    std::memcpy(hm + n_slots, m.slot_group.data(), n_slots * 4);
+    std::memcpy(hm + 2 * n_slots, m.dwell_after.data(), n_slots * 4);
+    std::memcpy(hm + 3 * n_slots, m.center.data(), n_slots * 4);
+    std::memcpy(hm + 4 * n_slots, m.group_piece_base.data(), n_groups * 4);
+    B200_CUDA(cudaMemcpyAsync(h->d_meta.p, hm, meta_words * 4, cudaMemcpyHostToDevice, h->stream));
+    const uint32_t* d_slots = h->d_meta.as<uint32_t>();
+    const uint32_t* d_slot_group = d_slots + n_slots;
+    const uint32_t* d_dwell = d_slots + 2 * n_slots;
+    const int32_t* d_center = reinterpret_cast<const int32_t*>(d_slots + 3 * n_slots);
+    const uint32_t* d_gpb = d_slots + 4 * n_slots;
+
+    const uint32_t n_fwd = n_groups * h->nD_local;
+    const uint32_t n_rows = n_slots * h->nD_local;
+    const uint32_t tiles_last = h->plan.stage[0].tiles;  // the inverse always ends with stage[0]
+    B200_CUDA(h->d_xbuf.reserve((size_t)n_fwd * h->N * 8));
+    B200_CUDA(h->d_partials.reserve(sizeof(RowPartial) * (size_t)n_rows * tiles_last));
+    B200_CUDA(h->d_results.reserve(sizeof(gnss_b200_acq_result) * n_slots));
+    B200_CUDA(h->h_results.reserve(sizeof(gnss_b200_acq_result) * n_slots));
+    B200_CUDA(h->d_bestk.reserve(sizeof(uint32_t) * n_slots));
+
+    // ---- forward: one transform per (Doppler group, bin) ----
+    {
+        StageArgs a = base_args(h, 0);
+        a.samples = d_samples;
+        a.is_cshort = is_cshort;
+        a.pieces = h->d_pieces.as<WipePiece>();
+        a.n_pieces = h->d_npieces.as<uint32_t>();
+        a.group_piece_base = d_gpb;
+        a.out_buf = h->d_xbuf.as<float2>();
+        int rc = launch_stage<LOAD_SAMPLES, STORE_BUF, false>(h, a, n_fwd);
+        if (rc) return rc;
+        if (h->plan.n_stages == 2)
+            {
+                StageArgs b = base_args(h, 1);
+                b.in_buf = h->d_xbuf.as<float2>();
+                b.out_buf = h->d_xbuf.as<float2>();
+                rc = launch_stage<LOAD_BUF, STORE_BUF, false>(h, b, n_fwd);
+                if (rc) return rc;
+            }
+    }
+
+    // ---- inverse: one row per (slot, bin) ----
+    auto inverse = [&](uint32_t rows, const uint32_t* k_override, float* mag_base, uint32_t mag_is_rowbuf, RowPartial* partials) -> int {
+        if (h->plan.n_stages == 1)
+            {
+                StageArgs a = base_args(h, 0);
+                a.in_buf = h->d_xbuf.as<float2>();
+                a.cbuf = h->d_cbuf.as<float2>();
+                a.slots = d_slots;
+                a.slot_group = d_slot_group;
+                a.k_override = k_override;
+                a.mag_base = mag_base;
+                a.mag_is_rowbuf = mag_is_rowbuf;
+                a.dwell_after = d_dwell;
+                a.partials = partials;
+                return launch_stage<LOAD_PRODUCT, STORE_MAG, true>(h, a, rows);
+            }
+        const uint32_t chunk = (uint32_t)std::max<size_t>(1, h->d_scratch.cap / ((size_t)h->N * 8));
+        for (uint32_t y0 = 0; y0 < rows; y0 += chunk)
+            {
+                const uint32_t cnt = std::min(chunk, rows - y0);
+                StageArgs a = base_args(h, 1);  // inverse order: lowest stage first
+                a.in_buf = h->d_xbuf.as<float2>();
+                a.cbuf = h->d_cbuf.as<float2>();
+                a.slots = d_slots;
+                a.slot_group = d_slot_group;
+                a.k_override = k_override;
+                a.y0 = y0;
+                a.out_buf = h->d_scratch.as<float2>();
+                a.out_y0 = y0;
+                int rc = launch_stage<LOAD_PRODUCT, STORE_BUF, true>(h, a, cnt);
+                if (rc) return rc;
+                StageArgs b = base_args(h, 0);
+                b.in_buf = h->d_scratch.as<float2>();
+                b.in_y0 = y0;
+                b.y0 = y0;
+                b.slots = d_slots;
+                b.slot_group = d_slot_group;
+                b.k_override = k_override;
+                b.mag_base = mag_base;
+                b.mag_is_rowbuf = mag_is_rowbuf;
+                b.dwell_after = d_dwell;
+                b.partials = partials;
+                rc = launch_stage<LOAD_BUF, STORE_MAG, true>(h, b, cnt);
+                if (rc) return rc;
+            }
+        return GNSS_B200_OK;
+    };
+    int rc = inverse(n_rows, nullptr, h->cfg.keep_grid ? h->d_grid.as<float>() : nullptr, 0, h->d_partials.as<RowPartial>());
+    if (rc) return rc;
+
+    // ---- decision ----
+    FinalizeArgs f;
+    f.partials = h->d_partials.as<RowPartial>();
+    f.tiles = tiles_last;
+    f.nD = h->nD;
+    f.nD_local = h->nD_local;
+    f.row_begin = h->row_begin;
+    f.eff = h->eff;
+    f.doppler_max = h->cfg.doppler_max;
+    f.doppler_step = h->cfg.doppler_step;
+    f.use_cfar = h->cfg.use_cfar;
+    f.slots = d_slots;
+    f.center = d_center;
+    f.dwell_after = d_dwell;
+    f.rows = h->d_rows.as<gnss_b200_acq_row>();
+    f.results = h->d_results.as<gnss_b200_acq_result>();
+    f.best_k_local = h->d_bestk.as<uint32_t>();
+    finalize_kernel<<<n_slots, 32, 0, h->stream>>>(f);
+    h->launches++;
+    B200_CUDA(cudaGetLastError());
+
+    if (!h->cfg.use_cfar)
+        {
+            SecondPeakArgs sp;
+            sp.nD_local = h->nD_local;
+            sp.eff = h->eff;
+            sp.N = h->N;
+            sp.samples_per_chip = h->cfg.samples_per_chip;
+            sp.slots = d_slots;
+            sp.best_k_local = h->d_bestk.as<uint32_t>();
+            sp.results = h->d_results.as<gnss_b200_acq_result>();
+            if (h->cfg.keep_grid)
+                {
+                    sp.mag_base = h->d_grid.as<float>();
+                    sp.is_rowbuf = 0;
+                }
+            else
+                {
+                    // the grid was never materialised: recompute the winning row of every slot into a row buffer
+                    B200_CUDA(h->d_rowbuf.reserve(sizeof(float) * (size_t)n_slots * h->eff));
+                    B200_CUDA(h->d_partials2.reserve(sizeof(RowPartial) * (size_t)n_slots * tiles_last));
+                    rc = inverse(n_slots, h->d_bestk.as<uint32_t>(), h->d_rowbuf.as<float>(), 1, h->d_partials2.as<RowPartial>());
+                    if (rc) return rc;
+                    sp.mag_base = h->d_rowbuf.as<float>();
+                    sp.is_rowbuf = 1;
+                }
+            second_peak_kernel<<<n_slots, 256, 0, h->stream>>>(sp);
+            h->launches++;
+            B200_CUDA(cudaGetLastError());
+        }
+    B200_CUDA(cudaMemcpyAsync(h->h_results.p, h->d_results.p, sizeof(gnss_b200_acq_result) * n_slots, cudaMemcpyDeviceToHost, h->stream));
+    h->last_n_slots = n_slots;
+    return GNSS_B200_OK;
+}
+}  // namespace
+
+extern "C"
+{
+    int gnss_b200_acq_create(const gnss_b200_acq_cfg* cfg, gnss_b200_acq** out)
+    {
+        B200_REQUIRE(cfg && out, GNSS_B200_ERR_INVALID, "acq_create: null argument");
+        B200_REQUIRE(cfg->fft_size >= 2 && cfg->consumed_samples >= 1 && cfg->consumed_samples <= cfg->fft_size, GNSS_B200_ERR_INVALID,
+            "acq_create: fft_size=%u consumed_samples=%u", cfg->fft_size, cfg->consumed_samples);
+        B200_REQUIRE(cfg->doppler_step > 0 && cfg->doppler_max > 0 && cfg->fs > 0 && cfg->max_slots > 0, GNSS_B200_ERR_INVALID, "acq_create: bad Doppler grid / fs / max_slots");
+        B200_REQUIRE(!cfg->bit_transition || cfg->fft_size % 2 == 0, GNSS_B200_ERR_INVALID, "acq_create: bit_transition needs an even fft_size");
+        int rc = select_device(cfg->device);
+        if (rc) return rc;
+        auto* h = new gnss_b200_acq();
+        h->cfg = *cfg;
+        h->N = cfg->fft_size;
+        h->consumed = cfg->consumed_samples;
+        h->eff = cfg->bit_transition ? h->N / 2 : h->N;                                   // :622
+        h->mag_offset = cfg->bit_transition ? h->eff : 0;                                 // :671
+        h->nD = (uint32_t)std::ceil((double)(cfg->doppler_max - (-cfg->doppler_max)) / (double)cfg->doppler_step);  // :264
+        h->row_begin = 0;
+        h->nD_local = h->nD;
+        if (cfg->row_end > cfg->row_begin)
+            {
+                if (cfg->row_end > h->nD)
+                    {
+                        delete h;
+                        return fail(GNSS_B200_ERR_INVALID, "acq_create: row range [%u,%u) exceeds %u Doppler bins", cfg->row_begin, cfg->row_end, h->nD);
+                    }
+                h->row_begin = cfg->row_begin;
+                h->nD_local = cfg->row_end - cfg->row_begin;
+            }
+        // set_local_code zero-pad layout (:188-205)
+        h->code_len = cfg->bit_transition ? h->N / 2 : h->consumed;
+        h->code_off = h->N - h->code_len;
+        if (!cfg->bit_transition && h->N == h->consumed) h->code_off = 0;
+        const char* why = nullptr;
+        if (!make_fft_plan(h->N, kMaxSingleStagePoints, &h->plan, &why))
+            {
+                delete h;
+                return fail(GNSS_B200_ERR_UNSUPPORTED, "acq_create: fft_size %u: %s", cfg->fft_size, why ? why : "unsupported");
+            }
+        h->center.assign(cfg->max_slots, 0);
+        h->bias.assign(cfg->max_slots, 0);
+        h->has_code.assign(cfg->max_slots, 0);
+        h->dwell.assign(cfg->max_slots, 0);
+        cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+        // twiddle table exp(-2 pi i k / N), computed in double and rounded once
+        std::vector<float2> W(h->N);
+        for (uint32_t k = 0; k < h->N; k++)
+            {
+                const long double ang = -2.0L * 3.14159265358979323846264338327950288L * (long double)k / (long double)h->N;
+                W[k] = make_float2((float)cosl(ang), (float)sinl(ang));
+            }
+        if (e == cudaSuccess) e = h->d_W.reserve((size_t)h->N * 8);
+        if (e == cudaSuccess) e = cudaMemcpy(h->d_W.p, W.data(), (size_t)h->N * 8, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = h->d_cbuf.reserve((size_t)cfg->max_slots * h->N * 8);
+        if (e == cudaSuccess) e = h->d_samples.reserve((size_t)h->consumed * 8);
+        if (e == cudaSuccess) e = h->h_samples.reserve((size_t)h->consumed * 8);
+        if (e == cudaSuccess) e = h->d_rows.reserve(sizeof(gnss_b200_acq_row) * (size_t)cfg->max_slots * h->nD);
+        if (e == cudaSuccess) e = cudaMemset(h->d_rows.p, 0, sizeof(gnss_b200_acq_row) * (size_t)cfg->max_slots * h->nD);
+        if (e == cudaSuccess) e = h->d_pieces.reserve(sizeof(WipePiece) * (size_t)kMaxCachedGroups * h->nD_local * kMaxPieces);
+        if (e == cudaSuccess) e = h->d_npieces.reserve(sizeof(uint32_t) * (size_t)kMaxCachedGroups * h->nD_local);
+        if (e == cudaSuccess && h->plan.n_stages == 2)
+            {
+                const size_t rows = std::max<size_t>(1, kScratchBudgetBytes / ((size_t)h->N * 8));
+                e = h->d_scratch.reserve(rows * h->N * 8);
+            }
+        if (e == cudaSuccess && cfg->keep_grid)
+            {
+                const size_t bytes = sizeof(float) * (size_t)cfg->max_slots * h->nD_local * h->eff;
+                e = h->d_grid.reserve(bytes);
+                if (e == cudaSuccess) e = cudaMemset(h->d_grid.p, 0, bytes);
+            }
+        if (e != cudaSuccess)
+            {
+                gnss_b200_acq_destroy(h);
+                return fail(GNSS_B200_ERR_CUDA, "acq_create: %s", cudaGetErrorString(e));
+            }
+        *out = h;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_destroy(gnss_b200_acq* h)
+    {
+        if (!h) return GNSS_B200_OK;
+        cudaSetDevice(h->cfg.device);
+        if (h->stream) cudaStreamSynchronize(h->stream);
+        for (DevBuf* b : {&h->d_W, &h->d_cbuf, &h->d_xbuf, &h->d_samples, &h->d_codes_td, &h->d_scratch, &h->d_pieces, &h->d_npieces, &h->d_meta,
+                 &h->d_partials, &h->d_partials2, &h->d_rows, &h->d_results, &h->d_bestk, &h->d_grid, &h->d_rowbuf})
+            b->release();
+        h->h_meta.release();
+        h->h_results.release();
+        h->h_samples.release();
+        if (h->stream) cudaStreamDestroy(h->stream);
+        delete h;
+        return GNSS_B200_OK;
+    }
+
+    uint32_t gnss_b200_acq_num_doppler_bins(const gnss_b200_acq* h) { return h ? h->nD : 0; }
+
+    int gnss_b200_acq_set_local_codes(gnss_b200_acq* h, uint32_t n_slots, const uint32_t* slots, const float* codes_c64)
+    {
+        B200_REQUIRE(h && slots && codes_c64 && n_slots > 0, GNSS_B200_ERR_INVALID, "acq_set_local_codes: bad arguments");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        for (uint32_t i = 0; i < n_slots; i++) B200_REQUIRE(slots[i] < h->cfg.max_slots, GNSS_B200_ERR_INVALID, "acq_set_local_codes: slot %u out of range", slots[i]);
+        // the adapter's buffer holds consumed_samples items per code; the reference reads code_len of them (:192,:198,:203)
+        const size_t in_stride = h->consumed;
+        B200_CUDA(h->d_codes_td.reserve((size_t)n_slots * h->code_len * 8 + (size_t)n_slots * 4));
+        B200_CUDA(cudaMemcpy2DAsync(h->d_codes_td.p, (size_t)h->code_len * 8, codes_c64, in_stride * 8, (size_t)h->code_len * 8, n_slots, cudaMemcpyHostToDevice, h->stream));
+        uint32_t* d_slots = reinterpret_cast<uint32_t*>(h->d_codes_td.as<char>() + (size_t)n_slots * h->code_len * 8);
+        B200_CUDA(cudaMemcpyAsync(d_slots, slots, (size_t)n_slots * 4, cudaMemcpyHostToDevice, h->stream));
+        int rc = run_code_forward(h, n_slots, d_slots);
+        if (rc) return rc;
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        for (uint32_t i = 0; i < n_slots; i++) h->has_code[slots[i]] = 1;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_set_local_code(gnss_b200_acq* h, uint32_t slot, const float* code_c64)
+    {
+        return gnss_b200_acq_set_local_codes(h, 1, &slot, code_c64);
+    }
+
+    int gnss_b200_acq_set_doppler_center(gnss_b200_acq* h, uint32_t slot, int32_t center_hz, int32_t bias_hz)
+    {
+        B200_REQUIRE(h && slot < h->cfg.max_slots, GNSS_B200_ERR_INVALID, "acq_set_doppler_center: bad slot");
+        std::lock_guard<std::mutex> lk(h->mu);
+        h->center[slot] = center_hz;
+        h->bias[slot] = bias_hz;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_reset(gnss_b200_acq* h, uint32_t slot)
+    {
+        B200_REQUIRE(h && slot < h->cfg.max_slots, GNSS_B200_ERR_INVALID, "acq_reset: bad slot");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        h->dwell[slot] = 0;
+        if (h->cfg.keep_grid)
+            {
+                const size_t n = (size_t)h->nD_local * h->eff;
+                B200_CUDA(cudaMemsetAsync(h->d_grid.as<float>() + (size_t)slot * n, 0, n * sizeof(float), h->stream));
+            }
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_dwell(gnss_b200_acq* h, const void* samples, int is_cshort, uint32_t n_slots, const uint32_t* slots, gnss_b200_acq_result* results)
+    {
+        B200_REQUIRE(h && samples && slots && results, GNSS_B200_ERR_INVALID, "acq_dwell: null argument");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        const size_t bytes = (size_t)h->consumed * (is_cshort ? 4 : 8);
+        B200_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, bytes, cudaMemcpyHostToDevice, h->stream));
+        int rc = enqueue_dwell(h, h->d_samples.p, is_cshort, n_slots, slots);
+        if (rc) return rc;
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        std::memcpy(results, h->h_results.p, sizeof(gnss_b200_acq_result) * n_slots);
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_dwell_device_async(gnss_b200_acq* h, const void* d_samples, uint32_t n_slots, const uint32_t* slots)
+    {
+        B200_REQUIRE(h && d_samples && slots, GNSS_B200_ERR_INVALID, "acq_dwell_device_async: null argument");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        return enqueue_dwell(h, d_samples, 0, n_slots, slots);
+    }
+
+    int gnss_b200_acq_sync(gnss_b200_acq* h, uint32_t n_slots, gnss_b200_acq_result* results)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_sync: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        if (results)
+            {
+                B200_REQUIRE(n_slots == h->last_n_slots, GNSS_B200_ERR_INVALID, "acq_sync: n_slots differs from the last dwell");
+                std::memcpy(results, h->h_results.p, sizeof(gnss_b200_acq_result) * n_slots);
+            }
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_read_grid(gnss_b200_acq* h, uint32_t slot, float* out)
+    {
+        B200_REQUIRE(h && out && slot < h->cfg.max_slots, GNSS_B200_ERR_INVALID, "acq_read_grid: bad arguments");
+        B200_REQUIRE(h->cfg.keep_grid, GNSS_B200_ERR_STATE, "acq_read_grid: handle was created with keep_grid = 0");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        const size_t n = (size_t)h->nD_local * h->eff;
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        B200_CUDA(cudaMemcpy(out, h->d_grid.as<float>() + (size_t)slot * n, n * sizeof(float), cudaMemcpyDeviceToHost));
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_read_rows(gnss_b200_acq* h, uint32_t slot, gnss_b200_acq_row* rows)
+    {
+        B200_REQUIRE(h && rows && slot < h->cfg.max_slots, GNSS_B200_ERR_INVALID, "acq_read_rows: bad arguments");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        B200_CUDA(cudaMemcpy(rows, h->d_rows.as<gnss_b200_acq_row>() + (size_t)slot * h->nD, sizeof(gnss_b200_acq_row) * h->nD, cudaMemcpyDeviceToHost));
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_finalize_rows(const gnss_b200_acq_row* rows, uint32_t n_doppler, uint32_t effective_size, int32_t doppler_max,
+        uint32_t doppler_step, int32_t doppler_center, uint32_t dwell_count, gnss_b200_acq_result* out)
+    {
+        B200_REQUIRE(rows && out && n_doppler > 0 && effective_size > 0 && dwell_count > 0, GNSS_B200_ERR_INVALID, "acq_finalize_rows: bad arguments");
+        float best = 0.f;
+        uint32_t bk = 0, bi = 0;
+        for (uint32_t k = 0; k < n_doppler; k++)
+            {
+                B200_REQUIRE(rows[k].valid, GNSS_B200_ERR_STATE, "acq_finalize_rows: row %u missing (merge all shards first)", k);
+                if (rows[k].max_val > best)  // :523
+                    {
+                        best = rows[k].max_val;
+                        bk = k;
+                        bi = rows[k].max_idx;
+                    }
+            }
+        const uint32_t opp = (bk + n_doppler / 2) % n_doppler;
+        const float per = rows[opp].row_sum / (float)(int32_t)effective_size;
+        out->input_power = (float)(((double)per / 2.0) / (double)dwell_count);
+        out->peak = best;
+        out->code_phase = bi;
+        out->doppler_index = bk;
+        out->doppler_hz = -doppler_max + doppler_center + (int32_t)doppler_step * (int32_t)bk;
+        out->second_peak = 0.f;
+        out->test_statistic = best / out->input_power;
+        out->dwell_count = dwell_count;
+        return GNSS_B200_OK;
+    }
+
+    // parity aids (pure host): the reference's binary32 running-sum wipe-off phase, and the FFT plan
+    int gnss_b200_debug_wipeoff_phase(int32_t doppler_hz_with_bias, double fs, uint32_t n, float* phase_out, uint32_t* n_pieces)
+    {
+        B200_REQUIRE(phase_out && n > 0, GNSS_B200_ERR_INVALID, "debug_wipeoff_phase: bad arguments");
+        std::vector<WipePieceHost> pc;
+        build_wipeoff_pieces(wipeoff_phase_inc(doppler_hz_with_bias, fs), n, &pc);
+        size_t cur = 0;
+        for (uint32_t i = 0; i < n; i++)
+            {
+                while (cur + 1 < pc.size() && i >= pc[cur + 1].start) cur++;
+                phase_out[i] = std::fmaf((float)(i - pc[cur].start), pc[cur].step, pc[cur].phi0);
+            }
+        if (n_pieces) *n_pieces = (uint32_t)pc.size();
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_debug_fft_plan(uint32_t n, uint32_t* n_stages, uint32_t* radices, uint32_t* n_radices, uint32_t* perm)
+    {
+        FftPlan plan;
+        const char* why = nullptr;
+        if (!make_fft_plan(n, kMaxSingleStagePoints, &plan, &why)) return fail(GNSS_B200_ERR_UNSUPPORTED, "fft plan %u: %s", n, why ? why : "?");
+        if (n_stages) *n_stages = plan.n_stages;
+        if (n_radices) *n_radices = (uint32_t)plan.radices.size();
+        if (radices)
+            for (size_t i = 0; i < plan.radices.size(); i++) radices[i] = plan.radices[i];
+        if (perm)
+            {
+                const std::vector<uint32_t> p = fft_plan_permutation(plan);
+                std::memcpy(perm, p.data(), sizeof(uint32_t) * n);
+            }
+        return GNSS_B200_OK;
+    }
+
+    void* gnss_b200_acq_stream(gnss_b200_acq* h) { return h ? (void*)h->stream : nullptr; }
+    uint64_t gnss_b200_acq_launch_count(const gnss_b200_acq* h) { return h ? h->launches : 0; }
+}

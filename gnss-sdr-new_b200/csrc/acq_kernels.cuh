@@ -1,0 +1,447 @@
+// Device side of the PCPS acquisition pipeline (sm_100a).
+//
+// One templated "stage kernel" runs one shared-memory FFT stage of the plan with a fused prologue and
+// epilogue, so that the Doppler-grid loop of pcps_acquisition::acquisition_core
+// (reference: src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.cc:655-686) becomes
+//
+//   forward  (once per Doppler bin, shared by every PRN of the batch):
+//       load samples -> x[n] * wipeoff_k[n] (:658) -> zero pad (:628-634) -> FFT (:662) -> X_k (scrambled order)
+//   inverse  (once per (PRN, Doppler bin) row):
+//       X_k * conj-code-spectrum (:665) -> IFFT (:668) -> |.|^2 (+ non-coherent accumulation) (:672-680)
+//       -> per-row {max, argmax, sum} (what :520-529 and :534 consume)
+//
+// The code spectra themselves (set_local_code, :176-209) go through the same forward stages with the
+// zero-pad layout as prologue and the conjugation (:208) as epilogue.
+#pragma once
+#include "common.cuh"
+#include "fft_smem.cuh"
+
+namespace b200
+{
+// Piecewise-linear description of the reference's binary32 running-sum phase (see wipeoff_pieces.cc):
+// for start <= n < next.start the reference's _phase at sample n is exactly phi0 + (n - start) * step.
+struct WipePiece
+{
+    uint32_t start;
+    float phi0;
+    float step;
+};
+constexpr int kMaxPieces = 64;
+
+struct RowPartial
+{
+    float max_val;
+    uint32_t max_idx;
+    float sum;
+    uint32_t pad;
+};
+
+enum
+{
+    LOAD_SAMPLES = 0,  // samples * carrier wipe-off, zero padded
+    LOAD_CODE = 1,     // time-domain local code in its zero-pad layout
+    LOAD_BUF = 2,      // plain buffer [transform][N]
+    LOAD_PRODUCT = 3   // X_k[pos] * C_prn[pos]
+};
+enum
+{
+    STORE_BUF = 0,
+    STORE_CONJ = 1,
+    STORE_MAG = 2
+};
+
+struct StageArgs
+{
+    FftStage st;
+    const float2* W;
+    uint32_t N;
+    // ---- LOAD_SAMPLES ----
+    const void* samples;
+    uint32_t is_cshort;
+    uint32_t consumed;
+    const WipePiece* pieces;   // [group][nD_local][kMaxPieces]
+    const uint32_t* n_pieces;  // [group][nD_local]
+    const uint32_t* group_piece_base;  // [call group] -> index of its first bin in pieces / n_pieces
+    uint32_t nD_local;
+    // ---- LOAD_CODE ----
+    const float2* codes_td;  // [transform][code_len]
+    uint32_t code_len;
+    uint32_t code_off;       // first position of the code inside the padded buffer
+    // ---- LOAD_BUF / LOAD_PRODUCT ----
+    const float2* in_buf;    // LOAD_BUF: [transform - in_y0][N]; LOAD_PRODUCT: X [call group][nD_local][N]
+    const float2* cbuf;      // code spectra [slot][N]
+    uint32_t in_y0;
+    // ---- row mapping of the inverse kernels: y -> (slot, Doppler bin) ----
+    const uint32_t* slots;       // [n_slots in call]
+    const uint32_t* slot_group;  // [n_slots in call] -> call group
+    const uint32_t* k_override;  // null, or [n_slots]: the single LOCAL bin to (re)compute per slot
+    uint32_t y0;                 // first row of this launch
+    // ---- STORE_BUF / STORE_CONJ ----
+    float2* out_buf;             // [transform - out_y0][N] (STORE_CONJ: [slots[transform]][N])
+    uint32_t out_y0;
+    uint32_t out_by_slot;
+    // ---- STORE_MAG ----
+    float* mag_base;             // grid [slot][nD_local][eff], or row buffer [si][eff], or null
+    uint32_t mag_is_rowbuf;
+    uint32_t eff;
+    uint32_t mag_offset;         // first IFFT output that belongs to the row (N/2 with bit_transition, :671)
+    const uint32_t* dwell_after; // [n_slots in call] dwell counter including this dwell
+    RowPartial* partials;        // [y][tiles], y = global row of the call (not chunk-relative)
+};
+
+__device__ __forceinline__ void row_of(const StageArgs& a, uint32_t y, uint32_t& si, uint32_t& kk)
+{
+    if (a.k_override)
+        {
+            si = y;
+            kk = a.k_override[y];
+        }
+    else
+        {
+            si = y / a.nD_local;
+            kk = y - si * a.nD_local;
+        }
+}
+
+template <int LOAD, int STORE, bool INV>
+__global__ void __launch_bounds__(512) stage_kernel(const StageArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* s = reinterpret_cast<float2*>(smem_raw);
+    __shared__ WipePiece s_pieces[LOAD == LOAD_SAMPLES ? kMaxPieces : 1];
+    __shared__ float s_rmax[16];
+    __shared__ uint32_t s_ridx[16];
+    __shared__ float s_rsum[16];
+
+    const FftStage& st = a.st;
+    const uint32_t y = a.y0 + blockIdx.x;  // transform / row index
+    const uint32_t tile = blockIdx.y;
+    const uint32_t tile_off = tile * st.tile_step;
+    const uint32_t points = st.tile_points, C = st.C;
+    const size_t N = a.N;
+
+    // ------------------------------ prologue: fill the tile ------------------------------
+    if constexpr (LOAD == LOAD_SAMPLES)
+        {
+            // y = call_group * nD_local + local bin
+            const uint32_t g = y / a.nD_local, kk = y - g * a.nD_local;
+            const uint32_t pb = a.group_piece_base[g] + kk;
+            const uint32_t np = a.n_pieces[pb];
+            for (uint32_t i = threadIdx.x; i < np; i += blockDim.x) s_pieces[i] = a.pieces[(size_t)pb * kMaxPieces + i];
+            __syncthreads();
+            uint32_t cur = 0;
+            for (uint32_t i = threadIdx.x; i < points; i += blockDim.x)
+                {
+                    const uint32_t idx = i / C, c = i - idx * C;
+                    const uint32_t pos = idx * st.pos_stride + tile_off + c;
+                    float2 v = make_float2(0.f, 0.f);
+                    if (pos < a.consumed)
+                        {
+                            float2 x;
+                            if (a.is_cshort)
+                                {
+                                    const short2 q = __ldg(static_cast<const short2*>(a.samples) + pos);  // :623-626
+                                    x = make_float2((float)q.x, (float)q.y);
+                                }
+                            else
+                                {
+                                    x = __ldg(static_cast<const float2*>(a.samples) + pos);
+                                }
+                            while (cur + 1 < np && pos >= s_pieces[cur + 1].start) cur++;
+                            const WipePiece pc = s_pieces[cur];
+                            // exact: the value is representable, the fma rounds once
+                            const float phi = fmaf((float)(pos - pc.start), pc.step, pc.phi0);
+                            float sn, cs;
+                            sincosf(phi, &sn, &cs);  // wipe-off sample (cos phi, sin phi), volk_gnsssdr_s32f_sincos_32fc
+                            v = make_float2(x.x * cs - x.y * sn, x.x * sn + x.y * cs);  // :658
+                        }
+                    s[i] = v;
+                }
+        }
+    else if constexpr (LOAD == LOAD_CODE)
+        {
+            const float2* code = a.codes_td + (size_t)y * a.code_len;
+            for (uint32_t i = threadIdx.x; i < points; i += blockDim.x)
+                {
+                    const uint32_t idx = i / C, c = i - idx * C;
+                    const uint32_t pos = idx * st.pos_stride + tile_off + c;
+                    s[i] = (pos >= a.code_off && pos - a.code_off < a.code_len) ? __ldg(code + (pos - a.code_off)) : make_float2(0.f, 0.f);
+                }
+        }
+    else if constexpr (LOAD == LOAD_BUF)
+        {
+            const float2* in = a.in_buf + (size_t)(y - a.in_y0) * N;
+            for (uint32_t i = threadIdx.x; i < points; i += blockDim.x)
+                {
+                    const uint32_t idx = i / C, c = i - idx * C;
+                    const uint32_t pos = idx * st.pos_stride + tile_off + c;
+                    s[i] = __ldcg(in + pos);
+                }
+        }
+    else
+        {
+            uint32_t si, kk;
+            row_of(a, y, si, kk);
+            const float2* X = a.in_buf + ((size_t)a.slot_group[si] * a.nD_local + kk) * N;
+            const float2* Cs = a.cbuf + (size_t)a.slots[si] * N;
+            for (uint32_t i = threadIdx.x; i < points; i += blockDim.x)
+                {
+                    const uint32_t idx = i / C, c = i - idx * C;
+                    const uint32_t pos = idx * st.pos_stride + tile_off + c;
+                    s[i] = fft::cmul(__ldg(X + pos), __ldg(Cs + pos));  // :665
+                }
+        }
+    __syncthreads();
+
+    // ------------------------------ the FFT stage ------------------------------
+    fft::run_stage<INV>(s, st, tile, a.W);
+
+    // ------------------------------ epilogue ------------------------------
+    if constexpr (STORE == STORE_BUF || STORE == STORE_CONJ)
+        {
+            float2* out = a.out_buf + (a.out_by_slot ? (size_t)a.slots[y] : (size_t)(y - a.out_y0)) * N;
+            for (uint32_t i = threadIdx.x; i < points; i += blockDim.x)
+                {
+                    const uint32_t idx = i / C, c = i - idx * C;
+                    const uint32_t pos = idx * st.pos_stride + tile_off + c;
+                    float2 v = s[i];
+                    if (STORE == STORE_CONJ) v.y = -v.y;  // :208
+                    out[pos] = v;
+                }
+        }
+    else
+        {
+            uint32_t si, kk;
+            row_of(a, y, si, kk);
+            float* mag = nullptr;
+            if (a.mag_base)
+                mag = a.mag_is_rowbuf ? a.mag_base + (size_t)si * a.eff : a.mag_base + ((size_t)a.slots[si] * a.nD_local + kk) * a.eff;
+            const bool accumulate = mag && !a.mag_is_rowbuf && a.dwell_after[si] > 1;
+            float best = -1.f, sum = 0.f;
+            uint32_t best_i = 0xffffffffu;
+            for (uint32_t i = threadIdx.x; i < points; i += blockDim.x)
+                {
+                    const uint32_t idx = i / C, c = i - idx * C;
+                    const uint32_t pos = idx * st.pos_stride + tile_off + c;
+                    const uint32_t m = pos - a.mag_offset;  // wraps for pos < offset -> fails the range test
+                    if (m < a.eff)
+                        {
+                            const float2 v = s[i];
+                            float g = v.x * v.x + v.y * v.y;      // :674
+                            if (accumulate) g = mag[m] + g;       // :679
+                            if (mag) mag[m] = g;
+                            sum += g;
+                            if (g > best || (g == best && m < best_i))
+                                {
+                                    best = g;
+                                    best_i = m;
+                                }
+                        }
+                }
+            // CTA reduction: lowest index among equal maxima (tie rule of volk_gnsssdr_32f_index_max_32u)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                {
+                    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+                    const uint32_t oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+                    sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                    if (ob > best || (ob == best && oi < best_i))
+                        {
+                            best = ob;
+                            best_i = oi;
+                        }
+                }
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            if (lane == 0)
+                {
+                    s_rmax[warp] = best;
+                    s_ridx[warp] = best_i;
+                    s_rsum[warp] = sum;
+                }
+            __syncthreads();
+            if (threadIdx.x == 0)
+                {
+                    const int nw = (blockDim.x + 31) / 32;
+                    for (int w = 1; w < nw; w++)
+                        {
+                            sum += s_rsum[w];
+                            if (s_rmax[w] > best || (s_rmax[w] == best && s_ridx[w] < best_i))
+                                {
+                                    best = s_rmax[w];
+                                    best_i = s_ridx[w];
+                                }
+                        }
+                    RowPartial rp;
+                    rp.max_val = best;
+                    rp.max_idx = best_i;
+                    rp.sum = sum;
+                    rp.pad = 0;
+                    a.partials[(size_t)y * gridDim.y + tile] = rp;
+                }
+        }
+}
+
+// ---- cross-tile and cross-row decision: max_to_input_power_statistic (:511-543) ----
+struct FinalizeArgs
+{
+    const RowPartial* partials;  // [n_slots * nD_local (or n_slots when recomputing)][tiles]
+    uint32_t tiles;
+    uint32_t nD, nD_local, row_begin;
+    uint32_t eff;
+    int32_t doppler_max;
+    uint32_t doppler_step;
+    uint32_t use_cfar;
+    const uint32_t* slots;
+    const int32_t* center;       // [n_slots in call]
+    const uint32_t* dwell_after; // [n_slots in call]
+    gnss_b200_acq_row* rows;     // [slot][nD]
+    gnss_b200_acq_result* results;  // [n_slots in call]
+    uint32_t* best_k_local;      // [n_slots in call]
+};
+
+// one warp per slot
+__global__ void finalize_kernel(const FinalizeArgs a)
+{
+    const uint32_t si = blockIdx.x;
+    const uint32_t slot = a.slots[si];
+    const int lane = threadIdx.x;
+    gnss_b200_acq_row* rows = a.rows + (size_t)slot * a.nD;
+    float best = 0.f;  // grid_maximum starts at 0 and is replaced on strict '>' (:513,:523)
+    uint32_t best_k = 0xffffffffu, best_i = 0;
+    for (uint32_t k = lane; k < a.nD; k += 32)
+        {
+            gnss_b200_acq_row r;
+            r.max_val = 0.f;
+            r.max_idx = 0;
+            r.row_sum = 0.f;
+            r.valid = 0;
+            if (k >= a.row_begin && k - a.row_begin < a.nD_local)
+                {
+                    const RowPartial* p = a.partials + ((size_t)si * a.nD_local + (k - a.row_begin)) * a.tiles;
+                    float m = p[0].max_val, s = p[0].sum;
+                    uint32_t mi = p[0].max_idx;
+                    for (uint32_t t = 1; t < a.tiles; t++)
+                        {
+                            s += p[t].sum;
+                            if (p[t].max_val > m || (p[t].max_val == m && p[t].max_idx < mi))
+                                {
+                                    m = p[t].max_val;
+                                    mi = p[t].max_idx;
+                                }
+                        }
+                    r.max_val = m;
+                    r.max_idx = mi;
+                    r.row_sum = s;
+                    r.valid = 1;
+                    if (m > best || (m == best && best_k != 0xffffffffu && k < best_k))
+                        {
+                            best = m;
+                            best_k = k;
+                            best_i = mi;
+                        }
+                }
+            rows[k] = r;
+        }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const uint32_t ok = __shfl_xor_sync(0xffffffffu, best_k, o);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+            if (ob > best || (ob == best && ok < best_k))
+                {
+                    best = ob;
+                    best_k = ok;
+                    best_i = oi;
+                }
+        }
+    __syncwarp();
+    if (lane == 0)
+        {
+            if (best_k == 0xffffffffu)  // nothing exceeded 0: the reference keeps index 0 / 0
+                {
+                    best_k = 0;
+                    best_i = 0;
+                }
+            gnss_b200_acq_result res;
+            res.peak = best;
+            res.code_phase = best_i;
+            res.doppler_index = best_k;
+            res.doppler_hz = -a.doppler_max + a.center[si] + (int32_t)a.doppler_step * (int32_t)best_k;  // :535
+            res.dwell_count = a.dwell_after[si];
+            res.second_peak = 0.f;
+            res.input_power = 0.f;
+            res.test_statistic = 0.f;
+            if (a.use_cfar)
+                {
+                    const uint32_t opp = (best_k + a.nD / 2) % a.nD;  // :533
+                    const gnss_b200_acq_row ro = rows[opp];
+                    if (ro.valid)
+                        {
+                            // float / int32 -> float, then / 2.0 / counter in double, narrowed (:534)
+                            const float per = ro.row_sum / (float)(int32_t)a.eff;
+                            res.input_power = (float)(((double)per / 2.0) / (double)a.dwell_after[si]);
+                            res.test_statistic = best / res.input_power;  // :542
+                        }
+                    else
+                        {
+                            res.input_power = nanf("");
+                            res.test_statistic = nanf("");  // row lives on another shard: merge with finalize_rows
+                        }
+                }
+            a.results[si] = res;
+            a.best_k_local[si] = (best_k >= a.row_begin && best_k - a.row_begin < a.nD_local) ? best_k - a.row_begin : 0;
+        }
+}
+
+// ---- first_vs_second_peak_statistic (:546-612): second maximum of the best row outside the +-1 chip window ----
+struct SecondPeakArgs
+{
+    const float* mag_base;  // grid [slot][nD_local][eff] or row buffer [si][eff]
+    uint32_t is_rowbuf;
+    uint32_t nD_local;
+    uint32_t eff, N;
+    uint32_t samples_per_chip;
+    const uint32_t* slots;
+    const uint32_t* best_k_local;
+    gnss_b200_acq_result* results;
+};
+
+__global__ void second_peak_kernel(const SecondPeakArgs a)
+{
+    __shared__ float s_max[32];
+    const uint32_t si = blockIdx.x;
+    const float* row = a.is_rowbuf ? a.mag_base + (size_t)si * a.eff : a.mag_base + ((size_t)a.slots[si] * a.nD_local + a.best_k_local[si]) * a.eff;
+    gnss_b200_acq_result res = a.results[si];
+    int32_t ex1 = (int32_t)res.code_phase - (int32_t)a.samples_per_chip;  // :580-591
+    int32_t ex2 = (int32_t)res.code_phase + (int32_t)a.samples_per_chip;
+    if (ex1 < 0)
+        ex1 += (int32_t)a.N;
+    else if (ex2 >= (int32_t)a.N)
+        ex2 -= (int32_t)a.N;
+    float best = 0.f;  // beyond eff (bit transition) and inside the window the reference's buffer holds zeros
+    for (uint32_t i = threadIdx.x; i < a.eff; i += blockDim.x)
+        {
+            const int32_t ii = (int32_t)i;
+            const bool excluded = (ex1 < ex2) ? (ii >= ex1 && ii < ex2) : (ii >= ex1 || ii < ex2);
+            if (!excluded) best = fmaxf(best, row[i]);
+        }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0)
+        {
+            for (uint32_t w = 1; w < (blockDim.x + 31) / 32; w++) best = fmaxf(best, s_max[w]);
+            res.second_peak = best;
+            res.test_statistic = res.peak / best;  // :611
+            a.results[si] = res;
+        }
+}
+
+__global__ void zero_kernel(float4* p, size_t n4)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) p[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+}  // namespace b200

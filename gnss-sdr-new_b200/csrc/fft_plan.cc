@@ -1,0 +1,216 @@
+// Host planner for the shared-memory mixed-radix FFT (see fft_plan.h).
+#include "fft_plan.h"
+#include <algorithm>
+#include <cmath>
+
+namespace b200
+{
+namespace
+{
+// Radices of one stage, lowest stride first. Odd radices go first so that the stride-1 dimension has an odd
+// element stride between neighbouring threads (conflict-free 64-bit shared-memory accesses).
+bool stage_radices(uint32_t M, std::vector<uint32_t>* out)
+{
+    out->clear();
+    uint32_t n2 = 0, n3 = 0, n5 = 0;
+    std::vector<uint32_t> primes;
+    uint32_t m = M;
+    while (m % 2 == 0) m /= 2, n2++;
+    while (m % 3 == 0) m /= 3, n3++;
+    while (m % 5 == 0) m /= 5, n5++;
+    for (uint32_t p : {7u, 11u, 13u})
+        while (m % p == 0) m /= p, primes.push_back(p);
+    if (m != 1) return false;
+    std::vector<uint32_t> odd, even;
+    while (n5 >= 2) odd.push_back(25), n5 -= 2;
+    while (n3 >= 2) odd.push_back(9), n3 -= 2;
+    if (n5 == 1 && n3 == 1) odd.push_back(15), n5 = n3 = 0;
+    for (uint32_t p : primes) odd.push_back(p);
+    if (n5 == 1)
+        {
+            if (n2 >= 2)
+                even.push_back(20), n2 -= 2;
+            else if (n2 == 1)
+                even.push_back(10), n2 -= 1;
+            else
+                odd.push_back(5);
+        }
+    if (n3 == 1)
+        {
+            if (n2 >= 2)
+                even.push_back(12), n2 -= 2;
+            else if (n2 == 1)
+                even.push_back(6), n2 -= 1;
+            else
+                odd.push_back(3);
+        }
+    while (n2 >= 4) even.push_back(16), n2 -= 4;
+    if (n2 == 3) even.push_back(8);
+    if (n2 == 2) even.push_back(4);
+    if (n2 == 1) even.push_back(2);
+    std::sort(odd.begin(), odd.end(), std::greater<uint32_t>());
+    std::sort(even.begin(), even.end());
+    for (uint32_t r : odd) out->push_back(r);
+    for (uint32_t r : even) out->push_back(r);
+    if (out->empty()) out->push_back(1);
+    return out->size() <= (size_t)kMaxPasses;
+}
+
+void fill_stage(FftStage* st, uint32_t N, uint32_t M, const std::vector<uint32_t>& rad, uint32_t base_stride, bool upper)
+{
+    st->M = M;
+    st->is_upper = upper ? 1 : 0;
+    st->pos_stride = base_stride;
+    st->tw_lo_mul = base_stride;
+    st->n_pass = 0;
+    std::vector<uint32_t> ls(rad.size());
+    uint32_t s = 1;
+    for (size_t j = 0; j < rad.size(); j++)
+        {
+            ls[j] = s;
+            s *= rad[j];
+        }
+    for (int j = (int)rad.size() - 1; j >= 0; j--)
+        {
+            if (rad[j] == 1) continue;
+            FftPass& p = st->pass[st->n_pass++];
+            p.radix = rad[j];
+            p.lstride = ls[j];
+            const uint64_t gstride = (uint64_t)ls[j] * base_stride;
+            p.tw_scale = (uint32_t)(N / (rad[j] * gstride));
+            p.has_tw = gstride > 1 ? 1 : 0;
+        }
+}
+
+uint32_t pick_threads(uint32_t tile_points)
+{
+    uint32_t t = (tile_points / 16 + 31) / 32 * 32;
+    return std::min(512u, std::max(128u, t));
+}
+}  // namespace
+
+bool make_fft_plan(uint32_t N, uint32_t max_single, FftPlan* plan, const char** why)
+{
+    static const char* kPrime = "FFT length has a prime factor > 13 (no codelet)";
+    static const char* kSplit = "FFT length cannot be split into two shared-memory stages";
+    plan->N = N;
+    plan->radices.clear();
+    std::vector<uint32_t> rad;
+    if (N <= max_single)
+        {
+            if (!stage_radices(N, &rad))
+                {
+                    // too many passes for one stage (or bad prime): fall through to the two-stage search
+                    uint32_t m = N;
+                    for (uint32_t p : {2u, 3u, 5u, 7u, 11u, 13u})
+                        while (m % p == 0) m /= p;
+                    if (m != 1)
+                        {
+                            if (why) *why = kPrime;
+                            return false;
+                        }
+                }
+            else
+                {
+                    plan->n_stages = 1;
+                    FftStage& st = plan->stage[0];
+                    fill_stage(&st, N, N, rad, 1, false);
+                    st.C = 1;
+                    st.blocks = 1;
+                    st.tiles = 1;
+                    st.tile_step = N;
+                    st.tile_points = N;
+                    st.threads = pick_threads(N);
+                    plan->radices = rad;
+                    return true;
+                }
+        }
+    // two stages: N = M_hi * M_lo, both small enough for a comfortable tile
+    const uint32_t kMaxStage = 8192;
+    uint32_t best_lo = 0;
+    double best_cost = 1e30;
+    std::vector<uint32_t> r_lo, r_hi;
+    for (uint32_t lo = 2; (uint64_t)lo * 2 <= N; lo++)
+        {
+            if (N % lo) continue;
+            const uint32_t hi = N / lo;
+            if (lo > kMaxStage || hi > kMaxStage) continue;
+            if (!stage_radices(lo, &r_lo) || !stage_radices(hi, &r_hi)) continue;
+            uint32_t c = 1;
+            for (uint32_t d = 1; d <= 32; d++)
+                if (lo % d == 0) c = d;
+            double cost = (double)(r_lo.size() + r_hi.size());
+            cost += 0.25 * std::fabs(std::log2((double)lo / (double)hi));  // balance
+            if (c < 16) cost += 2.0;                                          // narrow column tiles coalesce badly
+            if ((uint64_t)hi * c * 8 > 96 * 1024) cost += 4.0;                // upper tile must fit shared memory
+            if (cost < best_cost)
+                {
+                    best_cost = cost;
+                    best_lo = lo;
+                }
+        }
+    if (!best_lo)
+        {
+            uint32_t m = N;
+            for (uint32_t p : {2u, 3u, 5u, 7u, 11u, 13u})
+                while (m % p == 0) m /= p;
+            if (why) *why = (m != 1) ? kPrime : kSplit;
+            return false;
+        }
+    const uint32_t M_lo = best_lo, M_hi = N / best_lo;
+    stage_radices(M_lo, &r_lo);
+    stage_radices(M_hi, &r_hi);
+    plan->n_stages = 2;
+    // forward order: upper stage first
+    FftStage& up = plan->stage[0];
+    fill_stage(&up, N, M_hi, r_hi, M_lo, true);
+    uint32_t C = 1;
+    for (uint32_t d = 1; d <= 32; d++)
+        if (M_lo % d == 0 && (uint64_t)M_hi * d * 8 <= 96 * 1024) C = d;
+    up.C = C;
+    up.blocks = 1;
+    up.tiles = M_lo / C;
+    up.tile_step = C;
+    up.tile_points = M_hi * C;
+    up.threads = pick_threads(up.tile_points);
+    FftStage& lo = plan->stage[1];
+    fill_stage(&lo, N, M_lo, r_lo, 1, false);
+    uint32_t b = 1;
+    for (uint32_t d = 1; d <= M_hi; d++)
+        if (M_hi % d == 0 && (uint64_t)d * M_lo <= 4096) b = d;
+    lo.C = 1;
+    lo.blocks = b;
+    lo.tiles = M_hi / b;
+    lo.tile_step = b * M_lo;
+    lo.tile_points = b * M_lo;
+    lo.threads = pick_threads(lo.tile_points);
+    plan->radices = r_lo;
+    plan->radices.insert(plan->radices.end(), r_hi.begin(), r_hi.end());
+    return true;
+}
+
+std::vector<uint32_t> fft_plan_permutation(const FftPlan& plan)
+{
+    const uint32_t N = plan.N;
+    std::vector<uint32_t> perm(N);
+    std::vector<uint64_t> stride(plan.radices.size());
+    uint64_t s = 1;
+    for (size_t j = 0; j < plan.radices.size(); j++)
+        {
+            stride[j] = s;
+            s *= plan.radices[j];
+        }
+    for (uint32_t pos = 0; pos < N; pos++)
+        {
+            uint64_t f = 0;
+            for (size_t j = 0; j < plan.radices.size(); j++)
+                {
+                    const uint64_t u = (pos / stride[j]) % plan.radices[j];
+                    f += u * (N / (plan.radices[j] * stride[j]));
+                }
+            perm[pos] = (uint32_t)f;
+        }
+    return perm;
+}
+
+}  // namespace b200

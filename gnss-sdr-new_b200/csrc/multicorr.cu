@@ -1,0 +1,680 @@
+// Tracking multicorrelator for sm_100a: ONE kernel over all channels of an epoch that fuses the carrier
+// rotator, the nearest-chip code resampler and the E/P/L (or extended) dot products.
+//
+// Replaces, per channel, one call of
+//   Cpu_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler
+//     (reference: src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.cc:103-144)
+//   Cpu_Multicorrelator::Carrier_wipeoff_multicorrelator_resampler (cpu_multicorrelator.cc:87-101)
+// i.e. the volk_gnsssdr kernels  *_xn_resampler_*  +  *_rotator_dot_prod_*_xn.
+//
+// The reference materialises T resampled code vectors (T*n floats) and re-reads them; here a chip is a
+// shared-memory lookup and nothing but the sample stream is read from HBM (8 B / sample).
+//
+// Numerical contract (tests/test_multicorr_gpu.py):
+//   * chip indices are bit-exact: idx = floor(fl(fl(fl(step*n) + shift) - rem)) in binary32, evaluated in
+//     the reference's order with explicit round-to-nearest intrinsics (no FMA contraction);
+//   * the carrier phasor of sample n is P0 * exp(j*n*theta), where theta is the angle of the reference's
+//     *binary32-rounded* per-sample phasor exp(-j*step) — the recursion of the reference converges to that
+//     angle, not to `step`. Evaluated per thread in double at its first sample, then
+//     advanced by a stride phasor.
+#include "common.cuh"
+#include <cmath>
+#include <complex>
+#include <vector>
+
+namespace b200
+{
+namespace
+{
+constexpr int kThreads = 256;
+constexpr int kMaxTapsPerPass = 16;
+constexpr uint32_t kSmemCapBytes = 200 * 1024;
+
+enum : uint32_t
+{
+    F_HIGH_DYN_RESAMPLER = 1u,
+    F_HIGH_DYN_ROTATOR = 2u,
+    F_COMPLEX_CODE = 4u
+};
+
+struct alignas(16) ChanParams
+{
+    const float2* sig;   // device samples of this channel
+    const void* code;    // device code table (float or float2)
+    double theta;        // effective rotation per sample [rad]
+    uint32_t code_len;
+    uint32_t n;
+    float rem_code, code_step, code_rate;
+    float p0_re, p0_im;  // (cos rem_carr, -sin rem_carr)
+    float wb_re, wb_im;  // exp(j*kThreads*theta)
+    float rate_arg;      // arg of the rounded rate phasor (high-dynamics rotator)
+    uint32_t flags;
+    uint32_t shifts_off;  // offset into the shifts / shift_samples arrays
+};
+
+// chip-phase of sample n for one tap, exactly as volk_gnsssdr_32f_xn_resampler_32f_xn_generic evaluates it
+__device__ __forceinline__ int chip_index_plain(float step, float fn, float shift, float rem)
+{
+    const float a = __fmul_rn(step, fn);
+    return __float2int_rd(__fsub_rn(__fadd_rn(a, shift), rem));
+}
+
+// volk_gnsssdr_32f_xn_high_dynamics_resampler_32f_xn_generic, tap 0 expression at (already shifted) sample n
+__device__ __forceinline__ int chip_index_hd(float step, float rate, uint32_t n, float shift0, float rem)
+{
+    const float a = __fmul_rn(step, (float)n);
+    const float b = __fmul_rn(rate, (float)(n * n));
+    return __float2int_rd(__fsub_rn(__fadd_rn(__fadd_rn(a, b), shift0), rem));
+}
+
+__device__ __forceinline__ int wrap_chip(int idx, int len)
+{
+    int r = idx % len;
+    return r < 0 ? r + len : r;
+}
+
+template <class CodeT>
+struct CodeOps;
+template <>
+struct CodeOps<float>
+{
+    __device__ static __forceinline__ void mac(float2& acc, const float2 z, const float c)
+    {
+        acc.x = fmaf(z.x, c, acc.x);
+        acc.y = fmaf(z.y, c, acc.y);
+    }
+};
+template <>
+struct CodeOps<float2>
+{
+    __device__ static __forceinline__ void mac(float2& acc, const float2 z, const float2 c)
+    {
+        acc.x = fmaf(z.x, c.x, fmaf(-z.y, c.y, acc.x));
+        acc.y = fmaf(z.x, c.y, fmaf(z.y, c.x, acc.y));
+    }
+};
+
+// code-fetch modes, decided per CTA
+enum
+{
+    MODE_WINDOW = 0,  // smem holds code[(lo+j) mod L], no modulo at lookup
+    MODE_FULL_SMEM = 1,
+    MODE_GLOBAL = 2
+};
+
+template <class CodeT, int T>
+__global__ void __launch_bounds__(kThreads) multicorr_kernel(const ChanParams* __restrict__ chans, const float* __restrict__ shifts_all,
+    const uint32_t* __restrict__ shift_samples_all, float2* __restrict__ partials, uint32_t* __restrict__ tickets,
+    float2* __restrict__ out, int n_taps_total, int tap0, uint32_t smem_elems)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    CodeT* s_code = reinterpret_cast<CodeT*>(smem_raw);
+    __shared__ float2 s_red[kThreads / 32][T];
+    __shared__ int s_last;
+
+    const ChanParams cp = chans[blockIdx.y];
+    const uint32_t splits = gridDim.x;
+    const uint32_t per = (cp.n + splits - 1) / splits;
+    const uint32_t n0 = min(cp.n, blockIdx.x * per), n1 = min(cp.n, n0 + per);
+    const int L = (int)cp.code_len;
+    const CodeT* g_code = static_cast<const CodeT*>(cp.code);
+    const bool hd_res = cp.flags & F_HIGH_DYN_RESAMPLER;
+    const bool hd_rot = cp.flags & F_HIGH_DYN_ROTATOR;
+
+    float shift[T];
+    uint32_t ss[T];
+#pragma unroll
+    for (int t = 0; t < T; t++)
+        {
+            const int tt = min(tap0 + t, n_taps_total - 1);
+            shift[t] = shifts_all[cp.shifts_off + tt];
+            ss[t] = shift_samples_all[cp.shifts_off + tt];
+        }
+    const float shift0 = shifts_all[cp.shifts_off];
+
+    // ---- stage the code: a pre-wrapped window of exactly the chips this CTA can touch, else the whole code ----
+    int mode, lo = 0;
+    if (!hd_res)
+        {
+            float smin = shift[0], smax = shift[0];
+#pragma unroll
+            for (int t = 1; t < T; t++)
+                {
+                    smin = fminf(smin, shift[t]);
+                    smax = fmaxf(smax, shift[t]);
+                }
+            const double a0 = (double)cp.code_step * (double)n0, a1 = (double)cp.code_step * (double)(n1 > n0 ? n1 - 1 : n0);
+            const double vlo = fmin(a0, a1) + (double)smin - (double)cp.rem_code;
+            const double vhi = fmax(a0, a1) + (double)smax - (double)cp.rem_code;
+            lo = (int)floor(vlo) - 2;
+            const long long width = (long long)floor(vhi) + 2 - lo + 1;
+            mode = (width <= (long long)smem_elems) ? MODE_WINDOW : ((uint32_t)L <= smem_elems ? MODE_FULL_SMEM : MODE_GLOBAL);
+            if (mode == MODE_WINDOW)
+                {
+                    int src = wrap_chip(lo + (int)threadIdx.x, L);
+                    const int adv = kThreads % L;
+                    for (int j = threadIdx.x; j < (int)width; j += kThreads)
+                        {
+                            s_code[j] = g_code[src];
+                            src += adv;
+                            if (src >= L) src -= L;
+                        }
+                }
+        }
+    else
+        {
+            mode = ((uint32_t)L <= smem_elems) ? MODE_FULL_SMEM : MODE_GLOBAL;
+        }
+    if (mode == MODE_FULL_SMEM)
+        for (int j = threadIdx.x; j < L; j += kThreads) s_code[j] = g_code[j];
+    __syncthreads();
+
+    float2 acc[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) acc[t] = make_float2(0.f, 0.f);
+
+    uint32_t n = n0 + threadIdx.x;
+    if (n < n1)
+        {
+            // carrier phasor of the first sample of this thread: P0 * exp(j*n*theta), angle reduced in double
+            double ang = cp.theta * (double)n;
+            ang -= 6.283185307179586476925286766559 * rint(ang * 0.15915494309189533576888376337251);
+            float sr, cr;
+            sincosf((float)ang, &sr, &cr);
+            float2 ph = make_float2(cp.p0_re * cr - cp.p0_im * sr, cp.p0_re * sr + cp.p0_im * cr);
+            const float2 wb = make_float2(cp.wb_re, cp.wb_im);
+            const float step = cp.code_step, rem = cp.rem_code, rate = cp.code_rate;
+
+            for (; n < n1; n += kThreads)
+                {
+                    const float2 x = __ldg(cp.sig + n);
+                    float2 p = ph;
+                    if (hd_rot && n > 0)
+                        {
+                            // phase = phase_doppler * cpowf(inc_rate, (n-1)^2) normalised  (…high_dynamic_rotator…_generic)
+                            const uint32_t m = n - 1;
+                            float s2, c2;
+                            sincosf(__fmul_rn((float)(m * m), cp.rate_arg), &s2, &c2);
+                            p = make_float2(ph.x * c2 - ph.y * s2, ph.x * s2 + ph.y * c2);
+                        }
+                    const float2 z = make_float2(x.x * p.x - x.y * p.y, x.x * p.y + x.y * p.x);
+                    if (mode == MODE_WINDOW)
+                        {
+                            const float fn = (float)n;
+#pragma unroll
+                            for (int t = 0; t < T; t++)
+                                {
+                                    const int idx = chip_index_plain(step, fn, shift[t], rem) - lo;
+                                    CodeOps<CodeT>::mac(acc[t], z, s_code[idx]);
+                                }
+                        }
+                    else
+                        {
+#pragma unroll
+                            for (int t = 0; t < T; t++)
+                                {
+                                    int idx;
+                                    if (hd_res)
+                                        {
+                                            uint32_t nn = n + ss[t];
+                                            if (nn >= cp.n) nn -= cp.n;
+                                            idx = chip_index_hd(step, rate, nn, shift0, rem);
+                                        }
+                                    else
+                                        {
+                                            idx = chip_index_plain(step, (float)n, shift[t], rem);
+                                        }
+                                    idx = wrap_chip(idx, L);
+                                    const CodeT c = (mode == MODE_FULL_SMEM) ? s_code[idx] : g_code[idx];
+                                    CodeOps<CodeT>::mac(acc[t], z, c);
+                                }
+                        }
+                    // advance the phasor by kThreads samples
+                    ph = make_float2(ph.x * wb.x - ph.y * wb.y, ph.x * wb.y + ph.y * wb.x);
+                }
+        }
+
+    // ---- CTA reduction: warp shuffles, then one warp over the per-warp partials ----
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int t = 0; t < T; t++)
+        {
+            float2 v = acc[t];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                {
+                    v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+                    v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+                }
+            if (lane == 0) s_red[warp][t] = v;
+        }
+    __syncthreads();
+    const int live = min(T, n_taps_total - tap0);
+    if (threadIdx.x < live)
+        {
+            float2 v = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int w = 0; w < kThreads / 32; w++)
+                {
+                    v.x += s_red[w][threadIdx.x].x;
+                    v.y += s_red[w][threadIdx.x].y;
+                }
+            if (splits == 1)
+                out[(size_t)blockIdx.y * n_taps_total + tap0 + threadIdx.x] = v;
+            else
+                partials[((size_t)blockIdx.y * splits + blockIdx.x) * n_taps_total + tap0 + threadIdx.x] = v;
+        }
+    if (splits == 1) return;
+
+    // ---- last CTA of the channel adds the split partials in a fixed order (deterministic) ----
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+        {
+            const uint32_t ticket = atomicAdd(&tickets[blockIdx.y], 1u);
+            s_last = (ticket == splits - 1);
+        }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x < live)
+        {
+            float2 v = make_float2(0.f, 0.f);
+            for (uint32_t s = 0; s < splits; s++)
+                {
+                    const float2 p = __ldcg(&partials[((size_t)blockIdx.y * splits + s) * n_taps_total + tap0 + threadIdx.x]);
+                    v.x += p.x;
+                    v.y += p.y;
+                }
+            out[(size_t)blockIdx.y * n_taps_total + tap0 + threadIdx.x] = v;
+        }
+    if (threadIdx.x == 0) tickets[blockIdx.y] = 0;
+}
+
+// parity aid: the wrapped chip index of every (tap, sample) of one channel
+__global__ void chip_index_kernel(ChanParams cp, const float* __restrict__ shifts, const uint32_t* __restrict__ shift_samples,
+    int n_taps, int32_t* __restrict__ out)
+{
+    const bool hd = cp.flags & F_HIGH_DYN_RESAMPLER;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cp.n * (uint32_t)n_taps; i += gridDim.x * blockDim.x)
+        {
+            const uint32_t t = i / cp.n, n = i % cp.n;
+            int idx;
+            if (hd)
+                {
+                    uint32_t nn = n + shift_samples[t];
+                    if (nn >= cp.n) nn -= cp.n;
+                    idx = chip_index_hd(cp.code_step, cp.code_rate, nn, shifts[0], cp.rem_code);
+                }
+            else
+                {
+                    idx = chip_index_plain(cp.code_step, (float)n, shifts[t], cp.rem_code);
+                }
+            out[i] = wrap_chip(idx, (int)cp.code_len);
+        }
+}
+
+template <class CodeT>
+void launch_taps(int T, dim3 grid, size_t smem, cudaStream_t st, const ChanParams* chans, const float* shifts, const uint32_t* ss,
+    float2* partials, uint32_t* tickets, float2* out, int n_taps_total, int tap0, uint32_t smem_elems)
+{
+#define B200_MC_CASE(TT)                                                                                                           \
+    case TT:                                                                                                                       \
+        cudaFuncSetAttribute(multicorr_kernel<CodeT, TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCapBytes);         \
+        multicorr_kernel<CodeT, TT><<<grid, kThreads, smem, st>>>(chans, shifts, ss, partials, tickets, out, n_taps_total, tap0, smem_elems); \
+        break;
+    switch (T)
+        {
+            B200_MC_CASE(1)
+            B200_MC_CASE(2)
+            B200_MC_CASE(3)
+            B200_MC_CASE(4)
+            B200_MC_CASE(5)
+            B200_MC_CASE(6)
+            B200_MC_CASE(7)
+            B200_MC_CASE(8)
+            B200_MC_CASE(9)
+            B200_MC_CASE(10)
+            B200_MC_CASE(11)
+            B200_MC_CASE(12)
+            B200_MC_CASE(13)
+            B200_MC_CASE(14)
+            B200_MC_CASE(15)
+            B200_MC_CASE(16)
+        }
+#undef B200_MC_CASE
+}
+
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+struct gnss_b200_mc
+{
+    std::mutex mu;
+    int device = 0;
+    uint32_t max_channels = 0, max_samples = 0, max_taps = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<DevBuf> codes;  // per channel
+    std::vector<uint32_t> code_len;
+    std::vector<uint8_t> code_complex;
+    DevBuf d_sig;     // [max_channels][max_samples] staging for host-pointer calls
+    DevBuf d_stream;  // shared stream
+    uint64_t stream_len = 0;
+    DevBuf d_params;  // ChanParams[n] | shifts | shift_samples
+    PinBuf h_params;
+    DevBuf d_partials, d_tickets, d_out;
+    PinBuf h_out;
+    DevBuf d_idx;
+    uint64_t launches = 0;
+    uint32_t last_n_ch = 0, last_n_taps = 0;
+};
+
+namespace
+{
+// Host half of one batch: per-channel constants (the reference computes these at cpu_multicorrelator_real_codes.cc:114-119).
+int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_b200_mc_args* args, const float* shifts, uint32_t n_taps,
+    uint32_t flags, const float2* d_sig_base, uint64_t ch_stride, bool device_resident, uint32_t* out_smem_elems, uint32_t* out_splits, bool* out_complex)
+{
+    const size_t bytes = sizeof(ChanParams) * n_ch + sizeof(float) * n_ch * n_taps + sizeof(uint32_t) * n_ch * n_taps;
+    B200_CUDA(h->h_params.reserve(bytes));
+    B200_CUDA(h->d_params.reserve(bytes));
+    ChanParams* cp = h->h_params.as<ChanParams>();
+    float* hs = reinterpret_cast<float*>(cp + n_ch);
+    uint32_t* hss = reinterpret_cast<uint32_t*>(hs + (size_t)n_ch * n_taps);
+    std::memcpy(hs, shifts, sizeof(float) * n_ch * n_taps);
+
+    const bool hd_res = flags & GNSS_B200_MC_HIGH_DYN;
+    const bool hd_rot = hd_res && !(flags & GNSS_B200_MC_SIX_ARG);
+    uint64_t max_len = 1, max_n = 1;
+    for (uint32_t i = 0; i < n_ch; i++) max_n = std::max<uint64_t>(max_n, args[i].n_samples);
+    // split each channel over several CTAs when the batch alone cannot fill the machine
+    uint32_t splits = 1;
+    const uint32_t target_ctas = kNumSMs * 4;
+    if (n_ch < target_ctas)
+        {
+            splits = (target_ctas + n_ch - 1) / n_ch;
+            const uint32_t max_splits = (uint32_t)std::max<uint64_t>(1, max_n / 2048);
+            splits = std::max(1u, std::min(splits, max_splits));
+        }
+    uint64_t max_window = 1;  // widest per-CTA chip window over the batch
+    bool cplx = false;
+    for (uint32_t i = 0; i < n_ch; i++)
+        {
+            const uint32_t c = ch[i];
+            B200_REQUIRE(c < h->max_channels, GNSS_B200_ERR_INVALID, "channel %u out of range", c);
+            B200_REQUIRE(h->codes[c].p != nullptr, GNSS_B200_ERR_STATE, "channel %u has no local code (call gnss_b200_mc_set_code)", c);
+            const gnss_b200_mc_args& a = args[i];
+            B200_REQUIRE(a.n_samples <= h->max_samples, GNSS_B200_ERR_INVALID, "n_samples %u > max_samples %u", a.n_samples, h->max_samples);
+            if (i == 0) cplx = h->code_complex[c];
+            B200_REQUIRE((bool)h->code_complex[c] == cplx, GNSS_B200_ERR_INVALID, "a batch cannot mix real and complex local codes");
+            ChanParams& p = cp[i];
+            if (device_resident)
+                p.sig = d_sig_base + (size_t)i * ch_stride;
+            else if (a.sig_in_c64)
+                p.sig = h->d_sig.as<float2>() + (size_t)i * h->max_samples;
+            else
+                {
+                    B200_REQUIRE(a.stream_offset + a.n_samples <= h->stream_len, GNSS_B200_ERR_INVALID, "stream window out of range");
+                    p.sig = h->d_stream.as<float2>() + a.stream_offset;
+                }
+            p.code = h->codes[c].p;
+            p.code_len = h->code_len[c];
+            p.n = a.n_samples;
+            p.rem_code = a.rem_code_phase_chips;
+            p.code_step = a.code_step_chips;
+            p.code_rate = a.code_rate_chips;
+            // phase_offset_as_complex = (cos(rem), -sin(rem)) in binary32 (:114-115)
+            p.p0_re = std::cos(a.rem_carr_phase_rad);
+            p.p0_im = -std::sin(a.rem_carr_phase_rad);
+            // the reference's per-sample phasor std::exp(lv_32fc_t(0, -step)) rounded to binary32; its true angle
+            const std::complex<float> inc = std::exp(std::complex<float>(0.0f, -a.carr_step_rad));
+            p.theta = std::atan2((double)inc.imag(), (double)inc.real());
+            const double wb = p.theta * (double)kThreads;
+            p.wb_re = (float)std::cos(wb);
+            p.wb_im = (float)std::sin(wb);
+            p.rate_arg = 0.0f;
+            if (hd_rot)
+                {
+                    // cpowf(z, m) = cexpf(m * clogf(z)); after normalisation only arg z survives
+                    const std::complex<float> inc_rate = std::exp(std::complex<float>(0.0f, -a.carr_rate_rad));
+                    p.rate_arg = std::log(inc_rate).imag();
+                }
+            p.flags = (hd_res ? F_HIGH_DYN_RESAMPLER : 0u) | (hd_rot ? F_HIGH_DYN_ROTATOR : 0u) | (cplx ? F_COMPLEX_CODE : 0u);
+            p.shifts_off = i * n_taps;
+            // …high_dynamics_resampler…:84-87: cumulative integer sample shifts of taps 1.. relative to tap 0
+            uint32_t acc = 0;
+            hss[(size_t)i * n_taps] = 0;
+            for (uint32_t t = 1; t < n_taps; t++)
+                {
+                    const float d = (hs[(size_t)i * n_taps + t] - hs[(size_t)i * n_taps + t - 1]) / a.code_step_chips;
+                    acc += (uint32_t)(int)std::round((double)d);
+                    hss[(size_t)i * n_taps + t] = acc;
+                }
+            float smin = hs[(size_t)i * n_taps], smax = smin;
+            for (uint32_t t = 1; t < n_taps; t++)
+                {
+                    smin = std::fmin(smin, hs[(size_t)i * n_taps + t]);
+                    smax = std::fmax(smax, hs[(size_t)i * n_taps + t]);
+                }
+            const uint32_t per = (a.n_samples + splits - 1) / splits;
+            const double span = std::fabs((double)a.code_step_chips) * (double)per + ((double)smax - (double)smin) + 16.0;
+            max_window = std::max<uint64_t>(max_window, (uint64_t)span);
+            max_len = std::max<uint64_t>(max_len, p.code_len);
+        }
+    const uint32_t elem = cplx ? 8u : 4u;
+    const uint32_t cap = kSmemCapBytes / elem;
+    uint64_t want = hd_res ? max_len : max_window;
+    if (!hd_res && want > cap && max_len <= cap) want = max_len;  // window too wide: hold the whole code instead
+    *out_smem_elems = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(want, 32), cap);
+    *out_splits = splits;
+    *out_complex = cplx;
+    return GNSS_B200_OK;
+}
+
+int run_batch(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, uint32_t smem_elems, uint32_t splits, bool cplx)
+{
+    const size_t pbytes = sizeof(ChanParams) * n_ch + sizeof(float) * n_ch * n_taps + sizeof(uint32_t) * n_ch * n_taps;
+    B200_CUDA(cudaMemcpyAsync(h->d_params.p, h->h_params.p, pbytes, cudaMemcpyHostToDevice, h->stream));
+    B200_CUDA(h->d_out.reserve(sizeof(float2) * (size_t)n_ch * n_taps));
+    B200_CUDA(h->h_out.reserve(sizeof(float2) * (size_t)n_ch * n_taps));
+    if (splits > 1) B200_CUDA(h->d_partials.reserve(sizeof(float2) * (size_t)n_ch * splits * n_taps));
+    const ChanParams* d_cp = h->d_params.as<ChanParams>();
+    const float* d_shifts = reinterpret_cast<const float*>(d_cp + n_ch);
+    const uint32_t* d_ss = reinterpret_cast<const uint32_t*>(d_shifts + (size_t)n_ch * n_taps);
+    const dim3 grid(splits, n_ch);
+    const size_t smem = (size_t)smem_elems * (cplx ? 8 : 4);
+    for (uint32_t tap0 = 0; tap0 < n_taps; tap0 += kMaxTapsPerPass)
+        {
+            const int T = (int)std::min<uint32_t>(kMaxTapsPerPass, n_taps - tap0);
+            if (cplx)
+                launch_taps<float2>(T, grid, smem, h->stream, d_cp, d_shifts, d_ss, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
+                    h->d_out.as<float2>(), (int)n_taps, (int)tap0, smem_elems);
+            else
+                launch_taps<float>(T, grid, smem, h->stream, d_cp, d_shifts, d_ss, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
+                    h->d_out.as<float2>(), (int)n_taps, (int)tap0, smem_elems);
+            h->launches++;
+            B200_CUDA(cudaGetLastError());
+        }
+    B200_CUDA(cudaMemcpyAsync(h->h_out.p, h->d_out.p, sizeof(float2) * (size_t)n_ch * n_taps, cudaMemcpyDeviceToHost, h->stream));
+    h->last_n_ch = n_ch;
+    h->last_n_taps = n_taps;
+    return GNSS_B200_OK;
+}
+}  // namespace
+
+extern "C"
+{
+    int gnss_b200_mc_create(uint32_t max_channels, uint32_t max_samples, uint32_t max_taps, int32_t device, gnss_b200_mc** out)
+    {
+        B200_REQUIRE(out && max_channels > 0 && max_samples > 0 && max_taps > 0, GNSS_B200_ERR_INVALID, "mc_create: bad arguments");
+        int rc = select_device(device);
+        if (rc) return rc;
+        auto* h = new gnss_b200_mc();
+        h->device = device;
+        h->max_channels = max_channels;
+        h->max_samples = max_samples;
+        h->max_taps = max_taps;
+        h->codes.resize(max_channels);
+        h->code_len.assign(max_channels, 0);
+        h->code_complex.assign(max_channels, 0);
+        cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = h->d_tickets.reserve(sizeof(uint32_t) * max_channels);
+        if (e == cudaSuccess) e = cudaMemsetAsync(h->d_tickets.p, 0, sizeof(uint32_t) * max_channels, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess)
+            {
+                delete h;
+                return fail(GNSS_B200_ERR_CUDA, "mc_create: %s", cudaGetErrorString(e));
+            }
+        *out = h;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_mc_destroy(gnss_b200_mc* h)
+    {
+        if (!h) return GNSS_B200_OK;
+        cudaSetDevice(h->device);
+        if (h->stream) cudaStreamSynchronize(h->stream);
+        for (auto& c : h->codes) c.release();
+        h->d_sig.release();
+        h->d_stream.release();
+        h->d_params.release();
+        h->h_params.release();
+        h->d_partials.release();
+        h->d_tickets.release();
+        h->d_out.release();
+        h->h_out.release();
+        h->d_idx.release();
+        if (h->stream) cudaStreamDestroy(h->stream);
+        delete h;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_mc_set_code(gnss_b200_mc* h, uint32_t ch, uint32_t code_len, const float* code, int is_complex)
+    {
+        B200_REQUIRE(h && code && code_len > 0, GNSS_B200_ERR_INVALID, "mc_set_code: bad arguments");
+        B200_REQUIRE(ch < h->max_channels, GNSS_B200_ERR_INVALID, "mc_set_code: channel %u out of range", ch);
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->device));
+        const size_t bytes = (size_t)code_len * (is_complex ? 8 : 4);
+        B200_CUDA(h->codes[ch].reserve(bytes));
+        B200_CUDA(cudaMemcpyAsync(h->codes[ch].p, code, bytes, cudaMemcpyHostToDevice, h->stream));
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        h->code_len[ch] = code_len;
+        h->code_complex[ch] = is_complex ? 1 : 0;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_mc_set_stream(gnss_b200_mc* h, const float* samples_c64, uint64_t n_samples)
+    {
+        B200_REQUIRE(h && samples_c64 && n_samples > 0, GNSS_B200_ERR_INVALID, "mc_set_stream: bad arguments");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->device));
+        B200_CUDA(h->d_stream.reserve(n_samples * 8));
+        B200_CUDA(cudaMemcpyAsync(h->d_stream.p, samples_c64, n_samples * 8, cudaMemcpyHostToDevice, h->stream));
+        h->stream_len = n_samples;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_mc_correlate_batch(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_b200_mc_args* args, const float* shifts,
+        uint32_t n_taps, uint32_t flags, float* out_c64)
+    {
+        B200_REQUIRE(h && ch && args && shifts && out_c64, GNSS_B200_ERR_INVALID, "mc_correlate_batch: null argument");
+        B200_REQUIRE(n_ch > 0 && n_ch <= h->max_channels && n_taps > 0 && n_taps <= h->max_taps, GNSS_B200_ERR_INVALID,
+            "mc_correlate_batch: n_ch=%u n_taps=%u out of range", n_ch, n_taps);
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->device));
+        bool any_host = false;
+        for (uint32_t i = 0; i < n_ch; i++) any_host |= (args[i].sig_in_c64 != nullptr);
+        if (any_host) B200_CUDA(h->d_sig.reserve((size_t)h->max_channels * h->max_samples * 8));
+        uint32_t smem_elems, splits;
+        bool cplx;
+        int rc = build_params(h, n_ch, ch, args, shifts, n_taps, flags, nullptr, 0, false, &smem_elems, &splits, &cplx);
+        if (rc) return rc;
+        // host -> device sample copies; runs of channels that are contiguous in host memory go as one copy
+        for (uint32_t i = 0; i < n_ch;)
+            {
+                if (!args[i].sig_in_c64)
+                    {
+                        i++;
+                        continue;
+                    }
+                uint32_t j = i + 1;
+                while (j < n_ch && args[j].sig_in_c64 && args[j - 1].n_samples == h->max_samples &&
+                       args[j].sig_in_c64 == args[j - 1].sig_in_c64 + 2 * (size_t)h->max_samples)
+                    j++;
+                const size_t bytes = (j - i > 1) ? (size_t)(j - i - 1) * h->max_samples * 8 + (size_t)args[j - 1].n_samples * 8 : (size_t)args[i].n_samples * 8;
+                B200_CUDA(cudaMemcpyAsync(h->d_sig.as<float2>() + (size_t)i * h->max_samples, args[i].sig_in_c64, bytes, cudaMemcpyHostToDevice, h->stream));
+                i = j;
+            }
+        rc = run_batch(h, n_ch, n_taps, smem_elems, splits, cplx);
+        if (rc) return rc;
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        std::memcpy(out_c64, h->h_out.p, sizeof(float2) * (size_t)n_ch * n_taps);
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_mc_correlate_device_async(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_b200_mc_args* args, const float* shifts,
+        uint32_t n_taps, uint32_t flags, const void* d_sig, uint64_t ch_stride_samples)
+    {
+        B200_REQUIRE(h && ch && args && shifts && d_sig, GNSS_B200_ERR_INVALID, "mc_correlate_device_async: null argument");
+        B200_REQUIRE(n_ch > 0 && n_ch <= h->max_channels && n_taps > 0 && n_taps <= h->max_taps, GNSS_B200_ERR_INVALID,
+            "mc_correlate_device_async: n_ch=%u n_taps=%u out of range", n_ch, n_taps);
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->device));
+        uint32_t smem_elems, splits;
+        bool cplx;
+        int rc = build_params(h, n_ch, ch, args, shifts, n_taps, flags, static_cast<const float2*>(d_sig), ch_stride_samples, true, &smem_elems, &splits, &cplx);
+        if (rc) return rc;
+        return run_batch(h, n_ch, n_taps, smem_elems, splits, cplx);
+    }
+
+    int gnss_b200_mc_sync(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, float* out_c64)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "mc_sync: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->device));
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        if (out_c64)
+            {
+                B200_REQUIRE(n_ch == h->last_n_ch && n_taps == h->last_n_taps, GNSS_B200_ERR_INVALID, "mc_sync: shape differs from the last batch");
+                std::memcpy(out_c64, h->h_out.p, sizeof(float2) * (size_t)n_ch * n_taps);
+            }
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_mc_chip_indices(gnss_b200_mc* h, uint32_t ch, const gnss_b200_mc_args* args, const float* shifts, uint32_t n_taps, uint32_t flags, int32_t* idx_out)
+    {
+        B200_REQUIRE(h && args && shifts && idx_out && n_taps > 0, GNSS_B200_ERR_INVALID, "mc_chip_indices: bad arguments");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->device));
+        uint32_t smem_elems, splits;
+        bool cplx;
+        gnss_b200_mc_args a = *args;
+        a.sig_in_c64 = nullptr;
+        a.stream_offset = 0;
+        const uint64_t keep = h->stream_len;
+        h->stream_len = ~0ull;  // windows are not dereferenced by this kernel
+        int rc = build_params(h, 1, &ch, &a, shifts, n_taps, flags, nullptr, 0, false, &smem_elems, &splits, &cplx);
+        h->stream_len = keep;
+        if (rc) return rc;
+        const size_t pbytes = sizeof(ChanParams) + sizeof(float) * n_taps + sizeof(uint32_t) * n_taps;
+        B200_CUDA(cudaMemcpyAsync(h->d_params.p, h->h_params.p, pbytes, cudaMemcpyHostToDevice, h->stream));
+        const size_t obytes = sizeof(int32_t) * (size_t)n_taps * a.n_samples;
+        B200_CUDA(h->d_idx.reserve(obytes));
+        const ChanParams* d_cp = h->d_params.as<ChanParams>();
+        const float* d_shifts = reinterpret_cast<const float*>(d_cp + 1);
+        const uint32_t* d_ss = reinterpret_cast<const uint32_t*>(d_shifts + n_taps);
+        chip_index_kernel<<<kNumSMs, 256, 0, h->stream>>>(*h->h_params.as<ChanParams>(), d_shifts, d_ss, (int)n_taps, h->d_idx.as<int32_t>());
+        h->launches++;
+        B200_CUDA(cudaGetLastError());
+        B200_CUDA(cudaMemcpyAsync(idx_out, h->d_idx.p, obytes, cudaMemcpyDeviceToHost, h->stream));
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        return GNSS_B200_OK;
+    }
+
+    void* gnss_b200_mc_stream(gnss_b200_mc* h) { return h ? (void*)h->stream : nullptr; }
+    uint64_t gnss_b200_mc_launch_count(const gnss_b200_mc* h) { return h ? h->launches : 0; }
+}

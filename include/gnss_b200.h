@@ -1,0 +1,231 @@
+/*
+ * gnss_b200.h — C-ABI of libgnss_b200.so, the B200-native GNSS correlation engine.
+ *
+ * Two data-parallel hot paths of GNSS-SDR (bobzhangbo2012/gnss-sdr-new) live behind
+ * this boundary, each implemented as hand-written sm_100a CUDA kernels:
+ *
+ *   (a) PCPS acquisition: the Doppler-grid loop of pcps_acquisition::acquisition_core
+ *       (reference: src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.cc:615-713)
+ *       batched over PRN x Doppler x code phase;
+ *   (b) the tracking multicorrelator: Cpu_Multicorrelator_Real_Codes /
+ *       Cpu_Multicorrelator::Carrier_wipeoff_multicorrelator_resampler
+ *       (reference: src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.cc:103-144,
+ *        cpu_multicorrelator.cc:87-101) batched over channels.
+ *
+ * Conventions
+ *   - every call returns 0 on success, a negative gnss_b200_status otherwise;
+ *     gnss_b200_last_error() returns a thread-local message for the last failure;
+ *   - no C++ or torch types cross the boundary: opaque handles, plain pointers, sizes;
+ *   - complex data is interleaved {re, im} float32 (gr_complex / lv_32fc_t layout);
+ *   - the caller owns all host buffers; the engine owns all device memory and its stream;
+ *   - a handle is serialised internally; distinct handles may be used concurrently;
+ *   - calls are synchronous unless named *_async (then pair with *_sync);
+ *   - there is NO CPU fallback: without a usable CUDA device create() fails.
+ */
+#ifndef GNSS_B200_H
+#define GNSS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C"
+{
+#endif
+
+#if defined(__GNUC__)
+#define GNSS_B200_API __attribute__((visibility("default")))
+#else
+#define GNSS_B200_API
+#endif
+
+    typedef enum
+    {
+        GNSS_B200_OK = 0,
+        GNSS_B200_ERR_INVALID = -1,     /* bad argument */
+        GNSS_B200_ERR_CUDA = -2,        /* CUDA runtime error (message in last_error) */
+        GNSS_B200_ERR_UNSUPPORTED = -3, /* e.g. FFT length with an unsupported prime factor */
+        GNSS_B200_ERR_NO_DEVICE = -4,   /* no CUDA device: the engine has no CPU path */
+        GNSS_B200_ERR_STATE = -5        /* call order violated (e.g. dwell before set_local_code) */
+    } gnss_b200_status;
+
+    GNSS_B200_API const char* gnss_b200_last_error(void);
+    GNSS_B200_API const char* gnss_b200_version(void);
+    GNSS_B200_API int gnss_b200_device_count(void);
+    /* Pin / unpin a caller-owned host buffer so copies run at full PCIe rate (optional). */
+    GNSS_B200_API int gnss_b200_host_register(void* ptr, size_t bytes);
+    GNSS_B200_API int gnss_b200_host_unregister(void* ptr);
+
+    /* ------------------------------------------------------------------ */
+    /* (a) PCPS acquisition                                                */
+    /* ------------------------------------------------------------------ */
+
+    /* Replaces the state set up by pcps_acquisition::pcps_acquisition (pcps_acquisition.cc:49-166)
+       and pcps_acquisition::init (:249-295) for a whole batch of PRN "slots" that share one
+       sample stream and one search geometry (one Acq_Conf, acq_conf.h:33-82). */
+    typedef struct
+    {
+        uint32_t fft_size;         /* d_fft_size (:85-92) — any length whose prime factors are <= 13 */
+        uint32_t consumed_samples; /* d_consumed_samples (:71) */
+        uint32_t bit_transition;   /* Acq_Conf::bit_transition_flag */
+        int32_t doppler_max;       /* Acq_Conf::doppler_max [Hz] */
+        uint32_t doppler_step;     /* d_doppler_step [Hz]; bins k = 0 .. ceil(2*max/step)-1 (:264) */
+        double fs;                 /* Acq_Conf::fs_in, or resampled_fs with the automatic resampler */
+        uint32_t samples_per_chip; /* d_samplesPerChip (exclusion half-width of the 2nd-peak test, :580-581) */
+        uint32_t use_cfar;         /* d_use_CFAR_algorithm_flag: 1 = max/input-power (:511-543), 0 = 1st/2nd peak (:546-612) */
+        uint32_t keep_grid;        /* 1 = persistent magnitude grid per slot (needed for max_dwells > 1 or dump);
+                                      0 = fused search, the grid never reaches HBM (single-dwell searches) */
+        uint32_t max_slots;        /* number of PRN slots (each = one reference pcps_acquisition instance) */
+        int32_t device;            /* CUDA device ordinal */
+        /* Doppler rows [row_begin, row_end) searched by THIS handle; 0,0 = all rows. Lets one PRN's grid be
+           sharded across GPUs; merge with gnss_b200_acq_read_rows + gnss_b200_acq_finalize_rows. */
+        uint32_t row_begin, row_end;
+    } gnss_b200_acq_cfg;
+
+    /* What acquisition_core leaves behind for one PRN after one dwell (:688-713). */
+    typedef struct
+    {
+        float test_statistic;   /* d_test_statistics */
+        float peak;             /* grid_maximum / firstPeak */
+        float input_power;      /* d_input_power (CFAR only) */
+        float second_peak;      /* secondPeak (1st/2nd-peak test only) */
+        uint32_t code_phase;    /* indext */
+        uint32_t doppler_index; /* index_doppler */
+        int32_t doppler_hz;     /* -doppler_max + doppler_center + step*index (:535) */
+        uint32_t dwell_count;   /* d_num_noncoherent_integrations_counter after this dwell */
+    } gnss_b200_acq_result;
+
+    /* Per-Doppler-row reduction record (exchange unit when rows are sharded over GPUs). */
+    typedef struct
+    {
+        float max_val;    /* max over code phase of the (accumulated) |.|^2 row */
+        uint32_t max_idx; /* lowest code-phase index attaining it (volk_gnsssdr_32f_index_max_32u tie rule) */
+        float row_sum;    /* sum over the effective row (input-power estimate, :534) */
+        uint32_t valid;   /* 1 if this handle computed the row */
+    } gnss_b200_acq_row;
+
+    typedef struct gnss_b200_acq gnss_b200_acq;
+
+    GNSS_B200_API int gnss_b200_acq_create(const gnss_b200_acq_cfg* cfg, gnss_b200_acq** out);
+    GNSS_B200_API int gnss_b200_acq_destroy(gnss_b200_acq* h);
+    GNSS_B200_API uint32_t gnss_b200_acq_num_doppler_bins(const gnss_b200_acq* h);
+
+    /* pcps_acquisition::set_local_code (:176-209). `code_c64` is the adapter's time-domain code
+       (consumed_samples complex values; fft_size/2 are read when bit_transition). The zero-pad layout,
+       forward FFT and conjugation run on the device. */
+    GNSS_B200_API int gnss_b200_acq_set_local_code(gnss_b200_acq* h, uint32_t slot, const float* code_c64);
+    /* Batch form: codes_c64 = [n_slots][consumed_samples] for slots[0..n_slots). */
+    GNSS_B200_API int gnss_b200_acq_set_local_codes(gnss_b200_acq* h, uint32_t n_slots, const uint32_t* slots, const float* codes_c64);
+
+    /* pcps_acquisition::set_doppler_center (pcps_acquisition.h:199-208) plus the FDMA bias of is_fdma() (:212-230). */
+    GNSS_B200_API int gnss_b200_acq_set_doppler_center(gnss_b200_acq* h, uint32_t slot, int32_t center_hz, int32_t bias_hz);
+
+    /* Zero the slot's grid and dwell counter (init() :281-284, :879). */
+    GNSS_B200_API int gnss_b200_acq_reset(gnss_b200_acq* h, uint32_t slot);
+
+    /* One coherent dwell (one acquisition_core pass, :615-713) for a batch of slots on ONE sample block.
+       samples: consumed_samples items, gr_complex (is_cshort = 0) or lv_16sc_t (is_cshort = 1, :623-626).
+       results[i] belongs to slots[i]. */
+    GNSS_B200_API int gnss_b200_acq_dwell(gnss_b200_acq* h, const void* samples, int is_cshort,
+        uint32_t n_slots, const uint32_t* slots, gnss_b200_acq_result* results);
+
+    /* Same, with the sample block already resident in device memory (gr_complex only) and no host
+       synchronisation: results land in the handle's pinned result buffer; call _sync to wait and fetch. */
+    GNSS_B200_API int gnss_b200_acq_dwell_device_async(gnss_b200_acq* h, const void* d_samples,
+        uint32_t n_slots, const uint32_t* slots);
+    GNSS_B200_API int gnss_b200_acq_sync(gnss_b200_acq* h, uint32_t n_slots, gnss_b200_acq_result* results);
+
+    /* The accumulated magnitude grid of one slot, [n_doppler][effective_size] float32 (the content of the
+       reference's d_magnitude_grid / MAT dump `acq_grid`, :433-434,:684). Requires keep_grid = 1. */
+    GNSS_B200_API int gnss_b200_acq_read_grid(gnss_b200_acq* h, uint32_t slot, float* out);
+
+    /* Row records of the last dwell for one slot: rows[n_doppler]. */
+    GNSS_B200_API int gnss_b200_acq_read_rows(gnss_b200_acq* h, uint32_t slot, gnss_b200_acq_row* rows);
+    /* Pure host function: cross-row decision of max_to_input_power_statistic (:511-543) from (merged) row
+       records. Only the CFAR statistic can be finalised from records alone. */
+    GNSS_B200_API int gnss_b200_acq_finalize_rows(const gnss_b200_acq_row* rows, uint32_t n_doppler, uint32_t effective_size,
+        int32_t doppler_max, uint32_t doppler_step, int32_t doppler_center, uint32_t dwell_count, gnss_b200_acq_result* out);
+
+    /* calculate_threshold (:894-909): 2 * gamma_p_inv(2*dof_dwells, (1-pfa)^(1/num_bins)). Host only. */
+    GNSS_B200_API float gnss_b200_acq_threshold(float pfa, uint32_t effective_size, uint32_t n_doppler, uint32_t max_dwells, int bit_transition);
+
+    /* The CUDA stream (cudaStream_t) the handle launches on, and the number of kernel launches it has issued
+       (for event timing and launch accounting by the caller). */
+    GNSS_B200_API void* gnss_b200_acq_stream(gnss_b200_acq* h);
+    GNSS_B200_API uint64_t gnss_b200_acq_launch_count(const gnss_b200_acq* h);
+
+    /* ------------------------------------------------------------------ */
+    /* (b) tracking multicorrelator                                        */
+    /* ------------------------------------------------------------------ */
+
+    /* Arguments of one Carrier_wipeoff_multicorrelator_resampler call
+       (cpu_multicorrelator_real_codes.cc:103-110), for one channel of a batch. */
+    typedef struct
+    {
+        const float* sig_in_c64;     /* d_sig_in (host pointer), or NULL to window the shared stream */
+        uint64_t stream_offset;      /* first sample in the shared stream when sig_in_c64 == NULL */
+        uint32_t n_samples;          /* signal_length_samples */
+        float rem_carr_phase_rad;    /* rem_carrier_phase_in_rad */
+        float carr_step_rad;         /* phase_step_rad */
+        float carr_rate_rad;         /* phase_rate_step_rad (high-dynamics rotator only) */
+        float rem_code_phase_chips;  /* rem_code_phase_chips */
+        float code_step_chips;       /* code_phase_step_chips */
+        float code_rate_chips;       /* code_phase_rate_step_chips (high-dynamics resampler only) */
+    } gnss_b200_mc_args;
+
+    enum
+    {
+        GNSS_B200_MC_HIGH_DYN = 1, /* d_use_high_dynamics_resampler = true (set_high_dynamics_resampler) */
+        GNSS_B200_MC_SIX_ARG = 2   /* the 6-argument overload (:129-144): plain rotator even when HIGH_DYN */
+    };
+
+    typedef struct gnss_b200_mc gnss_b200_mc;
+
+    /* Cpu_Multicorrelator_Real_Codes::init (:36-49) for `max_channels` correlator objects at once. */
+    GNSS_B200_API int gnss_b200_mc_create(uint32_t max_channels, uint32_t max_samples, uint32_t max_taps, int32_t device, gnss_b200_mc** out);
+    GNSS_B200_API int gnss_b200_mc_destroy(gnss_b200_mc* h);
+
+    /* set_local_code_and_taps (:52-62), code part: copies the local code of channel `ch` to the device.
+       is_complex = 0: `code` holds code_len float32 (Cpu_Multicorrelator_Real_Codes);
+       is_complex = 1: code_len interleaved complex (Cpu_Multicorrelator, cpu_multicorrelator.cc:50-60). */
+    GNSS_B200_API int gnss_b200_mc_set_code(gnss_b200_mc* h, uint32_t ch, uint32_t code_len, const float* code, int is_complex);
+
+    /* Upload a sample stream shared by all channels (the signal-conditioner output every tracking block
+       reads, gnss_flowgraph.cc:1129-1135); channels then window it through stream_offset. */
+    GNSS_B200_API int gnss_b200_mc_set_stream(gnss_b200_mc* h, const float* samples_c64, uint64_t n_samples);
+
+    /* One correlation epoch for n_ch channels. shifts = [n_ch][n_taps] (d_shifts_chips, re-read on every
+       call: the reference mutates the borrowed array in place, dll_pll_veml_tracking.cc:1961-1979).
+       out_c64 = [n_ch][n_taps] (d_corr_out). */
+    GNSS_B200_API int gnss_b200_mc_correlate_batch(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch,
+        const gnss_b200_mc_args* args, const float* shifts, uint32_t n_taps, uint32_t flags, float* out_c64);
+
+    /* Device-resident form for throughput measurement: d_sig is [n_ch][max_samples] complex in device memory
+       (independent per-channel streams), no host synchronisation; fetch with _sync. */
+    GNSS_B200_API int gnss_b200_mc_correlate_device_async(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch,
+        const gnss_b200_mc_args* args, const float* shifts, uint32_t n_taps, uint32_t flags, const void* d_sig, uint64_t ch_stride_samples);
+    GNSS_B200_API int gnss_b200_mc_sync(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, float* out_c64);
+
+    /* Debug / parity aid: wrapped chip index of every (tap, sample) of one channel, as the kernel computes it. */
+    GNSS_B200_API int gnss_b200_mc_chip_indices(gnss_b200_mc* h, uint32_t ch, const gnss_b200_mc_args* args,
+        const float* shifts, uint32_t n_taps, uint32_t flags, int32_t* idx_out /* [n_taps][n_samples] */);
+
+    GNSS_B200_API void* gnss_b200_mc_stream(gnss_b200_mc* h);
+    GNSS_B200_API uint64_t gnss_b200_mc_launch_count(const gnss_b200_mc* h);
+
+    /* ------------------------------------------------------------------ */
+    /* parity aids (pure host, no device needed)                           */
+    /* ------------------------------------------------------------------ */
+
+    /* The binary32 running-sum phase of the reference's wipe-off row for one Doppler bin
+       (volk_gnsssdr_s32f_sincos_32fc_generic, volk_gnsssdr_s32f_sincos_32fc.h:390-400), as reproduced in closed
+       form by the engine: phase_out[n], n < n_samples. n_pieces (optional) = number of linear pieces used. */
+    GNSS_B200_API int gnss_b200_debug_wipeoff_phase(int32_t doppler_hz_with_bias, double fs, uint32_t n_samples, float* phase_out, uint32_t* n_pieces);
+    /* The FFT plan for length n: number of stages, radices (lowest stride first) and the position -> frequency
+       permutation of the forward transform's output (any of the out pointers may be NULL). */
+    GNSS_B200_API int gnss_b200_debug_fft_plan(uint32_t n, uint32_t* n_stages, uint32_t* radices, uint32_t* n_radices, uint32_t* perm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNSS_B200_H */

@@ -1,0 +1,172 @@
+"""The oracle against the reference's own known answers — CPU only.
+
+Pins:  * the two in-tree IQ captures with the expected values of the reference's unit tests
+         (gps_l1_ca_pcps_acquisition_test.cc:290-291,354-361; galileo_e1_pcps_ambiguous_acquisition_test.cc:304-305,359-369);
+       * the oracle's restated kernels bit-for-bit against the reference's generic volk_gnsssdr kernels
+         and against the reference's Cpu_Multicorrelator classes (oracle/_ref, container only);
+       * the samplers against digests of the reference generators' output.
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests/golden")
+
+
+def test_fft_matches_numpy(oracle):
+    rng = np.random.default_rng(0)
+    for n in (8, 97, 1009, 4000, 6625, 16000, 2 * 3 * 5 * 7 * 11 * 13):
+        x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+        ref = np.fft.fft(x.astype(np.complex128))
+        assert np.abs(oracle.fft(x, -1) - ref).max() / np.abs(ref).max() < 5e-7
+        refi = np.fft.ifft(x.astype(np.complex128)) * n  # unnormalised backward, FFTW convention
+        assert np.abs(oracle.fft(x, +1) - refi).max() / np.abs(refi).max() < 5e-7
+        y64 = oracle.fft(x.astype(np.complex128), -1)
+        assert np.abs(y64 - ref).max() / np.abs(ref).max() < 1e-13
+
+
+def _gps_capture_acq(orc, use_cfar, step=100):
+    d = np.fromfile(os.path.join(GOLD, "GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat"), dtype=np.complex64)
+    code = synth.adapter_code("gps_l1_ca", 1, 4000000, 1)
+    a = orc.acq(fft_size=4000, consumed_samples=4000, doppler_max=5000, doppler_step=step, fs=4e6,
+                samples_per_chip=4, samples_per_code=4000.0, use_cfar=use_cfar)
+    a.set_local_code(code)
+    a.reset()
+    return a, a.dwell(d[:4000])
+
+
+def test_gps_capture_known_answer(oracle):
+    # reference test config: doppler_max 5000, doppler_step 100, threshold 0.001, no pfa -> 1st/2nd peak statistic
+    a, r = _gps_capture_acq(oracle, use_cfar=False)
+    assert a.n_doppler == 100
+    assert r["test_statistic"] > 0.001  # positive acquisition
+    assert abs(r["acq_delay_samples"] - 524) < 0.5 * 4000 / 1023   # delay within 0.5 chip of 524 samples
+    assert abs(r["doppler_hz"] - 1680) <= 666                      # 2/(3*1ms)
+    assert r["code_phase"] == 524 and r["doppler_hz"] == 1700
+    assert r["test_statistic"] == pytest.approx(132.466, rel=1e-4)  # value re-derived in SURVEY.md §8c
+    _, r2 = _gps_capture_acq(oracle, use_cfar=True)
+    assert r2["code_phase"] == 524 and r2["test_statistic"] == pytest.approx(2577.16, rel=1e-4)
+
+
+def test_galileo_capture_known_answer(oracle):
+    d = np.fromfile(os.path.join(GOLD, "Galileo_E1_ID_1_Fs_4Msps_8ms.dat"), dtype=np.complex64)
+    code = synth.adapter_code("gal_e1b", 1, 4000000, 4)
+    a = oracle.acq(fft_size=16000, consumed_samples=16000, doppler_max=10000, doppler_step=250, fs=4e6,
+                   samples_per_chip=4, samples_per_code=16000.0, use_cfar=False)
+    a.set_local_code(code)
+    a.reset()
+    r = a.dwell(d[:16000])
+    assert a.n_doppler == 80
+    assert r["test_statistic"] > 1e-5
+    assert abs(r["acq_delay_samples"] - 2920) < 0.175 * 16000 / 4092 * 4  # 0.175 chip at ~3.91 samples/chip
+    assert abs(r["doppler_hz"] - (-632)) <= 166
+    assert r["code_phase"] == 2920 and r["doppler_hz"] == -750
+    assert r["test_statistic"] == pytest.approx(124.2028, rel=1e-4)
+
+
+def test_restated_kernels_equal_reference_kernels(oracle, ref_oracle):
+    """Same glue over (a) the restated kernels and (b) the reference's own generic kernels: bit-identical."""
+    assert oracle.flavour == "restated" and ref_oracle.flavour == "reference-generic"
+    res = []
+    for orc in (oracle, ref_oracle):
+        a, r = _gps_capture_acq(orc, use_cfar=True, step=250)
+        res.append((r, a.grid(), a.wipeoffs(), a.fft_codes()))
+    assert res[0][0] == res[1][0]
+    for i in (1, 2, 3):
+        assert np.array_equal(res[0][i], res[1][i])
+    # cshort input path
+    d = np.fromfile(os.path.join(GOLD, "GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat"), dtype=np.complex64)[:4000]
+    ds = synth.to_cshort(d, scale=2000.0)
+    outs = []
+    for orc in (oracle, ref_oracle):
+        a = orc.acq(fft_size=4000, consumed_samples=4000, doppler_max=5000, doppler_step=250, fs=4e6,
+                    samples_per_chip=4, samples_per_code=4000.0, use_cfar=True)
+        a.set_local_code(synth.adapter_code("gps_l1_ca", 1, 4000000, 1))
+        a.reset()
+        outs.append(a.dwell(ds))
+    assert outs[0] == outs[1] and outs[0]["code_phase"] == 524
+
+
+def _mc_case(rng, n, code_len, ntaps):
+    sig = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    code = rng.choice([-1.0, 1.0], code_len).astype(np.float32)
+    shifts = np.sort(rng.uniform(-1, 1, ntaps)).astype(np.float32)
+    args = dict(rem_carr=float(rng.uniform(0, 6.28)), carr_step=float(rng.uniform(-2e-3, 2e-3)), carr_rate=float(rng.uniform(-1e-9, 1e-9)),
+                rem_code=float(rng.uniform(0, 1)), code_step=float(rng.uniform(0.2, 0.6)), code_rate=float(rng.uniform(-1e-9, 1e-9)))
+    return sig, code, shifts, args
+
+
+@pytest.mark.parametrize("high_dyn,six", [(False, False), (True, False), (True, True)])
+def test_multicorrelator_oracle_equals_reference_class(oracle, ref_libs, high_dyn, six):
+    """oracle_mc.c (own glue + restated kernels) vs the reference's Cpu_Multicorrelator_Real_Codes class: bit-identical."""
+    rng = np.random.default_rng(7)
+    for n, L, T in ((2048, 1023, 3), (4000, 1023, 5), (8111, 10230, 11)):
+        sig, code, shifts, a = _mc_case(rng, n, L, T)
+        o = oracle.mc_real(sig, code, shifts, high_dyn=high_dyn, six_arg=six, **a)
+        r = ref_libs.mc_real(sig, code, shifts, high_dyn=high_dyn, six_arg=six, **a)
+        assert np.array_equal(o.view(np.float32), r.view(np.float32))
+
+
+def test_multicorrelator_complex_oracle_equals_reference_class(oracle, ref_libs):
+    rng = np.random.default_rng(8)
+    sig, code, shifts, a = _mc_case(rng, 4000, 511, 3)
+    ccode = (code[:511] + 1j * rng.choice([-1.0, 1.0], 511)).astype(np.complex64)
+    o = oracle.mc_cplx(sig, ccode, shifts, a["rem_carr"], a["carr_step"], a["rem_code"], a["code_step"])
+    r = ref_libs.mc_cplx(sig, ccode, shifts, a["rem_carr"], a["carr_step"], a["rem_code"], a["code_step"])
+    assert np.array_equal(o.view(np.float32), r.view(np.float32))
+
+
+def test_samplers_match_reference_digests(oracle):
+    """numpy samplers (tools/synth.py) and C samplers (oracle_codes.c) reproduce the reference generators' output."""
+    dig = json.load(open(os.path.join(GOLD, "sampled_code_sha256.json")))
+    for key, want in dig.items():
+        system, prn, fs = key.split("/")
+        prn, fs = int(prn), int(fs)
+        got = synth.local_code(system, prn, fs)
+        assert hashlib.sha256(got.tobytes()).hexdigest() == want, key
+        ch = synth.chips(system, prn)
+        c = {"gps_l1_ca": oracle.sample_gps_l1_ca, "bds_b1i": oracle.sample_beidou_b1i,
+             "gal_e1b": oracle.sample_galileo_e1, "gps_l5i": oracle.sample_gps_l5i}[system](ch, fs)
+        assert hashlib.sha256(c.tobytes()).hexdigest() == want, key
+
+
+def test_chip_fixture_matches_reference_generators(ref_libs):
+    ch = synth.load_chips()
+    assert np.array_equal(ch["gps_l1_ca"][9], ref_libs.gps_l1_ca_chips(10))
+    assert np.array_equal(ch["bds_b1i"][62], ref_libs.beidou_b1i_chips(63))
+    assert np.array_equal(ch["gal_e1b"][49], ref_libs.galileo_e1_chips(50))
+    assert np.array_equal(ch["gal_e1c"][0], ref_libs.galileo_e1_chips(1, pilot=True))
+    assert np.array_equal(ch["gps_l5i"][31], ref_libs.gps_l5_chips(32))
+
+
+def test_gamma_p_inv_against_scipy(oracle):
+    from scipy.special import gammaincinv
+    for a in (2.0, 4.0, 20.0):
+        for p in (1e-6, 0.3, 0.999, 1 - 1e-9):
+            assert oracle.gamma_p_inv(a, p) == pytest.approx(float(gammaincinv(a, p)), rel=1e-10 if p < 0.9999 else 1e-7)  # near 1, p itself limits the inverse
+    # calculate_threshold for the GSoC-2013 test geometry (pfa 0.001, 4000 x 80 cells)
+    want = 2.0 * float(gammaincinv(2.0, (1.0 - float(np.float32(0.001))) ** (1.0 / float(np.float32(4000 * 80)))))
+    assert oracle.threshold(0.001, 4000, 80) == pytest.approx(want, rel=1e-6)
+
+
+def test_gsoc2013_synthetic_case(oracle):
+    """gps_l1_ca_pcps_acquisition_gsoc2013_test.cc:204-263: PRN 10, 600 chips, 750 Hz, noise-free, pfa 0.001, +-10 kHz / 250 Hz."""
+    fs = 4000000
+    delay = int(round(600 * 4000 / 1023))
+    iq = synth.make_iq(4000, fs, [dict(system="gps_l1_ca", prn=10, delay=delay, doppler=750.0, cn0=90.0, phase=0.3)], seed=11,
+                       noise_sigma2=1e-12)
+    a = oracle.acq(fft_size=4000, consumed_samples=4000, doppler_max=10000, doppler_step=250, fs=fs,
+                   samples_per_chip=4, samples_per_code=4000.0, use_cfar=True)
+    a.set_local_code(synth.adapter_code("gps_l1_ca", 10, fs, 1))
+    a.reset()
+    r = a.dwell(iq)
+    thr = oracle.threshold(0.001, 4000, a.n_doppler)
+    assert r["test_statistic"] > thr
+    assert abs(r["acq_delay_samples"] - delay) < 0.5 * 4000 / 1023
+    assert abs(r["doppler_hz"] - 750) < 2.0 / (3.0 * 1e-3)

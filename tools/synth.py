@@ -1,0 +1,197 @@
+"""Seeded synthetic inputs for tests and bench: PRN chips from the golden fixture, local codes
+sampled the way the reference's acquisition adapters sample them, and IQ blocks with injected satellites + AWGN
+following the recipe of the reference's in-tree generator (src/algorithms/signal_generator/gnuradio_blocks/
+signal_generator_c.cc:326-420) with fixed seeds.
+
+This module is input generation only: it does not import oracle/ and is not part of the product path.
+The numpy float32 arithmetic below restates (and tests check bit-for-bit against) the reference samplers:
+  gps_l1_ca_code_gen_complex_sampled   src/algorithms/libs/gps_sdr_signal_replica.cc:136-176
+  beidou_b1i_code_gen_complex_sampled  src/algorithms/libs/beidou_b1i_signal_replica.cc:130-170
+  galileo_e1_code_gen_complex_sampled  src/algorithms/libs/galileo_e1_signal_replica.cc:143-228 (cboc=false)
+  resampler                            src/algorithms/libs/gnss_signal_replica.cc:257-272
+"""
+import json
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_f32 = np.float32
+_chips_cache = None
+
+SYSTEMS = {
+    # name: (chip_rate, code_len, ms_per_code)
+    "gps_l1_ca": (1023000, 1023, 1),
+    "bds_b1i": (2046000, 2046, 1),
+    "gal_e1b": (1023000, 4092, 4),
+    "gal_e1c": (1023000, 4092, 4),
+    "gps_l5i": (10230000, 10230, 1),
+    "gps_l5q": (10230000, 10230, 1),
+}
+
+
+def load_chips():
+    """{system: int8 [n_prn][code_len] of +1/-1} from tests/golden/prn_chips.npz."""
+    global _chips_cache
+    if _chips_cache is None:
+        z = np.load(os.path.join(ROOT, "tests/golden/prn_chips.npz"))
+        lens = json.loads(str(z["lengths"]))
+        out = {}
+        for k, n in lens.items():
+            bits = np.unpackbits(z[k], axis=1)[:, :n]
+            out[k] = (bits.astype(np.int8) * 2 - 1)
+        _chips_cache = out
+    return _chips_cache
+
+
+def chips(system, prn):
+    return load_chips()[system][prn - 1]
+
+
+def _aux_ceil(x_f32):
+    return (x_f32 + _f32(1)).astype(np.int64).astype(np.int32)
+
+
+def samples_per_code(fs, chip_rate, code_len):
+    return int(float(fs) / (float(chip_rate) / float(code_len)))
+
+
+def sample_lfsr_style(ch, chip_rate, fs, imag_code, tc_via_double):
+    code_len = ch.size
+    n = samples_per_code(fs, chip_rate, code_len)
+    tc = _f32(1.0 / float(_f32(chip_rate))) if tc_via_double else _f32(1) / _f32(chip_rate)
+    ts = _f32(1) / _f32(fs)
+    i = np.arange(n, dtype=np.float32)
+    aux = (ts * (i + _f32(1))) / tc
+    idx = _aux_ceil(aux) - 1
+    idx[n - 1] = code_len - 1
+    v = ch[idx].astype(np.float32)
+    out = np.zeros(n, dtype=np.complex64)
+    if imag_code:
+        out.imag = v
+    else:
+        out.real = v
+    return out
+
+
+def sample_e1_sinboc11(ch, fs):
+    code_len, chip_rate, spchip = 4092, 1023000, 2
+    boc = np.empty(2 * code_len, dtype=np.float32)
+    boc[0::2] = ch
+    boc[1::2] = -ch.astype(np.float32)
+    n = int(float(fs) / (float(chip_rate) / code_len))
+    if fs != spchip * chip_rate:
+        fs_in = _f32(spchip * chip_rate)
+        t_out = _f32(1) / _f32(fs)
+        i = np.arange(n - 1, dtype=np.float32)
+        aux = (t_out * (i + _f32(1))) * fs_in
+        res = np.empty(n, dtype=np.float32)
+        res[: n - 1] = boc[_aux_ceil(aux) - 1]
+        res[n - 1] = boc[-1]
+    else:
+        res = boc
+    return res.astype(np.complex64)
+
+
+def sample_l5(ch, fs):
+    code_len, chip_rate = 10230, 10230000
+    n = samples_per_code(fs, chip_rate, code_len)
+    tc = _f32(1.0 / float(_f32(chip_rate)))
+    ts = _f32(1) / _f32(fs)
+    i = np.arange(n, dtype=np.float32)
+    idx = np.ceil(ts * (i + _f32(1)) / tc).astype(np.int32) - 1
+    idx[n - 1] = code_len - 1
+    return ch[idx].astype(np.float32).astype(np.complex64)
+
+
+def local_code(system, prn, fs):
+    """One code period sampled at fs, as the adapter's set_local_code() generates it."""
+    ch = chips(system, prn)
+    if system == "gps_l1_ca":
+        return sample_lfsr_style(ch, 1023000, fs, True, False)
+    if system == "bds_b1i":
+        return sample_lfsr_style(ch, 2046000, fs, False, True)
+    if system in ("gal_e1b", "gal_e1c"):
+        return sample_e1_sinboc11(ch, fs)
+    if system in ("gps_l5i", "gps_l5q"):
+        return sample_l5(ch, fs)
+    raise KeyError(system)
+
+
+def adapter_code(system, prn, fs, sampled_ms):
+    """The vector the adapter hands to pcps_acquisition::set_local_code: the code period replicated over the
+    coherent time (gps_l1_ca_pcps_acquisition.cc:163-167, galileo_e1_pcps_ambiguous_acquisition.cc:190-194)."""
+    ms_per_code = SYSTEMS[system][2]
+    one = local_code(system, prn, fs)
+    reps = max(1, sampled_ms // ms_per_code)
+    return np.tile(one, reps)
+
+
+def make_iq(n_samples, fs, sats, seed, noise_sigma2=1.0):
+    """IQ block: sum of satellites + complex AWGN of total variance noise_sigma2.
+
+    sats: list of dict(system, prn, delay (samples, int), doppler (Hz), cn0 (dB-Hz), phase (rad, optional))
+    Amplitude follows the reference generator: sqrt(10^(CN0/10) / BW / 2) * sqrt(2) per unit-variance noise,
+    i.e. signal power / noise power = CN0 / fs.
+    """
+    rng = np.random.default_rng(seed)
+    x = (rng.standard_normal(n_samples) + 1j * rng.standard_normal(n_samples)) * np.sqrt(noise_sigma2 / 2.0)
+    n = np.arange(n_samples, dtype=np.float64)
+    for s in sats:
+        code = local_code(s["system"], s["prn"], fs)
+        # unit-modulus code value (GPS local code is purely imaginary; its modulus is what carries power)
+        c = np.where(np.abs(code.real) > 0, code.real, code.imag).astype(np.float64)
+        idx = (np.arange(n_samples) - int(s["delay"])) % code.size
+        amp = np.sqrt(noise_sigma2 * 10.0 ** (s["cn0"] / 10.0) / fs)
+        ph = s.get("phase", float(rng.uniform(0, 2 * np.pi)))
+        x = x + amp * c[idx] * np.exp(1j * (2.0 * np.pi * s["doppler"] * n / fs + ph))
+    return x.astype(np.complex64)
+
+
+def to_cshort(x, scale=64.0):
+    """gr_complex -> interleaved int16 (lv_16sc_t) the way a front-end delivers 'cshort' items."""
+    y = np.empty(2 * x.size, dtype=np.int16)
+    y[0::2] = np.clip(np.rint(x.real * scale), -32768, 32767)
+    y[1::2] = np.clip(np.rint(x.imag * scale), -32768, 32767)
+    return y
+
+
+# BASELINE.json configs made concrete
+CONFIGS = {
+    "C1": dict(system="gps_l1_ca", fs=4000000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=32,
+               present=[1, 3, 7, 10, 15, 21, 22, 30], cn0=(38, 50), seed=0),
+    "C2": dict(system="gal_e1b", fs=8000000, sampled_ms=4, doppler_max=5000, doppler_step=125, n_prn=50,
+               present=[1, 4, 9, 11, 19, 24, 27, 30, 36, 44], cn0=(36, 48), seed=2),
+    "C4_gps": dict(system="gps_l1_ca", fs=25000000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=32,
+                   present=[2, 5, 9, 13, 17, 23, 26, 31], cn0=(38, 50), seed=4),
+    "C4_gal": dict(system="gal_e1b", fs=25000000, sampled_ms=4, doppler_max=5000, doppler_step=250, n_prn=36,
+                   present=[2, 7, 8, 12, 21, 25, 31, 33], cn0=(36, 48), seed=5),
+    "C4_bds": dict(system="bds_b1i", fs=25000000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=63,
+                   present=[1, 6, 9, 14, 19, 27, 33, 40, 52, 60], cn0=(38, 50), seed=6),
+}
+
+
+def config_scene(name, n_prn=None):
+    """(geometry dict, codes [n_prn][consumed] c64, iq [consumed] c64, truth list) for a named config."""
+    c = CONFIGS[name]
+    chip_rate, _, ms_per_code = SYSTEMS[c["system"]]
+    fs = c["fs"]
+    n_prn = n_prn or c["n_prn"]
+    consumed = int(c["sampled_ms"] * float(_f32(_f32(fs) * _f32(0.001))))
+    fft_size = consumed if c["sampled_ms"] == ms_per_code else 2 * consumed
+    rng = np.random.default_rng(1000 + c["seed"])
+    one_len = local_code(c["system"], 1, fs).size
+    truth = []
+    for prn in c["present"]:
+        if prn > n_prn:
+            continue
+        truth.append(dict(system=c["system"], prn=prn, delay=int(rng.integers(0, one_len)),
+                          doppler=float(rng.uniform(-0.9, 0.9) * c["doppler_max"]) + 13.7,
+                          cn0=float(rng.uniform(*c["cn0"]))))
+    iq = make_iq(consumed, fs, truth, c["seed"])
+    codes = np.stack([adapter_code(c["system"], p, fs, c["sampled_ms"])[:consumed] for p in range(1, n_prn + 1)])
+    geo = dict(fft_size=fft_size, consumed_samples=consumed, fs=fs, doppler_max=c["doppler_max"],
+               doppler_step=c["doppler_step"], samples_per_chip=int(np.ceil(float(_f32(fs) / _f32(chip_rate)))),
+               samples_per_code=float(_f32(_f32(_f32(fs) * _f32(0.001)) * _f32(ms_per_code))), n_prn=n_prn,
+               system=c["system"], sampled_ms=c["sampled_ms"])
+    return geo, codes.astype(np.complex64), iq, truth
