@@ -56,8 +56,12 @@ int launch_stage(gnss_b200_acq* h, const StageArgs& a, uint32_t n_transforms)
     static thread_local size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured)
         {
-            B200_CUDA(cudaFuncSetAttribute(stage_kernel<LOAD, STORE, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            configured = 227 * 1024;
+            cudaFuncAttributes fa;
+            B200_CUDA(cudaFuncGetAttributes(&fa, stage_kernel<LOAD, STORE, INV>));
+            const size_t max_dyn = 227 * 1024 - fa.sharedSizeBytes;  // static + dynamic <= 227 KiB per CTA on sm_100
+            B200_REQUIRE(smem <= max_dyn, GNSS_B200_ERR_UNSUPPORTED, "FFT tile of %zu bytes exceeds shared memory", smem);
+            B200_CUDA(cudaFuncSetAttribute(stage_kernel<LOAD, STORE, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_dyn));
+            configured = max_dyn;
         }
     const dim3 grid(n_transforms, a.st.tiles);
     stage_kernel<LOAD, STORE, INV><<<grid, a.st.threads, smem, h->stream>>>(a);

@@ -145,7 +145,8 @@ def test_full_size_config5_properties(b200, oracle):
     codes, sigs, args, shifts = _scene(rng, 64, 30000, 10230, 11)
     _, _, got = _run_gpu(b200, codes, sigs, args, shifts)
     prompt = np.abs(got[:, 5])
-    assert (prompt > 3 * np.abs(got[:, 0])).all() and (prompt > 3 * np.abs(got[:, 10])).all()
+    far = 0.5 * (np.abs(got[:, 0]) + np.abs(got[:, 10]))  # +-1 chip taps: noise only (~sqrt(N) sigma)
+    assert (prompt > 2 * far).all() and prompt.mean() > 4 * far.mean()
     want = _run_oracle(oracle, codes[:2], sigs[:2], args[:2], shifts[:2])
     assert _rel_err(got[:2], want) < RTOL
 
