@@ -1,0 +1,401 @@
+#!/usr/bin/env python3
+"""bench.py — acquisition cells/s (headline, BASELINE config 2) and tracking channel-ms/s (config 5) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C2|C1]
+
+One "step" = one coherent dwell of the whole PRN x Doppler x code-phase grid of the workload on one batch of
+synthetic IQ (ours: through libgnss_b200.so; reference: the CPU path on the host cores).
+  value  : cells/s with the sample block already resident in HBM (device-timed with CUDA events on the engine stream)
+  e2e    : cells/s through the C-ABI call a GNSS-SDR adapter makes, HOST sample buffer in, host results out
+  N > 1  : one process per GPU (torchrun); every rank searches the full workload on its own sample block (weak scaling),
+           per-PRN results are all-gathered with NCCL inside the step.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tools")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import synth  # noqa: E402
+
+METRIC = "acq_cells_per_s"
+UNIT = "cells/s"
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    def __init__(self, index=0):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def acq_flops_per_cell(n):
+    return 10.0 * math.log2(n) + 17.0
+
+
+# ----------------------------------------------------------------------------------------------
+# reference arm: the CPU implementation of the same path on the host cores
+# ----------------------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from b200_import import load_oracle
+    load_oracle()
+    import oracle_fast
+    geo, codes, iq, _ = synth.config_scene(args.workload)
+    cores = oracle_fast.host_cores()
+    n_prn_sample = min(geo["n_prn"], max(cores, 8))  # bounded sample: one PRN per host thread, at least 8
+    fa = oracle_fast.FastAcq(geo["fft_size"], geo["consumed_samples"], geo["doppler_max"], geo["doppler_step"], geo["fs"],
+                             geo["samples_per_chip"], use_cfar=True, workers=cores)
+    specs = [fa.code_spectrum(c) for c in codes[:n_prn_sample]]
+    cells = n_prn_sample * fa.nD * fa.eff
+    for _ in range(args.warmup):
+        fa.dwell_all_like_reference(iq, specs)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        fa.dwell_all_like_reference(iq, specs)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = cells / dt
+    sample = (f"{n_prn_sample} of {geo['n_prn']} PRNs x {fa.nD} Doppler bins x {fa.eff} code phases per step, one thread per PRN "
+              f"(reference structure: per-channel forward+inverse FFT); numpy/scipy pocketfft complex64 port of "
+              f"pcps_acquisition::acquisition_core — CPU FFT = pocketfft, not FFTW (FFTW/GNU Radio/VOLK not installable here)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.workload, geo, fa.nD),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(name, geo, n_doppler):
+    desc = {"C2": "BASELINE configs[1]: Galileo E1b PCPS acquisition, 4 ms code, 8 MS/s, +-5 kHz / 125 Hz, 50 PRNs",
+            "C1": "BASELINE configs[0]: GPS L1 C/A PCPS acquisition, 1 ms, 4 MS/s, +-5 kHz / 250 Hz, 32 PRNs"}.get(name, name)
+    return {"workload": desc, "fft_size": geo["fft_size"], "n_doppler_bins": n_doppler, "n_prn": geo["n_prn"],
+            "cells_per_step_per_gpu": geo["n_prn"] * n_doppler * geo["fft_size"],
+            "l2_policy": "L2 flushed (256 MiB write) between timed iterations", "parallelism": "one process per GPU, PRN x Doppler grid per GPU"}
+
+
+# ----------------------------------------------------------------------------------------------
+# our arm
+# ----------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from b200_import import load_package
+    b = load_package()
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available() or b.lib().gnss_b200_device_count() < 1:
+        raise RuntimeError("bench.py: no CUDA device; libgnss_b200 has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    hbm_peak, peak_src = measured_peaks()
+    fp32_peak = b.fp32_peak_tflops(local)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def flush_l2():
+        flush.fill_(rank + 1)
+
+    # ------------------------------ acquisition ------------------------------
+    geo, codes, iq0, truth = synth.config_scene(args.workload)
+    # each rank searches the whole grid on its own sample block (weak scaling): same satellites, rank-specific noise
+    iq = iq0 if rank == 0 else synth.make_iq(geo["consumed_samples"], geo["fs"], truth, seed=1000 + rank)
+    n_prn = geo["n_prn"]
+    eng = b.PcpsAcquisitionB200(geo["fft_size"], geo["consumed_samples"], geo["doppler_max"], geo["doppler_step"], geo["fs"],
+                                geo["samples_per_chip"], n_prn, use_cfar=True, device=local)
+    slots = np.arange(n_prn, dtype=np.uint32)
+    eng.set_local_codes(slots, codes)
+    nD, eff = eng.n_doppler, eng.eff
+    cells = n_prn * nD * eff
+    est = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local))
+    d_iq = torch.from_numpy(iq.view(np.float32).copy()).cuda()
+    h_iq = torch.from_numpy(iq.view(np.float32).copy()).pin_memory()
+    h_iq_np = h_iq.numpy().view(np.complex64)
+    gathered = torch.empty(world * n_prn * 32, dtype=torch.uint8, device="cuda") if world > 1 else None
+
+    def gather(res):
+        if world > 1:
+            t = torch.from_numpy(res.view(np.uint8)).cuda(non_blocking=False)
+            dist.all_gather_into_tensor(gathered, t)
+
+    def step_device():
+        eng.dwell_device_async(d_iq.data_ptr(), slots)
+        res = eng.sync(n_prn)
+        gather(res)
+        return res
+
+    def step_e2e():
+        res = eng.dwell(h_iq_np, slots)
+        gather(res)
+        return res
+
+    torch.cuda.synchronize()
+    for _ in range(args.warmup):
+        res = step_device()
+    # sanity: the injected satellites are found (the bench refuses to time a wrong search)
+    thr = b.acq_threshold(0.001, eff, nD)
+    found = {int(p) + 1 for p in range(n_prn) if res[p]["test_statistic"] > thr}
+    want = {t["prn"] for t in truth if t["cn0"] > 41.0}
+    if not want <= found:
+        raise RuntimeError(f"bench.py: search is wrong, strong PRNs {sorted(want - found)} not detected")
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    eng.profile(True)
+    l0 = eng.launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush_l2()
+        torch.cuda.synchronize()
+        ev[i][0].record(est)
+        eng.dwell_device_async(d_iq.data_ptr(), slots)
+        ev[i][1].record(est)
+        res = eng.sync(n_prn)
+        gather(res)
+    barrier()
+    wall = time.perf_counter() - wall0
+    dev_ms = sum(a.elapsed_time(c) for a, c in ev) / args.steps
+    dev_ms = max_over_ranks(dev_ms)
+    launches = eng.launch_count() - l0
+    prof_ms, prof_cnt = eng.profile(False)
+    value = world * cells / (dev_ms * 1e-3)
+
+    # e2e through the host-buffer C-ABI call
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+    e2e = world * cells / e2e_s
+    clocks = sampler.stop() if rank == 0 else None
+
+    # dominant acquisition kernel and rooflines
+    names = ["fwd_fft_stages", "inv_first_stage", "inv_last_stage_mag_reduce", "code_spectra", "decision"]
+    dom = int(np.argmax(prof_ms[:5]))
+    dom_ms = prof_ms[dom] / max(1, prof_cnt[dom])
+    cells_per_launch = cells * args.steps / max(1, prof_cnt[dom])
+    alg_bytes_per_cell = 8.0 / nD  # sample block + code spectra + row records per dwell
+    achieved_gbs = cells_per_launch * alg_bytes_per_cell / (dom_ms * 1e-3) / 1e9
+    step_kernel_ms = sum(prof_ms[:5]) / args.steps
+    fp = acq_flops_per_cell(geo["fft_size"])
+    roofline = {"kernel": names[dom], "bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_cell": alg_bytes_per_cell, "cells_per_launch": cells_per_launch, "avg_launch_ms": dom_ms,
+                "note": "fused search: algorithmic HBM traffic is ~8/nDoppler B per cell, so HBM is not the binding roofline; see roofline_fp32"}
+    roofline_fp32 = {"bound": "fp32", "achieved": cells * fp / (step_kernel_ms * 1e-3) / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
+                     "frac": cells * fp / (step_kernel_ms * 1e-3) / 1e12 / fp32_peak, "flops_per_cell": fp,
+                     "peak_source": "measured FFMA loop (gnss_b200_debug_fp32_peak)",
+                     "kernel_ms_per_step": {names[i]: prof_ms[i] / args.steps for i in range(5)},
+                     "note": "algorithmic flops = SURVEY §8.4 (10 log2 N + 17 per cell, reference formulation with a forward FFT per row); "
+                             "the engine shares forward FFTs across PRNs, so executed flops are about half"}
+
+    # ------------------------------ tracking (config 5, per-GPU share) ------------------------------
+    trk = bench_tracking(b, torch, est.device, args, world, rank, local, flush_l2, barrier, max_over_ranks, hbm_peak, peak_src)
+
+    # ------------------------------ CPU baseline on rank 0 ------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_baseline(args.workload, geo, codes, iq)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args.workload, geo, nD),
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(iq.nbytes), "d2h_bytes_per_step": int(n_prn * 32), "ms_per_step": e2e_s * 1e3},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_fp32": roofline_fp32,
+            "wall_ms_per_step_incl_flush": wall / args.steps * 1e3, "tracking": trk,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def bench_tracking(b, torch, device, args, world, rank, local, flush_l2, barrier, max_over_ranks, hbm_peak, peak_src):
+    """BASELINE config 5: 2048 channels x 11 taps, GPS L5I at 30 MS/s, 1 ms (30 000 samples); channels are sharded over the
+    GPUs (2048 / N per GPU at N = 8; at smaller N every GPU still takes 256 so per-GPU work is fixed — weak scaling)."""
+    n_ch, n, T = 256 if world > 1 else 2048, 30000, 11
+    rng = np.random.default_rng(5 + rank)
+    chips = synth.load_chips()["gps_l5i"]
+    mc = b.MulticorrelatorB200(n_ch, n, T, device=local)
+    for c in range(n_ch):
+        mc.set_local_code(c, chips[c % 32].astype(np.float32))
+    shifts = np.tile(np.array([-1, -0.5, -0.25, -0.1, -0.05, 0, 0.05, 0.1, 0.25, 0.5, 1], np.float32), (n_ch, 1))
+    fd = rng.uniform(-5000, 5000, n_ch)
+    args_arr = mc.make_args(n_ch, n, rng.uniform(0, 2 * np.pi, n_ch), 2 * np.pi * fd / 30e6, 0.0, rng.uniform(0, 1, n_ch),
+                            10.23e6 * (1 + fd / 1176.45e6) / 30e6, 0.0)
+    g = torch.Generator(device="cuda")
+    g.manual_seed(7 + rank)
+    d_sig = torch.randn((n_ch, n, 2), generator=g, device="cuda", dtype=torch.float32)
+    chans = np.arange(n_ch, dtype=np.uint32)
+    est = torch.cuda.ExternalStream(mc.stream(), device=torch.device("cuda", local))
+    torch.cuda.synchronize()
+    for _ in range(args.warmup):
+        mc.correlate_device_async(chans, args_arr, shifts, d_sig.data_ptr(), n)
+        mc.sync(n_ch, T)
+    mc.profile(True)
+    steps = args.steps
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    barrier()
+    for i in range(steps):
+        if n_ch * n * 8 < (200 << 20):
+            flush_l2()
+            torch.cuda.synchronize()
+        ev[i][0].record(est)
+        mc.correlate_device_async(chans, args_arr, shifts, d_sig.data_ptr(), n)
+        ev[i][1].record(est)
+        mc.sync(n_ch, T)
+    barrier()
+    dev_ms = max_over_ranks(sum(a.elapsed_time(c) for a, c in ev) / steps)
+    pm, pc = mc.profile(False)
+    k_ms = pm[0] / max(1, pc[0])
+    # e2e: host sample buffers (pinned, contiguous) -> H2D inside the call
+    e2e_ch = min(n_ch, 512)
+    h_sig = torch.randn((e2e_ch, n, 2), dtype=torch.float32).pin_memory()
+    base = h_sig.data_ptr()
+    a2 = mc.make_args(e2e_ch, n, rng.uniform(0, 2 * np.pi, e2e_ch), 2 * np.pi * fd[:e2e_ch] / 30e6, 0.0, rng.uniform(0, 1, e2e_ch),
+                      10.23e6 * (1 + fd[:e2e_ch] / 1176.45e6) / 30e6, 0.0, sig_ptrs=[base + c * n * 8 for c in range(e2e_ch)])
+    mc.correlate_batch(chans[:e2e_ch], a2, shifts[:e2e_ch])
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(3, steps // 4)
+    for _ in range(e2e_steps):
+        mc.correlate_batch(chans[:e2e_ch], a2, shifts[:e2e_ch])
+    barrier()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
+    alg_bytes = n_ch * (8.0 * n + 8.0 * T)
+    return {
+        "metric": "tracking_channel_ms_per_s", "value": world * n_ch / (dev_ms * 1e-3), "unit": "channel-ms/s", "ms_per_step": dev_ms,
+        "config": {"workload": "BASELINE configs[4]: multicorrelator, GPS L5I, 30 MS/s, 1 ms, 11 taps", "channels_per_gpu": n_ch, "samples": n, "taps": T,
+                   "input_mode": "independent per-channel sample streams resident in HBM (491 MB > L2 at 2048 channels)"},
+        "e2e": {"value": world * e2e_ch / e2e_s, "unit": "channel-ms/s", "channels": e2e_ch, "h2d_bytes_per_step": int(e2e_ch * n * 8),
+                "d2h_bytes_per_step": int(e2e_ch * T * 8), "ms_per_step": e2e_s * 1e3},
+        "roofline": {"kernel": "multicorr_kernel", "bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src, "avg_launch_ms": k_ms,
+                     "algorithmic_bytes_per_channel_ms": 8.0 * n + 8.0 * T},
+        "gpu_launches": int(pc[0]),
+    }
+
+
+def cpu_baseline(workload, geo, codes, iq):
+    from b200_import import load_oracle
+    load_oracle()
+    import oracle_fast
+    cores = oracle_fast.host_cores()
+    n_s = min(geo["n_prn"], max(cores, 8))
+    fa = oracle_fast.FastAcq(geo["fft_size"], geo["consumed_samples"], geo["doppler_max"], geo["doppler_step"], geo["fs"],
+                             geo["samples_per_chip"], use_cfar=True, workers=cores)
+    specs = [fa.code_spectrum(c) for c in codes[:n_s]]
+    fa.dwell_all_like_reference(iq, specs)
+    reps, t0 = 0, time.perf_counter()
+    while reps < 3 or time.perf_counter() - t0 < 10.0:
+        fa.dwell_all_like_reference(iq, specs)
+        reps += 1
+        if time.perf_counter() - t0 > 30.0:
+            break
+    dt = (time.perf_counter() - t0) / reps
+    return {"value": n_s * fa.nD * fa.eff / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{n_s} of {geo['n_prn']} PRNs x {fa.nD} bins x {fa.eff} code phases, {reps} repetitions, one thread per PRN; "
+                      "numpy/scipy pocketfft complex64 port of acquisition_core (CPU FFT = pocketfft, not FFTW)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C2", choices=["C1", "C2"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -73,6 +73,7 @@ EXPORTS = [
     "gnss_b200_mc_set_code", "gnss_b200_mc_set_stream", "gnss_b200_mc_correlate_batch",
     "gnss_b200_mc_correlate_device_async", "gnss_b200_mc_sync", "gnss_b200_mc_chip_indices", "gnss_b200_mc_stream",
     "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan",
+    "gnss_b200_acq_profile", "gnss_b200_mc_profile", "gnss_b200_debug_fp32_peak",
 ]
 
 _lib = None
@@ -126,6 +127,9 @@ def lib():
     L.gnss_b200_mc_launch_count.restype = C.c_uint64
     L.gnss_b200_debug_wipeoff_phase.argtypes = [c_i32, C.c_double, c_u32, _fp, _u32p]
     L.gnss_b200_debug_fft_plan.argtypes = [c_u32, _u32p, _u32p, _u32p, _u32p]
+    L.gnss_b200_acq_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]
+    L.gnss_b200_mc_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]
+    L.gnss_b200_debug_fp32_peak.argtypes = [c_i32, C.POINTER(C.c_double)]
     _lib = L
     return L
 
@@ -242,6 +246,13 @@ class PcpsAcquisitionB200:
         _check(self.L.gnss_b200_acq_read_rows(self.h, slot, rows.ctypes.data_as(C.c_void_p)))
         return rows
 
+    def profile(self, enable, reset=True):
+        """(ms_by_kernel_class, launches_by_kernel_class) accumulated since the last reset; then enable/disable."""
+        ms = (C.c_double * 8)()
+        cnt = (C.c_uint64 * 8)()
+        _check(self.L.gnss_b200_acq_profile(self.h, int(enable), ms, cnt, int(reset)))
+        return list(ms), list(cnt)
+
     def stream(self):
         return self.L.gnss_b200_acq_stream(self.h)
 
@@ -266,6 +277,12 @@ def debug_wipeoff_phase(doppler_hz, fs, n):
     npc = c_u32(0)
     _check(lib().gnss_b200_debug_wipeoff_phase(int(doppler_hz), float(fs), n, _f32p(out), C.byref(npc)))
     return out, npc.value
+
+
+def fp32_peak_tflops(device=0):
+    v = C.c_double(0)
+    _check(lib().gnss_b200_debug_fp32_peak(device, C.byref(v)))
+    return v.value
 
 
 def debug_fft_plan(n):
@@ -354,6 +371,12 @@ class MulticorrelatorB200:
         out = np.zeros((shifts.size, n), dtype=np.int32)
         _check(self.L.gnss_b200_mc_chip_indices(self.h, ch, args_one, _f32p(shifts), shifts.size, flags, out.ctypes.data_as(C.POINTER(c_i32))))
         return out
+
+    def profile(self, enable, reset=True):
+        ms = (C.c_double * 8)()
+        cnt = (C.c_uint64 * 8)()
+        _check(self.L.gnss_b200_mc_profile(self.h, int(enable), ms, cnt, int(reset)))
+        return list(ms), list(cnt)
 
     def stream(self):
         return self.L.gnss_b200_mc_stream(self.h)

@@ -6,7 +6,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgnss_b200.so")
-SOURCES = ["api_misc.cu", "multicorr.cu", "acq.cu", "fft_plan.cc", "wipeoff_pieces.cc"]
+SOURCES = ["api_misc.cu", "multicorr.cu", "acq.cu", "acq_fast_lower.cu", "acq_fast_upper.cu", "fft_plan.cc", "wipeoff_pieces.cc"]
 
 
 def _stale():
@@ -23,12 +23,22 @@ def build(force=False, verbose=False):
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         raise RuntimeError("nvcc not found: libgnss_b200.so must be built where the CUDA toolkit is installed")
-    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
-           "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=hidden", "-shared", "-o", LIB]
+    flags = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
+             "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=hidden"]
     if verbose:
-        cmd += ["-Xptxas", "-v"]
-    cmd += [os.path.join(CSRC, s) for s in SOURCES]
-    subprocess.run(cmd, check=True, cwd=CSRC)
+        flags += ["-Xptxas", "-v"]
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+
+    def compile_one(src):
+        obj = os.path.join(objdir, src + ".o")
+        subprocess.run([nvcc] + flags + ["-c", "-o", obj, os.path.join(CSRC, src)], check=True, cwd=CSRC)
+        return obj
+
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 4)) as ex:
+        objs = list(ex.map(compile_one, SOURCES))
+    subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs, check=True)
     return LIB
 
 

@@ -1,5 +1,6 @@
 // Host side of the PCPS acquisition engine: handle, buffers, launch sequencing, C-ABI.
 // Reference for every entry point: include/gnss_b200.h.
+#include "acq_fast.cuh"
 #include "acq_kernels.cuh"
 #include "wipeoff_pieces.h"
 #include <algorithm>
@@ -14,6 +15,14 @@ namespace
 constexpr uint32_t kMaxSingleStagePoints = 24576;  // 192 KiB of complex64 in one CTA's shared memory
 constexpr size_t kScratchBudgetBytes = 48ull << 20;  // two-stage intermediate kept L2-resident by chunking rows
 constexpr uint32_t kMaxCachedGroups = 64;
+enum
+{
+    CAT_FWD = 0,
+    CAT_INV_FIRST = 1,  // two-stage plans only: product + lower stage -> scratch
+    CAT_INV_LAST = 2,   // IFFT last stage + |.|^2 + row reductions (single-stage plans: the whole inverse)
+    CAT_CODE = 3,
+    CAT_DECIDE = 4
+};
 
 struct CallMeta  // uploaded once per dwell call
 {
@@ -32,7 +41,7 @@ struct gnss_b200_acq
     cudaStream_t stream = nullptr;
     uint64_t launches = 0;
 
-    DevBuf d_W, d_cbuf, d_xbuf, d_samples, d_codes_td, d_scratch;
+    DevBuf d_W, d_cbuf, d_xbuf, d_xtmp, d_samples, d_codes_td, d_scratch;
     DevBuf d_pieces, d_npieces;  // per cached group: nD_local tables
     std::map<int64_t, uint32_t> group_cache;  // (center + bias) -> cached group ordinal
     DevBuf d_meta;
@@ -44,12 +53,13 @@ struct gnss_b200_acq
     std::vector<uint8_t> has_code;
     std::vector<uint32_t> dwell;
     uint32_t last_n_slots = 0;
+    EventProfiler prof;
 };
 
 namespace
 {
 template <int LOAD, int STORE, bool INV>
-int launch_stage(gnss_b200_acq* h, const StageArgs& a, uint32_t n_transforms)
+int launch_stage(gnss_b200_acq* h, const StageArgs& a, uint32_t n_transforms, int cat)
 {
     if (n_transforms == 0) return GNSS_B200_OK;
     const size_t smem = (size_t)a.st.tile_points * sizeof(float2);
@@ -64,7 +74,9 @@ int launch_stage(gnss_b200_acq* h, const StageArgs& a, uint32_t n_transforms)
             configured = max_dyn;
         }
     const dim3 grid(n_transforms, a.st.tiles);
+    h->prof.begin(cat, h->stream);
     stage_kernel<LOAD, STORE, INV><<<grid, a.st.threads, smem, h->stream>>>(a);
+    h->prof.end(h->stream);
     h->launches++;
     B200_CUDA(cudaGetLastError());
     return GNSS_B200_OK;
@@ -81,6 +93,12 @@ StageArgs base_args(const gnss_b200_acq* h, int stage)
     a.eff = h->eff;
     a.mag_offset = h->mag_offset;
     a.consumed = h->consumed;
+    if (h->plan.fast)
+        {
+            a.fmap_ra = h->plan.ra_lo;
+            a.fmap_rb = h->plan.rb_lo;
+            a.fmap_mlo = h->plan.ra_lo * h->plan.rb_lo;
+        }
     return a;
 }
 
@@ -96,7 +114,7 @@ int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
             a.slots = d_slots;
             a.out_buf = h->d_cbuf.as<float2>();
             a.out_by_slot = 1;
-            return launch_stage<LOAD_CODE, STORE_CONJ, false>(h, a, n);
+            return launch_stage<LOAD_CODE, STORE_CONJ, false>(h, a, n, CAT_CODE);
         }
     // two stages through the scratch buffer, in chunks that fit it
     const uint32_t chunk = (uint32_t)std::max<size_t>(1, h->d_scratch.cap / ((size_t)h->N * 8));
@@ -110,7 +128,7 @@ int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
             a.y0 = y0;
             a.out_buf = h->d_scratch.as<float2>();
             a.out_y0 = y0;
-            int rc = launch_stage<LOAD_CODE, STORE_BUF, false>(h, a, cnt);
+            int rc = launch_stage<LOAD_CODE, STORE_BUF, false>(h, a, cnt, CAT_CODE);
             if (rc) return rc;
             StageArgs b = base_args(h, 1);
             b.in_buf = h->d_scratch.as<float2>();
@@ -119,7 +137,8 @@ int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
             b.slots = d_slots;
             b.out_buf = h->d_cbuf.as<float2>();
             b.out_by_slot = 1;
-            rc = launch_stage<LOAD_BUF, STORE_CONJ, false>(h, b, cnt);
+            b.fmap_store = 1;
+            rc = launch_stage<LOAD_BUF, STORE_CONJ, false>(h, b, cnt, CAT_CODE);
             if (rc) return rc;
         }
     return GNSS_B200_OK;
@@ -214,6 +233,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     const uint32_t n_rows = n_slots * h->nD_local;
     const uint32_t tiles_last = h->plan.stage[0].tiles;  // the inverse always ends with stage[0]
     B200_CUDA(h->d_xbuf.reserve((size_t)n_fwd * h->N * 8));
+    if (h->plan.n_stages == 2) B200_CUDA(h->d_xtmp.reserve((size_t)n_fwd * h->N * 8));
     B200_CUDA(h->d_partials.reserve(sizeof(RowPartial) * (size_t)n_rows * tiles_last));
     B200_CUDA(h->d_results.reserve(sizeof(gnss_b200_acq_result) * n_slots));
     B200_CUDA(h->h_results.reserve(sizeof(gnss_b200_acq_result) * n_slots));
@@ -227,15 +247,16 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
         a.pieces = h->d_pieces.as<WipePiece>();
         a.n_pieces = h->d_npieces.as<uint32_t>();
         a.group_piece_base = d_gpb;
-        a.out_buf = h->d_xbuf.as<float2>();
-        int rc = launch_stage<LOAD_SAMPLES, STORE_BUF, false>(h, a, n_fwd);
+        a.out_buf = h->plan.n_stages == 2 ? h->d_xtmp.as<float2>() : h->d_xbuf.as<float2>();
+        int rc = launch_stage<LOAD_SAMPLES, STORE_BUF, false>(h, a, n_fwd, CAT_FWD);
         if (rc) return rc;
         if (h->plan.n_stages == 2)
             {
                 StageArgs b = base_args(h, 1);
-                b.in_buf = h->d_xbuf.as<float2>();
-                b.out_buf = h->d_xbuf.as<float2>();
-                rc = launch_stage<LOAD_BUF, STORE_BUF, false>(h, b, n_fwd);
+                b.in_buf = h->d_xtmp.as<float2>();
+                b.out_buf = h->d_xbuf.as<float2>();  // not in place: the fast layout permutes across tiles
+                b.fmap_store = 1;
+                rc = launch_stage<LOAD_BUF, STORE_BUF, false>(h, b, n_fwd, CAT_FWD);
                 if (rc) return rc;
             }
     }
@@ -254,9 +275,58 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 a.mag_is_rowbuf = mag_is_rowbuf;
                 a.dwell_after = d_dwell;
                 a.partials = partials;
-                return launch_stage<LOAD_PRODUCT, STORE_MAG, true>(h, a, rows);
+                return launch_stage<LOAD_PRODUCT, STORE_MAG, true>(h, a, rows, CAT_INV_LAST);
             }
         const uint32_t chunk = (uint32_t)std::max<size_t>(1, h->d_scratch.cap / ((size_t)h->N * 8));
+        if (h->plan.fast)
+            {
+                const FftPlan& pl = h->plan;
+                FastArgs fa;
+                std::memset(&fa, 0, sizeof(fa));
+                fa.W = h->d_W.as<float2>();
+                fa.N = h->N;
+                fa.M_lo = pl.ra_lo * pl.rb_lo;
+                fa.M_hi = pl.ra_hi * pl.rb_hi;
+                fa.ra_lo = pl.ra_lo;
+                fa.rb_lo = pl.rb_lo;
+                fa.ra_hi = pl.ra_hi;
+                fa.rb_hi = pl.rb_hi;
+                fa.slots = d_slots;
+                fa.slot_group = d_slot_group;
+                fa.k_override = k_override;
+                fa.nD_local = h->nD_local;
+                fa.X = h->d_xbuf.as<float2>();
+                fa.Cs = h->d_cbuf.as<float2>();
+                fa.scratch = h->d_scratch.as<float2>();
+                fa.nb = pl.stage[1].blocks;
+                fa.C = pl.stage[0].C;
+                fa.mag_base = mag_base;
+                fa.mag_is_rowbuf = mag_is_rowbuf;
+                fa.eff = h->eff;
+                fa.mag_offset = h->mag_offset;
+                fa.dwell_after = d_dwell;
+                fa.partials = partials;
+                const uint32_t pitch = (pl.ra_lo % 2 == 0) ? pl.ra_lo + 1 : pl.ra_lo;
+                const size_t smem_lo = ((size_t)fa.nb * pitch * pl.rb_lo + fa.M_lo) * sizeof(float2);
+                const size_t smem_hi = ((size_t)fa.M_hi * fa.C + fa.M_hi) * sizeof(float2);
+                const dim3 block_hi(fa.C, std::max(1u, (uint32_t)kFastThreads / fa.C));
+                for (uint32_t y0 = 0; y0 < rows; y0 += chunk)
+                    {
+                        const uint32_t cnt = std::min(chunk, rows - y0);
+                        fa.y0 = y0;
+                        h->prof.begin(CAT_INV_FIRST, h->stream);
+                        cudaError_t e = launch_inv_lower(pl.ra_lo, pl.rb_lo, dim3(cnt, fa.M_hi / fa.nb), smem_lo, h->stream, fa);
+                        h->prof.end(h->stream);
+                        h->launches++;
+                        B200_CUDA(e);
+                        h->prof.begin(CAT_INV_LAST, h->stream);
+                        e = launch_inv_upper(pl.ra_hi, pl.rb_hi, dim3(cnt, fa.M_lo / fa.C), block_hi, smem_hi, h->stream, fa);
+                        h->prof.end(h->stream);
+                        h->launches++;
+                        B200_CUDA(e);
+                    }
+                return GNSS_B200_OK;
+            }
         for (uint32_t y0 = 0; y0 < rows; y0 += chunk)
             {
                 const uint32_t cnt = std::min(chunk, rows - y0);
@@ -269,7 +339,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 a.y0 = y0;
                 a.out_buf = h->d_scratch.as<float2>();
                 a.out_y0 = y0;
-                int rc = launch_stage<LOAD_PRODUCT, STORE_BUF, true>(h, a, cnt);
+                int rc = launch_stage<LOAD_PRODUCT, STORE_BUF, true>(h, a, cnt, CAT_INV_FIRST);
                 if (rc) return rc;
                 StageArgs b = base_args(h, 0);
                 b.in_buf = h->d_scratch.as<float2>();
@@ -282,7 +352,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 b.mag_is_rowbuf = mag_is_rowbuf;
                 b.dwell_after = d_dwell;
                 b.partials = partials;
-                rc = launch_stage<LOAD_BUF, STORE_MAG, true>(h, b, cnt);
+                rc = launch_stage<LOAD_BUF, STORE_MAG, true>(h, b, cnt, CAT_INV_LAST);
                 if (rc) return rc;
             }
         return GNSS_B200_OK;
@@ -307,7 +377,9 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     f.rows = h->d_rows.as<gnss_b200_acq_row>();
     f.results = h->d_results.as<gnss_b200_acq_result>();
     f.best_k_local = h->d_bestk.as<uint32_t>();
+    h->prof.begin(CAT_DECIDE, h->stream);
     finalize_kernel<<<n_slots, 32, 0, h->stream>>>(f);
+    h->prof.end(h->stream);
     h->launches++;
     B200_CUDA(cudaGetLastError());
 
@@ -336,7 +408,9 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                     sp.mag_base = h->d_rowbuf.as<float>();
                     sp.is_rowbuf = 1;
                 }
+            h->prof.begin(CAT_DECIDE, h->stream);
             second_peak_kernel<<<n_slots, 256, 0, h->stream>>>(sp);
+            h->prof.end(h->stream);
             h->launches++;
             B200_CUDA(cudaGetLastError());
         }
@@ -432,12 +506,13 @@ extern "C"
         if (!h) return GNSS_B200_OK;
         cudaSetDevice(h->cfg.device);
         if (h->stream) cudaStreamSynchronize(h->stream);
-        for (DevBuf* b : {&h->d_W, &h->d_cbuf, &h->d_xbuf, &h->d_samples, &h->d_codes_td, &h->d_scratch, &h->d_pieces, &h->d_npieces, &h->d_meta,
+        for (DevBuf* b : {&h->d_W, &h->d_cbuf, &h->d_xbuf, &h->d_xtmp, &h->d_samples, &h->d_codes_td, &h->d_scratch, &h->d_pieces, &h->d_npieces, &h->d_meta,
                  &h->d_partials, &h->d_partials2, &h->d_rows, &h->d_results, &h->d_bestk, &h->d_grid, &h->d_rowbuf})
             b->release();
         h->h_meta.release();
         h->h_results.release();
         h->h_samples.release();
+        h->prof.release();
         if (h->stream) cudaStreamDestroy(h->stream);
         delete h;
         return GNSS_B200_OK;
@@ -609,6 +684,23 @@ extern "C"
                 const std::vector<uint32_t> p = fft_plan_permutation(plan);
                 std::memcpy(perm, p.data(), sizeof(uint32_t) * n);
             }
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_profile(gnss_b200_acq* h, int enable, double* ms_by_kernel, uint64_t* launches_by_kernel, int reset)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_profile: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        h->prof.collect();
+        for (int i = 0; i < GNSS_B200_PROFILE_SLOTS; i++)
+            {
+                if (ms_by_kernel) ms_by_kernel[i] = h->prof.ms[i];
+                if (launches_by_kernel) launches_by_kernel[i] = h->prof.count[i];
+            }
+        if (reset) h->prof.reset();
+        h->prof.on = enable != 0;
         return GNSS_B200_OK;
     }
 

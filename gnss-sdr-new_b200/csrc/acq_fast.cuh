@@ -1,0 +1,258 @@
+// Fast inverse path of the acquisition pipeline for "fast" FFT plans (fft_plan.h): two stages of two register
+// passes each. Every point makes exactly ONE round trip through shared memory per stage (the transpose between
+// the two register passes); the first pass reads global memory straight into registers and the last pass
+// leaves registers straight for global memory / the |.|^2 reduction. All radices are template parameters, so
+// the index arithmetic is constant-folded and there is no per-pass dispatch.
+//
+//   inv_lower_kernel<RA,RB>  : product X_k * C_prn (pcps_acquisition.cc:665) -> IDFT over the contiguous lower stage
+//                              (M_lo = RA*RB) -> inter-stage twiddle -> scratch
+//   inv_upper_kernel<RA,RB>  : scratch -> IDFT over the strided upper stage (M_hi = RA*RB) = the rest of the IFFT (:668)
+//                              -> |.|^2 (+ non-coherent accumulation) (:672-680) -> per-tile {max, argmax, sum}
+#pragma once
+#include "acq_kernels.cuh"
+
+namespace b200
+{
+struct FastArgs
+{
+    const float2* W;  // exp(-2 pi i k / N), k < N
+    uint32_t N, M_lo, M_hi;
+    uint32_t ra_lo, rb_lo, ra_hi, rb_hi;
+    // row mapping (same convention as StageArgs)
+    const uint32_t* slots;
+    const uint32_t* slot_group;
+    const uint32_t* k_override;
+    uint32_t nD_local;
+    uint32_t y0;
+    const float2* X;      // [call group][nD_local][N], fast layout
+    const float2* Cs;     // [slot][N], fast layout
+    float2* scratch;      // [row - y0][N], natural order between the stages
+    uint32_t nb;          // lower stage: contiguous sub-transforms per tile
+    uint32_t C;           // upper stage: columns per tile
+    // STORE_MAG part
+    float* mag_base;
+    uint32_t mag_is_rowbuf;
+    uint32_t eff;
+    uint32_t mag_offset;
+    const uint32_t* dwell_after;
+    RowPartial* partials;
+};
+
+__device__ __forceinline__ void fast_row_of(const FastArgs& a, uint32_t y, uint32_t& si, uint32_t& kk)
+{
+    if (a.k_override)
+        {
+            si = y;
+            kk = a.k_override[y];
+        }
+    else
+        {
+            si = y / a.nD_local;
+            kk = y - si * a.nD_local;
+        }
+}
+
+constexpr int kFastThreads = 256;
+
+// ------------------------------------------------------------------------------------------------
+// lower stage: grid (rows, M_hi / nb). Shared memory: nb * PITCH * RB data + M twiddles.
+// ------------------------------------------------------------------------------------------------
+template <int RA, int RB>
+__global__ void __launch_bounds__(kFastThreads) inv_lower_kernel(const FastArgs a)
+{
+    constexpr int M = RA * RB;
+    constexpr int P = (RA % 2 == 0) ? RA + 1 : RA;  // odd pitch: conflict-free 64-bit stores with stride P
+    constexpr int MP = P * RB;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* s = reinterpret_cast<float2*>(smem_raw);
+    float2* s_tw = s + (size_t)a.nb * MP;  // conj W_M^(a*ub), [ub][a]
+
+    const uint32_t y = a.y0 + blockIdx.x;
+    uint32_t si, kk;
+    fast_row_of(a, y, si, kk);
+    const size_t N = a.N;
+    const float2* X = a.X + ((size_t)a.slot_group[si] * a.nD_local + kk) * N;
+    const float2* Cs = a.Cs + (size_t)a.slots[si] * N;
+    const uint32_t blk0 = blockIdx.y * a.nb;
+    const uint32_t tw_scale = a.N / M;  // W_M = W_N^(N/M)
+
+    for (uint32_t i = threadIdx.x; i < (uint32_t)M; i += blockDim.x)
+        {
+            const uint32_t ub = i / RA, aa = i - ub * RA;
+            const float2 w = __ldg(a.W + (size_t)aa * ub * tw_scale);
+            s_tw[i] = make_float2(w.x, -w.y);
+        }
+
+    __syncthreads();
+
+    // ---- pass A (stride-1 dim, no twiddle): one thread per (block, ub) pencil ----
+    const uint32_t n_pen_a = a.nb * RB;
+    const uint32_t seg = a.N / RA;
+    for (uint32_t p = threadIdx.x; p < n_pen_a; p += blockDim.x)
+        {
+            const uint32_t bl = p / RB, ub = p - bl * RB;
+            const uint32_t src = (blk0 + bl) * RB + ub;  // + ua * seg  (fast layout: unit stride across threads)
+            float2 x[RA], c[RA];
+#pragma unroll
+            for (int u = 0; u < RA; u++) x[u] = __ldg(X + src + (size_t)u * seg);
+#pragma unroll
+            for (int u = 0; u < RA; u++) c[u] = __ldg(Cs + src + (size_t)u * seg);
+#pragma unroll
+            for (int u = 0; u < RA; u++) x[u] = fft::cmul(x[u], c[u]);
+            fft::Dft<RA, true>::run(x);
+            float2* dst = s + (size_t)bl * MP + (size_t)ub * P;
+#pragma unroll
+            for (int q = 0; q < RA; q++) dst[q] = fft::cmul(x[q], s_tw[ub * RA + q]);
+        }
+    __syncthreads();
+
+    // ---- pass B + inter-stage twiddle: one thread per (block, a) pencil ----
+    const uint32_t n_pen_b = a.nb * RA;
+    float2* out = a.scratch + (size_t)(y - a.y0) * N;
+    for (uint32_t p = threadIdx.x; p < n_pen_b; p += blockDim.x)
+        {
+            const uint32_t bl = p / RA, aa = p - bl * RA;
+            const uint32_t gblk = blk0 + bl;
+            // upper-stage frequency index of this block: block position = ua' + ra_hi * ub'  ->  k1 = ua' * rb_hi + ub'
+            const uint32_t ubh = gblk / a.ra_hi, uah = gblk - ubh * a.ra_hi;
+            const uint32_t k1 = uah * a.rb_hi + ubh;
+            const float2 wb = __ldg(a.W + (size_t)k1 * aa);  // W_N^(k1 * a)
+            const float2 ws = __ldg(a.W + (size_t)k1 * RA);  // W_N^(k1 * RA)
+            float2 v[RB];
+            const float2* src = s + (size_t)bl * MP + aa;
+#pragma unroll
+            for (int u = 0; u < RB; u++) v[u] = src[(size_t)u * P];
+            fft::Dft<RB, true>::run(v);
+            float2 tw = make_float2(wb.x, -wb.y);
+            const float2 st = make_float2(ws.x, -ws.y);
+            float2* dst = out + (size_t)gblk * M + aa;
+#pragma unroll
+            for (int b = 0; b < RB; b++)
+                {
+                    dst[(size_t)b * RA] = fft::cmul(v[b], tw);  // conj W_N^(k1 * (a + RA b))
+                    tw = fft::cmul(tw, st);
+                }
+        }
+}
+
+// ------------------------------------------------------------------------------------------------
+// upper stage: grid (rows, M_lo / C), block (C, threads / C). Shared memory: M * C data + M twiddles.
+// ------------------------------------------------------------------------------------------------
+template <int RA, int RB>
+__global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs a)
+{
+    constexpr int M = RA * RB;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* s = reinterpret_cast<float2*>(smem_raw);
+    float2* s_tw = s + (size_t)M * a.C;  // conj W_M^(a*ub), [ub][a]
+    __shared__ float s_rmax[kFastThreads / 32];
+    __shared__ uint32_t s_ridx[kFastThreads / 32];
+    __shared__ float s_rsum[kFastThreads / 32];
+
+    const uint32_t y = a.y0 + blockIdx.x;
+    uint32_t si, kk;
+    fast_row_of(a, y, si, kk);
+    const size_t N = a.N;
+    const uint32_t C = a.C, c = threadIdx.x, c0 = blockIdx.y * C;
+    const uint32_t tid = threadIdx.y * blockDim.x + threadIdx.x, nthreads = blockDim.x * blockDim.y;
+    const uint32_t tw_scale = a.N / M;
+    for (uint32_t i = tid; i < (uint32_t)M; i += nthreads)
+        {
+            const uint32_t ub = i / RA, aa = i - ub * RA;
+            const float2 w = __ldg(a.W + (size_t)aa * ub * tw_scale);
+            s_tw[i] = make_float2(w.x, -w.y);
+        }
+    const float2* in = a.scratch + (size_t)(y - a.y0) * N + c0 + c;
+
+    __syncthreads();
+
+    // ---- pass A: pencils (column c, ub) ----
+    for (uint32_t ub = threadIdx.y; ub < (uint32_t)RB; ub += blockDim.y)
+        {
+            float2 v[RA];
+#pragma unroll
+            for (int u = 0; u < RA; u++) v[u] = __ldcg(in + (size_t)(u + RA * ub) * a.M_lo);
+            fft::Dft<RA, true>::run(v);
+#pragma unroll
+            for (int q = 0; q < RA; q++) s[(size_t)(q + RA * ub) * C + c] = fft::cmul(v[q], s_tw[ub * RA + q]);
+        }
+    __syncthreads();
+
+    // ---- pass B + |.|^2 + reductions: pencils (column c, a) ----
+    float* mag = nullptr;
+    if (a.mag_base)
+        mag = a.mag_is_rowbuf ? a.mag_base + (size_t)si * a.eff : a.mag_base + ((size_t)a.slots[si] * a.nD_local + kk) * a.eff;
+    const bool accumulate = mag && !a.mag_is_rowbuf && a.dwell_after[si] > 1;
+    float best = -1.f, sum = 0.f;
+    uint32_t best_i = 0xffffffffu;
+    for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
+        {
+            float2 v[RB];
+#pragma unroll
+            for (int u = 0; u < RB; u++) v[u] = s[(size_t)(aa + RA * u) * C + c];
+            fft::Dft<RB, true>::run(v);
+#pragma unroll
+            for (int b = 0; b < RB; b++)
+                {
+                    const uint32_t pos = (aa + RA * b) * a.M_lo + c0 + c;  // natural time index
+                    const uint32_t m = pos - a.mag_offset;
+                    if (m < a.eff)
+                        {
+                            float g = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                            if (accumulate) g = mag[m] + g;               // :679
+                            if (mag) mag[m] = g;
+                            sum += g;
+                            if (g > best || (g == best && m < best_i))
+                                {
+                                    best = g;
+                                    best_i = m;
+                                }
+                        }
+                }
+        }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+            sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (ob > best || (ob == best && oi < best_i))
+                {
+                    best = ob;
+                    best_i = oi;
+                }
+        }
+    const int lane = tid & 31, warp = tid >> 5;
+    if (lane == 0)
+        {
+            s_rmax[warp] = best;
+            s_ridx[warp] = best_i;
+            s_rsum[warp] = sum;
+        }
+    __syncthreads();
+    if (tid == 0)
+        {
+            const int nw = (nthreads + 31) / 32;
+            for (int w = 1; w < nw; w++)
+                {
+                    sum += s_rsum[w];
+                    if (s_rmax[w] > best || (s_rmax[w] == best && s_ridx[w] < best_i))
+                        {
+                            best = s_rmax[w];
+                            best_i = s_ridx[w];
+                        }
+                }
+            RowPartial rp;
+            rp.max_val = best;
+            rp.max_idx = best_i;
+            rp.sum = sum;
+            rp.pad = 0;
+            a.partials[(size_t)y * gridDim.y + blockIdx.y] = rp;
+        }
+}
+
+// host-side launchers (instantiations live in acq_fast_lower.cu / acq_fast_upper.cu)
+cudaError_t launch_inv_lower(uint32_t ra, uint32_t rb, dim3 grid, size_t smem, cudaStream_t st, const FastArgs& a);
+cudaError_t launch_inv_upper(uint32_t ra, uint32_t rb, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a);
+
+}  // namespace b200

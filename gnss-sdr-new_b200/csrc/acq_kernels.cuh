@@ -87,7 +87,19 @@ struct StageArgs
     uint32_t mag_offset;         // first IFFT output that belongs to the row (N/2 with bit_transition, :671)
     const uint32_t* dwell_after; // [n_slots in call] dwell counter including this dwell
     RowPartial* partials;        // [y][tiles], y = global row of the call (not chunk-relative)
+    // ---- frequency-domain layout of fast plans (fft_plan.h): 0 = natural scrambled order ----
+    uint32_t fmap_ra, fmap_rb, fmap_mlo;
+    uint32_t fmap_store;         // apply the map when storing (last forward stage only)
 };
+
+// position in the plan's scrambled order -> position in the stored frequency-domain buffers
+__device__ __forceinline__ uint32_t fmap(const StageArgs& a, uint32_t pos)
+{
+    if (a.fmap_ra == 0) return pos;
+    const uint32_t blk = pos / a.fmap_mlo, l = pos - blk * a.fmap_mlo;
+    const uint32_t ub = l / a.fmap_ra, ua = l - ub * a.fmap_ra;
+    return ua * (a.N / a.fmap_ra) + blk * a.fmap_rb + ub;
+}
 
 __device__ __forceinline__ void row_of(const StageArgs& a, uint32_t y, uint32_t& si, uint32_t& kk)
 {
@@ -188,7 +200,8 @@ __global__ void __launch_bounds__(512) stage_kernel(const StageArgs a)
                 {
                     const uint32_t idx = i / C, c = i - idx * C;
                     const uint32_t pos = idx * st.pos_stride + tile_off + c;
-                    s[i] = fft::cmul(__ldg(X + pos), __ldg(Cs + pos));  // :665
+                    const uint32_t fp = fmap(a, pos);
+                    s[i] = fft::cmul(__ldg(X + fp), __ldg(Cs + fp));  // :665
                 }
         }
     __syncthreads();
@@ -206,7 +219,7 @@ __global__ void __launch_bounds__(512) stage_kernel(const StageArgs a)
                     const uint32_t pos = idx * st.pos_stride + tile_off + c;
                     float2 v = s[i];
                     if (STORE == STORE_CONJ) v.y = -v.y;  // :208
-                    out[pos] = v;
+                    out[a.fmap_store ? fmap(a, pos) : pos] = v;
                 }
         }
     else
@@ -300,7 +313,7 @@ struct FinalizeArgs
 };
 
 // one warp per slot
-__global__ void finalize_kernel(const FinalizeArgs a)
+static __global__ void finalize_kernel(const FinalizeArgs a)
 {
     const uint32_t si = blockIdx.x;
     const uint32_t slot = a.slots[si];
@@ -407,7 +420,7 @@ struct SecondPeakArgs
     gnss_b200_acq_result* results;
 };
 
-__global__ void second_peak_kernel(const SecondPeakArgs a)
+static __global__ void second_peak_kernel(const SecondPeakArgs a)
 {
     __shared__ float s_max[32];
     const uint32_t si = blockIdx.x;
@@ -437,11 +450,6 @@ __global__ void second_peak_kernel(const SecondPeakArgs a)
             res.test_statistic = res.peak / best;  // :611
             a.results[si] = res;
         }
-}
-
-__global__ void zero_kernel(float4* p, size_t n4)
-{
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) p[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
 }  // namespace b200

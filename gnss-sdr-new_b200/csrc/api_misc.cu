@@ -80,8 +80,60 @@ double gamma_p_inv(double a, double p)
 }
 }  // namespace b200
 
+namespace
+{
+__global__ void fp32_peak_kernel(float* out, int iters)
+{
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float m = 0.999f, c = 1e-3f;
+    for (int i = 0; i < iters; i++)
+        {
+            a0 = fmaf(a0, m, c);
+            a1 = fmaf(a1, m, c);
+            a2 = fmaf(a2, m, c);
+            a3 = fmaf(a3, m, c);
+            a4 = fmaf(a4, m, c);
+            a5 = fmaf(a5, m, c);
+            a6 = fmaf(a6, m, c);
+            a7 = fmaf(a7, m, c);
+        }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+}  // namespace
+
 extern "C"
 {
+    int gnss_b200_debug_fp32_peak(int32_t device, double* tflops)
+    {
+        B200_REQUIRE(tflops, GNSS_B200_ERR_INVALID, "fp32_peak: null");
+        int rc = b200::select_device(device);
+        if (rc) return rc;
+        const int blocks = b200::kNumSMs * 8, threads = 512, iters = 1 << 15;
+        float* d = nullptr;
+        B200_CUDA(cudaMalloc(&d, sizeof(float) * blocks * threads));
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        double best = 0;
+        for (int rep = 0; rep < 4; rep++)
+            {
+                cudaEventRecord(e0);
+                fp32_peak_kernel<<<blocks, threads>>>(d, iters);
+                cudaEventRecord(e1);
+                cudaEventSynchronize(e1);
+                float ms = 0;
+                cudaEventElapsedTime(&ms, e0, e1);
+                const double tf = 2.0 * 8.0 * (double)iters * blocks * threads / (ms * 1e-3) / 1e12;
+                if (rep > 0 && tf > best) best = tf;
+            }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        cudaFree(d);
+        B200_CUDA(cudaGetLastError());
+        *tflops = best;
+        return GNSS_B200_OK;
+    }
+
     const char* gnss_b200_last_error(void) { return b200::last_error_buf(); }
     const char* gnss_b200_version(void) { return "gnss_b200 0.1.0 (sm_100a)"; }
 

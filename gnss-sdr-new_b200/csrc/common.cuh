@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 namespace b200
 {
@@ -94,5 +95,70 @@ struct PinBuf
 };
 
 int select_device(int device);  // validates + cudaSetDevice; returns status
+
+// Optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline numbers).
+struct EventProfiler
+{
+    static constexpr int kCats = 8;
+    bool on = false;
+    struct Span
+    {
+        int cat;
+        cudaEvent_t a, b;
+    };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> pool;
+    double ms[kCats] = {0};
+    uint64_t count[kCats] = {0};
+    cudaEvent_t get()
+    {
+        if (!pool.empty())
+            {
+                cudaEvent_t e = pool.back();
+                pool.pop_back();
+                return e;
+            }
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        return e;
+    }
+    void begin(int cat, cudaStream_t st)
+    {
+        if (!on) return;
+        Span s{cat, get(), get()};
+        cudaEventRecord(s.a, st);
+        spans.push_back(s);
+    }
+    void end(cudaStream_t st)
+    {
+        if (!on) return;
+        cudaEventRecord(spans.back().b, st);
+    }
+    void collect()  // stream must be synchronised
+    {
+        for (auto& s : spans)
+            {
+                float t = 0.f;
+                if (cudaEventElapsedTime(&t, s.a, s.b) == cudaSuccess)
+                    {
+                        ms[s.cat] += t;
+                        count[s.cat]++;
+                    }
+                pool.push_back(s.a);
+                pool.push_back(s.b);
+            }
+        spans.clear();
+    }
+    void reset()
+    {
+        for (int i = 0; i < kCats; i++) ms[i] = 0, count[i] = 0;
+    }
+    void release()
+    {
+        collect();
+        for (auto e : pool) cudaEventDestroy(e);
+        pool.clear();
+    }
+};
 
 }  // namespace b200

@@ -89,13 +89,87 @@ uint32_t pick_threads(uint32_t tile_points)
 }
 }  // namespace
 
+bool fast_ra_supported(uint32_t r) { return r == 4 || r == 5 || r == 8 || r == 16 || r == 25; }
+bool fast_rb_supported(uint32_t r) { return r == 2 || r == 4 || r == 5 || r == 8 || r == 10 || r == 16 || r == 20; }
+
+namespace
+{
+uint32_t best_columns(uint32_t M_lo, uint32_t M_hi)
+{
+    uint32_t C = 1;
+    for (uint32_t d = 1; d <= 32; d++)
+        if (M_lo % d == 0 && (uint64_t)M_hi * d * 8 <= 64 * 1024) C = d;
+    return C;
+}
+
+// N = (ra_lo*rb_lo) * (ra_hi*rb_hi) with every radix in the instantiated sets; lower is better
+bool find_fast_plan(uint32_t N, FftPlan* plan)
+{
+    static const uint32_t RA[] = {25, 5, 16, 8, 4};
+    static const uint32_t RB[] = {2, 4, 5, 8, 10, 16, 20};
+    double best = 1e30;
+    bool found = false;
+    for (uint32_t a1 : RA)
+        for (uint32_t b1 : RB)
+            for (uint32_t a2 : RA)
+                for (uint32_t b2 : RB)
+                    {
+                        if ((uint64_t)a1 * b1 * a2 * b2 != N) continue;
+                        const uint32_t lo = a1 * b1, hi = a2 * b2;
+                        const uint32_t C = best_columns(lo, hi);
+                        double cost = 0.5 * std::fabs(std::log2((double)lo / (double)hi));
+                        if (a1 % 2 == 0) cost += 0.75;          // even stride-1 radix: padded shared-memory pitch
+                        if (C < 16) cost += 2.0 + (16 - C) * 0.1;  // narrow column tiles coalesce badly
+                        cost += 0.02 * (25.0 / a1 + 25.0 / a2);  // prefer big register passes first
+                        if (cost < best)
+                            {
+                                best = cost;
+                                found = true;
+                                plan->ra_lo = a1;
+                                plan->rb_lo = b1;
+                                plan->ra_hi = a2;
+                                plan->rb_hi = b2;
+                            }
+                    }
+    return found;
+}
+}  // namespace
+
 bool make_fft_plan(uint32_t N, uint32_t max_single, FftPlan* plan, const char** why)
 {
     static const char* kPrime = "FFT length has a prime factor > 13 (no codelet)";
     static const char* kSplit = "FFT length cannot be split into two shared-memory stages";
     plan->N = N;
     plan->radices.clear();
+    plan->fast = 0;
     std::vector<uint32_t> rad;
+    if (find_fast_plan(N, plan))
+        {
+            const uint32_t M_lo = plan->ra_lo * plan->rb_lo, M_hi = plan->ra_hi * plan->rb_hi;
+            plan->fast = 1;
+            plan->n_stages = 2;
+            FftStage& up = plan->stage[0];
+            fill_stage(&up, N, M_hi, {plan->ra_hi, plan->rb_hi}, M_lo, true);
+            up.C = best_columns(M_lo, M_hi);
+            up.blocks = 1;
+            up.tiles = M_lo / up.C;
+            up.tile_step = up.C;
+            up.tile_points = M_hi * up.C;
+            up.threads = pick_threads(up.tile_points);
+            FftStage& lo = plan->stage[1];
+            fill_stage(&lo, N, M_lo, {plan->ra_lo, plan->rb_lo}, 1, false);
+            uint32_t b = 1;
+            for (uint32_t d = 1; d <= M_hi; d++)
+                if (M_hi % d == 0 && (uint64_t)d * M_lo <= 4096) b = d;
+            lo.C = 1;
+            lo.blocks = b;
+            lo.tiles = M_hi / b;
+            lo.tile_step = b * M_lo;
+            lo.tile_points = b * M_lo;
+            lo.threads = pick_threads(lo.tile_points);
+            plan->radices = {plan->ra_lo, plan->rb_lo, plan->ra_hi, plan->rb_hi};
+            return true;
+        }
     if (N <= max_single)
         {
             if (!stage_radices(N, &rad))

@@ -44,6 +44,13 @@ struct FftStage
 
 struct FftPlan
 {
+    // "fast" plans: two stages of exactly two passes each, radices from the instantiated sets of acq_fast.cuh.
+    // Stage shapes: lower (contiguous) M_lo = ra_lo * rb_lo with ra_lo the stride-1 dim; upper M_hi = ra_hi * rb_hi.
+    // The frequency-domain buffers (X_k, code spectra) of a fast plan use the coalescing-friendly layout
+    //     F(pos) = u_a * (N / ra_lo) + blk * rb_lo + u_b,   pos = blk * M_lo + u_a + ra_lo * u_b
+    // so that the inverse's first register pass reads them with unit stride across threads.
+    uint32_t fast = 0;
+    uint32_t ra_lo = 0, rb_lo = 0, ra_hi = 0, rb_hi = 0;
     uint32_t N = 0;
     uint32_t n_stages = 0;  // 1 or 2; forward order: stage[0] then stage[1]
     FftStage stage[2];
@@ -52,6 +59,10 @@ struct FftPlan
 
 // Returns false (and leaves `why`) when N has a prime factor the codelets do not cover.
 bool make_fft_plan(uint32_t N, uint32_t max_single_stage_points, FftPlan* plan, const char** why);
+
+// radix sets the fast kernels are instantiated for (acq_fast.cuh)
+bool fast_ra_supported(uint32_t r);
+bool fast_rb_supported(uint32_t r);
 
 // position -> frequency-bin permutation of the forward transform's output (tests).
 std::vector<uint32_t> fft_plan_permutation(const FftPlan& plan);

@@ -369,6 +369,7 @@ struct gnss_b200_mc
     DevBuf d_idx;
     uint64_t launches = 0;
     uint32_t last_n_ch = 0, last_n_taps = 0;
+    EventProfiler prof;
 };
 
 namespace
@@ -488,12 +489,14 @@ int run_batch(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, uint32_t smem_ele
     for (uint32_t tap0 = 0; tap0 < n_taps; tap0 += kMaxTapsPerPass)
         {
             const int T = (int)std::min<uint32_t>(kMaxTapsPerPass, n_taps - tap0);
+            h->prof.begin(0, h->stream);
             if (cplx)
                 launch_taps<float2>(T, grid, smem, h->stream, d_cp, d_shifts, d_ss, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
                     h->d_out.as<float2>(), (int)n_taps, (int)tap0, smem_elems);
             else
                 launch_taps<float>(T, grid, smem, h->stream, d_cp, d_shifts, d_ss, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
                     h->d_out.as<float2>(), (int)n_taps, (int)tap0, smem_elems);
+            h->prof.end(h->stream);
             h->launches++;
             B200_CUDA(cudaGetLastError());
         }
@@ -547,6 +550,7 @@ extern "C"
         h->d_out.release();
         h->h_out.release();
         h->d_idx.release();
+        h->prof.release();
         if (h->stream) cudaStreamDestroy(h->stream);
         delete h;
         return GNSS_B200_OK;
@@ -672,6 +676,23 @@ extern "C"
         B200_CUDA(cudaGetLastError());
         B200_CUDA(cudaMemcpyAsync(idx_out, h->d_idx.p, obytes, cudaMemcpyDeviceToHost, h->stream));
         B200_CUDA(cudaStreamSynchronize(h->stream));
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_mc_profile(gnss_b200_mc* h, int enable, double* ms_by_kernel, uint64_t* launches_by_kernel, int reset)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "mc_profile: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->device));
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        h->prof.collect();
+        for (int i = 0; i < GNSS_B200_PROFILE_SLOTS; i++)
+            {
+                if (ms_by_kernel) ms_by_kernel[i] = h->prof.ms[i];
+                if (launches_by_kernel) launches_by_kernel[i] = h->prof.count[i];
+            }
+        if (reset) h->prof.reset();
+        h->prof.on = enable != 0;
         return GNSS_B200_OK;
     }
 

@@ -149,6 +149,14 @@ extern "C"
     /* calculate_threshold (:894-909): 2 * gamma_p_inv(2*dof_dwells, (1-pfa)^(1/num_bins)). Host only. */
     GNSS_B200_API float gnss_b200_acq_threshold(float pfa, uint32_t effective_size, uint32_t n_doppler, uint32_t max_dwells, int bit_transition);
 
+    /* Per-kernel timing with CUDA events on the handle's stream. enable = 1 starts recording around every kernel
+       launch; the call synchronises, returns the accumulated milliseconds and launch counts per kernel class and
+       (reset != 0) clears them. Kernel classes of the acquisition handle: 0 forward FFT stages, 1 inverse first
+       stage (two-stage plans), 2 inverse last stage + |.|^2 + row reductions, 3 code spectra, 4 decision kernels.
+       Multicorrelator handle: 0 the fused correlator kernel. */
+#define GNSS_B200_PROFILE_SLOTS 8
+    GNSS_B200_API int gnss_b200_acq_profile(gnss_b200_acq* h, int enable, double* ms_by_kernel, uint64_t* launches_by_kernel, int reset);
+
     /* The CUDA stream (cudaStream_t) the handle launches on, and the number of kernel launches it has issued
        (for event timing and launch accounting by the caller). */
     GNSS_B200_API void* gnss_b200_acq_stream(gnss_b200_acq* h);
@@ -210,6 +218,7 @@ extern "C"
     GNSS_B200_API int gnss_b200_mc_chip_indices(gnss_b200_mc* h, uint32_t ch, const gnss_b200_mc_args* args,
         const float* shifts, uint32_t n_taps, uint32_t flags, int32_t* idx_out /* [n_taps][n_samples] */);
 
+    GNSS_B200_API int gnss_b200_mc_profile(gnss_b200_mc* h, int enable, double* ms_by_kernel, uint64_t* launches_by_kernel, int reset);
     GNSS_B200_API void* gnss_b200_mc_stream(gnss_b200_mc* h);
     GNSS_B200_API uint64_t gnss_b200_mc_launch_count(const gnss_b200_mc* h);
 
@@ -223,6 +232,9 @@ extern "C"
     GNSS_B200_API int gnss_b200_debug_wipeoff_phase(int32_t doppler_hz_with_bias, double fs, uint32_t n_samples, float* phase_out, uint32_t* n_pieces);
     /* The FFT plan for length n: number of stages, radices (lowest stride first) and the position -> frequency
        permutation of the forward transform's output (any of the out pointers may be NULL). */
+    /* Measured FP32 FMA throughput of the device [TFLOP/s] (dependent-chain FFMA loop over all SMs): the
+       denominator for the FP32 roofline of the acquisition kernels, which no driver-written file provides. */
+    GNSS_B200_API int gnss_b200_debug_fp32_peak(int32_t device, double* tflops);
     GNSS_B200_API int gnss_b200_debug_fft_plan(uint32_t n, uint32_t* n_stages, uint32_t* radices, uint32_t* n_radices, uint32_t* perm);
 
 #ifdef __cplusplus
