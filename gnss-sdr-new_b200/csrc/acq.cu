@@ -13,7 +13,7 @@ using namespace b200;
 namespace
 {
 constexpr uint32_t kMaxSingleStagePoints = 24576;  // 192 KiB of complex64 in one CTA's shared memory
-constexpr size_t kScratchBudgetBytes = 48ull << 20;  // two-stage intermediate kept L2-resident by chunking rows
+constexpr size_t kScratchBudgetBytes = 80ull << 20;  // two-stage intermediate kept L2-resident by chunking rows
 constexpr uint32_t kMaxCachedGroups = 64;
 enum
 {
@@ -310,12 +310,13 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 const size_t smem_lo = ((size_t)fa.nb * pitch * pl.rb_lo + fa.M_lo) * sizeof(float2);
                 const size_t smem_hi = ((size_t)fa.M_hi * fa.C + fa.M_hi) * sizeof(float2);
                 const dim3 block_hi(fa.C, std::max(1u, (uint32_t)kFastThreads / fa.C));
+                const uint32_t threads_lo = std::min<uint32_t>(kFastThreads, (fa.nb * pl.rb_lo + 31) / 32 * 32);
                 for (uint32_t y0 = 0; y0 < rows; y0 += chunk)
                     {
                         const uint32_t cnt = std::min(chunk, rows - y0);
                         fa.y0 = y0;
                         h->prof.begin(CAT_INV_FIRST, h->stream);
-                        cudaError_t e = launch_inv_lower(pl.ra_lo, pl.rb_lo, dim3(cnt, fa.M_hi / fa.nb), smem_lo, h->stream, fa);
+                        cudaError_t e = launch_inv_lower(pl.ra_lo, pl.rb_lo, dim3(cnt, fa.M_hi / fa.nb), threads_lo, smem_lo, h->stream, fa);
                         h->prof.end(h->stream);
                         h->launches++;
                         B200_CUDA(e);

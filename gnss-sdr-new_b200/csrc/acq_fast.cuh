@@ -183,6 +183,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     if (a.mag_base)
         mag = a.mag_is_rowbuf ? a.mag_base + (size_t)si * a.eff : a.mag_base + ((size_t)a.slots[si] * a.nD_local + kk) * a.eff;
     const bool accumulate = mag && !a.mag_is_rowbuf && a.dwell_after[si] > 1;
+    const bool full_rows = (a.mag_offset == 0 && a.eff == a.N);
     float best = -1.f, sum = 0.f;
     uint32_t best_i = 0xffffffffu;
     for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
@@ -191,21 +192,55 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
 #pragma unroll
             for (int u = 0; u < RB; u++) v[u] = s[(size_t)(aa + RA * u) * C + c];
             fft::Dft<RB, true>::run(v);
-#pragma unroll
-            for (int b = 0; b < RB; b++)
+            if (full_rows)
                 {
-                    const uint32_t pos = (aa + RA * b) * a.M_lo + c0 + c;  // natural time index
-                    const uint32_t m = pos - a.mag_offset;
-                    if (m < a.eff)
+                    // common case (no bit transition): every output belongs to the row. Track the pencil maximum with
+                    // FMNMX and resolve the index only when it can change the running best (rare after warm-up).
+                    float g[RB];
+                    float pm = -1.f;
+                    const uint32_t pos0 = aa * a.M_lo + c0 + c;
+                    const uint32_t pstep = RA * a.M_lo;
+#pragma unroll
+                    for (int b = 0; b < RB; b++)
                         {
-                            float g = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
-                            if (accumulate) g = mag[m] + g;               // :679
-                            if (mag) mag[m] = g;
-                            sum += g;
-                            if (g > best || (g == best && m < best_i))
+                            g[b] = v[b].x * v[b].x + v[b].y * v[b].y;            // :674
+                            if (accumulate) g[b] = mag[pos0 + b * pstep] + g[b];  // :679
+                            if (mag) mag[pos0 + b * pstep] = g[b];
+                            sum += g[b];
+                            pm = fmaxf(pm, g[b]);
+                        }
+                    if (pm >= best)
+                        {
+#pragma unroll
+                            for (int b = 0; b < RB; b++)
                                 {
-                                    best = g;
-                                    best_i = m;
+                                    const uint32_t m = pos0 + b * pstep;
+                                    if (g[b] > best || (g[b] == best && m < best_i))
+                                        {
+                                            best = g[b];
+                                            best_i = m;
+                                        }
+                                }
+                        }
+                }
+            else
+                {
+#pragma unroll
+                    for (int b = 0; b < RB; b++)
+                        {
+                            const uint32_t pos = (aa + RA * b) * a.M_lo + c0 + c;  // natural time index
+                            const uint32_t m = pos - a.mag_offset;
+                            if (m < a.eff)
+                                {
+                                    float g = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                                    if (accumulate) g = mag[m] + g;               // :679
+                                    if (mag) mag[m] = g;
+                                    sum += g;
+                                    if (g > best || (g == best && m < best_i))
+                                        {
+                                            best = g;
+                                            best_i = m;
+                                        }
                                 }
                         }
                 }
@@ -252,7 +287,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
 }
 
 // host-side launchers (instantiations live in acq_fast_lower.cu / acq_fast_upper.cu)
-cudaError_t launch_inv_lower(uint32_t ra, uint32_t rb, dim3 grid, size_t smem, cudaStream_t st, const FastArgs& a);
+cudaError_t launch_inv_lower(uint32_t ra, uint32_t rb, dim3 grid, uint32_t threads, size_t smem, cudaStream_t st, const FastArgs& a);
 cudaError_t launch_inv_upper(uint32_t ra, uint32_t rb, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a);
 
 }  // namespace b200

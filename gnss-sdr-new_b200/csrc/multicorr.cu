@@ -291,6 +291,192 @@ __global__ void __launch_bounds__(kThreads) multicorr_kernel(const ChanParams* _
     if (threadIdx.x == 0) tickets[blockIdx.y] = 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Fast path (real codes, plain resampler, chip window fits shared memory) — the BASELINE config-5 case.
+// Blackwell packed-FP32 instructions do two taps per instruction: FADD2 for the two binary32 additions of the
+// reference's chip-phase expression, FADD2.RM against 1.5*2^23 for the floor (exact for |phase| < 2^22, and off
+// the quarter-rate conversion pipe), and FFMA2 for the complex accumulate with the chip held as a (c, c) pair.
+// Every lane of a packed op is an IEEE binary32 round-to-nearest (resp. round-down) operation, so the chip
+// indices stay bit-identical to volk_gnsssdr_32f_xn_resampler_32f_xn_generic.
+// ------------------------------------------------------------------------------------------------
+constexpr float kFloorMagic = 12582912.0f;  // 1.5 * 2^23
+constexpr int kFloorMagicBits = 0x4B400000;
+
+template <int T>
+__global__ void __launch_bounds__(kThreads) multicorr_window_kernel(const ChanParams* __restrict__ chans, const float* __restrict__ shifts_all,
+    float2* __restrict__ partials, uint32_t* __restrict__ tickets, float2* __restrict__ out, int n_taps_total, int tap0, uint32_t smem_elems)
+{
+    constexpr int TP = (T + 1) / 2;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* s_code2 = reinterpret_cast<float2*>(smem_raw);
+    __shared__ float2 s_red[kThreads / 32][T];
+    __shared__ int s_last;
+
+    const ChanParams cp = chans[blockIdx.y];
+    const uint32_t splits = gridDim.x;
+    const uint32_t per = (cp.n + splits - 1) / splits;
+    const uint32_t n0 = min(cp.n, blockIdx.x * per), n1 = min(cp.n, n0 + per);
+    const int L = (int)cp.code_len;
+    const float* g_code = static_cast<const float*>(cp.code);
+
+    float2 shift2[TP];
+    float smin = 3.4e38f, smax = -3.4e38f;
+#pragma unroll
+    for (int p = 0; p < TP; p++)
+        {
+            const float s0 = shifts_all[cp.shifts_off + tap0 + 2 * p];
+            const float s1 = shifts_all[cp.shifts_off + min(tap0 + 2 * p + 1, n_taps_total - 1)];
+            shift2[p] = make_float2(s0, s1);
+            smin = fminf(smin, fminf(s0, s1));
+            smax = fmaxf(smax, fmaxf(s0, s1));
+        }
+    const double a0 = (double)cp.code_step * (double)n0, a1 = (double)cp.code_step * (double)(n1 > n0 ? n1 - 1 : n0);
+    const int lo = (int)floor(fmin(a0, a1) + (double)smin - (double)cp.rem_code) - 2;
+    const int width = min((int)smem_elems, (int)floor(fmax(a0, a1) + (double)smax - (double)cp.rem_code) + 2 - lo + 1);
+    {
+        int src = wrap_chip(lo + (int)threadIdx.x, L);
+        const int adv = kThreads % L;
+        for (int j = threadIdx.x; j < width; j += kThreads)
+            {
+                const float c = g_code[src];
+                s_code2[j] = make_float2(c, c);
+                src += adv;
+                if (src >= L) src -= L;
+            }
+    }
+    __syncthreads();
+
+    float2 acc[2 * TP];
+#pragma unroll
+    for (int t = 0; t < 2 * TP; t++) acc[t] = make_float2(0.f, 0.f);
+
+    uint32_t n = n0 + threadIdx.x;
+    if (n < n1)
+        {
+            double ang = cp.theta * (double)n;
+            ang -= 6.283185307179586476925286766559 * rint(ang * 0.15915494309189533576888376337251);
+            float sr, cr;
+            sincosf((float)ang, &sr, &cr);
+            float2 ph = make_float2(cp.p0_re * cr - cp.p0_im * sr, cp.p0_re * sr + cp.p0_im * cr);
+            const float2 wb = make_float2(cp.wb_re, cp.wb_im);
+            const float step = cp.code_step;
+            const float2 nrem2 = make_float2(-cp.rem_code, -cp.rem_code);
+            const float2 magic2 = make_float2(kFloorMagic, kFloorMagic);
+            const int koff = kFloorMagicBits + lo;
+
+            auto one_sample = [&](const float2 x, const uint32_t nn, const float2 p) {
+                const float2 z = make_float2(x.x * p.x - x.y * p.y, x.x * p.y + x.y * p.x);
+                const float a = __fmul_rn(step, (float)nn);
+                const float2 a2 = make_float2(a, a);
+#pragma unroll
+                for (int q = 0; q < TP; q++)
+                    {
+                        // floor(fl(fl(a + shift) - rem)) for two taps at once
+                        const float2 f = __fadd2_rd(__fadd2_rn(__fadd2_rn(a2, shift2[q]), nrem2), magic2);
+                        const float2 c0 = s_code2[__float_as_int(f.x) - koff];
+                        const float2 c1 = s_code2[__float_as_int(f.y) - koff];
+                        acc[2 * q] = __ffma2_rn(c0, z, acc[2 * q]);
+                        acc[2 * q + 1] = __ffma2_rn(c1, z, acc[2 * q + 1]);
+                    }
+            };
+
+            // two samples in flight per thread
+            for (; n + kThreads < n1; n += 2 * kThreads)
+                {
+                    const float2 x0 = __ldg(cp.sig + n);
+                    const float2 x1 = __ldg(cp.sig + n + kThreads);
+                    const float2 ph1 = make_float2(ph.x * wb.x - ph.y * wb.y, ph.x * wb.y + ph.y * wb.x);
+                    one_sample(x0, n, ph);
+                    one_sample(x1, n + kThreads, ph1);
+                    ph = make_float2(ph1.x * wb.x - ph1.y * wb.y, ph1.x * wb.y + ph1.y * wb.x);
+                }
+            if (n < n1) one_sample(__ldg(cp.sig + n), n, ph);
+        }
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int t = 0; t < T; t++)
+        {
+            float2 v = acc[t];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                {
+                    v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+                    v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+                }
+            if (lane == 0) s_red[warp][t] = v;
+        }
+    __syncthreads();
+    const int live = min(T, n_taps_total - tap0);
+    if (threadIdx.x < live)
+        {
+            float2 v = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int w = 0; w < kThreads / 32; w++)
+                {
+                    v.x += s_red[w][threadIdx.x].x;
+                    v.y += s_red[w][threadIdx.x].y;
+                }
+            if (splits == 1)
+                out[(size_t)blockIdx.y * n_taps_total + tap0 + threadIdx.x] = v;
+            else
+                partials[((size_t)blockIdx.y * splits + blockIdx.x) * n_taps_total + tap0 + threadIdx.x] = v;
+        }
+    if (splits == 1) return;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+        {
+            const uint32_t ticket = atomicAdd(&tickets[blockIdx.y], 1u);
+            s_last = (ticket == splits - 1);
+        }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x < live)
+        {
+            float2 v = make_float2(0.f, 0.f);
+            for (uint32_t sp = 0; sp < splits; sp++)
+                {
+                    const float2 p = __ldcg(&partials[((size_t)blockIdx.y * splits + sp) * n_taps_total + tap0 + threadIdx.x]);
+                    v.x += p.x;
+                    v.y += p.y;
+                }
+            out[(size_t)blockIdx.y * n_taps_total + tap0 + threadIdx.x] = v;
+        }
+    if (threadIdx.x == 0) tickets[blockIdx.y] = 0;
+}
+
+void launch_window(int T, dim3 grid, size_t smem, cudaStream_t st, const ChanParams* chans, const float* shifts, float2* partials,
+    uint32_t* tickets, float2* out, int n_taps_total, int tap0, uint32_t smem_elems)
+{
+#define B200_MCW_CASE(TT)                                                                                                                  \
+    case TT:                                                                                                                               \
+        cudaFuncSetAttribute(multicorr_window_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCapBytes);                  \
+        multicorr_window_kernel<TT><<<grid, kThreads, smem, st>>>(chans, shifts, partials, tickets, out, n_taps_total, tap0, smem_elems);   \
+        break;
+    switch (T)
+        {
+            B200_MCW_CASE(1)
+            B200_MCW_CASE(2)
+            B200_MCW_CASE(3)
+            B200_MCW_CASE(4)
+            B200_MCW_CASE(5)
+            B200_MCW_CASE(6)
+            B200_MCW_CASE(7)
+            B200_MCW_CASE(8)
+            B200_MCW_CASE(9)
+            B200_MCW_CASE(10)
+            B200_MCW_CASE(11)
+            B200_MCW_CASE(12)
+            B200_MCW_CASE(13)
+            B200_MCW_CASE(14)
+            B200_MCW_CASE(15)
+            B200_MCW_CASE(16)
+        }
+#undef B200_MCW_CASE
+}
+
 // parity aid: the wrapped chip index of every (tap, sample) of one channel
 __global__ void chip_index_kernel(ChanParams cp, const float* __restrict__ shifts, const uint32_t* __restrict__ shift_samples,
     int n_taps, int32_t* __restrict__ out)
@@ -376,7 +562,7 @@ namespace
 {
 // Host half of one batch: per-channel constants (the reference computes these at cpu_multicorrelator_real_codes.cc:114-119).
 int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_b200_mc_args* args, const float* shifts, uint32_t n_taps,
-    uint32_t flags, const float2* d_sig_base, uint64_t ch_stride, bool device_resident, uint32_t* out_smem_elems, uint32_t* out_splits, bool* out_complex)
+    uint32_t flags, const float2* d_sig_base, uint64_t ch_stride, bool device_resident, uint32_t* out_smem_elems, uint32_t* out_splits, bool* out_complex, bool* out_fast = nullptr)
 {
     const size_t bytes = sizeof(ChanParams) * n_ch + sizeof(float) * n_ch * n_taps + sizeof(uint32_t) * n_ch * n_taps;
     B200_CUDA(h->h_params.reserve(bytes));
@@ -466,6 +652,24 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
         }
     const uint32_t elem = cplx ? 8u : 4u;
     const uint32_t cap = kSmemCapBytes / elem;
+    // fast (packed, window-only) kernel: real code, plain resampler, window of (c,c) pairs fits, |chip phase| < 2^22
+    bool fast = !cplx && !hd_res && max_window <= kSmemCapBytes / 8;
+    for (uint32_t i = 0; i < n_ch && fast; i++)
+        {
+            const gnss_b200_mc_args& a = args[i];
+            double lim = 0.0;
+            for (uint32_t t = 0; t < n_taps; t++) lim = std::max(lim, std::fabs((double)hs[(size_t)i * n_taps + t]));
+            lim += std::fabs((double)a.code_step_chips) * (double)a.n_samples + std::fabs((double)a.rem_code_phase_chips);
+            if (!(lim < 4.0e6)) fast = false;
+        }
+    if (out_fast) *out_fast = fast;
+    if (fast)
+        {
+            *out_smem_elems = (uint32_t)std::max<uint64_t>(max_window, 32);
+            *out_splits = splits;
+            *out_complex = false;
+            return GNSS_B200_OK;
+        }
     uint64_t want = hd_res ? max_len : max_window;
     if (!hd_res && want > cap && max_len <= cap) want = max_len;  // window too wide: hold the whole code instead
     *out_smem_elems = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(want, 32), cap);
@@ -474,7 +678,7 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
     return GNSS_B200_OK;
 }
 
-int run_batch(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, uint32_t smem_elems, uint32_t splits, bool cplx)
+int run_batch(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, uint32_t smem_elems, uint32_t splits, bool cplx, bool fast)
 {
     const size_t pbytes = sizeof(ChanParams) * n_ch + sizeof(float) * n_ch * n_taps + sizeof(uint32_t) * n_ch * n_taps;
     B200_CUDA(cudaMemcpyAsync(h->d_params.p, h->h_params.p, pbytes, cudaMemcpyHostToDevice, h->stream));
@@ -490,7 +694,10 @@ int run_batch(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, uint32_t smem_ele
         {
             const int T = (int)std::min<uint32_t>(kMaxTapsPerPass, n_taps - tap0);
             h->prof.begin(0, h->stream);
-            if (cplx)
+            if (fast)
+                launch_window(T, grid, (size_t)smem_elems * 8, h->stream, d_cp, d_shifts, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
+                    h->d_out.as<float2>(), (int)n_taps, (int)tap0, smem_elems);
+            else if (cplx)
                 launch_taps<float2>(T, grid, smem, h->stream, d_cp, d_shifts, d_ss, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
                     h->d_out.as<float2>(), (int)n_taps, (int)tap0, smem_elems);
             else
@@ -594,8 +801,8 @@ extern "C"
         for (uint32_t i = 0; i < n_ch; i++) any_host |= (args[i].sig_in_c64 != nullptr);
         if (any_host) B200_CUDA(h->d_sig.reserve((size_t)h->max_channels * h->max_samples * 8));
         uint32_t smem_elems, splits;
-        bool cplx;
-        int rc = build_params(h, n_ch, ch, args, shifts, n_taps, flags, nullptr, 0, false, &smem_elems, &splits, &cplx);
+        bool cplx, fast;
+        int rc = build_params(h, n_ch, ch, args, shifts, n_taps, flags, nullptr, 0, false, &smem_elems, &splits, &cplx, &fast);
         if (rc) return rc;
         // host -> device sample copies; runs of channels that are contiguous in host memory go as one copy
         for (uint32_t i = 0; i < n_ch;)
@@ -613,7 +820,7 @@ extern "C"
                 B200_CUDA(cudaMemcpyAsync(h->d_sig.as<float2>() + (size_t)i * h->max_samples, args[i].sig_in_c64, bytes, cudaMemcpyHostToDevice, h->stream));
                 i = j;
             }
-        rc = run_batch(h, n_ch, n_taps, smem_elems, splits, cplx);
+        rc = run_batch(h, n_ch, n_taps, smem_elems, splits, cplx, fast);
         if (rc) return rc;
         B200_CUDA(cudaStreamSynchronize(h->stream));
         std::memcpy(out_c64, h->h_out.p, sizeof(float2) * (size_t)n_ch * n_taps);
@@ -629,10 +836,10 @@ extern "C"
         std::lock_guard<std::mutex> lk(h->mu);
         B200_CUDA(cudaSetDevice(h->device));
         uint32_t smem_elems, splits;
-        bool cplx;
-        int rc = build_params(h, n_ch, ch, args, shifts, n_taps, flags, static_cast<const float2*>(d_sig), ch_stride_samples, true, &smem_elems, &splits, &cplx);
+        bool cplx, fast;
+        int rc = build_params(h, n_ch, ch, args, shifts, n_taps, flags, static_cast<const float2*>(d_sig), ch_stride_samples, true, &smem_elems, &splits, &cplx, &fast);
         if (rc) return rc;
-        return run_batch(h, n_ch, n_taps, smem_elems, splits, cplx);
+        return run_batch(h, n_ch, n_taps, smem_elems, splits, cplx, fast);
     }
 
     int gnss_b200_mc_sync(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, float* out_c64)
