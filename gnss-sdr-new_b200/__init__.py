@@ -10,6 +10,8 @@ import os
 
 import numpy as np
 
+from . import sharding  # noqa: F401  (multi-GPU partition / gather host logic)
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgnss_b200.so")
 
