@@ -42,6 +42,32 @@ def build(force=False, verbose=False):
     return LIB
 
 
+HOST_DIR = os.path.join(HERE, "host")
+HOST_LIB = os.path.join(HERE, "libgnss_b200_host.so")
+HOST_SOURCES = ["b200_correlator_pool.cc", "b200_multicorrelator_real_codes.cc", "b200_multicorrelator.cc",
+                "b200_acquisition_bank.cc", "pcps_acquisition_b200.cc"]
+HOST_TEST_SRC = os.path.join(HERE, "..", "tests", "host", "host_mirror_test.cc")
+HOST_TEST_BIN = os.path.join(HERE, "..", "tests", "host", "host_mirror_test")
+
+
+def build_host(force=False):
+    """The host C++ mirror of the reference's block / correlator classes (standalone flavour: stand-in headers for
+    Acq_Conf / Gnss_Synchro / ChannelFsm), and the test driver that exercises it. Plain g++; links the C-ABI library."""
+    build(force=False)
+    srcs = [os.path.join(HOST_DIR, f) for f in HOST_SOURCES]
+    deps = srcs + [os.path.join(HOST_DIR, f) for f in os.listdir(HOST_DIR) if f.endswith(".h")] + [LIB, HOST_TEST_SRC]
+    if not force and os.path.exists(HOST_LIB) and os.path.exists(HOST_TEST_BIN) and \
+            all(os.path.getmtime(d) <= min(os.path.getmtime(HOST_LIB), os.path.getmtime(HOST_TEST_BIN)) for d in deps):
+        return HOST_LIB, HOST_TEST_BIN
+    inc = ["-I", os.path.join(HERE, "..", "include"), "-I", HOST_DIR]
+    common = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", "-fPIC", "-pthread", "-DB200_HOST_STANDALONE"] + inc
+    subprocess.run(common + ["-shared", "-o", HOST_LIB] + srcs + ["-L", HERE, "-lgnss_b200", "-Wl,-rpath,$ORIGIN"], check=True)
+    subprocess.run(common + ["-o", HOST_TEST_BIN, HOST_TEST_SRC, "-L", HERE, "-lgnss_b200_host", "-lgnss_b200",
+                             "-Wl,-rpath,$ORIGIN/../../gnss-sdr-new_b200"], check=True)
+    return HOST_LIB, HOST_TEST_BIN
+
+
 if __name__ == "__main__":
     import sys
     print(build(force=True, verbose="-v" in sys.argv))
+    print(build_host(force=True))

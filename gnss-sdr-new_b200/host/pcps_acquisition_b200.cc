@@ -1,0 +1,481 @@
+/*
+ * pcps_acquisition_b200.cc — see the header. Comments of the form ":NNN" point at the line of
+ * src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.cc whose behaviour the statement reproduces.
+ */
+#include "pcps_acquisition_b200.h"
+#if !defined(B200_HOST_STANDALONE)
+#include "GLONASS_L1_L2_CA.h"  // DFRQ1_GLO, DFRQ2_GLO, GLONASS_PRN
+#endif
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <iostream>
+#include <stdexcept>
+#include <thread>
+
+pcps_acquisition_b200_sptr pcps_make_acquisition_b200(const Acq_Conf& conf_)
+{
+    return pcps_acquisition_b200_sptr(new pcps_acquisition_b200(conf_));
+}
+
+
+pcps_acquisition_b200::pcps_acquisition_b200(const Acq_Conf& conf_)
+    : d_acq_parameters(conf_),
+      d_samplesPerChip(conf_.samples_per_chip),
+      d_doppler_step(static_cast<uint32_t>(conf_.doppler_step)),
+      d_consumed_samples(static_cast<uint32_t>(conf_.sampled_ms * conf_.samples_per_ms * (conf_.bit_transition_flag ? 2.0 : 1.0))),  // :71
+      d_use_CFAR_algorithm_flag(conf_.use_CFAR_algorithm_flag)
+{
+    if (conf_.make_2_steps || conf_.make_repeat_steps)
+        {
+            throw std::invalid_argument("pcps_acquisition_b200: make_two_steps / make_repeat_steps are not available in the B200 implementation yet");
+        }
+    if (conf_.dump)
+        {
+            throw std::invalid_argument("pcps_acquisition_b200: dump=true is not available in the B200 implementation yet");
+        }
+    if (d_consumed_samples == 0)
+        {
+            throw std::invalid_argument("pcps_acquisition_b200: sampled_ms * samples_per_ms is zero");
+        }
+    d_fft_size = (conf_.sampled_ms == conf_.ms_per_code) ? d_consumed_samples : d_consumed_samples * 2;  // :85-92
+    d_cshort = (conf_.it_size != sizeof(std::complex<float>));                                           // :121-128
+    d_data_buffer.resize(d_consumed_samples);
+    if (d_cshort) d_data_buffer_sc.resize(static_cast<size_t>(d_consumed_samples) * 2);
+}
+
+
+pcps_acquisition_b200::~pcps_acquisition_b200()
+{
+    if (d_bank && d_slot >= 0) d_bank->release_slot(d_slot);
+}
+
+
+void pcps_acquisition_b200::require_engine(const char* where) const
+{
+    if (!d_bank || d_slot < 0)
+        {
+            // The reference has no failure path here; running without the device would silently change results,
+            // so this is loud.
+            throw std::runtime_error(std::string("pcps_acquisition_b200::") + where + ": B200 engine not available (call init() on a machine with a CUDA device)");
+        }
+}
+
+
+void pcps_acquisition_b200::set_gnss_synchro(Gnss_Synchro* p_gnss_synchro)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    d_gnss_synchro = p_gnss_synchro;
+}
+
+
+void pcps_acquisition_b200::set_active(bool active)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    d_active = active;
+}
+
+
+void pcps_acquisition_b200::set_threshold(float threshold)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    d_threshold = threshold;
+}
+
+
+void pcps_acquisition_b200::set_doppler_max(uint32_t doppler_max)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    d_acq_parameters.doppler_max = static_cast<int32_t>(doppler_max);
+}
+
+
+void pcps_acquisition_b200::set_doppler_step(uint32_t doppler_step)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    d_doppler_step = doppler_step;
+}
+
+
+void pcps_acquisition_b200::set_resampler_latency(uint32_t latency_samples)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    d_acq_parameters.resampler_latency_samples = latency_samples;  // :170-174
+}
+
+
+// pcps_acquisition.h:199-208 — a new centre rebuilds the wipe-off grid; here it re-keys the slot's Doppler group
+void pcps_acquisition_b200::set_doppler_center(int32_t doppler_center)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    if (doppler_center != d_doppler_center)
+        {
+            d_doppler_center = doppler_center;
+            refresh_doppler_grid();
+        }
+}
+
+
+void pcps_acquisition_b200::refresh_doppler_grid()
+{
+    if (d_bank && d_slot >= 0) d_bank->set_doppler_center(d_slot, d_doppler_center, d_doppler_bias);  // :298-306
+}
+
+
+// :212-230
+bool pcps_acquisition_b200::is_fdma()
+{
+    d_doppler_bias = 0;
+#if !defined(B200_HOST_STANDALONE)
+    if (d_gnss_synchro != nullptr && std::strcmp(d_gnss_synchro->Signal, "1G") == 0)
+        {
+            d_doppler_bias = static_cast<int32_t>(DFRQ1_GLO * GLONASS_PRN.at(d_gnss_synchro->PRN));
+            return true;
+        }
+    if (d_gnss_synchro != nullptr && std::strcmp(d_gnss_synchro->Signal, "2G") == 0)
+        {
+            d_doppler_bias += static_cast<int32_t>(DFRQ2_GLO * GLONASS_PRN.at(d_gnss_synchro->PRN));
+            return true;
+        }
+#endif
+    return false;
+}
+
+
+// :176-209 — zero-pad layout, forward FFT and conjugation happen on the device (gnss_b200_acq_set_local_code)
+void pcps_acquisition_b200::set_local_code(std::complex<float>* code)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    if (is_fdma())
+        {
+            refresh_doppler_grid();  // :179-183
+        }
+    const uint32_t n = d_acq_parameters.bit_transition_flag ? d_fft_size / 2 : d_consumed_samples;
+    d_code_copy.assign(d_consumed_samples, std::complex<float>(0.0F, 0.0F));
+    std::copy(code, code + n, d_code_copy.begin());
+    d_have_code = true;
+    if (d_bank && d_slot >= 0)
+        {
+            if (!d_bank->set_local_code(d_slot, d_code_copy.data()))
+                {
+                    throw std::runtime_error("pcps_acquisition_b200::set_local_code: " + d_bank->last_error());
+                }
+        }
+}
+
+
+// :249-295
+void pcps_acquisition_b200::init()
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    if (d_gnss_synchro != nullptr)
+        {
+            d_gnss_synchro->Flag_valid_acquisition = false;
+            d_gnss_synchro->Flag_valid_symbol_output = false;
+            d_gnss_synchro->Flag_valid_pseudorange = false;
+            d_gnss_synchro->Flag_valid_word = false;
+            d_gnss_synchro->Acq_doppler_step = 0U;
+            d_gnss_synchro->Acq_delay_samples = 0.0;
+            d_gnss_synchro->Acq_doppler_hz = 0.0;
+            d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
+        }
+    d_mag = 0.0;
+    d_input_power = 0.0;
+    d_num_doppler_bins = static_cast<uint32_t>(std::ceil(static_cast<double>(static_cast<int32_t>(d_acq_parameters.doppler_max) - static_cast<int32_t>(-d_acq_parameters.doppler_max)) / static_cast<double>(d_doppler_step)));  // :264
+
+    B200_Acquisition_Bank::Geometry g{};
+    g.fft_size = d_fft_size;
+    g.consumed_samples = d_consumed_samples;
+    g.doppler_max = d_acq_parameters.doppler_max;
+    g.doppler_step = d_doppler_step;
+    g.fs = static_cast<double>(d_acq_parameters.fs_in);
+    g.samples_per_chip = d_samplesPerChip;
+    g.bit_transition = d_acq_parameters.bit_transition_flag;
+    g.use_cfar = d_use_CFAR_algorithm_flag;
+    g.keep_grid = d_acq_parameters.max_dwells > 1 && !d_acq_parameters.bit_transition_flag;  // only then is the grid accumulated (:672-684)
+    g.device = 0;
+    std::string why;
+    auto bank = B200_Acquisition_Bank::get(g, &why);
+    if (!bank)
+        {
+            throw std::runtime_error("pcps_acquisition_b200::init: cannot create the B200 engine: " + why);
+        }
+    if (bank != d_bank)
+        {
+            if (d_bank && d_slot >= 0) d_bank->release_slot(d_slot);
+            d_bank = bank;
+            d_slot = d_bank->acquire_slot();
+            if (d_slot < 0) throw std::runtime_error("pcps_acquisition_b200::init: " + d_bank->last_error());
+            if (d_have_code && !d_bank->set_local_code(d_slot, d_code_copy.data()))  // d_fft_codes survives init() in the reference
+                {
+                    throw std::runtime_error("pcps_acquisition_b200::init: " + d_bank->last_error());
+                }
+        }
+    d_bank->reset(d_slot);  // :281-284
+    refresh_doppler_grid();  // :286
+    d_num_noncoherent_integrations_counter = 0U;
+    d_worker_active = false;
+}
+
+
+// :317-343
+void pcps_acquisition_b200::set_state(int32_t state)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    d_state = state;
+    if (d_state == 1)
+        {
+            d_gnss_synchro->Acq_delay_samples = 0.0;
+            d_gnss_synchro->Acq_doppler_hz = 0.0;
+            d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
+            d_gnss_synchro->Acq_doppler_step = 0U;
+            d_mag = 0.0;
+            d_test_statistics = 0.0;
+            d_active = true;
+        }
+    else if (d_state != 0)
+        {
+            std::cerr << "pcps_acquisition_b200: State can only be set to 0 or 1\n";
+        }
+}
+
+
+// :345-381
+void pcps_acquisition_b200::send_positive_acquisition()
+{
+    d_positive_acq = 1;
+    if (!d_channel_fsm.expired())
+        {
+            d_channel_fsm.lock()->Event_valid_acquisition();
+        }
+    else
+        {
+            publish_event(1);
+        }
+    if (d_acq_parameters.enable_monitor_output)
+        {
+            d_monitor_queue.push(*d_gnss_synchro);
+        }
+}
+
+
+// :384-405
+void pcps_acquisition_b200::send_negative_acquisition()
+{
+    d_positive_acq = 0;
+    publish_event(2);
+}
+
+
+// :885-890
+bool pcps_acquisition_b200::start()
+{
+    d_sample_counter = 0ULL;
+    calculate_threshold();
+    return true;
+}
+
+
+// :894-909
+void pcps_acquisition_b200::calculate_threshold()
+{
+    const float pfa = d_acq_parameters.pfa;
+    if (pfa <= 0.0) return;
+    const uint32_t effective_fft_size = d_acq_parameters.bit_transition_flag ? d_fft_size / 2 : d_fft_size;
+    d_threshold = gnss_b200_acq_threshold(pfa, effective_fft_size, d_num_doppler_bins, d_acq_parameters.max_dwells, d_acq_parameters.bit_transition_flag ? 1 : 0);
+}
+
+
+// :615-882 without the two-step branches. The Doppler loop (:655-687) and the statistic (:689-696) are one engine call.
+void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
+{
+    std::unique_lock<std::recursive_mutex> lk(d_setlock);
+    require_engine("acquisition_core");
+    d_mag = 0.0;
+    d_num_noncoherent_integrations_counter++;  // :638
+    const void* samples = d_cshort ? static_cast<const void*>(d_data_buffer_sc.data()) : static_cast<const void*>(d_data_buffer.data());
+    if (d_acq_parameters.blocking)
+        {
+            lk.unlock();  // :649-652
+        }
+
+    gnss_b200_acq_result res{};
+    const bool ok = d_bank->dwell(d_slot, samples, d_cshort, samp_count, &res);
+    if (!ok)
+        {
+            // the reference logs and keeps going; a failed device call must not look like a detection
+            std::cerr << "pcps_acquisition_b200: engine dwell failed: " << d_bank->last_error() << '\n';
+            res = gnss_b200_acq_result{};
+        }
+    const uint32_t indext = res.code_phase;
+    const int32_t doppler = res.doppler_hz;
+    d_input_power = res.input_power;
+    d_test_statistics = res.test_statistic;
+
+    if (d_acq_parameters.use_automatic_resampler)  // :699-705
+        {
+            d_gnss_synchro->Acq_delay_samples = static_cast<double>(std::fmod(static_cast<float>(indext), d_acq_parameters.samples_per_code)) * d_acq_parameters.resampler_ratio;
+            d_gnss_synchro->Acq_delay_samples -= static_cast<double>(d_acq_parameters.resampler_latency_samples);
+            d_gnss_synchro->Acq_doppler_hz = static_cast<double>(doppler);
+            d_gnss_synchro->Acq_samplestamp_samples = rint(static_cast<double>(samp_count) * d_acq_parameters.resampler_ratio);
+        }
+    else  // :707-712
+        {
+            d_gnss_synchro->Acq_delay_samples = static_cast<double>(std::fmod(static_cast<float>(indext), d_acq_parameters.samples_per_code));
+            d_gnss_synchro->Acq_doppler_hz = static_cast<double>(doppler);
+            d_gnss_synchro->Acq_samplestamp_samples = samp_count;
+        }
+
+    if (d_acq_parameters.blocking)
+        {
+            lk.lock();  // :776-779
+        }
+
+    if (!d_acq_parameters.bit_transition_flag)  // :781-829
+        {
+            if (d_test_statistics > d_threshold)
+                {
+                    d_active = false;
+                    send_positive_acquisition();
+                    d_state = 0;
+                }
+            else
+                {
+                    d_buffer_count = 0;
+                    d_state = 1;
+                }
+            if (d_num_noncoherent_integrations_counter == d_acq_parameters.max_dwells)
+                {
+                    if (d_state != 0)
+                        {
+                            send_negative_acquisition();
+                        }
+                    d_state = 0;
+                    d_active = false;
+                }
+        }
+    else  // :830-866
+        {
+            d_active = false;
+            if (d_test_statistics > d_threshold)
+                {
+                    send_positive_acquisition();
+                    d_state = 0;
+                }
+            else
+                {
+                    d_state = 0;
+                    send_negative_acquisition();
+                }
+        }
+    d_worker_active = false;
+
+    if ((d_num_noncoherent_integrations_counter == d_acq_parameters.max_dwells) || (d_positive_acq == 1) || d_acq_parameters.bit_transition_flag)  // :869-880
+        {
+            d_num_noncoherent_integrations_counter = 0U;
+            d_positive_acq = 0;
+            d_bank->reset(d_slot);  // the next dwell starts a fresh grid (:672-676 overwrite on counter == 1)
+        }
+}
+
+
+// :912-1050
+int pcps_acquisition_b200::general_work(int noutput_items, std::vector<int>& ninput_items, std::vector<const void*>& input_items,
+    std::vector<void*>& output_items)
+{
+    (void)noutput_items;
+    std::unique_lock<std::recursive_mutex> lk(d_setlock);
+    if (!d_active || d_worker_active)
+        {
+            // do not consume samples while a non-coherent integration is in progress (:931-937)
+            const bool consume_samples = ((!d_active) || (d_active && (d_num_noncoherent_integrations_counter == d_acq_parameters.max_dwells)));
+            if ((!d_acq_parameters.blocking_on_standby) && consume_samples)
+                {
+                    d_sample_counter += static_cast<uint64_t>(ninput_items[0]);
+                    consume_each(ninput_items[0]);
+                }
+            return 0;
+        }
+
+    switch (d_state)
+        {
+        case 0:  // :953-972 — restart
+            {
+                d_gnss_synchro->Acq_delay_samples = 0.0;
+                d_gnss_synchro->Acq_doppler_hz = 0.0;
+                d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
+                d_gnss_synchro->Acq_doppler_step = 0U;
+                d_mag = 0.0;
+                d_state = 1;
+                d_buffer_count = 0U;
+                if (!d_acq_parameters.blocking_on_standby)
+                    {
+                        d_sample_counter += static_cast<uint64_t>(ninput_items[0]);
+                        consume_each(ninput_items[0]);
+                    }
+                break;
+            }
+        case 1:  // :973-1011 — fill the dwell buffer
+            {
+                const uint32_t avail = static_cast<uint32_t>(ninput_items[0]);
+                const uint32_t buff_increment = (avail + d_buffer_count <= d_consumed_samples) ? avail : d_consumed_samples - d_buffer_count;
+                if (d_cshort)
+                    {
+                        const auto* in = static_cast<const int16_t*>(input_items[0]);
+                        std::copy(in, in + static_cast<size_t>(buff_increment) * 2, d_data_buffer_sc.begin() + static_cast<size_t>(d_buffer_count) * 2);
+                    }
+                else
+                    {
+                        const auto* in = static_cast<const std::complex<float>*>(input_items[0]);
+                        std::copy(in, in + buff_increment, d_data_buffer.begin() + d_buffer_count);
+                    }
+                // the reference tests the fill level BEFORE adding this call's samples (:1003-1007), so the state
+                // changes one call after the buffer filled; kept, because the sample stamp depends on it
+                if (d_buffer_count >= d_consumed_samples)
+                    {
+                        d_state = 2;
+                    }
+                d_buffer_count += buff_increment;
+                d_sample_counter += static_cast<uint64_t>(buff_increment);
+                consume_each(static_cast<int>(buff_increment));
+                break;
+            }
+        case 2:  // :1012-1029 — run the search
+            {
+                if (d_acq_parameters.blocking)
+                    {
+                        lk.unlock();
+                        acquisition_core(d_sample_counter);
+                        lk.lock();
+                    }
+                else
+                    {
+                        d_worker_active = true;
+                        std::thread worker(&pcps_acquisition_b200::acquisition_core, this, d_sample_counter);
+                        worker.detach();
+                    }
+                consume_each(0);
+                d_buffer_count = 0U;
+                break;
+            }
+        default:
+            break;
+        }
+
+    // :1032-1047 — monitor output
+    if (d_acq_parameters.enable_monitor_output && !output_items.empty())
+        {
+            auto** out = reinterpret_cast<Gnss_Synchro**>(&output_items[0]);
+            if (!d_monitor_queue.empty())
+                {
+                    const int num_gnss_synchro_objects = static_cast<int>(d_monitor_queue.size());
+                    for (int i = 0; i < num_gnss_synchro_objects; ++i)
+                        {
+                            *out[i] = d_monitor_queue.front();
+                            d_monitor_queue.pop();
+                        }
+                    return num_gnss_synchro_objects;
+                }
+        }
+    return 0;
+}

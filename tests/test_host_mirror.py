@@ -1,0 +1,202 @@
+"""The host C++ mirror (gnss-sdr-new_b200/host): pcps_acquisition_b200 and the B200 correlator classes, driven by
+tests/host/host_mirror_test.cc the way the reference's own tests drive pcps_acquisition
+(gps_l1_ca_pcps_acquisition_test.cc:290-361: Channel call order, set_state(1), feed the capture, check
+Gnss_Synchro against the expected delay / Doppler) and the way dll_pll_veml_tracking drives its correlator object.
+Expected values come from the oracle; the C++ driver computes none."""
+import importlib.util
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+import synth
+from conftest import ROOT, has_gpu
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="module")
+def driver():
+    spec = importlib.util.spec_from_file_location("b200_build", os.path.join(ROOT, "gnss-sdr-new_b200", "build.py"))
+    bld = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bld)
+    return bld.build_host()[1]
+
+
+@pytest.mark.skipif(has_gpu(), reason="checks the no-device behaviour")
+def test_mirror_refuses_to_run_without_a_device(driver):
+    r = subprocess.run([driver, "nodevice"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "mc.init=false acq_threw=true" in r.stdout
+    assert "no CPU path" in r.stdout
+
+
+def test_mirror_keeps_the_reference_method_set():
+    """Same member names and argument lists as the reference classes (cpu_multicorrelator_real_codes.h:40-50,
+    cpu_multicorrelator.h:40-47, pcps_acquisition.h:99-209)."""
+    def text(name):
+        return open(os.path.join(ROOT, "gnss-sdr-new_b200", "host", name)).read()
+    h = text("b200_multicorrelator_real_codes.h")
+    for sig in ("void set_high_dynamics_resampler(bool use_high_dynamics_resampler);",
+                "bool init(int max_signal_length_samples, int n_correlators);",
+                "bool set_local_code_and_taps(int code_length_chips, const float *local_code_in, float *shifts_chips);",
+                "bool set_input_output_vectors(std::complex<float> *corr_out, const std::complex<float> *sig_in);",
+                "float rem_code_phase_chips, float code_phase_step_chips, float code_phase_rate_step_chips, int signal_length_samples);",
+                "bool free();"):
+        assert sig in h, sig
+    h = text("b200_multicorrelator.h")
+    assert "bool set_local_code_and_taps(int code_length_chips, const std::complex<float> *local_code_in, float *shifts_chips);" in h
+    assert "bool Carrier_wipeoff_multicorrelator_resampler(float rem_carrier_phase_in_rad, float phase_step_rad, float rem_code_phase_chips, float code_phase_step_chips, int signal_length_samples);" in h
+    h = text("pcps_acquisition_b200.h")
+    for name in ("void init();", "void set_gnss_synchro(Gnss_Synchro* p_gnss_synchro);", "void set_local_code(std::complex<float>* code);",
+                 "void set_state(int32_t state);", "void set_resampler_latency(uint32_t latency_samples);", "uint32_t mag() const",
+                 "void set_active(bool active);", "void set_channel(uint32_t channel)", "void set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm)",
+                 "void set_threshold(float threshold);", "void set_doppler_max(uint32_t doppler_max);", "void set_doppler_step(uint32_t doppler_step);",
+                 "void set_doppler_center(int32_t doppler_center);", "int general_work(int noutput_items,"):
+        assert name in h, name
+
+
+def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, doppler_step, pfa, threshold, max_dwells, bit_transition,
+                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us):
+    with open(path, "wb") as f:
+        f.write(struct.pack("<q", int(fs)))
+        f.write(struct.pack("<IIIiI", sampled_ms, ms_per_code, spc, doppler_max, doppler_step))
+        f.write(struct.pack("<ff", pfa, threshold))
+        n_items = stream.size // 2 if cshort else stream.size
+        f.write(struct.pack("<IIIIIIIIII", max_dwells, int(bit_transition), int(use_cfar), int(cshort), int(blocking), len(codes), n_items,
+                            chunk, int(use_fsm), coalesce_us))
+        for c in codes:
+            f.write(np.ascontiguousarray(c, dtype=np.complex64).tobytes())
+        f.write(np.ascontiguousarray(stream, dtype=np.int16 if cshort else np.complex64).tobytes())
+
+
+def _read_acq_output(path):
+    raw = open(path, "rb").read()
+    n, = struct.unpack_from("<I", raw, 0)
+    out, off = [], 4
+    for _ in range(n):
+        ev, delay, dop, stamp, stat, thr, nd, nfft = struct.unpack_from("<iddQffII", raw, off)
+        off += struct.calcsize("<iddQffII")
+        out.append(dict(event=ev, delay=delay, doppler=dop, stamp=stamp, stat=stat, threshold=thr, n_doppler=nd, fft_size=nfft))
+    return out
+
+
+def _run(driver, mode, inp, outp):
+    r = subprocess.run([driver, mode, str(inp), str(outp)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_gps_capture_through_the_block_interface(driver, oracle, tmp_path):
+    """gps_l1_ca_pcps_acquisition_test.cc ValidationOfResults: PRN 1, 4 Msps, +-5000/100 Hz... here step 250, threshold
+    0.001 with the first-vs-second-peak test (pfa = 0): positive acquisition, delay 524 samples, Doppler within 666 Hz of 1680."""
+    iq = np.fromfile(os.path.join(GOLD, "GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat"), dtype=np.complex64)
+    code = synth.adapter_code("gps_l1_ca", 1, 4e6, 1)[:4000]
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_acq_input(inp, 4e6, 1, 1, 4, 5000, 250, 0.0, 0.001, 1, False, False, False, True, [code], iq, 1000, True, 0)
+    _run(driver, "acq", inp, outp)
+    got = _read_acq_output(outp)[0]
+    acq = oracle.acq(fft_size=4000, consumed_samples=4000, doppler_max=5000, doppler_step=250, fs=4e6, samples_per_chip=4,
+                     samples_per_code=4000, use_cfar=False)
+    acq.set_local_code(code)
+    # set_state(1) skips the restart state: the dwell buffer fills from the first item on
+    want = acq.dwell(iq[:4000])
+    assert got["event"] == 1
+    assert got["n_doppler"] == 40 and got["fft_size"] == 4000
+    assert got["delay"] == float(np.fmod(np.float32(want["code_phase"]), np.float32(4000)))
+    assert got["doppler"] == float(want["doppler_hz"])
+    assert got["stat"] == pytest.approx(want["test_statistic"], rel=1e-4)
+    assert got["stamp"] == 4000
+    # the reference test's own acceptance window
+    delay_chips = abs(got["delay"] - 524) * 1023.0 / 4000.0
+    assert delay_chips <= 0.5 and abs(got["doppler"] - 1680) <= 666
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cshort,blocking,coalesce_us", [(False, True, 0), (False, True, 20000), (True, False, 0)])
+def test_many_blocks_share_one_engine(driver, oracle, tmp_path, cshort, blocking, coalesce_us):
+    """Six channels (PRN 1..6 of config 1's scene, three of them present) run concurrently, one scheduler thread each;
+    CFAR statistic with pfa-derived threshold; decisions and Gnss_Synchro fields must equal the oracle's per channel."""
+    geo, codes, iq, truth = synth.config_scene("C1", n_prn=6)
+    stream = np.concatenate([iq, iq])
+    scale = 1500.0
+    s_in = synth.to_cshort(stream, scale) if cshort else stream
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_acq_input(inp, geo["fs"], 1, 1, geo["samples_per_chip"], geo["doppler_max"], geo["doppler_step"], 0.01, 0.0, 1, False, True,
+                     cshort, blocking, list(codes), s_in, 4000, False, coalesce_us)
+    _run(driver, "acq", inp, outp)
+    got = _read_acq_output(outp)
+    thr = oracle.threshold(0.01, 4000, 40, 1, False)
+    present = {t["prn"] for t in truth}
+    n_pos = 0
+    for p in range(6):
+        acq = oracle.acq(fft_size=4000, consumed_samples=4000, doppler_max=geo["doppler_max"], doppler_step=geo["doppler_step"],
+                         fs=geo["fs"], samples_per_chip=geo["samples_per_chip"], samples_per_code=geo["samples_per_code"])
+        acq.set_local_code(codes[p])
+        block = s_in.reshape(-1, 2)[:4000].reshape(-1) if cshort else stream[:4000]
+        want = acq.dwell(block)
+        g = got[p]
+        assert g["threshold"] == pytest.approx(thr, rel=2e-6)
+        assert g["stat"] == pytest.approx(want["test_statistic"], rel=1e-4)
+        assert g["event"] == (1 if want["test_statistic"] > thr else 2)
+        assert g["delay"] == float(want["code_phase"]) and g["doppler"] == float(want["doppler_hz"]) and g["stamp"] == 4000
+        n_pos += g["event"] == 1
+        if (p + 1) in present:
+            assert g["event"] == 1
+    assert n_pos >= len([t for t in truth if t["prn"] <= 6])
+
+
+def _write_mc_input(path, mode, high_dyn, coalesce_us, codes, shifts, sigs, args):
+    n_ch, n_epochs, n_samples = sigs.shape
+    with open(path, "wb") as f:
+        code_len = codes.shape[1] // (2 if mode == 2 else 1)
+        f.write(struct.pack("<IIIIIIII", n_ch, shifts.shape[1], n_samples, code_len, n_epochs, mode, int(high_dyn), coalesce_us))
+        for c in range(n_ch):
+            f.write(codes[c].astype(np.float32).tobytes())
+            f.write(shifts[c].astype(np.float32).tobytes())
+            f.write(sigs[c].astype(np.complex64).tobytes())
+            f.write(args[c].astype(np.float32).tobytes())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,high_dyn,coalesce_us", [(0, False, 0), (0, True, 0), (1, True, 0), (2, False, 0), (0, False, 20000)])
+def test_correlator_objects_match_oracle(driver, oracle, tmp_path, mode, high_dyn, coalesce_us):
+    """One correlator object per channel, each called for 3 code periods from its own thread (as tracking blocks do)."""
+    rng = np.random.default_rng(11 + mode)
+    n_ch, n_ep, n, L, T = 5, 3, 4000, 1023, 3
+    chips = np.stack([synth.chips("gps_l1_ca", p + 1) for p in range(n_ch)]).astype(np.float32)
+    if mode == 2:
+        cc = (chips + 1j * np.roll(chips, 7, axis=1)).astype(np.complex64)
+        codes = cc.view(np.float32).reshape(n_ch, 2 * L)
+    else:
+        codes = chips
+    shifts = np.tile(np.array([-0.5, 0.0, 0.5], np.float32), (n_ch, 1)) + rng.uniform(-0.01, 0.01, (n_ch, 1)).astype(np.float32)
+    sigs = (rng.standard_normal((n_ch, n_ep, n)) + 1j * rng.standard_normal((n_ch, n_ep, n))).astype(np.complex64)
+    args = np.zeros((n_ch, n_ep, 6), dtype=np.float32)
+    args[..., 0] = rng.uniform(0, 6.28, (n_ch, n_ep))
+    args[..., 1] = rng.uniform(-0.01, 0.01, (n_ch, n_ep))
+    args[..., 2] = rng.uniform(-1e-9, 1e-9, (n_ch, n_ep)) if high_dyn else 0
+    args[..., 3] = rng.uniform(0, 1, (n_ch, n_ep))
+    args[..., 4] = 1.023e6 / 4e6 * (1 + rng.uniform(-1e-5, 1e-5, (n_ch, n_ep)))
+    args[..., 5] = rng.uniform(-1e-10, 1e-10, (n_ch, n_ep)) if high_dyn else 0
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_mc_input(inp, mode, high_dyn, coalesce_us, codes, shifts, sigs, args)
+    _run(driver, "mc", inp, outp)
+    raw = open(outp, "rb").read()
+    failures, batches, calls = struct.unpack_from("<IQQ", raw, 0)
+    got = np.frombuffer(raw, dtype=np.complex64, offset=20).reshape(n_ch, n_ep, T)
+    assert failures == 0 and calls == n_ch * n_ep
+    if coalesce_us:
+        assert batches < calls   # concurrent calls were combined into fewer engine launches
+    for c in range(n_ch):
+        for e in range(n_ep):
+            a = args[c, e]
+            if mode == 2:
+                want = oracle.mc_cplx(sigs[c, e], cc[c], shifts[c], a[0], a[1], a[3], a[4])
+            else:
+                want = oracle.mc_real(sigs[c, e], chips[c], shifts[c], a[0], a[1], a[2], a[3], a[4], a[5], high_dyn=high_dyn,
+                                      six_arg=(mode == 1))
+            scale = np.abs(want).max() + np.sqrt(n)
+            assert np.abs(got[c, e] - want).max() <= 1e-4 * scale
