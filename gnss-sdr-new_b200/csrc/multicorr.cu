@@ -18,6 +18,7 @@
 //     angle, not to `step`. Evaluated per thread in double at its first sample, then
 //     advanced by a stride phasor.
 #include "common.cuh"
+#include <type_traits>
 #include <cmath>
 #include <complex>
 #include <vector>
@@ -51,6 +52,20 @@ struct alignas(16) ChanParams
     uint32_t flags;
     uint32_t shifts_off;  // offset into the shifts / shift_samples arrays
 };
+
+// Device half of the per-channel constants: the true angle of the binary32-rounded per-sample phasor the reference
+// multiplies by (its rotator advances by exactly that angle, not by phase_step_rad), and the stride phasor.
+__global__ void prep_kernel(ChanParams* __restrict__ chans, uint32_t n_ch)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_ch) return;
+    const double theta = atan2((double)chans[i].wb_im, (double)chans[i].wb_re);
+    double sb, cb;
+    sincos(theta * (double)kThreads, &sb, &cb);
+    chans[i].theta = theta;
+    chans[i].wb_re = (float)cb;
+    chans[i].wb_im = (float)sb;
+}
 
 // chip-phase of sample n for one tap, exactly as volk_gnsssdr_32f_xn_resampler_32f_xn_generic evaluates it
 __device__ __forceinline__ int chip_index_plain(float step, float fn, float shift, float rem)
@@ -295,22 +310,50 @@ __global__ void __launch_bounds__(kThreads) multicorr_kernel(const ChanParams* _
 // Fast path (real codes, plain resampler, chip window fits shared memory) — the BASELINE config-5 case.
 // Blackwell packed-FP32 instructions do two taps per instruction: FADD2 for the two binary32 additions of the
 // reference's chip-phase expression, FADD2.RM against 1.5*2^23 for the floor (exact for |phase| < 2^22, and off
-// the quarter-rate conversion pipe), and FFMA2 for the complex accumulate with the chip held as a (c, c) pair.
+// the quarter-rate conversion pipe), and FFMA2 for the accumulate with taps paired as (re_t, re_t+1), (im_t, im_t+1).
+// The sample stream is the only HBM traffic: every thread streams its own samples through a private shared-memory
+// ring with 8-byte cp.async (12 loads in flight per thread, no registers held, no block barrier), and a channel is
+// cut into segments of a few thousand samples so that the chip window of a CTA is ~10 KB and several CTAs fit per SM.
 // Every lane of a packed op is an IEEE binary32 round-to-nearest (resp. round-down) operation, so the chip
 // indices stay bit-identical to volk_gnsssdr_32f_xn_resampler_32f_xn_generic.
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float lds_f32(uint32_t addr)
+{
+    float v;
+    asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+
+__device__ __forceinline__ float2 lds_f32x2(uint32_t addr)
+{
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+
+// asynchronous 8-byte global -> shared copy; src_bytes = 0 zero-fills the destination
+__device__ __forceinline__ void cp_async_8(uint32_t smem_addr, const void* gptr, uint32_t src_bytes)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_addr), "l"(gptr), "r"(src_bytes) : "memory");
+}
+
 constexpr float kFloorMagic = 12582912.0f;  // 1.5 * 2^23
-constexpr int kFloorMagicBits = 0x4B400000;
+constexpr uint32_t kFloorMagicBits = 0x4B400000u;
+constexpr int kWinGroup = 4;                // samples per cp.async commit group (per thread)
+constexpr int kWinRing = 4;                 // commit groups in the per-thread shared-memory ring
+constexpr uint32_t kWinRingBytes = kWinRing * kWinGroup * kThreads * 8u;
 
 template <int T>
-__global__ void __launch_bounds__(kThreads) multicorr_window_kernel(const ChanParams* __restrict__ chans, const float* __restrict__ shifts_all,
+__global__ void __launch_bounds__(kThreads, 4) multicorr_window_kernel(const ChanParams* __restrict__ chans, const float* __restrict__ shifts_all,
     float2* __restrict__ partials, uint32_t* __restrict__ tickets, float2* __restrict__ out, int n_taps_total, int tap0, uint32_t smem_elems)
 {
     constexpr int TP = (T + 1) / 2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2* s_code2 = reinterpret_cast<float2*>(smem_raw);
+    unsigned char* s_ring = smem_raw;
+    float* s_code = reinterpret_cast<float*>(smem_raw + kWinRingBytes);
     __shared__ float2 s_red[kThreads / 32][T];
     __shared__ int s_last;
+    __shared__ uint32_t s_bias;
 
     const ChanParams cp = chans[blockIdx.y];
     const uint32_t splits = gridDim.x;
@@ -318,6 +361,39 @@ __global__ void __launch_bounds__(kThreads) multicorr_window_kernel(const ChanPa
     const uint32_t n0 = min(cp.n, blockIdx.x * per), n1 = min(cp.n, n0 + per);
     const int L = (int)cp.code_len;
     const float* g_code = static_cast<const float*>(cp.code);
+
+    // Sample ring: each thread copies ITS OWN samples global -> shared with 8-byte cp.async (no registers, no block
+    // barrier: a thread only ever reads back the slots it filled), kWinGroup samples per commit group and kWinRing
+    // groups in the ring, i.e. (kWinRing-1)*kWinGroup loads in flight per thread at all times. Slots past the end of
+    // the segment are zero-filled (src-size 0) and their chip index is clamped into the window.
+    const float2* sig = cp.sig;
+    const uint32_t ring = (uint32_t)__cvta_generic_to_shared(s_ring) + threadIdx.x * 8u;
+    const uint32_t n_groups = (n1 - n0 + kWinGroup * kThreads - 1) / (kWinGroup * kThreads);  // uniform over the CTA
+    const uint32_t n_full = (n1 - n0) / (kWinGroup * kThreads);                               // groups with no padding
+    const uint32_t first = n0 + threadIdx.x;
+    const uint32_t last = n1 > 0 ? n1 - 1 : 0;
+    auto issue = [&](const uint32_t g) {
+        const uint32_t slot = ring + (g % kWinRing) * (kWinGroup * kThreads * 8u);
+        if (g < n_full)
+            {
+                const float2* src = sig + first + g * (kWinGroup * kThreads);
+#pragma unroll
+                for (int u = 0; u < kWinGroup; u++) cp_async_8(slot + u * (kThreads * 8u), src + u * kThreads, 8u);
+            }
+        else if (g < n_groups)
+            {
+#pragma unroll
+                for (int u = 0; u < kWinGroup; u++)
+                    {
+                        const uint32_t nn = first + (g * kWinGroup + u) * kThreads;
+                        cp_async_8(slot + u * (kThreads * 8u), sig + min(nn, last), nn < n1 ? 8u : 0u);
+                    }
+            }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    // start streaming before anything else: the window fill below overlaps the first DRAM round trip
+#pragma unroll
+    for (int g = 0; g < kWinRing - 1; g++) issue(g);
 
     float2 shift2[TP];
     float smin = 3.4e38f, smax = -3.4e38f;
@@ -338,66 +414,73 @@ __global__ void __launch_bounds__(kThreads) multicorr_window_kernel(const ChanPa
         const int adv = kThreads % L;
         for (int j = threadIdx.x; j < width; j += kThreads)
             {
-                const float c = g_code[src];
-                s_code2[j] = make_float2(c, c);
+                s_code[j] = g_code[src];
                 src += adv;
                 if (src >= L) src -= L;
             }
     }
+    if (threadIdx.x == 0) s_bias = (uint32_t)__cvta_generic_to_shared(s_code) - 4u * (kFloorMagicBits + (uint32_t)lo);
     __syncthreads();
 
-    float2 acc[2 * TP];
+    // accumulators of a tap pair: (re_t, re_t+1) and (im_t, im_t+1), so that one FFMA2 serves two taps
+    float2 acc_re[TP], acc_im[TP];
 #pragma unroll
-    for (int t = 0; t < 2 * TP; t++) acc[t] = make_float2(0.f, 0.f);
+    for (int q = 0; q < TP; q++) acc_re[q] = acc_im[q] = make_float2(0.f, 0.f);
 
-    uint32_t n = n0 + threadIdx.x;
-    if (n < n1)
-        {
-            double ang = cp.theta * (double)n;
-            ang -= 6.283185307179586476925286766559 * rint(ang * 0.15915494309189533576888376337251);
-            float sr, cr;
-            sincosf((float)ang, &sr, &cr);
-            float2 ph = make_float2(cp.p0_re * cr - cp.p0_im * sr, cp.p0_re * sr + cp.p0_im * cr);
-            const float2 wb = make_float2(cp.wb_re, cp.wb_im);
-            const float step = cp.code_step;
-            const float2 nrem2 = make_float2(-cp.rem_code, -cp.rem_code);
-            const float2 magic2 = make_float2(kFloorMagic, kFloorMagic);
-            const int koff = kFloorMagicBits + lo;
+    {
+        double ang = cp.theta * (double)first;
+        ang -= 6.283185307179586476925286766559 * rint(ang * 0.15915494309189533576888376337251);
+        float sr, cr;
+        sincosf((float)ang, &sr, &cr);
+        float2 ph = make_float2(cp.p0_re * cr - cp.p0_im * sr, cp.p0_re * sr + cp.p0_im * cr);
+        const float2 wb = make_float2(cp.wb_re, cp.wb_im);
+        const float step = cp.code_step;
+        const float2 nrem2 = make_float2(-cp.rem_code, -cp.rem_code);
+        const float2 magic2 = make_float2(kFloorMagic, kFloorMagic);
+        // shared-memory address of chip k = base + 4 * (bits(k + magic) - (magicbits + lo)), modulo 2^32: one LEA per chip
+        // (read back from shared memory so that ptxas cannot split the constant part off again)
+        const uint32_t addr_bias = *reinterpret_cast<volatile uint32_t*>(&s_bias);
 
-            auto one_sample = [&](const float2 x, const uint32_t nn, const float2 p) {
-                const float2 z = make_float2(x.x * p.x - x.y * p.y, x.x * p.y + x.y * p.x);
-                const float a = __fmul_rn(step, (float)nn);
-                const float2 a2 = make_float2(a, a);
+        auto consume = [&](auto tail_tag, const uint32_t g) {
+            constexpr bool TAIL = decltype(tail_tag)::value;
+            issue(g + kWinRing - 1);
+            asm volatile("cp.async.wait_group %0;" ::"n"(kWinRing - 1) : "memory");
+            const uint32_t slot = ring + (g % kWinRing) * (kWinGroup * kThreads * 8u);
 #pragma unroll
-                for (int q = 0; q < TP; q++)
-                    {
-                        // floor(fl(fl(a + shift) - rem)) for two taps at once
-                        const float2 f = __fadd2_rd(__fadd2_rn(__fadd2_rn(a2, shift2[q]), nrem2), magic2);
-                        const float2 c0 = s_code2[__float_as_int(f.x) - koff];
-                        const float2 c1 = s_code2[__float_as_int(f.y) - koff];
-                        acc[2 * q] = __ffma2_rn(c0, z, acc[2 * q]);
-                        acc[2 * q + 1] = __ffma2_rn(c1, z, acc[2 * q + 1]);
-                    }
-            };
-
-            // two samples in flight per thread
-            for (; n + kThreads < n1; n += 2 * kThreads)
+            for (int u = 0; u < kWinGroup; u++)
                 {
-                    const float2 x0 = __ldg(cp.sig + n);
-                    const float2 x1 = __ldg(cp.sig + n + kThreads);
-                    const float2 ph1 = make_float2(ph.x * wb.x - ph.y * wb.y, ph.x * wb.y + ph.y * wb.x);
-                    one_sample(x0, n, ph);
-                    one_sample(x1, n + kThreads, ph1);
-                    ph = make_float2(ph1.x * wb.x - ph1.y * wb.y, ph1.x * wb.y + ph1.y * wb.x);
+                    const float2 x = lds_f32x2(slot + u * (kThreads * 8u));
+                    uint32_t nn = first + (g * kWinGroup + u) * kThreads;
+                    if (TAIL) nn = min(nn, last);
+                    const float zr = x.x * ph.x - x.y * ph.y;
+                    const float zi = x.x * ph.y + x.y * ph.x;
+                    const float2 zr2 = make_float2(zr, zr), zi2 = make_float2(zi, zi);
+                    const float a = __fmul_rn(step, (float)nn);
+                    const float2 a2 = make_float2(a, a);
+#pragma unroll
+                    for (int q = 0; q < TP; q++)
+                        {
+                            // floor(fl(fl(a + shift) - rem)) for two taps at once
+                            const float2 f = __fadd2_rd(__fadd2_rn(__fadd2_rn(a2, shift2[q]), nrem2), magic2);
+                            float2 c;
+                            c.x = lds_f32(__float_as_uint(f.x) * 4u + addr_bias);
+                            c.y = (2 * q + 1 < T) ? lds_f32(__float_as_uint(f.y) * 4u + addr_bias) : 0.f;
+                            acc_re[q] = __ffma2_rn(c, zr2, acc_re[q]);
+                            acc_im[q] = __ffma2_rn(c, zi2, acc_im[q]);
+                        }
+                    ph = make_float2(ph.x * wb.x - ph.y * wb.y, ph.x * wb.y + ph.y * wb.x);
                 }
-            if (n < n1) one_sample(__ldg(cp.sig + n), n, ph);
-        }
+        };
+        uint32_t g = 0;
+        for (; g < n_full; g++) consume(std::false_type{}, g);
+        for (; g < n_groups; g++) consume(std::true_type{}, g);
+    }
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int t = 0; t < T; t++)
         {
-            float2 v = acc[t];
+            float2 v = (t & 1) ? make_float2(acc_re[t / 2].y, acc_im[t / 2].y) : make_float2(acc_re[t / 2].x, acc_im[t / 2].x);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1)
                 {
@@ -452,7 +535,15 @@ void launch_window(int T, dim3 grid, size_t smem, cudaStream_t st, const ChanPar
 {
 #define B200_MCW_CASE(TT)                                                                                                                  \
     case TT:                                                                                                                               \
-        cudaFuncSetAttribute(multicorr_window_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCapBytes);                  \
+        {                                                                                                                                  \
+            static bool configured = false;                                                                                                \
+            if (!configured)                                                                                                               \
+                {                                                                                                                          \
+                    cudaFuncSetAttribute(multicorr_window_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCapBytes);    \
+                    cudaFuncSetAttribute(multicorr_window_kernel<TT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);                \
+                    configured = true;                                                                                                     \
+                }                                                                                                                          \
+        }                                                                                                                                  \
         multicorr_window_kernel<TT><<<grid, kThreads, smem, st>>>(chans, shifts, partials, tickets, out, n_taps_total, tap0, smem_elems);   \
         break;
     switch (T)
@@ -585,8 +676,27 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
             const uint32_t max_splits = (uint32_t)std::max<uint64_t>(1, max_n / 2048);
             splits = std::max(1u, std::min(splits, max_splits));
         }
+    if (!hd_res && !h->code_complex[ch[0] < h->max_channels ? ch[0] : 0] && max_n > 16ull * kWinGroup * kThreads)
+        {
+            // window kernel: segments of 8..16 sample groups per thread, chosen for the least zero padding of the last group
+            const uint64_t quantum = (uint64_t)kWinGroup * kThreads;
+            uint32_t best = 0;
+            double best_waste = 1e30;
+            for (uint64_t s = (max_n + 16 * quantum - 1) / (16 * quantum); s <= (max_n + 8 * quantum - 1) / (8 * quantum); s++)
+                {
+                    const uint64_t per = (max_n + s - 1) / s;
+                    const double waste = (double)((per + quantum - 1) / quantum * quantum) / (double)per;
+                    if (waste < best_waste - 1e-9)
+                        {
+                            best_waste = waste;
+                            best = (uint32_t)s;
+                        }
+                }
+            splits = std::max(splits, best);
+        }
     uint64_t max_window = 1;  // widest per-CTA chip window over the batch
-    bool cplx = false;
+    bool cplx = false, small_phase = true;
+    if (!hd_res) std::memset(hss, 0, sizeof(uint32_t) * (size_t)n_ch * n_taps);
     for (uint32_t i = 0; i < n_ch; i++)
         {
             const uint32_t c = ch[i];
@@ -613,14 +723,20 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
             p.code_step = a.code_step_chips;
             p.code_rate = a.code_rate_chips;
             // phase_offset_as_complex = (cos(rem), -sin(rem)) in binary32 (:114-115)
-            p.p0_re = std::cos(a.rem_carr_phase_rad);
-            p.p0_im = -std::sin(a.rem_carr_phase_rad);
+            float s0, c0;
+            sincosf(a.rem_carr_phase_rad, &s0, &c0);
+            p.p0_re = c0;
+            p.p0_im = -s0;
             // the reference's per-sample phasor std::exp(lv_32fc_t(0, -step)) rounded to binary32; its true angle
-            const std::complex<float> inc = std::exp(std::complex<float>(0.0f, -a.carr_step_rad));
-            p.theta = std::atan2((double)inc.imag(), (double)inc.real());
-            const double wb = p.theta * (double)kThreads;
-            p.wb_re = (float)std::cos(wb);
-            p.wb_im = (float)std::sin(wb);
+            // (theta = atan2 of these, and the stride phasor exp(j*kThreads*theta), are derived on the device by
+            // prep_kernel: wb_re/wb_im carry the rounded phasor until then)
+            // std::exp(complex<float>(0, y)) is (cosf y, sinf y) exactly (glibc cexpf: sincosf times exp(0) = 1); calling
+            // sincosf directly gives the same bits at a quarter of the cost
+            float inc_re, inc_im;
+            sincosf(-a.carr_step_rad, &inc_im, &inc_re);
+            p.theta = 0.0;
+            p.wb_re = inc_re;
+            p.wb_im = inc_im;
             p.rate_arg = 0.0f;
             if (hd_rot)
                 {
@@ -630,21 +746,29 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
                 }
             p.flags = (hd_res ? F_HIGH_DYN_RESAMPLER : 0u) | (hd_rot ? F_HIGH_DYN_ROTATOR : 0u) | (cplx ? F_COMPLEX_CODE : 0u);
             p.shifts_off = i * n_taps;
-            // …high_dynamics_resampler…:84-87: cumulative integer sample shifts of taps 1.. relative to tap 0
-            uint32_t acc = 0;
-            hss[(size_t)i * n_taps] = 0;
+            const float* hsi = hs + (size_t)i * n_taps;
+            if (hd_res)
+                {
+                    // …high_dynamics_resampler…:84-87: cumulative integer sample shifts of taps 1.. relative to tap 0
+                    uint32_t acc = 0;
+                    hss[(size_t)i * n_taps] = 0;
+                    for (uint32_t t = 1; t < n_taps; t++)
+                        {
+                            const float d = (hsi[t] - hsi[t - 1]) / a.code_step_chips;
+                            acc += (uint32_t)(int)std::round((double)d);
+                            hss[(size_t)i * n_taps + t] = acc;
+                        }
+                }
+            float smin = hsi[0], smax = hsi[0];
             for (uint32_t t = 1; t < n_taps; t++)
                 {
-                    const float d = (hs[(size_t)i * n_taps + t] - hs[(size_t)i * n_taps + t - 1]) / a.code_step_chips;
-                    acc += (uint32_t)(int)std::round((double)d);
-                    hss[(size_t)i * n_taps + t] = acc;
+                    smin = hsi[t] < smin ? hsi[t] : smin;
+                    smax = hsi[t] > smax ? hsi[t] : smax;
                 }
-            float smin = hs[(size_t)i * n_taps], smax = smin;
-            for (uint32_t t = 1; t < n_taps; t++)
-                {
-                    smin = std::fmin(smin, hs[(size_t)i * n_taps + t]);
-                    smax = std::fmax(smax, hs[(size_t)i * n_taps + t]);
-                }
+            // |chip phase| stays below 2^22 (the packed floor of the window kernel is exact there)
+            const double lim = std::max(std::fabs((double)smin), std::fabs((double)smax)) +
+                               std::fabs((double)a.code_step_chips) * (double)a.n_samples + std::fabs((double)a.rem_code_phase_chips);
+            if (!(lim < 4.0e6)) small_phase = false;
             const uint32_t per = (a.n_samples + splits - 1) / splits;
             const double span = std::fabs((double)a.code_step_chips) * (double)per + ((double)smax - (double)smin) + 16.0;
             max_window = std::max<uint64_t>(max_window, (uint64_t)span);
@@ -653,15 +777,7 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
     const uint32_t elem = cplx ? 8u : 4u;
     const uint32_t cap = kSmemCapBytes / elem;
     // fast (packed, window-only) kernel: real code, plain resampler, window of (c,c) pairs fits, |chip phase| < 2^22
-    bool fast = !cplx && !hd_res && max_window <= kSmemCapBytes / 8;
-    for (uint32_t i = 0; i < n_ch && fast; i++)
-        {
-            const gnss_b200_mc_args& a = args[i];
-            double lim = 0.0;
-            for (uint32_t t = 0; t < n_taps; t++) lim = std::max(lim, std::fabs((double)hs[(size_t)i * n_taps + t]));
-            lim += std::fabs((double)a.code_step_chips) * (double)a.n_samples + std::fabs((double)a.rem_code_phase_chips);
-            if (!(lim < 4.0e6)) fast = false;
-        }
+    const bool fast = !cplx && !hd_res && small_phase && max_window <= (kSmemCapBytes - kWinRingBytes) / 4;
     if (out_fast) *out_fast = fast;
     if (fast)
         {
@@ -690,12 +806,17 @@ int run_batch(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, uint32_t smem_ele
     const uint32_t* d_ss = reinterpret_cast<const uint32_t*>(d_shifts + (size_t)n_ch * n_taps);
     const dim3 grid(splits, n_ch);
     const size_t smem = (size_t)smem_elems * (cplx ? 8 : 4);
+    h->prof.begin(1, h->stream);
+    prep_kernel<<<(n_ch + 127) / 128, 128, 0, h->stream>>>(h->d_params.as<ChanParams>(), n_ch);
+    h->prof.end(h->stream);
+    h->launches++;
+    B200_CUDA(cudaGetLastError());
     for (uint32_t tap0 = 0; tap0 < n_taps; tap0 += kMaxTapsPerPass)
         {
             const int T = (int)std::min<uint32_t>(kMaxTapsPerPass, n_taps - tap0);
             h->prof.begin(0, h->stream);
             if (fast)
-                launch_window(T, grid, (size_t)smem_elems * 8, h->stream, d_cp, d_shifts, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
+                launch_window(T, grid, (size_t)smem_elems * 4 + kWinRingBytes, h->stream, d_cp, d_shifts, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
                     h->d_out.as<float2>(), (int)n_taps, (int)tap0, smem_elems);
             else if (cplx)
                 launch_taps<float2>(T, grid, smem, h->stream, d_cp, d_shifts, d_ss, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
