@@ -309,8 +309,9 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 const uint32_t pitch = (pl.ra_lo % 2 == 0) ? pl.ra_lo + 1 : pl.ra_lo;
                 const size_t smem_lo = ((size_t)fa.nb * pitch * pl.rb_lo + fa.M_lo) * sizeof(float2);
                 const size_t smem_hi = ((size_t)fa.M_hi * fa.C + fa.M_hi) * sizeof(float2);
-                const dim3 block_hi(fa.C, std::max(1u, (uint32_t)kFastThreads / fa.C));
-                const uint32_t threads_lo = std::min<uint32_t>(kFastThreads, (fa.nb * pl.rb_lo + 31) / 32 * 32);
+                const uint32_t rows_hi = std::max(1u, (uint32_t)kFastThreads / fa.C);
+                const dim3 block_hi(fa.C, rows_hi);
+                const uint32_t threads_lo = std::max<uint32_t>(64, std::min<uint32_t>(kFastThreads, (fa.nb * pl.rb_lo + 31) / 32 * 32));  // >= 64: twiddle fill
                 for (uint32_t y0 = 0; y0 < rows; y0 += chunk)
                     {
                         const uint32_t cnt = std::min(chunk, rows - y0);

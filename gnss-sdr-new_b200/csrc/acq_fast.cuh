@@ -76,33 +76,61 @@ __global__ void __launch_bounds__(kFastThreads) inv_lower_kernel(const FastArgs 
     const uint32_t blk0 = blockIdx.y * a.nb;
     const uint32_t tw_scale = a.N / M;  // W_M = W_N^(N/M)
 
-    for (uint32_t i = threadIdx.x; i < (uint32_t)M; i += blockDim.x)
-        {
-            const uint32_t ub = i / RA, aa = i - ub * RA;
-            const float2 w = __ldg(a.W + (size_t)aa * ub * tw_scale);
-            s_tw[i] = make_float2(w.x, -w.y);
-        }
-
-    __syncthreads();
-
     // ---- pass A (stride-1 dim, no twiddle): one thread per (block, ub) pencil ----
+    // Order of the first round: twiddle-table loads and the pencil's own global loads are issued together, the table
+    // is stored while the pencil data is still in flight, and the barrier sits between the butterfly (which needs no
+    // twiddles) and the twiddle multiply — so the table costs no extra L2 round trip.
     const uint32_t n_pen_a = a.nb * RB;
     const uint32_t seg = a.N / RA;
-    for (uint32_t p = threadIdx.x; p < n_pen_a; p += blockDim.x)
+    constexpr int kTwPerThread = (M + 63) / 64;  // enough for blockDim.x >= 64
+    float2 wreg[kTwPerThread];
+#pragma unroll
+    for (int j = 0; j < kTwPerThread; j++)
         {
-            const uint32_t bl = p / RB, ub = p - bl * RB;
-            const uint32_t src = (blk0 + bl) * RB + ub;  // + ua * seg  (fast layout: unit stride across threads)
-            float2 x[RA], c[RA];
+            const uint32_t i = threadIdx.x + j * blockDim.x;
+            if (i < (uint32_t)M)
+                {
+                    const uint32_t ub = i / RA, aa = i - ub * RA;
+                    wreg[j] = __ldg(a.W + (size_t)aa * ub * tw_scale);
+                }
+        }
+    auto load_product = [&](float2(&x)[RA], uint32_t p) {
+        const uint32_t bl = p / RB, ub = p - bl * RB;
+        const uint32_t src = (blk0 + bl) * RB + ub;  // + ua * seg  (fast layout: unit stride across threads)
+        float2 c[RA];
 #pragma unroll
-            for (int u = 0; u < RA; u++) x[u] = __ldg(X + src + (size_t)u * seg);
+        for (int u = 0; u < RA; u++) x[u] = __ldg(X + src + (size_t)u * seg);
 #pragma unroll
-            for (int u = 0; u < RA; u++) c[u] = __ldg(Cs + src + (size_t)u * seg);
+        for (int u = 0; u < RA; u++) c[u] = __ldg(Cs + src + (size_t)u * seg);
 #pragma unroll
-            for (int u = 0; u < RA; u++) x[u] = fft::cmul(x[u], c[u]);
+        for (int u = 0; u < RA; u++) x[u] = fft::cmul(x[u], c[u]);
+    };
+    auto twiddle_store = [&](float2(&x)[RA], uint32_t p) {
+        const uint32_t bl = p / RB, ub = p - bl * RB;
+        float2* dst = s + (size_t)bl * MP + (size_t)ub * P;
+#pragma unroll
+        for (int q = 0; q < RA; q++) dst[q] = fft::cmul(x[q], s_tw[ub * RA + q]);
+    };
+    {
+        float2 x[RA];
+        const bool have = threadIdx.x < n_pen_a;
+        if (have) load_product(x, threadIdx.x);
+#pragma unroll
+        for (int j = 0; j < kTwPerThread; j++)
+            {
+                const uint32_t i = threadIdx.x + j * blockDim.x;
+                if (i < (uint32_t)M) s_tw[i] = make_float2(wreg[j].x, -wreg[j].y);
+            }
+        if (have) fft::Dft<RA, true>::run(x);
+        __syncthreads();
+        if (have) twiddle_store(x, threadIdx.x);
+    }
+    for (uint32_t p = threadIdx.x + blockDim.x; p < n_pen_a; p += blockDim.x)
+        {
+            float2 x[RA];
+            load_product(x, p);
             fft::Dft<RA, true>::run(x);
-            float2* dst = s + (size_t)bl * MP + (size_t)ub * P;
-#pragma unroll
-            for (int q = 0; q < RA; q++) dst[q] = fft::cmul(x[q], s_tw[ub * RA + q]);
+            twiddle_store(x, p);
         }
     __syncthreads();
 
@@ -156,25 +184,49 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     const uint32_t C = a.C, c = threadIdx.x, c0 = blockIdx.y * C;
     const uint32_t tid = threadIdx.y * blockDim.x + threadIdx.x, nthreads = blockDim.x * blockDim.y;
     const uint32_t tw_scale = a.N / M;
-    for (uint32_t i = tid; i < (uint32_t)M; i += nthreads)
-        {
-            const uint32_t ub = i / RA, aa = i - ub * RA;
-            const float2 w = __ldg(a.W + (size_t)aa * ub * tw_scale);
-            s_tw[i] = make_float2(w.x, -w.y);
-        }
     const float2* in = a.scratch + (size_t)(y - a.y0) * N + c0 + c;
 
-    __syncthreads();
-
-    // ---- pass A: pencils (column c, ub) ----
-    for (uint32_t ub = threadIdx.y; ub < (uint32_t)RB; ub += blockDim.y)
+    // ---- pass A: pencils (column c, ub); same ordering trick as in the lower kernel ----
+    constexpr int kTwPerThread = (M + 63) / 64;
+    float2 wreg[kTwPerThread];
+#pragma unroll
+    for (int j = 0; j < kTwPerThread; j++)
+        {
+            const uint32_t i = tid + j * nthreads;
+            if (i < (uint32_t)M)
+                {
+                    const uint32_t ub = i / RA, aa = i - ub * RA;
+                    wreg[j] = __ldg(a.W + (size_t)aa * ub * tw_scale);
+                }
+        }
+    auto load_pencil = [&](float2(&v)[RA], uint32_t ub) {
+#pragma unroll
+        for (int u = 0; u < RA; u++) v[u] = __ldcg(in + (size_t)(u + RA * ub) * a.M_lo);
+    };
+    auto twiddle_store = [&](float2(&v)[RA], uint32_t ub) {
+#pragma unroll
+        for (int q = 0; q < RA; q++) s[(size_t)(q + RA * ub) * C + c] = fft::cmul(v[q], s_tw[ub * RA + q]);
+    };
+    {
+        float2 v[RA];
+        const bool have = threadIdx.y < (uint32_t)RB;
+        if (have) load_pencil(v, threadIdx.y);
+#pragma unroll
+        for (int j = 0; j < kTwPerThread; j++)
+            {
+                const uint32_t i = tid + j * nthreads;
+                if (i < (uint32_t)M) s_tw[i] = make_float2(wreg[j].x, -wreg[j].y);
+            }
+        if (have) fft::Dft<RA, true>::run(v);
+        __syncthreads();
+        if (have) twiddle_store(v, threadIdx.y);
+    }
+    for (uint32_t ub = threadIdx.y + blockDim.y; ub < (uint32_t)RB; ub += blockDim.y)
         {
             float2 v[RA];
-#pragma unroll
-            for (int u = 0; u < RA; u++) v[u] = __ldcg(in + (size_t)(u + RA * ub) * a.M_lo);
+            load_pencil(v, ub);
             fft::Dft<RA, true>::run(v);
-#pragma unroll
-            for (int q = 0; q < RA; q++) s[(size_t)(q + RA * ub) * C + c] = fft::cmul(v[q], s_tw[ub * RA + q]);
+            twiddle_store(v, ub);
         }
     __syncthreads();
 

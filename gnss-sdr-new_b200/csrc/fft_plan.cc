@@ -2,6 +2,8 @@
 #include "fft_plan.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 
 namespace b200
 {
@@ -109,6 +111,19 @@ bool find_fast_plan(uint32_t N, FftPlan* plan)
     static const uint32_t RB[] = {2, 4, 5, 8, 10, 16, 20};
     double best = 1e30;
     bool found = false;
+    if (const char* e = std::getenv("B200_FFT_PLAN"))  // tuning aid: "ra_lo,rb_lo,ra_hi,rb_hi"
+        {
+            unsigned a1, b1, a2, b2;
+            if (std::sscanf(e, "%u,%u,%u,%u", &a1, &b1, &a2, &b2) == 4 && (uint64_t)a1 * b1 * a2 * b2 == N && fast_ra_supported(a1) &&
+                fast_rb_supported(b1) && fast_ra_supported(a2) && fast_rb_supported(b2))
+                {
+                    plan->ra_lo = a1;
+                    plan->rb_lo = b1;
+                    plan->ra_hi = a2;
+                    plan->rb_hi = b2;
+                    return true;
+                }
+        }
     for (uint32_t a1 : RA)
         for (uint32_t b1 : RB)
             for (uint32_t a2 : RA)

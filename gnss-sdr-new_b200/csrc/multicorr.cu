@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include <type_traits>
 #include <cmath>
+#include <cstdlib>
 #include <complex>
 #include <vector>
 
@@ -332,6 +333,11 @@ __device__ __forceinline__ float2 lds_f32x2(uint32_t addr)
 }
 
 // asynchronous 8-byte global -> shared copy; src_bytes = 0 zero-fills the destination
+__device__ __forceinline__ void cp_async_4(uint32_t smem_addr, const void* gptr)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+
 __device__ __forceinline__ void cp_async_8(uint32_t smem_addr, const void* gptr, uint32_t src_bytes)
 {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_addr), "l"(gptr), "r"(src_bytes) : "memory");
@@ -410,17 +416,19 @@ __global__ void __launch_bounds__(kThreads, 4) multicorr_window_kernel(const Cha
     const int lo = (int)floor(fmin(a0, a1) + (double)smin - (double)cp.rem_code) - 2;
     const int width = min((int)smem_elems, (int)floor(fmax(a0, a1) + (double)smax - (double)cp.rem_code) + 2 - lo + 1);
     {
+        // the pre-wrapped chip window, also by cp.async: every element of the fill is in flight at once
         int src = wrap_chip(lo + (int)threadIdx.x, L);
         const int adv = kThreads % L;
+        const uint32_t s_code_addr = (uint32_t)__cvta_generic_to_shared(s_code);
         for (int j = threadIdx.x; j < width; j += kThreads)
             {
-                s_code[j] = g_code[src];
+                cp_async_4(s_code_addr + 4u * (uint32_t)j, g_code + src);
                 src += adv;
                 if (src >= L) src -= L;
             }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     }
     if (threadIdx.x == 0) s_bias = (uint32_t)__cvta_generic_to_shared(s_code) - 4u * (kFloorMagicBits + (uint32_t)lo);
-    __syncthreads();
 
     // accumulators of a tap pair: (re_t, re_t+1) and (im_t, im_t+1), so that one FFMA2 serves two taps
     float2 acc_re[TP], acc_im[TP];
@@ -439,6 +447,8 @@ __global__ void __launch_bounds__(kThreads, 4) multicorr_window_kernel(const Cha
         const float2 magic2 = make_float2(kFloorMagic, kFloorMagic);
         // shared-memory address of chip k = base + 4 * (bits(k + magic) - (magicbits + lo)), modulo 2^32: one LEA per chip
         // (read back from shared memory so that ptxas cannot split the constant part off again)
+        asm volatile("cp.async.wait_group 0;" ::: "memory");  // window + the first ring groups have landed
+        __syncthreads();
         const uint32_t addr_bias = *reinterpret_cast<volatile uint32_t*>(&s_bias);
 
         auto consume = [&](auto tail_tag, const uint32_t g) {
@@ -506,7 +516,7 @@ __global__ void __launch_bounds__(kThreads, 4) multicorr_window_kernel(const Cha
                 partials[((size_t)blockIdx.y * splits + blockIdx.x) * n_taps_total + tap0 + threadIdx.x] = v;
         }
     if (splits == 1) return;
-    __threadfence();
+    if (threadIdx.x < live) __threadfence();
     __syncthreads();
     if (threadIdx.x == 0)
         {
@@ -666,7 +676,12 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
     const bool hd_res = flags & GNSS_B200_MC_HIGH_DYN;
     const bool hd_rot = hd_res && !(flags & GNSS_B200_MC_SIX_ARG);
     uint64_t max_len = 1, max_n = 1;
-    for (uint32_t i = 0; i < n_ch; i++) max_n = std::max<uint64_t>(max_n, args[i].n_samples);
+    double max_span = 0.0;  // chips swept by one channel over its whole integration
+    for (uint32_t i = 0; i < n_ch; i++)
+        {
+            max_n = std::max<uint64_t>(max_n, args[i].n_samples);
+            max_span = std::max(max_span, std::fabs((double)args[i].code_step_chips) * (double)args[i].n_samples);
+        }
     // split each channel over several CTAs when the batch alone cannot fill the machine
     uint32_t splits = 1;
     const uint32_t target_ctas = kNumSMs * 4;
@@ -676,23 +691,13 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
             const uint32_t max_splits = (uint32_t)std::max<uint64_t>(1, max_n / 2048);
             splits = std::max(1u, std::min(splits, max_splits));
         }
-    if (!hd_res && !h->code_complex[ch[0] < h->max_channels ? ch[0] : 0] && max_n > 16ull * kWinGroup * kThreads)
+    if (!hd_res && !h->code_complex[ch[0] < h->max_channels ? ch[0] : 0])
         {
-            // window kernel: segments of 8..16 sample groups per thread, chosen for the least zero padding of the last group
-            const uint64_t quantum = (uint64_t)kWinGroup * kThreads;
-            uint32_t best = 0;
-            double best_waste = 1e30;
-            for (uint64_t s = (max_n + 16 * quantum - 1) / (16 * quantum); s <= (max_n + 8 * quantum - 1) / (8 * quantum); s++)
-                {
-                    const uint64_t per = (max_n + s - 1) / s;
-                    const double waste = (double)((per + quantum - 1) / quantum * quantum) / (double)per;
-                    if (waste < best_waste - 1e-9)
-                        {
-                            best_waste = waste;
-                            best = (uint32_t)s;
-                        }
-                }
-            splits = std::max(splits, best);
+            // window kernel: long segments amortise the per-CTA prologue/epilogue (one segment per channel when the
+            // batch fills the machine), but the chip window of a segment must leave room for 3 CTAs per SM
+            const double window_budget = 10800.0;  // floats: 42 KB next to the 32 KB sample ring
+            while (max_span / splits + 64.0 > window_budget && (uint64_t)splits * 2048 < max_n) splits++;
+            if (const char* e = std::getenv("B200_MC_SPLITS")) splits = (uint32_t)std::max(1, std::atoi(e));  // tuning aid
         }
     uint64_t max_window = 1;  // widest per-CTA chip window over the batch
     bool cplx = false, small_phase = true;
