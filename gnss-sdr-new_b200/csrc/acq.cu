@@ -13,7 +13,7 @@ using namespace b200;
 namespace
 {
 constexpr uint32_t kMaxSingleStagePoints = 24576;  // 192 KiB of complex64 in one CTA's shared memory
-constexpr size_t kScratchBudgetBytes = 80ull << 20;  // two-stage intermediate kept L2-resident by chunking rows
+constexpr size_t kScratchBudgetBytes = 2048ull << 20;  // cap of the two-stage intermediate (rows are chunked beyond it)
 constexpr uint32_t kMaxCachedGroups = 64;
 enum
 {
@@ -39,6 +39,8 @@ struct gnss_b200_acq
     uint32_t code_len = 0, code_off = 0, mag_offset = 0;
     FftPlan plan;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;  // last inverse stage of chunk i overlaps the first stage of chunk i+1
+    cudaEvent_t ev_lo[2] = {nullptr, nullptr}, ev_up[2] = {nullptr, nullptr}, ev_fork = nullptr;
     uint64_t launches = 0;
 
     DevBuf d_W, d_cbuf, d_xbuf, d_xtmp, d_samples, d_codes_td, d_scratch;
@@ -117,7 +119,8 @@ int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
             return launch_stage<LOAD_CODE, STORE_CONJ, false>(h, a, n, CAT_CODE);
         }
     // two stages through the scratch buffer, in chunks that fit it
-    const uint32_t chunk = (uint32_t)std::max<size_t>(1, h->d_scratch.cap / ((size_t)h->N * 8));
+    const uint32_t chunk = (uint32_t)std::min<size_t>(n, std::max<size_t>(1, kScratchBudgetBytes / ((size_t)h->N * 8)));
+    B200_CUDA(h->d_scratch.reserve((size_t)chunk * h->N * 8));
     for (uint32_t y0 = 0; y0 < n; y0 += chunk)
         {
             const uint32_t cnt = std::min(chunk, n - y0);
@@ -210,7 +213,13 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
             if (rc) return rc;
             m.group_piece_base.push_back(ord * h->nD_local);
         }
-    for (uint32_t i = 0; i < n_slots; i++) m.dwell_after.push_back(++h->dwell[slots[i]]);  // :638
+    for (uint32_t i = 0; i < n_slots; i++)
+        {
+            // :638. Without a persistent grid nothing is accumulated, so every dwell is a first dwell (max_dwells = 1
+            // in the reference resets the counter after each pass, :869-880).
+            if (!h->cfg.keep_grid) h->dwell[slots[i]] = 0;
+            m.dwell_after.push_back(++h->dwell[slots[i]]);
+        }
     const uint32_t n_groups = (uint32_t)call_keys.size();
 
     const size_t meta_words = (size_t)n_slots * 4 + n_groups;
@@ -277,7 +286,12 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 a.partials = partials;
                 return launch_stage<LOAD_PRODUCT, STORE_MAG, true>(h, a, rows, CAT_INV_LAST);
             }
-        const uint32_t chunk = (uint32_t)std::max<size_t>(1, h->d_scratch.cap / ((size_t)h->N * 8));
+        // inter-stage scratch: all rows of the call in one launch pair when they fit the budget (measured on B200: the
+        // HBM round trip of the intermediate costs less than the launch boundaries and tail waves of many small chunks)
+        size_t budget = kScratchBudgetBytes;
+        if (const char* e = std::getenv("B200_ACQ_SCRATCH_MB")) budget = (size_t)std::max(1, std::atoi(e)) << 20;  // tuning aid
+        const uint32_t chunk = (uint32_t)std::min<size_t>(rows, std::max<size_t>(1, budget / ((size_t)h->N * 8)));
+        B200_CUDA(h->d_scratch.reserve((size_t)chunk * h->N * 8));
         if (h->plan.fast)
             {
                 const FftPlan& pl = h->plan;
@@ -312,21 +326,42 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 const uint32_t rows_hi = std::max(1u, (uint32_t)kFastThreads / fa.C);
                 const dim3 block_hi(fa.C, rows_hi);
                 const uint32_t threads_lo = std::max<uint32_t>(64, std::min<uint32_t>(kFastThreads, (fa.nb * pl.rb_lo + 31) / 32 * 32));  // >= 64: twiddle fill
-                for (uint32_t y0 = 0; y0 < rows; y0 += chunk)
+                // Optional (B200_ACQ_OVERLAP=1): two half-size scratch buffers and two streams, the last stage of chunk i
+                // running while the first stage of chunk i+1 fills the other buffer.
+                static const bool overlap = [] {
+                    const char* e = std::getenv("B200_ACQ_OVERLAP");  // tuning aid; measured slower on B200, default off
+                    return e && e[0] == '1';
+                }();
+                const cudaStream_t s2 = overlap ? h->stream2 : h->stream;
+                const uint32_t half = overlap ? std::max(1u, chunk / 2) : chunk;
+                float2* const sbase = h->d_scratch.as<float2>();
+                B200_CUDA(cudaEventRecord(h->ev_fork, h->stream));
+                if (overlap) B200_CUDA(cudaStreamWaitEvent(s2, h->ev_fork, 0));
+                uint32_t it = 0;
+                for (uint32_t y0 = 0; y0 < rows; y0 += half, it++)
                     {
-                        const uint32_t cnt = std::min(chunk, rows - y0);
+                        const uint32_t cnt = std::min(half, rows - y0);
+                        const uint32_t buf = overlap ? (it & 1) : 0;
                         fa.y0 = y0;
+                        fa.scratch = sbase + (size_t)buf * half * h->N;
+                        if (overlap && it >= 2) B200_CUDA(cudaStreamWaitEvent(h->stream, h->ev_up[buf], 0));  // buffer free again
                         h->prof.begin(CAT_INV_FIRST, h->stream);
                         cudaError_t e = launch_inv_lower(pl.ra_lo, pl.rb_lo, dim3(cnt, fa.M_hi / fa.nb), threads_lo, smem_lo, h->stream, fa);
                         h->prof.end(h->stream);
                         h->launches++;
                         B200_CUDA(e);
-                        h->prof.begin(CAT_INV_LAST, h->stream);
-                        e = launch_inv_upper(pl.ra_hi, pl.rb_hi, dim3(cnt, fa.M_lo / fa.C), block_hi, smem_hi, h->stream, fa);
-                        h->prof.end(h->stream);
+                        B200_CUDA(cudaEventRecord(h->ev_lo[buf], h->stream));
+                        if (overlap) B200_CUDA(cudaStreamWaitEvent(s2, h->ev_lo[buf], 0));
+                        h->prof.begin(CAT_INV_LAST, s2);
+                        e = launch_inv_upper(pl.ra_hi, pl.rb_hi, dim3(cnt, fa.M_lo / fa.C), block_hi, smem_hi, s2, fa);
+                        h->prof.end(s2);
                         h->launches++;
                         B200_CUDA(e);
+                        B200_CUDA(cudaEventRecord(h->ev_up[buf], s2));
                     }
+                // join: everything after this (decision kernels, result copy) is on the main stream
+                if (overlap) B200_CUDA(cudaStreamWaitEvent(h->stream, h->ev_up[0], 0));
+                if (overlap && it >= 2) B200_CUDA(cudaStreamWaitEvent(h->stream, h->ev_up[1], 0));
                 return GNSS_B200_OK;
             }
         for (uint32_t y0 = 0; y0 < rows; y0 += chunk)
@@ -467,6 +502,9 @@ extern "C"
         h->has_code.assign(cfg->max_slots, 0);
         h->dwell.assign(cfg->max_slots, 0);
         cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
+        for (cudaEvent_t* ev : {&h->ev_lo[0], &h->ev_lo[1], &h->ev_up[0], &h->ev_up[1], &h->ev_fork})
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
         // twiddle table exp(-2 pi i k / N), computed in double and rounded once
         std::vector<float2> W(h->N);
         for (uint32_t k = 0; k < h->N; k++)
@@ -483,11 +521,6 @@ extern "C"
         if (e == cudaSuccess) e = cudaMemset(h->d_rows.p, 0, sizeof(gnss_b200_acq_row) * (size_t)cfg->max_slots * h->nD);
         if (e == cudaSuccess) e = h->d_pieces.reserve(sizeof(WipePiece) * (size_t)kMaxCachedGroups * h->nD_local * kMaxPieces);
         if (e == cudaSuccess) e = h->d_npieces.reserve(sizeof(uint32_t) * (size_t)kMaxCachedGroups * h->nD_local);
-        if (e == cudaSuccess && h->plan.n_stages == 2)
-            {
-                const size_t rows = std::max<size_t>(1, kScratchBudgetBytes / ((size_t)h->N * 8));
-                e = h->d_scratch.reserve(rows * h->N * 8);
-            }
         if (e == cudaSuccess && cfg->keep_grid)
             {
                 const size_t bytes = sizeof(float) * (size_t)cfg->max_slots * h->nD_local * h->eff;
@@ -515,6 +548,10 @@ extern "C"
         h->h_results.release();
         h->h_samples.release();
         h->prof.release();
+        if (h->stream2) cudaStreamSynchronize(h->stream2);
+        for (cudaEvent_t ev : {h->ev_lo[0], h->ev_lo[1], h->ev_up[0], h->ev_up[1], h->ev_fork})
+            if (ev) cudaEventDestroy(ev);
+        if (h->stream2) cudaStreamDestroy(h->stream2);
         if (h->stream) cudaStreamDestroy(h->stream);
         delete h;
         return GNSS_B200_OK;
