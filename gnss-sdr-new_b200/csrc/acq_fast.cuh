@@ -176,6 +176,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     __shared__ float s_rmax[kFastThreads / 32];
     __shared__ uint32_t s_ridx[kFastThreads / 32];
     __shared__ float s_rsum[kFastThreads / 32];
+    __shared__ uint32_t s_tile_idx;
 
     const uint32_t y = a.y0 + blockIdx.x;
     uint32_t si, kk;
@@ -238,61 +239,92 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     const bool full_rows = (a.mag_offset == 0 && a.eff == a.N);
     float best = -1.f, sum = 0.f;
     uint32_t best_i = 0xffffffffu;
+    if (tid == 0) s_tile_idx = 0xffffffffu;
+    if (full_rows)
+        {
+            // Common case (no bit transition): every output belongs to the row. The running maximum is a plain FMNMX;
+            // each |.|^2 is parked in the shared-memory slot its pencil just consumed (no other thread reads it), and
+            // once the tile maximum is known only the thread(s) holding it look their slots up for the lowest index.
+            for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
+                {
+                    float2 v[RB];
+#pragma unroll
+                    for (int u = 0; u < RB; u++) v[u] = s[(size_t)(aa + RA * u) * C + c];
+                    fft::Dft<RB, true>::run(v);
+                    const uint32_t pos0 = aa * a.M_lo + c0 + c;
+                    const uint32_t pstep = RA * a.M_lo;
+#pragma unroll
+                    for (int b = 0; b < RB; b++)
+                        {
+                            float g = v[b].x * v[b].x + v[b].y * v[b].y;       // :674
+                            if (accumulate) g = mag[pos0 + b * pstep] + g;      // :679
+                            if (mag) mag[pos0 + b * pstep] = g;
+                            sum += g;
+                            best = fmaxf(best, g);
+                            s[(size_t)(aa + RA * b) * C + c].x = g;
+                        }
+                }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+                {
+                    best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
+                    sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                }
+            const int lane = tid & 31, warp = tid >> 5;
+            if (lane == 0)
+                {
+                    s_rmax[warp] = best;
+                    s_rsum[warp] = sum;
+                }
+            __syncthreads();
+            const int nw = (nthreads + 31) / 32;
+            float tile_max = s_rmax[0];
+            for (int w = 1; w < nw; w++) tile_max = fmaxf(tile_max, s_rmax[w]);
+            if (best == tile_max)  // warp-uniform after the butterfly reduction: at most a few warps per tile get here
+                {
+                    uint32_t mine = 0xffffffffu;
+                    for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
+                        {
+#pragma unroll
+                            for (int b = 0; b < RB; b++)
+                                if (s[(size_t)(aa + RA * b) * C + c].x == tile_max) mine = min(mine, (aa + RA * b) * a.M_lo + c0 + c);
+                        }
+                    if (mine != 0xffffffffu) atomicMin(&s_tile_idx, mine);  // lowest index wins ties (:523)
+                }
+            __syncthreads();
+            if (tid == 0)
+                {
+                    for (int w = 1; w < nw; w++) sum += s_rsum[w];
+                    RowPartial rp;
+                    rp.max_val = tile_max;
+                    rp.max_idx = s_tile_idx;
+                    rp.sum = sum;
+                    rp.pad = 0;
+                    a.partials[(size_t)y * gridDim.y + blockIdx.y] = rp;
+                }
+            return;
+        }
     for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
         {
             float2 v[RB];
 #pragma unroll
             for (int u = 0; u < RB; u++) v[u] = s[(size_t)(aa + RA * u) * C + c];
             fft::Dft<RB, true>::run(v);
-            if (full_rows)
+#pragma unroll
+            for (int b = 0; b < RB; b++)
                 {
-                    // common case (no bit transition): every output belongs to the row. Track the pencil maximum with
-                    // FMNMX and resolve the index only when it can change the running best (rare after warm-up).
-                    float g[RB];
-                    float pm = -1.f;
-                    const uint32_t pos0 = aa * a.M_lo + c0 + c;
-                    const uint32_t pstep = RA * a.M_lo;
-#pragma unroll
-                    for (int b = 0; b < RB; b++)
+                    const uint32_t pos = (aa + RA * b) * a.M_lo + c0 + c;  // natural time index
+                    const uint32_t m = pos - a.mag_offset;
+                    if (m < a.eff)
                         {
-                            g[b] = v[b].x * v[b].x + v[b].y * v[b].y;            // :674
-                            if (accumulate) g[b] = mag[pos0 + b * pstep] + g[b];  // :679
-                            if (mag) mag[pos0 + b * pstep] = g[b];
-                            sum += g[b];
-                            pm = fmaxf(pm, g[b]);
-                        }
-                    if (pm >= best)
-                        {
-#pragma unroll
-                            for (int b = 0; b < RB; b++)
+                            float g = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                            if (accumulate) g = mag[m] + g;               // :679
+                            if (mag) mag[m] = g;
+                            sum += g;
+                            if (g > best || (g == best && m < best_i))
                                 {
-                                    const uint32_t m = pos0 + b * pstep;
-                                    if (g[b] > best || (g[b] == best && m < best_i))
-                                        {
-                                            best = g[b];
-                                            best_i = m;
-                                        }
-                                }
-                        }
-                }
-            else
-                {
-#pragma unroll
-                    for (int b = 0; b < RB; b++)
-                        {
-                            const uint32_t pos = (aa + RA * b) * a.M_lo + c0 + c;  // natural time index
-                            const uint32_t m = pos - a.mag_offset;
-                            if (m < a.eff)
-                                {
-                                    float g = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
-                                    if (accumulate) g = mag[m] + g;               // :679
-                                    if (mag) mag[m] = g;
-                                    sum += g;
-                                    if (g > best || (g == best && m < best_i))
-                                        {
-                                            best = g;
-                                            best_i = m;
-                                        }
+                                    best = g;
+                                    best_i = m;
                                 }
                         }
                 }
