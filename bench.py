@@ -142,6 +142,8 @@ def run_ours(args):
         raise RuntimeError("bench.py: no CUDA device; libgnss_b200 has no CPU path")
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # stdout carries exactly one JSON line (VERSION prints a banner there)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():

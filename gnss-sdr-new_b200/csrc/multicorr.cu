@@ -350,7 +350,7 @@ constexpr int kWinRing = 4;                 // commit groups in the per-thread s
 constexpr uint32_t kWinRingBytes = kWinRing * kWinGroup * kThreads * 8u;
 
 template <int T>
-__global__ void __launch_bounds__(kThreads, 4) multicorr_window_kernel(const ChanParams* __restrict__ chans, const float* __restrict__ shifts_all,
+__global__ void __launch_bounds__(kThreads, 3) multicorr_window_kernel(const ChanParams* __restrict__ chans, const float* __restrict__ shifts_all,
     float2* __restrict__ partials, uint32_t* __restrict__ tickets, float2* __restrict__ out, int n_taps_total, int tap0, uint32_t smem_elems)
 {
     constexpr int TP = (T + 1) / 2;

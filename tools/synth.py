@@ -162,6 +162,9 @@ CONFIGS = {
                present=[1, 3, 7, 10, 15, 21, 22, 30], cn0=(38, 50), seed=0),
     "C2": dict(system="gal_e1b", fs=8000000, sampled_ms=4, doppler_max=5000, doppler_step=125, n_prn=50,
                present=[1, 4, 9, 11, 19, 24, 27, 30, 36, 44], cn0=(36, 48), seed=2),
+    # weak-signal search: 20 ms coherent (N = 2 * 80 000 zero-padded, pcps_acquisition.cc:85-92) x 10 non-coherent dwells
+    "C3": dict(system="gps_l1_ca", fs=4000000, sampled_ms=20, doppler_max=10000, doppler_step=25, n_prn=32,
+               present=[4, 11, 18, 29], cn0=(25, 29), seed=3, max_dwells=10),
     "C4_gps": dict(system="gps_l1_ca", fs=25000000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=32,
                    present=[2, 5, 9, 13, 17, 23, 26, 31], cn0=(38, 50), seed=4),
     "C4_gal": dict(system="gal_e1b", fs=25000000, sampled_ms=4, doppler_max=5000, doppler_step=250, n_prn=36,
@@ -171,8 +174,9 @@ CONFIGS = {
 }
 
 
-def config_scene(name, n_prn=None):
-    """(geometry dict, codes [n_prn][consumed] c64, iq [consumed] c64, truth list) for a named config."""
+def config_scene(name, n_prn=None, n_dwells=1):
+    """(geometry dict, codes [n_prn][consumed] c64, iq [consumed] c64, truth list) for a named config.
+    With n_dwells > 1 `iq` is [n_dwells][consumed]: consecutive blocks of ONE continuous stream."""
     c = CONFIGS[name]
     chip_rate, _, ms_per_code = SYSTEMS[c["system"]]
     fs = c["fs"]
@@ -188,10 +192,12 @@ def config_scene(name, n_prn=None):
         truth.append(dict(system=c["system"], prn=prn, delay=int(rng.integers(0, one_len)),
                           doppler=float(rng.uniform(-0.9, 0.9) * c["doppler_max"]) + 13.7,
                           cn0=float(rng.uniform(*c["cn0"]))))
-    iq = make_iq(consumed, fs, truth, c["seed"])
+    iq = make_iq(consumed * n_dwells, fs, truth, c["seed"])
+    if n_dwells > 1:
+        iq = iq.reshape(n_dwells, consumed)
     codes = np.stack([adapter_code(c["system"], p, fs, c["sampled_ms"])[:consumed] for p in range(1, n_prn + 1)])
     geo = dict(fft_size=fft_size, consumed_samples=consumed, fs=fs, doppler_max=c["doppler_max"],
                doppler_step=c["doppler_step"], samples_per_chip=int(np.ceil(float(_f32(fs) / _f32(chip_rate)))),
                samples_per_code=float(_f32(_f32(_f32(fs) * _f32(0.001)) * _f32(ms_per_code))), n_prn=n_prn,
-               system=c["system"], sampled_ms=c["sampled_ms"])
+               system=c["system"], sampled_ms=c["sampled_ms"], max_dwells=c.get("max_dwells", 1))
     return geo, codes.astype(np.complex64), iq, truth
