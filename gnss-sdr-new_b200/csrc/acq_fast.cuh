@@ -166,7 +166,9 @@ __global__ void __launch_bounds__(kFastThreads) inv_lower_kernel(const FastArgs 
 // ------------------------------------------------------------------------------------------------
 // upper stage: grid (rows, M_lo / C), block (C, threads / C). Shared memory: M * C data + M twiddles.
 // ------------------------------------------------------------------------------------------------
-template <int RA, int RB>
+// GRID = true: persistent magnitude grid (max_dwells > 1 / dump), full rows: the old grid values of a pencil are requested
+// (streaming loads) before its butterfly so that their HBM latency hides behind it, and written back with streaming stores.
+template <int RA, int RB, bool GRID = false>
 __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs a)
 {
     constexpr int M = RA * RB;
@@ -248,17 +250,31 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
             for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
                 {
                     float2 v[RB];
+                    const uint32_t pos0 = aa * a.M_lo + c0 + c;
+                    const uint32_t pstep = RA * a.M_lo;
+                    float old[GRID ? RB : 1];
+                    if (GRID)
+                        {
+#pragma unroll
+                            for (int b = 0; b < RB; b++) old[b] = accumulate ? __ldcs(mag + pos0 + b * pstep) : 0.f;
+                        }
 #pragma unroll
                     for (int u = 0; u < RB; u++) v[u] = s[(size_t)(aa + RA * u) * C + c];
                     fft::Dft<RB, true>::run(v);
-                    const uint32_t pos0 = aa * a.M_lo + c0 + c;
-                    const uint32_t pstep = RA * a.M_lo;
 #pragma unroll
                     for (int b = 0; b < RB; b++)
                         {
                             float g = v[b].x * v[b].x + v[b].y * v[b].y;       // :674
-                            if (accumulate) g = mag[pos0 + b * pstep] + g;      // :679
-                            if (mag) mag[pos0 + b * pstep] = g;
+                            if (GRID)
+                                {
+                                    g = old[b] + g;                                 // :679 (0 + g on the first dwell)
+                                    __stcs(mag + pos0 + b * pstep, g);
+                                }
+                            else
+                                {
+                                    if (accumulate) g = mag[pos0 + b * pstep] + g;  // :679
+                                    if (mag) mag[pos0 + b * pstep] = g;
+                                }
                             sum += g;
                             best = fmaxf(best, g);
                             s[(size_t)(aa + RA * b) * C + c].x = g;
@@ -372,6 +388,6 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
 
 // host-side launchers (instantiations live in acq_fast_lower.cu / acq_fast_upper.cu)
 cudaError_t launch_inv_lower(uint32_t ra, uint32_t rb, dim3 grid, uint32_t threads, size_t smem, cudaStream_t st, const FastArgs& a);
-cudaError_t launch_inv_upper(uint32_t ra, uint32_t rb, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a);
+cudaError_t launch_inv_upper(uint32_t ra, uint32_t rb, bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a);
 
 }  // namespace b200

@@ -98,10 +98,16 @@ namespace
 {
 uint32_t best_columns(uint32_t M_lo, uint32_t M_hi)
 {
-    uint32_t C = 1;
+    // the widest column tile that fits; a multiple of 16 columns (128-byte scratch lines, 64-byte grid runs) wins over a
+    // wider odd one (measured on B200 at N = 160000: 16 beats 20 and 25)
+    uint32_t C = 1, C16 = 0;
     for (uint32_t d = 1; d <= 32; d++)
-        if (M_lo % d == 0 && (uint64_t)M_hi * d * 8 <= 64 * 1024) C = d;
-    return C;
+        if (M_lo % d == 0 && (uint64_t)M_hi * d * 8 <= 64 * 1024)
+            {
+                C = d;
+                if (d % 16 == 0) C16 = d;
+            }
+    return C16 ? C16 : C;
 }
 
 // N = (ra_lo*rb_lo) * (ra_hi*rb_hi) with every radix in the instantiated sets; lower is better
@@ -166,6 +172,11 @@ bool make_fft_plan(uint32_t N, uint32_t max_single, FftPlan* plan, const char** 
             FftStage& up = plan->stage[0];
             fill_stage(&up, N, M_hi, {plan->ra_hi, plan->rb_hi}, M_lo, true);
             up.C = best_columns(M_lo, M_hi);
+            if (const char* e = std::getenv("B200_FFT_COLS"))  // tuning aid: columns per upper-stage tile
+                {
+                    const uint32_t c = (uint32_t)std::atoi(e);
+                    if (c >= 1 && c <= 32 && M_lo % c == 0 && (uint64_t)M_hi * c * 8 <= 96 * 1024) up.C = c;
+                }
             up.blocks = 1;
             up.tiles = M_lo / up.C;
             up.tile_step = up.C;
@@ -176,6 +187,11 @@ bool make_fft_plan(uint32_t N, uint32_t max_single, FftPlan* plan, const char** 
             uint32_t b = 1;
             for (uint32_t d = 1; d <= M_hi; d++)
                 if (M_hi % d == 0 && (uint64_t)d * M_lo <= 4096) b = d;
+            if (const char* e = std::getenv("B200_FFT_NB"))  // tuning aid: sub-transforms per lower-stage tile
+                {
+                    const uint32_t c = (uint32_t)std::atoi(e);
+                    if (c >= 1 && M_hi % c == 0 && (uint64_t)c * M_lo <= 8192) b = c;
+                }
             lo.C = 1;
             lo.blocks = b;
             lo.tiles = M_hi / b;
