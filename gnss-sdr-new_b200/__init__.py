@@ -64,6 +64,52 @@ class McArgs(C.Structure):
 MC_HIGH_DYN = 1
 MC_SIX_ARG = 2
 
+
+class TrkCfg(C.Structure):
+    """gnss_b200_trk_cfg: Dll_Pll_Conf (dll_pll_conf.h:37-84) + the signal constants the block derives (dll_pll_veml_tracking.cc:105-460)."""
+    _fields_ = [
+        ("fs_in", C.c_double), ("code_chip_rate", C.c_double), ("signal_carrier_freq", C.c_double), ("code_period_s", C.c_double),
+        ("code_length_chips", c_u32), ("code_samples_per_chip", c_u32), ("vector_length", c_u32), ("veml", c_i32),
+        ("early_late_space_chips", C.c_float), ("very_early_late_space_chips", C.c_float), ("slope", C.c_float), ("y_intercept", C.c_float),
+        ("pll_bw_hz", C.c_float), ("dll_bw_hz", C.c_float), ("fll_bw_hz", C.c_float),
+        ("pll_filter_order", c_i32), ("dll_filter_order", c_i32),
+        ("enable_fll_pull_in", c_i32), ("enable_fll_steady_state", c_i32), ("carrier_aiding", c_i32),
+        ("pull_in_time_s", c_u32),
+        ("cn0_samples", c_i32), ("cn0_min", c_i32), ("max_code_lock_fail", c_i32), ("max_carrier_lock_fail", c_i32),
+        ("carrier_lock_th", C.c_double),
+        ("cn0_smoother_alpha", C.c_float), ("carrier_lock_test_smoother_alpha", C.c_float),
+        ("cn0_smoother_samples", c_i32), ("carrier_lock_test_smoother_samples", c_i32),
+        ("max_channels", c_u32), ("device", c_i32),
+    ]
+
+
+def trk_config(fs_in, code_chip_rate, code_length_chips, signal_carrier_freq, max_channels, code_samples_per_chip=1, veml=False, device=0, **kw):
+    """A gnss_b200_trk_cfg with the reference's defaults (dll_pll_conf.h:41-84, gnss_sdr_flags.cc:45-54); keyword
+    arguments override single fields."""
+    code_period_s = code_length_chips / code_chip_rate
+    c = TrkCfg(fs_in=fs_in, code_chip_rate=code_chip_rate, signal_carrier_freq=signal_carrier_freq, code_period_s=code_period_s,
+               code_length_chips=code_length_chips, code_samples_per_chip=code_samples_per_chip,
+               vector_length=int(round(fs_in / (code_chip_rate / code_length_chips))), veml=int(veml),
+               early_late_space_chips=0.25 if not veml else 0.15, very_early_late_space_chips=0.5, slope=1.0, y_intercept=1.0,
+               pll_bw_hz=35.0, dll_bw_hz=2.0, fll_bw_hz=35.0, pll_filter_order=3, dll_filter_order=2,
+               enable_fll_pull_in=0, enable_fll_steady_state=0, carrier_aiding=1, pull_in_time_s=10,
+               cn0_samples=20, cn0_min=25, max_code_lock_fail=50, max_carrier_lock_fail=5000, carrier_lock_th=0.7,
+               cn0_smoother_alpha=0.002, carrier_lock_test_smoother_alpha=0.002, cn0_smoother_samples=200,
+               carrier_lock_test_smoother_samples=25, max_channels=max_channels, device=device)
+    for k, v in kw.items():
+        if not hasattr(c, k):
+            raise B200Error(f"trk_config: unknown field {k}")
+        setattr(c, k, v)
+    return c
+
+
+TRK_EPOCH_DTYPE = np.dtype([("corr", np.float32, (10,)), ("carrier_doppler_hz", np.float64), ("code_freq_chips", np.float64),
+                            ("carr_error_hz", np.float64), ("carr_error_filt_hz", np.float64), ("code_error_chips", np.float64),
+                            ("code_error_filt_chips", np.float64), ("rem_code_phase_samples", np.float64),
+                            ("acc_carrier_phase_rad", np.float64), ("cn0_db_hz", np.float64), ("carrier_lock_test", np.float64),
+                            ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32)], align=True)
+TRK_VALID, TRK_PULL_IN, TRK_LOSS_OF_LOCK = 1, 2, 4
+
 # every symbol include/gnss_b200.h declares (tests check the library exports all of them)
 EXPORTS = [
     "gnss_b200_last_error", "gnss_b200_version", "gnss_b200_device_count", "gnss_b200_host_register",
@@ -76,6 +122,8 @@ EXPORTS = [
     "gnss_b200_mc_correlate_device_async", "gnss_b200_mc_sync", "gnss_b200_mc_chip_indices", "gnss_b200_mc_stream",
     "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan",
     "gnss_b200_acq_profile", "gnss_b200_mc_profile", "gnss_b200_debug_fp32_peak",
+    "gnss_b200_trk_create", "gnss_b200_trk_destroy", "gnss_b200_trk_set_code", "gnss_b200_trk_start", "gnss_b200_trk_run",
+    "gnss_b200_trk_stream", "gnss_b200_trk_launch_count",
 ]
 
 _lib = None
@@ -132,6 +180,15 @@ def lib():
     L.gnss_b200_acq_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]
     L.gnss_b200_mc_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]
     L.gnss_b200_debug_fp32_peak.argtypes = [c_i32, C.POINTER(C.c_double)]
+    L.gnss_b200_trk_create.argtypes = [C.POINTER(TrkCfg), C.POINTER(C.c_void_p)]
+    L.gnss_b200_trk_destroy.argtypes = [C.c_void_p]
+    L.gnss_b200_trk_set_code.argtypes = [C.c_void_p, c_u32, c_u32, _fp]
+    L.gnss_b200_trk_start.argtypes = [C.c_void_p, c_u32, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+    L.gnss_b200_trk_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, c_u32, _u32p, c_u32, C.c_void_p]
+    L.gnss_b200_trk_stream.argtypes = [C.c_void_p]
+    L.gnss_b200_trk_stream.restype = C.c_void_p
+    L.gnss_b200_trk_launch_count.argtypes = [C.c_void_p]
+    L.gnss_b200_trk_launch_count.restype = C.c_uint64
     _lib = L
     return L
 
@@ -385,3 +442,56 @@ class MulticorrelatorB200:
 
     def launch_count(self):
         return int(self.L.gnss_b200_mc_launch_count(self.h))
+
+
+class TrackingLoopB200:
+    """Many `dll_pll_veml_tracking` channels whose DLL/PLL loops are closed on the device.
+
+    start() is start_tracking() + the state-1 alignment; run() processes every code period the sample block holds
+    (state 2: correlate -> lock detectors -> discriminators -> loop filters -> NCO update) with no host round trip
+    between epochs and returns one record per epoch and channel."""
+
+    def __init__(self, cfg):
+        self.L = lib()
+        self.cfg = cfg
+        self.h = C.c_void_p()
+        _check(self.L.gnss_b200_trk_create(C.byref(cfg), C.byref(self.h)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.gnss_b200_trk_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_code(self, ch, code):
+        code = np.ascontiguousarray(code, dtype=np.float32)
+        _check(self.L.gnss_b200_trk_set_code(self.h, ch, code.size, _f32p(code)))
+
+    def start(self, ch, acq_delay_samples, acq_doppler_hz, acq_samplestamp, now_sample):
+        _check(self.L.gnss_b200_trk_start(self.h, ch, float(acq_delay_samples), float(acq_doppler_hz), int(acq_samplestamp), int(now_sample)))
+
+    def run(self, samples, stream_start, channels, max_epochs):
+        samples = np.ascontiguousarray(samples, dtype=np.complex64)
+        channels = _u32a(channels)
+        out = np.zeros((max_epochs, channels.size), dtype=TRK_EPOCH_DTYPE)
+        _check(self.L.gnss_b200_trk_run(self.h, samples.ctypes.data_as(C.c_void_p), 0, int(stream_start), samples.size, channels.size,
+                                        channels.ctypes.data_as(_u32p), max_epochs, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def run_device(self, d_samples_ptr, n_samples, stream_start, channels, max_epochs):
+        channels = _u32a(channels)
+        out = np.zeros((max_epochs, channels.size), dtype=TRK_EPOCH_DTYPE)
+        _check(self.L.gnss_b200_trk_run(self.h, C.c_void_p(d_samples_ptr), 1, int(stream_start), int(n_samples), channels.size,
+                                        channels.ctypes.data_as(_u32p), max_epochs, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def stream(self):
+        return self.L.gnss_b200_trk_stream(self.h)
+
+    def launch_count(self):
+        return int(self.L.gnss_b200_trk_launch_count(self.h))

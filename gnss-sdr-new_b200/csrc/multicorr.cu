@@ -17,7 +17,7 @@
 //     *binary32-rounded* per-sample phasor exp(-j*step) — the recursion of the reference converges to that
 //     angle, not to `step`. Evaluated per thread in double at its first sample, then
 //     advanced by a stride phasor.
-#include "common.cuh"
+#include "multicorr_internal.cuh"
 #include <type_traits>
 #include <cmath>
 #include <cstdlib>
@@ -26,34 +26,9 @@
 
 namespace b200
 {
+using namespace mc;
 namespace
 {
-constexpr int kThreads = 256;
-constexpr int kMaxTapsPerPass = 16;
-constexpr uint32_t kSmemCapBytes = 200 * 1024;
-
-enum : uint32_t
-{
-    F_HIGH_DYN_RESAMPLER = 1u,
-    F_HIGH_DYN_ROTATOR = 2u,
-    F_COMPLEX_CODE = 4u
-};
-
-struct alignas(16) ChanParams
-{
-    const float2* sig;   // device samples of this channel
-    const void* code;    // device code table (float or float2)
-    double theta;        // effective rotation per sample [rad]
-    uint32_t code_len;
-    uint32_t n;
-    float rem_code, code_step, code_rate;
-    float p0_re, p0_im;  // (cos rem_carr, -sin rem_carr)
-    float wb_re, wb_im;  // exp(j*kThreads*theta)
-    float rate_arg;      // arg of the rounded rate phasor (high-dynamics rotator)
-    uint32_t flags;
-    uint32_t shifts_off;  // offset into the shifts / shift_samples arrays
-};
-
 // Device half of the per-channel constants: the true angle of the binary32-rounded per-sample phasor the reference
 // multiplies by (its rotator advances by exactly that angle, not by phase_step_rad), and the stride phasor.
 __global__ void prep_kernel(ChanParams* __restrict__ chans, uint32_t n_ch)
@@ -345,9 +320,6 @@ __device__ __forceinline__ void cp_async_8(uint32_t smem_addr, const void* gptr,
 
 constexpr float kFloorMagic = 12582912.0f;  // 1.5 * 2^23
 constexpr uint32_t kFloorMagicBits = 0x4B400000u;
-constexpr int kWinGroup = 4;                // samples per cp.async commit group (per thread)
-constexpr int kWinRing = 4;                 // commit groups in the per-thread shared-memory ring
-constexpr uint32_t kWinRingBytes = kWinRing * kWinGroup * kThreads * 8u;
 
 template <int T>
 __global__ void __launch_bounds__(kThreads, 3) multicorr_window_kernel(const ChanParams* __restrict__ chans, const float* __restrict__ shifts_all,
@@ -633,6 +605,21 @@ void launch_taps(int T, dim3 grid, size_t smem, cudaStream_t st, const ChanParam
 }
 
 }  // namespace
+
+cudaError_t mc::launch_real_plain(bool fast, uint32_t n_ch, uint32_t splits, uint32_t smem_elems, cudaStream_t st, const ChanParams* d_cp,
+    const float* d_shifts, const uint32_t* d_shift_samples, float2* d_partials, uint32_t* d_tickets, float2* d_out, uint32_t n_taps)
+{
+    const dim3 grid(splits, n_ch);
+    for (uint32_t tap0 = 0; tap0 < n_taps; tap0 += kMaxTapsPerPass)
+        {
+            const int T = (int)std::min<uint32_t>(kMaxTapsPerPass, n_taps - tap0);
+            if (fast)
+                launch_window(T, grid, (size_t)smem_elems * 4 + kWinRingBytes, st, d_cp, d_shifts, d_partials, d_tickets, d_out, (int)n_taps, (int)tap0, smem_elems);
+            else
+                launch_taps<float>(T, grid, (size_t)smem_elems * 4, st, d_cp, d_shifts, d_shift_samples, d_partials, d_tickets, d_out, (int)n_taps, (int)tap0, smem_elems);
+        }
+    return cudaGetLastError();
+}
 }  // namespace b200
 
 using namespace b200;

@@ -222,6 +222,87 @@ extern "C"
     GNSS_B200_API void* gnss_b200_mc_stream(gnss_b200_mc* h);
     GNSS_B200_API uint64_t gnss_b200_mc_launch_count(const gnss_b200_mc* h);
 
+
+    /* ------------------------------------------------------------------ */
+    /* (f) N1: the dll_pll_veml tracking loop closed on the device          */
+    /* ------------------------------------------------------------------ */
+
+    /* Per-epoch loop of dll_pll_veml_tracking::general_work, state 2 (one code period per integration, data
+       component, Costas PLL): do_correlation_step (dll_pll_veml_tracking.cc:1064-1089) ->
+       cn0_and_tracking_lock_status (:968-1013) -> run_dll_pll (:1092-1182) -> update_tracking_vars (:1225-1297) ->
+       consume_each(d_current_prn_length_samples) (:2118), for many channels at once and for as many epochs as the
+       uploaded stream holds, WITHOUT a host round trip between epochs: a loop-update kernel turns the correlator
+       outputs of epoch e into the multicorrelator arguments of epoch e+1 in device memory.
+       Not covered (stay in the host block): secondary-code / bit synchronisation (:923-966), extended integration
+       (states 3-4), pilot + data correlator pairs, high-dynamics smoothing, dumps.
+       Field names follow Dll_Pll_Conf (dll_pll_conf.h:37-84) and the block's members (dll_pll_veml_tracking.h). */
+    typedef struct
+    {
+        double fs_in;                 /* Dll_Pll_Conf::fs_in */
+        double code_chip_rate;        /* d_code_chip_rate [chips/s] */
+        double signal_carrier_freq;   /* d_signal_carrier_freq [Hz] (carrier aiding) */
+        double code_period_s;         /* d_code_period */
+        uint32_t code_length_chips;   /* d_code_length_chips */
+        uint32_t code_samples_per_chip; /* d_code_samples_per_chip: 1, or 2 for Galileo E1 (:270) */
+        uint32_t vector_length;       /* Dll_Pll_Conf::vector_length: samples correlated per epoch */
+        int32_t veml;                 /* 1: five taps VE,E,P,L,VL (d_veml), 0: three taps E,P,L */
+        float early_late_space_chips, very_early_late_space_chips;
+        float slope, y_intercept;     /* dll_nc_e_minus_l_normalized parameters */
+        float pll_bw_hz, dll_bw_hz, fll_bw_hz;
+        int32_t pll_filter_order;     /* 2 or 3 */
+        int32_t dll_filter_order;     /* 1, 2 or 3 */
+        int32_t enable_fll_pull_in, enable_fll_steady_state, carrier_aiding;
+        uint32_t pull_in_time_s;
+        int32_t cn0_samples;          /* FLAGS_cn0_samples (<= 64) */
+        int32_t cn0_min, max_code_lock_fail, max_carrier_lock_fail;
+        double carrier_lock_th;
+        float cn0_smoother_alpha, carrier_lock_test_smoother_alpha;
+        int32_t cn0_smoother_samples, carrier_lock_test_smoother_samples;  /* smoother initialisation lengths (<= 256) */
+        uint32_t max_channels;
+        int32_t device;
+    } gnss_b200_trk_cfg;
+
+    /* What one epoch leaves behind per channel: the quantities log_data() dumps (:1403-1530) and the Gnss_Synchro
+       tracking fields. */
+    typedef struct
+    {
+        float corr[10];               /* VE,E,P,L,VL as (re,im) pairs; E,P,L in slots 1..3 when veml == 0 too */
+        double carrier_doppler_hz;    /* d_carrier_doppler_hz after this epoch's PLL update */
+        double code_freq_chips;       /* d_code_freq_chips */
+        double carr_error_hz, carr_error_filt_hz, code_error_chips, code_error_filt_chips;
+        double rem_code_phase_samples, acc_carrier_phase_rad;
+        double cn0_db_hz, carrier_lock_test;
+        uint64_t sample_counter;      /* absolute index of the first sample correlated in this epoch */
+        int32_t prn_length_samples;   /* samples consumed after this epoch (d_current_prn_length_samples) */
+        uint32_t flags;               /* GNSS_B200_TRK_* */
+    } gnss_b200_trk_epoch;
+
+    enum
+    {
+        GNSS_B200_TRK_VALID = 1,        /* the channel correlated in this epoch */
+        GNSS_B200_TRK_PULL_IN = 2,      /* d_pull_in_transitory still set */
+        GNSS_B200_TRK_LOSS_OF_LOCK = 4  /* cn0_and_tracking_lock_status() returned false: channel went to standby */
+    };
+
+    typedef struct gnss_b200_trk gnss_b200_trk;
+
+    GNSS_B200_API int gnss_b200_trk_create(const gnss_b200_trk_cfg* cfg, gnss_b200_trk** out);
+    GNSS_B200_API int gnss_b200_trk_destroy(gnss_b200_trk* h);
+    /* the tracking code of channel `ch` (d_tracking_code: code_samples_per_chip * code_length_chips floats) */
+    GNSS_B200_API int gnss_b200_trk_set_code(gnss_b200_trk* h, uint32_t ch, uint32_t code_len, const float* code);
+    /* start_tracking() (:640-880) + the state-1 alignment (:1812-1845): `now_sample` is the absolute index of the next
+       unread stream sample (nitems_read(0)); the channel's read cursor is moved to the next code-period start. */
+    GNSS_B200_API int gnss_b200_trk_start(gnss_b200_trk* h, uint32_t ch, double acq_delay_samples, double acq_doppler_hz,
+        uint64_t acq_samplestamp, uint64_t now_sample);
+    /* Runs every started channel over the stream block samples_c64[0 .. n_samples) whose first sample has absolute index
+       stream_start: up to max_epochs epochs, each needing 2 * vector_length samples ahead of the channel's cursor
+       (the block's forecast(), :609). out = [max_epochs][n_ch] records for the listed channels (flags == 0 where a channel
+       did not run). samples_is_device != 0: samples_c64 is a device pointer. */
+    GNSS_B200_API int gnss_b200_trk_run(gnss_b200_trk* h, const float* samples_c64, int samples_is_device, uint64_t stream_start,
+        uint64_t n_samples, uint32_t n_ch, const uint32_t* ch, uint32_t max_epochs, gnss_b200_trk_epoch* out);
+    GNSS_B200_API void* gnss_b200_trk_stream(gnss_b200_trk* h);
+    GNSS_B200_API uint64_t gnss_b200_trk_launch_count(const gnss_b200_trk* h);
+
     /* ------------------------------------------------------------------ */
     /* parity aids (pure host, no device needed)                           */
     /* ------------------------------------------------------------------ */

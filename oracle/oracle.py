@@ -38,6 +38,31 @@ class AcqResult(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class TrkCfg(C.Structure):
+    """oracle_trk_cfg == gnss_b200_trk_cfg (include/gnss_b200.h)."""
+    _fields_ = [
+        ("fs_in", C.c_double), ("code_chip_rate", C.c_double), ("signal_carrier_freq", C.c_double), ("code_period_s", C.c_double),
+        ("code_length_chips", c_u), ("code_samples_per_chip", c_u), ("vector_length", c_u), ("veml", C.c_int32),
+        ("early_late_space_chips", c_f), ("very_early_late_space_chips", c_f), ("slope", c_f), ("y_intercept", c_f),
+        ("pll_bw_hz", c_f), ("dll_bw_hz", c_f), ("fll_bw_hz", c_f),
+        ("pll_filter_order", C.c_int32), ("dll_filter_order", C.c_int32),
+        ("enable_fll_pull_in", C.c_int32), ("enable_fll_steady_state", C.c_int32), ("carrier_aiding", C.c_int32),
+        ("pull_in_time_s", c_u),
+        ("cn0_samples", C.c_int32), ("cn0_min", C.c_int32), ("max_code_lock_fail", C.c_int32), ("max_carrier_lock_fail", C.c_int32),
+        ("carrier_lock_th", C.c_double),
+        ("cn0_smoother_alpha", c_f), ("carrier_lock_test_smoother_alpha", c_f),
+        ("cn0_smoother_samples", C.c_int32), ("carrier_lock_test_smoother_samples", C.c_int32),
+        ("max_channels", c_u), ("device", C.c_int32),
+    ]
+
+
+TRK_EPOCH_DTYPE = np.dtype([("corr", np.float32, (10,)), ("carrier_doppler_hz", np.float64), ("code_freq_chips", np.float64),
+                            ("carr_error_hz", np.float64), ("carr_error_filt_hz", np.float64), ("code_error_chips", np.float64),
+                            ("code_error_filt_chips", np.float64), ("rem_code_phase_samples", np.float64),
+                            ("acc_carrier_phase_rad", np.float64), ("cn0_db_hz", np.float64), ("carrier_lock_test", np.float64),
+                            ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32)], align=True)
+
+
 def build(ref=None):
     """Compile liboracle.so (always) and _ref/ (when the reference tree is present)."""
     subprocess.run(["make", "-s", "-C", _HERE], check=True)
@@ -74,6 +99,13 @@ def _bind_oracle(lib):
     lib.oracle_mc_real.argtypes = [_fp, c_i, _fp, c_i, _fp, c_i, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, _fp]
     lib.oracle_mc_cplx.argtypes = [_fp, c_i, _fp, c_i, _fp, c_i, c_f, c_f, c_f, c_f, _fp]
     lib.oracle_mc_chip_indices.argtypes = [c_i, c_i, _fp, c_i, c_f, c_f, c_f, c_i, C.POINTER(C.c_int32)]
+    lib.oracle_trk_create.restype = C.c_void_p
+    lib.oracle_trk_create.argtypes = [C.POINTER(TrkCfg)]
+    lib.oracle_trk_destroy.argtypes = [C.c_void_p]
+    lib.oracle_trk_set_code.argtypes = [C.c_void_p, _fp, c_i]
+    lib.oracle_trk_start.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+    lib.oracle_trk_run.restype = c_i
+    lib.oracle_trk_run.argtypes = [C.c_void_p, _fp, C.c_uint64, C.c_uint64, c_i, C.c_void_p]
     lib.oracle_fft_c64.argtypes = [_fp, _fp, c_i, c_i]
     lib.oracle_fft_c128.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), c_i, c_i]
     lib.oracle_samples_per_code.restype = c_i
@@ -116,6 +148,10 @@ class Oracle:
 
     def gamma_p_inv(self, a, p):
         return float(self.lib.oracle_gamma_p_inv(a, p))
+
+    # ---- tracking loop (dll_pll_veml_tracking, state 2) ----
+    def trk(self, cfg):
+        return OracleTrk(self, cfg)
 
     # ---- multicorrelator ----
     def mc_real(self, sig, code, shifts, rem_carr, carr_step, carr_rate, rem_code, code_step, code_rate,
@@ -232,17 +268,63 @@ class OracleAcq:
         return np.ctypeslib.as_array(p, shape=(self.n_doppler, self.fft_size * 2)).copy().view(np.complex64)
 
 
+class OracleTrk:
+    """One channel of the reference block's state-2 loop (oracle_trk.c)."""
+
+    def __init__(self, oracle, cfg):
+        self.lib = oracle.lib
+        self.cfg = cfg
+        self.h = self.lib.oracle_trk_create(C.byref(cfg))
+
+    def close(self):
+        if self.h:
+            self.lib.oracle_trk_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def set_code(self, code):
+        code = np.ascontiguousarray(code, dtype=np.float32)
+        self.lib.oracle_trk_set_code(self.h, _ptr(code), code.size)
+
+    def start(self, acq_delay_samples, acq_doppler_hz, acq_samplestamp, now_sample):
+        self.lib.oracle_trk_start(self.h, float(acq_delay_samples), float(acq_doppler_hz), int(acq_samplestamp), int(now_sample))
+
+    def run(self, samples, stream_start, max_epochs):
+        samples = np.ascontiguousarray(samples, dtype=np.complex64)
+        out = np.zeros(max_epochs, dtype=TRK_EPOCH_DTYPE)
+        n = self.lib.oracle_trk_run(self.h, _ptr(samples.view(np.float32)), int(stream_start), samples.size, max_epochs, out.ctypes.data_as(C.c_void_p))
+        return out, n
+
+
 class RefLibs:
     """The reference's own code generators and multicorrelator classes (oracle/_ref). Container-only."""
 
     def __init__(self):
         d = os.path.join(_HERE, "_ref")
-        if not (os.path.exists(os.path.join(d, "libref_codes.so")) and os.path.exists(os.path.join(d, "libref_mc.so"))):
+        if not all(os.path.exists(os.path.join(d, f)) for f in ("libref_codes.so", "libref_mc.so", "libref_trk.so")):
             build(ref=True)
         self.codes = C.CDLL(os.path.join(d, "libref_codes.so"))
         self.mc = C.CDLL(os.path.join(d, "libref_mc.so"))
         self.mc.ref_mc_real.argtypes = [_fp, c_i, _fp, c_i, _fp, c_i, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, _fp]
         self.mc.ref_mc_cplx.argtypes = [_fp, c_i, _fp, c_i, _fp, c_i, c_f, c_f, c_f, c_f, _fp]
+        t = self.trk = C.CDLL(os.path.join(d, "libref_trk.so"))
+        t.ref_trk_loop_filter_run.argtypes = [c_f, c_f, c_i, c_i, c_f, _fp, c_i, _fp]
+        t.ref_trk_carrier_filter_run.argtypes = [c_f, c_f, c_i, c_f, _fp, _fp, c_f, c_i, _fp]
+        t.ref_trk_smoother_run.argtypes = [c_f, c_f, c_f, c_i, _fp, c_i, _fp]
+        t.ref_trk_fll_diff_atan.restype = C.c_double
+        t.ref_trk_fll_diff_atan.argtypes = [c_f, c_f, c_f, c_f, C.c_double, C.c_double]
+        t.ref_trk_pll_cloop.restype = C.c_double
+        t.ref_trk_pll_cloop.argtypes = [c_f, c_f]
+        t.ref_trk_dll_e_minus_l.restype = C.c_double
+        t.ref_trk_dll_e_minus_l.argtypes = [c_f] * 7
+        t.ref_trk_dll_vemlp.restype = C.c_double
+        t.ref_trk_dll_vemlp.argtypes = [_fp, _fp, _fp, _fp]
+        t.ref_trk_cn0_m2m4.restype = c_f
+        t.ref_trk_cn0_m2m4.argtypes = [_fp, c_i, c_f]
+        t.ref_trk_carrier_lock.restype = c_f
+        t.ref_trk_carrier_lock.argtypes = [_fp, c_i]
 
     def _i32(self, fn, n, prn):
         a = np.zeros(n, dtype=np.int32)

@@ -1,0 +1,136 @@
+"""GPU parity of the on-device dll_pll_veml tracking loop (gnss_b200_trk_*) against the oracle's
+restatement of the reference block's state-2 loop, through the C-ABI.
+
+Bar: the loop is a feedback system fed by correlator outputs that agree to ~1e-6, so trajectories are compared with
+explicit tolerances: integer quantities (samples consumed per epoch, sample counters, flags) exact; Doppler / code
+frequency within 1e-4 relative of their excursion scale (0.02 Hz / 1e-3 chips/s); correlator outputs within 1e-4 of |P|
+for the typical epoch (see _compare)."""
+import numpy as np
+import pytest
+
+import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfgs(b200, oracle_mod, system, veml, fs, n_ch, **kw):
+    chip_rate, code_len, _ = synth.SYSTEMS[system]
+    carrier = {"gps_l1_ca": 1575.42e6, "gal_e1b": 1575.42e6, "gps_l5i": 1176.45e6}[system]
+    spc = 2 if system == "gal_e1b" else 1
+    base = dict(enable_fll_pull_in=1, pull_in_time_s=0)
+    base.update(kw)
+    g = b200.trk_config(fs, chip_rate, code_len, carrier, n_ch, code_samples_per_chip=spc, veml=veml, **base)
+    o = oracle_mod.TrkCfg()
+    for name, _ in g._fields_:
+        setattr(o, name, getattr(g, name))
+    return g, o
+
+
+def _compare(gpu, want, n_min):
+    ok = want["flags"] & 1 == 1
+    assert ok.sum() >= n_min
+    assert np.array_equal(gpu["flags"], want["flags"])
+    assert np.array_equal(gpu["sample_counter"][ok], want["sample_counter"][ok])
+    assert np.array_equal(gpu["prn_length_samples"][ok], want["prn_length_samples"][ok])
+    # Correlator outputs: once the two loops differ in the last bits of their doubles, the binary32 code step handed to
+    # the resampler can differ by one ulp, which moves a few samples at chip boundaries to the neighbouring chip (each
+    # worth ~2|z| ~ 3): typical epochs agree to a few 1e-4 of |P|, no epoch is off by more than a handful of boundary samples.
+    scale = np.abs(want["corr"][ok][:, 4] + 1j * want["corr"][ok][:, 5]).mean()
+    d = np.abs(gpu["corr"][ok] - want["corr"][ok]).max(axis=1)
+    assert np.median(d) <= 3e-4 * scale  # closed loop: a 0.01 Hz Doppler difference already rotates P by ~1e-4 rad
+    assert d.max() <= 24.0
+    assert np.abs(gpu["carrier_doppler_hz"][ok] - want["carrier_doppler_hz"][ok]).max() <= 0.1   # the PLL jitter itself is ~1 Hz rms
+    assert np.median(np.abs(gpu["carrier_doppler_hz"][ok] - want["carrier_doppler_hz"][ok])) <= 2e-3
+    assert np.abs(gpu["code_freq_chips"][ok] - want["code_freq_chips"][ok]).max() <= 0.05  # 5e-8 of the chip rate; the DLL echoes a boundary-sample flip
+    # integrated quantities drift apart by what the per-epoch differences above add up to over 100-400 epochs
+    assert np.abs(gpu["rem_code_phase_samples"][ok] - want["rem_code_phase_samples"][ok]).max() <= 2e-3   # ~5e-4 chip; DLL jitter is ~1e-2 chip
+    assert np.abs(gpu["acc_carrier_phase_rad"][ok] - want["acc_carrier_phase_rad"][ok]).max() <= 5e-3
+    # the M2M4 estimator takes sqrt(2*m2^2 - m4), a difference of nearly equal numbers: 1e-4 in P becomes ~1e-2 dB
+    assert np.abs(gpu["cn0_db_hz"][ok] - want["cn0_db_hz"][ok]).max() <= 0.1
+    assert np.abs(gpu["carrier_lock_test"][ok] - want["carrier_lock_test"][ok]).max() <= 5e-3
+    assert np.abs(gpu["code_error_chips"][ok] - want["code_error_chips"][ok]).max() <= 1e-2
+    assert np.median(np.abs(gpu["code_error_chips"][ok] - want["code_error_chips"][ok])) <= 1e-4
+
+
+@pytest.mark.parametrize("system,veml,pll_order,dll_order", [("gps_l1_ca", False, 3, 2), ("gps_l1_ca", False, 2, 1), ("gal_e1b", True, 3, 3)])
+def test_loop_trajectories_match_oracle(b200, oracle, oracle_mod, system, veml, pll_order, dll_order):
+    fs, n_ms = 4e6, 400
+    prns = [3, 7, 12, 19]
+    dop = [1830.0, -2950.5, 310.25, 3999.0]
+    iq, truth, _ = synth.tracking_stream(system, prns, fs, n_ms, seed=21, cn0=46.0, dopplers=dop, delays=[1234.4, 77.9, 3999.2, 2500.0])
+    g, o = _cfgs(b200, oracle_mod, system, veml, fs, len(prns), pll_filter_order=pll_order, dll_filter_order=dll_order)
+    trk = b200.TrackingLoopB200(g)
+    chip_rate, code_len, _ = synth.SYSTEMS[system]
+    n_ep = int(n_ms / (1e3 * code_len / chip_rate)) - 2
+    err = 150.0 if system == "gps_l1_ca" else 30.0
+    for c, (p, t) in enumerate(zip(prns, truth)):
+        trk.set_code(c, synth.tracking_code(system, p))
+        trk.start(c, round(t["delay"]) - 1.0, t["doppler"] + err, 0, 2500)
+    got = trk.run(iq, 0, np.arange(len(prns)), n_ep)
+    for c, (p, t) in enumerate(zip(prns, truth)):
+        ot = oracle.trk(o)
+        ot.set_code(synth.tracking_code(system, p))
+        ot.start(round(t["delay"]) - 1.0, t["doppler"] + err, 0, 2500)
+        want, done = ot.run(iq, 0, n_ep)
+        _compare(got[:, c], want, n_ep - 3)
+        tail = got[:, c][got[:, c]["flags"] & 1 == 1][-30:]
+        assert abs(tail["carrier_doppler_hz"].mean() - t["doppler"]) < 3.0   # and the loop is actually locked on the satellite
+        ot.close()
+    assert trk.launch_count() == 2 * n_ep + 1   # one launch pair per epoch for ALL channels, no host round trip in between
+    trk.close()
+
+
+def test_streaming_in_blocks_equals_one_block(b200, oracle_mod):
+    """The stream may arrive in arbitrary blocks: cursors persist, a channel idles until 2 * vector_length samples are ahead."""
+    fs = 4e6
+    iq, truth, _ = synth.tracking_stream("gps_l1_ca", [5, 9], fs, 120, seed=5, cn0=45.0, dopplers=[500.0, -1200.0], delays=[10.0, 3000.5])
+    g, _ = _cfgs(b200, oracle_mod, "gps_l1_ca", False, fs, 2)
+    res = []
+    for blocks in ([iq.size], [100000, 130000, iq.size - 230000]):
+        trk = b200.TrackingLoopB200(g)
+        for c, t in enumerate(truth):
+            trk.set_code(c, synth.tracking_code("gps_l1_ca", t["prn"]))
+            trk.start(c, round(t["delay"]), t["doppler"] + 50.0, 0, 100)
+        recs, pos, keep = [], 0, 0
+        for n in blocks:
+            # the host keeps the unconsumed tail: re-present everything from the slowest cursor on (here simply 3 periods back)
+            lo = max(0, pos - 12000)
+            r = trk.run(iq[lo:pos + n], lo, [0, 1], 140)
+            recs.append(r)
+            pos += n
+        r = np.concatenate(recs, axis=0)
+        res.append([r[:, c][r[:, c]["flags"] & 1 == 1] for c in range(2)])
+        trk.close()
+    for c in range(2):
+        a, b_ = res[0][c], res[1][c]
+        assert a.size == b_.size and a.size >= 115
+        assert np.array_equal(a["sample_counter"], b_["sample_counter"])
+        assert np.array_equal(a["corr"], b_["corr"]) and np.array_equal(a["carrier_doppler_hz"], b_["carrier_doppler_hz"])
+
+
+def test_loss_of_lock_and_errors(b200, oracle, oracle_mod):
+    fs = 4e6
+    rng = np.random.default_rng(0)
+    noise = ((rng.standard_normal(400000) + 1j * rng.standard_normal(400000)) * np.sqrt(0.5)).astype(np.complex64)
+    g, o = _cfgs(b200, oracle_mod, "gps_l1_ca", False, fs, 1, max_code_lock_fail=5, cn0_smoother_samples=10, cn0_min=35)  # noise alone reads ~27 dB-Hz
+    trk = b200.TrackingLoopB200(g)
+    with pytest.raises(b200.B200Error):
+        trk.start(0, 0.0, 0.0, 0, 0)            # no code yet
+    trk.set_code(0, synth.tracking_code("gps_l1_ca", 1))
+    with pytest.raises(b200.B200Error):
+        trk.run(noise, 0, [0], 10)              # not started
+    # pull-in ends after whole elapsed seconds (:1795-1803): tracking starts 2 s after the acquisition sample stamp
+    t0 = 8000000
+    trk.start(0, 12.0, 100.0, 0, t0)
+    got = trk.run(noise, t0, [0], 95)[:, 0]
+    ot = oracle.trk(o)
+    ot.set_code(synth.tracking_code("gps_l1_ca", 1))
+    ot.start(12.0, 100.0, 0, t0)
+    want, _ = ot.run(noise, t0, 95)
+    assert np.array_equal(got["flags"], want["flags"])
+    assert (want["flags"] & 4).any()            # noise only: the code-lock counter trips and the channel goes to standby
+    lost = int(np.argmax(want["flags"] & 4 != 0))
+    assert not (got["flags"][lost + 1:] & 1).any()
+    with pytest.raises(b200.B200Error):
+        b200.TrackingLoopB200(b200.trk_config(fs, 1.023e6, 1023, 1575.42e6, 1, pll_filter_order=1))
+    trk.close()

@@ -201,3 +201,47 @@ def config_scene(name, n_prn=None, n_dwells=1):
                samples_per_code=float(_f32(_f32(_f32(fs) * _f32(0.001)) * _f32(ms_per_code))), n_prn=n_prn,
                system=c["system"], sampled_ms=c["sampled_ms"], max_dwells=c.get("max_dwells", 1))
     return geo, codes.astype(np.complex64), iq, truth
+
+
+def tracking_stream(system, prns, fs, n_ms, seed, cn0=45.0, dopplers=None, delays=None, code_samples_per_chip=1, data_bits=True):
+    """A continuous IQ stream for closed-loop tracking tests: every listed PRN with its own code delay (samples, may be
+    fractional), carrier Doppler AND the matching code Doppler (chip rate scaled by 1 + f_d / f_carrier), 50 bps-like
+    data-bit flips every 20 code periods, unit-variance complex AWGN. Returns (iq c64, truth list, carrier_hz)."""
+    chip_rate, code_len, _ = SYSTEMS[system]
+    carrier = {"gps_l1_ca": 1575.42e6, "gal_e1b": 1575.42e6, "bds_b1i": 1561.098e6, "gps_l5i": 1176.45e6}[system]
+    rng = np.random.default_rng(seed)
+    n = int(round(fs * 1e-3 * n_ms))
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * np.sqrt(0.5)
+    t = np.arange(n, dtype=np.float64)
+    truth = []
+    for k, prn in enumerate(prns):
+        fd = float(dopplers[k]) if dopplers is not None else float(rng.uniform(-4000, 4000))
+        delay = float(delays[k]) if delays is not None else float(rng.uniform(0, fs / (chip_rate / code_len)))
+        ch = chips(system, prn).astype(np.float64)
+        rate = chip_rate * (1.0 + fd / carrier)
+        phase_chips = (t - delay) * (rate / fs)          # chip phase of every sample
+        idx = np.floor(phase_chips).astype(np.int64)
+        c = ch[np.mod(idx, code_len)]
+        if system == "gal_e1b":                          # sinBOC(1,1): second half of each chip inverted
+            c = c * np.where(np.mod(phase_chips, 1.0) < 0.5, 1.0, -1.0)
+        if data_bits:
+            period = np.floor_divide(idx, code_len)
+            bits = rng.integers(0, 2, int(period.max() - period.min()) // 20 + 2) * 2 - 1
+            c = c * bits[(period - period.min()) // 20]
+        amp = np.sqrt(10.0 ** (cn0 / 10.0) / fs)
+        ph0 = float(rng.uniform(0, 2 * np.pi))
+        x = x + amp * c * np.exp(1j * (2.0 * np.pi * fd * t / fs + ph0))
+        truth.append(dict(system=system, prn=prn, doppler=fd, delay=delay, cn0=cn0, code_rate=rate))
+    return x.astype(np.complex64), truth, carrier
+
+
+def tracking_code(system, prn):
+    """d_tracking_code as start_tracking() generates it (dll_pll_veml_tracking.cc:663-700): one float per chip, or the
+    sinBOC(1,1) replica at 2 samples per chip for Galileo E1 (galileo_e1_code_gen_sinboc11_float)."""
+    ch = chips(system, prn).astype(np.float32)
+    if system in ("gal_e1b", "gal_e1c"):
+        out = np.empty(2 * ch.size, dtype=np.float32)
+        out[0::2] = ch
+        out[1::2] = -ch
+        return out
+    return ch
