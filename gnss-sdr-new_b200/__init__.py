@@ -272,7 +272,11 @@ class PcpsAcquisitionB200:
     def dwell(self, samples, slots):
         slots = _u32a(slots)
         samples = np.ascontiguousarray(samples)
-        if samples.dtype == np.int16:
+        if samples.dtype == np.int8:
+            is_cshort = 2  # GNSS_B200_SAMPLES_CBYTE
+            if samples.size < 2 * self.consumed:
+                raise B200Error("dwell: not enough cbyte samples")
+        elif samples.dtype == np.int16:
             is_cshort = 1
             if samples.size < 2 * self.consumed:
                 raise B200Error("dwell: not enough cshort samples")

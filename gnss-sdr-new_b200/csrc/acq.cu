@@ -613,7 +613,8 @@ extern "C"
         B200_REQUIRE(h && samples && slots && results, GNSS_B200_ERR_INVALID, "acq_dwell: null argument");
         std::lock_guard<std::mutex> lk(h->mu);
         B200_CUDA(cudaSetDevice(h->cfg.device));
-        const size_t bytes = (size_t)h->consumed * (is_cshort ? 4 : 8);
+        B200_REQUIRE(is_cshort >= 0 && is_cshort <= 2, GNSS_B200_ERR_INVALID, "acq_dwell: unknown sample format %d", is_cshort);
+        const size_t bytes = (size_t)h->consumed * (is_cshort == 2 ? 2 : (is_cshort == 1 ? 4 : 8));
         B200_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, bytes, cudaMemcpyHostToDevice, h->stream));
         int rc = enqueue_dwell(h, h->d_samples.p, is_cshort, n_slots, slots);
         if (rc) return rc;

@@ -57,7 +57,7 @@ struct StageArgs
     uint32_t N;
     // ---- LOAD_SAMPLES ----
     const void* samples;
-    uint32_t is_cshort;
+    uint32_t is_cshort;  // sample format: 0 gr_complex, 1 lv_16sc_t, 2 lv_8sc_t (GNSS_B200_SAMPLES_*)
     uint32_t consumed;
     const WipePiece* pieces;   // [group][nD_local][kMaxPieces]
     const uint32_t* n_pieces;  // [group][nD_local]
@@ -150,9 +150,15 @@ __global__ void __launch_bounds__(512) stage_kernel(const StageArgs a)
                     if (pos < a.consumed)
                         {
                             float2 x;
-                            if (a.is_cshort)
+                            if (a.is_cshort == 1)
                                 {
                                     const short2 q = __ldg(static_cast<const short2*>(a.samples) + pos);  // :623-626
+                                    x = make_float2((float)q.x, (float)q.y);
+                                }
+                            else if (a.is_cshort == 2)
+                                {
+                                    // cbyte items: the adapter's cbyte_to_float_x2 + float_to_complex (gps_l1_ca_pcps_acquisition.cc:76-80,191-198)
+                                    const char2 q = __ldg(static_cast<const char2*>(a.samples) + pos);
                                     x = make_float2((float)q.x, (float)q.y);
                                 }
                             else

@@ -104,6 +104,13 @@ extern "C"
         uint32_t valid;   /* 1 if this handle computed the row */
     } gnss_b200_acq_row;
 
+    enum
+    {
+        GNSS_B200_SAMPLES_GR_COMPLEX = 0,
+        GNSS_B200_SAMPLES_CSHORT = 1,
+        GNSS_B200_SAMPLES_CBYTE = 2
+    };
+
     typedef struct gnss_b200_acq gnss_b200_acq;
 
     GNSS_B200_API int gnss_b200_acq_create(const gnss_b200_acq_cfg* cfg, gnss_b200_acq** out);
@@ -124,7 +131,9 @@ extern "C"
     GNSS_B200_API int gnss_b200_acq_reset(gnss_b200_acq* h, uint32_t slot);
 
     /* One coherent dwell (one acquisition_core pass, :615-713) for a batch of slots on ONE sample block.
-       samples: consumed_samples items, gr_complex (is_cshort = 0) or lv_16sc_t (is_cshort = 1, :623-626).
+       samples: consumed_samples items, gr_complex (is_cshort = 0) or lv_16sc_t (is_cshort = 1, :623-626); is_cshort = 2
+       (GNSS_B200_SAMPLES_CBYTE) takes interleaved int8 "cbyte" items straight from the signal conditioner and
+       does the adapter's cbyte -> gr_complex conversion (gps_l1_ca_pcps_acquisition.cc:76-80,191-198) on the device.
        results[i] belongs to slots[i]. */
     GNSS_B200_API int gnss_b200_acq_dwell(gnss_b200_acq* h, const void* samples, int is_cshort,
         uint32_t n_slots, const uint32_t* slots, gnss_b200_acq_result* results);

@@ -197,6 +197,26 @@ def test_cshort_input_and_doppler_center(b200, oracle):
         _compare(got[p], want[p][0], strict_idx=(p == 0))
 
 
+def test_cbyte_input(b200, oracle):
+    """interleaved int8 items (the adapters' `cbyte` item type, gps_l1_ca_pcps_acquisition.cc:76-80,191-198)
+    converted on the device: identical to handing the block the converted gr_complex stream."""
+    geo, codes, iq, truth = synth.config_scene("C1", n_prn=4)
+    q = np.empty(2 * iq.size, dtype=np.int8)
+    q[0::2] = np.clip(np.rint(iq.real * 24.0), -128, 127)
+    q[1::2] = np.clip(np.rint(iq.imag * 24.0), -128, 127)
+    as_complex = (q[0::2].astype(np.float32) + 1j * q[1::2].astype(np.float32)).astype(np.complex64)
+    e = _gpu_engine(b200, geo, 4, use_cfar=True)
+    e.set_local_codes(np.arange(4), codes)
+    got = e.dwell(q, np.arange(4))
+    same = e.dwell(as_complex, np.arange(4))
+    assert got.tobytes() == same.tobytes()
+    want, _ = _oracle_search(oracle, geo, codes, [as_complex])
+    for p in range(4):
+        _compare(got[p], want[p][0], strict_idx=(p in (0, 2)))
+    with pytest.raises(b200.B200Error):
+        b200._check(e.L.gnss_b200_acq_dwell(e.h, q.ctypes.data, 3, 1, np.zeros(1, np.uint32).ctypes.data_as(b200._u32p), got.ctypes.data))
+
+
 def test_row_sharding_merge(b200, oracle):
     """Doppler rows of one PRN split over two handles (two GPUs in production), merged with finalize_rows."""
     geo, codes, iq, _ = synth.config_scene("C1", n_prn=2)

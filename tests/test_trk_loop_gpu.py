@@ -134,3 +134,36 @@ def test_loss_of_lock_and_errors(b200, oracle, oracle_mod):
     with pytest.raises(b200.B200Error):
         b200.TrackingLoopB200(b200.trk_config(fs, 1.023e6, 1023, 1575.42e6, 1, pll_filter_order=1))
     trk.close()
+
+
+def test_acquisition_hands_over_to_tracking(b200):
+    """SURVEY 8.6 N3 (hand-off part): the acquisition records seed the tracking channels the way the reference's channel FSM does
+    (Gnss_Synchro::Acq_delay_samples / Acq_doppler_hz / Acq_samplestamp_samples -> start_tracking, dll_pll_veml_tracking.cc:640-660):
+    search the first millisecond of a stream, start one loop per detected satellite, and every loop locks onto its satellite."""
+    fs = 4e6
+    prns = [2, 9, 17, 26]
+    iq, truth, carrier = synth.tracking_stream("gps_l1_ca", prns, fs, 300, seed=77, cn0=47.0, dopplers=[2210.0, -3340.0, 120.0, 4480.0])
+    geo = b200.acq_geometry(fs, 1.023e6, 1, 1)
+    acq = b200.PcpsAcquisitionB200(geo["fft_size"], geo["consumed_samples"], 5000, 250, fs, geo["samples_per_chip"], 32, use_cfar=True)
+    codes = np.stack([synth.adapter_code("gps_l1_ca", p, int(fs), 1) for p in range(1, 33)])
+    acq.set_local_codes(np.arange(32), codes)
+    stamp = 8000                                           # samp_count of the dwell (pcps_acquisition.cc:760-771)
+    res = acq.dwell(iq[stamp:stamp + 4000], np.arange(32))
+    thr = b200.acq_threshold(0.001, acq.eff, acq.n_doppler)
+    found = [p for p in range(32) if res[p]["test_statistic"] > thr]
+    assert sorted(p + 1 for p in found) == prns
+    cfg = b200.trk_config(fs, 1.023e6, 1023, carrier, len(found), enable_fll_pull_in=1, pull_in_time_s=0)
+    trk = b200.TrackingLoopB200(cfg)
+    for c, p in enumerate(found):
+        trk.set_code(c, synth.tracking_code("gps_l1_ca", p + 1))
+        delay = float(np.fmod(np.float32(res[p]["code_phase"]), np.float32(geo["samples_per_code"])))   # Acq_delay_samples (:760)
+        trk.start(c, delay, float(res[p]["doppler_hz"]), stamp, stamp + 4000)
+    rec = trk.run(iq, 0, np.arange(len(found)), 290)
+    for c, p in enumerate(found):
+        t = truth[prns.index(p + 1)]
+        ok = rec[:, c][rec[:, c]["flags"] & 1 == 1]
+        assert ok.size > 280 and not (ok["flags"] & 4).any()
+        assert abs(ok[-50:]["carrier_doppler_hz"].mean() - t["doppler"]) < 3.0
+        assert abs(ok[-50:]["cn0_db_hz"].mean() - 47.0) < 3.0
+    trk.close()
+    acq.close()
