@@ -1,6 +1,6 @@
 // Host side of the PCPS acquisition engine: handle, buffers, launch sequencing, C-ABI.
 // Reference for every entry point: include/gnss_b200.h.
-#include "acq_fast.cuh"
+#include "acq_fast_fwd.cuh"
 #include "acq_kernels.cuh"
 #include "wipeoff_pieces.h"
 #include <algorithm>
@@ -249,6 +249,52 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     B200_CUDA(h->d_bestk.reserve(sizeof(uint32_t) * n_slots));
 
     // ---- forward: one transform per (Doppler group, bin) ----
+    static const bool fwd_generic = [] {
+        const char* e = std::getenv("B200_ACQ_FWD_GENERIC");  // tuning aid: the generic multi-pass forward stages
+        return e && e[0] == '1';
+    }();
+    if (h->plan.fast && !fwd_generic)
+        {
+            const FftPlan& pl = h->plan;
+            FastFwdArgs fa;
+            std::memset(&fa, 0, sizeof(fa));
+            fa.W = h->d_W.as<float2>();
+            fa.N = h->N;
+            fa.M_lo = pl.ra_lo * pl.rb_lo;
+            fa.M_hi = pl.ra_hi * pl.rb_hi;
+            fa.ra_lo = pl.ra_lo;
+            fa.rb_lo = pl.rb_lo;
+            fa.ra_hi = pl.ra_hi;
+            fa.rb_hi = pl.rb_hi;
+            fa.samples = d_samples;
+            fa.fmt = (uint32_t)is_cshort;
+            fa.consumed = h->consumed;
+            fa.pieces = h->d_pieces.as<WipePiece>();
+            fa.n_pieces = h->d_npieces.as<uint32_t>();
+            fa.group_piece_base = d_gpb;
+            fa.nD_local = h->nD_local;
+            fa.scratch = h->d_xtmp.as<float2>();
+            fa.X = h->d_xbuf.as<float2>();
+            fa.nb = pl.stage[1].blocks;
+            fa.C = pl.stage[0].C;
+            const uint32_t pitch = (pl.ra_lo % 2 == 0) ? pl.ra_lo + 1 : pl.ra_lo;
+            const size_t smem_lo = ((size_t)fa.nb * pitch * pl.rb_lo + fa.M_lo) * sizeof(float2);
+            const size_t smem_hi = ((size_t)fa.M_hi * fa.C + fa.M_hi) * sizeof(float2);
+            const dim3 block_hi(fa.C, std::max(1u, (uint32_t)kFastThreads / fa.C));
+            const uint32_t pen = fa.nb * std::max(pl.ra_lo, pl.rb_lo);
+            const uint32_t threads_lo = std::max<uint32_t>(64, std::min<uint32_t>(kFastThreads, (pen + 31) / 32 * 32));
+            h->prof.begin(CAT_FWD, h->stream);
+            cudaError_t e = launch_fwd_upper(pl.ra_hi, pl.rb_hi, dim3(n_fwd, fa.M_lo / fa.C), block_hi, smem_hi, h->stream, fa);
+            h->prof.end(h->stream);
+            h->launches++;
+            B200_CUDA(e);
+            h->prof.begin(CAT_FWD, h->stream);
+            e = launch_fwd_lower(pl.ra_lo, pl.rb_lo, dim3(n_fwd, fa.M_hi / fa.nb), threads_lo, smem_lo, h->stream, fa);
+            h->prof.end(h->stream);
+            h->launches++;
+            B200_CUDA(e);
+        }
+    else
     {
         StageArgs a = base_args(h, 0);
         a.samples = d_samples;
