@@ -250,3 +250,61 @@ def test_unsupported_and_state_errors(b200):
         e.read_grid(0)  # keep_grid = 0
     with pytest.raises(b200.B200Error):
         e.set_local_codes([7], np.zeros((1, 4000), np.complex64))  # slot out of range
+
+
+@pytest.mark.parametrize("name,min_cn0", [("C4_gps", 47.0), ("C4_gal", 41.0), ("C4_bds", 47.0)])
+def test_full_size_config4_properties(b200, name, min_cn0):
+    """BASELINE config 4 at full size (25 MS/s; N = 25 000 / 100 000; 32 / 36 / 63 PRNs x 40 bins), where the oracle would take
+    minutes: size-independent properties instead. (1) every strong injected satellite is found at its injected cell and nothing
+    else crosses the threshold; (2) homogeneity: samples x 2 gives peak x 4 exactly (power-of-two scaling commutes with every
+    binary32 operation of the pipeline), identical cells and an identical statistic."""
+    geo, codes, iq, truth = synth.config_scene(name)
+    n = geo["n_prn"]
+    e = _gpu_engine(b200, geo, n, use_cfar=True)
+    e.set_local_codes(np.arange(n), codes)
+    r1 = e.dwell(iq, np.arange(n))
+    thr = b200.acq_threshold(0.001, e.eff, e.n_doppler)
+    one = int(round(geo["samples_per_code"]))
+    present = {t["prn"] for t in truth}
+    for t in truth:
+        if t["cn0"] >= min_cn0:
+            r = r1[t["prn"] - 1]
+            assert r["test_statistic"] > thr
+            assert abs(int(r["code_phase"]) % one - t["delay"]) <= 1 and abs(r["doppler_hz"] - t["doppler"]) <= geo["doppler_step"]
+    assert not ({p + 1 for p in range(n) if r1[p]["test_statistic"] > thr} - present)
+    r2 = e.dwell((iq * np.float32(2.0)).astype(np.complex64), np.arange(n))
+    assert np.array_equal(r2["code_phase"], r1["code_phase"]) and np.array_equal(r2["doppler_index"], r1["doppler_index"])
+    assert np.array_equal(r2["peak"], r1["peak"] * np.float32(4.0))
+    assert np.array_equal(r2["test_statistic"], r1["test_statistic"])
+    e.close()
+
+
+def test_full_size_config3_properties(b200):
+    """BASELINE config 3 geometry at full row size (N = 160 000, 800 bins, persistent grid), 2 PRNs: (1) searching the SAME block
+    twice doubles every grid cell exactly (x + x in binary32), so the peak doubles, the cell stays, and the CFAR statistic
+    doubles too (the noise row is divided by the dwell count, pcps_acquisition.cc:533-536); (2) reset() returns to the one-dwell result bit for bit; (3) the weak satellite comes out after the 10 dwells."""
+    geo, codes, iq, truth = synth.config_scene("C3", n_prn=4, n_dwells=10)
+    e = _gpu_engine(b200, geo, 2, use_cfar=True, keep_grid=True)
+    sel = np.array([3, 0])                       # PRN 4 (present, weak) and PRN 1 (absent)
+    e.set_local_codes([0, 1], codes[sel])
+    a = e.dwell(iq[0], [0, 1])
+    b2 = e.dwell(iq[0], [0, 1])
+    assert np.array_equal(b2["peak"], a["peak"] * np.float32(2.0))
+    assert np.array_equal(b2["code_phase"], a["code_phase"]) and np.array_equal(b2["doppler_index"], a["doppler_index"])
+    assert np.allclose(b2["test_statistic"], 2.0 * a["test_statistic"], rtol=1e-6) and list(b2["dwell_count"]) == [2, 2]
+    assert np.array_equal(b2["input_power"], a["input_power"])
+    for s in (0, 1):
+        e.reset(s)
+    c = e.dwell(iq[0], [0, 1])
+    assert c.tobytes() == a.tobytes()
+    for k in range(1, 10):
+        c = e.dwell(iq[k], [0, 1])
+    thr = b200.acq_threshold(0.001, e.eff, e.n_doppler, max_dwells=10)
+    t = truth[0]
+    # (the absent PRN is not required to stay below the pfa threshold: with the zero-padded 2N transform the noise variance of a
+    # code phase grows with its overlap, while the reference normalises by the row AVERAGE (:533-536), so noise peaks read ~2x high)
+    assert t["prn"] == 4 and c[0]["test_statistic"] > thr and c[0]["test_statistic"] > 2.0 * c[1]["test_statistic"]
+    assert abs(int(c[0]["code_phase"]) % 4000 - t["delay"]) <= 1 and abs(c[0]["doppler_hz"] - t["doppler"]) <= 25
+    g = e.read_grid(0)
+    assert g.shape == (800, 160000) and float(g.max()) == float(c[0]["peak"])
+    e.close()
