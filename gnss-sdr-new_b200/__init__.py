@@ -122,6 +122,7 @@ EXPORTS = [
     "gnss_b200_mc_correlate_device_async", "gnss_b200_mc_sync", "gnss_b200_mc_chip_indices", "gnss_b200_mc_stream",
     "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan",
     "gnss_b200_acq_profile", "gnss_b200_mc_profile", "gnss_b200_debug_fp32_peak",
+    "gnss_b200_acq_create_step2", "gnss_b200_acq_set_step2_center",
     "gnss_b200_trk_create", "gnss_b200_trk_destroy", "gnss_b200_trk_set_code", "gnss_b200_trk_start", "gnss_b200_trk_run",
     "gnss_b200_trk_stream", "gnss_b200_trk_launch_count",
 ]
@@ -142,6 +143,8 @@ def lib():
     L.gnss_b200_version.restype = C.c_char_p
     L.gnss_b200_acq_create.argtypes = [C.POINTER(AcqCfg), C.POINTER(C.c_void_p)]
     L.gnss_b200_acq_destroy.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_create_step2.argtypes = [C.POINTER(AcqCfg), c_u32, C.c_float, C.POINTER(C.c_void_p)]
+    L.gnss_b200_acq_set_step2_center.argtypes = [C.c_void_p, c_u32, C.c_float, C.c_float]
     L.gnss_b200_acq_num_doppler_bins.argtypes = [C.c_void_p]
     L.gnss_b200_acq_num_doppler_bins.restype = c_u32
     L.gnss_b200_acq_set_local_code.argtypes = [C.c_void_p, c_u32, _fp]
@@ -228,13 +231,17 @@ class PcpsAcquisitionB200:
     """
 
     def __init__(self, fft_size, consumed_samples, doppler_max, doppler_step, fs, samples_per_chip, max_slots,
-                 use_cfar=True, bit_transition=False, keep_grid=False, device=0, row_begin=0, row_end=0):
+                 use_cfar=True, bit_transition=False, keep_grid=False, device=0, row_begin=0, row_end=0, step2=None):
+        """step2 = (num_doppler_bins_step2, doppler_step2): the narrow second-search handle of make_two_steps."""
         self.L = lib()
         self.cfg = AcqCfg(fft_size, consumed_samples, int(bit_transition), int(doppler_max), int(doppler_step), float(fs),
                           int(samples_per_chip), int(use_cfar), int(keep_grid), int(max_slots), int(device),
                           int(row_begin), int(row_end))
         self.h = C.c_void_p()
-        _check(self.L.gnss_b200_acq_create(C.byref(self.cfg), C.byref(self.h)))
+        if step2 is None:
+            _check(self.L.gnss_b200_acq_create(C.byref(self.cfg), C.byref(self.h)))
+        else:
+            _check(self.L.gnss_b200_acq_create_step2(C.byref(self.cfg), int(step2[0]), float(step2[1]), C.byref(self.h)))
         self.fft_size = fft_size
         self.consumed = consumed_samples
         self.eff = fft_size // 2 if bit_transition else fft_size
@@ -265,6 +272,9 @@ class PcpsAcquisitionB200:
 
     def set_doppler_center(self, slot, center_hz, bias_hz=0):
         _check(self.L.gnss_b200_acq_set_doppler_center(self.h, slot, int(center_hz), int(bias_hz)))
+
+    def set_step2_center(self, slot, doppler_center_step_two_hz, input_power_step_one):
+        _check(self.L.gnss_b200_acq_set_step2_center(self.h, slot, float(doppler_center_step_two_hz), float(input_power_step_one)))
 
     def reset(self, slot):
         _check(self.L.gnss_b200_acq_reset(self.h, slot))

@@ -27,7 +27,8 @@ enum
 struct CallMeta  // uploaded once per dwell call
 {
     std::vector<uint32_t> slots, slot_group, dwell_after, group_piece_base;
-    std::vector<int32_t> center;
+    std::vector<int32_t> center;  // step-two handles: the bits of the float centre
+    std::vector<float> input_power1;
 };
 }  // namespace
 
@@ -52,6 +53,11 @@ struct gnss_b200_acq
     PinBuf h_results, h_samples;
 
     std::vector<int32_t> center, bias;
+    // make_two_steps handles (gnss_b200_acq_create_step2): nD = num_doppler_bins_step2 bins spaced step2_step around each
+    // slot's own float centre; the CFAR statistic divides by the input power the first step left behind
+    bool step2 = false;
+    float step2_step = 0.f;
+    std::vector<float> center_f, input_power1;
     std::vector<uint8_t> has_code;
     std::vector<uint32_t> dwell;
     uint32_t last_n_slots = 0;
@@ -164,8 +170,21 @@ int ensure_group(gnss_b200_acq* h, int64_t key, uint32_t* ordinal)
     for (uint32_t kk = 0; kk < h->nD_local; kk++)
         {
             const uint32_t k = h->row_begin + kk;
-            const int32_t doppler = -h->cfg.doppler_max + (int32_t)(h->cfg.doppler_step * k);  // + center + bias = key
-            const float inc = wipeoff_phase_inc((int32_t)(key + doppler), h->cfg.fs);
+            float inc;
+            if (h->step2)
+                {
+                    // update_grid_doppler_wipeoffs_step2 (:308-315): key carries the bits of d_doppler_center_step_two
+                    const uint32_t bits = (uint32_t)(key & 0xffffffffll);
+                    float centre;
+                    std::memcpy(&centre, &bits, 4);
+                    const float doppler = (static_cast<float>(k) - static_cast<float>(std::floor(h->nD / 2.0))) * h->step2_step;
+                    inc = wipeoff_phase_inc_f(centre + doppler, h->cfg.fs);
+                }
+            else
+                {
+                    const int32_t doppler = -h->cfg.doppler_max + (int32_t)(h->cfg.doppler_step * k);  // + center + bias = key
+                    inc = wipeoff_phase_inc((int32_t)(key + doppler), h->cfg.fs);
+                }
             build_wipeoff_pieces(inc, h->N, &pc);
             B200_REQUIRE(pc.size() <= (size_t)kMaxPieces, GNSS_B200_ERR_UNSUPPORTED, "carrier phase table needs %zu pieces (> %d)", pc.size(), kMaxPieces);
             cnt[kk] = (uint32_t)pc.size();
@@ -192,14 +211,23 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
             const uint32_t s = slots[i];
             B200_REQUIRE(s < h->cfg.max_slots, GNSS_B200_ERR_INVALID, "dwell: slot %u out of range", s);
             B200_REQUIRE(h->has_code[s], GNSS_B200_ERR_STATE, "dwell: slot %u has no local code (call gnss_b200_acq_set_local_code)", s);
-            const int64_t key = (int64_t)h->center[s] + (int64_t)h->bias[s];
+            int64_t key = (int64_t)h->center[s] + (int64_t)h->bias[s];
+            int32_t centre_word = h->center[s];
+            if (h->step2)
+                {
+                    uint32_t bits;
+                    std::memcpy(&bits, &h->center_f[s], 4);
+                    key = (int64_t)bits | (1ll << 40);
+                    centre_word = (int32_t)bits;
+                }
             uint32_t g = 0;
             for (; g < call_keys.size(); g++)
                 if (call_keys[g] == key) break;
             if (g == call_keys.size()) call_keys.push_back(key);
             m.slots.push_back(s);
             m.slot_group.push_back(g);
-            m.center.push_back(h->center[s]);
+            m.center.push_back(centre_word);
+            m.input_power1.push_back(h->step2 ? h->input_power1[s] : 0.f);
         }
     B200_REQUIRE(call_keys.size() <= kMaxCachedGroups, GNSS_B200_ERR_UNSUPPORTED, "dwell: more than %u distinct Doppler centres in one call", kMaxCachedGroups);
     for (int64_t key : call_keys)
@@ -222,7 +250,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
         }
     const uint32_t n_groups = (uint32_t)call_keys.size();
 
-    const size_t meta_words = (size_t)n_slots * 4 + n_groups;
+    const size_t meta_words = (size_t)n_slots * 5 + n_groups;
     B200_CUDA(h->h_meta.reserve(meta_words * 4));
     B200_CUDA(h->d_meta.reserve(meta_words * 4));
     uint32_t* hm = h->h_meta.as<uint32_t>();
@@ -230,13 +258,15 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     std::memcpy(hm + n_slots, m.slot_group.data(), n_slots * 4);
     std::memcpy(hm + 2 * n_slots, m.dwell_after.data(), n_slots * 4);
     std::memcpy(hm + 3 * n_slots, m.center.data(), n_slots * 4);
-    std::memcpy(hm + 4 * n_slots, m.group_piece_base.data(), n_groups * 4);
+    std::memcpy(hm + 4 * n_slots, m.input_power1.data(), n_slots * 4);
+    std::memcpy(hm + 5 * n_slots, m.group_piece_base.data(), n_groups * 4);
     B200_CUDA(cudaMemcpyAsync(h->d_meta.p, hm, meta_words * 4, cudaMemcpyHostToDevice, h->stream));
     const uint32_t* d_slots = h->d_meta.as<uint32_t>();
     const uint32_t* d_slot_group = d_slots + n_slots;
     const uint32_t* d_dwell = d_slots + 2 * n_slots;
     const int32_t* d_center = reinterpret_cast<const int32_t*>(d_slots + 3 * n_slots);
-    const uint32_t* d_gpb = d_slots + 4 * n_slots;
+    const float* d_ip1 = reinterpret_cast<const float*>(d_slots + 4 * n_slots);
+    const uint32_t* d_gpb = d_slots + 5 * n_slots;
 
     const uint32_t n_fwd = n_groups * h->nD_local;
     const uint32_t n_rows = n_slots * h->nD_local;
@@ -458,6 +488,9 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     f.use_cfar = h->cfg.use_cfar;
     f.slots = d_slots;
     f.center = d_center;
+    f.step2 = h->step2 ? 1u : 0u;
+    f.step2_step = h->step2_step;
+    f.input_power1 = d_ip1;
     f.dwell_after = d_dwell;
     f.rows = h->d_rows.as<gnss_b200_acq_row>();
     f.results = h->d_results.as<gnss_b200_acq_result>();
@@ -505,9 +538,38 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
 }
 }  // namespace
 
+namespace
+{
+int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, gnss_b200_acq** out);
+}
+
 extern "C"
 {
-    int gnss_b200_acq_create(const gnss_b200_acq_cfg* cfg, gnss_b200_acq** out)
+    int gnss_b200_acq_create(const gnss_b200_acq_cfg* cfg, gnss_b200_acq** out) { return create_impl(cfg, 0, 0.f, out); }
+
+    int gnss_b200_acq_create_step2(const gnss_b200_acq_cfg* cfg, uint32_t num_doppler_bins_step2, float doppler_step2, gnss_b200_acq** out)
+    {
+        B200_REQUIRE(num_doppler_bins_step2 >= 1 && num_doppler_bins_step2 <= 4096 && doppler_step2 > 0.f, GNSS_B200_ERR_INVALID,
+            "acq_create_step2: second_nbins=%u second_doppler_step=%g", num_doppler_bins_step2, (double)doppler_step2);
+        B200_REQUIRE(cfg && !(cfg->row_end > cfg->row_begin), GNSS_B200_ERR_INVALID, "acq_create_step2: the narrow grid is not row-sharded");
+        return create_impl(cfg, num_doppler_bins_step2, doppler_step2, out);
+    }
+
+    int gnss_b200_acq_set_step2_center(gnss_b200_acq* h, uint32_t slot, float doppler_center_step_two_hz, float input_power_step_one)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_set_step2_center: null handle");
+        B200_REQUIRE(h->step2, GNSS_B200_ERR_STATE, "acq_set_step2_center: not a second-step handle (gnss_b200_acq_create_step2)");
+        B200_REQUIRE(slot < h->cfg.max_slots, GNSS_B200_ERR_INVALID, "acq_set_step2_center: slot %u out of range", slot);
+        std::lock_guard<std::mutex> lk(h->mu);
+        h->center_f[slot] = doppler_center_step_two_hz;
+        h->input_power1[slot] = input_power_step_one;
+        return GNSS_B200_OK;
+    }
+}
+
+namespace
+{
+int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, gnss_b200_acq** out)
     {
         B200_REQUIRE(cfg && out, GNSS_B200_ERR_INVALID, "acq_create: null argument");
         B200_REQUIRE(cfg->fft_size >= 2 && cfg->consumed_samples >= 1 && cfg->consumed_samples <= cfg->fft_size, GNSS_B200_ERR_INVALID,
@@ -523,6 +585,14 @@ extern "C"
         h->eff = cfg->bit_transition ? h->N / 2 : h->N;                                   // :622
         h->mag_offset = cfg->bit_transition ? h->eff : 0;                                 // :671
         h->nD = (uint32_t)std::ceil((double)(cfg->doppler_max - (-cfg->doppler_max)) / (double)cfg->doppler_step);  // :264
+        if (n_step2)
+            {
+                h->step2 = true;  // d_num_doppler_bins_step2 bins of doppler_step2 (:73, acq_conf.h:51,62)
+                h->step2_step = step2_hz;
+                h->nD = n_step2;
+            }
+        h->center_f.assign(cfg->max_slots, 0.f);
+        h->input_power1.assign(cfg->max_slots, 0.f);
         h->row_begin = 0;
         h->nD_local = h->nD;
         if (cfg->row_end > cfg->row_begin)
@@ -583,7 +653,10 @@ extern "C"
         *out = h;
         return GNSS_B200_OK;
     }
+}  // namespace
 
+extern "C"
+{
     int gnss_b200_acq_destroy(gnss_b200_acq* h)
     {
         if (!h) return GNSS_B200_OK;

@@ -311,7 +311,10 @@ struct FinalizeArgs
     uint32_t doppler_step;
     uint32_t use_cfar;
     const uint32_t* slots;
-    const int32_t* center;       // [n_slots in call]
+    const int32_t* center;       // [n_slots in call]; second-step handles: bits of the float centre
+    uint32_t step2;              // make_two_steps narrow grid (:308-315,:531-540)
+    float step2_step;
+    const float* input_power1;   // [n_slots in call] d_input_power left by the first step
     const uint32_t* dwell_after; // [n_slots in call]
     gnss_b200_acq_row* rows;     // [slot][nD]
     gnss_b200_acq_result* results;  // [n_slots in call]
@@ -391,7 +394,16 @@ static __global__ void finalize_kernel(const FinalizeArgs a)
             res.second_peak = 0.f;
             res.input_power = 0.f;
             res.test_statistic = 0.f;
-            if (a.use_cfar)
+            if (a.step2)
+                {
+                    // :539: static_cast<int32_t>(centre + (float(k) - float(floor(n2 / 2.0))) * doppler_step2); d_input_power is not refreshed
+                    const float centre = __int_as_float(a.center[si]);
+                    const float off = __fmul_rn(__fsub_rn((float)best_k, (float)(a.nD / 2)), a.step2_step);
+                    res.doppler_hz = (int32_t)__fadd_rn(centre, off);
+                    res.input_power = a.input_power1[si];
+                    if (a.use_cfar) res.test_statistic = best / res.input_power;  // :542
+                }
+            else if (a.use_cfar)
                 {
                     const uint32_t opp = (best_k + a.nD / 2) % a.nD;  // :533
                     const gnss_b200_acq_row ro = rows[opp];

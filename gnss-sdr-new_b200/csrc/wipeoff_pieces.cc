@@ -21,6 +21,13 @@ float wipeoff_phase_inc(int32_t doppler_hz_with_bias, double fs)
     return -phase_step_rad;
 }
 
+float wipeoff_phase_inc_f(float freq_hz, double fs)
+{
+    // update_local_carrier with the float frequency of the second-step grid (pcps_acquisition.cc:233-246,308-315)
+    const float phase_step_rad = static_cast<float>(6.283185307179586) * freq_hz / static_cast<float>(fs);
+    return -phase_step_rad;
+}
+
 void build_wipeoff_pieces(float inc, uint32_t N, std::vector<WipePieceHost>* out)
 {
     out->clear();

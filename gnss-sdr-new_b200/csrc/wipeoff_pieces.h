@@ -23,4 +23,6 @@ void build_wipeoff_pieces(float phase_inc, uint32_t n_samples, std::vector<WipeP
 
 // phase_inc for one Doppler bin exactly as the reference computes it (pcps_acquisition.cc:238-245,:302-303)
 float wipeoff_phase_inc(int32_t doppler_hz_with_bias, double fs);
+// the same for the float frequencies of the second-step grid (make_two_steps, :308-315)
+float wipeoff_phase_inc_f(float freq_hz, double fs);
 }  // namespace b200

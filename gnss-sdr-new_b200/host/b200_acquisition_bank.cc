@@ -21,7 +21,7 @@ bool B200_Acquisition_Bank::Geometry::operator==(const Geometry& o) const
 {
     return fft_size == o.fft_size && consumed_samples == o.consumed_samples && doppler_max == o.doppler_max && doppler_step == o.doppler_step &&
            fs == o.fs && samples_per_chip == o.samples_per_chip && bit_transition == o.bit_transition && use_cfar == o.use_cfar &&
-           keep_grid == o.keep_grid && device == o.device;
+           keep_grid == o.keep_grid && device == o.device && step2_bins == o.step2_bins && step2_hz == o.step2_hz;
 }
 
 
@@ -69,8 +69,16 @@ std::shared_ptr<B200_Acquisition_Bank> B200_Acquisition_Bank::get(const Geometry
             if (why != nullptr) *why = gnss_b200_last_error();
             return nullptr;
         }
+    gnss_b200_acq* engine2 = nullptr;
+    if (g.step2_bins != 0 && gnss_b200_acq_create_step2(&cfg, g.step2_bins, g.step2_hz, &engine2) != GNSS_B200_OK)
+        {
+            if (why != nullptr) *why = gnss_b200_last_error();
+            gnss_b200_acq_destroy(engine);
+            return nullptr;
+        }
     std::shared_ptr<B200_Acquisition_Bank> bank(new B200_Acquisition_Bank(g));
     bank->d_engine = engine;
+    bank->d_engine2 = engine2;
     bank->d_num_doppler_bins = gnss_b200_acq_num_doppler_bins(engine);
     bank->d_used.assign(g_capacity, 0);
     g_registry.emplace_back(bank);
@@ -82,6 +90,7 @@ std::shared_ptr<B200_Acquisition_Bank> B200_Acquisition_Bank::get(const Geometry
 B200_Acquisition_Bank::~B200_Acquisition_Bank()
 {
     if (d_engine != nullptr) gnss_b200_acq_destroy(d_engine);
+    if (d_engine2 != nullptr) gnss_b200_acq_destroy(d_engine2);
 }
 
 
@@ -111,7 +120,11 @@ void B200_Acquisition_Bank::release_slot(int slot)
 bool B200_Acquisition_Bank::set_local_code(int slot, const std::complex<float>* code)
 {
     if (slot < 0 || code == nullptr) return false;
-    const int rc = gnss_b200_acq_set_local_code(d_engine, static_cast<uint32_t>(slot), reinterpret_cast<const float*>(code));
+    int rc = gnss_b200_acq_set_local_code(d_engine, static_cast<uint32_t>(slot), reinterpret_cast<const float*>(code));
+    if (rc == GNSS_B200_OK && d_engine2 != nullptr)  // d_fft_codes serves both grids in the reference (:727, :723 of the step-two loop)
+        {
+            rc = gnss_b200_acq_set_local_code(d_engine2, static_cast<uint32_t>(slot), reinterpret_cast<const float*>(code));
+        }
     if (rc != GNSS_B200_OK)
         {
             std::lock_guard<std::mutex> lk(d_mu);
@@ -131,7 +144,8 @@ bool B200_Acquisition_Bank::set_doppler_center(int slot, int32_t center_hz, int3
 bool B200_Acquisition_Bank::reset(int slot)
 {
     if (slot < 0) return false;
-    return gnss_b200_acq_reset(d_engine, static_cast<uint32_t>(slot)) == GNSS_B200_OK;
+    const bool ok2 = d_engine2 == nullptr || gnss_b200_acq_reset(d_engine2, static_cast<uint32_t>(slot)) == GNSS_B200_OK;
+    return gnss_b200_acq_reset(d_engine, static_cast<uint32_t>(slot)) == GNSS_B200_OK && ok2;
 }
 
 
@@ -142,7 +156,7 @@ bool B200_Acquisition_Bank::read_grid(int slot, float* out)
 }
 
 
-// Leader with d_mu held: issue one engine call per distinct (sample stamp, item type) among the pending dwells.
+// Leader with d_mu held: issue one engine call per distinct (sample stamp, item type, step) among the pending dwells.
 void B200_Acquisition_Bank::drain_locked(std::unique_lock<std::mutex>& lk)
 {
     while (!d_pending.empty())
@@ -150,9 +164,11 @@ void B200_Acquisition_Bank::drain_locked(std::unique_lock<std::mutex>& lk)
             std::vector<Request*> group;
             const uint64_t stamp = d_pending.front()->stamp;
             const bool is_cshort = d_pending.front()->is_cshort;
+            const bool step2 = d_pending.front()->step2;
             for (auto it = d_pending.begin(); it != d_pending.end();)
                 {
-                    if ((*it)->stamp == stamp && (*it)->is_cshort == is_cshort)
+                    // a second-step call holds at most 64 distinct Doppler centres (include/gnss_b200.h)
+                    if ((*it)->stamp == stamp && (*it)->is_cshort == is_cshort && (*it)->step2 == step2 && (!step2 || group.size() < 64))
                         {
                             group.push_back(*it);
                             it = d_pending.erase(it);
@@ -171,7 +187,18 @@ void B200_Acquisition_Bank::drain_locked(std::unique_lock<std::mutex>& lk)
             std::vector<uint32_t> slots(n);
             std::vector<gnss_b200_acq_result> results(n);
             for (uint32_t i = 0; i < n; i++) slots[i] = group[i]->slot;
-            const int rc = gnss_b200_acq_dwell(d_engine, group[0]->samples, is_cshort ? 1 : 0, n, slots.data(), results.data());
+            int rc = GNSS_B200_OK;
+            if (step2)
+                {
+                    for (uint32_t i = 0; i < n && rc == GNSS_B200_OK; i++)
+                        {
+                            rc = d_engine2 == nullptr ? GNSS_B200_ERR_STATE : gnss_b200_acq_set_step2_center(d_engine2, slots[i], group[i]->center2, group[i]->input_power1);
+                        }
+                }
+            if (rc == GNSS_B200_OK)
+                {
+                    rc = gnss_b200_acq_dwell(step2 ? d_engine2 : d_engine, group[0]->samples, is_cshort ? 1 : 0, n, slots.data(), results.data());
+                }
 
             lk.lock();
             if (rc != GNSS_B200_OK) d_error = gnss_b200_last_error();
@@ -189,6 +216,41 @@ void B200_Acquisition_Bank::drain_locked(std::unique_lock<std::mutex>& lk)
 bool B200_Acquisition_Bank::dwell(int slot, const void* samples, bool is_cshort, uint64_t sample_stamp, gnss_b200_acq_result* result)
 {
     if (slot < 0 || samples == nullptr || result == nullptr) return false;
+    Request req;
+    req.slot = static_cast<uint32_t>(slot);
+    req.samples = samples;
+    req.is_cshort = is_cshort;
+    req.stamp = sample_stamp;
+    req.result = result;
+    return submit(req);
+}
+
+
+bool B200_Acquisition_Bank::dwell_step2(int slot, const void* samples, bool is_cshort, uint64_t sample_stamp, float doppler_center_step_two,
+    float input_power_step_one, gnss_b200_acq_result* result)
+{
+    if (slot < 0 || samples == nullptr || result == nullptr) return false;
+    if (d_engine2 == nullptr)
+        {
+            std::lock_guard<std::mutex> lk(d_mu);
+            d_error = "B200_Acquisition_Bank: this bank was created without a second-step grid";
+            return false;
+        }
+    Request req;
+    req.slot = static_cast<uint32_t>(slot);
+    req.samples = samples;
+    req.is_cshort = is_cshort;
+    req.stamp = sample_stamp;
+    req.result = result;
+    req.step2 = true;
+    req.center2 = doppler_center_step_two;
+    req.input_power1 = input_power_step_one;
+    return submit(req);
+}
+
+
+bool B200_Acquisition_Bank::submit(Request& req)
+{
     uint32_t window_us;
     uint32_t expected;
     {
@@ -196,13 +258,6 @@ bool B200_Acquisition_Bank::dwell(int slot, const void* samples, bool is_cshort,
         window_us = g_window_us;
         expected = g_expected;
     }
-    Request req;
-    req.slot = static_cast<uint32_t>(slot);
-    req.samples = samples;
-    req.is_cshort = is_cshort;
-    req.stamp = sample_stamp;
-    req.result = result;
-
     std::unique_lock<std::mutex> lk(d_mu);
     d_pending.push_back(&req);
     if (d_leader_active)

@@ -31,6 +31,8 @@ public:
         uint32_t samples_per_chip;
         bool bit_transition, use_cfar, keep_grid;
         int device;
+        uint32_t step2_bins;  // make_two_steps: num_doppler_bins_step2 (0 = no second engine)
+        float step2_hz;       //                 doppler_step2
         bool operator==(const Geometry& o) const;
     };
 
@@ -50,6 +52,10 @@ public:
     bool reset(int slot);
     // One acquisition_core pass for `slot` on `samples` (consumed_samples items). Blocks until `result` is written.
     bool dwell(int slot, const void* samples, bool is_cshort, uint64_t sample_stamp, gnss_b200_acq_result* result);
+    // The same with d_step_two set (pcps_acquisition.cc:715-775): the narrow grid around doppler_center_step_two, the
+    // CFAR statistic over the input power the first step measured.
+    bool dwell_step2(int slot, const void* samples, bool is_cshort, uint64_t sample_stamp, float doppler_center_step_two,
+        float input_power_step_one, gnss_b200_acq_result* result);
     bool read_grid(int slot, float* out);
     std::string last_error() const;
     uint64_t engine_calls() const;
@@ -64,12 +70,16 @@ private:
         bool is_cshort;
         uint64_t stamp;
         gnss_b200_acq_result* result;
+        bool step2 = false;
+        float center2 = 0.F, input_power1 = 0.F;
         bool done = false, ok = false;
     };
+    bool submit(Request& req);
     void drain_locked(std::unique_lock<std::mutex>& lk);
 
     Geometry d_geo;
     gnss_b200_acq* d_engine{nullptr};
+    gnss_b200_acq* d_engine2{nullptr};  // second-step handle (gnss_b200_acq_create_step2), same slots
     uint32_t d_num_doppler_bins{0};
     mutable std::mutex d_mu;
     std::condition_variable d_cv_leader, d_cv_done;

@@ -24,11 +24,16 @@ pcps_acquisition_b200::pcps_acquisition_b200(const Acq_Conf& conf_)
       d_samplesPerChip(conf_.samples_per_chip),
       d_doppler_step(static_cast<uint32_t>(conf_.doppler_step)),
       d_consumed_samples(static_cast<uint32_t>(conf_.sampled_ms * conf_.samples_per_ms * (conf_.bit_transition_flag ? 2.0 : 1.0))),  // :71
+      d_num_doppler_bins_step2(conf_.num_doppler_bins_step2),                                                                          // :73
       d_use_CFAR_algorithm_flag(conf_.use_CFAR_algorithm_flag)
 {
-    if (conf_.make_2_steps || conf_.make_repeat_steps)
+    if (conf_.make_repeat_steps)
         {
-            throw std::invalid_argument("pcps_acquisition_b200: make_two_steps / make_repeat_steps are not available in the B200 implementation yet");
+            throw std::invalid_argument("pcps_acquisition_b200: make_repeat_steps is not available in the B200 implementation");
+        }
+    if (conf_.make_2_steps && (conf_.num_doppler_bins_step2 == 0 || !(conf_.doppler_step2 > 0.0F)))
+        {
+            throw std::invalid_argument("pcps_acquisition_b200: make_two_steps needs second_nbins >= 1 and second_doppler_step > 0");
         }
     if (conf_.dump)
         {
@@ -194,6 +199,8 @@ void pcps_acquisition_b200::init()
     g.use_cfar = d_use_CFAR_algorithm_flag;
     g.keep_grid = d_acq_parameters.max_dwells > 1 && !d_acq_parameters.bit_transition_flag;  // only then is the grid accumulated (:672-684)
     g.device = 0;
+    g.step2_bins = d_acq_parameters.make_2_steps ? d_num_doppler_bins_step2 : 0U;
+    g.step2_hz = d_acq_parameters.make_2_steps ? d_acq_parameters.doppler_step2 : 0.0F;
     std::string why;
     auto bank = B200_Acquisition_Bank::get(g, &why);
     if (!bank)
@@ -279,14 +286,15 @@ bool pcps_acquisition_b200::start()
 // :894-909
 void pcps_acquisition_b200::calculate_threshold()
 {
-    const float pfa = d_acq_parameters.pfa;
+    const float pfa = (d_step_two ? d_acq_parameters.pfa2 : d_acq_parameters.pfa);
     if (pfa <= 0.0) return;
     const uint32_t effective_fft_size = d_acq_parameters.bit_transition_flag ? d_fft_size / 2 : d_fft_size;
-    d_threshold = gnss_b200_acq_threshold(pfa, effective_fft_size, d_num_doppler_bins, d_acq_parameters.max_dwells, d_acq_parameters.bit_transition_flag ? 1 : 0);
+    const uint32_t num_doppler_bins = (d_step_two ? d_num_doppler_bins_step2 : d_num_doppler_bins);
+    d_threshold = gnss_b200_acq_threshold(pfa, effective_fft_size, num_doppler_bins, d_acq_parameters.max_dwells, d_acq_parameters.bit_transition_flag ? 1 : 0);
 }
 
 
-// :615-882 without the two-step branches. The Doppler loop (:655-687) and the statistic (:689-696) are one engine call.
+// :615-882. Either Doppler loop (:655-687 wide, :715-745 narrow) with its statistic (:689-696, :746-754) is one engine call.
 void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
 {
     std::unique_lock<std::recursive_mutex> lk(d_setlock);
@@ -300,7 +308,9 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
         }
 
     gnss_b200_acq_result res{};
-    const bool ok = d_bank->dwell(d_slot, samples, d_cshort, samp_count, &res);
+    const bool step_two = d_step_two;
+    const bool ok = step_two ? d_bank->dwell_step2(d_slot, samples, d_cshort, samp_count, d_doppler_center_step_two, d_input_power, &res)
+                             : d_bank->dwell(d_slot, samples, d_cshort, samp_count, &res);
     if (!ok)
         {
             // the reference logs and keeps going; a failed device call must not look like a detection
@@ -309,7 +319,7 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
         }
     const uint32_t indext = res.code_phase;
     const int32_t doppler = res.doppler_hz;
-    d_input_power = res.input_power;
+    if (!step_two) d_input_power = res.input_power;  // :531-535 refresh it in the first step only
     d_test_statistics = res.test_statistic;
 
     if (d_acq_parameters.use_automatic_resampler)  // :699-705
@@ -325,6 +335,10 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
             d_gnss_synchro->Acq_doppler_hz = static_cast<double>(doppler);
             d_gnss_synchro->Acq_samplestamp_samples = samp_count;
         }
+    if (step_two)
+        {
+            d_gnss_synchro->Acq_doppler_step = d_acq_parameters.doppler_step2;  // :763, :770
+        }
 
     if (d_acq_parameters.blocking)
         {
@@ -336,8 +350,29 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
             if (d_test_statistics > d_threshold)
                 {
                     d_active = false;
-                    send_positive_acquisition();
-                    d_state = 0;
+                    if (d_acq_parameters.make_2_steps)  // :786-803
+                        {
+                            if (d_step_two)
+                                {
+                                    send_positive_acquisition();
+                                    d_step_two = false;
+                                    d_state = 0;
+                                }
+                            else
+                                {
+                                    d_step_two = true;  // general_work re-arms the block around Acq_doppler_hz (:937-943)
+                                    d_num_noncoherent_integrations_counter = 0;
+                                    d_positive_acq = 0;
+                                    d_state = 0;
+                                    d_bank->reset(d_slot);  // counter == 1 on the next pass overwrites the grid (:735)
+                                }
+                            calculate_threshold();
+                        }
+                    else
+                        {
+                            send_positive_acquisition();
+                            d_state = 0;
+                        }
                 }
             else
                 {
@@ -352,6 +387,12 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
                         }
                     d_state = 0;
                     d_active = false;
+                    const bool was_step_two = d_step_two;  // :823-828
+                    d_step_two = false;
+                    if (was_step_two)
+                        {
+                            calculate_threshold();
+                        }
                 }
         }
     else  // :830-866
@@ -359,12 +400,37 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
             d_active = false;
             if (d_test_statistics > d_threshold)
                 {
-                    send_positive_acquisition();
-                    d_state = 0;
+                    if (d_acq_parameters.make_2_steps)  // :835-849
+                        {
+                            if (d_step_two)
+                                {
+                                    send_positive_acquisition();
+                                    d_step_two = false;
+                                    d_state = 0;
+                                }
+                            else
+                                {
+                                    d_step_two = true;
+                                    d_num_noncoherent_integrations_counter = 0U;
+                                    d_state = 0;
+                                }
+                            calculate_threshold();
+                        }
+                    else
+                        {
+                            send_positive_acquisition();
+                            d_state = 0;
+                        }
                 }
             else
                 {
                     d_state = 0;
+                    const bool was_step_two = d_step_two;  // :859-864
+                    d_step_two = false;
+                    if (was_step_two)
+                        {
+                            calculate_threshold();
+                        }
                     send_negative_acquisition();
                 }
         }
@@ -393,6 +459,12 @@ int pcps_acquisition_b200::general_work(int noutput_items, std::vector<int>& nin
                 {
                     d_sample_counter += static_cast<uint64_t>(ninput_items[0]);
                     consume_each(ninput_items[0]);
+                }
+            if (d_step_two)  // :937-943 — the narrow grid is centred on the coarse Doppler, then the block re-arms itself
+                {
+                    d_doppler_center_step_two = static_cast<float>(d_gnss_synchro->Acq_doppler_hz);
+                    d_state = 0;
+                    d_active = true;
                 }
             return 0;
         }

@@ -7,8 +7,9 @@
  * statistics) runs in the B200 engine through the C-ABI. The class is independent of GNU Radio so that it can be
  * compiled and tested here; INTEGRATION.md shows the 30-line gr::block shell that forwards general_work to it.
  *
- * Not mirrored in this round: make_2_steps, the fork's make_repeat_steps mode, MAT-file dumps.
- * A configuration asking for them is rejected in the constructor (std::invalid_argument) instead of being ignored.
+ * make_2_steps is mirrored: the narrow second search runs on the bank's second-step engine handle.
+ * Not mirrored (N4 and the fork's private mode): make_repeat_steps, MAT-file dumps. A configuration asking for them
+ * is rejected in the constructor (std::invalid_argument) instead of being ignored.
  */
 #ifndef GNSS_SDR_PCPS_ACQUISITION_B200_H
 #define GNSS_SDR_PCPS_ACQUISITION_B200_H
@@ -66,6 +67,7 @@ public:
     float test_statistics() const { return d_test_statistics; }
     float threshold() const { return d_threshold; }
     uint32_t num_doppler_bins() const { return d_num_doppler_bins; }
+    bool step_two() const { return d_step_two; }
     uint32_t fft_size() const { return d_fft_size; }
 
 private:
@@ -96,6 +98,7 @@ private:
     float d_mag{0.0F};
     float d_input_power{0.0F};
     float d_test_statistics{0.0F};
+    float d_doppler_center_step_two{0.0F};
     int32_t d_state{0};
     int32_t d_positive_acq{0};
     int32_t d_doppler_center{0};
@@ -107,8 +110,10 @@ private:
     uint32_t d_fft_size{0};
     uint32_t d_consumed_samples{0};
     uint32_t d_num_doppler_bins{0};
+    uint32_t d_num_doppler_bins_step2{0};
     uint32_t d_buffer_count{0};
     bool d_active{false};
+    bool d_step_two{false};
     bool d_worker_active{false};
     bool d_cshort{false};
     bool d_use_CFAR_algorithm_flag{true};

@@ -117,6 +117,17 @@ extern "C"
     GNSS_B200_API int gnss_b200_acq_destroy(gnss_b200_acq* h);
     GNSS_B200_API uint32_t gnss_b200_acq_num_doppler_bins(const gnss_b200_acq* h);
 
+    /* make_two_steps (Acq_Conf::make_2_steps, num_doppler_bins_step2, doppler_step2, acq_conf.h:51,62,77):
+       a handle for the SECOND, narrow search of acquisition_core (:715-775) — num_doppler_bins_step2 bins spaced
+       doppler_step2 Hz around each slot's own d_doppler_center_step_two (update_grid_doppler_wipeoffs_step2, :308-315).
+       Same geometry fields as the first-step handle (doppler_max / doppler_step / row range are ignored). Codes, dwell and
+       results work as for a first-step handle; doppler_hz is static_cast<int32_t>(centre + (k - floor(n2/2)) * step2) (:539)
+       and the CFAR statistic divides by the input power the FIRST step left behind (:531-540 do not refresh it). At most
+       64 slots per dwell call (every slot has its own Doppler grid). */
+    GNSS_B200_API int gnss_b200_acq_create_step2(const gnss_b200_acq_cfg* cfg, uint32_t num_doppler_bins_step2, float doppler_step2, gnss_b200_acq** out);
+    /* d_doppler_center_step_two = Acq_doppler_hz of the first step (:937-940), and that step's d_input_power */
+    GNSS_B200_API int gnss_b200_acq_set_step2_center(gnss_b200_acq* h, uint32_t slot, float doppler_center_step_two_hz, float input_power_step_one);
+
     /* pcps_acquisition::set_local_code (:176-209). `code_c64` is the adapter's time-domain code
        (consumed_samples complex values; fft_size/2 are read when bit_transition). The zero-pad layout,
        forward FFT and conjugation run on the device. */

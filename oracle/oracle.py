@@ -89,6 +89,7 @@ def _bind_oracle(lib):
     lib.oracle_acq_set_local_code.argtypes = [C.c_void_p, _fp]
     lib.oracle_acq_reset.argtypes = [C.c_void_p]
     lib.oracle_acq_dwell.argtypes = [C.c_void_p, C.c_void_p, c_i, C.POINTER(AcqResult)]
+    lib.oracle_acq_dwell_step2.argtypes = [C.c_void_p, C.c_void_p, c_i, c_u, c_f, c_f, C.POINTER(AcqResult)]
     for n in ("oracle_acq_grid", "oracle_acq_fft_codes", "oracle_acq_wipeoffs"):
         getattr(lib, n).restype = _fp
         getattr(lib, n).argtypes = [C.c_void_p]
@@ -253,6 +254,17 @@ class OracleAcq:
             samples = samples.astype(np.complex64, copy=False)
             assert samples.size >= self.consumed
             self.o.lib.oracle_acq_dwell(self.h, samples.ctypes.data_as(C.c_void_p), 0, C.byref(r))
+        return r.as_dict()
+
+    def dwell_step2(self, samples, num_doppler_bins_step2, doppler_step2, doppler_center_step_two):
+        """acquisition_core with d_step_two (make_two_steps) after a first-step dwell() on this object."""
+        samples = np.ascontiguousarray(samples)
+        r = AcqResult()
+        is_cshort = int(samples.dtype == np.int16)
+        if not is_cshort:
+            samples = samples.astype(np.complex64, copy=False)
+        self.o.lib.oracle_acq_dwell_step2(self.h, samples.ctypes.data_as(C.c_void_p), is_cshort, int(num_doppler_bins_step2),
+                                          float(doppler_step2), float(doppler_center_step_two), C.byref(r))
         return r.as_dict()
 
     def grid(self):

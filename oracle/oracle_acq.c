@@ -256,6 +256,91 @@ void oracle_acq_dwell(oracle_acq* h, const void* samples, int is_cshort, oracle_
     r->dwell_count = h->dwell_count;
 }
 
+void oracle_acq_dwell_step2(oracle_acq* h, const void* samples, int is_cshort, uint32_t num_doppler_bins_step2, float doppler_step2,
+    float doppler_center_step_two, oracle_acq_result* r)
+{
+    /* acquisition_core with d_step_two == true (:715-775): the narrow grid of make_two_steps around the coarse Doppler. The
+     * block zeroes d_num_noncoherent_integrations_counter when it enters step two (:796-799), d_magnitude_grid rows
+     * 0..n2-1 are reused, and d_input_power keeps the value step one left (:531-540 only refresh it when !d_step_two). */
+    const uint32_t N = h->c.fft_size, consumed = h->c.consumed_samples, n2 = num_doppler_bins_step2;
+    const uint32_t eff = h->c.bit_transition ? N / 2 : N;
+    ocf* wipe2 = (ocf*)malloc(sizeof(ocf) * (size_t)n2 * N);
+    float* grid2 = (float*)calloc((size_t)n2 * N, sizeof(float));
+    for (uint32_t k = 0; k < n2; k++)
+        {
+            /* update_grid_doppler_wipeoffs_step2 :308-315 + update_local_carrier :233-246 */
+            const float doppler = ((float)k - (float)floor(n2 / 2.0)) * doppler_step2;
+            const float freq = doppler_center_step_two + doppler;
+            const float phase_step_rad = (float)(2.0 * M_PI) * freq / (float)h->c.fs;
+            float phase = 0.0f;
+            k_sincos(wipe2 + (size_t)k * N, -phase_step_rad, &phase, N);
+        }
+    if (is_cshort)
+        k_convert_16ic(h->input, (const void*)samples, consumed);
+    else
+        memcpy(h->input, samples, sizeof(ocf) * consumed);
+    for (uint32_t i = consumed; i < N; i++) h->input[i] = 0.0f;
+    const size_t offset = h->c.bit_transition ? eff : 0;
+    for (uint32_t k = 0; k < n2; k++)
+        {
+            v_multiply(h->fft_in, h->input, wipe2 + (size_t)k * N, N);             /* :719 */
+            offt_f_execute(h->fwd, (const float*)h->fft_in, (float*)h->fft_out);   /* :723 */
+            v_multiply(h->fft_in, h->fft_out, h->fft_codes, N);                    /* :727 */
+            offt_f_execute(h->bwd, (const float*)h->fft_in, (float*)h->ifft_out);  /* :730 */
+            v_mag_squared(grid2 + (size_t)k * N, h->ifft_out + offset, eff);       /* :735 (counter == 1) */
+        }
+    memset(r, 0, sizeof(*r));
+    /* the two statistics with d_step_two (:511-543, :546-612) */
+    const uint32_t len = h->c.use_cfar ? eff : N;
+    float best = 0.0f;
+    uint32_t index_doppler = 0, index_time = 0, tmp_t = 0;
+    for (uint32_t i = 0; i < n2; i++)
+        {
+            const float* row = grid2 + (size_t)i * N;
+            k_index_max(&tmp_t, row, len);
+            if (row[tmp_t] > best)
+                {
+                    best = row[tmp_t];
+                    index_doppler = i;
+                    index_time = tmp_t;
+                }
+        }
+    r->peak = best;
+    r->code_phase = index_time;
+    r->doppler_index = index_doppler;
+    r->doppler_hz = (int32_t)(doppler_center_step_two + ((float)index_doppler - (float)floor(n2 / 2.0)) * doppler_step2); /* :539 */
+    r->input_power = h->input_power;
+    if (h->c.use_cfar)
+        {
+            r->test_statistic = best / h->input_power; /* :542 */
+        }
+    else
+        {
+            int32_t ex1 = (int32_t)index_time - (int32_t)h->c.samples_per_chip;
+            int32_t ex2 = (int32_t)index_time + (int32_t)h->c.samples_per_chip;
+            if (ex1 < 0)
+                ex1 = (int32_t)N + ex1;
+            else if (ex2 >= (int32_t)N)
+                ex2 = ex2 - (int32_t)N;
+            memcpy(h->tmp, grid2 + (size_t)index_doppler * N, sizeof(float) * N);
+            int32_t idx = ex1;
+            do
+                {
+                    h->tmp[idx] = 0.0f;
+                    idx++;
+                    if (idx == (int32_t)N) idx = 0;
+                }
+            while (idx != ex2);
+            k_index_max(&tmp_t, h->tmp, N);
+            r->second_peak = h->tmp[tmp_t];
+            r->test_statistic = best / r->second_peak;
+        }
+    r->acq_delay_samples = (double)fmodf((float)r->code_phase, h->c.samples_per_code); /* :769 */
+    r->dwell_count = 1;
+    free(wipe2);
+    free(grid2);
+}
+
 /* ---- threshold: 2 * gamma_p_inv(a, p) (:894-909). boost::math is third-party
  * and absent; P(a,x) is evaluated by its series / continued fraction and inverted
  * by bracketed Newton. Cross-checked against scipy.special.gammaincinv in tests. ---- */

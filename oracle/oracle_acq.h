@@ -46,6 +46,9 @@ extern "C"
     void oracle_acq_set_local_code(oracle_acq* h, const float* code_c64);
     void oracle_acq_reset(oracle_acq* h);
     void oracle_acq_dwell(oracle_acq* h, const void* samples, int is_cshort, oracle_acq_result* r);
+    /* make_two_steps: the narrow second search (acquisition_core with d_step_two, :715-775) after a first-step dwell */
+    void oracle_acq_dwell_step2(oracle_acq* h, const void* samples, int is_cshort, uint32_t num_doppler_bins_step2, float doppler_step2,
+        float doppler_center_step_two, oracle_acq_result* r);
     const float* oracle_acq_grid(const oracle_acq* h);      /* [nD][fft_size] */
     const float* oracle_acq_fft_codes(const oracle_acq* h); /* [fft_size] c64 */
     const float* oracle_acq_wipeoffs(const oracle_acq* h);  /* [nD][fft_size] c64 */

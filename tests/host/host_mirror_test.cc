@@ -113,6 +113,13 @@ int run_acq(const char* in_path, const char* out_path)
         stream_sc = r.vec<int16_t>(static_cast<size_t>(n_items) * 2);
     else
         stream_fc = r.vec<std::complex<float>>(n_items);
+    if (r.f.peek() != std::ifstream::traits_type::eof())  // optional trailer: make_two_steps (acq_conf.cc:84-90)
+        {
+            conf.make_2_steps = r.get<uint32_t>() != 0;
+            conf.num_doppler_bins_step2 = r.get<uint32_t>();
+            conf.doppler_step2 = r.get<float>();
+            conf.pfa2 = r.get<float>();
+        }
 
     B200_Acquisition_Bank::set_default_capacity(std::max(1U, n_blocks));
     B200_Acquisition_Bank::set_coalescing(coalesce_us, coalesce_us ? n_blocks : 0);
@@ -153,7 +160,8 @@ int run_acq(const char* in_path, const char* out_path)
     auto feed = [&](uint32_t b) {
         size_t pos = 0;
         int idle_calls = 0;
-        while (true)
+        const auto t_end = std::chrono::steady_clock::now() + std::chrono::seconds(60);
+        while (std::chrono::steady_clock::now() < t_end)
             {
                 const size_t avail = std::min<size_t>(chunk, n_items - pos);
                 std::vector<int> ninput{static_cast<int>(avail)};
@@ -188,6 +196,8 @@ int run_acq(const char* in_path, const char* out_path)
             w.put<float>(blocks[b]->threshold());
             w.put<uint32_t>(blocks[b]->num_doppler_bins());
             w.put<uint32_t>(blocks[b]->fft_size());
+            w.put<uint32_t>(synchro[b].Acq_doppler_step);
+            w.put<uint32_t>(blocks[b]->step_two() ? 1U : 0U);
         }
     return 0;
 }

@@ -308,3 +308,47 @@ def test_full_size_config3_properties(b200):
     g = e.read_grid(0)
     assert g.shape == (800, 160000) and float(g.max()) == float(c[0]["peak"])
     e.close()
+
+
+@pytest.mark.parametrize("use_cfar", [True, False])
+def test_two_step_acquisition(b200, oracle, use_cfar):
+    """SURVEY 8.6 N3, make_two_steps (pcps_acquisition.cc:308-315,715-775): after the coarse search a narrow grid of
+    second_nbins bins spaced second_doppler_step around each PRN's own coarse Doppler; float Doppler arithmetic, the
+    Doppler reported by :539, and a CFAR statistic that keeps the first step's input power."""
+    geo, codes, iq, truth = synth.config_scene("C1", n_prn=8)
+    iq2 = synth.make_iq(4000, geo["fs"], [dict(t, phase=0.7) for t in truth], seed=123)   # the block the second step runs on
+    e1 = _gpu_engine(b200, geo, 8, use_cfar=use_cfar)
+    e2 = _gpu_engine(b200, geo, 8, use_cfar=use_cfar, step2=(4, 125.0))
+    assert e2.n_doppler == 4
+    e1.set_local_codes(np.arange(8), codes)
+    e2.set_local_codes(np.arange(8), codes)
+    r1 = e1.dwell(iq, np.arange(8))
+    for p in range(8):
+        e2.set_step2_center(p, float(r1[p]["doppler_hz"]), r1[p]["input_power"])
+    r2 = e2.dwell(iq2, np.arange(8))
+    present = {t["prn"]: t for t in truth}
+    for p in range(8):
+        a = oracle.acq(fft_size=geo["fft_size"], consumed_samples=geo["consumed_samples"], doppler_max=geo["doppler_max"],
+                       doppler_step=geo["doppler_step"], fs=geo["fs"], samples_per_chip=geo["samples_per_chip"],
+                       samples_per_code=geo["samples_per_code"], use_cfar=use_cfar)
+        a.set_local_code(codes[p])
+        a.reset()
+        w1 = a.dwell(iq)
+        w2 = a.dwell_step2(iq2, 4, 125.0, float(w1["doppler_hz"]))
+        strong = (p + 1) in present
+        _compare(r1[p], w1, strict_idx=strong)
+        if int(r1[p]["doppler_hz"]) != w1["doppler_hz"]:
+            continue        # a noise-only PRN whose coarse peak moved: the second grids differ by construction
+        assert r2[p]["peak"] == pytest.approx(w2["peak"], rel=RTOL)
+        assert r2[p]["test_statistic"] == pytest.approx(w2["test_statistic"], rel=RTOL)
+        if strong:
+            assert int(r2[p]["code_phase"]) == w2["code_phase"] and int(r2[p]["doppler_index"]) == w2["doppler_index"]
+            assert int(r2[p]["doppler_hz"]) == w2["doppler_hz"]
+            t = present[p + 1]
+            # a 1 ms dwell has a 1 kHz main lobe: the fine bin is noise-limited, it only has to stay inside the narrow grid
+            assert abs(int(r2[p]["doppler_hz"]) - int(r1[p]["doppler_hz"])) <= 2 * 125 and abs(r2[p]["doppler_hz"] - t["doppler"]) < 500
+        a.close()
+    with pytest.raises(b200.B200Error):
+        e1.set_step2_center(0, 0.0, 1.0)          # not a second-step handle
+    e1.close()
+    e2.close()

@@ -59,7 +59,7 @@ def test_mirror_keeps_the_reference_method_set():
 
 
 def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, doppler_step, pfa, threshold, max_dwells, bit_transition,
-                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us):
+                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us, two_steps=None):
     with open(path, "wb") as f:
         f.write(struct.pack("<q", int(fs)))
         f.write(struct.pack("<IIIiI", sampled_ms, ms_per_code, spc, doppler_max, doppler_step))
@@ -70,6 +70,8 @@ def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, dopple
         for c in codes:
             f.write(np.ascontiguousarray(c, dtype=np.complex64).tobytes())
         f.write(np.ascontiguousarray(stream, dtype=np.int16 if cshort else np.complex64).tobytes())
+        if two_steps is not None:          # (second_nbins, second_doppler_step, pfa2)
+            f.write(struct.pack("<IIff", 1, int(two_steps[0]), float(two_steps[1]), float(two_steps[2])))
 
 
 def _read_acq_output(path):
@@ -77,9 +79,10 @@ def _read_acq_output(path):
     n, = struct.unpack_from("<I", raw, 0)
     out, off = [], 4
     for _ in range(n):
-        ev, delay, dop, stamp, stat, thr, nd, nfft = struct.unpack_from("<iddQffII", raw, off)
-        off += struct.calcsize("<iddQffII")
-        out.append(dict(event=ev, delay=delay, doppler=dop, stamp=stamp, stat=stat, threshold=thr, n_doppler=nd, fft_size=nfft))
+        ev, delay, dop, stamp, stat, thr, nd, nfft, dstep, st2 = struct.unpack_from("<iddQffIIII", raw, off)
+        off += struct.calcsize("<iddQffIIII")
+        out.append(dict(event=ev, delay=delay, doppler=dop, stamp=stamp, stat=stat, threshold=thr, n_doppler=nd, fft_size=nfft,
+                        doppler_step=dstep, step_two=st2))
     return out
 
 
@@ -200,3 +203,46 @@ def test_correlator_objects_match_oracle(driver, oracle, tmp_path, mode, high_dy
                                       six_arg=(mode == 1))
             scale = np.abs(want).max() + np.sqrt(n)
             assert np.abs(got[c, e] - want).max() <= 1e-4 * scale
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("blocking,coalesce_us", [(True, 0), (True, 20000)])
+def test_two_step_acquisition_through_the_block_interface(driver, oracle, tmp_path, blocking, coalesce_us):
+    """make_two_steps (pcps_acquisition.cc:786-803, 823-828, 937-943): a positive coarse search re-arms the block around
+    Acq_doppler_hz, the second search runs num_doppler_bins_step2 bins of doppler_step2 on a LATER block of the stream
+    and only its decision is reported. Six channels share one bank (and its second-step engine). Only the blocking mode
+    (the reference's default) is deterministic: with a worker thread, a general_work call that wins the lock between the
+    thread's creation and its first statement re-reads Acq_doppler_hz — zeroed by the restart state — as the narrow
+    grid's centre (:937-943 run whenever d_worker_active). The mirror keeps that order; the test stays away from it."""
+    geo, codes, iq, truth = synth.config_scene("C1", n_prn=6, n_dwells=6)
+    stream = iq.reshape(-1)
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_acq_input(inp, geo["fs"], 1, 1, geo["samples_per_chip"], geo["doppler_max"], geo["doppler_step"], 0.01, 0.0, 1, False, True,
+                     False, blocking, list(codes), stream, 4000, False, coalesce_us, two_steps=(4, 125.0, 0.02))
+    _run(driver, "acq", inp, outp)
+    got = _read_acq_output(outp)
+    thr1 = oracle.threshold(0.01, 4000, 40, 1, False)
+    thr2 = oracle.threshold(0.02, 4000, 4, 1, False)
+    n_two = 0
+    for p in range(6):
+        acq = oracle.acq(fft_size=4000, consumed_samples=4000, doppler_max=geo["doppler_max"], doppler_step=geo["doppler_step"],
+                         fs=geo["fs"], samples_per_chip=geo["samples_per_chip"], samples_per_code=geo["samples_per_code"])
+        acq.set_local_code(codes[p])
+        w1 = acq.dwell(stream[:4000])
+        g = got[p]
+        assert g["step_two"] == 0 and g["threshold"] == pytest.approx(thr1, rel=1e-6)   # both exits restore the first threshold
+        if w1["test_statistic"] > thr1:
+            # call sequence: fill, switch, search (stamp 4000), idle call consumes a block and re-arms, restart state
+            # consumes another, fill takes stream[12000:16000], switch, search (stamp 16000)
+            w2 = acq.dwell_step2(stream[12000:16000], 4, 125.0, float(w1["doppler_hz"]))
+            n_two += 1
+            assert g["stamp"] == 16000
+            assert g["stat"] == pytest.approx(w2["test_statistic"], rel=1e-4)
+            assert g["doppler"] == float(w2["doppler_hz"]) and g["delay"] == float(w2["code_phase"] % 4000)
+            assert g["doppler_step"] == 125
+            assert g["event"] == (1 if w2["test_statistic"] > thr2 else 2)
+        else:
+            assert g["event"] == 2 and g["stamp"] == 4000
+            assert g["stat"] == pytest.approx(w1["test_statistic"], rel=1e-4)
+        acq.close()
+    assert n_two >= 1

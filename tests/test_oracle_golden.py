@@ -170,3 +170,21 @@ def test_gsoc2013_synthetic_case(oracle):
     assert r["test_statistic"] > thr
     assert abs(r["acq_delay_samples"] - delay) < 0.5 * 4000 / 1023
     assert abs(r["doppler_hz"] - 750) < 2.0 / (3.0 * 1e-3)
+
+
+def test_step_two_single_bin_reproduces_coarse_row(oracle):
+    """make_two_steps restatement (pcps_acquisition.cc:308-315,715-775) pinned on the reference's GPS capture: a one-bin
+    narrow grid centred on the coarse answer builds the very carrier of the coarse row (both go through
+    update_local_carrier(float), :233-246), so peak, code phase, Doppler and the CFAR statistic (which keeps the first
+    step's input power) must repeat the known answer; a 5-bin grid spaced 50 Hz must contain it at its centre bin."""
+    a, r = _gps_capture_acq(oracle, use_cfar=True)
+    d = np.fromfile(os.path.join(GOLD, "GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat"), dtype=np.complex64)
+    r1 = a.dwell_step2(d[:4000], 1, 125.0, float(r["doppler_hz"]))
+    assert r1["code_phase"] == 524 and r1["doppler_hz"] == 1700 and r1["doppler_index"] == 0
+    assert r1["peak"] == r["peak"] and r1["test_statistic"] == r["test_statistic"]
+    r5 = a.dwell_step2(d[:4000], 5, 50.0, float(r["doppler_hz"]))
+    assert r5["code_phase"] == 524 and r5["peak"] >= r["peak"]
+    assert r5["doppler_hz"] == 1700 + (r5["doppler_index"] - 2) * 50 and abs(r5["doppler_hz"] - 1680) <= 100
+    # second block of the same capture: the statistic still divides by the FIRST block's input power
+    r2 = a.dwell_step2(d[4000:8000], 1, 125.0, float(r["doppler_hz"]))
+    assert r2["input_power"] == r["input_power"] and r2["test_statistic"] == pytest.approx(r2["peak"] / r["input_power"], rel=1e-6)

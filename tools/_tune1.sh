@@ -1,8 +1,4 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -15
-python tools/acq_tune.py C1 32
-python tools/acq_tune.py C4_gps 32
-python tools/acq_tune.py C4_gal 36
-python tools/acq_tune.py C4_bds 63
-python tools/acq_tune.py C2 50
-B200_ACQ_FWD_GENERIC=1 python tools/acq_tune.py C2 50
-python tools/c3_tune.py 4 4
+for nb in 5 10 20 40 80; do B200_FFT_NB=$nb python tools/acq_tune.py C2 50; done
+for nb in 5 10 20 40 80; do B200_FFT_NB=$nb python tools/acq_tune.py C2 50; done
+for nb in 4 5 10 20 25; do B200_FFT_NB=$nb python tools/acq_tune.py C4_gal 36; done
+for nb in 5 10 20 25 50; do B200_FFT_NB=$nb python tools/acq_tune.py C4_bds 63; done
