@@ -400,7 +400,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 const bool grid_path = mag_base && !mag_is_rowbuf && h->mag_offset == 0 && h->eff == h->N;
                 const uint32_t pitch = (pl.ra_lo % 2 == 0) ? pl.ra_lo + 1 : pl.ra_lo;
                 const size_t smem_lo = ((size_t)fa.nb * pitch * pl.rb_lo + fa.M_lo) * sizeof(float2);
-                const size_t smem_hi = ((size_t)fa.M_hi * fa.C + fa.M_hi) * sizeof(float2);
+                const size_t smem_hi = ((size_t)pl.rb_hi * upper_group_stride(pl.ra_hi, fa.C) + fa.M_hi) * sizeof(float2);
                 const uint32_t rows_hi = std::max(1u, (uint32_t)kFastThreads / fa.C);
                 const dim3 block_hi(fa.C, rows_hi);
                 const uint32_t threads_lo = std::max<uint32_t>(64, std::min<uint32_t>(kFastThreads, (fa.nb * pl.rb_lo + 31) / 32 * 32));  // >= 64: twiddle fill

@@ -166,6 +166,15 @@ __global__ void __launch_bounds__(kFastThreads) inv_lower_kernel(const FastArgs 
 // ------------------------------------------------------------------------------------------------
 // upper stage: grid (rows, M_lo / C), block (C, threads / C). Shared memory: M * C data + M twiddles.
 // ------------------------------------------------------------------------------------------------
+// Shared-memory layout of the upper stage: element (q + RA*ub, c) at ub*G + q*C + c with the group stride G = RA*C padded so that
+// G = C (mod 16): with blockDim.x = C not a multiple of 16 a warp spans two ub groups (pass A) or two rows (pass B), and
+// the lanes of the second one then continue on the banks right after the first one's instead of landing on top of them.
+__host__ __device__ __forceinline__ uint32_t upper_group_stride(uint32_t ra, uint32_t C)
+{
+    const uint32_t g = ra * C;
+    return g + ((C + 16u - (g & 15u)) & 15u);
+}
+
 // GRID = true: persistent magnitude grid (max_dwells > 1 / dump), full rows: the old grid values of a pencil are requested
 // (streaming loads) before its butterfly so that their HBM latency hides behind it, and written back with streaming stores.
 template <int RA, int RB, bool GRID = false>
@@ -174,7 +183,8 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     constexpr int M = RA * RB;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* s = reinterpret_cast<float2*>(smem_raw);
-    float2* s_tw = s + (size_t)M * a.C;  // conj W_M^(a*ub), [ub][a]
+    const uint32_t G = upper_group_stride(RA, a.C);
+    float2* s_tw = s + (size_t)RB * G;  // conj W_M^(a*ub), [ub][a]
     __shared__ float s_rmax[kFastThreads / 32];
     __shared__ uint32_t s_ridx[kFastThreads / 32];
     __shared__ float s_rsum[kFastThreads / 32];
@@ -208,7 +218,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     };
     auto twiddle_store = [&](float2(&v)[RA], uint32_t ub) {
 #pragma unroll
-        for (int q = 0; q < RA; q++) s[(size_t)(q + RA * ub) * C + c] = fft::cmul(v[q], s_tw[ub * RA + q]);
+        for (int q = 0; q < RA; q++) s[(size_t)ub * G + q * C + c] = fft::cmul(v[q], s_tw[ub * RA + q]);
     };
     {
         float2 v[RA];
@@ -259,7 +269,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
                             for (int b = 0; b < RB; b++) old[b] = accumulate ? __ldcs(mag + pos0 + b * pstep) : 0.f;
                         }
 #pragma unroll
-                    for (int u = 0; u < RB; u++) v[u] = s[(size_t)(aa + RA * u) * C + c];
+                    for (int u = 0; u < RB; u++) v[u] = s[(size_t)u * G + aa * C + c];
                     fft::Dft<RB, true>::run(v);
 #pragma unroll
                     for (int b = 0; b < RB; b++)
@@ -277,7 +287,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
                                 }
                             sum += g;
                             best = fmaxf(best, g);
-                            s[(size_t)(aa + RA * b) * C + c].x = g;
+                            s[(size_t)b * G + aa * C + c].x = g;
                         }
                 }
 #pragma unroll
@@ -303,7 +313,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
                         {
 #pragma unroll
                             for (int b = 0; b < RB; b++)
-                                if (s[(size_t)(aa + RA * b) * C + c].x == tile_max) mine = min(mine, (aa + RA * b) * a.M_lo + c0 + c);
+                                if (s[(size_t)b * G + aa * C + c].x == tile_max) mine = min(mine, (aa + RA * b) * a.M_lo + c0 + c);
                         }
                     if (mine != 0xffffffffu) atomicMin(&s_tile_idx, mine);  // lowest index wins ties (:523)
                 }
@@ -324,7 +334,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
         {
             float2 v[RB];
 #pragma unroll
-            for (int u = 0; u < RB; u++) v[u] = s[(size_t)(aa + RA * u) * C + c];
+            for (int u = 0; u < RB; u++) v[u] = s[(size_t)u * G + aa * C + c];
             fft::Dft<RB, true>::run(v);
 #pragma unroll
             for (int b = 0; b < RB; b++)

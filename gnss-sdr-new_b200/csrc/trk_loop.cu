@@ -53,7 +53,7 @@ struct TrkChan
     double carrier_doppler_hz, carrier_phase_step_rad, code_freq_chips, code_phase_step_chips;
     double rem_code_phase_samples, rem_code_phase_chips, acc_carrier_phase_rad;
     double carr_phase_error_hz, carr_freq_error_hz, carr_error_filt_hz, code_error_chips, code_error_filt_chips;
-    double cn0_db_hz, carrier_lock_test;
+    double cn0_db_hz, carrier_lock_test, evm;
     unsigned long long cursor, acq_sample_stamp;
     float rem_carr_phase_rad;
     float2 P_old;
@@ -278,6 +278,21 @@ __global__ void trk_update_kernel(const TrkDevCfg cfg, TrkChan* __restrict__ cha
                                     s.code_lock_fail = 0;
                                     lock_ok = false;
                                 }
+                            else
+                                {
+                                    // EVM indicator of the fork (:1027-1053): binary32 sums in buffer order
+                                    float tmp_sum = 0.f;
+                                    for (int k = 0; k < cfg.cn0_samples; k++) tmp_sum = __fadd_rn(tmp_sum, __fmul_rn(s.prompt_buf[k].x, s.prompt_buf[k].x));
+                                    const float d = __fsqrt_rn(__fdiv_rn(tmp_sum, (float)cfg.cn0_samples));
+                                    tmp_sum = 0.f;
+                                    for (int k = 0; k < cfg.cn0_samples; k++)
+                                        {
+                                            const float a = __fsub_rn(fabsf(__fdiv_rn(s.prompt_buf[k].x, d)), 1.f);
+                                            const float b = fabsf(__fdiv_rn(s.prompt_buf[k].y, d));
+                                            tmp_sum = __fadd_rn(__fadd_rn(tmp_sum, __fmul_rn(a, a)), __fmul_rn(b, b));
+                                        }
+                                    s.evm = sqrt((double)__fdiv_rn(tmp_sum, (float)cfg.cn0_samples));
+                                }
                         }
                     e.flags = GNSS_B200_TRK_VALID | (s.pull_in ? GNSS_B200_TRK_PULL_IN : 0u);
                     if (!lock_ok)
@@ -371,6 +386,7 @@ __global__ void trk_update_kernel(const TrkDevCfg cfg, TrkChan* __restrict__ cha
                     e.acc_carrier_phase_rad = s.acc_carrier_phase_rad;
                     e.cn0_db_hz = s.cn0_db_hz;
                     e.carrier_lock_test = s.carrier_lock_test;
+                    e.evm = s.evm;
                     e.sample_counter = nread;
                     e.prn_length_samples = s.current_prn_length_samples;
                     s.cursor += (unsigned long long)s.current_prn_length_samples;  // consume_each

@@ -156,6 +156,13 @@ bool B200_Acquisition_Bank::read_grid(int slot, float* out)
 }
 
 
+bool B200_Acquisition_Bank::read_grid_step2(int slot, float* out)
+{
+    if (slot < 0 || out == nullptr || d_engine2 == nullptr) return false;
+    return gnss_b200_acq_read_grid(d_engine2, static_cast<uint32_t>(slot), out) == GNSS_B200_OK;
+}
+
+
 // Leader with d_mu held: issue one engine call per distinct (sample stamp, item type, step) among the pending dwells.
 void B200_Acquisition_Bank::drain_locked(std::unique_lock<std::mutex>& lk)
 {

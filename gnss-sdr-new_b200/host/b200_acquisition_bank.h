@@ -56,7 +56,8 @@ public:
     // CFAR statistic over the input power the first step measured.
     bool dwell_step2(int slot, const void* samples, bool is_cshort, uint64_t sample_stamp, float doppler_center_step_two,
         float input_power_step_one, gnss_b200_acq_result* result);
-    bool read_grid(int slot, float* out);
+    bool read_grid(int slot, float* out);        // [num_doppler_bins][effective size]; bank geometry with keep_grid
+    bool read_grid_step2(int slot, float* out);  // [step2_bins][effective size]
     std::string last_error() const;
     uint64_t engine_calls() const;
     uint64_t dwells_served() const;

@@ -6,8 +6,10 @@
 #if !defined(B200_HOST_STANDALONE)
 #include "GLONASS_L1_L2_CA.h"  // DFRQ1_GLO, DFRQ2_GLO, GLONASS_PRN
 #endif
+#include "b200_mat_writer.h"
 #include <algorithm>
 #include <cmath>
+#include <filesystem>
 #include <cstring>
 #include <iostream>
 #include <stdexcept>
@@ -20,13 +22,16 @@ pcps_acquisition_b200_sptr pcps_make_acquisition_b200(const Acq_Conf& conf_)
 
 
 pcps_acquisition_b200::pcps_acquisition_b200(const Acq_Conf& conf_)
-    : d_acq_parameters(conf_),
+    : d_dump_filename(conf_.dump_filename),  // :55
+      d_acq_parameters(conf_),
       d_samplesPerChip(conf_.samples_per_chip),
       d_doppler_step(static_cast<uint32_t>(conf_.doppler_step)),
       d_consumed_samples(static_cast<uint32_t>(conf_.sampled_ms * conf_.samples_per_ms * (conf_.bit_transition_flag ? 2.0 : 1.0))),  // :71
       d_num_doppler_bins_step2(conf_.num_doppler_bins_step2),                                                                          // :73
       d_use_CFAR_algorithm_flag(conf_.use_CFAR_algorithm_flag)
 {
+    d_dump_channel = conf_.dump_channel;  // :74
+    d_dump = conf_.dump;                  // :81
     if (conf_.make_repeat_steps)
         {
             throw std::invalid_argument("pcps_acquisition_b200: make_repeat_steps is not available in the B200 implementation");
@@ -34,10 +39,6 @@ pcps_acquisition_b200::pcps_acquisition_b200(const Acq_Conf& conf_)
     if (conf_.make_2_steps && (conf_.num_doppler_bins_step2 == 0 || !(conf_.doppler_step2 > 0.0F)))
         {
             throw std::invalid_argument("pcps_acquisition_b200: make_two_steps needs second_nbins >= 1 and second_doppler_step > 0");
-        }
-    if (conf_.dump)
-        {
-            throw std::invalid_argument("pcps_acquisition_b200: dump=true is not available in the B200 implementation yet");
         }
     if (d_consumed_samples == 0)
         {
@@ -47,6 +48,53 @@ pcps_acquisition_b200::pcps_acquisition_b200(const Acq_Conf& conf_)
     d_cshort = (conf_.it_size != sizeof(std::complex<float>));                                           // :121-128
     d_data_buffer.resize(d_consumed_samples);
     if (d_cshort) d_data_buffer_sc.resize(static_cast<size_t>(d_consumed_samples) * 2);
+
+    if (d_dump)  // :135-165 — split the path, default name, drop the extension, create the directory
+        {
+            std::string dump_path;
+            if (d_dump_filename.find_last_of('/') != std::string::npos)
+                {
+                    const std::string dump_filename_ = d_dump_filename.substr(d_dump_filename.find_last_of('/') + 1);
+                    dump_path = d_dump_filename.substr(0, d_dump_filename.find_last_of('/'));
+                    d_dump_filename = dump_filename_;
+                }
+            else
+                {
+                    dump_path = std::string(".");
+                }
+            if (d_dump_filename.empty())
+                {
+                    d_dump_filename = "acquisition";
+                }
+            if (d_dump_filename.substr(1).find_last_of('.') != std::string::npos)
+                {
+                    d_dump_filename = d_dump_filename.substr(0, d_dump_filename.find_last_of('.'));
+                }
+            d_dump_filename = dump_path + '/' + d_dump_filename;
+            std::error_code ec;
+            std::filesystem::create_directories(dump_path, ec);
+            if (ec)
+                {
+                    std::cerr << "GNSS-SDR cannot create dump file for the Acquisition block. Wrong permissions?\n";
+                    d_dump = false;
+                }
+        }
+}
+
+
+// pcps_acquisition.h:160-163. The dump channel keeps its magnitude grid on the device, so a channel number that arrives
+// after init() re-attaches the block to a bank of the matching kind.
+void pcps_acquisition_b200::set_channel(uint32_t channel)
+{
+    std::lock_guard<std::recursive_mutex> lock(d_setlock);
+    const bool was = dumping();
+    d_channel = channel;
+    if (d_bank && was != dumping())
+        {
+            attach_engine();
+            d_bank->reset(d_slot);
+            refresh_doppler_grid();
+        }
 }
 
 
@@ -188,6 +236,17 @@ void pcps_acquisition_b200::init()
     d_input_power = 0.0;
     d_num_doppler_bins = static_cast<uint32_t>(std::ceil(static_cast<double>(static_cast<int32_t>(d_acq_parameters.doppler_max) - static_cast<int32_t>(-d_acq_parameters.doppler_max)) / static_cast<double>(d_doppler_step)));  // :264
 
+    attach_engine();
+    d_bank->reset(d_slot);  // :281-284
+    refresh_doppler_grid();  // :286
+    d_num_noncoherent_integrations_counter = 0U;
+    d_worker_active = false;
+}
+
+
+// The engine side of init(): a bank for this block's search geometry, a slot in it, the local code if there is one.
+void pcps_acquisition_b200::attach_engine()
+{
     B200_Acquisition_Bank::Geometry g{};
     g.fft_size = d_fft_size;
     g.consumed_samples = d_consumed_samples;
@@ -197,7 +256,8 @@ void pcps_acquisition_b200::init()
     g.samples_per_chip = d_samplesPerChip;
     g.bit_transition = d_acq_parameters.bit_transition_flag;
     g.use_cfar = d_use_CFAR_algorithm_flag;
-    g.keep_grid = d_acq_parameters.max_dwells > 1 && !d_acq_parameters.bit_transition_flag;  // only then is the grid accumulated (:672-684)
+    // the grid stays on the device only where it is needed: accumulated over dwells (:672-684) or dumped (:682, :743)
+    g.keep_grid = (d_acq_parameters.max_dwells > 1 && !d_acq_parameters.bit_transition_flag) || dumping();
     g.device = 0;
     g.step2_bins = d_acq_parameters.make_2_steps ? d_num_doppler_bins_step2 : 0U;
     g.step2_hz = d_acq_parameters.make_2_steps ? d_acq_parameters.doppler_step2 : 0.0F;
@@ -205,23 +265,25 @@ void pcps_acquisition_b200::init()
     auto bank = B200_Acquisition_Bank::get(g, &why);
     if (!bank)
         {
-            throw std::runtime_error("pcps_acquisition_b200::init: cannot create the B200 engine: " + why);
+            throw std::runtime_error("pcps_acquisition_b200: engine: cannot create the B200 engine: " + why);
         }
     if (bank != d_bank)
         {
             if (d_bank && d_slot >= 0) d_bank->release_slot(d_slot);
             d_bank = bank;
             d_slot = d_bank->acquire_slot();
-            if (d_slot < 0) throw std::runtime_error("pcps_acquisition_b200::init: " + d_bank->last_error());
+            if (d_slot < 0) throw std::runtime_error("pcps_acquisition_b200: engine: " + d_bank->last_error());
             if (d_have_code && !d_bank->set_local_code(d_slot, d_code_copy.data()))  // d_fft_codes survives init() in the reference
                 {
-                    throw std::runtime_error("pcps_acquisition_b200::init: " + d_bank->last_error());
+                    throw std::runtime_error("pcps_acquisition_b200: engine: " + d_bank->last_error());
                 }
         }
-    d_bank->reset(d_slot);  // :281-284
-    refresh_doppler_grid();  // :286
-    d_num_noncoherent_integrations_counter = 0U;
-    d_worker_active = false;
+    if (dumping())  // :289-294
+        {
+            const uint32_t effective_fft_size = (d_acq_parameters.bit_transition_flag ? (d_fft_size / 2) : d_fft_size);
+            d_grid.assign(static_cast<size_t>(effective_fft_size) * d_num_doppler_bins, 0.0F);
+            d_narrow_grid.assign(static_cast<size_t>(effective_fft_size) * d_num_doppler_bins_step2, 0.0F);
+        }
 }
 
 
@@ -274,6 +336,52 @@ void pcps_acquisition_b200::send_negative_acquisition()
 }
 
 
+// :408-508 — same file name, variables, classes and shapes; Level-5 container (b200_mat_writer.h)
+void pcps_acquisition_b200::dump_results(int32_t effective_fft_size)
+{
+    d_dump_number++;
+    std::string filename = d_dump_filename;
+    filename.append("_");
+    filename.append(1, d_gnss_synchro->System);
+    filename.append("_");
+    filename.append(1, d_gnss_synchro->Signal[0]);
+    filename.append(1, d_gnss_synchro->Signal[1]);
+    filename.append("_ch_");
+    filename.append(std::to_string(d_channel));
+    filename.append("_");
+    filename.append(std::to_string(d_dump_number));
+    filename.append("_sat_");
+    filename.append(std::to_string(d_gnss_synchro->PRN));
+    filename.append(".mat");
+
+    B200_Mat_Writer mat;
+    if (!mat.open(filename))
+        {
+            std::cout << "Unable to create or open Acquisition dump file\n";
+            return;
+        }
+    mat.write_single("acq_grid", d_grid.data(), static_cast<size_t>(effective_fft_size), d_num_doppler_bins);
+    mat.write_int32("doppler_max", static_cast<int32_t>(d_acq_parameters.doppler_max));
+    mat.write_int32("doppler_step", static_cast<int32_t>(d_doppler_step));
+    mat.write_int32("d_positive_acq", d_positive_acq);
+    mat.write_single("acq_doppler_hz", static_cast<float>(d_gnss_synchro->Acq_doppler_hz));
+    mat.write_single("acq_delay_samples", static_cast<float>(d_gnss_synchro->Acq_delay_samples));
+    mat.write_single("test_statistic", d_test_statistics);
+    mat.write_single("threshold", d_threshold);
+    mat.write_single("input_power", d_input_power);
+    mat.write_uint64("sample_counter", d_sample_counter);
+    mat.write_uint32("PRN", d_gnss_synchro->PRN);
+    mat.write_int32("num_dwells", static_cast<int32_t>(d_num_noncoherent_integrations_counter));
+    if (d_acq_parameters.make_2_steps)
+        {
+            mat.write_single("acq_grid_narrow", d_narrow_grid.data(), static_cast<size_t>(effective_fft_size), d_num_doppler_bins_step2);
+            mat.write_single("doppler_step_narrow", d_acq_parameters.doppler_step2);
+            mat.write_single("doppler_grid_narrow_min", d_doppler_center_step_two - static_cast<float>(std::floor(d_num_doppler_bins_step2 / 2.0)) * d_acq_parameters.doppler_step2);
+        }
+    mat.close();
+}
+
+
 // :885-890
 bool pcps_acquisition_b200::start()
 {
@@ -316,6 +424,11 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
             // the reference logs and keeps going; a failed device call must not look like a detection
             std::cerr << "pcps_acquisition_b200: engine dwell failed: " << d_bank->last_error() << '\n';
             res = gnss_b200_acq_result{};
+        }
+    if (ok && dumping())  // :682-685, :743-746 — the dump channel mirrors the magnitude grid after every pass
+        {
+            const bool got = step_two ? d_bank->read_grid_step2(d_slot, d_narrow_grid.data()) : d_bank->read_grid(d_slot, d_grid.data());
+            if (!got) std::cerr << "pcps_acquisition_b200: cannot read the magnitude grid for the dump\n";
         }
     const uint32_t indext = res.code_phase;
     const int32_t doppler = res.doppler_hz;
@@ -438,6 +551,10 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
 
     if ((d_num_noncoherent_integrations_counter == d_acq_parameters.max_dwells) || (d_positive_acq == 1) || d_acq_parameters.bit_transition_flag)  // :869-880
         {
+            if (dumping())  // :875-878
+                {
+                    dump_results(static_cast<int32_t>(d_acq_parameters.bit_transition_flag ? d_fft_size / 2 : d_fft_size));
+                }
             d_num_noncoherent_integrations_counter = 0U;
             d_positive_acq = 0;
             d_bank->reset(d_slot);  // the next dwell starts a fresh grid (:672-676 overwrite on counter == 1)

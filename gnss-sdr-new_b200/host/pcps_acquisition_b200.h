@@ -8,8 +8,10 @@
  * compiled and tested here; INTEGRATION.md shows the 30-line gr::block shell that forwards general_work to it.
  *
  * make_2_steps is mirrored: the narrow second search runs on the bank's second-step engine handle.
- * Not mirrored (N4 and the fork's private mode): make_repeat_steps, MAT-file dumps. A configuration asking for them
- * is rejected in the constructor (std::invalid_argument) instead of being ignored.
+ * dump = true (N4) writes the reference's per-acquisition .mat file (same name pattern, variables, classes and shapes,
+ * :408-508) in the Level-5 container (b200_mat_writer.h) instead of matio's v7.3.
+ * Not mirrored: the fork's private make_repeat_steps mode. A configuration asking for it is rejected in the
+ * constructor (std::invalid_argument) instead of being ignored.
  */
 #ifndef GNSS_SDR_PCPS_ACQUISITION_B200_H
 #define GNSS_SDR_PCPS_ACQUISITION_B200_H
@@ -30,6 +32,7 @@
 #include <memory>
 #include <mutex>
 #include <queue>
+#include <string>
 #include <vector>
 
 class pcps_acquisition_b200;
@@ -49,7 +52,7 @@ public:
     void set_resampler_latency(uint32_t latency_samples);
     uint32_t mag() const { return d_mag; }
     void set_active(bool active);
-    void set_channel(uint32_t channel) { d_channel = channel; }
+    void set_channel(uint32_t channel);
     void set_channel_fsm(std::weak_ptr<ChannelFsm> channel_fsm) { d_channel_fsm = std::move(channel_fsm); }
     void set_threshold(float threshold);
     void set_doppler_max(uint32_t doppler_max);
@@ -80,6 +83,9 @@ private:
     bool is_fdma();
     void calculate_threshold();
     void refresh_doppler_grid();
+    void attach_engine();
+    void dump_results(int32_t effective_fft_size);
+    bool dumping() const { return d_dump && d_channel == d_dump_channel; }
     void require_engine(const char* where) const;
 
     std::recursive_mutex d_setlock;  // gr::block::d_setlock in the reference
@@ -88,6 +94,10 @@ private:
     std::vector<std::complex<float>> d_data_buffer;
     std::vector<int16_t> d_data_buffer_sc;  // interleaved lv_16sc_t
     std::vector<std::complex<float>> d_code_copy;
+    std::vector<float> d_grid;         // [num_doppler_bins][effective size] = arma::fmat(effective, bins) in memory
+    std::vector<float> d_narrow_grid;  // [num_doppler_bins_step2][effective size]
+    std::string d_dump_filename;
+    int64_t d_dump_number{0};
     std::weak_ptr<ChannelFsm> d_channel_fsm;
     Acq_Conf d_acq_parameters;
     Gnss_Synchro* d_gnss_synchro{nullptr};
@@ -104,6 +114,7 @@ private:
     int32_t d_doppler_center{0};
     int32_t d_doppler_bias{0};
     uint32_t d_channel{0};
+    uint32_t d_dump_channel{0};
     uint32_t d_samplesPerChip{0};
     uint32_t d_doppler_step{0};
     uint32_t d_num_noncoherent_integrations_counter{0};
@@ -114,6 +125,7 @@ private:
     uint32_t d_buffer_count{0};
     bool d_active{false};
     bool d_step_two{false};
+    bool d_dump{false};
     bool d_worker_active{false};
     bool d_cshort{false};
     bool d_use_CFAR_algorithm_flag{true};

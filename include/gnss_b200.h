@@ -292,6 +292,7 @@ extern "C"
         double carr_error_hz, carr_error_filt_hz, code_error_chips, code_error_filt_chips;
         double rem_code_phase_samples, acc_carrier_phase_rad;
         double cn0_db_hz, carrier_lock_test;
+        double evm;                   /* d_EVM, the fork's error-vector-magnitude indicator over the prompt buffer (:1027-1053) */
         uint64_t sample_counter;      /* absolute index of the first sample correlated in this epoch */
         int32_t prn_length_samples;   /* samples consumed after this epoch (d_current_prn_length_samples) */
         uint32_t flags;               /* GNSS_B200_TRK_* */

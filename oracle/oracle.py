@@ -60,7 +60,7 @@ TRK_EPOCH_DTYPE = np.dtype([("corr", np.float32, (10,)), ("carrier_doppler_hz", 
                             ("carr_error_hz", np.float64), ("carr_error_filt_hz", np.float64), ("code_error_chips", np.float64),
                             ("code_error_filt_chips", np.float64), ("rem_code_phase_samples", np.float64),
                             ("acc_carrier_phase_rad", np.float64), ("cn0_db_hz", np.float64), ("carrier_lock_test", np.float64),
-                            ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32)], align=True)
+                            ("evm", np.float64), ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32)], align=True)
 
 
 def build(ref=None):

@@ -316,7 +316,7 @@ struct oracle_trk
     double carrier_doppler_hz, carrier_phase_step_rad, code_freq_chips, code_phase_step_chips;
     double rem_code_phase_samples, rem_code_phase_chips, acc_carrier_phase_rad;
     double carr_phase_error_hz, carr_freq_error_hz, carr_error_filt_hz, code_error_chips, code_error_filt_chips;
-    double cn0_db_hz, carrier_lock_test;
+    double cn0_db_hz, carrier_lock_test, evm;
     uint64_t cursor, acq_sample_stamp;
     float rem_carr_phase_rad;
     float P_old[2];
@@ -366,6 +366,7 @@ void oracle_trk_start(oracle_trk* t, double acq_delay_samples, double acq_dopple
     t->acc_carrier_phase_rad = 0.0;
     t->cn0_counter = 0;
     t->carrier_lock_test = 1.0;
+    t->evm = 0.0; /* :845 */
     t->cn0_db_hz = 0.0;
     t->P_old[0] = t->P_old[1] = 0.0f;
     t->carr_phase_error_hz = t->carr_freq_error_hz = t->carr_error_filt_hz = t->code_error_chips = t->code_error_filt_chips = 0.0;
@@ -444,6 +445,25 @@ static int cn0_and_tracking_lock_status(oracle_trk* t, const float* P, double co
             t->code_lock_fail = 0;
             return 0;
         }
+    /* EVM indicator of the fork (dll_pll_veml_tracking.cc:1027-1053): prompt buffer scaled by the RMS of its real parts,
+     * distance of (|I|, |Q|) from (1, 0); binary32 sums in buffer order, reached only when the lock test passed */
+    {
+        const float Prompt_I_ref = 1, Prompt_Q_ref = 0;
+        float tmp_sum = 0;
+        for (int i = 0; i < c->cn0_samples; i++) tmp_sum = tmp_sum + t->prompt_buf[2 * i] * t->prompt_buf[2 * i];
+        float d = tmp_sum / (float)c->cn0_samples;
+        d = sqrtf(d);
+        tmp_sum = 0;
+        for (int i = 0; i < c->cn0_samples; i++)
+            {
+                const float a = fabsf(t->prompt_buf[2 * i] / d) - Prompt_I_ref;
+                const float b = fabsf(t->prompt_buf[2 * i + 1] / d) - Prompt_Q_ref;
+                const float aa = a * a, bb = b * b;
+                tmp_sum = tmp_sum + aa + bb;
+            }
+        t->evm = (double)(tmp_sum / (float)c->cn0_samples / (Prompt_I_ref * Prompt_I_ref + Prompt_Q_ref * Prompt_Q_ref));
+        t->evm = sqrt(t->evm);
+    }
     return 1;
 }
 
@@ -556,6 +576,7 @@ int oracle_trk_run(oracle_trk* t, const float* samples_c64, uint64_t stream_star
             o->acc_carrier_phase_rad = t->acc_carrier_phase_rad;
             o->cn0_db_hz = t->cn0_db_hz;
             o->carrier_lock_test = t->carrier_lock_test;
+            o->evm = t->evm;
             o->sample_counter = nread;
             o->prn_length_samples = t->current_prn_length_samples;
             t->cursor += (uint64_t)t->current_prn_length_samples; /* consume_each */

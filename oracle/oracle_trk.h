@@ -35,6 +35,7 @@ extern "C"
         float corr[10];
         double carrier_doppler_hz, code_freq_chips, carr_error_hz, carr_error_filt_hz, code_error_chips, code_error_filt_chips;
         double rem_code_phase_samples, acc_carrier_phase_rad, cn0_db_hz, carrier_lock_test;
+        double evm;
         uint64_t sample_counter;
         int32_t prn_length_samples;
         uint32_t flags;

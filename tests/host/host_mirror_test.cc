@@ -8,7 +8,9 @@
  */
 #include "b200_acquisition_bank.h"
 #include "b200_correlator_pool.h"
+#include "b200_mat_writer.h"
 #include "b200_multicorrelator.h"
+#include "b200_tracking_dump.h"
 #include "b200_multicorrelator_real_codes.h"
 #include "pcps_acquisition_b200.h"
 #include <algorithm>
@@ -119,6 +121,11 @@ int run_acq(const char* in_path, const char* out_path)
             conf.num_doppler_bins_step2 = r.get<uint32_t>();
             conf.doppler_step2 = r.get<float>();
             conf.pfa2 = r.get<float>();
+            conf.dump = r.get<uint32_t>() != 0;
+            conf.dump_channel = r.get<uint32_t>();
+            const auto len = r.get<uint32_t>();
+            const auto name = r.vec<char>(len);
+            conf.dump_filename.assign(name.begin(), name.end());
         }
 
     B200_Acquisition_Bank::set_default_capacity(std::max(1U, n_blocks));
@@ -303,6 +310,44 @@ int run_nodevice()
     std::cout << "mc.init=" << (init_ok ? "true" : "false") << " acq_threw=" << (threw ? "true" : "false") << '\n';
     return (!init_ok && threw) ? 0 : 4;
 }
+// A MAT file with one variable of every class the dump uses; tests/test_host_cpu.py reads it back with scipy.
+int run_mat(const char* out_path)
+{
+    B200_Mat_Writer mat;
+    if (!mat.open(out_path)) return 3;
+    std::vector<float> grid(7 * 3);
+    for (size_t i = 0; i < grid.size(); i++) grid[i] = 0.5F * static_cast<float>(i);  // column-major 7 x 3
+    bool ok = mat.write_single("acq_grid", grid.data(), 7, 3);
+    ok = ok && mat.write_int32("doppler_max", -5000);
+    ok = ok && mat.write_uint32("PRN", 4000000000U);
+    ok = ok && mat.write_uint64("sample_counter", 0x123456789ABCDEFULL);
+    ok = ok && mat.write_single("threshold", 2.5F);
+    ok = ok && mat.write_double("x", 1.0 / 3.0);
+    const int32_t v[5] = {1, -2, 3, -4, 5};
+    ok = ok && mat.write_int32("odd_length_name_", v, 1, 5);
+    ok = ok && !mat.write_single("", 1.0F);  // refused, nothing written
+    return (ok && mat.close()) ? 0 : 4;
+}
+// Tracking dump: <in> = u32 n, u32 veml, u32 channel, u32 prn, f64 acq code phase, f64 acq Doppler, then n
+// gnss_b200_trk_epoch records (as gnss_b200_trk_run returns them); <out> = the configured dump_filename.
+int run_trkdump(const char* in_path, const char* dump_filename)
+{
+    Reader r(in_path);
+    const auto n = r.get<uint32_t>();
+    const bool veml = r.get<uint32_t>() != 0;
+    const auto channel = r.get<uint32_t>();
+    const auto prn = r.get<uint32_t>();
+    const auto acq_phase = r.get<double>();
+    const auto acq_doppler = r.get<double>();
+    const auto epochs = r.vec<gnss_b200_trk_epoch>(n);
+    B200_Tracking_Dump dump;
+    if (!dump.configure(dump_filename, true)) return 3;
+    if (!dump.set_channel(channel)) return 4;
+    dump.set_acquisition(prn, acq_phase, acq_doppler);
+    // two calls, as two gnss_b200_trk_run blocks would deliver them
+    if (!dump.log(epochs.data(), n / 2, veml) || !dump.log(epochs.data() + n / 2, n - n / 2, veml)) return 5;
+    return dump.finish() == 0 ? 0 : 6;
+}
 }  // namespace
 
 int main(int argc, char** argv)
@@ -312,12 +357,14 @@ int main(int argc, char** argv)
             if (argc == 4 && std::strcmp(argv[1], "acq") == 0) return run_acq(argv[2], argv[3]);
             if (argc == 4 && std::strcmp(argv[1], "mc") == 0) return run_mc(argv[2], argv[3]);
             if (argc == 2 && std::strcmp(argv[1], "nodevice") == 0) return run_nodevice();
+            if (argc == 3 && std::strcmp(argv[1], "mat") == 0) return run_mat(argv[2]);
+            if (argc == 4 && std::strcmp(argv[1], "trkdump") == 0) return run_trkdump(argv[2], argv[3]);
         }
     catch (const std::exception& e)
         {
             std::cerr << "host_mirror_test: " << e.what() << '\n';
             return 2;
         }
-    std::cerr << "usage: host_mirror_test acq|mc <in> <out> | nodevice\n";
+    std::cerr << "usage: host_mirror_test acq|mc <in> <out> | trkdump <in> <dump_filename> | mat <out> | nodevice\n";
     return 1;
 }

@@ -59,7 +59,7 @@ def test_mirror_keeps_the_reference_method_set():
 
 
 def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, doppler_step, pfa, threshold, max_dwells, bit_transition,
-                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us, two_steps=None):
+                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us, two_steps=None, dump=None):
     with open(path, "wb") as f:
         f.write(struct.pack("<q", int(fs)))
         f.write(struct.pack("<IIIiI", sampled_ms, ms_per_code, spc, doppler_max, doppler_step))
@@ -70,8 +70,12 @@ def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, dopple
         for c in codes:
             f.write(np.ascontiguousarray(c, dtype=np.complex64).tobytes())
         f.write(np.ascontiguousarray(stream, dtype=np.int16 if cshort else np.complex64).tobytes())
-        if two_steps is not None:          # (second_nbins, second_doppler_step, pfa2)
-            f.write(struct.pack("<IIff", 1, int(two_steps[0]), float(two_steps[1]), float(two_steps[2])))
+        if two_steps is not None or dump is not None:
+            ts = two_steps or (0, 125.0, 0.0)             # (second_nbins, second_doppler_step, pfa2)
+            f.write(struct.pack("<IIff", int(two_steps is not None), int(ts[0]), float(ts[1]), float(ts[2])))
+            name = (dump[1] if dump else "").encode()     # dump = (dump_channel, dump_filename)
+            f.write(struct.pack("<III", int(dump is not None), int(dump[0]) if dump else 0, len(name)))
+            f.write(name)
 
 
 def _read_acq_output(path):
@@ -246,3 +250,138 @@ def test_two_step_acquisition_through_the_block_interface(driver, oracle, tmp_pa
             assert g["stat"] == pytest.approx(w1["test_statistic"], rel=1e-4)
         acq.close()
     assert n_two >= 1
+
+
+def test_mat_writer_is_read_by_scipy(driver, tmp_path):
+    """b200_mat_writer: Level-5 MAT container with the classes the acquisition dump uses (pcps_acquisition.cc:425-500)."""
+    from scipy.io import loadmat
+    out = tmp_path / "t.mat"
+    r = subprocess.run([driver, "mat", str(out)], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout + r.stderr
+    m = loadmat(str(out))
+    assert m["acq_grid"].dtype == np.float32 and m["acq_grid"].shape == (7, 3)
+    assert np.array_equal(m["acq_grid"], (0.5 * np.arange(21, dtype=np.float32)).reshape(3, 7).T)
+    assert m["doppler_max"].dtype == np.int32 and int(m["doppler_max"][0, 0]) == -5000
+    assert m["PRN"].dtype == np.uint32 and int(m["PRN"][0, 0]) == 4000000000
+    assert m["sample_counter"].dtype == np.uint64 and int(m["sample_counter"][0, 0]) == 0x123456789ABCDEF
+    assert m["threshold"].dtype == np.float32 and float(m["threshold"][0, 0]) == 2.5
+    assert m["x"].dtype == np.float64 and float(m["x"][0, 0]) == 1.0 / 3.0
+    assert np.array_equal(m["odd_length_name_"], np.array([[1, -2, 3, -4, 5]], dtype=np.int32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("two_steps", [False, True])
+def test_acquisition_dump_file(driver, oracle, tmp_path, two_steps):
+    """dump = true (pcps_acquisition.cc:135-165, 408-508, 875-878): channel `dump_channel` writes
+    <dump_filename>_<System>_<Signal>_ch_<channel>_<n>_sat_<PRN>.mat with the magnitude grid (effective size x Doppler bins,
+    column per bin) and the scalars of the decision; with make_two_steps also the narrow grid and its geometry."""
+    from scipy.io import loadmat
+    geo, codes, iq, truth = synth.config_scene("C1", n_prn=4, n_dwells=6)
+    stream = iq.reshape(-1)
+    def first_stat(p):
+        a = oracle.acq(fft_size=4000, consumed_samples=4000, doppler_max=geo["doppler_max"], doppler_step=geo["doppler_step"],
+                       fs=geo["fs"], samples_per_chip=geo["samples_per_chip"], samples_per_code=geo["samples_per_code"])
+        a.set_local_code(codes[p])
+        v = a.dwell(stream[:4000])["test_statistic"]
+        a.close()
+        return v
+    strong = int(np.argmax([first_stat(p) for p in range(4)]))      # the channel that certainly reaches the second step
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_acq_input(inp, geo["fs"], 1, 1, geo["samples_per_chip"], geo["doppler_max"], geo["doppler_step"], 0.01, 0.0, 1, False, True,
+                     False, True, list(codes), stream, 4000, False, 0, two_steps=(4, 125.0, 0.02) if two_steps else None,
+                     dump=(strong, str(tmp_path / "dumps" / "acq_dump.dat")))
+    _run(driver, "acq", inp, outp)
+    got = _read_acq_output(outp)[strong]
+    files = sorted(os.listdir(tmp_path / "dumps"))
+    assert files == ["acq_dump_G_1C_ch_%d_1_sat_%d.mat" % (strong, strong + 1)]     # only the dump channel writes, extension dropped
+    m = loadmat(str(tmp_path / "dumps" / files[0]))
+    acq = oracle.acq(fft_size=4000, consumed_samples=4000, doppler_max=geo["doppler_max"], doppler_step=geo["doppler_step"],
+                     fs=geo["fs"], samples_per_chip=geo["samples_per_chip"], samples_per_code=geo["samples_per_code"])
+    acq.set_local_code(codes[strong])
+    w1 = acq.dwell(stream[:4000])
+    assert m["acq_grid"].dtype == np.float32 and m["acq_grid"].shape == (4000, 40)
+    np.testing.assert_allclose(m["acq_grid"].T, acq.grid()[:, :4000], rtol=2e-4, atol=2e-4 * w1["peak"])
+    assert int(m["doppler_max"][0, 0]) == geo["doppler_max"] and int(m["doppler_step"][0, 0]) == geo["doppler_step"]
+    assert int(m["PRN"][0, 0]) == strong + 1 and int(m["d_positive_acq"][0, 0]) == int(got["event"] == 1) and int(m["num_dwells"][0, 0]) == 1
+    assert w1["test_statistic"] > got["threshold"]
+    assert float(m["input_power"][0, 0]) == pytest.approx(w1["input_power"], rel=1e-4)
+    assert float(m["threshold"][0, 0]) == pytest.approx(got["threshold"], rel=1e-6)
+    assert float(m["acq_doppler_hz"][0, 0]) == got["doppler"] and float(m["acq_delay_samples"][0, 0]) == got["delay"]
+    assert float(m["test_statistic"][0, 0]) == pytest.approx(got["stat"], rel=1e-6)
+    assert m["sample_counter"].dtype == np.uint64 and int(m["sample_counter"][0, 0]) == got["stamp"]
+    if two_steps:
+        w2 = acq.dwell_step2(stream[12000:16000], 4, 125.0, float(w1["doppler_hz"]))
+        assert m["acq_grid_narrow"].shape == (4000, 4)
+        assert float(m["acq_grid_narrow"].max()) == pytest.approx(w2["peak"], rel=2e-4)
+        assert np.unravel_index(np.argmax(m["acq_grid_narrow"].T), (4, 4000)) == (w2["doppler_index"], w2["code_phase"])
+        assert float(m["doppler_step_narrow"][0, 0]) == 125.0
+        assert float(m["doppler_grid_narrow_min"][0, 0]) == float(w1["doppler_hz"]) - 2 * 125.0
+    else:
+        assert "acq_grid_narrow" not in m
+
+
+# one record of dll_pll_veml_tracking::log_data() (dll_pll_veml_tracking.cc:1445-1502), in file order
+TRK_DUMP_DTYPE = np.dtype([("abs_VE", "<f4"), ("abs_E", "<f4"), ("abs_P", "<f4"), ("abs_L", "<f4"), ("abs_VL", "<f4"), ("Prompt_I", "<f4"),
+                           ("Prompt_Q", "<f4"), ("PRN_start_sample_count", "<u8"), ("acc_carrier_phase_rad", "<f4"),
+                           ("carrier_doppler_hz", "<f4"), ("carrier_doppler_rate_hz", "<f4"), ("code_freq_chips", "<f4"),
+                           ("code_freq_rate_chips", "<f4"), ("carr_error_hz", "<f4"), ("carr_error_filt_hz", "<f4"),
+                           ("code_error_chips", "<f4"), ("code_error_filt_chips", "<f4"), ("CN0_SNV_dB_Hz", "<f4"),
+                           ("carrier_lock_test", "<f4"), ("aux1", "<f4"), ("aux2", "<f8"), ("PRN", "<u4"),
+                           ("acq_code_phase_samples", "<f4"), ("acq_carrier_doppler_hz", "<f4"), ("EVM", "<f4")])
+
+
+@pytest.mark.parametrize("veml", [False, True])
+def test_tracking_dump_files(driver, oracle, oracle_mod, tmp_path, veml):
+    """B200_Tracking_Dump: epoch records of the tracking loop (here the oracle's, same layout as gnss_b200_trk_epoch) become
+    the reference's <dump_filename><channel>.dat (108-byte records, log_data :1403-1509) and .mat (save_matfile :1511-1735:
+    one 1 x num_epoch variable per field, same names and classes)."""
+    from scipy.io import loadmat
+    assert TRK_DUMP_DTYPE.itemsize == 108
+    system = "gal_e1b" if veml else "gps_l1_ca"
+    chip_rate, code_len, _ = synth.SYSTEMS[system]
+    fs = 4e6
+    iq, truth, carrier = synth.tracking_stream(system, [7], fs, 120, seed=5, cn0=47.0, dopplers=[1500.0], delays=[321.6],
+                                               code_samples_per_chip=2 if veml else 1)
+    cfg = oracle_mod.TrkCfg(fs_in=fs, code_chip_rate=chip_rate, signal_carrier_freq=carrier, code_period_s=code_len / chip_rate,
+                            code_length_chips=code_len, code_samples_per_chip=2 if veml else 1, vector_length=int(round(fs * code_len / chip_rate)),
+                            veml=int(veml), early_late_space_chips=0.15 if veml else 0.25, very_early_late_space_chips=0.5, slope=1.0, y_intercept=1.0,
+                            pll_bw_hz=35.0, dll_bw_hz=2.0, fll_bw_hz=35.0, pll_filter_order=3, dll_filter_order=2, enable_fll_pull_in=1,
+                            enable_fll_steady_state=0, carrier_aiding=1, pull_in_time_s=0, cn0_samples=20, cn0_min=25, max_code_lock_fail=50,
+                            max_carrier_lock_fail=5000, carrier_lock_th=0.7, cn0_smoother_alpha=0.002, carrier_lock_test_smoother_alpha=0.002,
+                            cn0_smoother_samples=200, carrier_lock_test_smoother_samples=25, max_channels=1, device=0)
+    trk = oracle.trk(cfg)
+    trk.set_code(synth.tracking_code(system, 7))
+    trk.start(acq_delay_samples=322.0, acq_doppler_hz=1460.0, acq_samplestamp=0, now_sample=2000)
+    ep, done = trk.run(iq, 0, 40)
+    trk.close()
+    ep = ep[:done + 1]                                            # the record after the last one is not valid: it must be skipped
+    assert (ep["flags"][:done] & 1).all() and done >= 20
+    inp = tmp_path / "ep.bin"
+    with open(inp, "wb") as f:
+        f.write(struct.pack("<IIIIdd", len(ep), int(veml), 3, 7, 322.0, 1460.0))
+        f.write(ep.tobytes())
+    r = subprocess.run([driver, "trkdump", str(inp), str(tmp_path / "trk" / "track_ch_.bin")], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert sorted(os.listdir(tmp_path / "trk")) == ["track_ch_3.dat", "track_ch_3.mat"]
+    rec = np.fromfile(tmp_path / "trk" / "track_ch_3.dat", dtype=TRK_DUMP_DTYPE)
+    ok = ep[:done]
+    assert len(rec) == done
+    z = ok["corr"].reshape(-1, 5, 2)
+    mag = np.abs(z[..., 0].astype(np.complex64) + 1j * z[..., 1].astype(np.complex64)).astype(np.float32)
+    for k, name in enumerate(["abs_VE", "abs_E", "abs_P", "abs_L", "abs_VL"]):
+        want = mag[:, k] if (veml or k in (1, 2, 3)) else np.zeros(done, np.float32)
+        np.testing.assert_allclose(rec[name], want, rtol=1e-6)
+    assert np.array_equal(rec["Prompt_I"], ok["corr"][:, 4]) and np.array_equal(rec["Prompt_Q"], ok["corr"][:, 5])
+    stamp = ok["sample_counter"] + ok["prn_length_samples"].astype(np.uint64)
+    assert np.array_equal(rec["PRN_start_sample_count"], stamp) and np.array_equal(rec["aux2"], stamp.astype(np.float64))
+    for name, src in [("acc_carrier_phase_rad", "acc_carrier_phase_rad"), ("carrier_doppler_hz", "carrier_doppler_hz"),
+                      ("code_freq_chips", "code_freq_chips"), ("carr_error_hz", "carr_error_hz"), ("carr_error_filt_hz", "carr_error_filt_hz"),
+                      ("code_error_chips", "code_error_chips"), ("code_error_filt_chips", "code_error_filt_chips"), ("CN0_SNV_dB_Hz", "cn0_db_hz"),
+                      ("carrier_lock_test", "carrier_lock_test"), ("aux1", "rem_code_phase_samples"), ("EVM", "evm")]:
+        assert np.array_equal(rec[name], ok[src].astype(np.float32)), name
+    assert (rec["carrier_doppler_rate_hz"] == 0).all() and (rec["code_freq_rate_chips"] == 0).all()
+    assert (rec["PRN"] == 7).all() and (rec["acq_code_phase_samples"] == 322.0).all() and (rec["acq_carrier_doppler_hz"] == 1460.0).all()
+    m = loadmat(str(tmp_path / "trk" / "track_ch_3.mat"))
+    for name in TRK_DUMP_DTYPE.names:
+        assert m[name].shape == (1, done) and m[name].dtype == TRK_DUMP_DTYPE[name].newbyteorder("="), name
+        assert np.array_equal(m[name][0], rec[name]), name

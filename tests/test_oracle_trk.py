@@ -144,6 +144,13 @@ def test_closed_loop_converges_on_injected_signal(oracle, oracle_mod, system, ve
     P = tail["corr"][:, 4] + 1j * tail["corr"][:, 5]
     E = tail["corr"][:, 2] + 1j * tail["corr"][:, 3]
     assert np.mean(np.abs(P)) > 1.1 * np.mean(np.abs(E))
+    # the fork's EVM indicator (dll_pll_veml_tracking.cc:1027-1053) over the last cn0_samples prompts, recomputed in float64
+    for j in (len(ok) - 1, len(ok) - 37):
+        buf = ok["corr"][j - 19:j + 1, 4].astype(np.float64) + 1j * ok["corr"][j - 19:j + 1, 5].astype(np.float64)
+        d = np.sqrt(np.mean(buf.real ** 2))
+        evm = np.sqrt(np.mean((np.abs(buf.real / d) - 1.0) ** 2 + np.abs(buf.imag / d) ** 2))
+        assert ok["evm"][j] == pytest.approx(evm, rel=1e-5) and 0.02 < evm < 0.5
+    assert ok["evm"][0] == 0.0                                # nothing before the prompt buffer has filled (:845, :975-979)
     period = fs * code_len / t["code_rate"]
     assert np.all(np.abs(np.mod(tail["sample_counter"].astype(np.float64) - tail["rem_code_phase_samples"] * 0 - t["delay"] + period / 2, period) - period / 2) < 2.5)
     trk.close()

@@ -48,6 +48,7 @@ def _compare(gpu, want, n_min):
     # the M2M4 estimator takes sqrt(2*m2^2 - m4), a difference of nearly equal numbers: 1e-4 in P becomes ~1e-2 dB
     assert np.abs(gpu["cn0_db_hz"][ok] - want["cn0_db_hz"][ok]).max() <= 0.1
     assert np.abs(gpu["carrier_lock_test"][ok] - want["carrier_lock_test"][ok]).max() <= 5e-3
+    assert np.abs(gpu["evm"][ok] - want["evm"][ok]).max() <= 2e-3 and want["evm"][ok].max() > 0.02   # ~1e-4 in P over 20 prompts
     assert np.abs(gpu["code_error_chips"][ok] - want["code_error_chips"][ok]).max() <= 1e-2
     assert np.median(np.abs(gpu["code_error_chips"][ok] - want["code_error_chips"][ok])) <= 1e-4
 
