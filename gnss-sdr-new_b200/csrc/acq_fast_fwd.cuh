@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(kFastThreads) fwd_upper_kernel(const FastFwdAr
                             const WipePiece pc = s_pieces[cur];
                             const float phi = fmaf((float)(pos - pc.start), pc.step, pc.phi0);  // exact inside a piece
                             float sn, cs;
-                            sincosf(phi, &sn, &cs);  // volk_gnsssdr_s32f_sincos_32fc
+                            wipeoff_sincos(phi, sn, cs);  // volk_gnsssdr_s32f_sincos_32fc
                             w = make_float2(x.x * cs - x.y * sn, x.x * sn + x.y * cs);  // :658
                         }
                     v[b] = w;
@@ -108,10 +108,17 @@ __global__ void __launch_bounds__(kFastThreads) fwd_upper_kernel(const FastFwdAr
 #pragma unroll
             for (int q = 0; q < RA; q++) v[q] = s[(size_t)(q + RA * ub) * C + c];
             fft::Dft<RA, false>::run(v);
+            // W_N^(k1*m) = W_N^(ub*m) * (W_N^(RB*m))^uah: the table is read at every 8th uah only (a gather: neighbouring
+            // columns sit k1 entries apart) and stepped in between, which keeps the recurrence error below 1e-6
+            const float2 st = __ldg(a.W + (size_t)RB * m);  // RB * m < N
+            float2 tw = make_float2(1.f, 0.f);
 #pragma unroll
             for (int uah = 0; uah < RA; uah++)
                 {
-                    const float2 tw = __ldg(a.W + (size_t)(uah * RB + ub) * m);  // k1 * m < N
+                    if (uah % 8 == 0)
+                        tw = __ldg(a.W + (size_t)(uah * RB + ub) * m);  // k1 * m < N
+                    else
+                        tw = fft::cmul(tw, st);
                     out[(size_t)(uah + RA * ub) * a.M_lo] = fft::cmul(v[uah], tw);
                 }
         }

@@ -18,6 +18,19 @@
 
 namespace b200
 {
+
+// (cos phi, sin phi) of a wipe-off phase (volk_gnsssdr_s32f_sincos_32fc): two-constant Cody-Waite reduction to [-pi, pi]
+// (exact for the |phi| < 2^15 rad a dwell accumulates) and the SFU's MUFU.SIN / MUFU.COS, absolute error 2^-21.4 there — below
+// the spread between the reference's own protokernels (libm in the generic one, polynomials in the SIMD ones).
+__device__ __forceinline__ void wipeoff_sincos(float phi, float& sn, float& cs)
+{
+    const float k = rintf(phi * 0.15915494309189535f);
+    float r = fmaf(-k, 6.2831854820251465f, phi);   // float(2 pi)
+    r = fmaf(-k, -1.7484555314695172e-07f, r);      // 2 pi - float(2 pi)
+    sn = __sinf(r);
+    cs = __cosf(r);
+}
+
 // Piecewise-linear description of the reference's binary32 running-sum phase (see wipeoff_pieces.cc):
 // for start <= n < next.start the reference's _phase at sample n is exactly phi0 + (n - start) * step.
 struct WipePiece
@@ -170,7 +183,7 @@ __global__ void __launch_bounds__(512) stage_kernel(const StageArgs a)
                             // exact: the value is representable, the fma rounds once
                             const float phi = fmaf((float)(pos - pc.start), pc.step, pc.phi0);
                             float sn, cs;
-                            sincosf(phi, &sn, &cs);  // wipe-off sample (cos phi, sin phi), volk_gnsssdr_s32f_sincos_32fc
+                            wipeoff_sincos(phi, sn, cs);  // wipe-off sample (cos phi, sin phi), volk_gnsssdr_s32f_sincos_32fc
                             v = make_float2(x.x * cs - x.y * sn, x.x * sn + x.y * cs);  // :658
                         }
                     s[i] = v;
