@@ -58,7 +58,7 @@ constexpr int kFastThreads = 256;
 // lower stage: grid (rows, M_hi / nb). Shared memory: nb * PITCH * RB data + M twiddles.
 // ------------------------------------------------------------------------------------------------
 template <int RA, int RB>
-__global__ void __launch_bounds__(kFastThreads) inv_lower_kernel(const FastArgs a)
+__global__ void __launch_bounds__(kFastThreads, 4) inv_lower_kernel(const FastArgs a)
 {
     constexpr int M = RA * RB;
     constexpr int P = (RA % 2 == 0) ? RA + 1 : RA;  // odd pitch: conflict-free 64-bit stores with stride P

@@ -75,6 +75,35 @@ __device__ __forceinline__ void static_for(F&& f)
     static_for_impl(static_cast<F&&>(f), std::make_integer_sequence<int, N>{});
 }
 
+// ---------------- value types ----------------
+// The codelets are written once over a scalar type T. The kernels use T = float (complex value = float2). A packed
+// FP32x2 scalar (two transforms per thread in the lanes of FADD2 / FFMA2) was measured with tools/scratch/dft_pack_bench.cu:
+// the packed instructions issue at half rate, so points/s of the codelets do not change (radix 16: 3.37 vs 3.39 T points/s
+// on B200) and the kernels, which are not issue-bound, keep the scalar form.
+using ::fmaf;
+template <class T>
+struct cx  // complex value over T; cx<float> has the layout of float2
+{
+    T x, y;
+};
+template <class T>
+__device__ __forceinline__ cx<T> make_cx(T x, T y)
+{
+    return cx<T>{x, y};
+}
+template <class T>
+__device__ __forceinline__ T zero_of();
+template <>
+__device__ __forceinline__ float zero_of<float>()
+{
+    return 0.f;
+}
+
+template <class T>
+__device__ __forceinline__ cx<T> cmul(const cx<T> a, const cx<T> b)
+{
+    return make_cx<T>(fmaf(a.x, b.x, -(a.y * b.y)), fmaf(a.x, b.y, a.y * b.x));
+}
 __device__ __forceinline__ float2 cmul(const float2 a, const float2 b)
 {
     return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
@@ -85,8 +114,8 @@ __device__ __forceinline__ float2 cmul_conj(const float2 a, const float2 b)  // 
 }
 
 // x *= exp(-/+ 2*pi*i*E/R) with E, R compile-time (sign '-' forward, '+' inverse)
-template <int E_, int R, bool INV>
-__device__ __forceinline__ void mul_root(float2& x)
+template <int E_, int R, bool INV, class T>
+__device__ __forceinline__ void mul_root(cx<T>& x)
 {
     constexpr int E = ((E_ % R) + R) % R;
     if constexpr (E == 0)
@@ -94,15 +123,15 @@ __device__ __forceinline__ void mul_root(float2& x)
         }
     else if constexpr (2 * E == R)
         {
-            x = make_float2(-x.x, -x.y);
+            x = make_cx<T>(-x.x, -x.y);
         }
     else if constexpr (4 * E == R)  // -i (fwd) / +i (inv)
         {
-            x = INV ? make_float2(-x.y, x.x) : make_float2(x.y, -x.x);
+            x = INV ? make_cx<T>(-x.y, x.x) : make_cx<T>(x.y, -x.x);
         }
     else if constexpr (4 * E == 3 * R)  // +i (fwd) / -i (inv)
         {
-            x = INV ? make_float2(x.y, -x.x) : make_float2(-x.y, x.x);
+            x = INV ? make_cx<T>(x.y, -x.x) : make_cx<T>(-x.y, x.x);
         }
     else if constexpr ((8 * E) % R == 0)  // odd multiples of pi/4
         {
@@ -113,18 +142,18 @@ __device__ __forceinline__ void mul_root(float2& x)
             constexpr float s0 = (o == 1 || o == 3) ? h : -h;
             constexpr float s = INV ? -s0 : s0;  // forward multiplies by (c - i s0)
             // (x.x + i x.y)(c - i s) = (x.x c + x.y s) + i (x.y c - x.x s)
-            const float re = x.x * c + x.y * s;
-            const float im = x.y * c - x.x * s;
-            x = make_float2(re, im);
+            const T re = x.x * c + x.y * s;
+            const T im = x.y * c - x.x * s;
+            x = make_cx<T>(re, im);
         }
     else
         {
             constexpr float c = (float)cx_cos_frac(E, R);
             constexpr float s0 = (float)cx_sin_frac(E, R);
             constexpr float s = INV ? -s0 : s0;
-            const float re = fmaf(x.x, c, x.y * s);
-            const float im = fmaf(x.y, c, -x.x * s);
-            x = make_float2(re, im);
+            const T re = fmaf(x.x, c, x.y * s);
+            const T im = fmaf(x.y, c, x.x * (-s));  // the same bits as -(x.x * s)
+            x = make_cx<T>(re, im);
         }
 }
 
@@ -134,35 +163,43 @@ struct Dft;
 template <bool INV>
 struct Dft<1, INV>
 {
+    template <class T>
+    static __device__ __forceinline__ void run(cx<T> (&)[1])
+    {
+    }
     static __device__ __forceinline__ void run(float2 (&)[1]) {}
 };
 
 template <bool INV>
 struct Dft<2, INV>
 {
-    static __device__ __forceinline__ void run(float2 (&v)[2])
+    static __device__ __forceinline__ void run(float2 (&v)[2]) { run(reinterpret_cast<cx<float>(&)[2]>(v)); }
+    template <class T>
+    static __device__ __forceinline__ void run(cx<T> (&v)[2])
     {
-        const float2 a = v[0], b = v[1];
-        v[0] = make_float2(a.x + b.x, a.y + b.y);
-        v[1] = make_float2(a.x - b.x, a.y - b.y);
+        const cx<T> a = v[0], b = v[1];
+        v[0] = make_cx<T>(a.x + b.x, a.y + b.y);
+        v[1] = make_cx<T>(a.x - b.x, a.y - b.y);
     }
 };
 
 template <bool INV>
 struct Dft<4, INV>
 {
-    static __device__ __forceinline__ void run(float2 (&v)[4])
+    static __device__ __forceinline__ void run(float2 (&v)[4]) { run(reinterpret_cast<cx<float>(&)[4]>(v)); }
+    template <class T>
+    static __device__ __forceinline__ void run(cx<T> (&v)[4])
     {
-        const float2 s02 = make_float2(v[0].x + v[2].x, v[0].y + v[2].y);
-        const float2 d02 = make_float2(v[0].x - v[2].x, v[0].y - v[2].y);
-        const float2 s13 = make_float2(v[1].x + v[3].x, v[1].y + v[3].y);
-        const float2 d13 = make_float2(v[1].x - v[3].x, v[1].y - v[3].y);
+        const cx<T> s02 = make_cx<T>(v[0].x + v[2].x, v[0].y + v[2].y);
+        const cx<T> d02 = make_cx<T>(v[0].x - v[2].x, v[0].y - v[2].y);
+        const cx<T> s13 = make_cx<T>(v[1].x + v[3].x, v[1].y + v[3].y);
+        const cx<T> d13 = make_cx<T>(v[1].x - v[3].x, v[1].y - v[3].y);
         // forward: X1 = d02 - i d13, X3 = d02 + i d13
-        const float2 r = INV ? make_float2(-d13.y, d13.x) : make_float2(d13.y, -d13.x);
-        v[0] = make_float2(s02.x + s13.x, s02.y + s13.y);
-        v[2] = make_float2(s02.x - s13.x, s02.y - s13.y);
-        v[1] = make_float2(d02.x + r.x, d02.y + r.y);
-        v[3] = make_float2(d02.x - r.x, d02.y - r.y);
+        const cx<T> r = INV ? make_cx<T>(-d13.y, d13.x) : make_cx<T>(d13.y, -d13.x);
+        v[0] = make_cx<T>(s02.x + s13.x, s02.y + s13.y);
+        v[2] = make_cx<T>(s02.x - s13.x, s02.y - s13.y);
+        v[1] = make_cx<T>(d02.x + r.x, d02.y + r.y);
+        v[3] = make_cx<T>(d02.x - r.x, d02.y - r.y);
     }
 };
 
@@ -179,26 +216,28 @@ template <int P, bool INV>
 struct Dft<P, INV, std::enable_if_t<is_odd_prime(P)>>
 {
     static constexpr int H = (P - 1) / 2;
-    static __device__ __forceinline__ void run(float2 (&v)[P])
+    static __device__ __forceinline__ void run(float2 (&v)[P]) { run(reinterpret_cast<cx<float>(&)[P]>(v)); }
+    template <class T>
+    static __device__ __forceinline__ void run(cx<T> (&v)[P])
     {
-        float2 tp[H], tm[H];
+        cx<T> tp[H], tm[H];
         static_for<H>([&](auto kc) {
             constexpr int k = decltype(kc)::value + 1;
-            tp[k - 1] = make_float2(v[k].x + v[P - k].x, v[k].y + v[P - k].y);
-            tm[k - 1] = make_float2(v[k].x - v[P - k].x, v[k].y - v[P - k].y);
+            tp[k - 1] = make_cx<T>(v[k].x + v[P - k].x, v[k].y + v[P - k].y);
+            tm[k - 1] = make_cx<T>(v[k].x - v[P - k].x, v[k].y - v[P - k].y);
         });
-        const float2 v0 = v[0];
-        float2 dc = v0;
+        const cx<T> v0 = v[0];
+        cx<T> dc = v0;
         static_for<H>([&](auto kc) {
             constexpr int k = decltype(kc)::value;
-            dc.x += tp[k].x;
-            dc.y += tp[k].y;
+            dc.x = dc.x + tp[k].x;
+            dc.y = dc.y + tp[k].y;
         });
         v[0] = dc;
         static_for<H>([&](auto mc) {
             constexpr int m = decltype(mc)::value + 1;
-            float2 a = v0;                        // cosine part
-            float2 b = make_float2(0.f, 0.f);     // sine part: sum_k sin(2 pi m k / P) * tm[k]
+            cx<T> a = v0;                        // cosine part
+            cx<T> b = make_cx<T>(zero_of<T>(), zero_of<T>());     // sine part: sum_k sin(2 pi m k / P) * tm[k]
             static_for<H>([&](auto kc) {
                 constexpr int k = decltype(kc)::value + 1;
                 constexpr float c = (float)cx_cos_frac((long long)m * k, P);
@@ -211,13 +250,13 @@ struct Dft<P, INV, std::enable_if_t<is_odd_prime(P)>>
             // forward: X[m] = a - i b = (a.x + b.y, a.y - b.x); X[P-m] = a + i b
             if (INV)
                 {
-                    v[m] = make_float2(a.x - b.y, a.y + b.x);
-                    v[P - m] = make_float2(a.x + b.y, a.y - b.x);
+                    v[m] = make_cx<T>(a.x - b.y, a.y + b.x);
+                    v[P - m] = make_cx<T>(a.x + b.y, a.y - b.x);
                 }
             else
                 {
-                    v[m] = make_float2(a.x + b.y, a.y - b.x);
-                    v[P - m] = make_float2(a.x - b.y, a.y + b.x);
+                    v[m] = make_cx<T>(a.x + b.y, a.y - b.x);
+                    v[P - m] = make_cx<T>(a.x - b.y, a.y + b.x);
                 }
         });
     }
@@ -228,11 +267,12 @@ template <int R1, int R2, bool INV>
 struct DftCT
 {
     static constexpr int R = R1 * R2;
-    static __device__ __forceinline__ void run(float2 (&v)[R])
+    template <class T>
+    static __device__ __forceinline__ void run(cx<T> (&v)[R])
     {
         static_for<R2>([&](auto n2c) {
             constexpr int n2 = decltype(n2c)::value;
-            float2 t[R1];
+            cx<T> t[R1];
             static_for<R1>([&](auto n1c) {
                 constexpr int n1 = decltype(n1c)::value;
                 t[n1] = v[R2 * n1 + n2];
@@ -240,14 +280,14 @@ struct DftCT
             Dft<R1, INV>::run(t);
             static_for<R1>([&](auto k1c) {
                 constexpr int k1 = decltype(k1c)::value;
-                mul_root<k1 * n2, R, INV>(t[k1]);
+                mul_root<k1 * n2, R, INV, T>(t[k1]);
                 v[R2 * k1 + n2] = t[k1];
             });
         });
-        float2 o[R];
+        cx<T> o[R];
         static_for<R1>([&](auto k1c) {
             constexpr int k1 = decltype(k1c)::value;
-            float2 t[R2];
+            cx<T> t[R2];
             static_for<R2>([&](auto n2c) {
                 constexpr int n2 = decltype(n2c)::value;
                 t[n2] = v[R2 * k1 + n2];
@@ -269,7 +309,15 @@ struct DftCT
     template <bool INV>                                                                 \
     struct Dft<R, INV>                                                                  \
     {                                                                                   \
-        static __device__ __forceinline__ void run(float2 (&v)[R]) { DftCT<R1, R2, INV>::run(v); } \
+        template <class T>                                                              \
+        static __device__ __forceinline__ void run(cx<T> (&v)[R])                        \
+        {                                                                               \
+            DftCT<R1, R2, INV>::run(v);                                                 \
+        }                                                                               \
+        static __device__ __forceinline__ void run(float2 (&v)[R])                       \
+        {                                                                               \
+            DftCT<R1, R2, INV>::run(reinterpret_cast<cx<float>(&)[R]>(v));              \
+        }                                                                               \
     };
 B200_DFT_COMPOSITE(6, 2, 3)
 B200_DFT_COMPOSITE(8, 4, 2)
