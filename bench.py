@@ -142,8 +142,6 @@ def run_ours(args):
         raise RuntimeError("bench.py: no CUDA device; libgnss_b200 has no CPU path")
     torch.cuda.set_device(local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # stdout carries exactly one JSON line (VERSION prints a banner there)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -621,6 +619,12 @@ def main():
     ap.add_argument("--workload", default="C2", choices=["C1", "C2"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: file descriptor 1 is pointed at stderr for everything native code prints there
+    # (NCCL's version banner at any NCCL_DEBUG level), Python's own sys.stdout keeps the real one
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference(args)
