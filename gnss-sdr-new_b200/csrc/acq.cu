@@ -403,7 +403,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 const size_t smem_hi = ((size_t)pl.rb_hi * upper_group_stride(pl.ra_hi, fa.C) + fa.M_hi) * sizeof(float2);
                 const uint32_t rows_hi = std::max(1u, (uint32_t)kFastThreads / fa.C);
                 const dim3 block_hi(fa.C, rows_hi);
-                const uint32_t threads_lo = std::max<uint32_t>(64, std::min<uint32_t>(kFastThreads, (fa.nb * pl.rb_lo + 31) / 32 * 32));  // >= 64: twiddle fill
+                const uint32_t threads_lo = lower_threads(fa.nb, pl.rb_lo);
                 // Optional (B200_ACQ_OVERLAP=1): two half-size scratch buffers and two streams, the last stage of chunk i
                 // running while the first stage of chunk i+1 fills the other buffer.
                 static const bool overlap = [] {

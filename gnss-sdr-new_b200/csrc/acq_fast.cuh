@@ -57,37 +57,47 @@ constexpr int kFastThreads = 256;
 // ------------------------------------------------------------------------------------------------
 // lower stage: grid (rows, M_hi / nb). Shared memory: nb * PITCH * RB data + M twiddles.
 // ------------------------------------------------------------------------------------------------
-template <int RA, int RB>
+constexpr uint32_t lower_threads(uint32_t nb, uint32_t rb)  // >= 64: twiddle fill
+{
+    const uint32_t t = (nb * rb + 31) / 32 * 32;
+    return t < 64 ? 64 : (t > (uint32_t)kFastThreads ? (uint32_t)kFastThreads : t);
+}
+
+// RAH, RBH, NB != 0: the upper-stage radices and the sub-transforms per tile are compile-time (launch with
+// lower_threads(NB, RB) threads): loop trip counts, tile offsets and the k1 arithmetic fold into constants.
+template <int RA, int RB, int RAH = 0, int RBH = 0, int NB = 0>
 __global__ void __launch_bounds__(kFastThreads, 4) inv_lower_kernel(const FastArgs a)
 {
+    const uint32_t nb = NB ? NB : a.nb, ra_hi = RAH ? RAH : a.ra_hi, rb_hi = RBH ? RBH : a.rb_hi;
+    const uint32_t bd = NB ? lower_threads(NB, RB) : blockDim.x;
     constexpr int M = RA * RB;
     constexpr int P = (RA % 2 == 0) ? RA + 1 : RA;  // odd pitch: conflict-free 64-bit stores with stride P
     constexpr int MP = P * RB;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* s = reinterpret_cast<float2*>(smem_raw);
-    float2* s_tw = s + (size_t)a.nb * MP;  // conj W_M^(a*ub), [ub][a]
+    float2* s_tw = s + (size_t)nb * MP;  // conj W_M^(a*ub), [ub][a]
 
     const uint32_t y = a.y0 + blockIdx.x;
     uint32_t si, kk;
     fast_row_of(a, y, si, kk);
-    const size_t N = a.N;
+    const size_t N = RAH ? (size_t)RA * RB * RAH * RBH : a.N;
     const float2* X = a.X + ((size_t)a.slot_group[si] * a.nD_local + kk) * N;
     const float2* Cs = a.Cs + (size_t)a.slots[si] * N;
-    const uint32_t blk0 = blockIdx.y * a.nb;
-    const uint32_t tw_scale = a.N / M;  // W_M = W_N^(N/M)
+    const uint32_t blk0 = blockIdx.y * nb;
+    const uint32_t tw_scale = (uint32_t)N / M;  // W_M = W_N^(N/M)
 
     // ---- pass A (stride-1 dim, no twiddle): one thread per (block, ub) pencil ----
     // Order of the first round: twiddle-table loads and the pencil's own global loads are issued together, the table
     // is stored while the pencil data is still in flight, and the barrier sits between the butterfly (which needs no
     // twiddles) and the twiddle multiply — so the table costs no extra L2 round trip.
-    const uint32_t n_pen_a = a.nb * RB;
-    const uint32_t seg = a.N / RA;
+    const uint32_t n_pen_a = nb * RB;
+    const uint32_t seg = (uint32_t)N / RA;
     constexpr int kTwPerThread = (M + 63) / 64;  // enough for blockDim.x >= 64
     float2 wreg[kTwPerThread];
 #pragma unroll
     for (int j = 0; j < kTwPerThread; j++)
         {
-            const uint32_t i = threadIdx.x + j * blockDim.x;
+            const uint32_t i = threadIdx.x + j * bd;
             if (i < (uint32_t)M)
                 {
                     const uint32_t ub = i / RA, aa = i - ub * RA;
@@ -118,14 +128,14 @@ __global__ void __launch_bounds__(kFastThreads, 4) inv_lower_kernel(const FastAr
 #pragma unroll
         for (int j = 0; j < kTwPerThread; j++)
             {
-                const uint32_t i = threadIdx.x + j * blockDim.x;
+                const uint32_t i = threadIdx.x + j * bd;
                 if (i < (uint32_t)M) s_tw[i] = make_float2(wreg[j].x, -wreg[j].y);
             }
         if (have) fft::Dft<RA, true>::run(x);
         __syncthreads();
         if (have) twiddle_store(x, threadIdx.x);
     }
-    for (uint32_t p = threadIdx.x + blockDim.x; p < n_pen_a; p += blockDim.x)
+    for (uint32_t p = threadIdx.x + bd; p < n_pen_a; p += bd)
         {
             float2 x[RA];
             load_product(x, p);
@@ -135,15 +145,15 @@ __global__ void __launch_bounds__(kFastThreads, 4) inv_lower_kernel(const FastAr
     __syncthreads();
 
     // ---- pass B + inter-stage twiddle: one thread per (block, a) pencil ----
-    const uint32_t n_pen_b = a.nb * RA;
+    const uint32_t n_pen_b = nb * RA;
     float2* out = a.scratch + (size_t)(y - a.y0) * N;
-    for (uint32_t p = threadIdx.x; p < n_pen_b; p += blockDim.x)
+    for (uint32_t p = threadIdx.x; p < n_pen_b; p += bd)
         {
             const uint32_t bl = p / RA, aa = p - bl * RA;
             const uint32_t gblk = blk0 + bl;
             // upper-stage frequency index of this block: block position = ua' + ra_hi * ub'  ->  k1 = ua' * rb_hi + ub'
-            const uint32_t ubh = gblk / a.ra_hi, uah = gblk - ubh * a.ra_hi;
-            const uint32_t k1 = uah * a.rb_hi + ubh;
+            const uint32_t ubh = gblk / ra_hi, uah = gblk - ubh * ra_hi;
+            const uint32_t k1 = uah * rb_hi + ubh;
             const float2 wb = __ldg(a.W + (size_t)k1 * aa);  // W_N^(k1 * a)
             const float2 ws = __ldg(a.W + (size_t)k1 * RA);  // W_N^(k1 * RA)
             float2 v[RB];
@@ -177,13 +187,17 @@ __host__ __device__ __forceinline__ uint32_t upper_group_stride(uint32_t ra, uin
 
 // GRID = true: persistent magnitude grid (max_dwells > 1 / dump), full rows: the old grid values of a pencil are requested
 // (streaming loads) before its butterfly so that their HBM latency hides behind it, and written back with streaming stores.
-template <int RA, int RB, bool GRID = false>
+// MLO, CC != 0: the lower-stage length and the column tile are compile-time (launch with block (CC, kFastThreads / CC)): every
+// shared-memory and global offset of a pencil folds into an immediate and the pencil loops unroll.
+template <int RA, int RB, bool GRID = false, int MLO = 0, int CC = 0>
 __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs a)
 {
     constexpr int M = RA * RB;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* s = reinterpret_cast<float2*>(smem_raw);
-    const uint32_t G = upper_group_stride(RA, a.C);
+    const uint32_t C = CC ? CC : a.C, M_lo = MLO ? MLO : a.M_lo;
+    const uint32_t bdx = CC ? CC : blockDim.x, bdy = CC ? kFastThreads / CC : blockDim.y;
+    const uint32_t G = upper_group_stride(RA, C);
     float2* s_tw = s + (size_t)RB * G;  // conj W_M^(a*ub), [ub][a]
     __shared__ float s_rmax[kFastThreads / 32];
     __shared__ uint32_t s_ridx[kFastThreads / 32];
@@ -193,10 +207,10 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     const uint32_t y = a.y0 + blockIdx.x;
     uint32_t si, kk;
     fast_row_of(a, y, si, kk);
-    const size_t N = a.N;
-    const uint32_t C = a.C, c = threadIdx.x, c0 = blockIdx.y * C;
-    const uint32_t tid = threadIdx.y * blockDim.x + threadIdx.x, nthreads = blockDim.x * blockDim.y;
-    const uint32_t tw_scale = a.N / M;
+    const size_t N = MLO ? (size_t)MLO * M : a.N;
+    const uint32_t c = threadIdx.x, c0 = blockIdx.y * C;
+    const uint32_t tid = threadIdx.y * bdx + threadIdx.x, nthreads = bdx * bdy;
+    const uint32_t tw_scale = M_lo;  // N / M
     const float2* in = a.scratch + (size_t)(y - a.y0) * N + c0 + c;
 
     // ---- pass A: pencils (column c, ub); same ordering trick as in the lower kernel ----
@@ -214,7 +228,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
         }
     auto load_pencil = [&](float2(&v)[RA], uint32_t ub) {
 #pragma unroll
-        for (int u = 0; u < RA; u++) v[u] = __ldcg(in + (size_t)(u + RA * ub) * a.M_lo);
+        for (int u = 0; u < RA; u++) v[u] = __ldcg(in + (size_t)(u + RA * ub) * M_lo);
     };
     auto twiddle_store = [&](float2(&v)[RA], uint32_t ub) {
 #pragma unroll
@@ -234,7 +248,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
         __syncthreads();
         if (have) twiddle_store(v, threadIdx.y);
     }
-    for (uint32_t ub = threadIdx.y + blockDim.y; ub < (uint32_t)RB; ub += blockDim.y)
+    for (uint32_t ub = threadIdx.y + bdy; ub < (uint32_t)RB; ub += bdy)
         {
             float2 v[RA];
             load_pencil(v, ub);
@@ -248,7 +262,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     if (a.mag_base)
         mag = a.mag_is_rowbuf ? a.mag_base + (size_t)si * a.eff : a.mag_base + ((size_t)a.slots[si] * a.nD_local + kk) * a.eff;
     const bool accumulate = mag && !a.mag_is_rowbuf && a.dwell_after[si] > 1;
-    const bool full_rows = (a.mag_offset == 0 && a.eff == a.N);
+    const bool full_rows = (a.mag_offset == 0 && a.eff == N);
     float best = -1.f, sum = 0.f;
     uint32_t best_i = 0xffffffffu;
     if (tid == 0) s_tile_idx = 0xffffffffu;
@@ -257,11 +271,11 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
             // Common case (no bit transition): every output belongs to the row. The running maximum is a plain FMNMX;
             // each |.|^2 is parked in the shared-memory slot its pencil just consumed (no other thread reads it), and
             // once the tile maximum is known only the thread(s) holding it look their slots up for the lowest index.
-            for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
+            for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += bdy)
                 {
                     float2 v[RB];
-                    const uint32_t pos0 = aa * a.M_lo + c0 + c;
-                    const uint32_t pstep = RA * a.M_lo;
+                    const uint32_t pos0 = aa * M_lo + c0 + c;
+                    const uint32_t pstep = RA * M_lo;
                     float old[GRID ? RB : 1];
                     if (GRID)
                         {
@@ -309,11 +323,11 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
             if (best == tile_max)  // warp-uniform after the butterfly reduction: at most a few warps per tile get here
                 {
                     uint32_t mine = 0xffffffffu;
-                    for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
+                    for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += bdy)
                         {
 #pragma unroll
                             for (int b = 0; b < RB; b++)
-                                if (s[(size_t)b * G + aa * C + c].x == tile_max) mine = min(mine, (aa + RA * b) * a.M_lo + c0 + c);
+                                if (s[(size_t)b * G + aa * C + c].x == tile_max) mine = min(mine, (aa + RA * b) * M_lo + c0 + c);
                         }
                     if (mine != 0xffffffffu) atomicMin(&s_tile_idx, mine);  // lowest index wins ties (:523)
                 }
@@ -330,7 +344,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
                 }
             return;
         }
-    for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += blockDim.y)
+    for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += bdy)
         {
             float2 v[RB];
 #pragma unroll
@@ -339,7 +353,7 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
 #pragma unroll
             for (int b = 0; b < RB; b++)
                 {
-                    const uint32_t pos = (aa + RA * b) * a.M_lo + c0 + c;  // natural time index
+                    const uint32_t pos = (aa + RA * b) * M_lo + c0 + c;  // natural time index
                     const uint32_t m = pos - a.mag_offset;
                     if (m < a.eff)
                         {

@@ -1,5 +1,6 @@
 // Instantiations of inv_lower_kernel<RA, RB> for every supported stage shape (generated list; see fft_plan.cc).
 #include "acq_fast.cuh"
+#include <cstdlib>
 
 namespace b200
 {
@@ -14,10 +15,32 @@ void configure(size_t smem)
     if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     done = true;
 }
+// geometries with their own instantiation (see acq_fast_upper.cu): N = 4000, 8000, 16000, 25000, 32000, 50000, 100000, 160000
+template <int RA, int RB, int RAH, int RBH, int NB>
+bool launch_fixed(dim3 grid, uint32_t threads, size_t smem, cudaStream_t st, const FastArgs& a)
+{
+    if (a.ra_lo != (uint32_t)RA || a.rb_lo != (uint32_t)RB || a.ra_hi != (uint32_t)RAH || a.rb_hi != (uint32_t)RBH || a.nb != (uint32_t)NB ||
+        threads != lower_threads(NB, RB))
+        return false;
+    configure<inv_lower_kernel<RA, RB, RAH, RBH, NB>>(smem);
+    inv_lower_kernel<RA, RB, RAH, RBH, NB><<<grid, threads, smem, st>>>(a);
+    return true;
+}
+
+bool try_fixed(dim3 grid, uint32_t threads, size_t smem, cudaStream_t st, const FastArgs& a)
+{
+    static const bool off = std::getenv("B200_NO_FIXED") != nullptr;  // tuning aid: the runtime-geometry kernels only
+    if (off) return false;
+    return launch_fixed<25, 2, 16, 5, 80>(grid, threads, smem, st, a) || launch_fixed<25, 4, 16, 5, 40>(grid, threads, smem, st, a) ||
+           launch_fixed<25, 5, 16, 8, 32>(grid, threads, smem, st, a) || launch_fixed<25, 5, 25, 8, 25>(grid, threads, smem, st, a) ||
+           launch_fixed<25, 8, 16, 10, 20>(grid, threads, smem, st, a) || launch_fixed<25, 8, 25, 10, 10>(grid, threads, smem, st, a) ||
+           launch_fixed<25, 16, 25, 10, 10>(grid, threads, smem, st, a) || launch_fixed<25, 16, 25, 16, 10>(grid, threads, smem, st, a);
+}
 }  // namespace
 
 cudaError_t launch_inv_lower(uint32_t ra, uint32_t rb, dim3 grid, uint32_t threads, size_t smem, cudaStream_t st, const FastArgs& a)
 {
+    if (try_fixed(grid, threads, smem, st, a)) return cudaGetLastError();
     const uint32_t key = ra * 100 + rb;
     switch (key)
         {

@@ -1,5 +1,6 @@
 // Instantiations of inv_upper_kernel<RA, RB, GRID> for every supported stage shape (see fft_plan.cc).
 #include "acq_fast.cuh"
+#include <cstdlib>
 
 namespace b200
 {
@@ -15,9 +16,45 @@ void configure(size_t smem)
     done = true;
 }
 
+// geometries with their own instantiation (lower-stage length and column tile compile-time): the plans of the common
+// GNSS dwell lengths N = 4000, 8000, 16000, 25000, 32000, 50000, 100000, 160000 (fft_plan.cc picks (RA, RB, M_lo, C))
+template <int RA, int RB, int MLO, int CC>
+bool launch_fixed(bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
+{
+    if (a.M_lo != (uint32_t)MLO || a.C != (uint32_t)CC || block.x != (unsigned)CC || block.y != (unsigned)(kFastThreads / CC)) return false;
+    if (grid_path)
+        {
+            configure<inv_upper_kernel<RA, RB, true, MLO, CC>>(smem);
+            inv_upper_kernel<RA, RB, true, MLO, CC><<<grid, block, smem, st>>>(a);
+        }
+    else
+        {
+            configure<inv_upper_kernel<RA, RB, false, MLO, CC>>(smem);
+            inv_upper_kernel<RA, RB, false, MLO, CC><<<grid, block, smem, st>>>(a);
+        }
+    return true;
+}
+
+template <int RA, int RB>
+bool try_fixed(bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
+{
+    static const bool off = std::getenv("B200_NO_FIXED") != nullptr;  // tuning aid: the runtime-geometry kernels only
+    if (off) return false;
+    if constexpr (RA == 16 && RB == 5)
+        return launch_fixed<16, 5, 50, 25>(grid_path, grid, block, smem, st, a) || launch_fixed<16, 5, 100, 25>(grid_path, grid, block, smem, st, a);
+    if constexpr (RA == 16 && RB == 8) return launch_fixed<16, 8, 125, 25>(grid_path, grid, block, smem, st, a);
+    if constexpr (RA == 25 && RB == 8) return launch_fixed<25, 8, 125, 25>(grid_path, grid, block, smem, st, a);
+    if constexpr (RA == 16 && RB == 10) return launch_fixed<16, 10, 200, 25>(grid_path, grid, block, smem, st, a);
+    if constexpr (RA == 25 && RB == 10)
+        return launch_fixed<25, 10, 200, 25>(grid_path, grid, block, smem, st, a) || launch_fixed<25, 10, 400, 16>(grid_path, grid, block, smem, st, a);
+    if constexpr (RA == 25 && RB == 16) return launch_fixed<25, 16, 400, 16>(grid_path, grid, block, smem, st, a);
+    return false;
+}
+
 template <int RA, int RB>
 void launch(bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
 {
+    if (try_fixed<RA, RB>(grid_path, grid, block, smem, st, a)) return;
     if (grid_path)
         {
             configure<inv_upper_kernel<RA, RB, true>>(smem);

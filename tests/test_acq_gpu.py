@@ -352,3 +352,17 @@ def test_two_step_acquisition(b200, oracle, use_cfar):
         e1.set_step2_center(0, 0.0, 1.0)          # not a second-step handle
     e1.close()
     e2.close()
+
+
+def test_runtime_geometry_kernels_agree_with_fixed_ones():
+    """The common dwell lengths have inverse-stage instantiations with compile-time geometry (acq_fast_lower.cu /
+    acq_fast_upper.cu: launch_fixed); every other fast-plan length runs the runtime-geometry instantiations of the same
+    kernels. B200_NO_FIXED=1 sends the whole suite's lengths through the latter: same parity tests, in a child process
+    because the switch is read once per process."""
+    import subprocess
+    import sys
+    env = dict(os.environ, B200_NO_FIXED="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
+                        "known_answer or config1 or config2 or noncoherent or zero_padded or cshort or cbyte or two_step"], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
