@@ -398,6 +398,8 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 fa.partials = partials;
                 // persistent grid with full rows: the specialised last stage (old values prefetched, streaming stores)
                 const bool grid_path = mag_base && !mag_is_rowbuf && h->mag_offset == 0 && h->eff == h->N;
+                // 2: nothing but the per-tile records leaves the last stage (no grid kept, full rows)
+                const int upper_mode = grid_path ? 1 : ((!mag_base && h->mag_offset == 0 && h->eff == h->N) ? 2 : 0);
                 const uint32_t pitch = (pl.ra_lo % 2 == 0) ? pl.ra_lo + 1 : pl.ra_lo;
                 const size_t smem_lo = ((size_t)fa.nb * pitch * pl.rb_lo + fa.M_lo) * sizeof(float2);
                 const size_t smem_hi = ((size_t)pl.rb_hi * upper_group_stride(pl.ra_hi, fa.C) + fa.M_hi) * sizeof(float2);
@@ -431,7 +433,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                         B200_CUDA(cudaEventRecord(h->ev_lo[buf], h->stream));
                         if (overlap) B200_CUDA(cudaStreamWaitEvent(s2, h->ev_lo[buf], 0));
                         h->prof.begin(CAT_INV_LAST, s2);
-                        e = launch_inv_upper(pl.ra_hi, pl.rb_hi, grid_path, dim3(cnt, fa.M_lo / fa.C), block_hi, smem_hi, s2, fa);
+                        e = launch_inv_upper(pl.ra_hi, pl.rb_hi, upper_mode, dim3(cnt, fa.M_lo / fa.C), block_hi, smem_hi, s2, fa);
                         h->prof.end(s2);
                         h->launches++;
                         B200_CUDA(e);

@@ -185,11 +185,13 @@ __host__ __device__ __forceinline__ uint32_t upper_group_stride(uint32_t ra, uin
     return g + ((C + 16u - (g & 15u)) & 15u);
 }
 
-// GRID = true: persistent magnitude grid (max_dwells > 1 / dump), full rows: the old grid values of a pencil are requested
+// MODE 0: what to do with the magnitudes is read from the arguments (row buffer, partial rows of the bit-transition search, ...).
+// MODE 2: no magnitude output at all (CFAR search without a kept grid, full rows): only the per-tile records leave the kernel.
+// MODE 1 (GRID): persistent magnitude grid (max_dwells > 1 / dump), full rows: the old grid values of a pencil are requested
 // (streaming loads) before its butterfly so that their HBM latency hides behind it, and written back with streaming stores.
 // MLO, CC != 0: the lower-stage length and the column tile are compile-time (launch with block (CC, kFastThreads / CC)): every
 // shared-memory and global offset of a pencil folds into an immediate and the pencil loops unroll.
-template <int RA, int RB, bool GRID = false, int MLO = 0, int CC = 0>
+template <int RA, int RB, int MODE = 0, int MLO = 0, int CC = 0>
 __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs a)
 {
     constexpr int M = RA * RB;
@@ -258,11 +260,12 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
     __syncthreads();
 
     // ---- pass B + |.|^2 + reductions: pencils (column c, a) ----
+    constexpr bool GRID = (MODE == 1);
     float* mag = nullptr;
-    if (a.mag_base)
+    if (MODE != 2 && a.mag_base)
         mag = a.mag_is_rowbuf ? a.mag_base + (size_t)si * a.eff : a.mag_base + ((size_t)a.slots[si] * a.nD_local + kk) * a.eff;
-    const bool accumulate = mag && !a.mag_is_rowbuf && a.dwell_after[si] > 1;
-    const bool full_rows = (a.mag_offset == 0 && a.eff == N);
+    const bool accumulate = MODE != 2 && mag && !a.mag_is_rowbuf && a.dwell_after[si] > 1;
+    const bool full_rows = MODE == 2 || (a.mag_offset == 0 && a.eff == N);
     float best = -1.f, sum = 0.f;
     uint32_t best_i = 0xffffffffu;
     if (tid == 0) s_tile_idx = 0xffffffffu;
@@ -412,6 +415,6 @@ __global__ void __launch_bounds__(kFastThreads) inv_upper_kernel(const FastArgs 
 
 // host-side launchers (instantiations live in acq_fast_lower.cu / acq_fast_upper.cu)
 cudaError_t launch_inv_lower(uint32_t ra, uint32_t rb, dim3 grid, uint32_t threads, size_t smem, cudaStream_t st, const FastArgs& a);
-cudaError_t launch_inv_upper(uint32_t ra, uint32_t rb, bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a);
+cudaError_t launch_inv_upper(uint32_t ra, uint32_t rb, int mode, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a);
 
 }  // namespace b200

@@ -1,4 +1,4 @@
-// Instantiations of inv_upper_kernel<RA, RB, GRID> for every supported stage shape (see fft_plan.cc).
+// Instantiations of inv_upper_kernel<RA, RB, MODE> for every supported stage shape (see fft_plan.cc).
 #include "acq_fast.cuh"
 #include <cstdlib>
 
@@ -19,60 +19,64 @@ void configure(size_t smem)
 // geometries with their own instantiation (lower-stage length and column tile compile-time): the plans of the common
 // GNSS dwell lengths N = 4000, 8000, 16000, 25000, 32000, 50000, 100000, 160000 (fft_plan.cc picks (RA, RB, M_lo, C))
 template <int RA, int RB, int MLO, int CC>
-bool launch_fixed(bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
+bool launch_fixed(int mode, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
 {
     if (a.M_lo != (uint32_t)MLO || a.C != (uint32_t)CC || block.x != (unsigned)CC || block.y != (unsigned)(kFastThreads / CC)) return false;
-    if (grid_path)
+    if (mode == 1)
         {
-            configure<inv_upper_kernel<RA, RB, true, MLO, CC>>(smem);
-            inv_upper_kernel<RA, RB, true, MLO, CC><<<grid, block, smem, st>>>(a);
+            configure<inv_upper_kernel<RA, RB, 1, MLO, CC>>(smem);
+            inv_upper_kernel<RA, RB, 1, MLO, CC><<<grid, block, smem, st>>>(a);
+        }
+    else if (mode == 2)
+        {
+            configure<inv_upper_kernel<RA, RB, 2, MLO, CC>>(smem);
+            inv_upper_kernel<RA, RB, 2, MLO, CC><<<grid, block, smem, st>>>(a);
         }
     else
         {
-            configure<inv_upper_kernel<RA, RB, false, MLO, CC>>(smem);
-            inv_upper_kernel<RA, RB, false, MLO, CC><<<grid, block, smem, st>>>(a);
+            return false;  // row buffer / partial rows: the runtime kernel
         }
     return true;
 }
 
 template <int RA, int RB>
-bool try_fixed(bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
+bool try_fixed(int mode, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
 {
     static const bool off = std::getenv("B200_NO_FIXED") != nullptr;  // tuning aid: the runtime-geometry kernels only
     if (off) return false;
     if constexpr (RA == 16 && RB == 5)
-        return launch_fixed<16, 5, 50, 25>(grid_path, grid, block, smem, st, a) || launch_fixed<16, 5, 100, 25>(grid_path, grid, block, smem, st, a);
-    if constexpr (RA == 16 && RB == 8) return launch_fixed<16, 8, 125, 25>(grid_path, grid, block, smem, st, a);
-    if constexpr (RA == 25 && RB == 8) return launch_fixed<25, 8, 125, 25>(grid_path, grid, block, smem, st, a);
-    if constexpr (RA == 16 && RB == 10) return launch_fixed<16, 10, 200, 25>(grid_path, grid, block, smem, st, a);
+        return launch_fixed<16, 5, 50, 25>(mode, grid, block, smem, st, a) || launch_fixed<16, 5, 100, 25>(mode, grid, block, smem, st, a);
+    if constexpr (RA == 16 && RB == 8) return launch_fixed<16, 8, 125, 25>(mode, grid, block, smem, st, a);
+    if constexpr (RA == 25 && RB == 8) return launch_fixed<25, 8, 125, 25>(mode, grid, block, smem, st, a);
+    if constexpr (RA == 16 && RB == 10) return launch_fixed<16, 10, 200, 25>(mode, grid, block, smem, st, a);
     if constexpr (RA == 25 && RB == 10)
-        return launch_fixed<25, 10, 200, 25>(grid_path, grid, block, smem, st, a) || launch_fixed<25, 10, 400, 16>(grid_path, grid, block, smem, st, a);
-    if constexpr (RA == 25 && RB == 16) return launch_fixed<25, 16, 400, 16>(grid_path, grid, block, smem, st, a);
+        return launch_fixed<25, 10, 200, 25>(mode, grid, block, smem, st, a) || launch_fixed<25, 10, 400, 16>(mode, grid, block, smem, st, a);
+    if constexpr (RA == 25 && RB == 16) return launch_fixed<25, 16, 400, 16>(mode, grid, block, smem, st, a);
     return false;
 }
 
 template <int RA, int RB>
-void launch(bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
+void launch(int mode, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
 {
-    if (try_fixed<RA, RB>(grid_path, grid, block, smem, st, a)) return;
-    if (grid_path)
+    if (try_fixed<RA, RB>(mode, grid, block, smem, st, a)) return;
+    if (mode == 1)
         {
-            configure<inv_upper_kernel<RA, RB, true>>(smem);
-            inv_upper_kernel<RA, RB, true><<<grid, block, smem, st>>>(a);
+            configure<inv_upper_kernel<RA, RB, 1>>(smem);
+            inv_upper_kernel<RA, RB, 1><<<grid, block, smem, st>>>(a);
         }
     else
         {
-            configure<inv_upper_kernel<RA, RB, false>>(smem);
-            inv_upper_kernel<RA, RB, false><<<grid, block, smem, st>>>(a);
+            configure<inv_upper_kernel<RA, RB, 0>>(smem);
+            inv_upper_kernel<RA, RB, 0><<<grid, block, smem, st>>>(a);
         }
 }
 }  // namespace
 
-cudaError_t launch_inv_upper(uint32_t ra, uint32_t rb, bool grid_path, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
+cudaError_t launch_inv_upper(uint32_t ra, uint32_t rb, int mode, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const FastArgs& a)
 {
 #define B200_UPPER_CASE(RA, RB)                            \
     case RA * 100 + RB:                                     \
-        launch<RA, RB>(grid_path, grid, block, smem, st, a); \
+        launch<RA, RB>(mode, grid, block, smem, st, a); \
         break;
     switch (ra * 100 + rb)
         {
