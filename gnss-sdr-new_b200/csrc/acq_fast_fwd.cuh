@@ -34,22 +34,25 @@ struct FastFwdArgs
 };
 
 // upper stage: grid (transforms, M_lo / C), block (C, threads / C). Shared memory: M * C data + M twiddles.
-template <int RA, int RB>
+// MLO, CC != 0: lower-stage length and column tile compile-time (block (CC, kFastThreads / CC)), as in acq_fast.cuh
+template <int RA, int RB, int MLO = 0, int CC = 0>
 __global__ void __launch_bounds__(kFastThreads) fwd_upper_kernel(const FastFwdArgs a)
 {
     constexpr int M = RA * RB;
+    const uint32_t gC = CC ? CC : a.C, gM_lo = MLO ? MLO : a.M_lo, gN = MLO ? (uint32_t)MLO * M : a.N;
+    const uint32_t bdx = CC ? CC : blockDim.x, bdy = CC ? kFastThreads / CC : blockDim.y;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* s = reinterpret_cast<float2*>(smem_raw);
-    float2* s_tw = s + (size_t)M * a.C;  // W_M^(q*ub), [ub][q]
+    float2* s_tw = s + (size_t)M * gC;  // W_M^(q*ub), [ub][q]
     __shared__ WipePiece s_pieces[kMaxPieces];
 
     const uint32_t y = blockIdx.x;
     const uint32_t g = y / a.nD_local, kk = y - g * a.nD_local;
     const uint32_t pb = a.group_piece_base[g] + kk;
     const uint32_t np = a.n_pieces[pb];
-    const uint32_t C = a.C, c = threadIdx.x, m = blockIdx.y * C + c;
-    const uint32_t tid = threadIdx.y * blockDim.x + threadIdx.x, nthreads = blockDim.x * blockDim.y;
-    const uint32_t tw_scale = a.N / M;
+    const uint32_t C = gC, c = threadIdx.x, m = blockIdx.y * C + c;
+    const uint32_t tid = threadIdx.y * bdx + threadIdx.x, nthreads = bdx * bdy;
+    const uint32_t tw_scale = gN / M;
     for (uint32_t i = tid; i < np; i += nthreads) s_pieces[i] = a.pieces[(size_t)pb * kMaxPieces + i];
     for (uint32_t i = tid; i < (uint32_t)M; i += nthreads)
         {
@@ -59,14 +62,14 @@ __global__ void __launch_bounds__(kFastThreads) fwd_upper_kernel(const FastFwdAr
     __syncthreads();
 
     // ---- pass 1 (radix RB over b, stride RA*M_lo): pencils (column c, q) ----
-    for (uint32_t q = threadIdx.y; q < (uint32_t)RA; q += blockDim.y)
+    for (uint32_t q = threadIdx.y; q < (uint32_t)RA; q += bdy)
         {
             float2 v[RB];
             uint32_t cur = 0;
 #pragma unroll
             for (int b = 0; b < RB; b++)
                 {
-                    const uint32_t pos = m + a.M_lo * (q + RA * b);
+                    const uint32_t pos = m + gM_lo * (q + RA * b);
                     float2 w = make_float2(0.f, 0.f);
                     if (pos < a.consumed)
                         {
@@ -101,8 +104,8 @@ __global__ void __launch_bounds__(kFastThreads) fwd_upper_kernel(const FastFwdAr
     __syncthreads();
 
     // ---- pass 2 (radix RA over q) + inter-stage twiddle W_N^(k1*m), k1 = uah*RB + ub: pencils (column c, ub) ----
-    float2* out = a.scratch + (size_t)y * a.N + m;
-    for (uint32_t ub = threadIdx.y; ub < (uint32_t)RB; ub += blockDim.y)
+    float2* out = a.scratch + (size_t)y * gN + m;
+    for (uint32_t ub = threadIdx.y; ub < (uint32_t)RB; ub += bdy)
         {
             float2 v[RA];
 #pragma unroll
@@ -119,27 +122,29 @@ __global__ void __launch_bounds__(kFastThreads) fwd_upper_kernel(const FastFwdAr
                         tw = __ldg(a.W + (size_t)(uah * RB + ub) * m);  // k1 * m < N
                     else
                         tw = fft::cmul(tw, st);
-                    out[(size_t)(uah + RA * ub) * a.M_lo] = fft::cmul(v[uah], tw);
+                    out[(size_t)(uah + RA * ub) * gM_lo] = fft::cmul(v[uah], tw);
                 }
         }
 }
 
 // lower stage: grid (transforms, M_hi / nb). Shared memory: nb * PITCH * RB data + M twiddles.
-template <int RA, int RB>
+// MHI, NB != 0: upper-stage length and sub-transforms per tile compile-time (kFastThreads threads)
+template <int RA, int RB, int MHI = 0, int NB = 0>
 __global__ void __launch_bounds__(kFastThreads) fwd_lower_kernel(const FastFwdArgs a)
 {
     constexpr int M = RA * RB;
+    const uint32_t gnb = NB ? NB : a.nb, gN = MHI ? (uint32_t)MHI * M : a.N, bd = NB ? kFastThreads : blockDim.x;
     constexpr int P = (RA % 2 == 0) ? RA + 1 : RA;  // odd pitch: conflict-free 64-bit accesses with stride P
     constexpr int MP = P * RB;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* s = reinterpret_cast<float2*>(smem_raw);
-    float2* s_tw = s + (size_t)a.nb * MP;  // W_M^(a*ub), [ub][a]
+    float2* s_tw = s + (size_t)gnb * MP;  // W_M^(a*ub), [ub][a]
 
     const uint32_t y = blockIdx.x;
-    const uint32_t blk0 = blockIdx.y * a.nb;
-    const uint32_t tw_scale = a.N / M;
-    const float2* in = a.scratch + (size_t)y * a.N + (size_t)blk0 * M;
-    for (uint32_t i = threadIdx.x; i < (uint32_t)M; i += blockDim.x)
+    const uint32_t blk0 = blockIdx.y * gnb;
+    const uint32_t tw_scale = gN / M;
+    const float2* in = a.scratch + (size_t)y * gN + (size_t)blk0 * M;
+    for (uint32_t i = threadIdx.x; i < (uint32_t)M; i += bd)
         {
             const uint32_t ub = i / RA, aa = i - ub * RA;
             s_tw[i] = __ldg(a.W + (size_t)aa * ub * tw_scale);
@@ -147,8 +152,8 @@ __global__ void __launch_bounds__(kFastThreads) fwd_lower_kernel(const FastFwdAr
     __syncthreads();
 
     // ---- pass 1 (radix RB over b', stride RA): pencils (block, a) ----
-    const uint32_t n_pen_1 = a.nb * RA;
-    for (uint32_t p = threadIdx.x; p < n_pen_1; p += blockDim.x)
+    const uint32_t n_pen_1 = gnb * RA;
+    for (uint32_t p = threadIdx.x; p < n_pen_1; p += bd)
         {
             const uint32_t bl = p / RA, aa = p - bl * RA;
             float2 v[RB];
@@ -163,10 +168,10 @@ __global__ void __launch_bounds__(kFastThreads) fwd_lower_kernel(const FastFwdAr
     __syncthreads();
 
     // ---- pass 2 (radix RA over a, stride 1): pencils (block, ub); bin j = ub + RB*ua goes to F(pos) ----
-    const uint32_t n_pen_2 = a.nb * RB;
-    const uint32_t seg = a.N / RA;
-    float2* X = a.X + (size_t)y * a.N;
-    for (uint32_t p = threadIdx.x; p < n_pen_2; p += blockDim.x)
+    const uint32_t n_pen_2 = gnb * RB;
+    const uint32_t seg = gN / RA;
+    float2* X = a.X + (size_t)y * gN;
+    for (uint32_t p = threadIdx.x; p < n_pen_2; p += bd)
         {
             const uint32_t bl = p / RB, ub = p - bl * RB;
             float2 v[RA];
