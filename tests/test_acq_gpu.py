@@ -250,6 +250,20 @@ def test_unsupported_and_state_errors(b200):
         e.read_grid(0)  # keep_grid = 0
     with pytest.raises(b200.B200Error):
         e.set_local_codes([7], np.zeros((1, 4000), np.complex64))  # slot out of range
+    e.close()
+    # second-step handles (make_two_steps)
+    with pytest.raises(b200.B200Error):
+        b200.PcpsAcquisitionB200(4000, 4000, 5000, 250, 4e6, 4, 2, step2=(0, 125.0))      # second_nbins = 0
+    with pytest.raises(b200.B200Error):
+        b200.PcpsAcquisitionB200(4000, 4000, 5000, 250, 4e6, 4, 2, step2=(4, 0.0))        # second_doppler_step = 0
+    with pytest.raises(b200.B200Error):
+        b200.PcpsAcquisitionB200(4000, 4000, 5000, 250, 4e6, 4, 2, step2=(4, 125.0), row_begin=0, row_end=2)   # not row-sharded
+    e2 = b200.PcpsAcquisitionB200(4000, 4000, 5000, 250, 4e6, 4, 2, step2=(4, 125.0))
+    with pytest.raises(b200.B200Error):
+        e2.set_step2_center(2, 0.0, 1.0)          # slot out of range
+    with pytest.raises(b200.B200Error):
+        e2.dwell(np.zeros(4000, np.complex64), [0])  # no local code
+    e2.close()
 
 
 @pytest.mark.parametrize("name,min_cn0", [("C4_gps", 47.0), ("C4_gal", 41.0), ("C4_bds", 47.0)])
