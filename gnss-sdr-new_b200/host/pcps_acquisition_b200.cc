@@ -32,10 +32,6 @@ pcps_acquisition_b200::pcps_acquisition_b200(const Acq_Conf& conf_)
 {
     d_dump_channel = conf_.dump_channel;  // :74
     d_dump = conf_.dump;                  // :81
-    if (conf_.make_repeat_steps)
-        {
-            throw std::invalid_argument("pcps_acquisition_b200: make_repeat_steps is not available in the B200 implementation");
-        }
     if (conf_.make_2_steps && (conf_.num_doppler_bins_step2 == 0 || !(conf_.doppler_step2 > 0.0F)))
         {
             throw std::invalid_argument("pcps_acquisition_b200: make_two_steps needs second_nbins >= 1 and second_doppler_step > 0");
@@ -234,6 +230,7 @@ void pcps_acquisition_b200::init()
         }
     d_mag = 0.0;
     d_input_power = 0.0;
+    d_step_repeat = false;  // :262
     d_num_doppler_bins = static_cast<uint32_t>(std::ceil(static_cast<double>(static_cast<int32_t>(d_acq_parameters.doppler_max) - static_cast<int32_t>(-d_acq_parameters.doppler_max)) / static_cast<double>(d_doppler_step)));  // :264
 
     attach_engine();
@@ -294,10 +291,13 @@ void pcps_acquisition_b200::set_state(int32_t state)
     d_state = state;
     if (d_state == 1)
         {
-            d_gnss_synchro->Acq_delay_samples = 0.0;
-            d_gnss_synchro->Acq_doppler_hz = 0.0;
-            d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
-            d_gnss_synchro->Acq_doppler_step = 0U;
+            if (!d_step_repeat)  // :324 — the fork's repeat mode keeps the last answer in Gnss_Synchro
+                {
+                    d_gnss_synchro->Acq_delay_samples = 0.0;
+                    d_gnss_synchro->Acq_doppler_hz = 0.0;
+                    d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
+                    d_gnss_synchro->Acq_doppler_step = 0U;
+                }
             d_mag = 0.0;
             d_test_statistics = 0.0;
             d_active = true;
@@ -312,7 +312,14 @@ void pcps_acquisition_b200::set_state(int32_t state)
 // :345-381
 void pcps_acquisition_b200::send_positive_acquisition()
 {
-    d_positive_acq = 1;
+    if (!d_step_repeat)  // :360-363 — no dump file while repeating
+        {
+            d_positive_acq = 1;
+        }
+    if (d_acq_parameters.make_repeat_steps)  // :365-368
+        {
+            d_step_repeat = true;
+        }
     if (!d_channel_fsm.expired())
         {
             d_channel_fsm.lock()->Event_valid_acquisition();
@@ -435,7 +442,11 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
     if (!step_two) d_input_power = res.input_power;  // :531-535 refresh it in the first step only
     d_test_statistics = res.test_statistic;
 
-    if (d_acq_parameters.use_automatic_resampler)  // :699-705
+    if (!step_two && d_acq_parameters.make_2_steps && d_step_repeat)
+        {
+            // :697 — a repeated coarse search of the two-step mode leaves Gnss_Synchro alone
+        }
+    else if (d_acq_parameters.use_automatic_resampler)  // :699-705
         {
             d_gnss_synchro->Acq_delay_samples = static_cast<double>(std::fmod(static_cast<float>(indext), d_acq_parameters.samples_per_code)) * d_acq_parameters.resampler_ratio;
             d_gnss_synchro->Acq_delay_samples -= static_cast<double>(d_acq_parameters.resampler_latency_samples);
@@ -583,6 +594,10 @@ int pcps_acquisition_b200::general_work(int noutput_items, std::vector<int>& nin
                     d_state = 0;
                     d_active = true;
                 }
+            if (d_step_repeat)  // :944-947 — the fork's repeat mode never goes idle after the first detection
+                {
+                    d_active = true;
+                }
             return 0;
         }
 
@@ -590,10 +605,13 @@ int pcps_acquisition_b200::general_work(int noutput_items, std::vector<int>& nin
         {
         case 0:  // :953-972 — restart
             {
-                d_gnss_synchro->Acq_delay_samples = 0.0;
-                d_gnss_synchro->Acq_doppler_hz = 0.0;
-                d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
-                d_gnss_synchro->Acq_doppler_step = 0U;
+                if (!d_step_repeat)
+                    {
+                        d_gnss_synchro->Acq_delay_samples = 0.0;
+                        d_gnss_synchro->Acq_doppler_hz = 0.0;
+                        d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
+                        d_gnss_synchro->Acq_doppler_step = 0U;
+                    }
                 d_mag = 0.0;
                 d_state = 1;
                 d_buffer_count = 0U;

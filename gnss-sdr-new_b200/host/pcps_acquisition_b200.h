@@ -10,8 +10,7 @@
  * make_2_steps is mirrored: the narrow second search runs on the bank's second-step engine handle.
  * dump = true (N4) writes the reference's per-acquisition .mat file (same name pattern, variables, classes and shapes,
  * :408-508) in the Level-5 container (b200_mat_writer.h) instead of matio's v7.3.
- * Not mirrored: the fork's private make_repeat_steps mode. A configuration asking for it is rejected in the
- * constructor (std::invalid_argument) instead of being ignored.
+ * The fork's make_repeat_steps mode (the block re-arms itself after the first detection and keeps reporting) is mirrored too.
  */
 #ifndef GNSS_SDR_PCPS_ACQUISITION_B200_H
 #define GNSS_SDR_PCPS_ACQUISITION_B200_H
@@ -125,6 +124,7 @@ private:
     uint32_t d_buffer_count{0};
     bool d_active{false};
     bool d_step_two{false};
+    bool d_step_repeat{false};
     bool d_dump{false};
     bool d_worker_active{false};
     bool d_cshort{false};

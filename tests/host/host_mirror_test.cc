@@ -115,6 +115,7 @@ int run_acq(const char* in_path, const char* out_path)
         stream_sc = r.vec<int16_t>(static_cast<size_t>(n_items) * 2);
     else
         stream_fc = r.vec<std::complex<float>>(n_items);
+    uint32_t want_events = 1;  // decisions to wait for per block (the fork's repeat mode keeps reporting)
     if (r.f.peek() != std::ifstream::traits_type::eof())  // optional trailer: make_two_steps (acq_conf.cc:84-90)
         {
             conf.make_2_steps = r.get<uint32_t>() != 0;
@@ -126,6 +127,11 @@ int run_acq(const char* in_path, const char* out_path)
             const auto len = r.get<uint32_t>();
             const auto name = r.vec<char>(len);
             conf.dump_filename.assign(name.begin(), name.end());
+            if (r.f.peek() != std::ifstream::traits_type::eof())
+                {
+                    conf.make_repeat_steps = r.get<uint32_t>() != 0;
+                    want_events = r.get<uint32_t>();
+                }
         }
 
     B200_Acquisition_Bank::set_default_capacity(std::max(1U, n_blocks));
@@ -136,16 +142,23 @@ int run_acq(const char* in_path, const char* out_path)
     std::vector<std::shared_ptr<RecordingFsm>> fsm(n_blocks);
     std::vector<std::atomic<long>> events(n_blocks);
     std::vector<std::atomic<long>> consumed_items(n_blocks);
+    std::vector<std::atomic<uint32_t>> n_positive(n_blocks), n_negative(n_blocks);
     for (uint32_t b = 0; b < n_blocks; b++)
         {
             events[b] = 0;
             consumed_items[b] = 0;
+            n_positive[b] = 0;
+            n_negative[b] = 0;
             synchro[b].System = 'G';
             std::strcpy(synchro[b].Signal, "1C");
             synchro[b].PRN = b + 1;
             blocks[b] = pcps_make_acquisition_b200(conf);
             blocks[b]->consume_each = [&consumed_items, b](int n) { consumed_items[b] += n; };
-            blocks[b]->publish_event = [&events, b](long e) { events[b] = e; };
+            blocks[b]->publish_event = [&events, &n_positive, &n_negative, b](long e) {
+                events[b] = e;
+                if (e == 1) n_positive[b]++;
+                if (e == 2) n_negative[b]++;
+            };
             // Channel's order (channel.cc:49-93)
             blocks[b]->set_channel(b);
             if (use_fsm != 0)
@@ -177,7 +190,8 @@ int run_acq(const char* in_path, const char* out_path)
                 const long before = consumed_items[b];
                 blocks[b]->general_work(0, ninput, in, out);
                 pos += static_cast<size_t>(consumed_items[b] - before);
-                if ((events[b] != 0) || (fsm[b] && fsm[b]->valid > 0)) break;  // decision taken
+                const uint32_t decisions = fsm[b] ? static_cast<uint32_t>(fsm[b]->valid + fsm[b]->failed) : n_positive[b] + n_negative[b];
+                if (decisions >= want_events) break;  // decision(s) taken
                 if (avail == 0)
                     {
                         // stream exhausted: a non-blocking worker may still be running
@@ -205,6 +219,8 @@ int run_acq(const char* in_path, const char* out_path)
             w.put<uint32_t>(blocks[b]->fft_size());
             w.put<uint32_t>(synchro[b].Acq_doppler_step);
             w.put<uint32_t>(blocks[b]->step_two() ? 1U : 0U);
+            w.put<uint32_t>(fsm[b] ? static_cast<uint32_t>(fsm[b]->valid) : n_positive[b].load());
+            w.put<uint32_t>(fsm[b] ? static_cast<uint32_t>(fsm[b]->failed) : n_negative[b].load());
         }
     return 0;
 }

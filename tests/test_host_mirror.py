@@ -59,7 +59,7 @@ def test_mirror_keeps_the_reference_method_set():
 
 
 def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, doppler_step, pfa, threshold, max_dwells, bit_transition,
-                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us, two_steps=None, dump=None):
+                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us, two_steps=None, dump=None, repeat_events=None):
     with open(path, "wb") as f:
         f.write(struct.pack("<q", int(fs)))
         f.write(struct.pack("<IIIiI", sampled_ms, ms_per_code, spc, doppler_max, doppler_step))
@@ -70,12 +70,14 @@ def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, dopple
         for c in codes:
             f.write(np.ascontiguousarray(c, dtype=np.complex64).tobytes())
         f.write(np.ascontiguousarray(stream, dtype=np.int16 if cshort else np.complex64).tobytes())
-        if two_steps is not None or dump is not None:
+        if two_steps is not None or dump is not None or repeat_events is not None:
             ts = two_steps or (0, 125.0, 0.0)             # (second_nbins, second_doppler_step, pfa2)
             f.write(struct.pack("<IIff", int(two_steps is not None), int(ts[0]), float(ts[1]), float(ts[2])))
             name = (dump[1] if dump else "").encode()     # dump = (dump_channel, dump_filename)
             f.write(struct.pack("<III", int(dump is not None), int(dump[0]) if dump else 0, len(name)))
             f.write(name)
+            if repeat_events is not None:             # make_repeat_steps: wait for this many decisions per block
+                f.write(struct.pack("<II", 1, int(repeat_events)))
 
 
 def _read_acq_output(path):
@@ -83,10 +85,10 @@ def _read_acq_output(path):
     n, = struct.unpack_from("<I", raw, 0)
     out, off = [], 4
     for _ in range(n):
-        ev, delay, dop, stamp, stat, thr, nd, nfft, dstep, st2 = struct.unpack_from("<iddQffIIII", raw, off)
-        off += struct.calcsize("<iddQffIIII")
+        ev, delay, dop, stamp, stat, thr, nd, nfft, dstep, st2, npos, nneg = struct.unpack_from("<iddQffIIIIII", raw, off)
+        off += struct.calcsize("<iddQffIIIIII")
         out.append(dict(event=ev, delay=delay, doppler=dop, stamp=stamp, stat=stat, threshold=thr, n_doppler=nd, fft_size=nfft,
-                        doppler_step=dstep, step_two=st2))
+                        doppler_step=dstep, step_two=st2, n_positive=npos, n_negative=nneg))
     return out
 
 
@@ -385,3 +387,40 @@ def test_tracking_dump_files(driver, oracle, oracle_mod, tmp_path, veml):
     for name in TRK_DUMP_DTYPE.names:
         assert m[name].shape == (1, done) and m[name].dtype == TRK_DUMP_DTYPE[name].newbyteorder("="), name
         assert np.array_equal(m[name][0], rec[name]), name
+
+
+@pytest.mark.gpu
+def test_repeat_mode_keeps_reporting(driver, oracle, tmp_path):
+    """The fork's make_repeat_steps (pcps_acquisition.cc:324, 360-368, 944-947, 956): after the first positive acquisition
+    the block re-arms itself and searches again and again without clearing Gnss_Synchro in between; only the first
+    detection writes a dump. Every search is one block of the stream; blocks in between are consumed by the idle and
+    restart calls, so the k-th search sees stream[12000 k : 12000 k + 4000]."""
+    from scipy.io import loadmat
+    geo, codes, iq, truth = synth.config_scene("C1", n_prn=4, n_dwells=10)
+    stream = iq.reshape(-1)
+
+    def search(p, k):
+        a = oracle.acq(fft_size=4000, consumed_samples=4000, doppler_max=geo["doppler_max"], doppler_step=geo["doppler_step"],
+                       fs=geo["fs"], samples_per_chip=geo["samples_per_chip"], samples_per_code=geo["samples_per_code"])
+        a.set_local_code(codes[p])
+        r = a.dwell(stream[12000 * k:12000 * k + 4000])
+        a.close()
+        return r
+    thr = oracle.threshold(0.01, 4000, 40, 1, False)
+    strong = int(np.argmax([search(p, 0)["test_statistic"] for p in range(4)]))
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_acq_input(inp, geo["fs"], 1, 1, geo["samples_per_chip"], geo["doppler_max"], geo["doppler_step"], 0.01, 0.0, 1, False, True,
+                     False, True, [codes[strong]], stream, 4000, False, 0, dump=(0, str(tmp_path / "rep" / "acq")), repeat_events=3)
+    _run(driver, "acq", inp, outp)
+    g = _read_acq_output(outp)[0]
+    want = [search(strong, k) for k in range(3)]
+    assert want[0]["test_statistic"] > thr
+    assert g["n_positive"] + g["n_negative"] == 3
+    assert g["n_positive"] == sum(w["test_statistic"] > thr for w in want)
+    assert g["stamp"] == 4000 + 12000 * 2 and g["stat"] == pytest.approx(want[2]["test_statistic"], rel=1e-4)
+    assert g["doppler"] == float(want[2]["doppler_hz"]) and g["delay"] == float(want[2]["code_phase"] % 4000)
+    # the dump counter moves with every finished search, but d_positive_acq is only raised by the first detection
+    files = sorted(os.listdir(tmp_path / "rep"))
+    assert files[0] == "acq_G_1C_ch_0_1_sat_1.mat" and int(loadmat(str(tmp_path / "rep" / files[0]))["d_positive_acq"][0, 0]) == 1
+    for f in files[1:]:
+        assert int(loadmat(str(tmp_path / "rep" / f))["d_positive_acq"][0, 0]) == 0
