@@ -123,6 +123,8 @@ EXPORTS = [
     "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan",
     "gnss_b200_acq_profile", "gnss_b200_mc_profile", "gnss_b200_debug_fp32_peak",
     "gnss_b200_acq_create_step2", "gnss_b200_acq_set_step2_center",
+    "gnss_b200_firdes_low_pass", "gnss_b200_resampler_create", "gnss_b200_resampler_destroy", "gnss_b200_resampler_reset",
+    "gnss_b200_resampler_work",
     "gnss_b200_trk_create", "gnss_b200_trk_destroy", "gnss_b200_trk_set_code", "gnss_b200_trk_start", "gnss_b200_trk_run",
     "gnss_b200_trk_stream", "gnss_b200_trk_launch_count",
 ]
@@ -142,6 +144,11 @@ def lib():
     L.gnss_b200_last_error.restype = C.c_char_p
     L.gnss_b200_version.restype = C.c_char_p
     L.gnss_b200_acq_create.argtypes = [C.POINTER(AcqCfg), C.POINTER(C.c_void_p)]
+    L.gnss_b200_firdes_low_pass.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, c_u32, C.POINTER(C.c_float), C.POINTER(c_u32)]
+    L.gnss_b200_resampler_create.argtypes = [c_u32, c_u32, C.POINTER(C.c_float), c_u32, c_i32, C.POINTER(C.c_void_p)]
+    L.gnss_b200_resampler_destroy.argtypes = [C.c_void_p]
+    L.gnss_b200_resampler_reset.argtypes = [C.c_void_p]
+    L.gnss_b200_resampler_work.argtypes = [C.c_void_p, C.c_void_p, c_u32, C.c_void_p, C.POINTER(C.c_void_p)]
     L.gnss_b200_acq_destroy.argtypes = [C.c_void_p]
     L.gnss_b200_acq_create_step2.argtypes = [C.POINTER(AcqCfg), c_u32, C.c_float, C.POINTER(C.c_void_p)]
     L.gnss_b200_acq_set_step2_center.argtypes = [C.c_void_p, c_u32, C.c_float, C.c_float]
@@ -509,3 +516,47 @@ class TrackingLoopB200:
 
     def launch_count(self):
         return int(self.L.gnss_b200_trk_launch_count(self.h))
+
+
+def firdes_low_pass(gain, fs, cutoff, transition):
+    """gr::filter::firdes::low_pass (Hamming) as the flow graph calls it for the acquisition resampler."""
+    taps = np.zeros(4096, dtype=np.float32)
+    n = c_u32(0)
+    _check(lib().gnss_b200_firdes_low_pass(float(gain), float(fs), float(cutoff), float(transition), taps.size,
+                                           taps.ctypes.data_as(C.POINTER(C.c_float)), C.byref(n)))
+    return taps[:n.value].copy()
+
+
+class AcqResamplerB200:
+    """The decimating FIR in front of the acquisition blocks (gnss_flowgraph.cc:1063-1118), output resident on the device."""
+
+    def __init__(self, decimation, taps, max_input_items, device=0):
+        self.L = lib()
+        self.decimation = int(decimation)
+        taps = np.ascontiguousarray(taps, dtype=np.float32)
+        self.latency = (taps.size - 1) // 2          # Channel::acquisition()->set_resampler_latency (:1111)
+        self.h = C.c_void_p()
+        _check(self.L.gnss_b200_resampler_create(self.decimation, taps.size, taps.ctypes.data_as(C.POINTER(C.c_float)), int(max_input_items),
+                                                 int(device), C.byref(self.h)))
+
+    def reset(self):
+        _check(self.L.gnss_b200_resampler_reset(self.h))
+
+    def work(self, x, want_host=True):
+        """-> (decimated items on the host or None, device pointer of the same items)"""
+        x = np.ascontiguousarray(x, dtype=np.complex64)
+        out = np.empty(x.size // self.decimation, dtype=np.complex64) if want_host else None
+        dptr = C.c_void_p()
+        _check(self.L.gnss_b200_resampler_work(self.h, x.ctypes.data, x.size, out.ctypes.data if want_host else None, C.byref(dptr)))
+        return out, dptr.value
+
+    def close(self):
+        if self.h:
+            self.L.gnss_b200_resampler_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

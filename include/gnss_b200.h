@@ -328,6 +328,32 @@ extern "C"
     /* parity aids (pure host, no device needed)                           */
     /* ------------------------------------------------------------------ */
 
+    /* ---------------------------------------------------------------------------------------------
+     * Acquisition resampler: the decimating low-pass FIR GNSSFlowgraph connects in front of the
+     * acquisition blocks with GNSS-SDR.use_acquisition_resampler (gnss_flowgraph.cc:1063-1118; decimation from
+     * Acq_Conf::ConfigureAutomaticResampler, acq_conf.cc:93-111). Replaces gr::filter::firdes::low_pass and
+     * gr::filter::fir_filter_ccf (GNU Radio, not part of the reference tree: published algorithm restated).
+     * ------------------------------------------------------------------------------------------- */
+    typedef struct gnss_b200_resampler gnss_b200_resampler;
+    /* firdes::low_pass(gain, fs, cutoff, transition) with the default Hamming window: odd tap count
+       int(53 fs / (22 transition)), windowed sinc, unity DC gain times `gain`. The flow graph calls it as
+       low_pass(1.0, fs, acq_fs / 2.1, acq_fs / 2) (:1084-1087). */
+    GNSS_B200_API int gnss_b200_firdes_low_pass(double gain, double sampling_freq, double cutoff_freq, double transition_width,
+        uint32_t max_taps, float* taps, uint32_t* n_taps);
+    /* fir_filter_ccf::make(decimation, taps) (:1089); max_input_items bounds one work() call */
+    GNSS_B200_API int gnss_b200_resampler_create(uint32_t decimation, uint32_t n_taps, const float* taps, uint32_t max_input_items,
+        int32_t device, gnss_b200_resampler** out);
+    GNSS_B200_API int gnss_b200_resampler_destroy(gnss_b200_resampler* h);
+    /* forget the history: the next item is the first of a stream (ntaps - 1 zeros before it) */
+    GNSS_B200_API int gnss_b200_resampler_reset(gnss_b200_resampler* h);
+    /* one work() call: n_input_items (a multiple of the decimation) gr_complex items from the host, y[m] = sum_j taps[j] x[m D - j]
+       with the previous calls' items as history. The n_input_items / decimation output items stay in device memory
+       (*out_device, valid until the next call: pass it to gnss_b200_acq_dwell_device_async) and are copied to out_c64 if
+       that is not NULL. The filter delay the block has to report is (ntaps - 1) / 2 input items
+       (set_resampler_latency, :1111). */
+    GNSS_B200_API int gnss_b200_resampler_work(gnss_b200_resampler* h, const float* in_c64, uint32_t n_input_items, float* out_c64,
+        const void** out_device);
+
     /* The binary32 running-sum phase of the reference's wipe-off row for one Doppler bin
        (volk_gnsssdr_s32f_sincos_32fc_generic, volk_gnsssdr_s32f_sincos_32fc.h:390-400), as reproduced in closed
        form by the engine: phase_out[n], n < n_samples. n_pieces (optional) = number of linear pieces used. */
