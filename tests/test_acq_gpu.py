@@ -380,3 +380,46 @@ def test_runtime_geometry_kernels_agree_with_fixed_ones():
                         "known_answer or config1 or config2 or noncoherent or zero_padded or cshort or cbyte or two_step"], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout
+
+
+_FIXED_CHILD = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tools")
+from b200_import import load_package
+b = load_package()
+out = {}
+rng = np.random.default_rng(77)
+for N in (4000, 8000, 16000, 25000, 32000, 50000, 100000, 160000):
+    for keep in (False, True):
+        e = b.PcpsAcquisitionB200(N, N, 500, 250, 4e6, 4, 2, use_cfar=True, keep_grid=keep)
+        codes = np.sign(rng.standard_normal((2, N))).astype(np.complex64)
+        x = (rng.standard_normal(N) + 1j * rng.standard_normal(N)).astype(np.complex64)
+        x += 0.2 * np.roll(codes[0], 1234 % N) * np.exp(2j * np.pi * 250.0 / 4e6 * np.arange(N))
+        e.set_local_codes([0, 1], codes)
+        r = e.dwell(x, [0, 1])
+        if keep:
+            r = e.dwell(x[::-1].copy(), [0, 1])          # second dwell: accumulation path
+            out["grid%d" % N] = e.read_grid(0)
+        out["res%d_%d" % (N, keep)] = r.view(np.uint8).copy()
+        e.close()
+np.savez(sys.argv[2], **out)
+"""
+
+
+def test_fixed_geometry_kernels_are_bit_identical_to_runtime_ones(tmp_path):
+    """Every dwell length with compile-time-geometry instantiations (forward, both inverse stages, records-only and
+    persistent-grid modes): result records and accumulated grids must equal those of the runtime-geometry kernels BIT FOR
+    BIT — same arithmetic in the same order, only the address computations differ."""
+    import subprocess
+    import sys
+    outs = []
+    for tag, extra in (("fixed", {}), ("runtime", {"B200_NO_FIXED": "1"})):
+        path = str(tmp_path / (tag + ".npz"))
+        r = subprocess.run([sys.executable, "-c", _FIXED_CHILD, os.path.dirname(os.path.dirname(os.path.abspath(__file__))), path],
+                           env=dict(os.environ, **extra), capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+        outs.append(np.load(path))
+    a, c = outs
+    assert sorted(a.files) == sorted(c.files) and len(a.files) == 24
+    for k in a.files:
+        assert np.array_equal(a[k], c[k]), k
