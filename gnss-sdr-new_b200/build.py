@@ -45,7 +45,7 @@ def build(force=False, verbose=False):
 HOST_DIR = os.path.join(HERE, "host")
 HOST_LIB = os.path.join(HERE, "libgnss_b200_host.so")
 HOST_SOURCES = ["b200_correlator_pool.cc", "b200_multicorrelator_real_codes.cc", "b200_multicorrelator.cc",
-                "b200_acquisition_bank.cc", "b200_mat_writer.cc", "b200_tracking_dump.cc", "pcps_acquisition_b200.cc"]
+                "b200_acquisition_bank.cc", "b200_mat_writer.cc", "b200_tracking_dump.cc", "b200_symbol_sync.cc", "pcps_acquisition_b200.cc"]
 HOST_TEST_SRC = os.path.join(HERE, "..", "tests", "host", "host_mirror_test.cc")
 HOST_TEST_BIN = os.path.join(HERE, "..", "tests", "host", "host_mirror_test")
 

@@ -10,6 +10,7 @@
 #include "b200_correlator_pool.h"
 #include "b200_mat_writer.h"
 #include "b200_multicorrelator.h"
+#include "b200_symbol_sync.h"
 #include "b200_tracking_dump.h"
 #include "b200_multicorrelator_real_codes.h"
 #include "pcps_acquisition_b200.h"
@@ -364,6 +365,47 @@ int run_trkdump(const char* in_path, const char* dump_filename)
     if (!dump.log(epochs.data(), n / 2, veml) || !dump.log(epochs.data() + n / 2, n - n / 2, veml)) return 5;
     return dump.finish() == 0 ? 0 : 6;
 }
+// Symbol synchronisation: <in> = u32 n, u32 secondary, u32 code_len, u32 symbols_per_bit, u32 data_len, code string bytes
+// (code_len), data code string bytes (data_len), then n gnss_b200_trk_epoch records; <out> = u32 count, then per symbol
+// { u32 epoch index, f64 I, f64 Q, u64 counter, u32 pll_180 }, then u32 locked, u32 current_symbol.
+int run_symsync(const char* in_path, const char* out_path)
+{
+    Reader r(in_path);
+    const auto n = r.get<uint32_t>();
+    const bool secondary = r.get<uint32_t>() != 0;
+    const auto code_len = r.get<uint32_t>();
+    const auto spb = r.get<uint32_t>();
+    const auto data_len = r.get<uint32_t>();
+    const auto code = r.vec<char>(code_len);
+    const auto data_code = r.vec<char>(data_len);
+    const auto epochs = r.vec<gnss_b200_trk_epoch>(n);
+    B200_Symbol_Sync sync;
+    sync.configure(secondary, std::string(code.begin(), code.end()), code_len, spb, std::string(data_code.begin(), data_code.end()), data_len, false);
+    struct Rec
+    {
+        uint32_t i;
+        B200_Symbol_Sync::Symbol s;
+    };
+    std::vector<Rec> got;
+    for (uint32_t i = 0; i < n; i++)
+        {
+            B200_Symbol_Sync::Symbol s{};
+            if (sync.push(epochs[i], &s)) got.push_back(Rec{i, s});
+        }
+    Writer w(out_path);
+    w.put<uint32_t>(static_cast<uint32_t>(got.size()));
+    for (const auto& g : got)
+        {
+            w.put<uint32_t>(g.i);
+            w.put<double>(g.s.Prompt_I);
+            w.put<double>(g.s.Prompt_Q);
+            w.put<uint64_t>(g.s.Tracking_sample_counter);
+            w.put<uint32_t>(g.s.Flag_PLL_180_deg_phase_locked ? 1U : 0U);
+        }
+    w.put<uint32_t>(sync.locked() ? 1U : 0U);
+    w.put<uint32_t>(sync.current_symbol());
+    return 0;
+}
 }  // namespace
 
 int main(int argc, char** argv)
@@ -375,12 +417,13 @@ int main(int argc, char** argv)
             if (argc == 2 && std::strcmp(argv[1], "nodevice") == 0) return run_nodevice();
             if (argc == 3 && std::strcmp(argv[1], "mat") == 0) return run_mat(argv[2]);
             if (argc == 4 && std::strcmp(argv[1], "trkdump") == 0) return run_trkdump(argv[2], argv[3]);
+            if (argc == 4 && std::strcmp(argv[1], "symsync") == 0) return run_symsync(argv[2], argv[3]);
         }
     catch (const std::exception& e)
         {
             std::cerr << "host_mirror_test: " << e.what() << '\n';
             return 2;
         }
-    std::cerr << "usage: host_mirror_test acq|mc <in> <out> | trkdump <in> <dump_filename> | mat <out> | nodevice\n";
+    std::cerr << "usage: host_mirror_test acq|mc <in> <out> | trkdump <in> <dump_filename> | symsync <in> <out> | mat <out> | nodevice\n";
     return 1;
 }

@@ -424,3 +424,95 @@ def test_repeat_mode_keeps_reporting(driver, oracle, tmp_path):
     assert files[0] == "acq_G_1C_ch_0_1_sat_1.mat" and int(loadmat(str(tmp_path / "rep" / files[0]))["d_positive_acq"][0, 0]) == 1
     for f in files[1:]:
         assert int(loadmat(str(tmp_path / "rep" / f))["d_positive_acq"][0, 0]) == 0
+
+
+def _symsync_expected(prompts, flags, secondary, code, spb, data_code):
+    """dll_pll_veml_tracking.cc:1890-1946 (collect + acquire_secondary), :1290-1400 and :2041-2066 (accumulate + emit), restated
+    in Python for the prompt only; binary32 sums in arrival order."""
+    out, buf, locked, cur_d, acc, flag180 = [], [], False, 0, np.complex64(0), False
+    for i, (p, fl) in enumerate(zip(prompts, flags)):
+        if not fl & 1:
+            continue
+        if fl & 4:
+            buf, locked, cur_d, acc, flag180 = [], False, 0, np.complex64(0), False
+            continue
+        if not locked:
+            if fl & 2:
+                continue
+            if secondary or spb > 1:
+                buf = (buf + [p])[-len(code):]
+                if len(buf) == len(code):
+                    corr = sum((1 if c == "0" else -1) if b.real < 0 else (-1 if c == "0" else 1) for b, c in zip(buf, code))
+                    if abs(corr) == len(code):
+                        locked, flag180, buf, cur_d, acc = True, corr < 0, [], 0, np.complex64(0)
+            else:
+                locked = True
+            continue
+        if spb > 1:
+            if data_code:
+                acc = np.complex64(acc + p) if data_code[cur_d] == "0" else np.complex64(acc - p)
+                cur_d = (cur_d + 1) % len(data_code)
+            else:
+                acc = np.complex64(acc + p)
+                cur_d = (cur_d + 1) % spb
+        else:
+            acc = p
+        if cur_d == 0:
+            out.append((i, float(acc.real), float(acc.imag), flag180))
+            acc = np.complex64(0)
+    return out, locked
+
+
+GPS_CA_PREAMBLE_SYMBOLS_STR = "".join(c * 20 for c in "10001011")   # GPS_L1_CA.h:73
+BEIDOU_B1I_SECONDARY_CODE_STR = "00000100110101001110"              # Beidou_B1I.h
+
+
+@pytest.mark.parametrize("case", ["gps_l1_ca", "gps_l1_ca_inverted", "bds_b1i_nh", "one_symbol_per_period"])
+def test_symbol_synchronisation_on_epoch_records(driver, b200, tmp_path, case):
+    """B200_Symbol_Sync: bit / secondary-code lock and per-bit prompt accumulation from the device loop's records."""
+    rng = np.random.default_rng(11)
+    if case.startswith("gps_l1_ca"):
+        secondary, code, spb, data_code = False, GPS_CA_PREAMBLE_SYMBOLS_STR, 20, ""
+        bits = list(rng.integers(0, 2, 7)) + [1, 0, 0, 0, 1, 0, 1, 1] + list(rng.integers(0, 2, 12))
+        signs = np.repeat(np.array(bits) * 2 - 1, 20)[7:]             # the stream starts in the middle of a bit
+        if case.endswith("inverted"):
+            signs = -signs                                             # Costas loop locked half a cycle off
+    elif case == "bds_b1i_nh":
+        secondary, code, spb, data_code = True, BEIDOU_B1I_SECONDARY_CODE_STR, 20, BEIDOU_B1I_SECONDARY_CODE_STR
+        nh = np.array([1 if c == "1" else -1 for c in code])
+        bits = rng.integers(0, 2, 14) * 2 - 1
+        signs = (np.repeat(bits, 20) * np.tile(nh, 14))[13:]
+    else:
+        secondary, code, spb, data_code = False, "", 1, ""
+        signs = rng.integers(0, 2, 60) * 2 - 1
+    n = signs.size
+    ep = np.zeros(n, dtype=b200.TRK_EPOCH_DTYPE)
+    ep["corr"][:, 4] = (1000.0 * signs + rng.standard_normal(n) * 40).astype(np.float32)
+    ep["corr"][:, 5] = (rng.standard_normal(n) * 40).astype(np.float32)
+    ep["sample_counter"] = 5000 + 4000 * np.arange(n)
+    ep["prn_length_samples"] = 4000
+    ep["flags"] = 1
+    ep["flags"][:9] |= 2                               # pull-in transitory: nothing collected
+    ep["flags"][n - 30] |= 4                           # a loss of lock near the end: back to the search
+    ep["flags"][n - 12] = 0                            # an unused record
+    prompts = (ep["corr"][:, 4] + 1j * ep["corr"][:, 5]).astype(np.complex64)
+    want, want_locked = _symsync_expected(prompts, ep["flags"], secondary, code, spb, data_code)
+    inp, outp = tmp_path / "s.bin", tmp_path / "s.out"
+    with open(inp, "wb") as f:
+        f.write(struct.pack("<IIIII", n, int(secondary), len(code), spb, len(data_code)))
+        f.write(code.encode() + data_code.encode())
+        f.write(ep.tobytes())
+    r = subprocess.run([driver, "symsync", str(inp), str(outp)], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = open(outp, "rb").read()
+    cnt, = struct.unpack_from("<I", raw, 0)
+    got = [struct.unpack_from("<IddQI", raw, 4 + k * struct.calcsize("<IddQI")) for k in range(cnt)]
+    locked, _ = struct.unpack_from("<II", raw, 4 + cnt * struct.calcsize("<IddQI"))
+    assert cnt == len(want) and cnt >= (3 if spb > 1 else 40)
+    for g, w in zip(got, want):
+        assert g[0] == w[0] and g[1] == w[1] and g[2] == w[2] and bool(g[4]) == w[3]
+        assert g[3] == 5000 + 4000 * g[0]
+    assert bool(locked) == want_locked
+    if case.startswith("gps_l1_ca"):
+        # the first symbols after the preamble are whole bits: 20 prompts of one sign (inverted stream: flag set, sign kept)
+        assert all(abs(abs(g[1]) - 20000.0) < 1500.0 for g in got[:3]) and bool(got[0][4]) == case.endswith("inverted")
