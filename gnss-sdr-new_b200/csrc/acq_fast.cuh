@@ -192,7 +192,7 @@ __host__ __device__ __forceinline__ uint32_t upper_group_stride(uint32_t ra, uin
 // MLO, CC != 0: the lower-stage length and the column tile are compile-time (launch with block (CC, kFastThreads / CC)): every
 // shared-memory and global offset of a pencil folds into an immediate and the pencil loops unroll.
 template <int RA, int RB, int MODE = 0, int MLO = 0, int CC = 0>
-__global__ void __launch_bounds__(kFastThreads, (MODE == 2 && CC != 0 && RA <= 16) ? 6 : 1) inv_upper_kernel(const FastArgs a)
+__global__ void __launch_bounds__(kFastThreads, (MODE == 2 && CC != 0 && RA <= 16) ? 6 : 0) inv_upper_kernel(const FastArgs a)
 {
     constexpr int M = RA * RB;
     extern __shared__ __align__(16) unsigned char smem_raw[];
