@@ -65,6 +65,17 @@ MC_HIGH_DYN = 1
 MC_SIX_ARG = 2
 
 
+class McNoAllocChan(C.Structure):
+    """gnss_b200_mc_noalloc_chan: one channel of gnss_b200_mc_correlate_noalloc (device pointers, no handle)."""
+    _fields_ = [
+        ("d_sig_c64", C.c_void_p), ("d_code", C.c_void_p), ("code_len", c_u32), ("n_samples", c_u32),
+        ("rem_carr_phase_rad", C.c_float), ("carr_step_rad", C.c_float), ("rem_code_phase_chips", C.c_float), ("code_step_chips", C.c_float),
+    ]
+
+
+MC_NOALLOC_MAX_CHANNELS, MC_NOALLOC_MAX_TAPS, MC_NOALLOC_MAX_SAMPLES = 64, 16, 1 << 22
+
+
 class TrkCfg(C.Structure):
     """gnss_b200_trk_cfg: Dll_Pll_Conf (dll_pll_conf.h:37-84) + the signal constants the block derives (dll_pll_veml_tracking.cc:105-460)."""
     _fields_ = [
@@ -123,6 +134,7 @@ EXPORTS = [
     "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan",
     "gnss_b200_acq_profile", "gnss_b200_mc_profile", "gnss_b200_debug_fp32_peak",
     "gnss_b200_acq_create_step2", "gnss_b200_acq_set_step2_center",
+    "gnss_b200_mc_correlate_noalloc", "gnss_b200_mc_noalloc_scratch_bytes",
     "gnss_b200_firdes_low_pass", "gnss_b200_resampler_create", "gnss_b200_resampler_destroy", "gnss_b200_resampler_reset",
     "gnss_b200_resampler_work",
     "gnss_b200_trk_create", "gnss_b200_trk_destroy", "gnss_b200_trk_set_code", "gnss_b200_trk_start", "gnss_b200_trk_run",
@@ -144,6 +156,9 @@ def lib():
     L.gnss_b200_last_error.restype = C.c_char_p
     L.gnss_b200_version.restype = C.c_char_p
     L.gnss_b200_acq_create.argtypes = [C.POINTER(AcqCfg), C.POINTER(C.c_void_p)]
+    L.gnss_b200_mc_correlate_noalloc.argtypes = [c_i32, C.c_void_p, c_u32, C.POINTER(McNoAllocChan), C.POINTER(C.c_float), c_u32, C.c_void_p]
+    L.gnss_b200_mc_noalloc_scratch_bytes.restype = C.c_uint64
+    L.gnss_b200_mc_noalloc_scratch_bytes.argtypes = []
     L.gnss_b200_firdes_low_pass.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, c_u32, C.POINTER(C.c_float), C.POINTER(c_u32)]
     L.gnss_b200_resampler_create.argtypes = [c_u32, c_u32, C.POINTER(C.c_float), c_u32, c_i32, C.POINTER(C.c_void_p)]
     L.gnss_b200_resampler_destroy.argtypes = [C.c_void_p]
@@ -560,3 +575,15 @@ class AcqResamplerB200:
             self.close()
         except Exception:
             pass
+
+
+def mc_correlate_noalloc(device, cuda_stream, chans, shifts, d_out_ptr):
+    """gnss_b200_mc_correlate_noalloc: `chans` = list of dict(d_sig, d_code, code_len, n_samples, rem_carr, carr_step, rem_code,
+    code_step) with DEVICE pointers, `shifts` host [n_ch][n_taps], d_out_ptr DEVICE [n_ch][n_taps] c64. Enqueues only."""
+    shifts = np.ascontiguousarray(shifts, dtype=np.float32)
+    arr = (McNoAllocChan * len(chans))()
+    for i, c in enumerate(chans):
+        arr[i] = McNoAllocChan(c["d_sig"], c["d_code"], int(c["code_len"]), int(c["n_samples"]), float(c["rem_carr"]), float(c["carr_step"]),
+                               float(c["rem_code"]), float(c["code_step"]))
+    _check(lib().gnss_b200_mc_correlate_noalloc(int(device), cuda_stream, len(chans), arr, _f32p(shifts), shifts.shape[1] if shifts.ndim == 2 else shifts.size,
+                                                d_out_ptr))

@@ -1019,3 +1019,136 @@ extern "C"
     void* gnss_b200_mc_stream(gnss_b200_mc* h) { return h ? (void*)h->stream : nullptr; }
     uint64_t gnss_b200_mc_launch_count(const gnss_b200_mc* h) { return h ? h->launches : 0; }
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// gnss_b200_mc_correlate_noalloc: the multicorrelator for callers that may not allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// Same kernels as gnss_b200_mc_correlate_batch (general real-code kernel, plain resampler); everything the
+// handle-based path keeps in cudaMalloc'ed buffers — the per-channel parameter blocks, the tap shifts, the per-CTA split
+// partials and the per-channel tickets — lives in ONE file-scope device array of fixed size instead. Every GPU that loads
+// the library holds that array (kNoAllocScratchBytes, ~141 KB) until the process exits.
+//
+// In host code `g_mc_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is asked for
+// with cudaGetSymbolAddress once per device, with that device current, and only that pointer is handed to kernels.
+// Every call on a device shares the array and finds the previous call's contents in it: the tickets are cleared on the
+// stream before each launch, the parameter blocks and shifts are rewritten, the partials are fully overwritten before
+// they are read. Two calls whose GPU work overlaps (different streams, or different host threads) race on it.
+// ------------------------------------------------------------------------------------------------------------------
+namespace
+{
+constexpr uint32_t kNoAllocMaxChannels = GNSS_B200_MC_NOALLOC_MAX_CHANNELS;
+constexpr uint32_t kNoAllocMaxTaps = GNSS_B200_MC_NOALLOC_MAX_TAPS;
+constexpr uint32_t kNoAllocMaxSamples = GNSS_B200_MC_NOALLOC_MAX_SAMPLES;
+constexpr uint32_t kNoAllocMaxCtas = 1024;  // channels x splits
+constexpr uint32_t kNoAllocSmemElems = 8192;  // 32 KB of chips per CTA (window, whole code, or global fallback)
+constexpr int kNoAllocMaxDevices = 64;
+static_assert(kNoAllocMaxTaps <= (uint32_t)kMaxTapsPerPass, "one pass per call");
+
+struct NoAllocScratch
+{
+    ChanParams params[kNoAllocMaxChannels];
+    float shifts[kNoAllocMaxChannels * kNoAllocMaxTaps];
+    uint32_t shift_samples[kNoAllocMaxChannels * kNoAllocMaxTaps];  // stays zero: plain resampler
+    uint32_t tickets[kNoAllocMaxChannels];
+    float2 partials[kNoAllocMaxCtas * kNoAllocMaxTaps];
+};
+constexpr size_t kNoAllocScratchBytes = sizeof(NoAllocScratch);
+static_assert(kNoAllocScratchBytes < 160 * 1024, "keep the resident scratch modest");
+
+static __device__ __align__(256) unsigned char g_mc_noalloc_scratch[kNoAllocScratchBytes];
+
+std::mutex g_noalloc_mu;
+NoAllocScratch* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+
+// device address of the scratch on `device` (current): resolved once per device
+int noalloc_scratch(int device, NoAllocScratch** out)
+{
+    B200_REQUIRE(device >= 0 && device < kNoAllocMaxDevices, GNSS_B200_ERR_INVALID, "mc_correlate_noalloc: device %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (g_noalloc_ptr[device] == nullptr)
+        {
+            void* p = nullptr;
+            B200_CUDA(cudaGetSymbolAddress(&p, g_mc_noalloc_scratch));
+            B200_REQUIRE(p != nullptr, GNSS_B200_ERR_CUDA, "mc_correlate_noalloc: cudaGetSymbolAddress returned a null address");
+            g_noalloc_ptr[device] = static_cast<NoAllocScratch*>(p);
+        }
+    *out = g_noalloc_ptr[device];
+    return GNSS_B200_OK;
+}
+}  // namespace
+
+extern "C"
+{
+    int gnss_b200_mc_correlate_noalloc(int32_t device, void* cuda_stream, uint32_t n_ch, const gnss_b200_mc_noalloc_chan* chans, const float* shifts,
+        uint32_t n_taps, void* d_out_c64)
+    {
+        B200_REQUIRE(chans && shifts && d_out_c64, GNSS_B200_ERR_INVALID, "mc_correlate_noalloc: null argument");
+        B200_REQUIRE(n_ch >= 1 && n_ch <= kNoAllocMaxChannels, GNSS_B200_ERR_INVALID,
+            "mc_correlate_noalloc: %u channels, the resident scratch holds at most %u per call", n_ch, kNoAllocMaxChannels);
+        B200_REQUIRE(n_taps >= 1 && n_taps <= kNoAllocMaxTaps, GNSS_B200_ERR_INVALID,
+            "mc_correlate_noalloc: %u taps, the resident scratch holds at most %u", n_taps, kNoAllocMaxTaps);
+        uint32_t max_n = 1;
+        for (uint32_t i = 0; i < n_ch; i++)
+            {
+                B200_REQUIRE(chans[i].d_sig_c64 && chans[i].d_code && chans[i].code_len >= 1, GNSS_B200_ERR_INVALID, "mc_correlate_noalloc: channel %u: null device pointer or empty code", i);
+                B200_REQUIRE(chans[i].n_samples >= 1 && chans[i].n_samples <= kNoAllocMaxSamples, GNSS_B200_ERR_INVALID,
+                    "mc_correlate_noalloc: channel %u: %u samples, at most %u per call", i, chans[i].n_samples, kNoAllocMaxSamples);
+                max_n = std::max(max_n, chans[i].n_samples);
+            }
+        int rc = select_device(device);
+        if (rc) return rc;
+        NoAllocScratch* scr = nullptr;
+        rc = noalloc_scratch(device, &scr);
+        if (rc) return rc;
+        cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+
+        // split each channel over several CTAs when the batch alone cannot fill the machine (as build_params does)
+        uint32_t splits = 1;
+        const uint32_t target_ctas = kNumSMs * 4;
+        if (n_ch < target_ctas)
+            {
+                splits = (target_ctas + n_ch - 1) / n_ch;
+                splits = std::max(1u, std::min(splits, std::max(1u, max_n / 2048)));
+            }
+        splits = std::max(1u, std::min(splits, kNoAllocMaxCtas / n_ch));
+
+        // per-channel constants (cpu_multicorrelator_real_codes.cc:114-119), on the stack: nothing is allocated
+        ChanParams cp[kNoAllocMaxChannels];
+        for (uint32_t i = 0; i < n_ch; i++)
+            {
+                const gnss_b200_mc_noalloc_chan& a = chans[i];
+                ChanParams& p = cp[i];
+                std::memset(&p, 0, sizeof(p));
+                p.sig = static_cast<const float2*>(a.d_sig_c64);
+                p.code = a.d_code;
+                p.code_len = a.code_len;
+                p.n = a.n_samples;
+                p.rem_code = a.rem_code_phase_chips;
+                p.code_step = a.code_step_chips;
+                p.code_rate = 0.f;
+                float s0, c0;
+                sincosf(a.rem_carr_phase_rad, &s0, &c0);
+                p.p0_re = c0;
+                p.p0_im = -s0;
+                float inc_re, inc_im;
+                sincosf(-a.carr_step_rad, &inc_im, &inc_re);  // the rounded per-sample phasor; prep_kernel derives theta from it
+                p.theta = 0.0;
+                p.wb_re = inc_re;
+                p.wb_im = inc_im;
+                p.rate_arg = 0.f;
+                p.flags = 0u;
+                p.shifts_off = i * n_taps;
+            }
+        // pageable host memory: the runtime stages these copies before it returns, so the stack buffers may go away
+        B200_CUDA(cudaMemcpyAsync(scr->params, cp, sizeof(ChanParams) * n_ch, cudaMemcpyHostToDevice, st));
+        B200_CUDA(cudaMemcpyAsync(scr->shifts, shifts, sizeof(float) * (size_t)n_ch * n_taps, cudaMemcpyHostToDevice, st));
+        B200_CUDA(cudaMemsetAsync(scr->tickets, 0, sizeof(uint32_t) * n_ch, st));  // must start at zero whatever the last call left
+        prep_kernel<<<(n_ch + 127) / 128, 128, 0, st>>>(scr->params, n_ch);
+        B200_CUDA(cudaGetLastError());
+        B200_CUDA(mc::launch_real_plain(false, n_ch, splits, kNoAllocSmemElems, st, scr->params, scr->shifts, scr->shift_samples, scr->partials, scr->tickets,
+            static_cast<float2*>(d_out_c64), n_taps));
+        return GNSS_B200_OK;
+    }
+
+    uint64_t gnss_b200_mc_noalloc_scratch_bytes(void) { return (uint64_t)kNoAllocScratchBytes; }
+}

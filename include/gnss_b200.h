@@ -329,6 +329,35 @@ extern "C"
     /* ------------------------------------------------------------------ */
 
     /* ---------------------------------------------------------------------------------------------
+     * Multicorrelator without allocation. NO COUNTERPART IN THE REFERENCE: added for
+     * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+     * The same computation as gnss_b200_mc_correlate_batch for real codes and the plain resampler, without a handle: inputs
+     * and outputs are the caller's DEVICE buffers, and the scratch (parameter blocks, tap shifts, split partials, tickets)
+     * is a fixed device array inside the library (gnss_b200_mc_noalloc_scratch_bytes(), ~141 KB, held by every GPU that
+     * loads the library until the process exits). The call allocates nothing (no cudaMalloc / cudaFree / allocating
+     * library routine), enqueues its work on `cuda_stream` (a cudaStream_t; NULL = the default stream) and returns without
+     * synchronising: d_out_c64 is valid once that stream has caught up.
+     * Limits (GNSS_B200_ERR_INVALID with a message beyond them): GNSS_B200_MC_NOALLOC_MAX_CHANNELS channels,
+     * GNSS_B200_MC_NOALLOC_MAX_TAPS taps, GNSS_B200_MC_NOALLOC_MAX_SAMPLES samples per channel and call.
+     * All calls on one GPU share the scratch: calls whose GPU work overlaps (two streams, two threads) RACE — serialise them.
+     * ------------------------------------------------------------------------------------------- */
+#define GNSS_B200_MC_NOALLOC_MAX_CHANNELS 64u
+#define GNSS_B200_MC_NOALLOC_MAX_TAPS 16u
+#define GNSS_B200_MC_NOALLOC_MAX_SAMPLES (1u << 22)
+    typedef struct
+    {
+        const void* d_sig_c64;      /* DEVICE pointer: n_samples gr_complex (interleaved float re, im) */
+        const float* d_code;        /* DEVICE pointer: code_len floats (d_local_code_in) */
+        uint32_t code_len;          /* code_length_chips (x samples per chip) */
+        uint32_t n_samples;         /* signal_length_samples */
+        float rem_carr_phase_rad, carr_step_rad, rem_code_phase_chips, code_step_chips;
+    } gnss_b200_mc_noalloc_chan;
+    /* shifts: HOST [n_ch][n_taps] (d_shifts_chips); d_out_c64: DEVICE [n_ch][n_taps] gr_complex (d_corr_out) */
+    GNSS_B200_API int gnss_b200_mc_correlate_noalloc(int32_t device, void* cuda_stream, uint32_t n_ch, const gnss_b200_mc_noalloc_chan* chans,
+        const float* shifts, uint32_t n_taps, void* d_out_c64);
+    GNSS_B200_API uint64_t gnss_b200_mc_noalloc_scratch_bytes(void);
+
+    /* ---------------------------------------------------------------------------------------------
      * Acquisition resampler: the decimating low-pass FIR GNSSFlowgraph connects in front of the
      * acquisition blocks with GNSS-SDR.use_acquisition_resampler (gnss_flowgraph.cc:1063-1118; decimation from
      * Acq_Conf::ConfigureAutomaticResampler, acq_conf.cc:93-111). Replaces gr::filter::firdes::low_pass and
