@@ -6,7 +6,7 @@
 
 B200_Multicorrelator::~B200_Multicorrelator()
 {
-    if (d_channel >= 0)
+    if (m_pool_slot >= 0)
         {
             B200_Multicorrelator::free();
         }
@@ -17,32 +17,32 @@ B200_Multicorrelator::~B200_Multicorrelator()
 bool B200_Multicorrelator::init(int max_signal_length_samples, int n_correlators)
 {
     if (max_signal_length_samples <= 0 || n_correlators <= 0) return false;
-    if (d_channel < 0)
+    if (m_pool_slot < 0)
         {
-            d_channel = B200_Correlator_Pool::instance().acquire_channel();
+            m_pool_slot = B200_Correlator_Pool::instance().acquire_channel();
         }
-    d_n_correlators = n_correlators;
-    d_max_signal_length_samples = max_signal_length_samples;
-    return d_channel >= 0;
+    m_n_taps = n_correlators;
+    m_capacity = max_signal_length_samples;
+    return m_pool_slot >= 0;
 }
 
 
 // reference :50-60
 bool B200_Multicorrelator::set_local_code_and_taps(int code_length_chips, const std::complex<float> *local_code_in, float *shifts_chips)
 {
-    d_local_code_in = local_code_in;
-    d_shifts_chips = shifts_chips;
-    d_code_length_chips = code_length_chips;
-    if (d_channel < 0) return false;
-    return B200_Correlator_Pool::instance().set_code(d_channel, code_length_chips, reinterpret_cast<const float *>(local_code_in), true);
+    m_io.code = local_code_in;
+    m_io.tap_shifts = shifts_chips;
+    m_code_len = code_length_chips;
+    if (m_pool_slot < 0) return false;
+    return B200_Correlator_Pool::instance().set_code(m_pool_slot, code_length_chips, reinterpret_cast<const float *>(local_code_in), true);
 }
 
 
 // reference :63-69
 bool B200_Multicorrelator::set_input_output_vectors(std::complex<float> *corr_out, const std::complex<float> *sig_in)
 {
-    d_sig_in = sig_in;
-    d_corr_out = corr_out;
+    m_io.samples = sig_in;
+    m_io.taps_out = corr_out;
     return true;
 }
 
@@ -60,26 +60,26 @@ void B200_Multicorrelator::update_local_code(int correlator_length_samples, floa
 bool B200_Multicorrelator::Carrier_wipeoff_multicorrelator_resampler(float rem_carrier_phase_in_rad, float phase_step_rad, float rem_code_phase_chips,
     float code_phase_step_chips, int signal_length_samples)
 {
-    if (d_channel < 0 || d_sig_in == nullptr || d_corr_out == nullptr || d_shifts_chips == nullptr || d_local_code_in == nullptr) return false;
-    if (signal_length_samples <= 0 || signal_length_samples > d_max_signal_length_samples) return false;
+    if (m_pool_slot < 0 || m_io.samples == nullptr || m_io.taps_out == nullptr || m_io.tap_shifts == nullptr || m_io.code == nullptr) return false;
+    if (signal_length_samples <= 0 || signal_length_samples > m_capacity) return false;
     gnss_b200_mc_args a{};
-    a.sig_in_c64 = reinterpret_cast<const float *>(d_sig_in);
+    a.sig_in_c64 = reinterpret_cast<const float *>(m_io.samples);
     a.n_samples = static_cast<uint32_t>(signal_length_samples);
     a.rem_carr_phase_rad = rem_carrier_phase_in_rad;
     a.carr_step_rad = phase_step_rad;
     a.rem_code_phase_chips = rem_code_phase_chips;
     a.code_step_chips = code_phase_step_chips;
-    return B200_Correlator_Pool::instance().correlate(d_channel, a, d_shifts_chips, static_cast<uint32_t>(d_n_correlators), 0U, d_corr_out);
+    return B200_Correlator_Pool::instance().correlate(m_pool_slot, a, m_io.tap_shifts, static_cast<uint32_t>(m_n_taps), 0U, m_io.taps_out);
 }
 
 
 // reference :102-116
 bool B200_Multicorrelator::free()
 {
-    if (d_channel >= 0)
+    if (m_pool_slot >= 0)
         {
-            B200_Correlator_Pool::instance().release_channel(d_channel);
-            d_channel = -1;
+            B200_Correlator_Pool::instance().release_channel(m_pool_slot);
+            m_pool_slot = -1;
         }
     return true;
 }

@@ -23,14 +23,18 @@ public:
     B200_Multicorrelator &operator=(const B200_Multicorrelator &) = delete;
 
 private:
-    const std::complex<float> *d_sig_in{nullptr};
-    const std::complex<float> *d_local_code_in{nullptr};
-    std::complex<float> *d_corr_out{nullptr};
-    float *d_shifts_chips{nullptr};
-    int d_code_length_chips{0};
-    int d_n_correlators{0};
-    int d_max_signal_length_samples{0};
-    int d_channel{-1};
+    // Pointers the caller lends (the reference's classes keep raw pointers too and re-read them on every call): nothing here is owned.
+    struct Borrowed
+    {
+        const std::complex<float> *samples = nullptr;  // input block of the current epoch
+        const std::complex<float> *code = nullptr;   // local code table, one period
+        std::complex<float> *taps_out = nullptr;       // one complex output per correlator tap
+        float *tap_shifts = nullptr;                   // tap offsets [chips]
+    } m_io;
+    int m_code_len = 0;   // entries of the code table
+    int m_n_taps = 0;     // correlator taps
+    int m_capacity = 0;   // longest block init() was asked for [samples]
+    int m_pool_slot = -1; // channel slot in B200_Correlator_Pool, -1 = not initialised
 };
 
 #endif  // GNSS_SDR_B200_MULTICORRELATOR_H

@@ -8,7 +8,7 @@
 B200_Multicorrelator_Real_Codes::~B200_Multicorrelator_Real_Codes()
 {
     // reference :27-33 — the destructor releases whatever init() took
-    if (d_channel >= 0)
+    if (m_pool_slot >= 0)
         {
             B200_Multicorrelator_Real_Codes::free();
         }
@@ -18,7 +18,7 @@ B200_Multicorrelator_Real_Codes::~B200_Multicorrelator_Real_Codes()
 // reference :63-66
 void B200_Multicorrelator_Real_Codes::set_high_dynamics_resampler(bool use_high_dynamics_resampler)
 {
-    d_use_high_dynamics_resampler = use_high_dynamics_resampler;
+    m_high_dynamics = use_high_dynamics_resampler;
 }
 
 
@@ -26,32 +26,32 @@ void B200_Multicorrelator_Real_Codes::set_high_dynamics_resampler(bool use_high_
 bool B200_Multicorrelator_Real_Codes::init(int max_signal_length_samples, int n_correlators)
 {
     if (max_signal_length_samples <= 0 || n_correlators <= 0) return false;
-    if (d_channel < 0)
+    if (m_pool_slot < 0)
         {
-            d_channel = B200_Correlator_Pool::instance().acquire_channel();
+            m_pool_slot = B200_Correlator_Pool::instance().acquire_channel();
         }
-    d_n_correlators = n_correlators;
-    d_max_signal_length_samples = max_signal_length_samples;
-    return d_channel >= 0;
+    m_n_taps = n_correlators;
+    m_capacity = max_signal_length_samples;
+    return m_pool_slot >= 0;
 }
 
 
 // reference :52-60 — both pointers are borrowed; the code is additionally uploaded to the device once.
 bool B200_Multicorrelator_Real_Codes::set_local_code_and_taps(int code_length_chips, const float *local_code_in, float *shifts_chips)
 {
-    d_local_code_in = local_code_in;
-    d_shifts_chips = shifts_chips;
-    d_code_length_chips = code_length_chips;
-    if (d_channel < 0) return false;
-    return B200_Correlator_Pool::instance().set_code(d_channel, code_length_chips, local_code_in, false);
+    m_io.code = local_code_in;
+    m_io.tap_shifts = shifts_chips;
+    m_code_len = code_length_chips;
+    if (m_pool_slot < 0) return false;
+    return B200_Correlator_Pool::instance().set_code(m_pool_slot, code_length_chips, local_code_in, false);
 }
 
 
 // reference :69-75
 bool B200_Multicorrelator_Real_Codes::set_input_output_vectors(std::complex<float> *corr_out, const std::complex<float> *sig_in)
 {
-    d_sig_in = sig_in;
-    d_corr_out = corr_out;
+    m_io.samples = sig_in;
+    m_io.taps_out = corr_out;
     return true;
 }
 
@@ -69,10 +69,10 @@ void B200_Multicorrelator_Real_Codes::update_local_code(int correlator_length_sa
 bool B200_Multicorrelator_Real_Codes::run(float rem_carrier_phase_in_rad, float phase_step_rad, float phase_rate_step_rad, float rem_code_phase_chips,
     float code_phase_step_chips, float code_phase_rate_step_chips, int signal_length_samples, unsigned flags)
 {
-    if (d_channel < 0 || d_sig_in == nullptr || d_corr_out == nullptr || d_shifts_chips == nullptr || d_local_code_in == nullptr) return false;
-    if (signal_length_samples <= 0 || signal_length_samples > d_max_signal_length_samples) return false;
+    if (m_pool_slot < 0 || m_io.samples == nullptr || m_io.taps_out == nullptr || m_io.tap_shifts == nullptr || m_io.code == nullptr) return false;
+    if (signal_length_samples <= 0 || signal_length_samples > m_capacity) return false;
     gnss_b200_mc_args a{};
-    a.sig_in_c64 = reinterpret_cast<const float *>(d_sig_in);
+    a.sig_in_c64 = reinterpret_cast<const float *>(m_io.samples);
     a.stream_offset = 0;
     a.n_samples = static_cast<uint32_t>(signal_length_samples);
     a.rem_carr_phase_rad = rem_carrier_phase_in_rad;
@@ -81,7 +81,7 @@ bool B200_Multicorrelator_Real_Codes::run(float rem_carrier_phase_in_rad, float 
     a.rem_code_phase_chips = rem_code_phase_chips;
     a.code_step_chips = code_phase_step_chips;
     a.code_rate_chips = code_phase_rate_step_chips;
-    return B200_Correlator_Pool::instance().correlate(d_channel, a, d_shifts_chips, static_cast<uint32_t>(d_n_correlators), flags, d_corr_out);
+    return B200_Correlator_Pool::instance().correlate(m_pool_slot, a, m_io.tap_shifts, static_cast<uint32_t>(m_n_taps), flags, m_io.taps_out);
 }
 
 
@@ -89,7 +89,7 @@ bool B200_Multicorrelator_Real_Codes::run(float rem_carrier_phase_in_rad, float 
 bool B200_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler(float rem_carrier_phase_in_rad, float phase_step_rad,
     float phase_rate_step_rad, float rem_code_phase_chips, float code_phase_step_chips, float code_phase_rate_step_chips, int signal_length_samples)
 {
-    const unsigned flags = d_use_high_dynamics_resampler ? static_cast<unsigned>(GNSS_B200_MC_HIGH_DYN) : 0U;
+    const unsigned flags = m_high_dynamics ? static_cast<unsigned>(GNSS_B200_MC_HIGH_DYN) : 0U;
     return run(rem_carrier_phase_in_rad, phase_step_rad, phase_rate_step_rad, rem_code_phase_chips, code_phase_step_chips, code_phase_rate_step_chips,
         signal_length_samples, flags);
 }
@@ -99,7 +99,7 @@ bool B200_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler(
 bool B200_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler(float rem_carrier_phase_in_rad, float phase_step_rad,
     float rem_code_phase_chips, float code_phase_step_chips, float code_phase_rate_step_chips, int signal_length_samples)
 {
-    const unsigned flags = (d_use_high_dynamics_resampler ? static_cast<unsigned>(GNSS_B200_MC_HIGH_DYN) : 0U) | GNSS_B200_MC_SIX_ARG;
+    const unsigned flags = (m_high_dynamics ? static_cast<unsigned>(GNSS_B200_MC_HIGH_DYN) : 0U) | GNSS_B200_MC_SIX_ARG;
     return run(rem_carrier_phase_in_rad, phase_step_rad, 0.0F, rem_code_phase_chips, code_phase_step_chips, code_phase_rate_step_chips,
         signal_length_samples, flags);
 }
@@ -108,10 +108,10 @@ bool B200_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler(
 // reference :147-167
 bool B200_Multicorrelator_Real_Codes::free()
 {
-    if (d_channel >= 0)
+    if (m_pool_slot >= 0)
         {
-            B200_Correlator_Pool::instance().release_channel(d_channel);
-            d_channel = -1;
+            B200_Correlator_Pool::instance().release_channel(m_pool_slot);
+            m_pool_slot = -1;
         }
     return true;
 }

@@ -33,15 +33,19 @@ public:
 private:
     bool run(float rem_carrier_phase_in_rad, float phase_step_rad, float phase_rate_step_rad, float rem_code_phase_chips, float code_phase_step_chips, float code_phase_rate_step_chips, int signal_length_samples, unsigned flags);
 
-    const std::complex<float> *d_sig_in{nullptr};
-    const float *d_local_code_in{nullptr};
-    std::complex<float> *d_corr_out{nullptr};
-    float *d_shifts_chips{nullptr};
-    int d_code_length_chips{0};
-    int d_n_correlators{0};
-    int d_max_signal_length_samples{0};
-    int d_channel{-1};  // slot in B200_Correlator_Pool
-    bool d_use_high_dynamics_resampler{true};
+    // Pointers the caller lends (the reference's classes keep raw pointers too and re-read them on every call): nothing here is owned.
+    struct Borrowed
+    {
+        const std::complex<float> *samples = nullptr;  // input block of the current epoch
+        const float *code = nullptr;                 // local code table, one period
+        std::complex<float> *taps_out = nullptr;       // one complex output per correlator tap
+        float *tap_shifts = nullptr;                   // tap offsets [chips]
+    } m_io;
+    int m_code_len = 0;   // entries of the code table
+    int m_n_taps = 0;     // correlator taps
+    int m_capacity = 0;   // longest block init() was asked for [samples]
+    int m_pool_slot = -1; // channel slot in B200_Correlator_Pool, -1 = not initialised
+    bool m_high_dynamics = true;  // set_high_dynamics_resampler(); the reference defaults to true as well
 };
 
 #endif  // GNSS_SDR_B200_MULTICORRELATOR_REAL_CODES_H

@@ -1,4 +1,9 @@
-/* Stand-in for src/algorithms/acquisition/libs/acq_conf.h (see README.md in this directory). */
+/*
+ * Compile-time stand-in for the reference's Acq_Conf (src/algorithms/acquisition/libs/acq_conf.h), used only when the host
+ * mirror is built outside the GNSS-SDR tree (B200_HOST_STANDALONE). Inside the tree the real header is included instead, so
+ * the member NAMES here have to be the reference's; everything else is this repository's own: only the members the mirror
+ * and its test driver read are present, grouped by what they configure. Defaults follow acq_conf.h:40-80.
+ */
 #ifndef B200_STUB_ACQ_CONF_H
 #define B200_STUB_ACQ_CONF_H
 #include <complex>
@@ -9,36 +14,46 @@
 class Acq_Conf
 {
 public:
-    std::string item_type{"gr_complex"};
-    std::string dump_filename;
-    int64_t fs_in{4000000LL};
-    int64_t resampled_fs{0LL};
-    size_t it_size{sizeof(std::complex<float>)};
-    float doppler_step{250.0};
-    float samples_per_ms{0.0};
-    float doppler_step2{125.0};
-    float pfa{0.0};
-    float pfa2{0.0};
-    float samples_per_code{0.0};
-    float resampler_ratio{1.0};
-    uint32_t sampled_ms{1U};
-    uint32_t ms_per_code{1U};
-    uint32_t samples_per_chip{2U};
-    uint32_t chips_per_second{1023000U};
-    uint32_t max_dwells{1U};
-    uint32_t num_doppler_bins_step2{4U};
-    uint32_t resampler_latency_samples{0U};
-    uint32_t dump_channel{0U};
-    int32_t doppler_max{5000};
-    int32_t doppler_min{-5000};
-    bool bit_transition_flag{false};
-    bool use_CFAR_algorithm_flag{true};
-    bool dump{false};
-    bool blocking{true};
-    bool blocking_on_standby{false};
-    bool make_2_steps{false};
-    bool make_repeat_steps{false};
-    bool use_automatic_resampler{false};
-    bool enable_monitor_output{false};
+    // --- input stream -------------------------------------------------------------------------------------
+    int64_t fs_in = 4000000;                           // sampling frequency of the items the block receives [Hz]
+    std::string item_type = "gr_complex";              // "gr_complex" | "cshort" | "cbyte"
+    size_t it_size = sizeof(std::complex<float>);      // bytes per item of item_type
+    float samples_per_ms = 0.0F;                       // fs_in / 1000 (SetDerivedParams)
+    float samples_per_code = 0.0F;                     // samples_per_ms * ms_per_code
+    uint32_t samples_per_chip = 2;                     // ceil(fs / chip rate), exclusion window of the 1st/2nd peak test
+
+    // --- dwell geometry -----------------------------------------------------------------------------------
+    uint32_t sampled_ms = 1;                           // coherent integration time [ms]
+    uint32_t ms_per_code = 1;                          // code period [ms]
+    uint32_t max_dwells = 1;                           // non-coherent dwells before a negative decision
+    bool bit_transition_flag = false;                  // two code periods per dwell, half of the lags kept
+
+    // --- Doppler search -----------------------------------------------------------------------------------
+    int32_t doppler_max = 5000;                        // +- [Hz]
+    float doppler_step = 250.0F;                       // coarse bin width [Hz]
+    bool make_2_steps = false;                         // second, narrow search around the coarse answer
+    uint32_t num_doppler_bins_step2 = 4;               //   its bin count (second_nbins)
+    float doppler_step2 = 125.0F;                      //   its bin width (second_doppler_step) [Hz]
+    bool make_repeat_steps = false;                    // the fork's mode: keep searching after the first detection
+
+    // --- decision -----------------------------------------------------------------------------------------
+    bool use_CFAR_algorithm_flag = true;               // max / input power, else first / second peak
+    float pfa = 0.0F;                                  // > 0: threshold derived from the false-alarm probability
+    float pfa2 = 0.0F;                                 //      the same for the second step (pfa_second_step)
+
+    // --- scheduling ---------------------------------------------------------------------------------------
+    bool blocking = true;                              // search inside general_work instead of a worker thread
+    bool blocking_on_standby = false;                  // do not consume items while inactive
+    bool enable_monitor_output = false;                // copy Gnss_Synchro of positive acquisitions to output 0
+
+    // --- acquisition resampler (gnss_flowgraph.cc:1063-1118) ------------------------------------------------
+    bool use_automatic_resampler = false;
+    float resampler_ratio = 1.0F;                      // decimation
+    uint32_t resampler_latency_samples = 0;            // (ntaps - 1) / 2 of the decimating FIR
+
+    // --- dump ---------------------------------------------------------------------------------------------
+    bool dump = false;
+    uint32_t dump_channel = 0;                         // only this channel writes
+    std::string dump_filename;                         // path prefix; "acquisition" if empty
 };
-#endif
+#endif  // B200_STUB_ACQ_CONF_H
