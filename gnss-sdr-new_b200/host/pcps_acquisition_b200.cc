@@ -223,10 +223,7 @@ void pcps_acquisition_b200::init()
             d_gnss_synchro->Flag_valid_symbol_output = false;
             d_gnss_synchro->Flag_valid_pseudorange = false;
             d_gnss_synchro->Flag_valid_word = false;
-            d_gnss_synchro->Acq_doppler_step = 0U;
-            d_gnss_synchro->Acq_delay_samples = 0.0;
-            d_gnss_synchro->Acq_doppler_hz = 0.0;
-            d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
+            forget_last_answer();
         }
     d_mag = 0.0;
     d_input_power = 0.0;
@@ -283,6 +280,36 @@ void pcps_acquisition_b200::attach_engine()
         }
 }
 
+// The four Gnss_Synchro fields an acquisition owns, back to "nothing found yet" (:255-258, :326-329, :958-961).
+void pcps_acquisition_b200::forget_last_answer()
+{
+    if (d_gnss_synchro == nullptr) return;
+    d_gnss_synchro->Acq_delay_samples = 0.0;
+    d_gnss_synchro->Acq_doppler_hz = 0.0;
+    d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
+    d_gnss_synchro->Acq_doppler_step = 0U;
+}
+
+
+// Code phase, Doppler and sample stamp of a finished search into Gnss_Synchro; with the acquisition resampler the delay and
+// the stamp go back to the input rate and the FIR's latency is taken off (:699-712).
+void pcps_acquisition_b200::report_answer(uint32_t indext, int32_t doppler, uint64_t samp_count)
+{
+    const auto delay = static_cast<double>(std::fmod(static_cast<float>(indext), d_acq_parameters.samples_per_code));
+    d_gnss_synchro->Acq_doppler_hz = static_cast<double>(doppler);
+    if (d_acq_parameters.use_automatic_resampler)
+        {
+            d_gnss_synchro->Acq_delay_samples = delay * d_acq_parameters.resampler_ratio;
+            d_gnss_synchro->Acq_delay_samples -= static_cast<double>(d_acq_parameters.resampler_latency_samples);
+            d_gnss_synchro->Acq_samplestamp_samples = rint(static_cast<double>(samp_count) * d_acq_parameters.resampler_ratio);
+        }
+    else
+        {
+            d_gnss_synchro->Acq_delay_samples = delay;
+            d_gnss_synchro->Acq_samplestamp_samples = samp_count;
+        }
+}
+
 
 // :317-343
 void pcps_acquisition_b200::set_state(int32_t state)
@@ -293,10 +320,7 @@ void pcps_acquisition_b200::set_state(int32_t state)
         {
             if (!d_step_repeat)  // :324 — the fork's repeat mode keeps the last answer in Gnss_Synchro
                 {
-                    d_gnss_synchro->Acq_delay_samples = 0.0;
-                    d_gnss_synchro->Acq_doppler_hz = 0.0;
-                    d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
-                    d_gnss_synchro->Acq_doppler_step = 0U;
+                    forget_last_answer();
                 }
             d_mag = 0.0;
             d_test_statistics = 0.0;
@@ -442,22 +466,10 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
     if (!step_two) d_input_power = res.input_power;  // :531-535 refresh it in the first step only
     d_test_statistics = res.test_statistic;
 
-    if (!step_two && d_acq_parameters.make_2_steps && d_step_repeat)
+    // :697 — a repeated coarse search of the two-step mode leaves Gnss_Synchro alone
+    if (step_two || !(d_acq_parameters.make_2_steps && d_step_repeat))
         {
-            // :697 — a repeated coarse search of the two-step mode leaves Gnss_Synchro alone
-        }
-    else if (d_acq_parameters.use_automatic_resampler)  // :699-705
-        {
-            d_gnss_synchro->Acq_delay_samples = static_cast<double>(std::fmod(static_cast<float>(indext), d_acq_parameters.samples_per_code)) * d_acq_parameters.resampler_ratio;
-            d_gnss_synchro->Acq_delay_samples -= static_cast<double>(d_acq_parameters.resampler_latency_samples);
-            d_gnss_synchro->Acq_doppler_hz = static_cast<double>(doppler);
-            d_gnss_synchro->Acq_samplestamp_samples = rint(static_cast<double>(samp_count) * d_acq_parameters.resampler_ratio);
-        }
-    else  // :707-712
-        {
-            d_gnss_synchro->Acq_delay_samples = static_cast<double>(std::fmod(static_cast<float>(indext), d_acq_parameters.samples_per_code));
-            d_gnss_synchro->Acq_doppler_hz = static_cast<double>(doppler);
-            d_gnss_synchro->Acq_samplestamp_samples = samp_count;
+            report_answer(indext, doppler, samp_count);
         }
     if (step_two)
         {
@@ -607,10 +619,7 @@ int pcps_acquisition_b200::general_work(int noutput_items, std::vector<int>& nin
             {
                 if (!d_step_repeat)
                     {
-                        d_gnss_synchro->Acq_delay_samples = 0.0;
-                        d_gnss_synchro->Acq_doppler_hz = 0.0;
-                        d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
-                        d_gnss_synchro->Acq_doppler_step = 0U;
+                        forget_last_answer();
                     }
                 d_mag = 0.0;
                 d_state = 1;

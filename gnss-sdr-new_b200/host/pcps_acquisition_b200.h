@@ -82,6 +82,8 @@ private:
     bool is_fdma();
     void calculate_threshold();
     void refresh_doppler_grid();
+    void forget_last_answer();
+    void report_answer(uint32_t indext, int32_t doppler, uint64_t samp_count);
     void attach_engine();
     void dump_results(int32_t effective_fft_size);
     bool dumping() const { return d_dump && d_channel == d_dump_channel; }
