@@ -271,6 +271,68 @@ __global__ void __launch_bounds__(kFastThreads, (MODE == 2 && CC != 0 && RA <= 1
     if (tid == 0) s_tile_idx = 0xffffffffu;
     if (full_rows)
         {
+            if constexpr (MODE == 2)
+                {
+                    // Records only: the running maximum AND its position stay in registers (a compare and two selects per point),
+                    // so the shared-memory pipe, which this kernel saturates first, carries nothing for the reduction. Within a
+                    // pencil positions ascend with b, so "strictly greater" keeps the lowest index; across the pencils of a thread
+                    // and across threads the tie goes to the lower position explicitly (:523).
+                    uint32_t best_pos = 0xffffffffu;
+                    for (uint32_t aa = threadIdx.y; aa < (uint32_t)RA; aa += bdy)
+                        {
+                            float2 v[RB];
+#pragma unroll
+                            for (int u = 0; u < RB; u++) v[u] = s[(size_t)u * G + aa * C + c];
+                            fft::Dft<RB, true>::run(v);
+                            float pbest = -1.f;
+                            uint32_t pb = 0;
+#pragma unroll
+                            for (int b = 0; b < RB; b++)
+                                {
+                                    const float g = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                                    sum += g;
+                                    const bool gt = g > pbest;
+                                    pbest = gt ? g : pbest;
+                                    pb = gt ? (uint32_t)b : pb;
+                                }
+                            const uint32_t ppos = (aa + RA * pb) * M_lo + c0 + c;
+                            if (pbest > best || (pbest == best && ppos < best_pos))
+                                {
+                                    best = pbest;
+                                    best_pos = ppos;
+                                }
+                        }
+                    const float mine_best = best;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1)
+                        {
+                            best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
+                            sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                        }
+                    const int lane = tid & 31, warp = tid >> 5;
+                    if (lane == 0)
+                        {
+                            s_rmax[warp] = best;
+                            s_rsum[warp] = sum;
+                        }
+                    __syncthreads();
+                    const int nw = (nthreads + 31) / 32;
+                    float tile_max = s_rmax[0];
+                    for (int w = 1; w < nw; w++) tile_max = fmaxf(tile_max, s_rmax[w]);
+                    if (mine_best == tile_max && best_pos != 0xffffffffu) atomicMin(&s_tile_idx, best_pos);
+                    __syncthreads();
+                    if (tid == 0)
+                        {
+                            for (int w = 1; w < nw; w++) sum += s_rsum[w];
+                            RowPartial rp;
+                            rp.max_val = tile_max;
+                            rp.max_idx = s_tile_idx;
+                            rp.sum = sum;
+                            rp.pad = 0;
+                            a.partials[(size_t)y * gridDim.y + blockIdx.y] = rp;
+                        }
+                    return;
+                }
             // Common case (no bit transition): every output belongs to the row. The running maximum is a plain FMNMX;
             // each |.|^2 is parked in the shared-memory slot its pencil just consumed (no other thread reads it), and
             // once the tile maximum is known only the thread(s) holding it look their slots up for the lowest index.
