@@ -261,7 +261,7 @@ def run_ours(args):
     # DRAM bytes per (PRN, Doppler) row of the two inverse kernels from the ncu --set full capture under profiles/
     # (r01_acq_ncu_full_summary.txt: dram__bytes_read + dram__bytes_write of an 800-row launch / 800): the inter-stage
     # intermediate (8 B/cell written by the first stage, read by the last) is what exceeds the algorithmic bytes
-    ncu_bytes_per_row = {"inv_first_stage": (23.171072e6 + 149.704960e6) / 800.0, "inv_last_stage_mag_reduce": (213.111296e6 + 4.048384e6) / 800.0}
+    ncu_bytes_per_row = {"inv_first_stage": (23.196160e6 + 150.798080e6) / 800.0, "inv_last_stage_mag_reduce": (216.051712e6 + 4.115968e6) / 800.0}
     traffic = ncu_bytes_per_row.get(names[dom])
     traffic = traffic * (geo["fft_size"] / 32000.0) * n_prn * nD * args.steps / max(1, prof_cnt[dom]) if traffic else None
     roofline = {"kernel": names[dom], "bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
@@ -388,7 +388,7 @@ def bench_tracking(b, torch, device, args, world, rank, local, flush_l2, barrier
                                     "d2h_bytes_per_step": int(e2e_ch * T * 8), "ms_per_step": e2e_s * 1e3,
                                     "input_mode": "a separate host sample buffer per channel (PCIe-bound: 240 kB per channel-ms)"},
         "roofline": {"kernel": "multicorr_kernel", "bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "traffic": (575.692544e6 + 3.952384e6) * n_ch / 2048.0,
+                     "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "traffic": (575.693056e6 + 4.326144e6) * n_ch / 2048.0,
                      "traffic_source": "ncu --set full, profiles/r01_multicorr_ncu_full_summary.txt (bytes per launch)",
                      "peak_source": peak_src, "avg_launch_ms": k_ms,
                      "algorithmic_bytes_per_channel_ms": 8.0 * n + 8.0 * T},
