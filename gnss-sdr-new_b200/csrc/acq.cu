@@ -71,15 +71,16 @@ int launch_stage(gnss_b200_acq* h, const StageArgs& a, uint32_t n_transforms, in
 {
     if (n_transforms == 0) return GNSS_B200_OK;
     const size_t smem = (size_t)a.st.tile_points * sizeof(float2);
-    static thread_local size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured)
+    static std::atomic<size_t> configured[kMaxDeviceSlots];  // per kernel instantiation and device
+    const int slot = device_slot();
+    if (smem > 48 * 1024 && (slot < 0 || smem > configured[slot].load(std::memory_order_relaxed)))
         {
             cudaFuncAttributes fa;
             B200_CUDA(cudaFuncGetAttributes(&fa, stage_kernel<LOAD, STORE, INV>));
             const size_t max_dyn = 227 * 1024 - fa.sharedSizeBytes;  // static + dynamic <= 227 KiB per CTA on sm_100
             B200_REQUIRE(smem <= max_dyn, GNSS_B200_ERR_UNSUPPORTED, "FFT tile of %zu bytes exceeds shared memory", smem);
             B200_CUDA(cudaFuncSetAttribute(stage_kernel<LOAD, STORE, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_dyn));
-            configured = max_dyn;
+            if (slot >= 0) configured[slot].store(max_dyn, std::memory_order_relaxed);
         }
     const dim3 grid(n_transforms, a.st.tiles);
     h->prof.begin(cat, h->stream);

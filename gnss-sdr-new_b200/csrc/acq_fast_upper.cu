@@ -9,11 +9,12 @@ namespace
 template <void (*kernel)(const FastArgs)>
 void configure(size_t smem)
 {
-    static thread_local bool done = false;  // one static per kernel instantiation
-    if (done && smem <= 48 * 1024) return;
+    static std::atomic<bool> done[kMaxDeviceSlots];  // one set per kernel instantiation, one flag per device
+    const int slot = device_slot();
+    if (slot >= 0 && done[slot].load(std::memory_order_relaxed) && smem <= 48 * 1024) return;
     cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    done = true;
+    if (slot >= 0) done[slot].store(true, std::memory_order_relaxed);
 }
 
 // geometries with their own instantiation (lower-stage length and column tile compile-time): the plans of the common

@@ -1,5 +1,6 @@
 // Shared plumbing of libgnss_b200.so: error reporting, CUDA call checking.
 #pragma once
+#include <atomic>
 #include "../../include/gnss_b200.h"
 #include <cuda_runtime.h>
 #include <cstdarg>
@@ -95,6 +96,15 @@ struct PinBuf
 };
 
 int select_device(int device);  // validates + cudaSetDevice; returns status
+
+// cudaFuncSetAttribute acts on the current device only, so "this kernel is configured" is remembered per device
+// ordinal (a receiver process may drive several GPUs). -1: ordinal not tracked, configure on every launch.
+constexpr int kMaxDeviceSlots = 64;
+inline int device_slot()
+{
+    int d = 0;
+    return (cudaGetDevice(&d) == cudaSuccess && d >= 0 && d < kMaxDeviceSlots) ? d : -1;
+}
 
 // Optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline numbers).
 struct EventProfiler

@@ -18,6 +18,7 @@
 //     angle, not to `step`. Evaluated per thread in double at its first sample, then
 //     advanced by a stride phasor.
 #include "multicorr_internal.cuh"
+#include <atomic>
 #include <type_traits>
 #include <cmath>
 #include <cstdlib>
@@ -518,12 +519,15 @@ void launch_window(int T, dim3 grid, size_t smem, cudaStream_t st, const ChanPar
 #define B200_MCW_CASE(TT)                                                                                                                  \
     case TT:                                                                                                                               \
         {                                                                                                                                  \
-            static bool configured = false;                                                                                                \
-            if (!configured)                                                                                                               \
+            /* function attributes are per device: one flag per device ordinal, not one per process */                                     \
+            static std::atomic<bool> configured[kMaxDeviceSlots];                                                                          \
+            const int dev = device_slot();                                                                                                 \
+            const bool tracked = dev >= 0;                                                                                                 \
+            if (!tracked || !configured[dev].load(std::memory_order_acquire))                                                              \
                 {                                                                                                                          \
                     cudaFuncSetAttribute(multicorr_window_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCapBytes);    \
                     cudaFuncSetAttribute(multicorr_window_kernel<TT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);                \
-                    configured = true;                                                                                                     \
+                    if (tracked) configured[dev].store(true, std::memory_order_release);                                                   \
                 }                                                                                                                          \
         }                                                                                                                                  \
         multicorr_window_kernel<TT><<<grid, kThreads, smem, st>>>(chans, shifts, partials, tickets, out, n_taps_total, tap0, smem_elems);   \

@@ -1,0 +1,62 @@
+"""One host process driving two GPUs through the C-ABI (the reference receiver is a single process: its blocks would
+carry different `device` ordinals). Kernel attributes (dynamic shared memory, carve-out) are per device, so the second
+device must be configured on its own; results are bit-identical to the first device's.
+
+Skipped on a one-GPU box.
+"""
+import numpy as np
+import pytest
+
+import synth
+from test_acq_gpu import _gpu_engine
+from test_multicorr_gpu import _scene
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def two_devices(b200):
+    if b200.lib().gnss_b200_device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    return b200
+
+
+def _correlate_on(b200, device, codes, sigs, args, shifts):
+    n_ch, n = len(sigs), sigs[0].size
+    mc = b200.MulticorrelatorB200(n_ch, n, shifts.shape[1], device=device)
+    for c in range(n_ch):
+        mc.set_local_code(c, codes[c])
+    host = np.ascontiguousarray(np.stack(sigs))
+    a = mc.make_args(n_ch, n, args[:, 0], args[:, 1], args[:, 2], args[:, 3], args[:, 4], args[:, 5], sig_ptrs=[host[c].ctypes.data for c in range(n_ch)])
+    out = mc.correlate_batch(np.arange(n_ch), a, shifts, 0).copy()
+    mc.close()
+    return out
+
+
+@pytest.mark.parametrize("n,code_len,ntaps,n_ch", [(30000, 10230, 11, 6), (30000, 10230, 20, 2), (8192, 1023, 3, 3)])
+def test_multicorrelator_on_the_second_device(two_devices, n, code_len, ntaps, n_ch):
+    b200 = two_devices
+    rng = np.random.default_rng(77 + ntaps)
+    codes, sigs, args, shifts = _scene(rng, n_ch, n, code_len, ntaps)
+    first = _correlate_on(b200, 0, codes, sigs, args, shifts)
+    second = _correlate_on(b200, 1, codes, sigs, args, shifts)
+    again = _correlate_on(b200, 0, codes, sigs, args, shifts)
+    assert np.array_equal(first.view(np.uint32), second.view(np.uint32))
+    assert np.array_equal(first.view(np.uint32), again.view(np.uint32))
+
+
+@pytest.mark.parametrize("scene", ["C1", "C2"])
+def test_acquisition_on_the_second_device(two_devices, scene):
+    """C1: single-stage plan (tile > 48 KB of dynamic shared memory); C2: the two-stage fast kernels."""
+    b200 = two_devices
+    n_prn = 8
+    geo, codes, iq, _ = synth.config_scene(scene, n_prn=n_prn)
+    records = []
+    for device in (0, 1, 0):
+        e = _gpu_engine(b200, geo, n_prn, use_cfar=True, device=device)
+        e.set_local_codes(np.arange(n_prn), codes[:n_prn])
+        got = e.dwell(iq, np.arange(n_prn))
+        records.append([(int(r["code_phase"]), int(r["doppler_index"]), np.float32(r["test_statistic"]).view(np.uint32),
+                         np.float32(r["peak"]).view(np.uint32)) for r in got])
+        e.close()
+    assert records[0] == records[1] == records[2]
