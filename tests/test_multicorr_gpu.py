@@ -138,6 +138,36 @@ def test_shared_stream_windows_and_linearity(b200, oracle):
     assert np.allclose(got2, 2 * got, rtol=1e-6, atol=0)
 
 
+def test_ragged_batch_and_tiny_blocks(b200, oracle):
+    """One batch whose channels differ in length (down to one sample: fewer samples than threads, partial copy groups,
+    a split boundary that is not a multiple of anything), code length and tap spread (shifts of several chips, negative
+    and beyond a code period); every channel against the oracle, chip indices of the extremes bit-exact."""
+    rng = np.random.default_rng(404)
+    lens = [1, 2, 31, 255, 256, 257, 1023, 4097, 12289, 29999]
+    n_ch, n_max, T = len(lens), max(lens), 5
+    code_lens = [1023, 1023, 511, 4092, 1023, 10230, 1023, 2046, 10230, 10230]
+    shifts = np.stack([np.linspace(-w, w, T).astype(np.float32) for w in (0.5, 1.0, 2.5, 0.1, 7.0, 0.5, 1100.0, 0.25, 3.0, 0.5)])
+    mc = b200.MulticorrelatorB200(n_ch, n_max, T)
+    sigs, codes = [], []
+    for c in range(n_ch):
+        codes.append(rng.choice([-1.0, 1.0], code_lens[c]).astype(np.float32))
+        sigs.append((rng.standard_normal(lens[c]) + 1j * rng.standard_normal(lens[c])).astype(np.complex64))
+        mc.set_local_code(c, codes[c])
+    rem_carr = rng.uniform(0, 2 * np.pi, n_ch).astype(np.float32)
+    carr_step = rng.uniform(-0.01, 0.01, n_ch).astype(np.float32)
+    rem_code = rng.uniform(0, 1, n_ch).astype(np.float32)
+    code_step = (np.float32(0.341) * (1 + rng.uniform(-1e-5, 1e-5, n_ch))).astype(np.float32)
+    a = mc.make_args(n_ch, lens, rem_carr, carr_step, 0.0, rem_code, code_step, 0.0, sig_ptrs=[x.ctypes.data for x in sigs])
+    got = mc.correlate_batch(np.arange(n_ch), a, shifts)
+    for c in range(n_ch):
+        want = oracle.mc_real(sigs[c], codes[c], shifts[c], float(rem_carr[c]), float(carr_step[c]), 0.0, float(rem_code[c]), float(code_step[c]), 0.0)
+        scale = max(np.abs(want).max(), np.sqrt(lens[c]))  # a few samples: the sum itself can be near zero
+        assert (np.abs(got[c] - want) / scale).max() < RTOL, (c, lens[c])
+    for c in (0, 6, 9):
+        one = mc.make_args(1, lens[c], float(rem_carr[c]), float(carr_step[c]), 0.0, float(rem_code[c]), float(code_step[c]), 0.0)
+        assert np.array_equal(mc.chip_indices(c, one, shifts[c]), oracle.mc_chip_indices(lens[c], code_lens[c], shifts[c], float(rem_code[c]), float(code_step[c]), 0.0))
+
+
 def test_full_size_config5_properties(b200, oracle):
     """BASELINE config 5 at full per-channel size (30 000 samples, 11 taps, L5I), 64 channels: the prompt tap of every
     channel carries the injected signal, and one channel is checked against the oracle."""
