@@ -22,6 +22,10 @@ bool stage_radices(uint32_t M, std::vector<uint32_t>* out)
     while (m % 5 == 0) m /= 5, n5++;
     for (uint32_t p : {7u, 11u, 13u})
         while (m % p == 0) m /= p, primes.push_back(p);
+    // larger primes (sample rates that are multiples of 1.023 MHz carry 31): no register codelet, the kernels run
+    // them as a direct DFT of that length out of shared memory (fft_smem.cuh: smem_pass_any)
+    for (uint32_t p = 17; p <= kMaxAnyRadix && m > 1; p += 2)
+        while (m % p == 0) m /= p, primes.push_back(p);
     if (m != 1) return false;
     std::vector<uint32_t> odd, even;
     while (n5 >= 2) odd.push_back(25), n5 -= 2;
@@ -82,6 +86,15 @@ void fill_stage(FftStage* st, uint32_t N, uint32_t M, const std::vector<uint32_t
             p.tw_scale = (uint32_t)(N / (rad[j] * gstride));
             p.has_tw = gstride > 1 ? 1 : 0;
         }
+}
+
+// true when every prime factor of N has a codelet or fits the direct-DFT pass
+bool primes_covered(uint32_t N)
+{
+    uint32_t m = N;
+    for (uint32_t p = 2; p <= kMaxAnyRadix && m > 1; p++)
+        while (m % p == 0) m /= p;
+    return m == 1;
 }
 
 uint32_t pick_threads(uint32_t tile_points)
@@ -158,7 +171,7 @@ bool find_fast_plan(uint32_t N, FftPlan* plan)
 
 bool make_fft_plan(uint32_t N, uint32_t max_single, FftPlan* plan, const char** why)
 {
-    static const char* kPrime = "FFT length has a prime factor > 13 (no codelet)";
+    static const char* kPrime = "FFT length has a prime factor > 127 (no codelet and no direct-DFT pass)";
     static const char* kSplit = "FFT length cannot be split into two shared-memory stages";
     plan->N = N;
     plan->radices.clear();
@@ -206,10 +219,7 @@ bool make_fft_plan(uint32_t N, uint32_t max_single, FftPlan* plan, const char** 
             if (!stage_radices(N, &rad))
                 {
                     // too many passes for one stage (or bad prime): fall through to the two-stage search
-                    uint32_t m = N;
-                    for (uint32_t p : {2u, 3u, 5u, 7u, 11u, 13u})
-                        while (m % p == 0) m /= p;
-                    if (m != 1)
+                    if (!primes_covered(N))
                         {
                             if (why) *why = kPrime;
                             return false;
@@ -256,10 +266,7 @@ bool make_fft_plan(uint32_t N, uint32_t max_single, FftPlan* plan, const char** 
         }
     if (!best_lo)
         {
-            uint32_t m = N;
-            for (uint32_t p : {2u, 3u, 5u, 7u, 11u, 13u})
-                while (m % p == 0) m /= p;
-            if (why) *why = (m != 1) ? kPrime : kSplit;
+            if (why) *why = !primes_covered(N) ? kPrime : kSplit;
             return false;
         }
     const uint32_t M_lo = best_lo, M_hi = N / best_lo;

@@ -1,4 +1,5 @@
-// Host-side plan of the any-length (prime factors <= 13) mixed-radix FFT used by the acquisition pipeline.
+// Host-side plan of the any-length mixed-radix FFT used by the acquisition pipeline: prime factors <= 13 have register
+// codelets, primes 17 ... 127 run as a direct DFT of that length (fft_smem.cuh: smem_pass_any); beyond that: unsupported.
 //
 // The transform of length N is an in-place multi-dimensional decimation: N = R_0 * R_1 * ... * R_{m-1},
 // index i = sum_j d_j * stride_j with stride_0 = 1. The forward transform is decimation-in-frequency
@@ -24,6 +25,7 @@ struct FftPass
 };
 
 constexpr int kMaxPasses = 6;
+constexpr uint32_t kMaxAnyRadix = 127;  // largest radix of the direct-DFT pass (<= the smallest CTA, 128 threads)
 
 struct FftStage
 {

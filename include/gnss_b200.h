@@ -65,7 +65,7 @@ extern "C"
        sample stream and one search geometry (one Acq_Conf, acq_conf.h:33-82). */
     typedef struct
     {
-        uint32_t fft_size;         /* d_fft_size (:85-92) — any length whose prime factors are <= 13 */
+        uint32_t fft_size;         /* d_fft_size (:85-92) — any length whose prime factors are <= 127 (register codelets up to 13) */
         uint32_t consumed_samples; /* d_consumed_samples (:71) */
         uint32_t bit_transition;   /* Acq_Conf::bit_transition_flag */
         int32_t doppler_max;       /* Acq_Conf::doppler_max [Hz] */

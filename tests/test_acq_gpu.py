@@ -105,6 +105,28 @@ def test_config1_all_prns(b200, oracle):
     assert same >= 30
 
 
+@pytest.mark.parametrize("name", ["F4092", "F16368", "F65472"])
+def test_dwell_lengths_with_the_prime_31(b200, oracle, name):
+    """Sample rates that are multiples of 1.023 MHz (4.092, 16.368 MS/s front ends): N = 4092 = 4*3*11*31, 16 368 and
+    65 472 (two stages). The reference's FFT takes any length; here the 31 runs as a direct-DFT pass. Every PRN against the
+    oracle, injected satellites found at their cells."""
+    geo, codes, iq, truth = synth.config_scene(name)
+    n = geo["n_prn"]
+    assert geo["fft_size"] % 31 == 0
+    e = _gpu_engine(b200, geo, n, use_cfar=True, keep_grid=True)
+    e.set_local_codes(np.arange(n), codes)
+    got = e.dwell(iq, np.arange(n))
+    want, grids = _oracle_search(oracle, geo, codes, [iq], keep=True)
+    thr = oracle.threshold(0.001, geo["fft_size"], e.n_doppler)
+    for p in range(n):
+        _compare(got[p], want[p][0], thr=thr, strict_idx=False)
+        g = e.read_grid(p)
+        assert np.abs(g - grids[p]).max() <= RTOL * grids[p].max()
+    det_g = {p + 1 for p in range(n) if got[p]["test_statistic"] > thr}
+    det_o = {p + 1 for p in range(n) if want[p][0]["test_statistic"] > thr}
+    assert det_g == det_o and det_o and det_o <= {t["prn"] for t in truth}
+
+
 def test_config2_two_stage_plan(b200, oracle):
     """BASELINE config 2 geometry (Galileo E1, 8 MS/s, 4 ms, N = 32000 -> two-stage FFT), 6 of the 50 PRNs against the oracle."""
     geo, codes, iq, truth = synth.config_scene("C2", n_prn=50)
@@ -242,7 +264,7 @@ def test_row_sharding_merge(b200, oracle):
 
 def test_unsupported_and_state_errors(b200):
     with pytest.raises(b200.B200Error):
-        b200.PcpsAcquisitionB200(4092, 4092, 5000, 250, 4.092e6, 4, 1)  # 31 | 4092: no codelet yet
+        b200.PcpsAcquisitionB200(2056, 2056, 5000, 250, 2.056e6, 3, 1)  # 257 | 2056: beyond the direct-DFT pass
     e = b200.PcpsAcquisitionB200(4000, 4000, 5000, 250, 4e6, 4, 2)
     with pytest.raises(b200.B200Error):
         e.dwell(np.zeros(4000, np.complex64), [0])  # no local code

@@ -87,7 +87,7 @@ def test_wipeoff_table_matches_oracle(b200, oracle):
 
 
 @pytest.mark.parametrize("n", [4000, 8000, 8192, 16000, 16384, 25000, 32000, 50000, 65536, 100000, 160000, 2000, 1024, 5040,
-                               6000, 12000, 7 * 11 * 13 * 4])
+                               6000, 12000, 7 * 11 * 13 * 4, 4092, 16368, 65472, 31 * 64, 17 * 1000, 127 * 8])
 def test_fft_plan_is_a_digit_scramble(b200, n):
     """The forward transform leaves bins in digit-scrambled order; the map must be a permutation of 0..N-1 that keeps DC
     in place, and the radices must multiply to N."""
@@ -105,7 +105,7 @@ def test_fft_plan_is_a_digit_scramble(b200, n):
     assert np.array_equal(want, perm.astype(np.int64))
 
 
-@pytest.mark.parametrize("n", [4092, 31 * 64, 17 * 1000])
+@pytest.mark.parametrize("n", [2056, 131 * 64, 257 * 1000])
 def test_fft_plan_rejects_uncovered_primes(b200, n):
     with pytest.raises(b200.B200Error) as e:
         b200.debug_fft_plan(n)

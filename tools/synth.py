@@ -169,6 +169,13 @@ CONFIGS = {
                    present=[2, 5, 9, 13, 17, 23, 26, 31], cn0=(38, 50), seed=4),
     "C4_gal": dict(system="gal_e1b", fs=25000000, sampled_ms=4, doppler_max=5000, doppler_step=250, n_prn=36,
                    present=[2, 7, 8, 12, 21, 25, 31, 33], cn0=(36, 48), seed=5),
+    # sample rates that are multiples of 1.023 MHz: the dwell length carries the prime 31 (direct-DFT pass of the FFT)
+    "F4092": dict(system="gps_l1_ca", fs=4092000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=8,
+                  present=[1, 3, 7], cn0=(46, 52), seed=7),
+    "F16368": dict(system="gps_l1_ca", fs=16368000, sampled_ms=1, doppler_max=2000, doppler_step=250, n_prn=6,
+                   present=[2, 5], cn0=(46, 52), seed=8),
+    "F65472": dict(system="gal_e1b", fs=16368000, sampled_ms=4, doppler_max=1000, doppler_step=250, n_prn=4,
+                   present=[1, 4], cn0=(42, 50), seed=9),
     "C4_bds": dict(system="bds_b1i", fs=25000000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=63,
                    present=[1, 6, 9, 14, 19, 27, 33, 40, 52, 60], cn0=(38, 50), seed=6),
 }
