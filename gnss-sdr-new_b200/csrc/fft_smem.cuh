@@ -68,13 +68,16 @@ __device__ __forceinline__ void smem_pass(float2* __restrict__ s, const uint32_t
 
 // The same pass for a radix without a register codelet (primes 17 ... kMaxAnyRadix, e.g. the 31 of every sample rate that is
 // a multiple of 1.023 MHz): a direct DFT of length R out of shared memory, one output per thread and round, a round
-// being as many whole butterflies as the CTA has threads for. All R-th roots and all twiddle powers are entries of W
-// (w^u = W[q*tw_scale*u], index < N), so nothing is stepped. The pass is in place: a round reads, the CTA meets, the
-// round writes. Few registers on purpose: the codelet passes set the register budget of the kernels, not this one.
+// being as many whole butterflies as the CTA has threads for. The R-th roots are staged in shared memory once per pass
+// (read from W they would be R different cache lines per warp and step); the twiddle powers are entries of W
+// (w^u = W[q*tw_scale*u], index < N), so nothing is stepped. The pass is in place: a round twiddles its inputs (inverse),
+// the CTA meets, the round reads, the CTA meets, the round writes. Few registers on purpose: the codelet passes set the
+// register budget of the kernels, not this one.
 template <bool INV>
 __device__ __noinline__ void smem_pass_any(float2* __restrict__ s, const uint32_t points, const uint32_t C, const FftPass p,
     const uint32_t tw_col0, const uint32_t tw_col_en, const uint32_t tw_lo_mul, const float2* __restrict__ W)
 {
+    __shared__ float2 s_root[kMaxAnyRadix + 1];
     const uint32_t R = p.radix;
     const uint32_t nb = points / R;
     const uint32_t ls = p.lstride;
@@ -82,39 +85,45 @@ __device__ __noinline__ void smem_pass_any(float2* __restrict__ s, const uint32_
     const uint32_t nr = p.tw_scale * ls * tw_lo_mul;  // N / R: W[j * nr] = exp(-2 pi i j / R)
     const uint32_t per_round = blockDim.x / R;
     const uint32_t bl = threadIdx.x / R, m = threadIdx.x - bl * R;
+    if (threadIdx.x < R)
+        {
+            const float2 w = __ldg(W + (size_t)threadIdx.x * nr);
+            s_root[threadIdx.x] = INV ? make_float2(w.x, -w.y) : w;
+        }
+    __syncthreads();
     for (uint32_t b0 = 0; b0 < nb; b0 += per_round)  // trip count uniform over the CTA
         {
             const uint32_t b = b0 + bl;
             const bool live = bl < per_round && b < nb;
-            float2 acc = make_float2(0.f, 0.f);
             float2* base = s;
+            uint32_t tq = 0;
             if (live)
                 {
                     const uint32_t c = b % C, r = b / C;
                     const uint32_t lo = r % ls, hi = r / ls;
                     base = s + (size_t)(hi * ls * R + lo) * C + c;
-                    const uint32_t tq = p.has_tw ? ((tw_col_en ? tw_col0 + c : 0u) + tw_lo_mul * lo) * p.tw_scale : 0u;
-                    uint32_t e = 0, tk = 0;  // (m * k) mod R and tq * k
+                    if (p.has_tw) tq = ((tw_col_en ? tw_col0 + c : 0u) + tw_lo_mul * lo) * p.tw_scale;
+                }
+            if (INV && p.has_tw)  // uniform condition
+                {
+                    if (live && tq && m) base[(size_t)m * st] = cmul_conj(base[(size_t)m * st], __ldg(W + (size_t)tq * m));
+                    __syncthreads();
+                }
+            float2 acc = make_float2(0.f, 0.f);
+            if (live)
+                {
+                    uint32_t e = 0;  // (m * k) mod R
+                    const float2* x = base;
                     for (uint32_t k = 0; k < R; k++)
                         {
-                            float2 x = base[(size_t)k * st];
-                            const float2 root = __ldg(W + (size_t)e * nr);
-                            if (INV)
-                                {
-                                    if (tq) x = cmul_conj(x, __ldg(W + tk));
-                                    x = cmul_conj(x, root);
-                                }
-                            else
-                                {
-                                    x = cmul(x, root);
-                                }
-                            acc.x += x.x;
-                            acc.y += x.y;
+                            const float2 v = cmul(*x, s_root[e]);
+                            acc.x += v.x;
+                            acc.y += v.y;
+                            x += st;
                             e += m;
                             if (e >= R) e -= R;
-                            tk += tq;
                         }
-                    if (!INV && tq) acc = cmul(acc, __ldg(W + (size_t)tq * m));
+                    if (!INV && tq && m) acc = cmul(acc, __ldg(W + (size_t)tq * m));
                 }
             __syncthreads();
             if (live) base[(size_t)m * st] = acc;
