@@ -67,7 +67,7 @@ __device__ __forceinline__ void smem_pass(float2* __restrict__ s, const uint32_t
 }
 
 // The same pass for a radix without a register codelet (primes 17 ... kMaxAnyRadix, e.g. the 31 of every sample rate that is
-// a multiple of 1.023 MHz): a direct DFT of length R out of shared memory, one output per thread and round, a round
+// a multiple of 1.023 MHz): a direct DFT of length R out of shared memory, one conjugate pair of outputs per thread and round, a round
 // being as many whole butterflies as the CTA has threads for. The R-th roots are staged in shared memory once per pass
 // (read from W they would be R different cache lines per warp and step); the twiddle powers are entries of W
 // (w^u = W[q*tw_scale*u], index < N), so nothing is stepped. The pass is in place: a round twiddles its inputs (inverse),
@@ -83,8 +83,10 @@ __device__ __noinline__ void smem_pass_any(float2* __restrict__ s, const uint32_
     const uint32_t ls = p.lstride;
     const uint32_t st = ls * C;
     const uint32_t nr = p.tw_scale * ls * tw_lo_mul;  // N / R: W[j * nr] = exp(-2 pi i j / R)
-    const uint32_t per_round = blockDim.x / R;
-    const uint32_t bl = threadIdx.x / R, m = threadIdx.x - bl * R;
+    // a thread owns the output pair (m, R - m): their roots are conjugates, so the four real products of one input serve both
+    const uint32_t G = (R + 1) / 2;  // R is an odd prime: m = 0 ... (R-1)/2
+    const uint32_t per_round = blockDim.x / G;
+    const uint32_t bl = threadIdx.x / G, m = threadIdx.x - bl * G, m2 = R - m;
     if (threadIdx.x < R)
         {
             const float2 w = __ldg(W + (size_t)threadIdx.x * nr);
@@ -106,27 +108,44 @@ __device__ __noinline__ void smem_pass_any(float2* __restrict__ s, const uint32_
                 }
             if (INV && p.has_tw)  // uniform condition
                 {
-                    if (live && tq && m) base[(size_t)m * st] = cmul_conj(base[(size_t)m * st], __ldg(W + (size_t)tq * m));
+                    if (live && tq && m)
+                        {
+                            base[(size_t)m * st] = cmul_conj(base[(size_t)m * st], __ldg(W + (size_t)tq * m));
+                            base[(size_t)m2 * st] = cmul_conj(base[(size_t)m2 * st], __ldg(W + (size_t)tq * m2));
+                        }
                     __syncthreads();
                 }
-            float2 acc = make_float2(0.f, 0.f);
+            float2 acc = make_float2(0.f, 0.f), acc2 = make_float2(0.f, 0.f);
             if (live)
                 {
-                    uint32_t e = 0;  // (m * k) mod R
+                    float rr = 0.f, ii = 0.f, ri = 0.f, ir = 0.f;  // sums of x.re*w.re, x.im*w.im, x.re*w.im, x.im*w.re
+                    uint32_t e = 0;                                  // (m * k) mod R
                     const float2* x = base;
                     for (uint32_t k = 0; k < R; k++)
                         {
-                            const float2 v = cmul(*x, s_root[e]);
-                            acc.x += v.x;
-                            acc.y += v.y;
+                            const float2 v = *x, w = s_root[e];
+                            rr = fmaf(v.x, w.x, rr);
+                            ii = fmaf(v.y, w.y, ii);
+                            ri = fmaf(v.x, w.y, ri);
+                            ir = fmaf(v.y, w.x, ir);
                             x += st;
                             e += m;
                             if (e >= R) e -= R;
                         }
-                    if (!INV && tq && m) acc = cmul(acc, __ldg(W + (size_t)tq * m));
+                    acc = make_float2(rr - ii, ri + ir);   // sum x * w
+                    acc2 = make_float2(rr + ii, ir - ri);  // sum x * conj(w)
+                    if (!INV && tq && m)
+                        {
+                            acc = cmul(acc, __ldg(W + (size_t)tq * m));
+                            acc2 = cmul(acc2, __ldg(W + (size_t)tq * m2));
+                        }
                 }
             __syncthreads();
-            if (live) base[(size_t)m * st] = acc;
+            if (live)
+                {
+                    base[(size_t)m * st] = acc;
+                    if (m) base[(size_t)m2 * st] = acc2;
+                }
             __syncthreads();
         }
 }
