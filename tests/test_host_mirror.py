@@ -124,6 +124,27 @@ def test_gps_capture_through_the_block_interface(driver, oracle, tmp_path):
 
 
 @pytest.mark.gpu
+def test_block_interface_at_a_sample_rate_with_the_prime_31(driver, oracle, tmp_path):
+    """4.092 MS/s front end: the block derives d_fft_size = 4092 = 4*3*11*31 from fs as the adapter does; decision,
+    delay, Doppler and statistic equal the oracle's."""
+    geo, codes, iq, truth = synth.config_scene("F4092", n_prn=1)
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_acq_input(inp, geo["fs"], 1, 1, geo["samples_per_chip"], geo["doppler_max"], geo["doppler_step"], 0.001, 0.0, 1, False, True, False,
+                     True, [codes[0]], np.concatenate([iq, iq]), 1023, True, 0)
+    _run(driver, "acq", inp, outp)
+    got = _read_acq_output(outp)[0]
+    acq = oracle.acq(fft_size=4092, consumed_samples=4092, doppler_max=geo["doppler_max"], doppler_step=geo["doppler_step"], fs=geo["fs"],
+                     samples_per_chip=geo["samples_per_chip"], samples_per_code=geo["samples_per_code"], use_cfar=True)
+    acq.set_local_code(codes[0])
+    want = acq.dwell(iq)
+    assert got["fft_size"] == 4092 and got["n_doppler"] == 40
+    assert got["event"] == 1 and truth[0]["prn"] == 1
+    assert got["delay"] == float(np.fmod(np.float32(want["code_phase"]), np.float32(geo["samples_per_code"])))
+    assert got["doppler"] == float(want["doppler_hz"])
+    assert got["stat"] == pytest.approx(want["test_statistic"], rel=1e-4)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("cshort,blocking,coalesce_us", [(False, True, 0), (False, True, 20000), (True, False, 0)])
 def test_many_blocks_share_one_engine(driver, oracle, tmp_path, cshort, blocking, coalesce_us):
     """Six channels (PRN 1..6 of config 1's scene, three of them present) run concurrently, one scheduler thread each;
