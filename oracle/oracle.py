@@ -107,6 +107,8 @@ def _bind_oracle(lib):
     lib.oracle_trk_start.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
     lib.oracle_trk_run.restype = c_i
     lib.oracle_trk_run.argtypes = [C.c_void_p, _fp, C.c_uint64, C.c_uint64, c_i, C.c_void_p]
+    lib.oracle_trk_run_traced.restype = c_i
+    lib.oracle_trk_run_traced.argtypes = [C.c_void_p, _fp, C.c_uint64, C.c_uint64, c_i, C.c_void_p, C.POINTER(C.c_double)]
     lib.oracle_fft_c64.argtypes = [_fp, _fp, c_i, c_i]
     lib.oracle_fft_c128.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), c_i, c_i]
     lib.oracle_samples_per_code.restype = c_i
@@ -303,9 +305,16 @@ class OracleTrk:
     def start(self, acq_delay_samples, acq_doppler_hz, acq_samplestamp, now_sample):
         self.lib.oracle_trk_start(self.h, float(acq_delay_samples), float(acq_doppler_hz), int(acq_samplestamp), int(now_sample))
 
-    def run(self, samples, stream_start, max_epochs):
+    def run(self, samples, stream_start, max_epochs, trace=False):
+        """trace=True: also returns [max_epochs][6] = (rem_carr_phase_rad, carr_step, rem_code, code_step, first sample, ran) per
+        epoch, the correlator arguments of do_correlation_step."""
         samples = np.ascontiguousarray(samples, dtype=np.complex64)
         out = np.zeros(max_epochs, dtype=TRK_EPOCH_DTYPE)
+        if trace:
+            tr = np.zeros((max_epochs, 6), dtype=np.float64)
+            n = self.lib.oracle_trk_run_traced(self.h, _ptr(samples.view(np.float32)), int(stream_start), samples.size, max_epochs,
+                                               out.ctypes.data_as(C.c_void_p), _ptr(tr, C.c_double))
+            return out, n, tr
         n = self.lib.oracle_trk_run(self.h, _ptr(samples.view(np.float32)), int(stream_start), samples.size, max_epochs, out.ctypes.data_as(C.c_void_p))
         return out, n
 

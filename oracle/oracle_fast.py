@@ -24,24 +24,27 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def wipeoff_table(n_doppler, doppler_max, doppler_step, fs, n, center=0, bias=0):
+def wipeoff_table(n_doppler, doppler_max, doppler_step, fs, n, center=0, bias=0, row_begin=0):
     """update_grid_doppler_wipeoffs (:298-305): float32 running-sum phase per row (np.cumsum in float32 is a
-    sequential add, i.e. the same rounding sequence as the reference's loop)."""
+    sequential add, i.e. the same rounding sequence as the reference's loop). Rows row_begin .. row_begin + n_doppler - 1."""
     out = np.empty((n_doppler, n), dtype=np.complex64)
-    for k in range(n_doppler):
+    for kk in range(n_doppler):
+        k = kk + row_begin
         doppler = -int(doppler_max) + int(center) + int(doppler_step) * k
         step = _f32(_f32(2.0 * np.pi) * _f32(bias + doppler) / _f32(fs))
         inc = np.full(n, -step, dtype=np.float32)
         inc[0] = 0.0
         ph = np.cumsum(inc, dtype=np.float32)
-        out[k].real = np.cos(ph)
-        out[k].imag = np.sin(ph)
+        out[kk].real = np.cos(ph)
+        out[kk].imag = np.sin(ph)
     return out
 
 
 class FastAcq:
     def __init__(self, fft_size, consumed_samples, doppler_max, doppler_step, fs, samples_per_chip, use_cfar=True,
-                 bit_transition=False, workers=None):
+                 bit_transition=False, workers=None, rows=None, center=0):
+        """rows = (begin, end): only those Doppler rows of the grid are built (a row-sharded search; `search` then returns
+        the per-row records of the shard through `row_records`, the decision needs all rows)."""
         self.N, self.consumed = fft_size, consumed_samples
         self.eff = fft_size // 2 if bit_transition else fft_size
         self.bt = bit_transition
@@ -49,7 +52,9 @@ class FastAcq:
         self.doppler_max, self.doppler_step, self.fs, self.spc = doppler_max, doppler_step, fs, samples_per_chip
         self.use_cfar = use_cfar
         self.workers = workers or host_cores()
-        self.wipe = wipeoff_table(self.nD, doppler_max, doppler_step, fs, fft_size)
+        self.row_begin, self.row_end = rows if rows is not None else (0, self.nD)
+        self.center = center
+        self.wipe = wipeoff_table(self.row_end - self.row_begin, doppler_max, doppler_step, fs, fft_size, center=center, row_begin=self.row_begin)
 
     def code_spectrum(self, code):
         buf = np.zeros(self.N, dtype=np.complex64)
@@ -74,10 +79,13 @@ class FastAcq:
             g = grid + g if dwell > 1 else g
             grid[...] = g
         idx = g.argmax(axis=1)
-        mx = g[np.arange(self.nD), idx]
+        mx = g[np.arange(g.shape[0]), idx]
+        self.row_records = dict(max_val=mx.copy(), max_idx=idx.copy(), row_sum=g.sum(axis=1, dtype=np.float32))
+        if g.shape[0] != self.nD:
+            return None
         k = int(mx.argmax())
         res = dict(peak=float(mx[k]), code_phase=int(idx[k]), doppler_index=k,
-                   doppler_hz=-self.doppler_max + self.doppler_step * k, dwell_count=dwell)
+                   doppler_hz=-self.doppler_max + self.center + self.doppler_step * k, dwell_count=dwell)
         if self.use_cfar:
             opp = (k + self.nD // 2) % self.nD
             power = _f32(np.float64(_f32(g[opp].sum(dtype=np.float32)) / _f32(self.eff)) / 2.0 / dwell)

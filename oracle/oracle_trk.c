@@ -469,6 +469,15 @@ static int cn0_and_tracking_lock_status(oracle_trk* t, const float* P, double co
 
 int oracle_trk_run(oracle_trk* t, const float* samples_c64, uint64_t stream_start, uint64_t n_samples, int max_epochs, oracle_trk_epoch* out)
 {
+    return oracle_trk_run_traced(t, samples_c64, stream_start, n_samples, max_epochs, out, NULL);
+}
+
+/* trace (optional): per epoch {rem_carr_phase_rad, carrier step, rem code phase, code step (both in code samples), first sample
+   of the epoch, 1 if the epoch ran} exactly as handed to the correlator (do_correlation_step, :1064-1089): what an open-loop
+   parity test feeds to the correlator under test. */
+int oracle_trk_run_traced(oracle_trk* t, const float* samples_c64, uint64_t stream_start, uint64_t n_samples, int max_epochs, oracle_trk_epoch* out,
+    double* trace)
+{
     const oracle_trk_cfg* c = &t->cfg;
     const uint64_t stream_end = stream_start + n_samples;
     const float spc = (float)c->code_samples_per_chip;
@@ -487,6 +496,16 @@ int oracle_trk_run(oracle_trk* t, const float* samples_c64, uint64_t stream_star
                 }
             /* do_correlation_step */
             float outs[10];
+            if (trace)
+                {
+                    double* tr = trace + 6 * (size_t)e;
+                    tr[0] = (double)t->rem_carr_phase_rad;
+                    tr[1] = (double)(float)t->carrier_phase_step_rad;
+                    tr[2] = (double)((float)t->rem_code_phase_chips * spc);
+                    tr[3] = (double)((float)t->code_phase_step_chips * spc);
+                    tr[4] = (double)nread;
+                    tr[5] = 1.0;
+                }
             oracle_mc_real(samples_c64 + 2 * (nread - stream_start), (int)c->vector_length, t->code, t->code_len, t->shifts, t->n_taps,
                 t->rem_carr_phase_rad, (float)t->carrier_phase_step_rad, 0.0f, (float)t->rem_code_phase_chips * spc, (float)t->code_phase_step_chips * spc,
                 0.0f * spc, 0, 0, outs);

@@ -83,6 +83,9 @@ extern "C"
     void oracle_trk_start(oracle_trk* t, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t now_sample);
     /* out[max_epochs]; returns the number of epochs that ran */
     int oracle_trk_run(oracle_trk* t, const float* samples_c64, uint64_t stream_start, uint64_t n_samples, int max_epochs, oracle_trk_epoch* out);
+    /* same, and trace[max_epochs][6] = the correlator arguments of every epoch (NULL: no trace) */
+    int oracle_trk_run_traced(oracle_trk* t, const float* samples_c64, uint64_t stream_start, uint64_t n_samples, int max_epochs, oracle_trk_epoch* out,
+        double* trace);
 
 #ifdef __cplusplus
 }

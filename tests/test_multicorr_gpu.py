@@ -170,15 +170,16 @@ def test_ragged_batch_and_tiny_blocks(b200, oracle):
 
 def test_full_size_config5_properties(b200, oracle):
     """BASELINE config 5 at full per-channel size (30 000 samples, 11 taps, L5I), 64 channels: the prompt tap of every
-    channel carries the injected signal, and one channel is checked against the oracle."""
+    channel carries the injected signal, and EVERY channel is checked against the oracle."""
     rng = np.random.default_rng(55)
     codes, sigs, args, shifts = _scene(rng, 64, 30000, 10230, 11)
     _, _, got = _run_gpu(b200, codes, sigs, args, shifts)
     prompt = np.abs(got[:, 5])
     far = 0.5 * (np.abs(got[:, 0]) + np.abs(got[:, 10]))  # +-1 chip taps: noise only (~sqrt(N) sigma)
     assert (prompt > 2 * far).all() and prompt.mean() > 4 * far.mean()
-    want = _run_oracle(oracle, codes[:2], sigs[:2], args[:2], shifts[:2])
-    assert _rel_err(got[:2], want) < RTOL
+    want = _run_oracle(oracle, codes, sigs, args, shifts)
+    assert want.shape == got.shape == (64, 11)
+    assert _rel_err(got, want) < RTOL
 
 
 def test_error_behaviour(b200):

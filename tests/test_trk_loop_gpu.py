@@ -168,3 +168,45 @@ def test_acquisition_hands_over_to_tracking(b200):
         assert abs(ok[-50:]["cn0_db_hz"].mean() - 47.0) < 3.0
     trk.close()
     acq.close()
+
+
+@pytest.mark.parametrize("system,veml", [("gps_l1_ca", False), ("gal_e1b", True)])
+def test_open_loop_every_epoch_meets_1e4(b200, oracle, oracle_mod, system, veml):
+    """The closed-loop comparison above is loose because a loop echoes one-ulp parameter differences. Open loop: the
+    ORACLE's loop runs and records the correlator arguments of every epoch (do_correlation_step,
+    dll_pll_veml_tracking.cc:1064-1089); the GPU correlator gets exactly those arguments on the same samples, all epochs
+    in one batch. With identical parameters every epoch of every tap must meet the 1e-4 bar of the north star."""
+    fs, n_ms = 4e6, 300
+    prns, dop = [3, 19], [1830.0, -2950.5]
+    iq, truth, _ = synth.tracking_stream(system, prns, fs, n_ms, seed=33, cn0=46.0, dopplers=dop, delays=[1234.4, 2500.0])
+    g, o = _cfgs(b200, oracle_mod, system, veml, fs, 1)
+    chip_rate, code_len, _ = synth.SYSTEMS[system]
+    n_ep = int(n_ms / (1e3 * code_len / chip_rate)) - 2
+    n_taps = 5 if veml else 3
+    if veml:
+        shifts = np.array([-g.very_early_late_space_chips, -g.early_late_space_chips, 0.0, g.early_late_space_chips,
+                           g.very_early_late_space_chips], np.float32) * np.float32(g.code_samples_per_chip)
+    else:
+        shifts = np.array([-g.early_late_space_chips, 0.0, g.early_late_space_chips], np.float32) * np.float32(g.code_samples_per_chip)
+    for p, t in zip(prns, truth):
+        code = synth.tracking_code(system, p)
+        ot = oracle.trk(o)
+        ot.set_code(code)
+        ot.start(round(t["delay"]) - 1.0, t["doppler"] + 40.0, 0, 2500)
+        want, done, tr = ot.run(iq, 0, n_ep, trace=True)
+        ot.close()
+        ran = np.flatnonzero(tr[:, 5] == 1.0)
+        assert ran.size >= n_ep - 3 and np.array_equal(ran, np.flatnonzero(want["flags"] & 1 == 1))
+        n = int(g.vector_length)
+        mc = b200.MulticorrelatorB200(ran.size, n, n_taps)
+        for c in range(ran.size):
+            mc.set_local_code(c, code)
+        ptrs = [iq.ctypes.data + 8 * int(tr[e, 4]) for e in ran]
+        a = mc.make_args(ran.size, n, tr[ran, 0], tr[ran, 1], 0.0, tr[ran, 2], tr[ran, 3], 0.0, sig_ptrs=ptrs)
+        got = mc.correlate_batch(np.arange(ran.size), a, np.tile(shifts, (ran.size, 1)))
+        base = 0 if veml else 1                                   # corr holds VE, E, P, L, VL; E-P-L channels leave VE / VL empty
+        w = np.ascontiguousarray(want["corr"][ran][:, 2 * base: 2 * (base + n_taps)], dtype=np.float32).view(np.complex64).reshape(ran.size, n_taps)
+        scale = np.abs(w).max(axis=1, keepdims=True)
+        err = np.abs(got - w) / scale
+        assert err.max() < 1e-4, (system, p, float(err.max()), int(err.argmax()))
+        mc.close()
