@@ -162,7 +162,9 @@ int ensure_group(gnss_b200_acq* h, int64_t key, uint32_t* ordinal)
             *ordinal = it->second;
             return GNSS_B200_OK;
         }
-    if (h->group_cache.size() >= kMaxCachedGroups) h->group_cache.clear();
+    // never evicts: the caller (enqueue_dwell) makes room for all uncached keys of a call BEFORE resolving any of them, so an
+    // ordinal handed out earlier in the same call cannot be overwritten
+    B200_REQUIRE(h->group_cache.size() < kMaxCachedGroups, GNSS_B200_ERR_STATE, "Doppler-group cache full (%zu entries)", h->group_cache.size());
     const uint32_t ord = (uint32_t)h->group_cache.size();
     // host: one piece table per local Doppler bin (the reference's update_grid_doppler_wipeoffs, :298-305)
     std::vector<WipePiece> tab((size_t)h->nD_local * kMaxPieces);
@@ -231,10 +233,13 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
             m.input_power1.push_back(h->step2 ? h->input_power1[s] : 0.f);
         }
     B200_REQUIRE(call_keys.size() <= kMaxCachedGroups, GNSS_B200_ERR_UNSUPPORTED, "dwell: more than %u distinct Doppler centres in one call", kMaxCachedGroups);
-    for (int64_t key : call_keys)
-        {
-            if (h->group_cache.size() >= kMaxCachedGroups && !h->group_cache.count(key)) h->group_cache.clear();
-        }
+    {
+        // room for every uncached key of this call, decided once up front: clearing in the middle of the call would hand the
+        // ordinal (= device piece table) of a group resolved earlier in the call to a later one
+        size_t n_new = 0;
+        for (int64_t key : call_keys) n_new += h->group_cache.count(key) ? 0 : 1;
+        if (h->group_cache.size() + n_new > kMaxCachedGroups) h->group_cache.clear();
+    }
     for (int64_t key : call_keys)
         {
             uint32_t ord;

@@ -21,7 +21,7 @@ bool B200_Acquisition_Bank::Geometry::operator==(const Geometry& o) const
 {
     return fft_size == o.fft_size && consumed_samples == o.consumed_samples && doppler_max == o.doppler_max && doppler_step == o.doppler_step &&
            fs == o.fs && samples_per_chip == o.samples_per_chip && bit_transition == o.bit_transition && use_cfar == o.use_cfar &&
-           keep_grid == o.keep_grid && device == o.device && step2_bins == o.step2_bins && step2_hz == o.step2_hz;
+           keep_grid == o.keep_grid && device == o.device && step2_bins == o.step2_bins && step2_hz == o.step2_hz && source_id == o.source_id;
 }
 
 
@@ -163,7 +163,21 @@ bool B200_Acquisition_Bank::read_grid_step2(int slot, float* out)
 }
 
 
-// Leader with d_mu held: issue one engine call per distinct (sample stamp, item type, step) among the pending dwells.
+// Guard behind the source id: two requests with the same stamp are served from ONE buffer, so their blocks must really hold
+// the same samples. Every block has its own copy (d_data_buffer), so pointers differ; the head and the tail of the dwell are
+// compared instead (a few cache lines; noise makes two different streams differ in the first sample already).
+bool B200_Acquisition_Bank::same_block(const void* a, const void* b, bool is_cshort) const
+{
+    if (a == b) return true;
+    const size_t item = is_cshort ? 4 : 8;
+    const size_t bytes = static_cast<size_t>(d_geo.consumed_samples) * item;
+    const size_t probe = std::min<size_t>(bytes, 256);
+    return std::memcmp(a, b, probe) == 0 &&
+           std::memcmp(static_cast<const char*>(a) + bytes - probe, static_cast<const char*>(b) + bytes - probe, probe) == 0;
+}
+
+
+// Leader with d_mu held: issue one engine call per distinct (sample stamp, item type, step, sample block) among the pending dwells.
 void B200_Acquisition_Bank::drain_locked(std::unique_lock<std::mutex>& lk)
 {
     while (!d_pending.empty())
@@ -175,7 +189,8 @@ void B200_Acquisition_Bank::drain_locked(std::unique_lock<std::mutex>& lk)
             for (auto it = d_pending.begin(); it != d_pending.end();)
                 {
                     // a second-step call holds at most 64 distinct Doppler centres (include/gnss_b200.h)
-                    if ((*it)->stamp == stamp && (*it)->is_cshort == is_cshort && (*it)->step2 == step2 && (!step2 || group.size() < 64))
+                    if ((*it)->stamp == stamp && (*it)->is_cshort == is_cshort && (*it)->step2 == step2 && (!step2 || group.size() < 64) &&
+                        same_block(d_pending.front()->samples, (*it)->samples, is_cshort))
                         {
                             group.push_back(*it);
                             it = d_pending.erase(it);

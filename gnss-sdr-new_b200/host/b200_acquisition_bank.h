@@ -33,6 +33,8 @@ public:
         int device;
         uint32_t step2_bins;  // make_two_steps: num_doppler_bins_step2 (0 = no second engine)
         float step2_hz;       //                 doppler_step2
+        uint32_t source_id;   // which sample stream feeds the blocks (RF_channel_ID / signal-source index): banks are never
+                              // shared across streams, because equal sample stamps only mean equal samples on ONE stream
         bool operator==(const Geometry& o) const;
     };
 
@@ -77,6 +79,7 @@ private:
     };
     bool submit(Request& req);
     void drain_locked(std::unique_lock<std::mutex>& lk);
+    bool same_block(const void* a, const void* b, bool is_cshort) const;
 
     Geometry d_geo;
     gnss_b200_acq* d_engine{nullptr};

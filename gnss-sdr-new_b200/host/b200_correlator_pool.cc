@@ -53,6 +53,7 @@ bool B200_Correlator_Pool::ensure_engine_locked()
             return false;
         }
     d_used.assign(d_max_channels, 0);
+    d_is_complex.assign(d_max_channels, 0);
     return true;
 }
 
@@ -87,6 +88,7 @@ bool B200_Correlator_Pool::set_code(int ch, int code_length, const float* code, 
     if (d_engine == nullptr || ch < 0 || code_length <= 0 || code == nullptr) return false;
     const int rc = gnss_b200_mc_set_code(d_engine, static_cast<uint32_t>(ch), static_cast<uint32_t>(code_length), code, is_complex ? 1 : 0);
     if (rc != GNSS_B200_OK) d_error = gnss_b200_last_error();
+    if (rc == GNSS_B200_OK && static_cast<uint32_t>(ch) < d_is_complex.size()) d_is_complex[ch] = is_complex ? 1 : 0;
     return rc == GNSS_B200_OK;
 }
 
@@ -112,7 +114,10 @@ bool B200_Correlator_Pool::correlate_many(uint32_t n, const uint32_t* ch, const 
 }
 
 
-// Called by the leader with d_mu held: drains d_pending in groups of equal (n_taps, flags).
+// Called by the leader with d_mu held: drains d_pending in groups of equal (n_taps, flags, code type, block length). Real- and
+// complex-code correlators (B200_Multicorrelator_Real_Codes / B200_Multicorrelator) share this pool and the engine refuses a
+// batch that mixes them; channels of different signals (different vector_length) go in separate launches so that a long
+// block does not take the short ones off the engine's fast path.
 void B200_Correlator_Pool::run_batch_locked(std::unique_lock<std::mutex>& lk)
 {
     while (!d_pending.empty())
@@ -120,9 +125,11 @@ void B200_Correlator_Pool::run_batch_locked(std::unique_lock<std::mutex>& lk)
             std::vector<Request*> group;
             const uint32_t n_taps = d_pending.front()->n_taps;
             const uint32_t flags = d_pending.front()->flags;
+            const bool is_complex = d_pending.front()->is_complex;
+            const uint32_t n_samples = d_pending.front()->args.n_samples;
             for (auto it = d_pending.begin(); it != d_pending.end();)
                 {
-                    if ((*it)->n_taps == n_taps && (*it)->flags == flags)
+                    if ((*it)->n_taps == n_taps && (*it)->flags == flags && (*it)->is_complex == is_complex && (*it)->args.n_samples == n_samples)
                         {
                             group.push_back(*it);
                             it = d_pending.erase(it);
@@ -185,6 +192,7 @@ bool B200_Correlator_Pool::correlate(int ch, const gnss_b200_mc_args& args, cons
 
     std::unique_lock<std::mutex> lk(d_mu);
     if (d_engine == nullptr) return false;
+    req.is_complex = req.ch < d_is_complex.size() && d_is_complex[req.ch] != 0;
     d_pending.push_back(&req);
     if (d_leader_active)
         {

@@ -60,6 +60,7 @@ private:
         gnss_b200_mc_args args;
         const float* shifts;
         uint32_t n_taps, flags;
+        bool is_complex;  // local code type of the channel: the engine does not mix real and complex codes in one batch
         std::complex<float>* out;
         bool done = false, ok = false;
     };
@@ -72,6 +73,7 @@ private:
     uint32_t d_max_channels{4096}, d_max_samples{1u << 20}, d_max_taps{16};
     uint32_t d_window_us{0}, d_expected{0};
     std::vector<uint8_t> d_used;
+    std::vector<uint8_t> d_is_complex;  // per channel, recorded by set_code
     std::vector<Request*> d_pending;
     bool d_leader_active{false};
     uint64_t d_batches{0}, d_calls{0};

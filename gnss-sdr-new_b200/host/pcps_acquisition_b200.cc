@@ -246,13 +246,15 @@ void pcps_acquisition_b200::attach_engine()
     g.consumed_samples = d_consumed_samples;
     g.doppler_max = d_acq_parameters.doppler_max;
     g.doppler_step = d_doppler_step;
-    g.fs = static_cast<double>(d_acq_parameters.fs_in);
+    // update_local_carrier (:236-243): the carrier is generated at the rate of the items the block receives
+    g.fs = static_cast<double>(d_acq_parameters.use_automatic_resampler ? d_acq_parameters.resampled_fs : d_acq_parameters.fs_in);
     g.samples_per_chip = d_samplesPerChip;
     g.bit_transition = d_acq_parameters.bit_transition_flag;
     g.use_cfar = d_use_CFAR_algorithm_flag;
     // the grid stays on the device only where it is needed: accumulated over dwells (:672-684) or dumped (:682, :743)
     g.keep_grid = (d_acq_parameters.max_dwells > 1 && !d_acq_parameters.bit_transition_flag) || dumping();
-    g.device = 0;
+    g.device = d_device;
+    g.source_id = d_source_id;
     g.step2_bins = d_acq_parameters.make_2_steps ? d_num_doppler_bins_step2 : 0U;
     g.step2_hz = d_acq_parameters.make_2_steps ? d_acq_parameters.doppler_step2 : 0.0F;
     std::string why;

@@ -59,6 +59,13 @@ public:
     void set_doppler_center(int32_t doppler_center);
     bool start();  // gr::block::start(): resets the sample counter and derives the threshold from pfa
 
+    // B200-only knobs (no counterpart in pcps_acquisition); both take effect at the next init().
+    // Which sample stream feeds this block (the adapter passes the channel's RF_channel_ID / signal-source index): blocks on
+    // different streams never share an engine bank, whatever their sample stamps.
+    void set_source_id(uint32_t source_id) { d_source_id = source_id; }
+    // CUDA device the block's bank lives on (Acquisition_XX.device, default 0).
+    void set_device(int device) { d_device = device; }
+
     // Same contract as gr::block::general_work (gr_vector_int = std::vector<int>, ...). Items consumed and events
     // published go through the two hooks below, which the gr::block shell binds to consume_each / message_port_pub.
     int general_work(int noutput_items, std::vector<int>& ninput_items, std::vector<const void*>& input_items, std::vector<void*>& output_items);
@@ -115,6 +122,8 @@ private:
     int32_t d_doppler_center{0};
     int32_t d_doppler_bias{0};
     uint32_t d_channel{0};
+    uint32_t d_source_id{0};
+    int d_device{0};
     uint32_t d_dump_channel{0};
     uint32_t d_samplesPerChip{0};
     uint32_t d_doppler_step{0};

@@ -15,10 +15,11 @@ class Acq_Conf
 {
 public:
     // --- input stream -------------------------------------------------------------------------------------
-    int64_t fs_in = 4000000;                           // sampling frequency of the items the block receives [Hz]
+    int64_t fs_in = 4000000;                           // GNSS-SDR.internal_fs_sps: the UNDECIMATED rate, also with the resampler on [Hz]
+    int64_t resampled_fs = 0;                          // rate of the items the block receives: fs_in, or fs_in / resampler_ratio
     std::string item_type = "gr_complex";              // "gr_complex" | "cshort" | "cbyte"
     size_t it_size = sizeof(std::complex<float>);      // bytes per item of item_type
-    float samples_per_ms = 0.0F;                       // fs_in / 1000 (SetDerivedParams)
+    float samples_per_ms = 0.0F;                       // resampled_fs / 1000 (SetDerivedParams, acq_conf.cc:113-119)
     float samples_per_code = 0.0F;                     // samples_per_ms * ms_per_code
     uint32_t samples_per_chip = 2;                     // ceil(fs / chip rate), exclusion window of the 1st/2nd peak test
 

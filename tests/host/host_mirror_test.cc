@@ -103,7 +103,8 @@ int run_acq(const char* in_path, const char* out_path)
     const auto chunk = r.get<uint32_t>();
     const auto use_fsm = r.get<uint32_t>();
     const auto coalesce_us = r.get<uint32_t>();
-    conf.samples_per_ms = static_cast<float>(conf.fs_in) * 0.001F;                                    // acq_conf.cc:113-119
+    conf.resampled_fs = conf.fs_in;                                                                    // acq_conf.cc:55
+    conf.samples_per_ms = static_cast<float>(conf.resampled_fs) * 0.001F;                              // acq_conf.cc:113-119
     conf.samples_per_code = conf.samples_per_ms * static_cast<float>(conf.ms_per_code);
     conf.it_size = cshort ? 2 * sizeof(int16_t) : sizeof(std::complex<float>);
     conf.item_type = cshort ? "cshort" : "gr_complex";
@@ -132,6 +133,13 @@ int run_acq(const char* in_path, const char* out_path)
                 {
                     conf.make_repeat_steps = r.get<uint32_t>() != 0;
                     want_events = r.get<uint32_t>();
+                }
+            if (r.f.peek() != std::ifstream::traits_type::eof())  // the acquisition resampler (acq_conf.cc:93-111): the header's fs is the
+                {                                                   // rate of the stream in this file, fs_in becomes the undecimated rate
+                    conf.use_automatic_resampler = r.get<uint32_t>() != 0;
+                    conf.resampler_ratio = r.get<float>();
+                    conf.resampler_latency_samples = r.get<uint32_t>();
+                    conf.fs_in = r.get<int64_t>();
                 }
         }
 
@@ -234,7 +242,7 @@ int run_mc(const char* in_path, const char* out_path)
     const auto n_samples = r.get<uint32_t>();
     const auto code_len = r.get<uint32_t>();
     const auto n_epochs = r.get<uint32_t>();
-    const auto mode = r.get<uint32_t>();  // 0 real 7-arg, 1 real 6-arg, 2 complex codes
+    const auto mode = r.get<uint32_t>();  // 0 real 7-arg, 1 real 6-arg, 2 complex codes, 3 mixed: even channels real (5-arg), odd complex
     const auto high_dyn = r.get<uint32_t>();
     const auto coalesce_us = r.get<uint32_t>();
     struct Chan
@@ -248,7 +256,7 @@ int run_mc(const char* in_path, const char* out_path)
     std::vector<Chan> ch(n_ch);
     for (auto& c : ch)
         {
-            c.code = r.vec<float>(mode == 2 ? 2 * code_len : code_len);
+            c.code = r.vec<float>(mode >= 2 ? 2 * code_len : code_len);  // mixed: real channels use the first code_len values
             c.shifts = r.vec<float>(n_taps);
             c.sig = r.vec<std::complex<float>>(static_cast<size_t>(n_epochs) * n_samples);
             c.args = r.vec<float>(static_cast<size_t>(n_epochs) * 6);
@@ -260,7 +268,7 @@ int run_mc(const char* in_path, const char* out_path)
     auto work = [&](uint32_t i) {
         Chan& c = ch[i];
         std::vector<std::complex<float>> corr(n_taps);
-        if (mode == 2)
+        if (mode == 2 || (mode == 3 && (i & 1U) != 0))
             {
                 B200_Multicorrelator mc;
                 if (!mc.init(static_cast<int>(n_samples), static_cast<int>(n_taps))) failures++;
@@ -283,8 +291,9 @@ int run_mc(const char* in_path, const char* out_path)
             {
                 const float* a = &c.args[static_cast<size_t>(e) * 6];
                 mc.set_input_output_vectors(corr.data(), c.sig.data() + static_cast<size_t>(e) * n_samples);
-                const bool ok = (mode == 0) ? mc.Carrier_wipeoff_multicorrelator_resampler(a[0], a[1], a[2], a[3], a[4], a[5], static_cast<int>(n_samples))
-                                            : mc.Carrier_wipeoff_multicorrelator_resampler(a[0], a[1], a[3], a[4], a[5], static_cast<int>(n_samples));
+                const bool ok = (mode == 0)   ? mc.Carrier_wipeoff_multicorrelator_resampler(a[0], a[1], a[2], a[3], a[4], a[5], static_cast<int>(n_samples))
+                                : (mode == 1) ? mc.Carrier_wipeoff_multicorrelator_resampler(a[0], a[1], a[3], a[4], a[5], static_cast<int>(n_samples))
+                                              : mc.Carrier_wipeoff_multicorrelator_resampler(a[0], a[1], 0.0F, a[3], a[4], 0.0F, static_cast<int>(n_samples));  // flags 0, like the complex class
                 if (!ok) failures++;
                 std::copy(corr.begin(), corr.end(), c.out.begin() + static_cast<size_t>(e) * n_taps);
             }

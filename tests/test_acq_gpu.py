@@ -219,6 +219,34 @@ def test_cshort_input_and_doppler_center(b200, oracle):
         _compare(got[p], want[p][0], strict_idx=(p == 0))
 
 
+def test_doppler_group_cache_never_aliases_within_a_call(b200):
+    """The engine caches the wipe-off piece tables of up to 64 Doppler centres. A call whose centres overflow the cache must
+    not hand the table slot of one of ITS OWN groups to another: fill the cache to 63 entries, then search three
+    centres of which the first is the oldest cached one; every slot must equal a fresh engine's answer bit for bit."""
+    geo, codes, iq, _ = synth.config_scene("C1", n_prn=3)
+    e = _gpu_engine(b200, geo, 3, use_cfar=True)
+    e.set_local_codes(np.arange(3), codes)
+    first = None
+    for i in range(21):                                  # 21 calls x 3 new centres = 63 cached groups
+        cs = [7 * (3 * i + s) - 400 for s in range(3)]
+        first = first or cs
+        for s, c in enumerate(cs):
+            e.set_doppler_center(s, c)
+        e.dwell(iq, np.arange(3))
+    probe = [first[0], 1234, -2222]                      # cached at ordinal 0, new, new (the second one overflows)
+    for s, c in enumerate(probe):
+        e.set_doppler_center(s, c)
+    got = e.dwell(iq, np.arange(3))
+    fresh = _gpu_engine(b200, geo, 3, use_cfar=True)
+    fresh.set_local_codes(np.arange(3), codes)
+    for s, c in enumerate(probe):
+        fresh.set_doppler_center(s, c)
+    want = fresh.dwell(iq, np.arange(3))
+    assert got.tobytes() == want.tobytes()
+    e.close()
+    fresh.close()
+
+
 def test_cbyte_input(b200, oracle):
     """interleaved int8 items (the adapters' `cbyte` item type, gps_l1_ca_pcps_acquisition.cc:76-80,191-198)
     converted on the device: identical to handing the block the converted gr_complex stream."""

@@ -59,7 +59,8 @@ def test_mirror_keeps_the_reference_method_set():
 
 
 def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, doppler_step, pfa, threshold, max_dwells, bit_transition,
-                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us, two_steps=None, dump=None, repeat_events=None):
+                     use_cfar, cshort, blocking, codes, stream, chunk, use_fsm, coalesce_us, two_steps=None, dump=None, repeat_events=None,
+                     resampler=None):
     with open(path, "wb") as f:
         f.write(struct.pack("<q", int(fs)))
         f.write(struct.pack("<IIIiI", sampled_ms, ms_per_code, spc, doppler_max, doppler_step))
@@ -70,6 +71,9 @@ def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, dopple
         for c in codes:
             f.write(np.ascontiguousarray(c, dtype=np.complex64).tobytes())
         f.write(np.ascontiguousarray(stream, dtype=np.int16 if cshort else np.complex64).tobytes())
+        repeat_flag = repeat_events is not None
+        if resampler is not None and repeat_events is None:
+            repeat_events = 1
         if two_steps is not None or dump is not None or repeat_events is not None:
             ts = two_steps or (0, 125.0, 0.0)             # (second_nbins, second_doppler_step, pfa2)
             f.write(struct.pack("<IIff", int(two_steps is not None), int(ts[0]), float(ts[1]), float(ts[2])))
@@ -77,7 +81,9 @@ def _write_acq_input(path, fs, sampled_ms, ms_per_code, spc, doppler_max, dopple
             f.write(struct.pack("<III", int(dump is not None), int(dump[0]) if dump else 0, len(name)))
             f.write(name)
             if repeat_events is not None:             # make_repeat_steps: wait for this many decisions per block
-                f.write(struct.pack("<II", 1, int(repeat_events)))
+                f.write(struct.pack("<II", int(repeat_flag), int(repeat_events)))
+            if resampler is not None:                 # (resampler_ratio, resampler_latency_samples, undecimated fs_in); `fs` above = resampled_fs
+                f.write(struct.pack("<IfIq", 1, float(resampler[0]), int(resampler[1]), int(resampler[2])))
 
 
 def _read_acq_output(path):
@@ -121,6 +127,33 @@ def test_gps_capture_through_the_block_interface(driver, oracle, tmp_path):
     # the reference test's own acceptance window
     delay_chips = abs(got["delay"] - 524) * 1023.0 / 4000.0
     assert delay_chips <= 0.5 and abs(got["doppler"] - 1680) <= 666
+
+
+@pytest.mark.gpu
+def test_block_behind_the_acquisition_resampler(driver, oracle, tmp_path):
+    """GNSS-SDR.use_acquisition_resampler: the block receives the DECIMATED stream (resampled_fs = 5 MS/s) while
+    Acq_Conf::fs_in stays the undecimated 25 MS/s (acq_conf.cc:93-111). The carrier wipe-off must be generated at
+    resampled_fs (update_local_carrier, pcps_acquisition.cc:236-243), and the answer goes back to the input rate:
+    Acq_delay_samples = delay * ratio - latency, Acq_samplestamp_samples = rint(stamp * ratio) (:699-705)."""
+    fs_in, acq_fs, ratio, latency = 25000000, 5000000, 5.0, 37
+    N = 5000
+    truth = [dict(system="gps_l1_ca", prn=9, delay=1403, doppler=-1830.0, cn0=50.0)]
+    iq = synth.make_iq(2 * N, acq_fs, truth, seed=18)          # what the decimating FIR hands to the block
+    code = synth.adapter_code("gps_l1_ca", 9, acq_fs, 1)[:N]
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_acq_input(inp, acq_fs, 1, 1, 5, 5000, 250, 0.001, 0.0, 1, False, True, False, True, [code], iq, 1000, True, 0,
+                     resampler=(ratio, latency, fs_in))
+    _run(driver, "acq", inp, outp)
+    got = _read_acq_output(outp)[0]
+    a = oracle.acq(fft_size=N, consumed_samples=N, doppler_max=5000, doppler_step=250, fs=acq_fs, samples_per_chip=5, samples_per_code=float(N))
+    a.set_local_code(code)
+    want = a.dwell(iq[:N])
+    assert got["event"] == 1 and got["fft_size"] == N
+    assert got["doppler"] == float(want["doppler_hz"]) and abs(got["doppler"] - truth[0]["doppler"]) <= 250
+    assert got["stat"] == pytest.approx(want["test_statistic"], rel=1e-4)
+    assert got["delay"] == float(np.fmod(np.float32(want["code_phase"]), np.float32(N))) * ratio - latency
+    assert got["stamp"] == int(np.rint(N * ratio))
+    a.close()
 
 
 @pytest.mark.gpu
@@ -181,7 +214,7 @@ def test_many_blocks_share_one_engine(driver, oracle, tmp_path, cshort, blocking
 def _write_mc_input(path, mode, high_dyn, coalesce_us, codes, shifts, sigs, args):
     n_ch, n_epochs, n_samples = sigs.shape
     with open(path, "wb") as f:
-        code_len = codes.shape[1] // (2 if mode == 2 else 1)
+        code_len = codes.shape[1] // (2 if mode >= 2 else 1)
         f.write(struct.pack("<IIIIIIII", n_ch, shifts.shape[1], n_samples, code_len, n_epochs, mode, int(high_dyn), coalesce_us))
         for c in range(n_ch):
             f.write(codes[c].astype(np.float32).tobytes())
@@ -230,6 +263,40 @@ def test_correlator_objects_match_oracle(driver, oracle, tmp_path, mode, high_dy
                                       six_arg=(mode == 1))
             scale = np.abs(want).max() + np.sqrt(n)
             assert np.abs(got[c, e] - want).max() <= 1e-4 * scale
+
+
+@pytest.mark.gpu
+def test_real_and_complex_correlators_share_the_pool(driver, oracle, tmp_path):
+    """B200_Multicorrelator_Real_Codes and B200_Multicorrelator objects with EQUAL tap counts and flags call at the same
+    time through the one pool (e.g. GPS L1 dll_pll_veml next to a complex-code tracker). The engine refuses a batch that
+    mixes code types, so the pool must not coalesce them into one: every call succeeds and matches the oracle."""
+    rng = np.random.default_rng(5)
+    n_ch, n_ep, n, L, T = 6, 3, 4000, 1023, 3
+    chips = np.stack([synth.chips("gps_l1_ca", p + 1) for p in range(n_ch)]).astype(np.float32)
+    cc = (chips + 1j * np.roll(chips, 7, axis=1)).astype(np.complex64)
+    codes = np.empty((n_ch, 2 * L), np.float32)
+    for c in range(n_ch):
+        codes[c] = cc[c].view(np.float32) if c & 1 else np.concatenate([chips[c], np.zeros(L, np.float32)])
+    shifts = np.tile(np.array([-0.5, 0.0, 0.5], np.float32), (n_ch, 1))
+    sigs = (rng.standard_normal((n_ch, n_ep, n)) + 1j * rng.standard_normal((n_ch, n_ep, n))).astype(np.complex64)
+    args = np.zeros((n_ch, n_ep, 6), dtype=np.float32)
+    args[..., 0] = rng.uniform(0, 6.28, (n_ch, n_ep))
+    args[..., 1] = rng.uniform(-0.01, 0.01, (n_ch, n_ep))
+    args[..., 3] = rng.uniform(0, 1, (n_ch, n_ep))
+    args[..., 4] = 1.023e6 / 4e6 * (1 + rng.uniform(-1e-5, 1e-5, (n_ch, n_ep)))
+    inp, outp = tmp_path / "in.bin", tmp_path / "out.bin"
+    _write_mc_input(inp, 3, False, 20000, codes, shifts, sigs, args)
+    _run(driver, "mc", inp, outp)
+    raw = open(outp, "rb").read()
+    failures, batches, calls = struct.unpack_from("<IQQ", raw, 0)
+    got = np.frombuffer(raw, dtype=np.complex64, offset=20).reshape(n_ch, n_ep, T)
+    assert failures == 0 and calls == n_ch * n_ep and batches < calls
+    for c in range(n_ch):
+        for e in range(n_ep):
+            a = args[c, e]
+            want = (oracle.mc_cplx(sigs[c, e], cc[c], shifts[c], a[0], a[1], a[3], a[4]) if c & 1 else
+                    oracle.mc_real(sigs[c, e], chips[c], shifts[c], a[0], a[1], 0.0, a[3], a[4], 0.0))
+            assert np.abs(got[c, e] - want).max() <= 1e-4 * (np.abs(want).max() + np.sqrt(n))
 
 
 @pytest.mark.gpu
