@@ -1,5 +1,6 @@
 // Host side of the PCPS acquisition engine: handle, buffers, launch sequencing, C-ABI.
 // Reference for every entry point: include/gnss_b200.h.
+#include "acq_cluster.cuh"
 #include "acq_fast_fwd.cuh"
 #include "acq_kernels.cuh"
 #include "wipeoff_pieces.h"
@@ -276,10 +277,17 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
 
     const uint32_t n_fwd = n_groups * h->nD_local;
     const uint32_t n_rows = n_slots * h->nD_local;
-    const uint32_t tiles_last = h->plan.stage[0].tiles;  // the inverse always ends with stage[0]
+    // Row-resident inverse (acq_cluster.cuh): full rows, records only or persistent grid, plans with a cluster instantiation.
+    // It writes one record per CTA of the cluster instead of one per column tile.
+    const bool full_rows = h->mag_offset == 0 && h->eff == h->N;
+    const uint32_t cluster_cs = (h->plan.fast && h->plan.n_stages == 2 && full_rows)
+                                    ? cl::cluster_tiles(h->plan.ra_lo, h->plan.rb_lo, h->plan.ra_hi, h->plan.rb_hi)
+                                    : 0u;
+    const uint32_t tiles_plan = h->plan.stage[0].tiles;  // the inverse always ends with stage[0]
+    const uint32_t tiles_last = cluster_cs ? cluster_cs : tiles_plan;
     B200_CUDA(h->d_xbuf.reserve((size_t)n_fwd * h->N * 8));
     if (h->plan.n_stages == 2) B200_CUDA(h->d_xtmp.reserve((size_t)n_fwd * h->N * 8));
-    B200_CUDA(h->d_partials.reserve(sizeof(RowPartial) * (size_t)n_rows * tiles_last));
+    B200_CUDA(h->d_partials.reserve(sizeof(RowPartial) * (size_t)n_rows * std::max(tiles_last, tiles_plan)));
     B200_CUDA(h->d_results.reserve(sizeof(gnss_b200_acq_result) * n_slots));
     B200_CUDA(h->h_results.reserve(sizeof(gnss_b200_acq_result) * n_slots));
     B200_CUDA(h->d_bestk.reserve(sizeof(uint32_t) * n_slots));
@@ -373,7 +381,8 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
         size_t budget = kScratchBudgetBytes;
         if (const char* e = std::getenv("B200_ACQ_SCRATCH_MB")) budget = (size_t)std::max(1, std::atoi(e)) << 20;  // tuning aid
         const uint32_t chunk = (uint32_t)std::min<size_t>(rows, std::max<size_t>(1, budget / ((size_t)h->N * 8)));
-        B200_CUDA(h->d_scratch.reserve((size_t)chunk * h->N * 8));
+        const bool row_resident = cluster_cs && !k_override && (mag_base ? !mag_is_rowbuf : true);  // needs no HBM scratch at all
+        if (!row_resident) B200_CUDA(h->d_scratch.reserve((size_t)chunk * h->N * 8));
         if (h->plan.fast)
             {
                 const FftPlan& pl = h->plan;
@@ -406,6 +415,17 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 const bool grid_path = mag_base && !mag_is_rowbuf && h->mag_offset == 0 && h->eff == h->N;
                 // 2: nothing but the per-tile records leaves the last stage (no grid kept, full rows)
                 const int upper_mode = grid_path ? 1 : ((!mag_base && h->mag_offset == 0 && h->eff == h->N) ? 2 : 0);
+                if (row_resident && (upper_mode == 1 || upper_mode == 2))
+                    {
+                        // one persistent launch for all rows: the inter-stage intermediate stays in (distributed) shared memory
+                        fa.y0 = 0;
+                        h->prof.begin(CAT_INV_LAST, h->stream);
+                        cudaError_t e = cl::launch_inv_cluster(pl.ra_lo, pl.rb_lo, pl.ra_hi, pl.rb_hi, upper_mode, rows, h->stream, fa);
+                        h->prof.end(h->stream);
+                        h->launches++;
+                        B200_CUDA(e);
+                        return GNSS_B200_OK;
+                    }
                 const uint32_t pitch = (pl.ra_lo % 2 == 0) ? pl.ra_lo + 1 : pl.ra_lo;
                 const size_t smem_lo = ((size_t)fa.nb * pitch * pl.rb_lo + fa.M_lo) * sizeof(float2);
                 const size_t smem_hi = ((size_t)pl.rb_hi * upper_group_stride(pl.ra_hi, fa.C) + fa.M_hi) * sizeof(float2);
@@ -528,7 +548,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
                 {
                     // the grid was never materialised: recompute the winning row of every slot into a row buffer
                     B200_CUDA(h->d_rowbuf.reserve(sizeof(float) * (size_t)n_slots * h->eff));
-                    B200_CUDA(h->d_partials2.reserve(sizeof(RowPartial) * (size_t)n_slots * tiles_last));
+                    B200_CUDA(h->d_partials2.reserve(sizeof(RowPartial) * (size_t)n_slots * std::max(tiles_last, tiles_plan)));
                     rc = inverse(n_slots, h->d_bestk.as<uint32_t>(), h->d_rowbuf.as<float>(), 1, h->d_partials2.as<RowPartial>());
                     if (rc) return rc;
                     sp.mag_base = h->d_rowbuf.as<float>();

@@ -1,0 +1,117 @@
+// Instantiations and launcher of the row-resident (thread-block cluster + DSMEM + TMA) inverse kernel, acq_cluster.cuh.
+#include "acq_cluster.cuh"
+#include <cstdlib>
+
+namespace b200
+{
+namespace cl
+{
+namespace
+{
+// B200_ACQ_CLUSTER: 0 = never use the row-resident kernel (two-kernel path), N = force cluster size N where an instantiation
+// exists; unset = the default variant per plan. Read once per process (tuning aid, like B200_NO_FIXED).
+int env_variant()
+{
+    static const int v = [] {
+        const char* e = std::getenv("B200_ACQ_CLUSTER");
+        return e ? std::atoi(e) : 0;  // off by default until it beats the two-kernel path
+    }();
+    return v;
+}
+
+template <class G, int MODE>
+cudaError_t launch_one(uint32_t n_rows, cudaStream_t st, const FastArgs& a)
+{
+    auto kernel = inv_cluster_kernel<G, MODE>;
+    static std::atomic<int> n_clusters_cached[kMaxDeviceSlots];  // per instantiation and device: co-resident clusters (0 = not yet)
+    const int slot = device_slot();
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(G::THREADS);
+    cfg.dynamicSmemBytes = G::smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = G::CS;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n_clusters = slot >= 0 ? n_clusters_cached[slot].load(std::memory_order_relaxed) : 0;
+    if (n_clusters <= 0)
+        {
+            cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
+            if (e != cudaSuccess) return e;
+            if (G::CS > 8)
+                {
+                    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+                    if (e != cudaSuccess) return e;
+                }
+            cfg.gridDim = dim3(G::CS * kNumSMs);  // only the shape matters for the query
+            e = cudaOccupancyMaxActiveClusters(&n_clusters, kernel, &cfg);
+            if (e != cudaSuccess) return e;
+            if (n_clusters <= 0) return cudaErrorLaunchOutOfResources;
+            if (slot >= 0) n_clusters_cached[slot].store(n_clusters, std::memory_order_relaxed);
+            if (std::getenv("B200_CL_VERBOSE")) fprintf(stderr, "inv_cluster CS=%d threads=%d smem=%zu: %d co-resident clusters\n", G::CS, G::THREADS, (size_t)G::smem_bytes, n_clusters);
+        }
+    const uint32_t use = std::min<uint32_t>((uint32_t)n_clusters, n_rows);
+    cfg.gridDim = dim3(use * G::CS);
+    static const uint32_t dbg = [] {
+        const char* e = std::getenv("B200_CL_DBG");  // timing experiments only (results are wrong with any bit set)
+        return e ? (uint32_t)std::atoi(e) : 0u;
+    }();
+    return cudaLaunchKernelEx(&cfg, kernel, a, n_rows, dbg);
+}
+
+template <class G>
+cudaError_t launch_mode(int mode, uint32_t n_rows, cudaStream_t st, const FastArgs& a)
+{
+    if (mode == 1) return launch_one<G, 1>(n_rows, st, a);
+    if (mode == 2) return launch_one<G, 2>(n_rows, st, a);
+    return cudaErrorInvalidValue;
+}
+
+// N = 32 000 = (16 x 10) x (25 x 8) (BASELINE configs[1], Galileo E1 at 8 MS/s): a row is 256 kB = the shared memory of an SM pair.
+// The radices are balanced so that every pass has at least as many pencils as a CTA has threads (fft_plan.cc prefers this plan
+// for the length when the row-resident path is on).
+using G32k_2a = Geo<16, 10, 25, 8, 2, 25, 256, 1>;
+using G32k_2b = Geo<16, 10, 25, 8, 2, 25, 512, 1>;
+// (8 x 8) x (25 x 20): small lower radices = 400 pencils per 3200-point tile in both lower passes, 640 / 800 in the upper ones
+using G32k_2c = Geo<8, 8, 25, 20, 2, 50, 416, 1, 3>;
+using G32k_2d = Geo<8, 8, 25, 20, 2, 50, 512, 1, 3>;
+}  // namespace
+
+bool cluster_preferred_plan(uint32_t N, uint32_t* ra_lo, uint32_t* rb_lo, uint32_t* ra_hi, uint32_t* rb_hi)
+{
+    if (env_variant() == 0) return false;
+    if (N == 32000)
+        {
+            if (env_variant() == 256 || env_variant() == 512)
+                *ra_lo = 16, *rb_lo = 10, *ra_hi = 25, *rb_hi = 8;
+            else
+                *ra_lo = 8, *rb_lo = 8, *ra_hi = 25, *rb_hi = 20;
+            return true;
+        }
+    return false;
+}
+
+uint32_t cluster_tiles(uint32_t ra_lo, uint32_t rb_lo, uint32_t ra_hi, uint32_t rb_hi)
+{
+    const int v = env_variant();
+    if (v == 0) return 0;
+    if (ra_lo == 16 && rb_lo == 10 && ra_hi == 25 && rb_hi == 8) return v == 512 ? 2 * G32k_2b::NW : 2 * G32k_2a::NW;
+    if (ra_lo == 8 && rb_lo == 8 && ra_hi == 25 && rb_hi == 20) return v == 1512 ? 2 * G32k_2d::NW : 2 * G32k_2c::NW;
+    return 0;
+}
+
+cudaError_t launch_inv_cluster(uint32_t ra_lo, uint32_t rb_lo, uint32_t ra_hi, uint32_t rb_hi, int mode, uint32_t n_rows, cudaStream_t st, const FastArgs& a)
+{
+    const int v = env_variant();
+    if (ra_lo == 16 && rb_lo == 10 && ra_hi == 25 && rb_hi == 8)
+        return v == 512 ? launch_mode<G32k_2b>(mode, n_rows, st, a) : launch_mode<G32k_2a>(mode, n_rows, st, a);
+    if (ra_lo == 8 && rb_lo == 8 && ra_hi == 25 && rb_hi == 20)
+        return v == 1512 ? launch_mode<G32k_2d>(mode, n_rows, st, a) : launch_mode<G32k_2c>(mode, n_rows, st, a);
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace cl
+}  // namespace b200

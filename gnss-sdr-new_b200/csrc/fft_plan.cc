@@ -7,6 +7,10 @@
 
 namespace b200
 {
+namespace cl
+{
+bool cluster_preferred_plan(uint32_t N, uint32_t* ra_lo, uint32_t* rb_lo, uint32_t* ra_hi, uint32_t* rb_hi);  // acq_cluster.cu
+}
 namespace
 {
 // Radices of one stage, lowest stride first. Odd radices go first so that the stride-1 dimension has an odd
@@ -126,6 +130,8 @@ uint32_t best_columns(uint32_t M_lo, uint32_t M_hi)
 // N = (ra_lo*rb_lo) * (ra_hi*rb_hi) with every radix in the instantiated sets; lower is better
 bool find_fast_plan(uint32_t N, FftPlan* plan)
 {
+    // lengths with a row-resident inverse kernel (acq_cluster.cuh) use the factorisation that kernel is instantiated for
+    if (!std::getenv("B200_FFT_PLAN") && cl::cluster_preferred_plan(N, &plan->ra_lo, &plan->rb_lo, &plan->ra_hi, &plan->rb_hi)) return true;
     static const uint32_t RA[] = {25, 5, 16, 8, 4};
     static const uint32_t RB[] = {2, 4, 5, 8, 10, 16, 20};
     double best = 1e30;
