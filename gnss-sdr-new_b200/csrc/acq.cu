@@ -507,6 +507,18 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     FinalizeArgs f;
     f.partials = h->d_partials.as<RowPartial>();
     f.tiles = tiles_last;
+    if (tiles_last > 8)
+        {
+            // one record per warp of the row-resident kernel: fold them per row first (one warp per row)
+            B200_CUDA(h->d_partials2.reserve(sizeof(RowPartial) * (size_t)std::max<size_t>(n_rows, (size_t)n_slots * std::max(tiles_last, tiles_plan))));
+            h->prof.begin(CAT_DECIDE, h->stream);
+            merge_partials_kernel<<<(n_rows + 7) / 8, 256, 0, h->stream>>>(h->d_partials.as<RowPartial>(), tiles_last, n_rows, h->d_partials2.as<RowPartial>());
+            h->prof.end(h->stream);
+            h->launches++;
+            B200_CUDA(cudaGetLastError());
+            f.partials = h->d_partials2.as<RowPartial>();
+            f.tiles = 1;
+        }
     f.nD = h->nD;
     f.nD_local = h->nD_local;
     f.row_begin = h->row_begin;

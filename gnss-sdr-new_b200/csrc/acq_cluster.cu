@@ -8,13 +8,13 @@ namespace cl
 {
 namespace
 {
-// B200_ACQ_CLUSTER: 0 = never use the row-resident kernel (two-kernel path), N = force cluster size N where an instantiation
-// exists; unset = the default variant per plan. Read once per process (tuning aid, like B200_NO_FIXED).
+// B200_ACQ_CLUSTER: 0 = never use the row-resident kernel (two-kernel path), 1 = the variant that stages X_k by TMA bulk copies;
+// unset / anything else = the default variant (operands in registers). Read once per process (tuning aid, like B200_NO_FIXED).
 int env_variant()
 {
     static const int v = [] {
         const char* e = std::getenv("B200_ACQ_CLUSTER");
-        return e ? std::atoi(e) : 0;  // off by default until it beats the two-kernel path
+        return e ? std::atoi(e) : -1;
     }();
     return v;
 }
@@ -22,7 +22,7 @@ int env_variant()
 template <class G, int MODE>
 cudaError_t launch_one(uint32_t n_rows, cudaStream_t st, const FastArgs& a)
 {
-    auto kernel = inv_cluster_kernel<G, MODE>;
+    auto kernel = inv_cluster_wl_kernel<G, MODE>;
     static std::atomic<int> n_clusters_cached[kMaxDeviceSlots];  // per instantiation and device: co-resident clusters (0 = not yet)
     const int slot = device_slot();
     cudaLaunchConfig_t cfg = {};
@@ -41,12 +41,7 @@ cudaError_t launch_one(uint32_t n_rows, cudaStream_t st, const FastArgs& a)
         {
             cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::smem_bytes);
             if (e != cudaSuccess) return e;
-            if (G::CS > 8)
-                {
-                    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-                    if (e != cudaSuccess) return e;
-                }
-            cfg.gridDim = dim3(G::CS * kNumSMs);  // only the shape matters for the query
+            cfg.gridDim = dim3(G::CS * kNumSMs * G::CTAS_PER_SM);  // only the shape matters for the query
             e = cudaOccupancyMaxActiveClusters(&n_clusters, kernel, &cfg);
             if (e != cudaSuccess) return e;
             if (n_clusters <= 0) return cudaErrorLaunchOutOfResources;
@@ -70,14 +65,10 @@ cudaError_t launch_mode(int mode, uint32_t n_rows, cudaStream_t st, const FastAr
     return cudaErrorInvalidValue;
 }
 
-// N = 32 000 = (16 x 10) x (25 x 8) (BASELINE configs[1], Galileo E1 at 8 MS/s): a row is 256 kB = the shared memory of an SM pair.
-// The radices are balanced so that every pass has at least as many pencils as a CTA has threads (fft_plan.cc prefers this plan
-// for the length when the row-resident path is on).
-using G32k_2a = Geo<16, 10, 25, 8, 2, 25, 256, 1>;
-using G32k_2b = Geo<16, 10, 25, 8, 2, 25, 512, 1>;
-// (8 x 8) x (25 x 20): small lower radices = 400 pencils per 3200-point tile in both lower passes, 640 / 800 in the upper ones
-using G32k_2c = Geo<8, 8, 25, 20, 2, 50, 416, 1, 3>;
-using G32k_2d = Geo<8, 8, 25, 20, 2, 50, 512, 1, 3>;
+// N = 32 000 = (8 x 8) x (25 x 20) (BASELINE configs[1], Galileo E1 at 8 MS/s): a row is 256 kB = the shared memory of an SM pair.
+// 8 x 8 lower blocks: 4 blocks = 32 pencils per warp in both lower passes; 16 warps x 2 columns of the 32 a CTA owns.
+using G32k_r = GeoW<8, 8, 25, 20, 2, 512, 0>;   // operands in registers, no staging (default)
+using G32k_w = GeoW<8, 8, 25, 20, 2, 512, 2>;   // X_k tiles by TMA bulk copies, two-stage ring
 }  // namespace
 
 bool cluster_preferred_plan(uint32_t N, uint32_t* ra_lo, uint32_t* rb_lo, uint32_t* ra_hi, uint32_t* rb_hi)
@@ -85,10 +76,7 @@ bool cluster_preferred_plan(uint32_t N, uint32_t* ra_lo, uint32_t* rb_lo, uint32
     if (env_variant() == 0) return false;
     if (N == 32000)
         {
-            if (env_variant() == 256 || env_variant() == 512)
-                *ra_lo = 16, *rb_lo = 10, *ra_hi = 25, *rb_hi = 8;
-            else
-                *ra_lo = 8, *rb_lo = 8, *ra_hi = 25, *rb_hi = 20;
+            *ra_lo = 8, *rb_lo = 8, *ra_hi = 25, *rb_hi = 20;
             return true;
         }
     return false;
@@ -96,20 +84,15 @@ bool cluster_preferred_plan(uint32_t N, uint32_t* ra_lo, uint32_t* rb_lo, uint32
 
 uint32_t cluster_tiles(uint32_t ra_lo, uint32_t rb_lo, uint32_t ra_hi, uint32_t rb_hi)
 {
-    const int v = env_variant();
-    if (v == 0) return 0;
-    if (ra_lo == 16 && rb_lo == 10 && ra_hi == 25 && rb_hi == 8) return v == 512 ? 2 * G32k_2b::NW : 2 * G32k_2a::NW;
-    if (ra_lo == 8 && rb_lo == 8 && ra_hi == 25 && rb_hi == 20) return v == 1512 ? 2 * G32k_2d::NW : 2 * G32k_2c::NW;
+    if (env_variant() == 0) return 0;
+    if (ra_lo == 8 && rb_lo == 8 && ra_hi == 25 && rb_hi == 20) return G32k_r::CS * G32k_r::NW;
     return 0;
 }
 
 cudaError_t launch_inv_cluster(uint32_t ra_lo, uint32_t rb_lo, uint32_t ra_hi, uint32_t rb_hi, int mode, uint32_t n_rows, cudaStream_t st, const FastArgs& a)
 {
-    const int v = env_variant();
-    if (ra_lo == 16 && rb_lo == 10 && ra_hi == 25 && rb_hi == 8)
-        return v == 512 ? launch_mode<G32k_2b>(mode, n_rows, st, a) : launch_mode<G32k_2a>(mode, n_rows, st, a);
     if (ra_lo == 8 && rb_lo == 8 && ra_hi == 25 && rb_hi == 20)
-        return v == 1512 ? launch_mode<G32k_2d>(mode, n_rows, st, a) : launch_mode<G32k_2c>(mode, n_rows, st, a);
+        return env_variant() == 1 ? launch_mode<G32k_w>(mode, n_rows, st, a) : launch_mode<G32k_r>(mode, n_rows, st, a);
     return cudaErrorInvalidValue;
 }
 

@@ -6,19 +6,25 @@
 // A thread-block CLUSTER of CS CTAs owns one row at a time (N = M_lo * M_hi points, 8 N bytes: 256 kB at N = 32 000 does not
 // fit one SM, it fits the distributed shared memory of a pair):
 //
-//   lower stage   CTA r transforms M_hi / CS of the M_hi contiguous length-M_lo blocks, NB at a time. The X_k tile arrives by bulk
-//                 copies (TMA, mbarrier) into a two-stage ring that runs ahead across rows, and is transformed in place; the
-//                 matching C* operands are loaded straight into registers one tile ahead (each is used exactly once);
-//                 the outputs of pass B go straight to the CTA that owns their COLUMN in the upper stage:
-//                 local shared memory or `st.shared::cluster` into the peer's (DSMEM) — this is the stage transpose.
+//   lower stage   CTA r transforms M_hi / CS of the M_hi contiguous length-M_lo blocks; the outputs of pass B go straight to the
+//                 CTA that owns their COLUMN in the upper stage: local shared memory or `st.shared::cluster` into the peer's
+//                 (DSMEM) — this is the stage transpose;
 //   cluster barrier
 //   upper stage   CTA r transforms its M_lo / CS columns (length M_hi, stride M_lo in the row) in place in its U buffer,
-//                 then |.|^2, the optional persistent-grid accumulation, and the per-CTA {max, first argmax, sum} record.
-//   cluster barrier (split: arrive after the upper stage, wait before the next row's first remote store)
+//                 then |.|^2, the optional persistent-grid accumulation, and per-warp {max, first argmax, sum} records;
+//   cluster barrier (split: arrive after the upper stage, wait before the next row's first remote store).
 //
-// The arithmetic (codelets, twiddle tables, operation order) is exactly that of the two-kernel path, so records and grids are
-// bit-identical to it; only where the intermediate lives differs. HBM traffic per row drops from 16 N bytes to the operands,
-// which L2 serves (X_k is shared by all PRNs, C* by all bins).
+// Both stages are WARP-LOCAL: a warp owns whole lower blocks and whole upper columns, so the transposes inside a stage need
+// __syncwarp only and there is no CTA-wide barrier in a records-only search. Operands: either straight from L2 into registers
+// one tile ahead (default: every element is used exactly once, and ncu shows shared-memory bandwidth to be this kernel's
+// scarcest resource), or the X_k tiles by bulk copies (TMA, mbarrier ring) with C* in registers (B200_ACQ_CLUSTER=1).
+//
+// The arithmetic (codelets, twiddle tables, operation order) is exactly that of the two-kernel path on the same FFT plan, so grids
+// are bit-identical to it and records differ only in the summation order of the row sum. DRAM traffic per C2 dwell drops from
+// 2.05 GB to 33 MB (profiles/r02_cluster_ncu_summary.txt). What was measured on the way (profiles/r02_cluster_experiments.md):
+// CTA-barrier versions with TMA rings (0.91-1.08 ms), a 4-CTA cluster with two CTAs per SM, and a warp-specialised version with
+// the two stages pipelined over a double-buffered U and remote mbarrier arrivals (1.09 ms: the kernel is issue-bound, overlap
+// buys nothing) — all bit-identical, all slower than this one (0.75 ms, two-kernel path 0.83 ms).
 #pragma once
 #include "acq_fast.cuh"
 #include <cooperative_groups.h>
@@ -80,158 +86,208 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// Geometry of one instantiation (everything compile-time).
-template <int RA_, int RB_, int RAH_, int RBH_, int CS_, int NB_, int THREADS_, int CTAS_PER_SM_, int STAGES_ = 2>
-struct Geo
+// ------------------------------------------------------------------------------------------------------------------------------
+// Warp-local variant. Same data flow, but no CTA-wide barrier anywhere in a records-only search:
+//   lower stage   a warp owns GB = 32 / RB whole blocks of a tile (32 pencils in pass A); pass A -> __syncwarp -> pass B inside
+//                 the warp's own 32-column window of the staged X tile (XOR-swizzled so that the transposed reads of pass B are
+//                 conflict-free although the bulk-copied rows force an even pitch);
+//   upper stage   a warp owns CW / NW whole columns of U (odd row pitch: both strided passes conflict-free);
+//   operand ring  the warp that is LAST to finish a tile (shared-memory counter) refills its stage with the tile kStages ahead.
+// Per row only the two cluster barriers remain (lower -> upper exchange complete; U free again).
+// ------------------------------------------------------------------------------------------------------------------------------
+// STAGES_ = 0: no operand staging at all — both operands are loaded straight from L2 into registers one tile ahead (each element is
+// used exactly once, so staging only costs shared-memory bandwidth, which ncu shows to be this kernel's scarcest resource); the
+// one "stage" left is the warps' transpose buffer between pass A and pass B.
+template <int RA_, int RB_, int RAH_, int RBH_, int CS_, int THREADS_, int STAGES_, int CTAS_PER_SM_ = 1>
+struct GeoW
 {
-    static constexpr int RA = RA_, RB = RB_, RAH = RAH_, RBH = RBH_, CS = CS_, NB = NB_, THREADS = THREADS_, CTAS_PER_SM = CTAS_PER_SM_;
+    static constexpr int RA = RA_, RB = RB_, RAH = RAH_, RBH = RBH_, CS = CS_, THREADS = THREADS_, CTAS_PER_SM = CTAS_PER_SM_;
+    static constexpr bool kTma = STAGES_ > 0;
+    static constexpr int kStages = STAGES_ > 0 ? STAGES_ : 1;
     static constexpr int M_LO = RA * RB, M_HI = RAH * RBH, N = M_LO * M_HI;
+    static constexpr int NW = THREADS / 32;
     static constexpr int CW = M_LO / CS;      // upper-stage columns owned by one CTA
+    static constexpr int CPW = CW / NW;       // ... by one warp
+    static constexpr int UP = CW + 1;         // U row pitch (odd)
     static constexpr int BPC = M_HI / CS;     // lower-stage blocks transformed by one CTA
-    static constexpr int NT = BPC / NB;       // operand tiles per row and CTA
-    static constexpr int SEG = N / RA;        // F layout (fft_plan.h): distance between consecutive u_a
-    static constexpr int TCOLS = NB * RB;     // elements of one u_a segment inside a tile (contiguous in the F layout)
-    // shared-memory pitch of a segment: rows stay 16-byte aligned (bulk copy) and TP = 2 (mod 16), i.e. a 4-bank skew per row —
-    // the best an even pitch can do for the transposed 64-bit reads of pass B (2-way)
-    static constexpr int TP = TCOLS + ((2 + 16 - (TCOLS & 15)) & 15);
-    static constexpr int TILE = RA * TP;      // float2 per staged X tile
-    static constexpr int kStages = STAGES_;
-    // U buffer [ub][u][CW] with the ub-group stride padded to G = CW (mod 16): a warp that runs over the end of a group continues
-    // on the banks right after it (same rule as upper_group_stride of the two-kernel path)
-    static constexpr int G0 = RAH * CW;
-    static constexpr int GS = G0 + ((CW + 16 - (G0 & 15)) & 15);
-    static constexpr int U_ELEMS = (RBH * GS + 1) / 2 * 2;
-    static constexpr int NW = THREADS / 32;   // per-warp records: CS * NW per row
-    static_assert(M_LO % CS == 0 && M_HI % CS == 0 && BPC % NB == 0, "cluster split");
-    static_assert(CW % RA == 0, "a pass-B output pencil must not straddle two CTAs' column ranges");
-    static_assert(TCOLS <= THREADS, "pass A: one pencil per thread (its code-spectrum operands live in registers)");
-    static_assert((TCOLS * 8) % 16 == 0 && (SEG * 8) % 16 == 0 && (TP * 8) % 16 == 0, "bulk copies need 16-byte granularity");
-    static constexpr size_t smem_bytes = (size_t)(U_ELEMS + kStages * TILE + M_LO + M_HI) * sizeof(float2) + kStages * sizeof(uint64_t);
+    static constexpr int GB = 32 / RB;        // blocks per warp and tile
+    static constexpr int TB = NW * GB;        // blocks per tile
+    static constexpr int NT = (BPC + TB - 1) / TB;
+    static constexpr int SEG = N / RA;
+    static constexpr int TCOLS = TB * RB;     // = 32 * NW
+    static constexpr int TP = TCOLS + 2;      // even pitch (16-byte aligned bulk-copy rows), 4-bank skew per row
+    static constexpr int TILE = RA * TP;
+    static constexpr int U_ELEMS = (M_HI * UP + 1) / 2 * 2;
+    static_assert(M_LO % CS == 0 && M_HI % CS == 0, "cluster split");
+    static_assert(32 % RB == 0 && (GB * RA) % 32 == 0, "a warp's blocks fill whole 32-lane rounds in both lower passes");
+    static_assert(CW % NW == 0 && CW % RA == 0, "columns per warp / pass-B pencils per column range");
+    static_assert(RA == 8 && RB == 8, "the pass-A swizzle below is derived for 8 x 8 blocks");
+    static_assert((BPC * RB * 8) % 16 == 0 && ((BPC % TB) * RB * 8) % 16 == 0 && (TP * 8) % 16 == 0, "bulk copies need 16-byte granularity");
+    static constexpr size_t smem_bytes = (size_t)(U_ELEMS + kStages * TILE + M_HI) * sizeof(float2) + kStages * (sizeof(uint64_t) + sizeof(uint32_t)) + 16;
 };
 
-// MODE 2: records only (CFAR search, no grid kept). MODE 1: persistent magnitude grid with full rows (max_dwells > 1 / dump).
 template <class G, int MODE>
-__global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_kernel(const FastArgs a, const uint32_t n_rows, const uint32_t dbg)
+__global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_kernel(const FastArgs a, const uint32_t n_rows, const uint32_t dbg)
 {
-    constexpr int RA = G::RA, RB = G::RB, RAH = G::RAH, RBH = G::RBH, CS = G::CS, NB = G::NB, NT = G::NT, kT = G::THREADS;
-    constexpr int M_LO = G::M_LO, M_HI = G::M_HI, N = G::N, CW = G::CW, BPC = G::BPC, SEG = G::SEG;
-    constexpr int TCOLS = G::TCOLS, TP = G::TP, TILE = G::TILE, GS = G::GS, S = G::kStages;
+    constexpr int RA = G::RA, RB = G::RB, RAH = G::RAH, RBH = G::RBH, CS = G::CS, NT = G::NT, kT = G::THREADS, NW = G::NW;
+    constexpr int M_LO = G::M_LO, M_HI = G::M_HI, N = G::N, CW = G::CW, CPW = G::CPW, UP = G::UP, BPC = G::BPC, SEG = G::SEG;
+    constexpr int GB = G::GB, TB = G::TB, TP = G::TP, TILE = G::TILE, S = G::kStages;
+    constexpr bool kTma = G::kTma;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    float2* U = reinterpret_cast<float2*>(smem_raw);   // this CTA's columns of the row between the stages
-    float2* xs = U + G::U_ELEMS;                       // [S][RA][TP]   X_k tiles; pass A transforms a tile in place
-    float2* tw_lo = xs + S * TILE;                     // conj W_Mlo^(q*ub), [ub][q]
-    float2* tw_hi = tw_lo + M_LO;                      // conj W_Mhi^(q*ub), [ub][q]
-    uint64_t* full = reinterpret_cast<uint64_t*>(tw_hi + M_HI);  // [S] "X tile landed"
+    float2* U = reinterpret_cast<float2*>(smem_raw);   // [M_HI][UP]: this CTA's columns of the row between the stages
+    float2* xs = U + G::U_ELEMS;                       // [S][RA][TP]: X_k tiles (kTma) / the warps' transpose windows
+    float2* tw_hi = xs + S * TILE;                     // conj W_Mhi^(q*ub), [ub][q]
+    uint64_t* full = reinterpret_cast<uint64_t*>(tw_hi + M_HI);  // [S] "tile landed"
+    uint32_t* done = reinterpret_cast<uint32_t*>(full + S);      // [S] warps that have finished with the stage's tile
 
-    const uint32_t tid = threadIdx.x;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, w = tid >> 5;
     const uint32_t rank = CS > 1 ? cluster_rank() : 0u;
     const uint32_t cluster_id = blockIdx.x / CS, n_clusters = gridDim.x / CS;
 
-    // ---- once per CTA: twiddle tables, barriers, DSMEM base addresses ----
-    for (uint32_t i = tid; i < (uint32_t)M_LO; i += kT)
-        {
-            const uint32_t ub = i / RA, q = i - ub * RA;
-            const float2 w = __ldg(a.W + (size_t)q * ub * (N / M_LO));
-            tw_lo[i] = make_float2(w.x, -w.y);
-        }
     for (uint32_t i = tid; i < (uint32_t)M_HI; i += kT)
         {
             const uint32_t ub = i / RAH, q = i - ub * RAH;
-            const float2 w = __ldg(a.W + (size_t)q * ub * (N / M_HI));
-            tw_hi[i] = make_float2(w.x, -w.y);
+            const float2 t = __ldg(a.W + (size_t)q * ub * (N / M_HI));
+            tw_hi[i] = make_float2(t.x, -t.y);
         }
-    if (tid == 0)
+    if (kTma && tid == 0)
         {
-            for (int s = 0; s < S; s++) mbar_init(&full[s], 1);
+            for (int s = 0; s < S; s++)
+                {
+                    mbar_init(&full[s], 1);
+                    done[s] = 0;
+                }
             fence_barrier_init();
         }
     uint32_t u_base[CS];
 #pragma unroll
     for (int d = 0; d < CS; d++) u_base[d] = CS > 1 ? map_rank(smem_u32(U), d) : smem_u32(U);
+    // pass-A pencil of this lane inside its warp's window: block w*GB + lane / RB of the tile, ub = lane % RB — the same for every
+    // tile, so its inner twiddles conj W_Mlo^(q*ub) stay in registers for the whole kernel
+    const uint32_t ub_a = lane % RB, bl_a = w * GB + lane / RB;
+    float2 twl[RA];
+#pragma unroll
+    for (int q = 0; q < RA; q++)
+        {
+            const float2 t = __ldg(a.W + (size_t)q * ub_a * (N / M_LO));
+            twl[q] = make_float2(t.x, -t.y);
+        }
     __syncthreads();
 
     const uint32_t my_rows = cluster_id < n_rows ? (n_rows - cluster_id + n_clusters - 1) / n_clusters : 0;
     const uint32_t total_tiles = my_rows * NT;
 
-    // operand tile g of this CTA: row g / NT of the cluster, blocks [rank*BPC + (g % NT)*NB, +NB)
-    auto operands = [&](uint32_t g, const float2*& X, const float2*& Cp) {
-        const uint32_t y = a.y0 + cluster_id + (g / NT) * n_clusters;
+    // operand rows of the row the tile counter is in, and of the one after it (resolved once per row, not once per tile)
+    const float2 *rowX[2] = {nullptr, nullptr}, *rowC[2] = {nullptr, nullptr};
+    auto resolve_row = [&](uint32_t r, int slot) {
+        if (r >= my_rows) return;
+        const uint32_t y = a.y0 + cluster_id + r * n_clusters;
         uint32_t si, kk;
         fast_row_of(a, y, si, kk);
-        const uint32_t col0 = (rank * BPC + (g % NT) * NB) * RB;
-        X = a.X + ((size_t)a.slot_group[si] * a.nD_local + kk) * N + col0;
-        Cp = a.Cs + (size_t)a.slots[si] * N + col0;
+        rowX[slot] = a.X + ((size_t)a.slot_group[si] * a.nD_local + kk) * N + rank * BPC * RB;
+        rowC[slot] = a.Cs + (size_t)a.slots[si] * N + rank * BPC * RB;
     };
-    // producer (thread 0): X_k tile g -> stage g % S, RA bulk copies of TCOLS elements (TMA, 1-D)
-    auto issue = [&](uint32_t g) {
+    auto operands = [&](uint32_t g, const float2*& X, const float2*& Cp) {
+        const uint32_t slot = (g / NT) & 1u, col0 = (g % NT) * TB * RB;
+        X = rowX[slot] + col0;
+        Cp = rowC[slot] + col0;
+    };
+    resolve_row(0, 0);
+    resolve_row(1, 1);
+    auto tile_blocks = [&](uint32_t g) -> uint32_t {  // the last tile of a row share may be partial
+        const uint32_t t = g % NT;
+        return (t + 1) * TB <= (uint32_t)BPC ? (uint32_t)TB : (uint32_t)BPC - t * TB;
+    };
+    auto issue = [&](uint32_t g) {  // one lane: X_k tile g -> stage g % S (TMA, 1-D bulk copies)
         const float2 *X, *Cp;
         operands(g, X, Cp);
+        const uint32_t bytes = tile_blocks(g) * RB * (uint32_t)sizeof(float2);
         uint64_t* bar = &full[g % S];
         float2* dst = xs + (g % S) * TILE;
-        mbar_expect_tx(bar, (uint32_t)(RA * TCOLS * sizeof(float2)));
-#pragma unroll 1
-        for (int u = 0; u < RA; u++) bulk_g2s(dst + u * TP, X + (size_t)u * SEG, TCOLS * sizeof(float2), bar);
-    };
-    // the code-spectrum operands of this thread's pass-A pencil of tile g, straight from L2 into registers one tile ahead
-    float2 c[RA];
-    auto load_code = [&](uint32_t g) {
-        const float2 *X, *Cp;
-        operands(g, X, Cp);
+        mbar_expect_tx(bar, RA * bytes);
 #pragma unroll
-        for (int u = 0; u < RA; u++) c[u] = __ldg(Cp + (size_t)u * SEG + tid);
+        for (int u = 0; u < RA; u++) bulk_g2s(dst + u * TP, X + (size_t)u * SEG, bytes, bar);
     };
-    if (tid == 0)
+    // operands of this lane's pass-A pencil of tile g, straight from L2 into registers one tile ahead
+    float2 cn[RA], xn[kTma ? 1 : RA];
+    auto load_operands = [&](uint32_t g) {
+        if (bl_a < tile_blocks(g))
+            {
+                const float2 *X, *Cp;
+                operands(g, X, Cp);
+#pragma unroll
+                for (int u = 0; u < RA; u++) cn[u] = __ldg(Cp + (size_t)u * SEG + w * 32 + lane);
+                if (!kTma)
+                    {
+#pragma unroll
+                        for (int u = 0; u < RA; u++) xn[kTma ? 0 : u] = __ldg(X + (size_t)u * SEG + w * 32 + lane);
+                    }
+            }
+    };
+    if (kTma && tid == 0)
         for (uint32_t g = 0; g < (uint32_t)S && g < total_tiles; g++) issue(g);
-    if (tid < (uint32_t)TCOLS && total_tiles > 0) load_code(0);
+    if (total_tiles > 0) load_operands(0);
 
-    uint32_t g = 0;  // running tile counter of this CTA
+    uint32_t g = 0;
     for (uint32_t r = 0; r < my_rows; r++)
         {
             const uint32_t y = a.y0 + cluster_id + r * n_clusters;
             uint32_t si, kk;
             fast_row_of(a, y, si, kk);
+            if (r > 0) resolve_row(r + 1, (r + 1) & 1);  // row r - 1's slot is free: its last tile was loaded before this row began
 
-            // ================= lower stage =================
+            // ================= lower stage: warp-local, tile after tile =================
 #pragma unroll 1
             for (int t = 0; t < NT; t++, g++)
                 {
-                    float2* xt = xs + (g % S) * TILE;
-                    if (!(dbg & 2u) || g < (uint32_t)S) mbar_wait(&full[g % S], (g / S) & 1u);
-                    // ---- pass A: pencil p = (block bl, ub): product, radix-RA IDFT, inner twiddle, in place ----
-                    if (tid < (uint32_t)TCOLS && !(dbg & 8u))
-                        {
-                            const uint32_t p = tid, ub = p % RB;
-                            float2 x[RA];
+                    float2* xt = xs + (kTma ? (g % S) * TILE : 0) + w * 32;  // this warp's 32-column window
+                    const uint32_t nblk = tile_blocks(g);
+                    if (kTma && (!(dbg & 2u) || g < (uint32_t)S)) mbar_wait(&full[g % S], (g / S) & 1u);
+                    // ---- pass A: product, radix-RA IDFT, inner twiddle; stored swizzled (column ^ (q >= RA/2)) ----
+                    {
+                        const bool act = bl_a < nblk && !(dbg & 8u);
+                        float2 x[RA];
+                        if (act)
+                            {
 #pragma unroll
-                            for (int u = 0; u < RA; u++) x[u] = fft::cmul(xt[u * TP + p], c[u]);  // :665
-                            fft::Dft<RA, true>::run(x);
+                                for (int u = 0; u < RA; u++) x[u] = fft::cmul(kTma ? xt[u * TP + lane] : xn[kTma ? 0 : u], cn[u]);  // :665
+                            }
+                        if (g + 1 < total_tiles && !(dbg & 128u)) load_operands(g + 1);  // in flight behind this tile (and the upper stage)
+                        if (act) fft::Dft<RA, true>::run(x);
+                        if (kTma) __syncwarp();  // every lane has read its inputs before any lane overwrites the window
+                        if (act)
+                            {
 #pragma unroll
-                            for (int q = 0; q < RA; q++) xt[q * TP + p] = fft::cmul(x[q], tw_lo[ub * RA + q]);
-                            if (g + 1 < total_tiles && !(dbg & 128u)) load_code(g + 1);  // in flight behind pass B (and the upper stage)
-                        }
-                    __syncthreads();
-                    if (t == 0 && r > 0 && CS > 1 && !(dbg & 64u)) cluster_wait();  // every CTA of the cluster is done READING its U of the previous row
-                    // ---- pass B: pencil p = (block bl, a): radix-RB IDFT, inter-stage twiddle, to the owner of each column ----
-                    for (uint32_t p = tid; p < (uint32_t)(NB * RA) && !(dbg & 16u); p += kT)
+                                for (int q = 0; q < RA; q++) xt[q * TP + (lane ^ (uint32_t)(q >= RA / 2))] = fft::cmul(x[q], twl[q]);
+                            }
+                    }
+                    __syncwarp();
+                    if (t == 0 && r > 0 && CS > 1 && !(dbg & 64u)) cluster_wait();  // every CTA is done READING its U of the previous row
+                    // ---- pass B: radix-RB IDFT, inter-stage twiddle, to the owner of each column ----
+#pragma unroll 1
+                    for (uint32_t pp = lane; pp < (uint32_t)(GB * RA) && !(dbg & 16u); pp += 32)
                         {
-                            const uint32_t bl = p / RA, aa = p - bl * RA;
-                            const uint32_t gblk = rank * BPC + t * NB + bl;
+                            const uint32_t bl_l = pp / RA, aa = pp - bl_l * RA;
+                            const uint32_t bl = w * GB + bl_l;
+                            if (bl >= nblk) continue;
+                            const uint32_t gblk = rank * BPC + t * TB + bl;
                             const uint32_t ubh = gblk / RAH, uah = gblk - ubh * RAH;
                             const uint32_t k1 = uah * RBH + ubh;  // upper-stage frequency index of this block
                             const float2 wb = __ldg(a.W + (size_t)k1 * aa);
                             const float2 ws = __ldg(a.W + (size_t)k1 * RA);
                             float2 v[RB];
+                            const uint32_t swz = aa >= RA / 2;
 #pragma unroll
-                            for (int u = 0; u < RB; u++) v[u] = xt[aa * TP + bl * RB + u];
+                            for (int u = 0; u < RB; u++) v[u] = xt[aa * TP + ((bl_l * RB + u) ^ swz)];
                             fft::Dft<RB, true>::run(v);
                             float2 tw = make_float2(wb.x, -wb.y);
                             const float2 stp = make_float2(ws.x, -ws.y);
-                            const uint32_t e0 = ubh * GS + uah * CW + aa;  // U element of column aa in the owner's buffer
+                            const uint32_t e0 = gblk * UP + aa;
 #pragma unroll
                             for (int b = 0; b < RB; b++)
                                 {
-                                    constexpr int kPer = CW / RA;  // b values per CTA column range
-                                    const int d = b / kPer;          // owner CTA of column aa + RA*b
+                                    constexpr int kPer = CW / RA;
+                                    const int d = b / kPer;
                                     const uint32_t e = e0 + RA * (b % kPer);
                                     const float2 val = fft::cmul(v[b], tw);
                                     if (CS == 1 || (uint32_t)d == rank || (dbg & 1u))
@@ -241,79 +297,113 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_kernel
                                     tw = fft::cmul(tw, stp);
                                 }
                         }
-                    fence_proxy_async();  // this thread's generic-proxy accesses to the tile before the async-proxy refill
-                    __syncthreads();
-                    if (tid == 0 && g + S < total_tiles && !(dbg & 2u)) issue(g + S);  // refill the stage with the tile S ahead
+                    if (kTma)
+                        {
+                            // the warp is done with the stage; the last warp to get here refills it
+                            fence_proxy_async();
+                            __syncwarp();
+                            if (lane == 0)
+                                {
+                                    __threadfence_block();
+                                    const uint32_t prev = atomicAdd(&done[g % S], 1u);
+                                    if (prev == (uint32_t)NW - 1)
+                                        {
+                                            done[g % S] = 0;
+                                            __threadfence_block();
+                                            if (g + S < total_tiles && !(dbg & 2u)) issue(g + S);
+                                        }
+                                }
+                        }
+                    else
+                        __syncwarp();  // pass B has read the window before the next tile's pass A overwrites it
                 }
             if (CS > 1 && !(dbg & 64u))
                 {
                     cluster_arrive();  // my remote stores of this row are done ...
                     cluster_wait();    // ... and so are everybody's into my U
                 }
+            else if (CS == 1)
+                __syncthreads();
 
-            // ================= upper stage (in place in U) =================
-            // ---- pass A: pencil (column cl, ub) ----
-            for (uint32_t p = tid; p < (uint32_t)(CW * RBH) && !(dbg & 4u); p += kT)
+            // ================= upper stage: warp-local, CPW columns of U in place =================
+            // lanes: half-warp h works on column (h % CPW) of the warp, lanes of a half-warp on 16 consecutive pencils of that
+            // column: with the odd row pitch every 64-bit access of both strided passes is conflict-free
+            static_assert(CPW == 2, "lane map of the upper stage: one column per half-warp");
+            float2* Uw = U + w * CPW + (lane >> 4);
+            const uint32_t l16 = lane & 15u;
+#pragma unroll 1
+            for (uint32_t ub = l16; ub < (uint32_t)RBH && !(dbg & 4u); ub += 16)
                 {
-                    const uint32_t ub = p / CW, cl = p - ub * CW;
                     float2 v[RAH];
-                    float2* col = U + ub * GS + cl;
+                    float2* col = Uw + (size_t)RAH * ub * UP;
 #pragma unroll
-                    for (int u = 0; u < RAH; u++) v[u] = col[u * CW];
+                    for (int u = 0; u < RAH; u++) v[u] = col[u * UP];
                     fft::Dft<RAH, true>::run(v);
 #pragma unroll
-                    for (int q = 0; q < RAH; q++) col[q * CW] = fft::cmul(v[q], tw_hi[ub * RAH + q]);
+                    for (int q = 0; q < RAH; q++) col[q * UP] = fft::cmul(v[q], tw_hi[ub * RAH + q]);
                 }
-            __syncthreads();
-            // ---- pass B + |.|^2 + reductions: pencil (column cl, a) ----
+            __syncwarp();
             float best = -1.f, sum = 0.f;
             uint32_t best_pos = 0xffffffffu;
-            float* mag = nullptr;
-            bool accumulate = false;
-            if (MODE == 1)
+#pragma unroll 1
+            for (uint32_t aa = l16; aa < (uint32_t)RAH && !(dbg & 32u); aa += 16)
                 {
-                    mag = a.mag_base + ((size_t)a.slots[si] * a.nD_local + kk) * N;
-                    accumulate = a.dwell_after[si] > 1;
-                }
-            for (uint32_t p = tid; p < (uint32_t)(CW * RAH) && !(dbg & 32u); p += kT)
-                {
-                    const uint32_t aa = p / CW, cl = p - aa * CW;
-                    const uint32_t pos0 = aa * M_LO + rank * CW + cl;
-                    float old[MODE == 1 ? RBH : 1];
+                    float2 v[RBH];
+                    float2* col = Uw + (size_t)aa * UP;
+#pragma unroll
+                    for (int u = 0; u < RBH; u++) v[u] = col[(size_t)RAH * u * UP];
+                    fft::Dft<RBH, true>::run(v);
                     if (MODE == 1)
                         {
+                            // persistent grid: park |.|^2 in the slots just consumed; the coalesced read-modify-write follows below
 #pragma unroll
-                            for (int b = 0; b < RBH; b++) old[b] = accumulate ? __ldcs(mag + pos0 + b * (RAH * M_LO)) : 0.f;
+                            for (int b = 0; b < RBH; b++) col[(size_t)RAH * b * UP].x = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
                         }
-                    float2 v[RBH];
-#pragma unroll
-                    for (int u = 0; u < RBH; u++) v[u] = U[u * GS + aa * CW + cl];
-                    fft::Dft<RBH, true>::run(v);
-                    float pbest = -1.f;
-                    uint32_t pb = 0;
-#pragma unroll
-                    for (int b = 0; b < RBH; b++)
+                    else
                         {
-                            float gm = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
-                            if (MODE == 1)
+                            const uint32_t pos0 = aa * M_LO + rank * CW + w * CPW + (lane >> 4);
+                            float pbest = -1.f;
+                            uint32_t pb = 0;
+#pragma unroll
+                            for (int b = 0; b < RBH; b++)
                                 {
-                                    gm = old[b] + gm;  // :679 (0 + g on the first dwell)
-                                    __stcs(mag + pos0 + b * (RAH * M_LO), gm);
+                                    const float gm = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                                    sum += gm;
+                                    const bool gt = gm > pbest;
+                                    pbest = gt ? gm : pbest;
+                                    pb = gt ? (uint32_t)b : pb;
                                 }
-                            sum += gm;
-                            const bool gt = gm > pbest;
-                            pbest = gt ? gm : pbest;
-                            pb = gt ? (uint32_t)b : pb;
-                        }
-                    const uint32_t ppos = pos0 + pb * (RAH * M_LO);
-                    if (pbest > best || (pbest == best && ppos < best_pos))
-                        {
-                            best = pbest;
-                            best_pos = ppos;
+                            const uint32_t ppos = pos0 + pb * (RAH * M_LO);
+                            if (pbest > best || (pbest == best && ppos < best_pos))
+                                {
+                                    best = pbest;
+                                    best_pos = ppos;
+                                }
                         }
                 }
-            if (CS > 1 && r + 1 < my_rows && !(dbg & 64u)) cluster_arrive();  // this thread is done reading U: peers may overwrite it (next row)
-            // one record per warp: maximum with the lowest position among equals (:523), and the warp's share of the row sum
+            if (MODE == 1)
+                {
+                    // rows of U are CW consecutive grid cells: one warp per row, old values streamed in, sums streamed out
+                    __syncthreads();
+                    float* mag = a.mag_base + ((size_t)a.slots[si] * a.nD_local + kk) * N + rank * CW;
+                    const bool accumulate = a.dwell_after[si] > 1;
+                    for (uint32_t blk = w; blk < (uint32_t)M_HI; blk += NW)
+                        for (uint32_t cl = lane; cl < (uint32_t)CW; cl += 32)
+                            {
+                                const uint32_t pos = blk * M_LO + cl;
+                                float gm = U[blk * UP + cl].x;
+                                if (accumulate) gm = __ldcs(mag + pos) + gm;  // :679
+                                __stcs(mag + pos, gm);
+                                sum += gm;
+                                const uint32_t gpos = pos + rank * CW;
+                                if (gm > best || (gm == best && gpos < best_pos))
+                                    {
+                                        best = gm;
+                                        best_pos = gpos;
+                                    }
+                            }
+                }
+            if (CS > 1 && r + 1 < my_rows && !(dbg & 64u)) cluster_arrive();  // this warp is done reading U
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1)
                 {
@@ -326,19 +416,19 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_kernel
                             best_pos = op;
                         }
                 }
-            if ((tid & 31u) == 0)
+            if (lane == 0)
                 {
                     RowPartial rp;
                     rp.max_val = best;
                     rp.max_idx = best_pos;
                     rp.sum = sum;
                     rp.pad = 0;
-                    a.partials[((size_t)y * CS + rank) * G::NW + (tid >> 5)] = rp;
+                    a.partials[((size_t)y * CS + rank) * NW + w] = rp;
                 }
+            if (CS == 1) __syncthreads();
         }
     if (CS > 1)
         {
-            // nobody leaves while a peer may still address its shared memory
             cluster_arrive();
             cluster_wait();
         }

@@ -334,6 +334,48 @@ struct FinalizeArgs
     uint32_t* best_k_local;      // [n_slots in call]
 };
 
+// Many records per row (the row-resident inverse writes one per warp): one warp per row merges them into a single record, so that
+// finalize_kernel's per-slot warp does not walk them one by one. Lowest index wins among equal maxima (:523); the sum is a fixed
+// shuffle tree, i.e. deterministic.
+static __global__ void merge_partials_kernel(const RowPartial* in, uint32_t tiles, uint32_t n_rows, RowPartial* out)
+{
+    const uint32_t y = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+    if (y >= n_rows) return;
+    float m = -1.f, s = 0.f;
+    uint32_t mi = 0xffffffffu;
+    for (uint32_t t = lane; t < tiles; t += 32)
+        {
+            const RowPartial p = in[(size_t)y * tiles + t];
+            s += p.sum;
+            if (p.max_val > m || (p.max_val == m && p.max_idx < mi))
+                {
+                    m = p.max_val;
+                    mi = p.max_idx;
+                }
+        }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            const float om = __shfl_xor_sync(0xffffffffu, m, o);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, mi, o);
+            s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (om > m || (om == m && oi < mi))
+                {
+                    m = om;
+                    mi = oi;
+                }
+        }
+    if (lane == 0)
+        {
+            RowPartial r;
+            r.max_val = m;
+            r.max_idx = mi;
+            r.sum = s;
+            r.pad = 0;
+            out[y] = r;
+        }
+}
+
 // one warp per slot
 static __global__ void finalize_kernel(const FinalizeArgs a)
 {

@@ -463,7 +463,8 @@ def test_fixed_geometry_kernels_are_bit_identical_to_runtime_ones(tmp_path):
     import subprocess
     import sys
     outs = []
-    for tag, extra in (("fixed", {}), ("runtime", {"B200_NO_FIXED": "1"})):
+    # B200_ACQ_CLUSTER=0: N = 32000 on the two-kernel path in both runs (its row-resident kernel has no runtime-geometry twin)
+    for tag, extra in (("fixed", {"B200_ACQ_CLUSTER": "0"}), ("runtime", {"B200_NO_FIXED": "1", "B200_ACQ_CLUSTER": "0"})):
         path = str(tmp_path / (tag + ".npz"))
         r = subprocess.run([sys.executable, "-c", _FIXED_CHILD, os.path.dirname(os.path.dirname(os.path.abspath(__file__))), path],
                            env=dict(os.environ, **extra), capture_output=True, text=True, timeout=600)

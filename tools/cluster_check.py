@@ -57,13 +57,10 @@ np.savez(out, **res)
 
 
 VARIANTS = {
-    "ref": dict(B200_ACQ_CLUSTER="0"),
-    "ref_sameplan": dict(B200_ACQ_CLUSTER="0", B200_FFT_PLAN="16,10,25,8"),
-    "ref_8_8": dict(B200_ACQ_CLUSTER="0", B200_FFT_PLAN="8,8,25,20"),
-    "cl416": dict(B200_ACQ_CLUSTER="1416"),
-    "cl1512": dict(B200_ACQ_CLUSTER="1512"),
-    "cl256": dict(B200_ACQ_CLUSTER="256"),
-    "cl512": dict(B200_ACQ_CLUSTER="512"),
+    "ref": dict(B200_ACQ_CLUSTER="0"),                                   # two-kernel path, its own plan
+    "ref_sameplan": dict(B200_ACQ_CLUSTER="0", B200_FFT_PLAN="8,8,25,20"),  # two-kernel path on the row-resident kernel's plan
+    "cl_tma": dict(B200_ACQ_CLUSTER="1"),
+    "cl": dict(),
 }
 REC = np.dtype([("test_statistic", np.float32), ("peak", np.float32), ("input_power", np.float32), ("second_peak", np.float32),
                 ("code_phase", np.uint32), ("doppler_index", np.uint32), ("doppler_hz", np.int32), ("dwell_count", np.uint32)])
