@@ -139,6 +139,11 @@ EXPORTS = [
     "gnss_b200_resampler_work",
     "gnss_b200_trk_create", "gnss_b200_trk_destroy", "gnss_b200_trk_set_code", "gnss_b200_trk_start", "gnss_b200_trk_run",
     "gnss_b200_trk_stream", "gnss_b200_trk_launch_count",
+    "gnss_b200_acq_exchange_buffers", "gnss_b200_acq_finalize_gathered_async",
+    "gnss_b200_acq_capture_begin", "gnss_b200_acq_capture_end", "gnss_b200_acq_replay_async",
+    "gnss_b200_acq_group_create", "gnss_b200_acq_group_destroy", "gnss_b200_acq_group_num_doppler_bins", "gnss_b200_acq_group_num_shards",
+    "gnss_b200_acq_group_set_local_codes", "gnss_b200_acq_group_set_doppler_center", "gnss_b200_acq_group_reset", "gnss_b200_acq_group_dwell",
+    "gnss_b200_acq_group_read_grid", "gnss_b200_acq_group_launch_count",
 ]
 
 _lib = None
@@ -176,6 +181,24 @@ def lib():
     L.gnss_b200_acq_dwell.argtypes = [C.c_void_p, C.c_void_p, C.c_int, c_u32, _u32p, C.c_void_p]
     L.gnss_b200_acq_dwell_device_async.argtypes = [C.c_void_p, C.c_void_p, c_u32, _u32p]
     L.gnss_b200_acq_sync.argtypes = [C.c_void_p, c_u32, C.c_void_p]
+    L.gnss_b200_acq_exchange_buffers.argtypes = [C.c_void_p, c_u32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), _u32p]
+    L.gnss_b200_acq_finalize_gathered_async.argtypes = [C.c_void_p, c_u32]
+    L.gnss_b200_acq_capture_begin.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_capture_end.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_replay_async.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_group_create.argtypes = [C.POINTER(AcqCfg), c_u32, C.POINTER(c_i32), C.POINTER(C.c_void_p)]
+    L.gnss_b200_acq_group_destroy.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_group_num_doppler_bins.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_group_num_doppler_bins.restype = c_u32
+    L.gnss_b200_acq_group_num_shards.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_group_num_shards.restype = c_u32
+    L.gnss_b200_acq_group_set_local_codes.argtypes = [C.c_void_p, c_u32, _u32p, _fp]
+    L.gnss_b200_acq_group_set_doppler_center.argtypes = [C.c_void_p, c_u32, c_i32, c_i32]
+    L.gnss_b200_acq_group_reset.argtypes = [C.c_void_p, c_u32]
+    L.gnss_b200_acq_group_dwell.argtypes = [C.c_void_p, C.c_void_p, C.c_int, c_u32, _u32p, C.c_void_p]
+    L.gnss_b200_acq_group_read_grid.argtypes = [C.c_void_p, c_u32, _fp]
+    L.gnss_b200_acq_group_launch_count.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_group_launch_count.restype = C.c_uint64
     L.gnss_b200_acq_read_grid.argtypes = [C.c_void_p, c_u32, _fp]
     L.gnss_b200_acq_read_rows.argtypes = [C.c_void_p, c_u32, C.c_void_p]
     L.gnss_b200_acq_finalize_rows.argtypes = [C.c_void_p, c_u32, c_u32, c_i32, c_u32, c_i32, c_u32, C.c_void_p]
@@ -331,6 +354,24 @@ class PcpsAcquisitionB200:
         _check(self.L.gnss_b200_acq_sync(self.h, n_slots, res.ctypes.data_as(C.c_void_p)))
         return res
 
+    def exchange_buffers(self, world):
+        """(d_send pointer, d_recv pointer, bytes per shard, rows per shard) of a sharded search (include/gnss_b200.h)."""
+        ds, dr, nb, ch = C.c_void_p(), C.c_void_p(), C.c_uint64(), c_u32()
+        _check(self.L.gnss_b200_acq_exchange_buffers(self.h, int(world), C.byref(ds), C.byref(dr), C.byref(nb), C.byref(ch)))
+        return ds.value, dr.value, int(nb.value), int(ch.value)
+
+    def finalize_gathered_async(self, n_slots):
+        _check(self.L.gnss_b200_acq_finalize_gathered_async(self.h, int(n_slots)))
+
+    def capture_begin(self):
+        _check(self.L.gnss_b200_acq_capture_begin(self.h))
+
+    def capture_end(self):
+        _check(self.L.gnss_b200_acq_capture_end(self.h))
+
+    def replay_async(self):
+        _check(self.L.gnss_b200_acq_replay_async(self.h))
+
     def read_grid(self, slot):
         out = np.zeros((self.n_doppler_local, self.eff), dtype=np.float32)
         _check(self.L.gnss_b200_acq_read_grid(self.h, slot, _f32p(out)))
@@ -353,6 +394,64 @@ class PcpsAcquisitionB200:
 
     def launch_count(self):
         return int(self.L.gnss_b200_acq_launch_count(self.h))
+
+
+class PcpsAcquisitionGroupB200:
+    """One search over several GPUs of this process (gnss_b200_acq_group_*): Doppler rows split over `devices`."""
+
+    def __init__(self, fft_size, consumed_samples, doppler_max, doppler_step, fs, samples_per_chip, max_slots, devices, bit_transition=False, keep_grid=False):
+        self.L = lib()
+        self.cfg = AcqCfg(fft_size, consumed_samples, int(bit_transition), int(doppler_max), int(doppler_step), float(fs),
+                          int(samples_per_chip), 1, int(keep_grid), int(max_slots), 0, 0, 0)
+        dev = (c_i32 * len(devices))(*[int(d) for d in devices])
+        self.h = C.c_void_p()
+        _check(self.L.gnss_b200_acq_group_create(C.byref(self.cfg), len(devices), dev, C.byref(self.h)))
+        self.consumed = consumed_samples
+        self.eff = fft_size // 2 if bit_transition else fft_size
+        self.n_doppler = self.L.gnss_b200_acq_group_num_doppler_bins(self.h)
+        self.n_shards = self.L.gnss_b200_acq_group_num_shards(self.h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.gnss_b200_acq_group_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_local_codes(self, slots, codes):
+        slots = _u32a(slots)
+        codes = np.ascontiguousarray(codes, dtype=np.complex64).reshape(slots.size, -1)
+        if codes.shape[1] != self.consumed:
+            raise B200Error(f"set_local_codes: each code needs consumed_samples={self.consumed} items, got {codes.shape[1]}")
+        _check(self.L.gnss_b200_acq_group_set_local_codes(self.h, slots.size, slots.ctypes.data_as(_u32p), _f32p(codes.view(np.float32))))
+
+    def set_doppler_center(self, slot, center_hz, bias_hz=0):
+        _check(self.L.gnss_b200_acq_group_set_doppler_center(self.h, slot, int(center_hz), int(bias_hz)))
+
+    def reset(self, slot):
+        _check(self.L.gnss_b200_acq_group_reset(self.h, slot))
+
+    def dwell(self, samples, slots):
+        slots = _u32a(slots)
+        samples = np.ascontiguousarray(samples, dtype=np.complex64)
+        if samples.size < self.consumed:
+            raise B200Error("dwell: not enough samples")
+        res = np.zeros(slots.size, dtype=ACQ_RESULT_DTYPE)
+        _check(self.L.gnss_b200_acq_group_dwell(self.h, samples.ctypes.data_as(C.c_void_p), 0, slots.size, slots.ctypes.data_as(_u32p),
+                                                res.ctypes.data_as(C.c_void_p)))
+        return res
+
+    def read_grid(self, slot):
+        out = np.zeros((self.n_doppler, self.eff), dtype=np.float32)
+        _check(self.L.gnss_b200_acq_group_read_grid(self.h, slot, _f32p(out)))
+        return out
+
+    def launch_count(self):
+        return int(self.L.gnss_b200_acq_group_launch_count(self.h))
 
 
 def finalize_rows(rows, effective_size, doppler_max, doppler_step, doppler_center, dwell_count):

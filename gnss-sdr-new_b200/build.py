@@ -6,7 +6,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgnss_b200.so")
-SOURCES = ["api_misc.cu", "multicorr.cu", "trk_loop.cu", "resampler.cu", "acq.cu", "acq_fast_lower.cu", "acq_fast_upper.cu", "acq_fast_fwd.cu", "acq_cluster.cu", "fft_plan.cc", "wipeoff_pieces.cc"]
+SOURCES = ["api_misc.cu", "multicorr.cu", "trk_loop.cu", "resampler.cu", "acq.cu", "acq_group.cu", "acq_fast_lower.cu", "acq_fast_upper.cu", "acq_fast_fwd.cu", "acq_cluster.cu", "fft_plan.cc", "wipeoff_pieces.cc"]
 
 
 def _stale():

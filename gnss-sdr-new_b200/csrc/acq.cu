@@ -63,6 +63,15 @@ struct gnss_b200_acq
     std::vector<uint32_t> dwell;
     uint32_t last_n_slots = 0;
     EventProfiler prof;
+    // sharded search (gnss_b200_acq_exchange_buffers): what this shard sends / what all shards sent
+    DevBuf d_send, d_recv;
+    uint32_t xchg_world = 0, xchg_chunk = 0;
+    // what the last dwell left on the device for gnss_b200_acq_finalize_gathered_async
+    FinalizeArgs last_f{};
+    // a captured dwell (gnss_b200_acq_capture_*)
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    bool capturing = false;
 };
 
 namespace
@@ -540,6 +549,15 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     h->prof.end(h->stream);
     h->launches++;
     B200_CUDA(cudaGetLastError());
+    h->last_f = f;
+    if (h->xchg_world)
+        {
+            // sharded search: this shard's rows of the call's slots, contiguous, ready to be sent
+            pack_rows_kernel<<<n_slots, 64, 0, h->stream>>>(h->d_rows.as<gnss_b200_acq_row>(), d_slots, h->nD, h->row_begin, h->nD_local, h->xchg_chunk,
+                h->d_send.as<gnss_b200_acq_row>());
+            h->launches++;
+            B200_CUDA(cudaGetLastError());
+        }
 
     if (!h->cfg.use_cfar)
         {
@@ -705,6 +723,10 @@ extern "C"
         for (DevBuf* b : {&h->d_W, &h->d_cbuf, &h->d_xbuf, &h->d_xtmp, &h->d_samples, &h->d_codes_td, &h->d_scratch, &h->d_pieces, &h->d_npieces, &h->d_meta,
                  &h->d_partials, &h->d_partials2, &h->d_rows, &h->d_results, &h->d_bestk, &h->d_grid, &h->d_rowbuf})
             b->release();
+        h->d_send.release();
+        h->d_recv.release();
+        if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+        if (h->graph) cudaGraphDestroy(h->graph);
         h->h_meta.release();
         h->h_results.release();
         h->h_samples.release();
@@ -902,6 +924,87 @@ extern "C"
             }
         if (reset) h->prof.reset();
         h->prof.on = enable != 0;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_exchange_buffers(gnss_b200_acq* h, uint32_t world, void** d_send, void** d_recv, uint64_t* bytes_per_shard, uint32_t* rows_per_shard)
+    {
+        B200_REQUIRE(h && world >= 1 && world <= 64, GNSS_B200_ERR_INVALID, "acq_exchange_buffers: bad arguments");
+        B200_REQUIRE(!h->step2, GNSS_B200_ERR_STATE, "acq_exchange_buffers: the narrow second grid is not row-sharded");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        const uint32_t chunk = (h->nD + world - 1) / world;
+        B200_REQUIRE(h->nD_local <= chunk && h->row_begin % chunk == 0, GNSS_B200_ERR_INVALID,
+            "acq_exchange_buffers: with %u shards a handle owns rows [r * %u, (r + 1) * %u), this one has [%u, %u)", world, chunk, chunk, h->row_begin,
+            h->row_begin + h->nD_local);
+        const size_t per = sizeof(gnss_b200_acq_row) * (size_t)h->cfg.max_slots * chunk;
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        B200_CUDA(h->d_send.reserve(per));
+        B200_CUDA(h->d_recv.reserve(per * world));
+        B200_CUDA(cudaMemset(h->d_recv.p, 0, per * world));
+        h->xchg_world = world;
+        h->xchg_chunk = chunk;
+        if (d_send) *d_send = h->d_send.p;
+        if (d_recv) *d_recv = h->d_recv.p;
+        if (bytes_per_shard) *bytes_per_shard = per;
+        if (rows_per_shard) *rows_per_shard = chunk;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_finalize_gathered_async(gnss_b200_acq* h, uint32_t n_slots)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_finalize_gathered_async: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_REQUIRE(h->xchg_world, GNSS_B200_ERR_STATE, "acq_finalize_gathered_async: call gnss_b200_acq_exchange_buffers first");
+        B200_REQUIRE(n_slots == h->last_n_slots && n_slots > 0, GNSS_B200_ERR_INVALID, "acq_finalize_gathered_async: n_slots differs from the last dwell");
+        B200_REQUIRE(h->cfg.use_cfar, GNSS_B200_ERR_UNSUPPORTED, "acq_finalize_gathered_async: only the CFAR statistic can be decided from row records");
+        finalize_gathered_kernel<<<n_slots, 32, 0, h->stream>>>(h->last_f, h->d_recv.as<gnss_b200_acq_row>(), h->xchg_world, h->xchg_chunk, n_slots);
+        h->launches++;
+        B200_CUDA(cudaGetLastError());
+        B200_CUDA(cudaMemcpyAsync(h->h_results.p, h->d_results.p, sizeof(gnss_b200_acq_result) * n_slots, cudaMemcpyDeviceToHost, h->stream));
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_capture_begin(gnss_b200_acq* h)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_capture_begin: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_REQUIRE(!h->capturing, GNSS_B200_ERR_STATE, "acq_capture_begin: already capturing");
+        B200_REQUIRE(!h->prof.on, GNSS_B200_ERR_STATE, "acq_capture_begin: switch the per-kernel profiler off first");
+        B200_REQUIRE(!h->cfg.keep_grid, GNSS_B200_ERR_UNSUPPORTED, "acq_capture_begin: a persistent grid counts its dwells on the host; capture single-dwell searches only");
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        B200_CUDA(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+        h->capturing = true;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_capture_end(gnss_b200_acq* h)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_capture_end: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_REQUIRE(h->capturing, GNSS_B200_ERR_STATE, "acq_capture_end: no capture in progress");
+        h->capturing = false;
+        cudaGraph_t g = nullptr;
+        B200_CUDA(cudaStreamEndCapture(h->stream, &g));
+        if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+        if (h->graph) cudaGraphDestroy(h->graph);
+        h->graph = g;
+        h->graph_exec = nullptr;
+        B200_CUDA(cudaGraphInstantiate(&h->graph_exec, h->graph, 0));
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_replay_async(gnss_b200_acq* h)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_replay_async: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_REQUIRE(h->graph_exec, GNSS_B200_ERR_STATE, "acq_replay_async: nothing captured");
+        B200_CUDA(cudaGraphLaunch(h->graph_exec, h->stream));
+        h->launches++;
         return GNSS_B200_OK;
     }
 

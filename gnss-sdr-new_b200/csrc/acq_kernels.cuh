@@ -480,6 +480,84 @@ static __global__ void finalize_kernel(const FinalizeArgs a)
         }
 }
 
+// ---- sharded search: the exchange unit and the decision from gathered rows ----
+// pack: the rows this handle computed, as [n_slots of the call][chunk] records, contiguous (what one rank sends)
+static __global__ void pack_rows_kernel(const gnss_b200_acq_row* rows, const uint32_t* slots, uint32_t nD, uint32_t row_begin, uint32_t nD_local,
+    uint32_t chunk, gnss_b200_acq_row* out)
+{
+    const uint32_t si = blockIdx.x;
+    const gnss_b200_acq_row* src = rows + (size_t)slots[si] * nD + row_begin;
+    for (uint32_t j = threadIdx.x; j < chunk; j += blockDim.x)
+        {
+            gnss_b200_acq_row r;
+            r.max_val = 0.f;
+            r.max_idx = 0;
+            r.row_sum = 0.f;
+            r.valid = 0;
+            if (j < nD_local) r = src[j];
+            out[(size_t)si * chunk + j] = r;
+        }
+}
+
+// decision (:511-543, CFAR statistic) from the records of ALL shards: gathered = [world][n_slots][chunk], shard r holds rows
+// [r * chunk, (r + 1) * chunk). One warp per slot; also refreshes this handle's full row table.
+static __global__ void finalize_gathered_kernel(const FinalizeArgs a, const gnss_b200_acq_row* gathered, uint32_t world, uint32_t chunk, uint32_t n_slots)
+{
+    const uint32_t si = blockIdx.x;
+    const uint32_t slot = a.slots[si];
+    const int lane = threadIdx.x;
+    gnss_b200_acq_row* rows = a.rows + (size_t)slot * a.nD;
+    float best = 0.f;
+    uint32_t best_k = 0xffffffffu, best_i = 0;
+    for (uint32_t k = lane; k < a.nD; k += 32)
+        {
+            const uint32_t r = k / chunk, j = k - r * chunk;
+            const gnss_b200_acq_row row = gathered[((size_t)r * n_slots + si) * chunk + j];
+            rows[k] = row;
+            if (row.valid && (row.max_val > best || (row.max_val == best && best_k != 0xffffffffu && k < best_k)))
+                {
+                    best = row.max_val;
+                    best_k = k;
+                    best_i = row.max_idx;
+                }
+        }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const uint32_t ok = __shfl_xor_sync(0xffffffffu, best_k, o);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+            if (ob > best || (ob == best && ok < best_k))
+                {
+                    best = ob;
+                    best_k = ok;
+                    best_i = oi;
+                }
+        }
+    __syncwarp();
+    if (lane == 0)
+        {
+            if (best_k == 0xffffffffu)
+                {
+                    best_k = 0;
+                    best_i = 0;
+                }
+            gnss_b200_acq_result res;
+            res.peak = best;
+            res.code_phase = best_i;
+            res.doppler_index = best_k;
+            res.doppler_hz = -a.doppler_max + a.center[si] + (int32_t)a.doppler_step * (int32_t)best_k;  // :535
+            res.dwell_count = a.dwell_after[si];
+            res.second_peak = 0.f;
+            const uint32_t opp = (best_k + a.nD / 2) % a.nD;  // :533
+            const gnss_b200_acq_row ro = rows[opp];
+            const float per = ro.row_sum / (float)(int32_t)a.eff;
+            res.input_power = ro.valid ? (float)(((double)per / 2.0) / (double)a.dwell_after[si]) : nanf("");
+            res.test_statistic = best / res.input_power;  // :542
+            a.results[si] = res;
+        }
+}
+
 // ---- first_vs_second_peak_statistic (:546-612): second maximum of the best row outside the +-1 chip window ----
 struct SecondPeakArgs
 {

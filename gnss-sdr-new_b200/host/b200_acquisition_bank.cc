@@ -21,7 +21,7 @@ bool B200_Acquisition_Bank::Geometry::operator==(const Geometry& o) const
 {
     return fft_size == o.fft_size && consumed_samples == o.consumed_samples && doppler_max == o.doppler_max && doppler_step == o.doppler_step &&
            fs == o.fs && samples_per_chip == o.samples_per_chip && bit_transition == o.bit_transition && use_cfar == o.use_cfar &&
-           keep_grid == o.keep_grid && device == o.device && step2_bins == o.step2_bins && step2_hz == o.step2_hz && source_id == o.source_id;
+           keep_grid == o.keep_grid && device == o.device && step2_bins == o.step2_bins && step2_hz == o.step2_hz && source_id == o.source_id && n_devices == o.n_devices;
 }
 
 
@@ -64,7 +64,18 @@ std::shared_ptr<B200_Acquisition_Bank> B200_Acquisition_Bank::get(const Geometry
     cfg.max_slots = g_capacity;
     cfg.device = g.device;
     gnss_b200_acq* engine = nullptr;
-    if (gnss_b200_acq_create(&cfg, &engine) != GNSS_B200_OK)
+    gnss_b200_acq_group* group = nullptr;
+    if (g.n_devices > 1)
+        {
+            std::vector<int32_t> devices(g.n_devices);
+            for (uint32_t i = 0; i < g.n_devices; i++) devices[i] = g.device + static_cast<int32_t>(i);
+            if (gnss_b200_acq_group_create(&cfg, g.n_devices, devices.data(), &group) != GNSS_B200_OK)
+                {
+                    if (why != nullptr) *why = gnss_b200_last_error();
+                    return nullptr;
+                }
+        }
+    else if (gnss_b200_acq_create(&cfg, &engine) != GNSS_B200_OK)
         {
             if (why != nullptr) *why = gnss_b200_last_error();
             return nullptr;
@@ -73,13 +84,15 @@ std::shared_ptr<B200_Acquisition_Bank> B200_Acquisition_Bank::get(const Geometry
     if (g.step2_bins != 0 && gnss_b200_acq_create_step2(&cfg, g.step2_bins, g.step2_hz, &engine2) != GNSS_B200_OK)
         {
             if (why != nullptr) *why = gnss_b200_last_error();
-            gnss_b200_acq_destroy(engine);
+            if (engine != nullptr) gnss_b200_acq_destroy(engine);
+            if (group != nullptr) gnss_b200_acq_group_destroy(group);
             return nullptr;
         }
     std::shared_ptr<B200_Acquisition_Bank> bank(new B200_Acquisition_Bank(g));
     bank->d_engine = engine;
+    bank->d_group = group;
     bank->d_engine2 = engine2;
-    bank->d_num_doppler_bins = gnss_b200_acq_num_doppler_bins(engine);
+    bank->d_num_doppler_bins = group != nullptr ? gnss_b200_acq_group_num_doppler_bins(group) : gnss_b200_acq_num_doppler_bins(engine);
     bank->d_used.assign(g_capacity, 0);
     g_registry.emplace_back(bank);
     g_registry_geo.push_back(g);
@@ -90,6 +103,7 @@ std::shared_ptr<B200_Acquisition_Bank> B200_Acquisition_Bank::get(const Geometry
 B200_Acquisition_Bank::~B200_Acquisition_Bank()
 {
     if (d_engine != nullptr) gnss_b200_acq_destroy(d_engine);
+    if (d_group != nullptr) gnss_b200_acq_group_destroy(d_group);
     if (d_engine2 != nullptr) gnss_b200_acq_destroy(d_engine2);
 }
 
@@ -120,7 +134,9 @@ void B200_Acquisition_Bank::release_slot(int slot)
 bool B200_Acquisition_Bank::set_local_code(int slot, const std::complex<float>* code)
 {
     if (slot < 0 || code == nullptr) return false;
-    int rc = gnss_b200_acq_set_local_code(d_engine, static_cast<uint32_t>(slot), reinterpret_cast<const float*>(code));
+    const auto uslot = static_cast<uint32_t>(slot);
+    int rc = d_group != nullptr ? gnss_b200_acq_group_set_local_codes(d_group, 1, &uslot, reinterpret_cast<const float*>(code))
+                                : gnss_b200_acq_set_local_code(d_engine, uslot, reinterpret_cast<const float*>(code));
     if (rc == GNSS_B200_OK && d_engine2 != nullptr)  // d_fft_codes serves both grids in the reference (:727, :723 of the step-two loop)
         {
             rc = gnss_b200_acq_set_local_code(d_engine2, static_cast<uint32_t>(slot), reinterpret_cast<const float*>(code));
@@ -137,6 +153,7 @@ bool B200_Acquisition_Bank::set_local_code(int slot, const std::complex<float>* 
 bool B200_Acquisition_Bank::set_doppler_center(int slot, int32_t center_hz, int32_t bias_hz)
 {
     if (slot < 0) return false;
+    if (d_group != nullptr) return gnss_b200_acq_group_set_doppler_center(d_group, static_cast<uint32_t>(slot), center_hz, bias_hz) == GNSS_B200_OK;
     return gnss_b200_acq_set_doppler_center(d_engine, static_cast<uint32_t>(slot), center_hz, bias_hz) == GNSS_B200_OK;
 }
 
@@ -145,13 +162,15 @@ bool B200_Acquisition_Bank::reset(int slot)
 {
     if (slot < 0) return false;
     const bool ok2 = d_engine2 == nullptr || gnss_b200_acq_reset(d_engine2, static_cast<uint32_t>(slot)) == GNSS_B200_OK;
-    return gnss_b200_acq_reset(d_engine, static_cast<uint32_t>(slot)) == GNSS_B200_OK && ok2;
+    const int rc = d_group != nullptr ? gnss_b200_acq_group_reset(d_group, static_cast<uint32_t>(slot)) : gnss_b200_acq_reset(d_engine, static_cast<uint32_t>(slot));
+    return rc == GNSS_B200_OK && ok2;
 }
 
 
 bool B200_Acquisition_Bank::read_grid(int slot, float* out)
 {
     if (slot < 0 || out == nullptr) return false;
+    if (d_group != nullptr) return gnss_b200_acq_group_read_grid(d_group, static_cast<uint32_t>(slot), out) == GNSS_B200_OK;
     return gnss_b200_acq_read_grid(d_engine, static_cast<uint32_t>(slot), out) == GNSS_B200_OK;
 }
 
@@ -219,7 +238,10 @@ void B200_Acquisition_Bank::drain_locked(std::unique_lock<std::mutex>& lk)
                 }
             if (rc == GNSS_B200_OK)
                 {
-                    rc = gnss_b200_acq_dwell(step2 ? d_engine2 : d_engine, group[0]->samples, is_cshort ? 1 : 0, n, slots.data(), results.data());
+                    if (!step2 && d_group != nullptr)
+                        rc = gnss_b200_acq_group_dwell(d_group, group[0]->samples, is_cshort ? 1 : 0, n, slots.data(), results.data());
+                    else
+                        rc = gnss_b200_acq_dwell(step2 ? d_engine2 : d_engine, group[0]->samples, is_cshort ? 1 : 0, n, slots.data(), results.data());
                 }
 
             lk.lock();

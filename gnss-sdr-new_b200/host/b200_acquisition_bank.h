@@ -30,7 +30,9 @@ public:
         double fs;
         uint32_t samples_per_chip;
         bool bit_transition, use_cfar, keep_grid;
-        int device;
+        int device;           // first CUDA device of the bank
+        uint32_t n_devices;   // > 1: ONE search per dwell spread Doppler-major over devices [device, device + n_devices), the
+                              // row records exchanged GPU to GPU (gnss_b200_acq_group_*); needs use_cfar, gr_complex items
         uint32_t step2_bins;  // make_two_steps: num_doppler_bins_step2 (0 = no second engine)
         float step2_hz;       //                 doppler_step2
         uint32_t source_id;   // which sample stream feeds the blocks (RF_channel_ID / signal-source index): banks are never
@@ -83,6 +85,7 @@ private:
 
     Geometry d_geo;
     gnss_b200_acq* d_engine{nullptr};
+    gnss_b200_acq_group* d_group{nullptr};  // instead of d_engine when the bank spans several devices
     gnss_b200_acq* d_engine2{nullptr};  // second-step handle (gnss_b200_acq_create_step2), same slots
     uint32_t d_num_doppler_bins{0};
     mutable std::mutex d_mu;

@@ -255,6 +255,8 @@ void pcps_acquisition_b200::attach_engine()
     g.keep_grid = (d_acq_parameters.max_dwells > 1 && !d_acq_parameters.bit_transition_flag) || dumping();
     g.device = d_device;
     g.source_id = d_source_id;
+    // several GPUs per search only where the decision can be taken from row records (gnss_b200_acq_group_create)
+    g.n_devices = (d_num_devices > 1 && d_use_CFAR_algorithm_flag && !d_cshort) ? d_num_devices : 1U;
     g.step2_bins = d_acq_parameters.make_2_steps ? d_num_doppler_bins_step2 : 0U;
     g.step2_hz = d_acq_parameters.make_2_steps ? d_acq_parameters.doppler_step2 : 0.0F;
     std::string why;

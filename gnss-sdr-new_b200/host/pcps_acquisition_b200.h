@@ -65,6 +65,9 @@ public:
     void set_source_id(uint32_t source_id) { d_source_id = source_id; }
     // CUDA device the block's bank lives on (Acquisition_XX.device, default 0).
     void set_device(int device) { d_device = device; }
+    // Acquisition_XX.devices > 1: every dwell of the bank is ONE search spread over that many GPUs, first one = `device`
+    // (Doppler rows split over the devices, row records exchanged GPU to GPU). CFAR statistic and gr_complex items only.
+    void set_num_devices(uint32_t n_devices) { d_num_devices = n_devices; }
 
     // Same contract as gr::block::general_work (gr_vector_int = std::vector<int>, ...). Items consumed and events
     // published go through the two hooks below, which the gr::block shell binds to consume_each / message_port_pub.
@@ -124,6 +127,7 @@ private:
     uint32_t d_channel{0};
     uint32_t d_source_id{0};
     int d_device{0};
+    uint32_t d_num_devices{1};
     uint32_t d_dump_channel{0};
     uint32_t d_samplesPerChip{0};
     uint32_t d_doppler_step{0};

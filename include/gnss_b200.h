@@ -155,6 +155,50 @@ extern "C"
         uint32_t n_slots, const uint32_t* slots);
     GNSS_B200_API int gnss_b200_acq_sync(gnss_b200_acq* h, uint32_t n_slots, gnss_b200_acq_result* results);
 
+    /* ---- sharded search: Doppler rows of ONE search spread over several handles / GPUs / processes ------------------------
+       No counterpart in the reference (its only multi-GPU logic is `rand() % num_devices`, cuda_multicorrelator.cu:153); the
+       unit that is exchanged is the per-row record the reference reduces its grid to (:511-543).
+       With `world` shards, shard r is a handle created with row_begin = r * chunk, row_end = min(n_doppler, (r + 1) * chunk),
+       chunk = ceil(n_doppler / world). gnss_b200_acq_exchange_buffers allocates, on the handle's device, `d_send`
+       ([max_slots][chunk] records: what this shard contributes) and `d_recv` ([world][max_slots][chunk]: everybody's).
+       From then on every dwell leaves this shard's rows of the call's n_slots slots in d_send as [n_slots][chunk], on the
+       handle's stream. The caller moves them — NCCL all-gather of n_slots * chunk records per rank straight between the
+       device buffers, or cudaMemcpyPeerAsync into the root's d_recv + r * n_slots * chunk — and then
+       gnss_b200_acq_finalize_gathered_async decides every slot from d_recv on the device (CFAR statistic; same arithmetic
+       and tie rule as an unsharded handle) and queues the result copy; gnss_b200_acq_sync fetches it. */
+    GNSS_B200_API int gnss_b200_acq_exchange_buffers(gnss_b200_acq* h, uint32_t world, void** d_send, void** d_recv,
+        uint64_t* bytes_per_shard, uint32_t* rows_per_shard);
+    GNSS_B200_API int gnss_b200_acq_finalize_gathered_async(gnss_b200_acq* h, uint32_t n_slots);
+
+    /* The same inside ONE process that drives several GPUs (the reference receiver is one process): a group owns one engine
+       per listed device, splits the Doppler rows of every slot over them (Doppler-major: no forward transform is computed
+       twice and every device carries an equal share of every PRN), broadcasts each sample block host -> devices[0] -> the
+       others, lets every device reduce its rows, moves the row records device-to-device into devices[0]
+       (cudaMemcpyPeerAsync, NVLink) and decides there. Same slots / codes / Doppler-centre / reset / dwell semantics as a
+       single handle (gnss_b200_acq_*); cfg->device and the row range are ignored; CFAR statistic and gr_complex blocks only
+       (the first-vs-second-peak test needs the winning row's magnitudes on one device). Listing one device twice is legal. */
+    typedef struct gnss_b200_acq_group gnss_b200_acq_group;
+    GNSS_B200_API int gnss_b200_acq_group_create(const gnss_b200_acq_cfg* cfg, uint32_t n_devices, const int32_t* devices, gnss_b200_acq_group** out);
+    GNSS_B200_API int gnss_b200_acq_group_destroy(gnss_b200_acq_group* g);
+    GNSS_B200_API uint32_t gnss_b200_acq_group_num_doppler_bins(const gnss_b200_acq_group* g);
+    GNSS_B200_API uint32_t gnss_b200_acq_group_num_shards(const gnss_b200_acq_group* g);   /* min(n_devices, Doppler rows) */
+    GNSS_B200_API int gnss_b200_acq_group_set_local_codes(gnss_b200_acq_group* g, uint32_t n_slots, const uint32_t* slots, const float* codes_c64);
+    GNSS_B200_API int gnss_b200_acq_group_set_doppler_center(gnss_b200_acq_group* g, uint32_t slot, int32_t center_hz, int32_t bias_hz);
+    GNSS_B200_API int gnss_b200_acq_group_reset(gnss_b200_acq_group* g, uint32_t slot);
+    GNSS_B200_API int gnss_b200_acq_group_dwell(gnss_b200_acq_group* g, const void* samples, int is_cshort, uint32_t n_slots, const uint32_t* slots,
+        gnss_b200_acq_result* results);
+    GNSS_B200_API int gnss_b200_acq_group_read_grid(gnss_b200_acq_group* g, uint32_t slot, float* out);  /* [n_doppler][effective], keep_grid */
+    GNSS_B200_API uint64_t gnss_b200_acq_group_launch_count(const gnss_b200_acq_group* g);
+
+    /* A dwell as a CUDA graph: between _capture_begin and _capture_end exactly one gnss_b200_acq_dwell_device_async is
+       recorded instead of executed (after at least one ordinary dwell with the same slots, so that nothing allocates);
+       gnss_b200_acq_replay_async then re-issues all its launches with ONE call on the handle's stream. The device sample
+       pointer and the slot list are baked in; handles with a persistent grid are refused (dwell counters live on the host).
+       For small grids (BASELINE configs[0]) and sharded searches the per-launch overhead is a large part of a dwell. */
+    GNSS_B200_API int gnss_b200_acq_capture_begin(gnss_b200_acq* h);
+    GNSS_B200_API int gnss_b200_acq_capture_end(gnss_b200_acq* h);
+    GNSS_B200_API int gnss_b200_acq_replay_async(gnss_b200_acq* h);
+
     /* The accumulated magnitude grid of one slot, [n_doppler][effective_size] float32 (the content of the
        reference's d_magnitude_grid / MAT dump `acq_grid`, :433-434,:684). Requires keep_grid = 1. */
     GNSS_B200_API int gnss_b200_acq_read_grid(gnss_b200_acq* h, uint32_t slot, float* out);

@@ -329,6 +329,15 @@ class RefLibs:
         self.codes = C.CDLL(os.path.join(d, "libref_codes.so"))
         self.mc = C.CDLL(os.path.join(d, "libref_mc.so"))
         self.mc.ref_mc_real.argtypes = [_fp, c_i, _fp, c_i, _fp, c_i, c_f, c_f, c_f, c_f, c_f, c_f, c_i, c_i, _fp]
+        # the reference's AVX protokernels (timed baseline); only on hosts that have AVX
+        self.mc_avx = None
+        avx = os.path.join(d, "libref_mc_avx.so")
+        try:
+            if os.path.exists(avx) and " avx " in open("/proc/cpuinfo").read().replace("\n", " "):
+                self.mc_avx = C.CDLL(avx)
+                self.mc_avx.ref_mc_real.argtypes = self.mc.ref_mc_real.argtypes
+        except OSError:
+            self.mc_avx = None
         self.mc.ref_mc_cplx.argtypes = [_fp, c_i, _fp, c_i, _fp, c_i, c_f, c_f, c_f, c_f, _fp]
         t = self.trk = C.CDLL(os.path.join(d, "libref_trk.so"))
         t.ref_trk_loop_filter_run.argtypes = [c_f, c_f, c_i, c_i, c_f, _fp, c_i, _fp]
@@ -386,12 +395,12 @@ class RefLibs:
         return self._sampled(self.codes.ref_galileo_e1_sampled, prn, fs, int(fs / (1023000 / 4092)), int(pilot), int(cboc))
 
     def mc_real(self, sig, code, shifts, rem_carr, carr_step, carr_rate, rem_code, code_step, code_rate,
-                high_dyn=False, six_arg=False):
+                high_dyn=False, six_arg=False, simd=False):
         sig = np.ascontiguousarray(sig, dtype=np.complex64)
         code = np.ascontiguousarray(code, dtype=np.float32)
         shifts = np.ascontiguousarray(shifts, dtype=np.float32)
         out = np.zeros(shifts.size, dtype=np.complex64)
-        self.mc.ref_mc_real(_ptr(sig.view(np.float32)), sig.size, _ptr(code), code.size, _ptr(shifts), shifts.size,
+        (self.mc_avx if simd else self.mc).ref_mc_real(_ptr(sig.view(np.float32)), sig.size, _ptr(code), code.size, _ptr(shifts), shifts.size,
                             rem_carr, carr_step, carr_rate, rem_code, code_step, code_rate,
                             int(high_dyn), int(six_arg), _ptr(out.view(np.float32)))
         return out

@@ -8,6 +8,17 @@
  * config headers).
  */
 #define LV_HAVE_GENERIC 1
+#ifdef REF_SIMD_AVX
+/* the TIMED baseline flavour (_ref/libref_mc_avx.so): the reference's own AVX protokernels of the two kernels the real-code
+   tracking correlator spends its time in — what volk_gnsssdr_profile selects on an AVX host */
+#define LV_HAVE_AVX 1
+#include <immintrin.h> /* volk_gnsssdr_common.h's bit256 union names __m256 when LV_HAVE_AVX is set */
+#define REF_RESAMPLER_REAL volk_gnsssdr_32f_xn_resampler_32f_xn_u_avx
+#define REF_ROTATOR_REAL volk_gnsssdr_32fc_32f_rotator_dot_prod_32fc_xn_u_avx
+#else
+#define REF_RESAMPLER_REAL volk_gnsssdr_32f_xn_resampler_32f_xn_generic
+#define REF_ROTATOR_REAL volk_gnsssdr_32fc_32f_rotator_dot_prod_32fc_xn_generic
+#endif
 #include <volk_gnsssdr/volk_gnsssdr.h>
 #include "volk_gnsssdr_16ic_convert_32fc.h"
 #include "volk_gnsssdr_32f_index_max_32u.h"
@@ -32,7 +43,7 @@ void volk_gnsssdr_free(void* p) { free(p); }
 
 void refd_resampler_real(float** result, const float* code, float rem, float step, float* shifts, unsigned int len, int ntaps, unsigned int n)
 {
-    volk_gnsssdr_32f_xn_resampler_32f_xn_generic(result, code, rem, step, shifts, len, ntaps, n);
+    REF_RESAMPLER_REAL(result, code, rem, step, shifts, len, ntaps, n);
 }
 void refd_resampler_real_hd(float** result, const float* code, float rem, float step, float rate, float* shifts, unsigned int len, int ntaps, unsigned int n)
 {
@@ -44,7 +55,7 @@ void refd_resampler_cplx(void** result, const void* code, float rem, float step,
 }
 void refd_rotator_real(void* result, const void* in, const float* pi2, void* phase, const float** codes, int ntaps, unsigned int n)
 {
-    volk_gnsssdr_32fc_32f_rotator_dot_prod_32fc_xn_generic((lv_32fc_t*)result, (const lv_32fc_t*)in, lv_cmake(pi2[0], pi2[1]), (lv_32fc_t*)phase, codes, ntaps, n);
+    REF_ROTATOR_REAL((lv_32fc_t*)result, (const lv_32fc_t*)in, lv_cmake(pi2[0], pi2[1]), (lv_32fc_t*)phase, codes, ntaps, n);
 }
 void refd_rotator_real_hd(void* result, const void* in, const float* pi2, const float* pr2, void* phase, const float** codes, int ntaps, unsigned int n)
 {

@@ -474,3 +474,36 @@ def test_fixed_geometry_kernels_are_bit_identical_to_runtime_ones(tmp_path):
     assert sorted(a.files) == sorted(c.files) and len(a.files) == 24
     for k in a.files:
         assert np.array_equal(a[k], c[k]), k
+
+
+@pytest.mark.parametrize("n_shards", [2, 3, 8])
+def test_group_of_shards_equals_one_engine(b200, n_shards):
+    """gnss_b200_acq_group_*: one search split Doppler-major over several engines (several GPUs in production; here the same
+    device listed n times, which exercises the same pack -> device-to-device copy -> decide-on-the-root path). Every field of
+    every record must equal the unsharded engine's bit for bit — same rows, same tie rule, same input-power arithmetic —
+    including Doppler centres, several non-coherent dwells with a persistent grid, reset, and the gathered grid."""
+    geo, codes, iq, truth = synth.config_scene("C1", n_prn=6)
+    blocks = [iq] + [synth.make_iq(4000, geo["fs"], [dict(t, phase=0.3 * k) for t in truth], seed=50 + k) for k in range(2)]
+    one = _gpu_engine(b200, geo, 6, use_cfar=True, keep_grid=True)
+    grp = b200.PcpsAcquisitionGroupB200(geo["fft_size"], geo["consumed_samples"], geo["doppler_max"], geo["doppler_step"], geo["fs"],
+                                        geo["samples_per_chip"], 6, [0] * n_shards, keep_grid=True)
+    assert grp.n_doppler == one.n_doppler == 40 and grp.n_shards == n_shards
+    for e in (one, grp):
+        e.set_local_codes(np.arange(6), codes)
+        e.set_doppler_center(1, 750)
+        e.set_doppler_center(4, -1125)
+    sel = np.array([0, 1, 2, 3, 4, 5])
+    for k, blk in enumerate(blocks):
+        a = one.dwell(blk, sel)
+        g = grp.dwell(blk, sel)
+        assert g.tobytes() == a.tobytes(), k
+    assert np.array_equal(grp.read_grid(2), one.read_grid(2))
+    for e in (one, grp):
+        e.reset(3)
+    a = one.dwell(blocks[0], [3, 0])
+    g = grp.dwell(blocks[0], [3, 0])                      # a slot subset in another order
+    assert g.tobytes() == a.tobytes() and list(a["dwell_count"]) == [1, 4]
+    with pytest.raises(b200.B200Error):
+        b200.PcpsAcquisitionGroupB200(4000, 4000, 5000, 250, 4e6, 4, 2, [7, 99])      # no such devices
+    one.close()
+    grp.close()

@@ -60,3 +60,23 @@ def test_acquisition_on_the_second_device(two_devices, scene):
                          np.float32(r["peak"]).view(np.uint32)) for r in got])
         e.close()
     assert records[0] == records[1] == records[2]
+
+
+@pytest.mark.parametrize("scene,n_prn", [("C1", 8), ("C2", 8), ("C4_gal", 4)])
+def test_one_search_over_two_devices(two_devices, scene, n_prn):
+    """gnss_b200_acq_group_*: the Doppler rows of one search split over the two GPUs, sample block broadcast host -> GPU 0 ->
+    GPU 1, row records sent GPU 1 -> GPU 0 (cudaMemcpyPeerAsync), decision on GPU 0. Records bit-identical to one engine."""
+    b200 = two_devices
+    geo, codes, iq, _ = synth.config_scene(scene, n_prn=n_prn)
+    one = _gpu_engine(b200, geo, n_prn, use_cfar=True)
+    one.set_local_codes(np.arange(n_prn), codes[:n_prn])
+    want = one.dwell(iq, np.arange(n_prn))
+    for devices in ([0, 1], [1, 0]):
+        grp = b200.PcpsAcquisitionGroupB200(geo["fft_size"], geo["consumed_samples"], geo["doppler_max"], geo["doppler_step"], geo["fs"],
+                                            geo["samples_per_chip"], n_prn, devices)
+        grp.set_local_codes(np.arange(n_prn), codes[:n_prn])
+        for _ in range(3):
+            got = grp.dwell(iq, np.arange(n_prn))
+            assert got.tobytes() == want.tobytes(), devices
+        grp.close()
+    one.close()
