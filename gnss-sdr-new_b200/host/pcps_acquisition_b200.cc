@@ -13,6 +13,7 @@
 #include <cstring>
 #include <iostream>
 #include <stdexcept>
+#include <sstream>
 #include <thread>
 
 pcps_acquisition_b200_sptr pcps_make_acquisition_b200(const Acq_Conf& conf_)
@@ -45,30 +46,18 @@ pcps_acquisition_b200::pcps_acquisition_b200(const Acq_Conf& conf_)
     d_data_buffer.resize(d_consumed_samples);
     if (d_cshort) d_data_buffer_sc.resize(static_cast<size_t>(d_consumed_samples) * 2);
 
-    if (d_dump)  // :135-165 — split the path, default name, drop the extension, create the directory
+    if (d_dump)
         {
-            std::string dump_path;
-            if (d_dump_filename.find_last_of('/') != std::string::npos)
-                {
-                    const std::string dump_filename_ = d_dump_filename.substr(d_dump_filename.find_last_of('/') + 1);
-                    dump_path = d_dump_filename.substr(0, d_dump_filename.find_last_of('/'));
-                    d_dump_filename = dump_filename_;
-                }
-            else
-                {
-                    dump_path = std::string(".");
-                }
-            if (d_dump_filename.empty())
-                {
-                    d_dump_filename = "acquisition";
-                }
-            if (d_dump_filename.substr(1).find_last_of('.') != std::string::npos)
-                {
-                    d_dump_filename = d_dump_filename.substr(0, d_dump_filename.find_last_of('.'));
-                }
-            d_dump_filename = dump_path + '/' + d_dump_filename;
+            // Same result as the reference's string surgery (:135-165): directory part or ".", default stem "acquisition", the last
+            // extension dropped (a leading dot is not an extension), directory created; on failure dumping is switched off.
+            namespace fs = std::filesystem;
+            const fs::path given(d_dump_filename);
+            const fs::path dir = d_dump_filename.find('/') != std::string::npos ? fs::path(d_dump_filename.substr(0, d_dump_filename.find_last_of('/'))) : fs::path(".");
+            std::string stem = given.filename().empty() ? std::string("acquisition") : given.filename().stem().string();
+            if (stem.empty()) stem = given.filename().string();
+            d_dump_filename = dir.string() + '/' + stem;
             std::error_code ec;
-            std::filesystem::create_directories(dump_path, ec);
+            fs::create_directories(dir, ec);
             if (ec)
                 {
                     std::cerr << "GNSS-SDR cannot create dump file for the Acquisition block. Wrong permissions?\n";
@@ -375,19 +364,11 @@ void pcps_acquisition_b200::send_negative_acquisition()
 void pcps_acquisition_b200::dump_results(int32_t effective_fft_size)
 {
     d_dump_number++;
-    std::string filename = d_dump_filename;
-    filename.append("_");
-    filename.append(1, d_gnss_synchro->System);
-    filename.append("_");
-    filename.append(1, d_gnss_synchro->Signal[0]);
-    filename.append(1, d_gnss_synchro->Signal[1]);
-    filename.append("_ch_");
-    filename.append(std::to_string(d_channel));
-    filename.append("_");
-    filename.append(std::to_string(d_dump_number));
-    filename.append("_sat_");
-    filename.append(std::to_string(d_gnss_synchro->PRN));
-    filename.append(".mat");
+    // <prefix>_<System>_<Signal>_ch_<channel>_<n>_sat_<PRN>.mat — the pattern the reference's readers glob for (:408-423)
+    std::ostringstream name;
+    name << d_dump_filename << '_' << d_gnss_synchro->System << '_' << d_gnss_synchro->Signal[0] << d_gnss_synchro->Signal[1] << "_ch_" << d_channel << '_'
+         << d_dump_number << "_sat_" << d_gnss_synchro->PRN << ".mat";
+    const std::string filename = name.str();
 
     B200_Mat_Writer mat;
     if (!mat.open(filename))
@@ -485,94 +466,55 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
             lk.lock();  // :776-779
         }
 
-    if (!d_acq_parameters.bit_transition_flag)  // :781-829
+    // What one finished dwell means for the block (the reference spells this out twice, for searches with and without the
+    // bit-transition option, :781-866; the two differ only in that a bit-transition search never waits for another dwell).
+    //   detected, and this is a one-step search or already the narrow second step   -> Verdict::positive
+    //   detected in the coarse step of a two-step search                           -> Verdict::refine (re-arm around the coarse Doppler)
+    //   not detected and dwells left                                               -> Verdict::another_dwell
+    //   not detected and this was the last dwell                                   -> Verdict::negative
+    enum class Verdict
+    {
+        positive,
+        refine,
+        another_dwell,
+        negative
+    };
+    const bool detected = d_test_statistics > d_threshold;
+    const bool last_dwell = d_acq_parameters.bit_transition_flag || d_num_noncoherent_integrations_counter == d_acq_parameters.max_dwells;
+    const Verdict verdict = detected ? ((d_acq_parameters.make_2_steps && !d_step_two) ? Verdict::refine : Verdict::positive)
+                                     : (last_dwell ? Verdict::negative : Verdict::another_dwell);
+    switch (verdict)
         {
-            if (d_test_statistics > d_threshold)
-                {
-                    d_active = false;
-                    if (d_acq_parameters.make_2_steps)  // :786-803
-                        {
-                            if (d_step_two)
-                                {
-                                    send_positive_acquisition();
-                                    d_step_two = false;
-                                    d_state = 0;
-                                }
-                            else
-                                {
-                                    d_step_two = true;  // general_work re-arms the block around Acq_doppler_hz (:937-943)
-                                    d_num_noncoherent_integrations_counter = 0;
-                                    d_positive_acq = 0;
-                                    d_state = 0;
-                                    d_bank->reset(d_slot);  // counter == 1 on the next pass overwrites the grid (:735)
-                                }
-                            calculate_threshold();
-                        }
-                    else
-                        {
-                            send_positive_acquisition();
-                            d_state = 0;
-                        }
-                }
-            else
-                {
-                    d_buffer_count = 0;
-                    d_state = 1;
-                }
-            if (d_num_noncoherent_integrations_counter == d_acq_parameters.max_dwells)
-                {
-                    if (d_state != 0)
-                        {
-                            send_negative_acquisition();
-                        }
-                    d_state = 0;
-                    d_active = false;
-                    const bool was_step_two = d_step_two;  // :823-828
-                    d_step_two = false;
-                    if (was_step_two)
-                        {
-                            calculate_threshold();
-                        }
-                }
-        }
-    else  // :830-866
-        {
+        case Verdict::positive:
             d_active = false;
-            if (d_test_statistics > d_threshold)
+            send_positive_acquisition();
+            d_step_two = false;
+            d_state = 0;
+            if (d_acq_parameters.make_2_steps) calculate_threshold();  // back to the coarse grid's pfa
+            break;
+        case Verdict::refine:
+            d_active = false;
+            d_step_two = true;  // general_work re-arms the block around Acq_doppler_hz
+            d_num_noncoherent_integrations_counter = 0U;
+            d_positive_acq = 0;
+            d_state = 0;
+            d_bank->reset(d_slot);  // the first narrow dwell starts a fresh grid
+            calculate_threshold();  // the narrow grid's pfa
+            break;
+        case Verdict::another_dwell:
+            d_buffer_count = 0U;
+            d_state = 1;
+            break;
+        case Verdict::negative:
+            send_negative_acquisition();
+            d_state = 0;
+            d_active = false;
+            if (d_step_two)
                 {
-                    if (d_acq_parameters.make_2_steps)  // :835-849
-                        {
-                            if (d_step_two)
-                                {
-                                    send_positive_acquisition();
-                                    d_step_two = false;
-                                    d_state = 0;
-                                }
-                            else
-                                {
-                                    d_step_two = true;
-                                    d_num_noncoherent_integrations_counter = 0U;
-                                    d_state = 0;
-                                }
-                            calculate_threshold();
-                        }
-                    else
-                        {
-                            send_positive_acquisition();
-                            d_state = 0;
-                        }
-                }
-            else
-                {
-                    d_state = 0;
-                    const bool was_step_two = d_step_two;  // :859-864
                     d_step_two = false;
-                    if (was_step_two)
-                        {
-                            calculate_threshold();
-                        }
-                    send_negative_acquisition();
+                    calculate_threshold();
                 }
+            break;
         }
     d_worker_active = false;
 
@@ -589,7 +531,82 @@ void pcps_acquisition_b200::acquisition_core(uint64_t samp_count)
 }
 
 
-// :912-1050
+// general_work (:912-1050) as four small steps; what each does to the sample counter and to the scheduler (consume_each) is the
+// reference's, because sample stamps and hand-over to tracking depend on it.
+
+// The block is idle, or a worker thread is searching: items flow past (unless blocking_on_standby), and a pending second step /
+// the fork's repeat mode re-arm the block.
+void pcps_acquisition_b200::pass_items_while_idle(int n_items)
+{
+    const bool dwells_exhausted = d_num_noncoherent_integrations_counter == d_acq_parameters.max_dwells;
+    if (!d_acq_parameters.blocking_on_standby && (!d_active || dwells_exhausted))  // not while a non-coherent integration is in progress
+        {
+            d_sample_counter += static_cast<uint64_t>(n_items);
+            consume_each(n_items);
+        }
+    if (d_step_two)
+        {
+            d_doppler_center_step_two = static_cast<float>(d_gnss_synchro->Acq_doppler_hz);  // centre of the narrow grid
+            d_state = 0;
+            d_active = true;
+        }
+    if (d_step_repeat) d_active = true;
+}
+
+// State 0: a search begins — forget the previous answer (not in repeat mode), drop this call's items.
+void pcps_acquisition_b200::begin_search(int n_items)
+{
+    if (!d_step_repeat) forget_last_answer();
+    d_mag = 0.0;
+    d_buffer_count = 0U;
+    d_state = 1;
+    if (!d_acq_parameters.blocking_on_standby)
+        {
+            d_sample_counter += static_cast<uint64_t>(n_items);
+            consume_each(n_items);
+        }
+}
+
+// State 1: copy items into the dwell buffer. The fill level is tested BEFORE this call's items are added (as the reference
+// does), so the search starts one call after the buffer filled.
+void pcps_acquisition_b200::fill_dwell_buffer(int n_items, const void* items)
+{
+    const auto offered = static_cast<uint32_t>(n_items);
+    const uint32_t room = d_consumed_samples - std::min(d_buffer_count, d_consumed_samples);
+    const uint32_t take = std::min(offered, room);
+    if (d_cshort)
+        {
+            const auto* in = static_cast<const int16_t*>(items);
+            std::copy_n(in, static_cast<size_t>(take) * 2, d_data_buffer_sc.begin() + static_cast<size_t>(d_buffer_count) * 2);
+        }
+    else
+        {
+            std::copy_n(static_cast<const std::complex<float>*>(items), take, d_data_buffer.begin() + d_buffer_count);
+        }
+    if (d_buffer_count >= d_consumed_samples) d_state = 2;
+    d_buffer_count += take;
+    d_sample_counter += static_cast<uint64_t>(take);
+    consume_each(static_cast<int>(take));
+}
+
+// State 2: run acquisition_core on the buffered dwell — inline, or on a detached worker thread when not blocking.
+void pcps_acquisition_b200::start_search(std::unique_lock<std::recursive_mutex>& lk)
+{
+    if (d_acq_parameters.blocking)
+        {
+            lk.unlock();
+            acquisition_core(d_sample_counter);
+            lk.lock();
+        }
+    else
+        {
+            d_worker_active = true;
+            std::thread(&pcps_acquisition_b200::acquisition_core, this, d_sample_counter).detach();
+        }
+    consume_each(0);
+    d_buffer_count = 0U;
+}
+
 int pcps_acquisition_b200::general_work(int noutput_items, std::vector<int>& ninput_items, std::vector<const void*>& input_items,
     std::vector<void*>& output_items)
 {
@@ -597,105 +614,24 @@ int pcps_acquisition_b200::general_work(int noutput_items, std::vector<int>& nin
     std::unique_lock<std::recursive_mutex> lk(d_setlock);
     if (!d_active || d_worker_active)
         {
-            // do not consume samples while a non-coherent integration is in progress (:931-937)
-            const bool consume_samples = ((!d_active) || (d_active && (d_num_noncoherent_integrations_counter == d_acq_parameters.max_dwells)));
-            if ((!d_acq_parameters.blocking_on_standby) && consume_samples)
-                {
-                    d_sample_counter += static_cast<uint64_t>(ninput_items[0]);
-                    consume_each(ninput_items[0]);
-                }
-            if (d_step_two)  // :937-943 — the narrow grid is centred on the coarse Doppler, then the block re-arms itself
-                {
-                    d_doppler_center_step_two = static_cast<float>(d_gnss_synchro->Acq_doppler_hz);
-                    d_state = 0;
-                    d_active = true;
-                }
-            if (d_step_repeat)  // :944-947 — the fork's repeat mode never goes idle after the first detection
-                {
-                    d_active = true;
-                }
+            pass_items_while_idle(ninput_items[0]);
             return 0;
         }
+    if (d_state == 0)
+        begin_search(ninput_items[0]);
+    else if (d_state == 1)
+        fill_dwell_buffer(ninput_items[0], input_items[0]);
+    else if (d_state == 2)
+        start_search(lk);
 
-    switch (d_state)
+    // positive acquisitions waiting for the monitor port
+    if (!d_acq_parameters.enable_monitor_output || output_items.empty() || d_monitor_queue.empty()) return 0;
+    // the reference hands object i to the first item of output buffer i (:1035-1044); beyond the connected buffers that is out
+    // of bounds there, here the rest stays queued for the next call
+    size_t produced = 0;
+    for (; !d_monitor_queue.empty() && produced < output_items.size(); d_monitor_queue.pop(), produced++)
         {
-        case 0:  // :953-972 — restart
-            {
-                if (!d_step_repeat)
-                    {
-                        forget_last_answer();
-                    }
-                d_mag = 0.0;
-                d_state = 1;
-                d_buffer_count = 0U;
-                if (!d_acq_parameters.blocking_on_standby)
-                    {
-                        d_sample_counter += static_cast<uint64_t>(ninput_items[0]);
-                        consume_each(ninput_items[0]);
-                    }
-                break;
-            }
-        case 1:  // :973-1011 — fill the dwell buffer
-            {
-                const uint32_t avail = static_cast<uint32_t>(ninput_items[0]);
-                const uint32_t buff_increment = (avail + d_buffer_count <= d_consumed_samples) ? avail : d_consumed_samples - d_buffer_count;
-                if (d_cshort)
-                    {
-                        const auto* in = static_cast<const int16_t*>(input_items[0]);
-                        std::copy(in, in + static_cast<size_t>(buff_increment) * 2, d_data_buffer_sc.begin() + static_cast<size_t>(d_buffer_count) * 2);
-                    }
-                else
-                    {
-                        const auto* in = static_cast<const std::complex<float>*>(input_items[0]);
-                        std::copy(in, in + buff_increment, d_data_buffer.begin() + d_buffer_count);
-                    }
-                // the reference tests the fill level BEFORE adding this call's samples (:1003-1007), so the state
-                // changes one call after the buffer filled; kept, because the sample stamp depends on it
-                if (d_buffer_count >= d_consumed_samples)
-                    {
-                        d_state = 2;
-                    }
-                d_buffer_count += buff_increment;
-                d_sample_counter += static_cast<uint64_t>(buff_increment);
-                consume_each(static_cast<int>(buff_increment));
-                break;
-            }
-        case 2:  // :1012-1029 — run the search
-            {
-                if (d_acq_parameters.blocking)
-                    {
-                        lk.unlock();
-                        acquisition_core(d_sample_counter);
-                        lk.lock();
-                    }
-                else
-                    {
-                        d_worker_active = true;
-                        std::thread worker(&pcps_acquisition_b200::acquisition_core, this, d_sample_counter);
-                        worker.detach();
-                    }
-                consume_each(0);
-                d_buffer_count = 0U;
-                break;
-            }
-        default:
-            break;
+            *static_cast<Gnss_Synchro*>(output_items[produced]) = d_monitor_queue.front();
         }
-
-    // :1032-1047 — monitor output
-    if (d_acq_parameters.enable_monitor_output && !output_items.empty())
-        {
-            auto** out = reinterpret_cast<Gnss_Synchro**>(&output_items[0]);
-            if (!d_monitor_queue.empty())
-                {
-                    const int num_gnss_synchro_objects = static_cast<int>(d_monitor_queue.size());
-                    for (int i = 0; i < num_gnss_synchro_objects; ++i)
-                        {
-                            *out[i] = d_monitor_queue.front();
-                            d_monitor_queue.pop();
-                        }
-                    return num_gnss_synchro_objects;
-                }
-        }
-    return 0;
+    return static_cast<int>(produced);
 }

@@ -87,6 +87,10 @@ private:
     explicit pcps_acquisition_b200(const Acq_Conf& conf_);
 
     void acquisition_core(uint64_t samp_count);
+    void pass_items_while_idle(int n_items);
+    void begin_search(int n_items);
+    void fill_dwell_buffer(int n_items, const void* items);
+    void start_search(std::unique_lock<std::recursive_mutex>& lk);
     void send_negative_acquisition();
     void send_positive_acquisition();
     bool is_fdma();
