@@ -322,6 +322,7 @@ def run_ours(args):
         eng.profile(True)
         for _ in range(5):
             flush_l2()
+            torch.cuda.synchronize()   # the flush runs on torch's stream: keep it out of the engine stream's first kernel
             step_device()
         prof_steps = 5
     else:

@@ -1034,11 +1034,14 @@ extern "C"
 //
 // In host code `g_mc_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is asked for
 // with cudaGetSymbolAddress once per device, with that device current, and only that pointer is handed to kernels.
-// Every call on a device shares the array and finds the previous call's contents in it: the tickets are cleared on the
-// stream before each launch, the parameter blocks and shifts are rewritten, the partials are fully overwritten before
-// they are read. Two calls whose GPU work overlaps (different streams, or different host threads) race on it.
+// Every call on a device shares the array and finds the previous call's contents in it: a fill kernel rewrites the parameter
+// blocks and shifts and clears the tickets on the stream before each launch, the partials are fully overwritten before they
+// are read. Two calls whose GPU work overlaps (different streams, or different host threads) race on it.
+// The call issues kernel launches only (no memcpy / memset nodes, no host pointer outlives the call), so it may be recorded
+// under stream capture and replayed (tests/test_zz_no_alloc.py does): a replay re-runs the SAME parameters on whatever the
+// caller's device buffers hold then. The first call on a device resolves the scratch address: make it before capturing.
 // ------------------------------------------------------------------------------------------------------------------
-namespace
+namespace b200_noalloc  // (a named namespace: nvcc cannot tell a kernel of a second anonymous namespace in this file from the first)
 {
 constexpr uint32_t kNoAllocMaxChannels = GNSS_B200_MC_NOALLOC_MAX_CHANNELS;
 constexpr uint32_t kNoAllocMaxTaps = GNSS_B200_MC_NOALLOC_MAX_TAPS;
@@ -1061,6 +1064,29 @@ static_assert(kNoAllocScratchBytes < 160 * 1024, "keep the resident scratch mode
 
 static __device__ __align__(256) unsigned char g_mc_noalloc_scratch[kNoAllocScratchBytes];
 
+// Parameter blocks and tap shifts travel as a by-value kernel argument (copied into the launch, or into the graph node under
+// stream capture) and a tiny kernel writes them into the resident scratch: no host-memory copy node, nothing the caller has to
+// keep alive after the call returns. 16 channels per launch keeps the argument under the 4 KB every driver accepts.
+constexpr uint32_t kNoAllocFillChannels = 16;
+struct NoAllocFill
+{
+    ChanParams cp[kNoAllocFillChannels];
+    float shifts[kNoAllocFillChannels * kNoAllocMaxTaps];
+    uint32_t first, count, n_taps, pad;
+};
+static_assert(sizeof(NoAllocFill) <= 4000, "kernel argument size");
+
+__global__ void noalloc_fill_kernel(const __grid_constant__ NoAllocFill f, NoAllocScratch* scr)
+{
+    const uint32_t t = threadIdx.x;
+    if (t < f.count)
+        {
+            scr->params[f.first + t] = f.cp[t];
+            scr->tickets[f.first + t] = 0u;  // must start at zero whatever the last call left
+        }
+    for (uint32_t i = t; i < f.count * f.n_taps; i += blockDim.x) scr->shifts[(size_t)f.first * f.n_taps + i] = f.shifts[i];
+}
+
 std::mutex g_noalloc_mu;
 NoAllocScratch* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
 
@@ -1079,7 +1105,8 @@ int noalloc_scratch(int device, NoAllocScratch** out)
     *out = g_noalloc_ptr[device];
     return GNSS_B200_OK;
 }
-}  // namespace
+}  // namespace b200_noalloc
+using namespace b200_noalloc;
 
 extern "C"
 {
@@ -1099,8 +1126,18 @@ extern "C"
                     "mc_correlate_noalloc: channel %u: %u samples, at most %u per call", i, chans[i].n_samples, kNoAllocMaxSamples);
                 max_n = std::max(max_n, chans[i].n_samples);
             }
+        int caller_device = -1;
+        cudaGetDevice(&caller_device);
         int rc = select_device(device);
         if (rc) return rc;
+        struct RestoreDevice  // the caller's current device is the caller's business
+        {
+            int d;
+            ~RestoreDevice()
+            {
+                if (d >= 0) cudaSetDevice(d);
+            }
+        } restore{caller_device};
         NoAllocScratch* scr = nullptr;
         rc = noalloc_scratch(device, &scr);
         if (rc) return rc;
@@ -1116,37 +1153,43 @@ extern "C"
             }
         splits = std::max(1u, std::min(splits, kNoAllocMaxCtas / n_ch));
 
-        // per-channel constants (cpu_multicorrelator_real_codes.cc:114-119), on the stack: nothing is allocated
-        ChanParams cp[kNoAllocMaxChannels];
-        for (uint32_t i = 0; i < n_ch; i++)
+        // per-channel constants (cpu_multicorrelator_real_codes.cc:114-119) go out as kernel arguments, 16 channels at a time
+        for (uint32_t first = 0; first < n_ch; first += kNoAllocFillChannels)
             {
-                const gnss_b200_mc_noalloc_chan& a = chans[i];
-                ChanParams& p = cp[i];
-                std::memset(&p, 0, sizeof(p));
-                p.sig = static_cast<const float2*>(a.d_sig_c64);
-                p.code = a.d_code;
-                p.code_len = a.code_len;
-                p.n = a.n_samples;
-                p.rem_code = a.rem_code_phase_chips;
-                p.code_step = a.code_step_chips;
-                p.code_rate = 0.f;
-                float s0, c0;
-                sincosf(a.rem_carr_phase_rad, &s0, &c0);
-                p.p0_re = c0;
-                p.p0_im = -s0;
-                float inc_re, inc_im;
-                sincosf(-a.carr_step_rad, &inc_im, &inc_re);  // the rounded per-sample phasor; prep_kernel derives theta from it
-                p.theta = 0.0;
-                p.wb_re = inc_re;
-                p.wb_im = inc_im;
-                p.rate_arg = 0.f;
-                p.flags = 0u;
-                p.shifts_off = i * n_taps;
+                NoAllocFill f;
+                std::memset(&f, 0, sizeof(f));
+                f.first = first;
+                f.count = std::min(kNoAllocFillChannels, n_ch - first);
+                f.n_taps = n_taps;
+                for (uint32_t j = 0; j < f.count; j++)
+                    {
+                        const uint32_t i = first + j;
+                        const gnss_b200_mc_noalloc_chan& a = chans[i];
+                        ChanParams& p = f.cp[j];
+                        p.sig = static_cast<const float2*>(a.d_sig_c64);
+                        p.code = a.d_code;
+                        p.code_len = a.code_len;
+                        p.n = a.n_samples;
+                        p.rem_code = a.rem_code_phase_chips;
+                        p.code_step = a.code_step_chips;
+                        p.code_rate = 0.f;
+                        float s0, c0;
+                        sincosf(a.rem_carr_phase_rad, &s0, &c0);
+                        p.p0_re = c0;
+                        p.p0_im = -s0;
+                        float inc_re, inc_im;
+                        sincosf(-a.carr_step_rad, &inc_im, &inc_re);  // the rounded per-sample phasor; prep_kernel derives theta from it
+                        p.theta = 0.0;
+                        p.wb_re = inc_re;
+                        p.wb_im = inc_im;
+                        p.rate_arg = 0.f;
+                        p.flags = 0u;
+                        p.shifts_off = i * n_taps;
+                        std::memcpy(&f.shifts[(size_t)j * n_taps], shifts + (size_t)i * n_taps, sizeof(float) * n_taps);
+                    }
+                noalloc_fill_kernel<<<1, 256, 0, st>>>(f, scr);
+                B200_CUDA(cudaGetLastError());
             }
-        // pageable host memory: the runtime stages these copies before it returns, so the stack buffers may go away
-        B200_CUDA(cudaMemcpyAsync(scr->params, cp, sizeof(ChanParams) * n_ch, cudaMemcpyHostToDevice, st));
-        B200_CUDA(cudaMemcpyAsync(scr->shifts, shifts, sizeof(float) * (size_t)n_ch * n_taps, cudaMemcpyHostToDevice, st));
-        B200_CUDA(cudaMemsetAsync(scr->tickets, 0, sizeof(uint32_t) * n_ch, st));  // must start at zero whatever the last call left
         prep_kernel<<<(n_ch + 127) / 128, 128, 0, st>>>(scr->params, n_ch);
         B200_CUDA(cudaGetLastError());
         B200_CUDA(mc::launch_real_plain(false, n_ch, splits, kNoAllocSmemElems, st, scr->params, scr->shifts, scr->shift_samples, scr->partials, scr->tickets,

@@ -384,6 +384,10 @@ extern "C"
      * Limits (GNSS_B200_ERR_INVALID with a message beyond them): GNSS_B200_MC_NOALLOC_MAX_CHANNELS channels,
      * GNSS_B200_MC_NOALLOC_MAX_TAPS taps, GNSS_B200_MC_NOALLOC_MAX_SAMPLES samples per channel and call.
      * All calls on one GPU share the scratch: calls whose GPU work overlaps (two streams, two threads) RACE — serialise them.
+     * The call issues kernel launches only — parameters and shifts travel as by-value kernel arguments, no host pointer
+     * outlives the call — so it may be recorded under stream capture and the graph replayed (the replay re-runs the same
+     * parameters on whatever the caller's device buffers hold then). Make the first call on a device before capturing (it
+     * resolves the scratch address). The caller's current device is restored on return.
      * ------------------------------------------------------------------------------------------- */
 #define GNSS_B200_MC_NOALLOC_MAX_CHANNELS 64u
 #define GNSS_B200_MC_NOALLOC_MAX_TAPS 16u

@@ -90,6 +90,44 @@ def test_noalloc_entry_point_matches_the_existing_one_twice_in_a_row(b200):
         assert grew <= 0, "device memory in use grew by %d bytes across the call" % grew
 
 
+def test_noalloc_entry_point_against_the_oracle_and_under_graph_capture(b200, oracle):
+    """(1) directly against the oracle (not only against the handle-based entry point); (2) recorded under CUDA stream capture
+    and replayed twice on NEW sample data in the caller's buffers: the call issues kernels only (parameters travel as by-value
+    kernel arguments), so the graph holds no pointer into this process's host memory."""
+    import torch
+    rng = np.random.default_rng(77)
+    n_ch, n, ntaps = 20, 8000, 5           # 20 channels: two by-value parameter launches (16 + 4)
+    codes, sigs, args, shifts = _scene(rng, n_ch, n, ntaps)
+    d_out = torch.full((2 * n_ch * ntaps,), float("nan"), dtype=torch.float32, device="cuda")
+    got, _ = _noalloc(b200, torch, codes, sigs, args, shifts, d_out)
+    for c in range(n_ch):
+        want = oracle.mc_real(sigs[c], codes[c], shifts[c], float(args[c, 0]), float(args[c, 1]), 0.0, float(args[c, 2]), float(args[c, 3]), 0.0)
+        assert np.abs(got[c] - want).max() <= RTOL * np.abs(want).max(), c
+    # capture: the caller's device buffers are fixed, their CONTENT changes between replays
+    d_sig = [torch.from_numpy(s.view(np.float32).copy()).cuda() for s in sigs]
+    d_code = [torch.from_numpy(c.copy()).cuda() for c in codes]
+    chans = [dict(d_sig=d_sig[c].data_ptr(), d_code=d_code[c].data_ptr(), code_len=codes[c].size, n_samples=n, rem_carr=args[c, 0],
+                  carr_step=args[c, 1], rem_code=args[c, 2], code_step=args[c, 3]) for c in range(n_ch)]
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    torch.cuda.synchronize()
+    with torch.cuda.graph(graph, stream=side):
+        b200.mc_correlate_noalloc(0, side.cuda_stream, chans, shifts, d_out.data_ptr())
+    for rep in range(2):
+        new = [(s * np.exp(1j * 0.3 * (rep + 1)) + np.float32(0.01 * rep)).astype(np.complex64) for s in sigs]
+        for c in range(n_ch):
+            d_sig[c].copy_(torch.from_numpy(new[c].view(np.float32).copy()))
+        d_out.fill_(float("nan"))
+        torch.cuda.synchronize()
+        graph.replay()
+        torch.cuda.synchronize()
+        out = d_out.cpu().numpy().view(np.complex64).reshape(n_ch, ntaps)
+        for c in (0, 7, 19):
+            want = oracle.mc_real(new[c], codes[c], shifts[c], float(args[c, 0]), float(args[c, 1]), 0.0, float(args[c, 2]), float(args[c, 3]), 0.0)
+            assert np.abs(out[c] - want).max() <= RTOL * np.abs(want).max(), (rep, c)
+    assert torch.cuda.current_device() == 0
+
+
 def test_noalloc_entry_point_rejects_sizes_beyond_the_scratch(b200):
     import torch
     d = torch.zeros(64, dtype=torch.float32, device="cuda")
