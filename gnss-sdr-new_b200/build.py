@@ -56,6 +56,7 @@ def build_host(force=False):
     build(force=False)
     srcs = [os.path.join(HOST_DIR, f) for f in HOST_SOURCES]
     deps = srcs + [os.path.join(HOST_DIR, f) for f in os.listdir(HOST_DIR) if f.endswith(".h")] + [LIB, HOST_TEST_SRC]
+    deps += [os.path.join(HOST_DIR, "stubs", f) for f in os.listdir(os.path.join(HOST_DIR, "stubs")) if f.endswith(".h")]
     if not force and os.path.exists(HOST_LIB) and os.path.exists(HOST_TEST_BIN) and \
             all(os.path.getmtime(d) <= min(os.path.getmtime(HOST_LIB), os.path.getmtime(HOST_TEST_BIN)) for d in deps):
         return HOST_LIB, HOST_TEST_BIN
@@ -67,7 +68,36 @@ def build_host(force=False):
     return HOST_LIB, HOST_TEST_BIN
 
 
+INTEGRATION_DIR = os.path.join(HERE, "..", "integration")
+ADAPTER_TEST_SRC = os.path.join(HERE, "..", "tests", "host", "adapter_test.cc")
+ADAPTER_TEST_BIN = os.path.join(HERE, "..", "tests", "host", "adapter_test")
+
+
+def build_integration(force=False):
+    """The sources a maintainer adds to the GNSS-SDR tree (integration/src: gr::block shell, the three adapters, the factory
+    arms), compiled with -Wall -Wextra -Werror against the stand-in headers of integration/stubs/, and the harness that drives
+    an adapter through Channel's call order (tests/host/adapter_test.cc)."""
+    build_host(force=False)
+    srcs = []
+    for root, _, files in os.walk(os.path.join(INTEGRATION_DIR, "src")):
+        srcs += [os.path.join(root, f) for f in sorted(files) if f.endswith(".cc")]
+    srcs.append(os.path.join(INTEGRATION_DIR, "stubs", "acq_conf_stub.cc"))
+    deps = list(srcs) + [ADAPTER_TEST_SRC, HOST_LIB]
+    for root, _, files in os.walk(INTEGRATION_DIR):
+        deps += [os.path.join(root, f) for f in files if f.endswith(".h")]
+    if not force and os.path.exists(ADAPTER_TEST_BIN) and all(os.path.getmtime(d) <= os.path.getmtime(ADAPTER_TEST_BIN) for d in deps):
+        return ADAPTER_TEST_BIN
+    inc = ["-I", os.path.join(HERE, "..", "include"), "-I", HOST_DIR, "-I", os.path.join(HOST_DIR, "stubs"), "-I", os.path.join(INTEGRATION_DIR, "stubs")]
+    for sub in ("algorithms/acquisition/gnuradio_blocks", "algorithms/acquisition/adapters", "core/receiver"):
+        inc += ["-I", os.path.join(INTEGRATION_DIR, "src", sub)]
+    cmd = ["g++", "-std=c++20", "-O2", "-Wall", "-Wextra", "-Werror", "-pthread", "-DB200_HOST_STANDALONE"] + inc + ["-o", ADAPTER_TEST_BIN, ADAPTER_TEST_SRC] + srcs + \
+          ["-L", HERE, "-lgnss_b200_host", "-lgnss_b200", "-Wl,-rpath,$ORIGIN/../../gnss-sdr-new_b200"]
+    subprocess.run(cmd, check=True)
+    return ADAPTER_TEST_BIN
+
+
 if __name__ == "__main__":
     import sys
     print(build(force=True, verbose="-v" in sys.argv))
     print(build_host(force=True))
+    print(build_integration(force=True))

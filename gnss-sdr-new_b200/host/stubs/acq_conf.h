@@ -11,9 +11,16 @@
 #include <cstdint>
 #include <string>
 
+class ConfigurationInterface;
+
 class Acq_Conf
 {
 public:
+    // Reads the Acquisition_XX.* / GNSS-SDR.* keys and derives the per-rate members, as acq_conf.cc:24-119 does. Only the
+    // integration sources call it; defined in integration/stubs/acq_conf_stub.cc for builds outside the GNSS-SDR tree.
+    void SetFromConfiguration(const ConfigurationInterface* configuration, const std::string& role, double chip_rate, double opt_freq);
+    uint32_t chips_per_second = 1023000;
+
     // --- input stream -------------------------------------------------------------------------------------
     int64_t fs_in = 4000000;                           // GNSS-SDR.internal_fs_sps: the UNDECIMATED rate, also with the resampler on [Hz]
     int64_t resampled_fs = 0;                          // rate of the items the block receives: fs_in, or fs_in / resampler_ratio

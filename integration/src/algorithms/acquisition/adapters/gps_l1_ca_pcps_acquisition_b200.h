@@ -1,0 +1,21 @@
+/*
+ * gps_l1_ca_pcps_acquisition_b200.h — AcquisitionInterface adapter: GpsL1CaPcpsAcquisition on the B200 engine.
+ * Selected by Acquisition_XX.implementation=GPS_L1_CA_PCPS_Acquisition_B200 (gnss_block_factory_b200.cc).
+ * SPDX-License-Identifier: GPL-3.0-or-later
+ */
+#ifndef GNSS_SDR_GPS_L1_CA_PCPS_ACQUISITION_B200_H
+#define GNSS_SDR_GPS_L1_CA_PCPS_ACQUISITION_B200_H
+
+#include "pcps_acquisition_b200_adapter.h"
+#include <string>
+
+class ConfigurationInterface;
+
+class GpsL1CaPcpsAcquisitionB200 : public PcpsAcquisitionB200Adapter
+{
+public:
+    GpsL1CaPcpsAcquisitionB200(const ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams,
+        uint32_t source_id = 0);
+};
+
+#endif  // GNSS_SDR_GPS_L1_CA_PCPS_ACQUISITION_B200_H

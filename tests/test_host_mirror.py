@@ -604,3 +604,80 @@ def test_symbol_synchronisation_on_epoch_records(driver, b200, tmp_path, case):
     if case.startswith("gps_l1_ca"):
         # the first symbols after the preamble are whole bits: 20 prompts of one sign (inverted stream: flag set, sign kept)
         assert all(abs(abs(g[1]) - 20000.0) < 1500.0 for g in got[:3]) and bool(got[0][4]) == case.endswith("inverted")
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# integration/: the adapters, the gr::block shell and the factory arms a maintainer adds to the GNSS-SDR tree
+# ------------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def adapter_driver():
+    spec = importlib.util.spec_from_file_location("b200_build", os.path.join(ROOT, "gnss-sdr-new_b200", "build.py"))
+    bld = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bld)
+    return bld.build_integration()
+
+
+def _write_adapter_input(path, fs, doppler_max, doppler_step, pfa, coherent_ms, which, prn, rf_channel, code, stream):
+    with open(path, "wb") as f:
+        f.write(struct.pack("<qiIfIIII", int(fs), int(doppler_max), int(doppler_step), float(pfa), int(coherent_ms), int(which), int(prn), int(rf_channel)))
+        f.write(struct.pack("<I", code.size))
+        f.write(np.ascontiguousarray(code, dtype=np.complex64).tobytes())
+        f.write(struct.pack("<I", stream.size))
+        f.write(np.ascontiguousarray(stream, dtype=np.complex64).tobytes())
+
+
+def _read_adapter_output(path):
+    ev, delay, dop, stamp, consumed, gen_calls, mag = struct.unpack("<iddQQii", open(path, "rb").read())
+    return dict(event=ev, delay=delay, doppler=dop, stamp=stamp, consumed=consumed, generator_calls=gen_calls, mag=mag)
+
+
+def test_integration_sources_compile_against_the_interface_stubs(adapter_driver):
+    """integration/src/** (gr::block shell, adapter base + GPS L1 C/A / Galileo E1 / BeiDou B1I adapters, factory arms) build with
+    -Wall -Wextra -Werror against stand-ins of the reference's interfaces (integration/stubs/) — runs on the CPU box."""
+    assert os.path.exists(adapter_driver)
+    patch = open(os.path.join(ROOT, "integration/src/core/receiver/gnss_block_factory.patch")).read()
+    for name in ("GPS_L1_CA_PCPS_Acquisition_B200", "Galileo_E1_PCPS_Ambiguous_Acquisition_B200", "BEIDOU_B1I_PCPS_Acquisition_B200"):
+        assert name in open(os.path.join(ROOT, "integration/src/core/receiver/gnss_block_factory_b200.cc")).read()
+    assert "IsB200AcquisitionImplementation(implementation)" in patch and "GetAcqBlock" in patch
+
+
+@pytest.mark.skipif(has_gpu(), reason="checks the no-device behaviour")
+def test_adapter_refuses_to_run_without_a_device(adapter_driver, tmp_path):
+    geo, codes, iq, _ = synth.config_scene("C1", n_prn=1)
+    inp, outp = tmp_path / "a.bin", tmp_path / "a.out"
+    _write_adapter_input(inp, geo["fs"], 5000, 250, 0.001, 1, 0, 1, 0, codes[0], iq)
+    r = subprocess.run([adapter_driver, str(inp), str(outp)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 7 and "cannot create the B200 engine" in r.stderr, r.stdout + r.stderr      # init() throws: no CPU path
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which,scene,system", [(0, "C1", "gps_l1_ca"), (1, "C2", "gal_e1b"), (2, "C4_bds", "bds_b1i")])
+def test_adapter_through_the_channel_call_order(adapter_driver, oracle, tmp_path, which, scene, system):
+    """GetAcqBlock -> Channel's constructor order (set_channel, set_channel_fsm, set_gnss_synchro, set_doppler_step,
+    set_threshold, init) -> set_signal's set_local_code -> connect / start -> reset -> the scheduler's general_work calls,
+    for each of the three B200 adapters: the ChannelFsm gets Event_valid_acquisition and Gnss_Synchro holds what the oracle's
+    block instance finds on the dwell the state machine really searched."""
+    geo, codes, iq1, truth = synth.config_scene(scene, n_prn=max(t["prn"] for t in synth.config_scene(scene)[3][:1]))
+    t = truth[0]
+    n = geo["consumed_samples"]
+    ms = geo["sampled_ms"]
+    iq = synth.make_iq(3 * n, geo["fs"], [dict(t, cn0=max(t["cn0"], 47.0))], seed=77)
+    one = synth.local_code(system, t["prn"], geo["fs"])
+    inp, outp = tmp_path / "a.bin", tmp_path / "a.out"
+    _write_adapter_input(inp, geo["fs"], geo["doppler_max"], geo["doppler_step"], 0.001, ms, which, t["prn"], 1, one, iq)
+    r = subprocess.run([adapter_driver, str(inp), str(outp)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    got = _read_adapter_output(outp)
+    assert got["event"] == 1 and got["generator_calls"] == 1
+    # which samples did the block search? state 0 drops the first call's items (1000), the buffer then fills from there
+    start = got["stamp"] - n
+    assert start >= 1000 and start % 1000 == 0
+    a = oracle.acq(fft_size=geo["fft_size"], consumed_samples=n, doppler_max=geo["doppler_max"], doppler_step=geo["doppler_step"], fs=geo["fs"],
+                   samples_per_chip=geo["samples_per_chip"], samples_per_code=geo["samples_per_code"], use_cfar=True)
+    a.set_local_code(np.tile(one, max(1, ms // synth.SYSTEMS[system][2]))[:n])
+    want = a.dwell(iq[start:start + n])
+    assert got["doppler"] == float(want["doppler_hz"]) and abs(got["doppler"] - t["doppler"]) <= geo["doppler_step"]
+    assert got["delay"] == float(np.fmod(np.float32(want["code_phase"]), np.float32(geo["samples_per_code"])))
+    one_len = one.size
+    assert abs(((got["delay"] + start) - t["delay"] + one_len / 2) % one_len - one_len / 2) <= 1
+    a.close()
