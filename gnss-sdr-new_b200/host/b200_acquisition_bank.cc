@@ -1,5 +1,6 @@
 /*
  * b200_acquisition_bank.cc — see the header.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #include "b200_acquisition_bank.h"
 #include <algorithm>

@@ -6,6 +6,7 @@
  * with the same search geometry share one engine handle (one "bank"); a block is a SLOT of that bank. Dwells that
  * arrive for the same sample block (equal sample stamp) within a bounded window are issued as ONE batched engine
  * call, so the forward transforms are computed once for all of them.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef GNSS_SDR_B200_ACQUISITION_BANK_H
 #define GNSS_SDR_B200_ACQUISITION_BANK_H

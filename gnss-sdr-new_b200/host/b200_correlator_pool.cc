@@ -1,5 +1,6 @@
 /*
  * b200_correlator_pool.cc — see the header. Leader/follower request combining in front of the C-ABI engine.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #include "b200_correlator_pool.h"
 #include <algorithm>

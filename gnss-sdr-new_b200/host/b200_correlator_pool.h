@@ -9,6 +9,7 @@
  * every call launches alone (exact reference timing, lowest throughput).
  *
  * Plain host C++17; no CUDA or GNU Radio types.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef GNSS_SDR_B200_CORRELATOR_POOL_H
 #define GNSS_SDR_B200_CORRELATOR_POOL_H

@@ -2,6 +2,7 @@
  * b200_mat_writer.cc — see the header. Layout after "MAT-File Format" (MathWorks), Level 5:
  * 128-byte header (116 text, 8 subsystem offset, version 0x0100, endian indicator "MI" as a 16-bit value), then one
  * miMATRIX element per variable = { array flags, dimensions, name, real part }, every sub-element padded to 8 bytes.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #include "b200_mat_writer.h"
 #include <cstring>

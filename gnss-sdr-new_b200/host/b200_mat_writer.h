@@ -6,6 +6,7 @@
  * older Level-5 container instead: the same variable names, classes and shapes, readable by MATLAB/Octave `load`,
  * scipy.io.loadmat and by matio's Mat_Open (which the reference's Acquisition_Dump_Reader uses and which detects the
  * container version by itself, acquisition_dump_reader.cc:30-60).
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef GNSS_SDR_B200_MAT_WRITER_H
 #define GNSS_SDR_B200_MAT_WRITER_H

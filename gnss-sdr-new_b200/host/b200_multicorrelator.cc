@@ -1,5 +1,6 @@
 /*
  * b200_multicorrelator.cc — see the header; mirrors cpu_multicorrelator.cc member by member.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #include "b200_multicorrelator.h"
 #include "b200_correlator_pool.h"

@@ -1,6 +1,7 @@
 /*
  * b200_multicorrelator.h — B200 drop-in for Cpu_Multicorrelator (complex local codes; used by the GLONASS and
  * TCP-connector tracking blocks). Reference: src/algorithms/tracking/libs/cpu_multicorrelator.h:37-58.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef GNSS_SDR_B200_MULTICORRELATOR_H
 #define GNSS_SDR_B200_MULTICORRELATOR_H

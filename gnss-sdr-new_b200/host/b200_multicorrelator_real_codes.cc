@@ -1,6 +1,7 @@
 /*
  * b200_multicorrelator_real_codes.cc — see the header.
  * Each method notes the reference member it mirrors (cpu_multicorrelator_real_codes.cc).
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #include "b200_multicorrelator_real_codes.h"
 #include "b200_correlator_pool.h"

@@ -5,6 +5,7 @@
  * Same method set, same borrowed-pointer conventions, same `bool` returns, so dll_pll_veml_tracking can hold it by
  * value in place of the CPU class (dll_pll_veml_tracking.h:90-91) with a one-line type change. The arithmetic runs in
  * the B200 engine (include/gnss_b200.h); there is no CPU fallback: without a CUDA device init() returns false.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef GNSS_SDR_B200_MULTICORRELATOR_REAL_CODES_H
 #define GNSS_SDR_B200_MULTICORRELATOR_REAL_CODES_H

@@ -1,5 +1,6 @@
 /*
  * b200_symbol_sync.cc — see the header. ":NNN" = line of dll_pll_veml_tracking.cc the statement follows.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #include "b200_symbol_sync.h"
 #include <cstdlib>

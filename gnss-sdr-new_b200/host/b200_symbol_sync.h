@@ -13,6 +13,7 @@
  *   - loss of lock (:1873-1879, :2035-2040) sends it back to the search.
  * The strings and lengths are the per-signal constants the constructor of the reference block selects (:180-450), e.g.
  * GPS L1 C/A: GPS_CA_PREAMBLE_SYMBOLS_STR / 160 with 20 symbols per bit; GPS L5I: GPS_L5I_NH_CODE_STR / 10, 10 symbols.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef GNSS_SDR_B200_SYMBOL_SYNC_H
 #define GNSS_SDR_B200_SYMBOL_SYNC_H

@@ -1,5 +1,6 @@
 /*
  * b200_tracking_dump.cc — see the header. ":NNN" = line of dll_pll_veml_tracking.cc the statement follows.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #include "b200_tracking_dump.h"
 #include "b200_mat_writer.h"

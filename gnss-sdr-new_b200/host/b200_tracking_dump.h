@@ -8,6 +8,7 @@
  * (include/gnss_b200.h) so that the reference's readers (Tracking_Dump_Reader, src/utils/matlab/dll_pll_veml_read_*.m,
  * the .mat plotting scripts) work on the output of gnss_b200_trk_run. The .mat is a Level-5 container
  * (b200_mat_writer.h) where the reference writes v7.3 through matio.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef GNSS_SDR_B200_TRACKING_DUMP_H
 #define GNSS_SDR_B200_TRACKING_DUMP_H

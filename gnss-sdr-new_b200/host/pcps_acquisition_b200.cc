@@ -1,6 +1,7 @@
 /*
  * pcps_acquisition_b200.cc — see the header. Comments of the form ":NNN" point at the line of
  * src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.cc whose behaviour the statement reproduces.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #include "pcps_acquisition_b200.h"
 #if !defined(B200_HOST_STANDALONE)

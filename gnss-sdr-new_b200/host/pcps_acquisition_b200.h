@@ -11,6 +11,7 @@
  * dump = true (N4) writes the reference's per-acquisition .mat file (same name pattern, variables, classes and shapes,
  * :408-508) in the Level-5 container (b200_mat_writer.h) instead of matio's v7.3.
  * The fork's make_repeat_steps mode (the block re-arms itself after the first detection and keeps reporting) is mirrored too.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef GNSS_SDR_PCPS_ACQUISITION_B200_H
 #define GNSS_SDR_PCPS_ACQUISITION_B200_H

@@ -3,6 +3,7 @@
  * mirror is built outside the GNSS-SDR tree (B200_HOST_STANDALONE). Inside the tree the real header is included instead, so
  * the member NAMES here have to be the reference's; everything else is this repository's own: only the members the mirror
  * and its test driver read are present, grouped by what they configure. Defaults follow acq_conf.h:40-80.
+ * SPDX-License-Identifier: GPL-3.0-or-later
  */
 #ifndef B200_STUB_ACQ_CONF_H
 #define B200_STUB_ACQ_CONF_H

@@ -1,4 +1,4 @@
-/* Stand-in for src/core/receiver/channel_fsm.h (see README.md in this directory): only the events acquisition raises. */
+/* Stand-in for src/core/receiver/channel_fsm.h (see README.md in this directory): only the events acquisition raises. SPDX-License-Identifier: GPL-3.0-or-later */
 #ifndef B200_STUB_CHANNEL_FSM_H
 #define B200_STUB_CHANNEL_FSM_H
 

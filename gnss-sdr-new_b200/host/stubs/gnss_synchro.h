@@ -1,4 +1,4 @@
-/* Stand-in for src/core/system_parameters/gnss_synchro.h (see README.md in this directory). */
+/* Stand-in for src/core/system_parameters/gnss_synchro.h (see README.md in this directory). SPDX-License-Identifier: GPL-3.0-or-later */
 #ifndef B200_STUB_GNSS_SYNCHRO_H
 #define B200_STUB_GNSS_SYNCHRO_H
 #include <cstdint>
