@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(kThreads) multicorr_kernel(const ChanParams* _
     const uint32_t* __restrict__ shift_samples_all, float2* __restrict__ partials, uint32_t* __restrict__ tickets,
     float2* __restrict__ out, int n_taps_total, int tap0, uint32_t smem_elems)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     CodeT* s_code = reinterpret_cast<CodeT*>(smem_raw);
     __shared__ float2 s_red[kThreads / 32][T];
     __shared__ int s_last;
@@ -285,12 +285,23 @@ __global__ void __launch_bounds__(kThreads) multicorr_kernel(const ChanParams* _
 
 // ------------------------------------------------------------------------------------------------
 // Fast path (real codes, plain resampler, chip window fits shared memory) — the BASELINE config-5 case.
-// Blackwell packed-FP32 instructions do two taps per instruction: FADD2 for the two binary32 additions of the
-// reference's chip-phase expression, FADD2.RM against 1.5*2^23 for the floor (exact for |phase| < 2^22, and off
-// the quarter-rate conversion pipe), and FFMA2 for the accumulate with taps paired as (re_t, re_t+1), (im_t, im_t+1).
-// The sample stream is the only HBM traffic: every thread streams its own samples through a private shared-memory
-// ring with 8-byte cp.async (12 loads in flight per thread, no registers held, no block barrier), and a channel is
-// cut into segments of a few thousand samples so that the chip window of a CTA is ~10 KB and several CTAs fit per SM.
+//
+// What bounds it (tools/scratch/ubench_pipes.cu, measured on B200): the packed FP32 instructions (FADD2, FFMA2) issue at
+// HALF the rate of their scalar forms, so packing saves issue slots but no FMA-pipe cycles. A (sample, tap) costs three
+// rounded additions (the reference's chip-phase expression, bit-exact) and two multiply-adds on that pipe, one shared
+// memory lookup and one address LEA; everything else is per-sample overhead, and this kernel is organised to keep that
+// overhead small:
+//   * samples  a warp owns a CONTIGUOUS 1 KB part of every chunk and streams it through a private ring with one bulk
+//              copy (cp.async.bulk + mbarrier) issued by lane 0: no per-thread copy instructions, no registers held, no
+//              block barrier in the loop. The segment starts on a 16-byte boundary (a misaligned first sample is peeled
+//              off), a partial last chunk is read with plain loads;
+//   * carrier  sample n = n_thread + m has the phasor P0 exp(j theta n) = P_thread * W[m], W warp-uniform: the loop
+//              multiplies by W[m] from a small table (one broadcast load per two rows) and the accumulators are rotated by
+//              P_thread once at the end, so there is no per-thread phasor recurrence;
+//   * taps     two taps per packed instruction: FADD2 for the two binary32 additions of the chip phase, FADD2.RM against
+//              1.5*2^23 for the floor (exact for |phase| < 2^22, off the quarter-rate conversion pipe), FFMA2 for the
+//              accumulate with taps paired as (re_t, re_t+1), (im_t, im_t+1); the last tap of an odd count runs on the
+//              full-rate scalar forms instead of wasting half of five packed instructions.
 // Every lane of a packed op is an IEEE binary32 round-to-nearest (resp. round-down) operation, so the chip
 // indices stay bit-identical to volk_gnsssdr_32f_xn_resampler_32f_xn_generic.
 // ------------------------------------------------------------------------------------------------
@@ -308,15 +319,45 @@ __device__ __forceinline__ float2 lds_f32x2(uint32_t addr)
     return v;
 }
 
-// asynchronous 8-byte global -> shared copy; src_bytes = 0 zero-fills the destination
+__device__ __forceinline__ float4 lds_f32x4(uint32_t addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ void cp_async_4(uint32_t smem_addr, const void* gptr)
 {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr), "l"(gptr) : "memory");
 }
 
-__device__ __forceinline__ void cp_async_8(uint32_t smem_addr, const void* gptr, uint32_t src_bytes)
+// mbarrier + 1-D bulk copy (TMA)
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
 {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_addr), "l"(gptr), "r"(src_bytes) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
 }
 
 constexpr float kFloorMagic = 12582912.0f;  // 1.5 * 2^23
@@ -326,144 +367,349 @@ template <int T>
 __global__ void __launch_bounds__(kThreads, 3) multicorr_window_kernel(const ChanParams* __restrict__ chans, const float* __restrict__ shifts_all,
     float2* __restrict__ partials, uint32_t* __restrict__ tickets, float2* __restrict__ out, int n_taps_total, int tap0, uint32_t smem_elems)
 {
-    constexpr int TP = (T + 1) / 2;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    unsigned char* s_ring = smem_raw;
+    constexpr int TP = T / 2;          // packed tap pairs
+    constexpr bool ODD = (T & 1) != 0;  // + one scalar tap
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     float* s_code = reinterpret_cast<float*>(smem_raw + kWinRingBytes);
     __shared__ float2 s_red[kThreads / 32][T];
     __shared__ int s_last;
     __shared__ uint32_t s_bias;
+    __shared__ float s_shift[T];
+    constexpr int kBinades = 22;  // a < 2^22 on this path
+    __shared__ __align__(8) float s_k[kBinades][T + (T & 1)];
+    __shared__ float2 s_short[kBinades];
 
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const ChanParams cp = chans[blockIdx.y];
     const uint32_t splits = gridDim.x;
     const uint32_t per = (cp.n + splits - 1) / splits;
     const uint32_t n0 = min(cp.n, blockIdx.x * per), n1 = min(cp.n, n0 + per);
     const int L = (int)cp.code_len;
     const float* g_code = static_cast<const float*>(cp.code);
-
-    // Sample ring: each thread copies ITS OWN samples global -> shared with 8-byte cp.async (no registers, no block
-    // barrier: a thread only ever reads back the slots it filled), kWinGroup samples per commit group and kWinRing
-    // groups in the ring, i.e. (kWinRing-1)*kWinGroup loads in flight per thread at all times. Slots past the end of
-    // the segment are zero-filled (src-size 0) and their chip index is clamped into the window.
     const float2* sig = cp.sig;
-    const uint32_t ring = (uint32_t)__cvta_generic_to_shared(s_ring) + threadIdx.x * 8u;
-    const uint32_t n_groups = (n1 - n0 + kWinGroup * kThreads - 1) / (kWinGroup * kThreads);  // uniform over the CTA
-    const uint32_t n_full = (n1 - n0) / (kWinGroup * kThreads);                               // groups with no padding
-    const uint32_t first = n0 + threadIdx.x;
-    const uint32_t last = n1 > 0 ? n1 - 1 : 0;
-    auto issue = [&](const uint32_t g) {
-        const uint32_t slot = ring + (g % kWinRing) * (kWinGroup * kThreads * 8u);
-        if (g < n_full)
-            {
-                const float2* src = sig + first + g * (kWinGroup * kThreads);
-#pragma unroll
-                for (int u = 0; u < kWinGroup; u++) cp_async_8(slot + u * (kThreads * 8u), src + u * kThreads, 8u);
-            }
-        else if (g < n_groups)
-            {
-#pragma unroll
-                for (int u = 0; u < kWinGroup; u++)
-                    {
-                        const uint32_t nn = first + (g * kWinGroup + u) * kThreads;
-                        cp_async_8(slot + u * (kThreads * 8u), sig + min(nn, last), nn < n1 ? 8u : 0u);
-                    }
-            }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    // start streaming before anything else: the window fill below overlaps the first DRAM round trip
-#pragma unroll
-    for (int g = 0; g < kWinRing - 1; g++) issue(g);
 
-    float2 shift2[TP];
+    // The segment [n0, n1) as: one peeled sample when sig + n0 is not 16-byte aligned | n_full whole chunks | a partial chunk.
+    const uint32_t peel = (n1 > n0) ? (uint32_t)((reinterpret_cast<uintptr_t>(sig + n0) >> 3) & 1u) : 0u;
+    const uint32_t m0 = n0 + peel;  // first sample of chunk 0
+    const uint32_t n_full = (n1 - m0) / kStChunk;
+    const uint32_t first = m0 + warp * kStPart + lane;  // this thread's sample in row 0 of chunk 0
+
+    // ---- start streaming before anything else: the window fill below overlaps the first DRAM round trip ----
+    const uint32_t wring = (uint32_t)__cvta_generic_to_shared(smem_raw) + warp * (kStRing * kStPart * 8u);
+    const uint32_t wbar = (uint32_t)__cvta_generic_to_shared(smem_raw + kStRingBytes + kStTableBytes) + warp * (kStRing * 8u);
+    const float2* wsrc = sig + m0 + warp * kStPart;
+    if (lane == 0)
+        {
+#pragma unroll
+            for (int s = 0; s < kStRing; s++) mbar_init(wbar + s * 8u, 1u);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            if (n_full > 0)
+                {
+                    mbar_expect_tx(wbar, kStPart * 8u);
+                    bulk_g2s(wring, wsrc, kStPart * 8u, wbar);
+                }
+        }
+
     float smin = 3.4e38f, smax = -3.4e38f;
 #pragma unroll
-    for (int p = 0; p < TP; p++)
+    for (int t = 0; t < T; t++)
         {
-            const float s0 = shifts_all[cp.shifts_off + tap0 + 2 * p];
-            const float s1 = shifts_all[cp.shifts_off + min(tap0 + 2 * p + 1, n_taps_total - 1)];
-            shift2[p] = make_float2(s0, s1);
-            smin = fminf(smin, fminf(s0, s1));
-            smax = fmaxf(smax, fmaxf(s0, s1));
+            const float sh = shifts_all[cp.shifts_off + tap0 + t];
+            smin = fminf(smin, sh);
+            smax = fmaxf(smax, sh);
         }
     const double a0 = (double)cp.code_step * (double)n0, a1 = (double)cp.code_step * (double)(n1 > n0 ? n1 - 1 : n0);
-    const int lo = (int)floor(fmin(a0, a1) + (double)smin - (double)cp.rem_code) - 2;
-    const int width = min((int)smem_elems, (int)floor(fmax(a0, a1) + (double)smax - (double)cp.rem_code) + 2 - lo + 1);
+    int lo = (int)floor(fmin(a0, a1) + (double)smin - (double)cp.rem_code) - 2;
+    int width = min((int)smem_elems, (int)floor(fmax(a0, a1) + (double)smax - (double)cp.rem_code) + 2 - lo + 1);
+    // The pre-wrapped chip window code[(lo + j) mod L], j < width. A doubled code table makes it one contiguous range: one bulk
+    // copy from a 16-byte aligned start (lo moves down by up to 3 chips; the launch reserves 8 floats for that and the rounding
+    // of the size). Otherwise 4-byte cp.async, every element of the fill in flight at once.
+    const uint32_t s_code_addr = (uint32_t)__cvta_generic_to_shared(s_code);
+    const uint32_t win_bar = (uint32_t)__cvta_generic_to_shared(smem_raw + kStRingBytes + kStTableBytes) + (kThreads / 32) * kStRing * 8u;
+    int start = wrap_chip(lo, L);
+    const bool bulk_window = (cp.flags & F_CODE_DOUBLED) && width + 6 <= L + (int)kCodeDoubledPad;
+    if (bulk_window)
+        {
+            lo -= start & 3;
+            width = (width + (start & 3) + 3) & ~3;
+            start &= ~3;
+            if (threadIdx.x == kThreads - 1)
+                {
+                    mbar_init(win_bar, 1u);
+                    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                    mbar_expect_tx(win_bar, (uint32_t)width * 4u);
+                    bulk_g2s(s_code_addr, g_code + start, (uint32_t)width * 4u, win_bar);
+                }
+        }
+    else
+        {
+            int src = wrap_chip(start + (int)threadIdx.x, L);
+            const int adv = kThreads % L;
+            for (int j = threadIdx.x; j < width; j += kThreads)
+                {
+                    cp_async_4(s_code_addr + 4u * (uint32_t)j, g_code + src);
+                    src += adv;
+                    if (src >= L) src -= L;
+                }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        }
+    if (threadIdx.x == 0) s_bias = s_code_addr - 4u * (kFloorMagicBits + (uint32_t)lo);
+    if (threadIdx.x < T) s_shift[threadIdx.x] = shifts_all[cp.shifts_off + tap0 + threadIdx.x];
+    // Short-form tables, one row per binade [2^e, 2^(e+1)) of the chip phase a (see sample_short below): the spacing there is
+    // u = 2^(e-23), RN_u(x) = fl(fl(x + 1.5 2^e) - 1.5 2^e) for |x| < 2^(e-1), k[e][t] = RN_u(shift_t) + RN_u(-rem) (exact), and the
+    // short form holds for a in [2^e + m, 2^(e+1) - m], m = max|shift| + |rem| + 4u, unless some rounding was a tie.
     {
-        // the pre-wrapped chip window, also by cp.async: every element of the fill is in flight at once
-        int src = wrap_chip(lo + (int)threadIdx.x, L);
-        const int adv = kThreads % L;
-        const uint32_t s_code_addr = (uint32_t)__cvta_generic_to_shared(s_code);
-        for (int j = threadIdx.x; j < width; j += kThreads)
+        const float nrem_p = -cp.rem_code;
+        for (int i = threadIdx.x; i < kBinades * T; i += kThreads)
             {
-                cp_async_4(s_code_addr + 4u * (uint32_t)j, g_code + src);
-                src += adv;
-                if (src >= L) src -= L;
+                const int e = i / T, t = i - e * T;
+                const float big = __uint_as_float((uint32_t)(e + 127) << 23) * 1.5f;
+                const float sh = shifts_all[cp.shifts_off + tap0 + t];
+                const float r = __fsub_rn(__fadd_rn(nrem_p, big), big);
+                s_k[e][t] = __fadd_rn(__fsub_rn(__fadd_rn(sh, big), big), r);
             }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (threadIdx.x < kBinades)
+            {
+                const int e = threadIdx.x;
+                const float lo2 = __uint_as_float((uint32_t)(e + 127) << 23);
+                const float u = lo2 * 1.1920928955078125e-07f, big = lo2 * 1.5f;
+                const float margin = fmaxf(fabsf(smin), fabsf(smax)) + fabsf(nrem_p) + 4.0f * u;
+                bool ok = margin * 4.0f < lo2;
+                const float r = __fsub_rn(__fadd_rn(nrem_p, big), big);
+                ok &= !(fabsf(__fsub_rn(nrem_p, r)) * 2.0f == u);
+                for (int t = 0; t < T; t++)
+                    {
+                        const float sh = shifts_all[cp.shifts_off + tap0 + t];
+                        const float q = __fsub_rn(__fadd_rn(sh, big), big);
+                        ok &= !(fabsf(__fsub_rn(sh, q)) * 2.0f == u);
+                    }
+                s_short[e] = ok ? make_float2(lo2 + margin, 2.0f * lo2 - margin) : make_float2(3.4e38f, -3.4e38f);
+            }
     }
-    if (threadIdx.x == 0) s_bias = (uint32_t)__cvta_generic_to_shared(s_code) - 4u * (kFloorMagicBits + (uint32_t)lo);
+
+    // carrier table, relative to the thread's own first sample (sample n = first + m has the phasor P_thread W(m)):
+    //   whole chunks   W[kStRows c + r] = exp(j theta (kStChunk c + 32 r))
+    //   partial chunk  rows of kThreads samples across the whole CTA (all warps busy): row r of warp w is
+    //                  m = kStChunk n_full + kThreads r + 32 w - kStPart w
+    //   peeled sample  m = -1 (thread 0 only)
+    // angles reduced in double
+    float2* s_w = reinterpret_cast<float2*>(smem_raw + kStRingBytes);
+    const uint32_t n_w = n_full * kStRows;
+    for (uint32_t i = threadIdx.x; i <= n_w + kStTailEntries; i += kThreads)
+        {
+            double m;
+            if (i < n_w)
+                m = (double)((i / kStRows) * kStChunk + (i % kStRows) * 32u);
+            else if (i < n_w + kStTailEntries)
+                {
+                    const int r = (int)(i - n_w) / (kThreads / 32), w = (int)(i - n_w) % (kThreads / 32);
+                    m = (double)(n_full * kStChunk) + (double)(r * kThreads + w * 32 - w * kStPart);
+                }
+            else
+                m = -1.0;
+            double ang = cp.theta * m;
+            ang -= 6.283185307179586476925286766559 * rint(ang * 0.15915494309189533576888376337251);
+            float sw, cw;
+            sincosf((float)ang, &sw, &cw);
+            s_w[i] = make_float2(cw, sw);
+        }
 
     // accumulators of a tap pair: (re_t, re_t+1) and (im_t, im_t+1), so that one FFMA2 serves two taps
-    float2 acc_re[TP], acc_im[TP];
+    float2 acc_re[TP > 0 ? TP : 1], acc_im[TP > 0 ? TP : 1];
+    float2 acc_last = make_float2(0.f, 0.f);
 #pragma unroll
     for (int q = 0; q < TP; q++) acc_re[q] = acc_im[q] = make_float2(0.f, 0.f);
 
+    const float step = cp.code_step;
+    const float nrem = -cp.rem_code;
+    const float2 nrem2 = make_float2(nrem, nrem);
+    const float2 magic2 = make_float2(kFloorMagic, kFloorMagic);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");  // the window has landed (element-wise fill)
+    __syncthreads();
+    if (bulk_window) mbar_wait(win_bar, 0u);
+    // shared-memory address of chip k = base + 4 * (bits(k + magic) - (magicbits + lo)), modulo 2^32: one LEA per chip
+    // (read back from shared memory so that ptxas cannot split the constant part off again)
+    const uint32_t addr_bias = *reinterpret_cast<volatile uint32_t*>(&s_bias);
+
+    // ---- one sample: x = the sample, w = its table phasor, fn = (float)n ----
+    // exact form: the reference's expression floor(fl(fl(a + shift) - rem)), three rounded operations per tap
+    auto sample = [&](const float2 x, const float2 w, const float fn) {
+        const float zr = x.x * w.x - x.y * w.y;
+        const float zi = x.x * w.y + x.y * w.x;
+        const float a = __fmul_rn(step, fn);
+        if (TP > 0)
+            {
+                const float2 zr2 = make_float2(zr, zr), zi2 = make_float2(zi, zi), a2 = make_float2(a, a);
+#pragma unroll
+                for (int q = 0; q < TP; q++)
+                    {
+                        const float2 sh = *reinterpret_cast<const float2*>(&s_shift[2 * q]);
+                        const float2 f = __fadd2_rd(__fadd2_rn(__fadd2_rn(a2, sh), nrem2), magic2);
+                        float2 c;
+                        c.x = lds_f32(__float_as_uint(f.x) * 4u + addr_bias);
+                        c.y = lds_f32(__float_as_uint(f.y) * 4u + addr_bias);
+                        acc_re[q] = __ffma2_rn(c, zr2, acc_re[q]);
+                        acc_im[q] = __ffma2_rn(c, zi2, acc_im[q]);
+                    }
+            }
+        if (ODD)
+            {
+                const float f = __fadd_rd(__fadd_rn(__fadd_rn(a, s_shift[T - 1]), nrem), kFloorMagic);
+                const float c = lds_f32(__float_as_uint(f) * 4u + addr_bias);
+                acc_last.x = fmaf(c, zr, acc_last.x);
+                acc_last.y = fmaf(c, zi, acc_last.y);
+            }
+    };
+    // short form, valid while a, a + shift and a + shift - rem all stay inside one binade [2^e, 2^(e+1)), whose spacing is
+    // u = 2^(e-23): a is a multiple of u, so fl(a + shift) = a + RN_u(shift) and fl(that - rem) = that + RN_u(-rem) (translation
+    // invariance of round-to-nearest on a uniform grid; a tie, whose result would depend on the parity of a / u, is excluded when
+    // the offsets are computed). The two roundings collapse into ONE exact addition of k = RN_u(shift) + RN_u(-rem).
+    float2 k2[TP > 0 ? TP : 1];
+    float k_last = 0.f;
+    auto sample_short = [&](const float2 x, const float2 w, const float fn) {
+        const float zr = x.x * w.x - x.y * w.y;
+        const float zi = x.x * w.y + x.y * w.x;
+        const float a = __fmul_rn(step, fn);
+        if (TP > 0)
+            {
+                const float2 zr2 = make_float2(zr, zr), zi2 = make_float2(zi, zi), a2 = make_float2(a, a);
+#pragma unroll
+                for (int q = 0; q < TP; q++)
+                    {
+                        const float2 f = __fadd2_rd(__fadd2_rn(a2, k2[q]), magic2);
+                        float2 c;
+                        c.x = lds_f32(__float_as_uint(f.x) * 4u + addr_bias);
+                        c.y = lds_f32(__float_as_uint(f.y) * 4u + addr_bias);
+                        acc_re[q] = __ffma2_rn(c, zr2, acc_re[q]);
+                        acc_im[q] = __ffma2_rn(c, zi2, acc_im[q]);
+                    }
+            }
+        if (ODD)
+            {
+                const float f = __fadd_rd(__fadd_rn(a, k_last), kFloorMagic);
+                const float c = lds_f32(__float_as_uint(f) * 4u + addr_bias);
+                acc_last.x = fmaf(c, zr, acc_last.x);
+                acc_last.y = fmaf(c, zi, acc_last.y);
+            }
+    };
+    // The binade [bin_lo, bin_hi) the offsets k are loaded for, and the range [short_lo, short_hi] of a inside it for which the
+    // short form is proven (empty when a tie or a too small binade rules it out; tables built in the prologue). Warp-uniform.
+    float bin_lo = 1.f, bin_hi = 0.f, short_lo = 3.4e38f, short_hi = -3.4e38f;
+    auto rebin = [&](const float a) {
+        const int e = (int)(__float_as_uint(a) >> 23) - 127;  // a > 0
+        bin_lo = __uint_as_float(__float_as_uint(a) & 0x7F800000u);
+        bin_hi = bin_lo * 2.0f;
+        short_lo = 3.4e38f;
+        short_hi = -3.4e38f;
+        if (e < 0 || e >= kBinades) return;
+        short_lo = s_short[e].x;
+        short_hi = s_short[e].y;
+#pragma unroll
+        for (int q = 0; q < TP; q++) k2[q] = *reinterpret_cast<const float2*>(&s_k[e][2 * q]);
+        if (ODD) k_last = s_k[e][T - 1];
+    };
+
+    // ---- whole chunks ----
+    float fnb = (float)first;  // exact: n < 2^24
+    const uint32_t w_addr = (uint32_t)__cvta_generic_to_shared(s_w);
+    uint32_t g = 0;
+    // one chunk of this warp: refill the slot consumed last, wait for this chunk's copy, kStRows samples per lane.
+    // Running state instead of expressions in g, so that nothing is recomputed per chunk: slot toggle, mbarrier phase,
+    // the address of the next bulk copy and of this chunk's carrier-table row.
+    uint32_t slot_sel = 0, phase = 0, wrow = w_addr;
+    const float2* next_src = wsrc + kStChunk;
+    const uint32_t lane_slot = wring + lane * 8u;
+    auto chunk = [&](auto short_tag) {
+        constexpr bool SHORT = decltype(short_tag)::value;
+        const uint32_t other = slot_sel ^ 1u;
+        __syncwarp();  // every lane is done with the slot of chunk g - 1: refill it with chunk g + 1
+        if (lane == 0 && g + 1 < n_full)
+            {
+                mbar_expect_tx(wbar + other * 8u, kStPart * 8u);
+                bulk_g2s(wring + other * (kStPart * 8u), next_src, kStPart * 8u, wbar + other * 8u);
+            }
+        next_src += kStChunk;
+        mbar_wait(wbar + slot_sel * 8u, phase);
+        const uint32_t slot = lane_slot + slot_sel * (kStPart * 8u);
+#pragma unroll
+        for (int r = 0; r < kStRows; r += 2)
+            {
+                const float4 w = lds_f32x4(wrow + r * 8u);
+                const float fn0 = (r == 0) ? fnb : fnb + (float)(32 * r);
+                if (SHORT)
+                    {
+                        sample_short(lds_f32x2(slot + r * 256u), make_float2(w.x, w.y), fn0);
+                        sample_short(lds_f32x2(slot + r * 256u + 256u), make_float2(w.z, w.w), fnb + (float)(32 * r + 32));
+                    }
+                else
+                    {
+                        sample(lds_f32x2(slot + r * 256u), make_float2(w.x, w.y), fn0);
+                        sample(lds_f32x2(slot + r * 256u + 256u), make_float2(w.z, w.w), fnb + (float)(32 * r + 32));
+                    }
+            }
+        fnb += (float)kStChunk;
+        wrow += kStRows * 8u;
+        phase ^= slot_sel;  // the phase of a slot flips every second chunk
+        slot_sel = other;
+        g++;
+    };
+    const float lane_f = (float)lane;
+    const bool may_short = step > 0.f && !(cp.flags & F_EXACT_ONLY);
+    while (g < n_full)
+        {
+            // chip phase of the first and of the last sample of this warp's part of chunk g (warp-uniform)
+            const float fn_last = fnb - lane_f + (float)(kStPart - 1);
+            const float a_min = __fmul_rn(step, fnb - lane_f), a_max = __fmul_rn(step, fn_last);
+            if (may_short && !(a_min >= bin_lo && a_min < bin_hi)) rebin(a_min);
+            if (may_short && a_min >= short_lo && a_max <= short_hi)
+                {
+                    // how many chunks in a row stay inside the proven range: estimate, then check the last one exactly
+                    uint32_t run = 1u + (uint32_t)((short_hi - a_max) / (step * (float)kStChunk));
+                    run = min(run, n_full - g);
+                    while (run > 1u && !(__fmul_rn(step, fn_last + (float)((run - 1u) * kStChunk)) <= short_hi)) run--;
+                    for (uint32_t i = 0; i < run; i++) chunk(std::true_type{});
+                }
+            else
+                chunk(std::false_type{});
+        }
+    // ---- the partial chunk: rows of kThreads samples across the CTA, plain loads; lanes past the end contribute a zero sample
+    // at the last chip phase ----
+    {
+        const uint32_t base = m0 + n_full * kStChunk;
+        if (base < n1)
+            {
+                const float f_last = (float)(n1 - 1);
+                const uint32_t rows = (n1 - base + kThreads - 1) / kThreads;  // <= kStRows
+                for (uint32_t r = 0; r < rows; r++)
+                    {
+                        const uint32_t nn = base + r * kThreads + threadIdx.x;
+                        const bool live = nn < n1;
+                        const float2 x = live ? __ldg(sig + nn) : make_float2(0.f, 0.f);
+                        sample(x, s_w[n_w + r * (kThreads / 32) + warp], live ? (float)nn : f_last);
+                    }
+            }
+        // ---- the peeled sample: phasor P(first of thread 0) * exp(-j theta) ----
+        if (peel && threadIdx.x == 0) sample(__ldg(sig + n0), s_w[n_w + kStTailEntries], (float)n0);
+    }
+
+    // rotate by this thread's constant phasor P0 exp(j theta first), angle reduced in double
+    float2 pt;
     {
         double ang = cp.theta * (double)first;
         ang -= 6.283185307179586476925286766559 * rint(ang * 0.15915494309189533576888376337251);
         float sr, cr;
         sincosf((float)ang, &sr, &cr);
-        float2 ph = make_float2(cp.p0_re * cr - cp.p0_im * sr, cp.p0_re * sr + cp.p0_im * cr);
-        const float2 wb = make_float2(cp.wb_re, cp.wb_im);
-        const float step = cp.code_step;
-        const float2 nrem2 = make_float2(-cp.rem_code, -cp.rem_code);
-        const float2 magic2 = make_float2(kFloorMagic, kFloorMagic);
-        // shared-memory address of chip k = base + 4 * (bits(k + magic) - (magicbits + lo)), modulo 2^32: one LEA per chip
-        // (read back from shared memory so that ptxas cannot split the constant part off again)
-        asm volatile("cp.async.wait_group 0;" ::: "memory");  // window + the first ring groups have landed
-        __syncthreads();
-        const uint32_t addr_bias = *reinterpret_cast<volatile uint32_t*>(&s_bias);
-
-        auto consume = [&](auto tail_tag, const uint32_t g) {
-            constexpr bool TAIL = decltype(tail_tag)::value;
-            issue(g + kWinRing - 1);
-            asm volatile("cp.async.wait_group %0;" ::"n"(kWinRing - 1) : "memory");
-            const uint32_t slot = ring + (g % kWinRing) * (kWinGroup * kThreads * 8u);
-#pragma unroll
-            for (int u = 0; u < kWinGroup; u++)
-                {
-                    const float2 x = lds_f32x2(slot + u * (kThreads * 8u));
-                    uint32_t nn = first + (g * kWinGroup + u) * kThreads;
-                    if (TAIL) nn = min(nn, last);
-                    const float zr = x.x * ph.x - x.y * ph.y;
-                    const float zi = x.x * ph.y + x.y * ph.x;
-                    const float2 zr2 = make_float2(zr, zr), zi2 = make_float2(zi, zi);
-                    const float a = __fmul_rn(step, (float)nn);
-                    const float2 a2 = make_float2(a, a);
-#pragma unroll
-                    for (int q = 0; q < TP; q++)
-                        {
-                            // floor(fl(fl(a + shift) - rem)) for two taps at once
-                            const float2 f = __fadd2_rd(__fadd2_rn(__fadd2_rn(a2, shift2[q]), nrem2), magic2);
-                            float2 c;
-                            c.x = lds_f32(__float_as_uint(f.x) * 4u + addr_bias);
-                            c.y = (2 * q + 1 < T) ? lds_f32(__float_as_uint(f.y) * 4u + addr_bias) : 0.f;
-                            acc_re[q] = __ffma2_rn(c, zr2, acc_re[q]);
-                            acc_im[q] = __ffma2_rn(c, zi2, acc_im[q]);
-                        }
-                    ph = make_float2(ph.x * wb.x - ph.y * wb.y, ph.x * wb.y + ph.y * wb.x);
-                }
-        };
-        uint32_t g = 0;
-        for (; g < n_full; g++) consume(std::false_type{}, g);
-        for (; g < n_groups; g++) consume(std::true_type{}, g);
+        pt = make_float2(cp.p0_re * cr - cp.p0_im * sr, cp.p0_re * sr + cp.p0_im * cr);
     }
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int t = 0; t < T; t++)
         {
-            float2 v = (t & 1) ? make_float2(acc_re[t / 2].y, acc_im[t / 2].y) : make_float2(acc_re[t / 2].x, acc_im[t / 2].x);
+            float2 v;
+            if (ODD && t == T - 1)
+                v = acc_last;
+            else
+                v = (t & 1) ? make_float2(acc_re[t / 2].y, acc_im[t / 2].y) : make_float2(acc_re[t / 2].x, acc_im[t / 2].x);
+            v = make_float2(v.x * pt.x - v.y * pt.y, v.x * pt.y + v.y * pt.x);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1)
                 {
@@ -610,6 +856,15 @@ void launch_taps(int T, dim3 grid, size_t smem, cudaStream_t st, const ChanParam
 
 }  // namespace
 
+cudaError_t mc::upload_doubled_code(void* d_dst, const float* h_code, uint32_t code_len, cudaStream_t st)
+{
+    std::vector<float> twice(doubled_code_floats(code_len));
+    for (size_t i = 0; i < twice.size(); i++) twice[i] = h_code[i % code_len];
+    cudaError_t e = cudaMemcpyAsync(d_dst, twice.data(), twice.size() * sizeof(float), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    return cudaStreamSynchronize(st);  // the staging vector dies with this call
+}
+
 cudaError_t mc::launch_real_plain(bool fast, uint32_t n_ch, uint32_t splits, uint32_t smem_elems, cudaStream_t st, const ChanParams* d_cp,
     const float* d_shifts, const uint32_t* d_shift_samples, float2* d_partials, uint32_t* d_tickets, float2* d_out, uint32_t n_taps)
 {
@@ -618,7 +873,7 @@ cudaError_t mc::launch_real_plain(bool fast, uint32_t n_ch, uint32_t splits, uin
         {
             const int T = (int)std::min<uint32_t>(kMaxTapsPerPass, n_taps - tap0);
             if (fast)
-                launch_window(T, grid, (size_t)smem_elems * 4 + kWinRingBytes, st, d_cp, d_shifts, d_partials, d_tickets, d_out, (int)n_taps, (int)tap0, smem_elems);
+                launch_window(T, grid, (size_t)(smem_elems + 8) * 4 + kWinRingBytes, st, d_cp, d_shifts, d_partials, d_tickets, d_out, (int)n_taps, (int)tap0, smem_elems);
             else
                 launch_taps<float>(T, grid, (size_t)smem_elems * 4, st, d_cp, d_shifts, d_shift_samples, d_partials, d_tickets, d_out, (int)n_taps, (int)tap0, smem_elems);
         }
@@ -666,6 +921,8 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
 
     const bool hd_res = flags & GNSS_B200_MC_HIGH_DYN;
     const bool hd_rot = hd_res && !(flags & GNSS_B200_MC_SIX_ARG);
+    const char* exact_env = std::getenv("B200_MC_EXACT_ONLY");  // parity aid, see F_EXACT_ONLY
+    const bool exact_only = exact_env && exact_env[0] == '1';
     uint64_t max_len = 1, max_n = 1;
     double max_span = 0.0;  // chips swept by one channel over its whole integration
     for (uint32_t i = 0; i < n_ch; i++)
@@ -686,8 +943,9 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
         {
             // window kernel: long segments amortise the per-CTA prologue/epilogue (one segment per channel when the
             // batch fills the machine), but the chip window of a segment must leave room for 3 CTAs per SM
-            const double window_budget = 10800.0;  // floats: 42 KB next to the 32 KB sample ring
+            const double window_budget = 10800.0;  // floats: 42 KB next to the 28 KB of sample ring and carrier table
             while (max_span / splits + 64.0 > window_budget && (uint64_t)splits * 2048 < max_n) splits++;
+            splits = std::max<uint32_t>(splits, (uint32_t)((max_n + kStMaxSegment - 1) / kStMaxSegment));
             if (const char* e = std::getenv("B200_MC_SPLITS")) splits = (uint32_t)std::max(1, std::atoi(e));  // tuning aid
         }
     uint64_t max_window = 1;  // widest per-CTA chip window over the batch
@@ -740,7 +998,7 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
                     const std::complex<float> inc_rate = std::exp(std::complex<float>(0.0f, -a.carr_rate_rad));
                     p.rate_arg = std::log(inc_rate).imag();
                 }
-            p.flags = (hd_res ? F_HIGH_DYN_RESAMPLER : 0u) | (hd_rot ? F_HIGH_DYN_ROTATOR : 0u) | (cplx ? F_COMPLEX_CODE : 0u);
+            p.flags = (hd_res ? F_HIGH_DYN_RESAMPLER : 0u) | (hd_rot ? F_HIGH_DYN_ROTATOR : 0u) | (cplx ? F_COMPLEX_CODE : F_CODE_DOUBLED) | (exact_only ? F_EXACT_ONLY : 0u);
             p.shifts_off = i * n_taps;
             const float* hsi = hs + (size_t)i * n_taps;
             if (hd_res)
@@ -773,7 +1031,8 @@ int build_params(gnss_b200_mc* h, uint32_t n_ch, const uint32_t* ch, const gnss_
     const uint32_t elem = cplx ? 8u : 4u;
     const uint32_t cap = kSmemCapBytes / elem;
     // fast (packed, window-only) kernel: real code, plain resampler, window of (c,c) pairs fits, |chip phase| < 2^22
-    const bool fast = !cplx && !hd_res && small_phase && max_window <= (kSmemCapBytes - kWinRingBytes) / 4;
+    const bool fast = !cplx && !hd_res && small_phase && max_window + 8 <= (kSmemCapBytes - kWinRingBytes) / 4 && max_n < (1u << 24) &&
+                      (max_n + splits - 1) / splits <= kStMaxSegment;
     if (out_fast) *out_fast = fast;
     if (fast)
         {
@@ -812,7 +1071,7 @@ int run_batch(gnss_b200_mc* h, uint32_t n_ch, uint32_t n_taps, uint32_t smem_ele
             const int T = (int)std::min<uint32_t>(kMaxTapsPerPass, n_taps - tap0);
             h->prof.begin(0, h->stream);
             if (fast)
-                launch_window(T, grid, (size_t)smem_elems * 4 + kWinRingBytes, h->stream, d_cp, d_shifts, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
+                launch_window(T, grid, (size_t)(smem_elems + 8) * 4 + kWinRingBytes, h->stream, d_cp, d_shifts, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
                     h->d_out.as<float2>(), (int)n_taps, (int)tap0, smem_elems);
             else if (cplx)
                 launch_taps<float2>(T, grid, smem, h->stream, d_cp, d_shifts, d_ss, h->d_partials.as<float2>(), h->d_tickets.as<uint32_t>(),
@@ -886,10 +1145,18 @@ extern "C"
         B200_REQUIRE(ch < h->max_channels, GNSS_B200_ERR_INVALID, "mc_set_code: channel %u out of range", ch);
         std::lock_guard<std::mutex> lk(h->mu);
         B200_CUDA(cudaSetDevice(h->device));
-        const size_t bytes = (size_t)code_len * (is_complex ? 8 : 4);
-        B200_CUDA(h->codes[ch].reserve(bytes));
-        B200_CUDA(cudaMemcpyAsync(h->codes[ch].p, code, bytes, cudaMemcpyHostToDevice, h->stream));
-        B200_CUDA(cudaStreamSynchronize(h->stream));
+        if (is_complex)
+            {
+                const size_t bytes = (size_t)code_len * 8;
+                B200_CUDA(h->codes[ch].reserve(bytes));
+                B200_CUDA(cudaMemcpyAsync(h->codes[ch].p, code, bytes, cudaMemcpyHostToDevice, h->stream));
+                B200_CUDA(cudaStreamSynchronize(h->stream));
+            }
+        else
+            {
+                B200_CUDA(h->codes[ch].reserve(mc::doubled_code_floats(code_len) * 4));
+                B200_CUDA(mc::upload_doubled_code(h->codes[ch].p, code, code_len, h->stream));
+            }
         h->code_len[ch] = code_len;
         h->code_complex[ch] = is_complex ? 1 : 0;
         return GNSS_B200_OK;

@@ -201,7 +201,7 @@ __device__ void write_params(const TrkDevCfg& cfg, TrkChan& s, mc::ChanParams& p
     p.wb_re = (float)cb;
     p.wb_im = (float)sb;
     p.rate_arg = 0.0f;
-    p.flags = 0u;
+    p.flags = mc::F_CODE_DOUBLED;  // gnss_b200_trk_set_code uploads the doubled layout
     p.shifts_off = ch_index * cfg.n_taps;
 }
 
@@ -545,7 +545,8 @@ extern "C"
         while (step * 1.01 * cfg->vector_length / splits + span_taps + 64.0 > 10800.0 && (uint64_t)splits * 2048 < cfg->vector_length) splits++;
         const double window = step * 1.01 * ((cfg->vector_length + splits - 1) / splits) + span_taps + 64.0;
         h->splits = splits;
-        h->fast = window <= (double)(mc::kSmemCapBytes - mc::kWinRingBytes) / 4 && step * cfg->vector_length + 16.0 < 4.0e6;
+        h->fast = window + 8 <= (double)(mc::kSmemCapBytes - mc::kWinRingBytes) / 4 && step * cfg->vector_length + 16.0 < 4.0e6 &&
+                  cfg->vector_length < (1u << 24) && (cfg->vector_length + splits - 1) / splits <= mc::kStMaxSegment;
         if (h->fast)
             h->smem_elems = (uint32_t)window;
         else
@@ -621,9 +622,8 @@ extern "C"
         B200_REQUIRE(ch < h->cfg.max_channels, GNSS_B200_ERR_INVALID, "trk_set_code: channel %u out of range", ch);
         std::lock_guard<std::mutex> lk(h->mu);
         B200_CUDA(cudaSetDevice(h->device));
-        B200_CUDA(h->codes[ch].reserve((size_t)code_len * 4));
-        B200_CUDA(cudaMemcpyAsync(h->codes[ch].p, code, (size_t)code_len * 4, cudaMemcpyHostToDevice, h->stream));
-        B200_CUDA(cudaStreamSynchronize(h->stream));
+        B200_CUDA(h->codes[ch].reserve(mc::doubled_code_floats(code_len) * 4));
+        B200_CUDA(mc::upload_doubled_code(h->codes[ch].p, code, code_len, h->stream));
         h->code_len[ch] = code_len;
         return GNSS_B200_OK;
     }

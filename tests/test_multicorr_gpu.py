@@ -88,6 +88,47 @@ def test_chip_indices_bit_exact(b200, oracle):
         assert np.array_equal(mc2.chip_indices(0, a2, sh), oracle.mc_chip_indices(n, L, sh, 1.75, float(args[0, 4])))
 
 
+@pytest.mark.parametrize("case", ["random", "dyadic", "misaligned", "small_phase"])
+def test_short_chip_phase_form_is_exact(b200, monkeypatch, case):
+    """The window kernel replaces floor(fl(fl(a + shift) - rem)) by floor(a + k) wherever a, a + shift and a + shift - rem share a
+    binade (multicorr.cu, sample_short). Both forms walk the samples in the same order with the same arithmetic, so if every chip
+    index agrees the correlator outputs are BIT-identical to a run with the short form switched off (B200_MC_EXACT_ONLY=1) —
+    one differing index anywhere in 6 x 30000 x 11 lookups would show. Cases: random shifts/rem; dyadic shifts and rem (the tie
+    candidates: multiples of the binade spacing and exact halves of it); a stream that starts on an 8-byte, not 16-byte, boundary
+    (the peeled first sample); chip phases below 64 (short form mostly unavailable) and a whole code period."""
+    rng = np.random.default_rng({"random": 1, "dyadic": 2, "misaligned": 3, "small_phase": 4}[case])
+    n_ch, n, ntaps = 6, 30000, 11
+    if case == "small_phase":
+        n = 9000
+    codes, sigs, args, shifts = _scene(rng, n_ch, n, 10230, ntaps)
+    if case == "random":
+        shifts = np.sort(rng.uniform(-1.5, 1.5, (n_ch, ntaps)).astype(np.float32), axis=1)
+    if case == "dyadic":
+        base = np.array([-1, -0.5, -0.25, -2.0 ** -9, -2.0 ** -11, 0, 2.0 ** -12, 2.0 ** -10, 0.25, 0.5, 1], np.float32)
+        shifts = np.tile(base, (n_ch, 1))
+        shifts[1] += np.float32(2.0 ** -13)
+        args[:, 3] = np.array([0.5, 0.25 + 2.0 ** -11, 2.0 ** -12, 0.0, 0.75 + 2.0 ** -13, 1 - 2.0 ** -10], np.float32)    # rem_code_phase_chips
+        args[2, 4] = np.float32(0.3125)                                                                                  # a dyadic code step too
+    results = []
+    for exact_only in ("0", "1"):
+        monkeypatch.setenv("B200_MC_EXACT_ONLY", exact_only)
+        mc = b200.MulticorrelatorB200(n_ch, n, ntaps)
+        for c in range(n_ch):
+            mc.set_local_code(c, codes[c])
+        if case == "misaligned":
+            stream = np.concatenate([np.zeros(1, np.complex64)] + sigs)          # every channel window starts at an odd sample
+            mc.set_stream(stream)
+            offs = 1 + n * np.arange(n_ch)
+            a = mc.make_args(n_ch, n, args[:, 0], args[:, 1], args[:, 2], args[:, 3], args[:, 4], args[:, 5], stream_offsets=offs)
+        else:
+            host = np.ascontiguousarray(np.stack(sigs))
+            a = mc.make_args(n_ch, n, args[:, 0], args[:, 1], args[:, 2], args[:, 3], args[:, 4], args[:, 5], sig_ptrs=[host[c].ctypes.data for c in range(n_ch)])
+        results.append(np.array(mc.correlate_batch(np.arange(n_ch), a, shifts), copy=True))
+        mc.close()
+    assert np.array_equal(results[0].view(np.uint32), results[1].view(np.uint32))
+    assert np.abs(results[0]).max() > 1.0
+
+
 @pytest.mark.parametrize("six", [False, True])
 def test_high_dynamics_mode(b200, oracle, six):
     rng = np.random.default_rng(17)
