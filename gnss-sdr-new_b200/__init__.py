@@ -91,6 +91,13 @@ class TrkCfg(C.Structure):
         ("cn0_smoother_alpha", C.c_float), ("carrier_lock_test_smoother_alpha", C.c_float),
         ("cn0_smoother_samples", c_i32), ("carrier_lock_test_smoother_samples", c_i32),
         ("max_channels", c_u32), ("device", c_i32),
+        # symbol synchronisation, extended integration, pilot tracking, high dynamics (all 0: the state-2 loop only)
+        ("symbol_sync", c_i32), ("secondary", c_i32),
+        ("secondary_code_length", c_u32), ("symbols_per_bit", c_u32), ("data_secondary_code_length", c_u32),
+        ("extend_correlation_symbols", c_i32), ("track_pilot", c_i32),
+        ("pll_bw_narrow_hz", C.c_float), ("dll_bw_narrow_hz", C.c_float), ("early_late_space_narrow_chips", C.c_float), ("very_early_late_space_narrow_chips", C.c_float),
+        ("high_dyn", c_i32), ("smoother_length", c_u32), ("bit_synchronization_time_limit_s", c_u32),
+        ("secondary_code_string", C.c_char * 208), ("data_secondary_code_string", C.c_char * 112),
     ]
 
 
@@ -118,7 +125,8 @@ TRK_EPOCH_DTYPE = np.dtype([("corr", np.float32, (10,)), ("carrier_doppler_hz", 
                             ("carr_error_hz", np.float64), ("carr_error_filt_hz", np.float64), ("code_error_chips", np.float64),
                             ("code_error_filt_chips", np.float64), ("rem_code_phase_samples", np.float64),
                             ("acc_carrier_phase_rad", np.float64), ("cn0_db_hz", np.float64), ("carrier_lock_test", np.float64),
-                            ("evm", np.float64), ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32)], align=True)
+                            ("evm", np.float64), ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32),
+                            ("accu", np.float32, (10,)), ("prompt_data", np.float32, (2,)), ("state", np.int32), ("reserved", np.int32)], align=True)
 TRK_VALID, TRK_PULL_IN, TRK_LOSS_OF_LOCK = 1, 2, 4
 
 # every symbol include/gnss_b200.h declares (tests check the library exports all of them)

@@ -53,6 +53,13 @@ class TrkCfg(C.Structure):
         ("cn0_smoother_alpha", c_f), ("carrier_lock_test_smoother_alpha", c_f),
         ("cn0_smoother_samples", C.c_int32), ("carrier_lock_test_smoother_samples", C.c_int32),
         ("max_channels", c_u), ("device", C.c_int32),
+        # symbol synchronisation, extended integration, pilot tracking, high dynamics (all 0: the state-2 loop only)
+        ("symbol_sync", C.c_int32), ("secondary", C.c_int32),
+        ("secondary_code_length", c_u), ("symbols_per_bit", c_u), ("data_secondary_code_length", c_u),
+        ("extend_correlation_symbols", C.c_int32), ("track_pilot", C.c_int32),
+        ("pll_bw_narrow_hz", c_f), ("dll_bw_narrow_hz", c_f), ("early_late_space_narrow_chips", c_f), ("very_early_late_space_narrow_chips", c_f),
+        ("high_dyn", C.c_int32), ("smoother_length", c_u), ("bit_synchronization_time_limit_s", c_u),
+        ("secondary_code_string", C.c_char * 208), ("data_secondary_code_string", C.c_char * 112),
     ]
 
 
@@ -60,7 +67,8 @@ TRK_EPOCH_DTYPE = np.dtype([("corr", np.float32, (10,)), ("carrier_doppler_hz", 
                             ("carr_error_hz", np.float64), ("carr_error_filt_hz", np.float64), ("code_error_chips", np.float64),
                             ("code_error_filt_chips", np.float64), ("rem_code_phase_samples", np.float64),
                             ("acc_carrier_phase_rad", np.float64), ("cn0_db_hz", np.float64), ("carrier_lock_test", np.float64),
-                            ("evm", np.float64), ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32)], align=True)
+                            ("evm", np.float64), ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32),
+                            ("accu", np.float32, (10,)), ("prompt_data", np.float32, (2,)), ("state", np.int32), ("reserved", np.int32)], align=True)
 
 
 def build(ref=None):
@@ -104,6 +112,7 @@ def _bind_oracle(lib):
     lib.oracle_trk_create.argtypes = [C.POINTER(TrkCfg)]
     lib.oracle_trk_destroy.argtypes = [C.c_void_p]
     lib.oracle_trk_set_code.argtypes = [C.c_void_p, _fp, c_i]
+    lib.oracle_trk_set_data_code.argtypes = [C.c_void_p, _fp, c_i]
     lib.oracle_trk_start.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
     lib.oracle_trk_run.restype = c_i
     lib.oracle_trk_run.argtypes = [C.c_void_p, _fp, C.c_uint64, C.c_uint64, c_i, C.c_void_p]
@@ -283,7 +292,7 @@ class OracleAcq:
 
 
 class OracleTrk:
-    """One channel of the reference block's state-2 loop (oracle_trk.c)."""
+    """One channel of the reference block's loop: states 2, 3, 4 (oracle_trk.c)."""
 
     def __init__(self, oracle, cfg):
         self.lib = oracle.lib
@@ -302,16 +311,20 @@ class OracleTrk:
         code = np.ascontiguousarray(code, dtype=np.float32)
         self.lib.oracle_trk_set_code(self.h, _ptr(code), code.size)
 
+    def set_data_code(self, code):
+        code = np.ascontiguousarray(code, dtype=np.float32)
+        self.lib.oracle_trk_set_data_code(self.h, _ptr(code), code.size)
+
     def start(self, acq_delay_samples, acq_doppler_hz, acq_samplestamp, now_sample):
         self.lib.oracle_trk_start(self.h, float(acq_delay_samples), float(acq_doppler_hz), int(acq_samplestamp), int(now_sample))
 
     def run(self, samples, stream_start, max_epochs, trace=False):
-        """trace=True: also returns [max_epochs][6] = (rem_carr_phase_rad, carr_step, rem_code, code_step, first sample, ran) per
-        epoch, the correlator arguments of do_correlation_step."""
+        """trace=True: also returns [max_epochs][8] = (rem_carr_phase_rad, carr_step, rem_code, code_step, first sample, ran,
+        carr_rate, code_rate) per epoch, the correlator arguments of do_correlation_step."""
         samples = np.ascontiguousarray(samples, dtype=np.complex64)
         out = np.zeros(max_epochs, dtype=TRK_EPOCH_DTYPE)
         if trace:
-            tr = np.zeros((max_epochs, 6), dtype=np.float64)
+            tr = np.zeros((max_epochs, 8), dtype=np.float64)
             n = self.lib.oracle_trk_run_traced(self.h, _ptr(samples.view(np.float32)), int(stream_start), samples.size, max_epochs,
                                                out.ctypes.data_as(C.c_void_p), _ptr(tr, C.c_double))
             return out, n, tr

@@ -1,9 +1,11 @@
 /*
  * TEST INFRASTRUCTURE — CPU oracle, not product code. Nothing under gnss-sdr-new_b200/ may include or link this.
  *
- * Plain-C restatement of the per-epoch loop of the reference's dll_pll_veml tracking block in state 2
- * (src/algorithms/tracking/gnuradio_blocks/dll_pll_veml_tracking.cc), one code period per integration, data
- * component, Costas PLL:
+ * Plain-C restatement of the per-epoch loop of the reference's dll_pll_veml tracking block
+ * (src/algorithms/tracking/gnuradio_blocks/dll_pll_veml_tracking.cc): state 2 (one code period per integration, Costas PLL) and,
+ * with cfg.symbol_sync, the whole symbol machine — secondary-code / bit synchronisation (:1888-1925, acquire_secondary :923-966),
+ * state 3 coherent extension (:1989-2027), state 4 narrow tracking (:2028-2084), save_correlation_results (:1290-1400), the
+ * pilot + data correlator pair (:1078-1088) and the high-dynamics rate smoothing (:1232-1284):
  *   start_tracking            :640-880      state 1 alignment      :1812-1845
  *   do_correlation_step       :1064-1089    (oracle_mc_real = Cpu_Multicorrelator_Real_Codes)
  *   cn0_and_tracking_lock_status :968-1013  run_dll_pll            :1092-1182
@@ -17,6 +19,9 @@
  * Pinned bit-for-bit against those reference files compiled unmodified into oracle/_ref/libref_trk.so
  * (tests/test_oracle_trk.py). The reference's unit tests hold no numeric expectations for this loop
  * (SURVEY.md §4): beyond that component pin, parity of the closed loop is "unpinned".
+ * pll_four_quadrant_atan (pilot tracking) calls gr::fast_atan2f, which lives in GNU Radio (gnuradio-runtime/lib/math/
+ * fast_atan2f.cc, GNU Radio 3.10; not vendored under /root/reference): restated here from its published algorithm (a 255-step
+ * arctangent table with linear interpolation, octant folding) — parity of that one function is "unpinned".
  */
 #include "oracle_trk.h"
 #include "oracle_mc.h"
@@ -252,6 +257,61 @@ double oracle_pll_cloop_two_quadrant_atan(float re, float im)
     return 0.0;
 }
 
+/* gr::fast_atan2f: |error| < 1e-5 rad; table[i] = atan(i / 255), two guard entries at pi/4 */
+float oracle_fast_atan2f(float y, float x)
+{
+    static float table[258];
+    static int ready = 0;
+    if (!ready)
+        {
+            for (int i = 0; i < 256; i++) table[i] = (float)atan((double)i / 255.0);
+            table[256] = table[257] = (float)atan(1.0);
+            ready = 1;
+        }
+    const float TAN_MAP_RES = 0.003921569f; /* 1 / 255 */
+    const float y_abs = fabsf(y), x_abs = fabsf(x);
+    if (!((y_abs > 0.0f) || (x_abs > 0.0f))) return 0.0f;
+    const float z = (y_abs < x_abs) ? y_abs / x_abs : x_abs / y_abs;
+    float base_angle;
+    if (z < TAN_MAP_RES)
+        base_angle = z;
+    else
+        {
+            float alpha = z * 255.0f;
+            const int index = ((int)alpha) & 0xff;
+            alpha -= (float)index;
+            base_angle = table[index] + (table[index + 1] - table[index]) * alpha;
+        }
+    float angle;
+    if (x_abs > y_abs)
+        {
+            if (x >= 0.0f)
+                angle = (y >= 0.0f) ? base_angle : -base_angle;
+            else
+                {
+                    angle = (float)M_PI;
+                    angle = (y >= 0.0f) ? angle - base_angle : base_angle - angle;
+                }
+        }
+    else
+        {
+            if (y >= 0.0f)
+                {
+                    angle = (float)(M_PI / 2.0);
+                    angle = (x >= 0.0f) ? angle - base_angle : angle + base_angle;
+                }
+            else
+                {
+                    angle = -(float)(M_PI / 2.0);
+                    angle = (x >= 0.0f) ? angle + base_angle : angle - base_angle;
+                }
+        }
+    return angle;
+}
+
+/* tracking_discriminators.cc:86-89 */
+double oracle_pll_four_quadrant_atan(float re, float im) { return (double)oracle_fast_atan2f(im, re); }
+
 double oracle_dll_nc_e_minus_l_normalized(float e_re, float e_im, float l_re, float l_im, float spc, float slope, float y_intercept)
 {
     const double P_early = hypotf(e_re, e_im); /* std::abs(std::complex<float>) */
@@ -304,7 +364,9 @@ float oracle_carrier_lock_detector(const float* prompt_c64, int length)
     return (I * I - Q * Q) / (I * I + Q * Q);
 }
 
-/* ---------------- the block's state-2 loop ---------------- */
+/* ---------------- the block's loop ---------------- */
+#define ORACLE_TRK_MAX_SECONDARY 208
+#define ORACLE_TRK_MAX_HISTORY 64
 struct oracle_trk
 {
     oracle_trk_cfg cfg;
@@ -312,18 +374,31 @@ struct oracle_trk
     float shifts[5];
     float* code;
     int code_len;
+    float* data_code;
+    int data_code_len;
     /* members of dll_pll_veml_tracking (dll_pll_veml_tracking.h:118-204) */
     double carrier_doppler_hz, carrier_phase_step_rad, code_freq_chips, code_phase_step_chips;
+    double carrier_phase_rate_step_rad, code_phase_rate_step_chips;
     double rem_code_phase_samples, rem_code_phase_chips, acc_carrier_phase_rad;
     double carr_phase_error_hz, carr_freq_error_hz, carr_error_filt_hz, code_error_chips, code_error_filt_chips;
-    double cn0_db_hz, carrier_lock_test, evm;
+    double cn0_db_hz, carrier_lock_test, evm, current_correlation_time_s;
     uint64_t cursor, acq_sample_stamp;
-    float rem_carr_phase_rad;
+    float rem_carr_phase_rad, spc;
     float P_old[2];
-    int current_prn_length_samples, state, pull_in;
+    float accu[10];      /* d_VE_accu, d_E_accu, d_P_accu, d_L_accu, d_VL_accu */
+    float P_data_accu[2];
+    int current_prn_length_samples, state, pull_in, cloop, acc_carrier_phase_initialized;
     int carrier_lock_fail, code_lock_fail, cn0_counter;
+    int current_symbol, current_data_symbol, extend_count, pll_180;
+    /* boost::circular_buffer<gr_complex> d_Prompt_circular_buffer: oldest first, push_back on a full buffer drops the oldest */
+    float circ[2 * ORACLE_TRK_MAX_SECONDARY];
+    int circ_size;
+    /* boost::circular_buffer<std::pair<double,double>> d_carr_ph_history / d_code_ph_history, capacity 2 * smoother_length */
+    double carr_hist[2 * ORACLE_TRK_MAX_HISTORY], code_hist[2 * ORACLE_TRK_MAX_HISTORY];
+    int carr_hist_size, code_hist_size;
     oracle_carrier_filter cf;
     oracle_loop_filter lf;
+    float lf_update_interval, lf_noise_bandwidth;
     oracle_smoother cn0_s, lock_s;
     float prompt_buf[2 * ORACLE_TRK_MAX_CN0_SAMPLES];
 };
@@ -333,6 +408,7 @@ oracle_trk* oracle_trk_create(const oracle_trk_cfg* cfg)
     oracle_trk* t = (oracle_trk*)calloc(1, sizeof(oracle_trk));
     t->cfg = *cfg;
     t->n_taps = cfg->veml ? 5 : 3;
+    if (t->cfg.extend_correlation_symbols < 1) t->cfg.extend_correlation_symbols = 1; /* :512-520 */
     return t;
 }
 
@@ -340,6 +416,7 @@ void oracle_trk_destroy(oracle_trk* t)
 {
     if (!t) return;
     free(t->code);
+    free(t->data_code);
     free(t);
 }
 
@@ -351,25 +428,18 @@ void oracle_trk_set_code(oracle_trk* t, const float* code, int code_len)
     t->code_len = code_len;
 }
 
-void oracle_trk_start(oracle_trk* t, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t now_sample)
+void oracle_trk_set_data_code(oracle_trk* t, const float* code, int code_len)
+{
+    free(t->data_code);
+    t->data_code = (float*)malloc(sizeof(float) * (size_t)code_len);
+    memcpy(t->data_code, code, sizeof(float) * (size_t)code_len);
+    t->data_code_len = code_len;
+}
+
+static void wide_shifts(oracle_trk* t)
 {
     const oracle_trk_cfg* c = &t->cfg;
     const float spc = (float)c->code_samples_per_chip;
-    /* start_tracking() */
-    t->carrier_doppler_hz = acq_doppler_hz;
-    t->carrier_phase_step_rad = TWO_PI * t->carrier_doppler_hz / c->fs_in;
-    t->acq_sample_stamp = acq_samplestamp;
-    t->carrier_lock_fail = t->code_lock_fail = 0;
-    t->rem_code_phase_samples = 0.0;
-    t->rem_carr_phase_rad = 0.0f;
-    t->rem_code_phase_chips = 0.0;
-    t->acc_carrier_phase_rad = 0.0;
-    t->cn0_counter = 0;
-    t->carrier_lock_test = 1.0;
-    t->evm = 0.0; /* :845 */
-    t->cn0_db_hz = 0.0;
-    t->P_old[0] = t->P_old[1] = 0.0f;
-    t->carr_phase_error_hz = t->carr_freq_error_hz = t->carr_error_filt_hz = t->code_error_chips = t->code_error_filt_chips = 0.0;
     if (c->veml)
         {
             t->shifts[0] = -c->very_early_late_space_chips * spc;
@@ -384,17 +454,67 @@ void oracle_trk_start(oracle_trk* t, double acq_delay_samples, double acq_dopple
             t->shifts[1] = 0.0f;
             t->shifts[2] = c->early_late_space_chips * spc;
         }
+}
+
+/* clear_tracking_vars (:1192-1213) except the correlator outputs, which the next correlation overwrites */
+static void clear_tracking_vars(oracle_trk* t)
+{
+    t->P_data_accu[0] = t->P_data_accu[1] = 0.0f;
+    t->P_old[0] = t->P_old[1] = 0.0f;
+    t->carr_phase_error_hz = t->carr_freq_error_hz = t->carr_error_filt_hz = 0.0;
+    t->code_error_chips = t->code_error_filt_chips = 0.0;
+    t->current_symbol = t->current_data_symbol = 0;
+    t->circ_size = 0;
+    t->carrier_phase_rate_step_rad = 0.0;
+    t->code_phase_rate_step_chips = 0.0;
+    t->carr_hist_size = t->code_hist_size = 0;
+}
+
+void oracle_trk_start(oracle_trk* t, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t now_sample)
+{
+    const oracle_trk_cfg* c = &t->cfg;
+    /* start_tracking() */
+    t->carrier_doppler_hz = acq_doppler_hz;
+    t->carrier_phase_step_rad = TWO_PI * t->carrier_doppler_hz / c->fs_in;
+    t->carrier_phase_rate_step_rad = 0.0;
+    t->code_phase_rate_step_chips = 0.0; /* constructor :135; clear_tracking_vars afterwards */
+    t->carr_hist_size = t->code_hist_size = 0;
+    t->acq_sample_stamp = acq_samplestamp;
+    t->carrier_lock_fail = t->code_lock_fail = 0;
+    t->rem_code_phase_samples = 0.0;
+    t->rem_carr_phase_rad = 0.0f;
+    t->rem_code_phase_chips = 0.0;
+    t->acc_carrier_phase_rad = 0.0;
+    t->cn0_counter = 0;
+    t->carrier_lock_test = 1.0;
+    t->evm = 0.0; /* :845 */
+    t->cn0_db_hz = 0.0;
+    t->P_old[0] = t->P_old[1] = 0.0f;
+    t->carr_phase_error_hz = t->carr_freq_error_hz = t->carr_error_filt_hz = t->code_error_chips = t->code_error_filt_chips = 0.0;
+    memset(t->accu, 0, sizeof(t->accu));
+    t->P_data_accu[0] = t->P_data_accu[1] = 0.0f;
+    t->current_symbol = t->current_data_symbol = t->extend_count = 0;
+    t->pll_180 = 0;
+    wide_shifts(t);
+    t->spc = c->early_late_space_chips;
+    t->current_correlation_time_s = c->code_period_s;
     oracle_carrier_filter_set_params(&t->cf, c->fll_bw_hz, c->pll_bw_hz, c->pll_filter_order);
-    oracle_loop_filter_init(&t->lf, (float)c->code_period_s, c->dll_bw_hz, c->dll_filter_order, 0);
+    t->lf_update_interval = (float)c->code_period_s;
+    t->lf_noise_bandwidth = c->dll_bw_hz;
+    oracle_loop_filter_init(&t->lf, t->lf_update_interval, t->lf_noise_bandwidth, c->dll_filter_order, 0);
     oracle_carrier_filter_initialize(&t->cf, (float)acq_doppler_hz);
     oracle_loop_filter_initialize(&t->lf, 0.0f);
     t->pull_in = 1;
+    t->cloop = 1;
+    t->circ_size = 0;
+    t->acc_carrier_phase_initialized = 0;
     /* state 1: alignment with the local replica */
     {
         const int64_t acq_trk_diff_samples = (int64_t)now_sample - (int64_t)acq_samplestamp;
         const double delta_trk_to_acq_prn_start_samples = (double)acq_trk_diff_samples - acq_delay_samples;
         t->code_freq_chips = c->code_chip_rate;
         t->code_phase_step_chips = t->code_freq_chips / c->fs_in;
+        t->code_phase_rate_step_chips = 0.0;
         const double T_chip_mod_seconds = 1.0 / t->code_freq_chips;
         const double T_prn_mod_seconds = T_chip_mod_seconds * (double)c->code_length_chips;
         const double T_prn_mod_samples = T_prn_mod_seconds * c->fs_in;
@@ -412,6 +532,7 @@ void oracle_trk_start(oracle_trk* t, double acq_delay_samples, double acq_dopple
     }
 }
 
+/* cn0_and_tracking_lock_status(coh_integration_time_s) (:968-1056): the prompt buffer takes d_P_accu */
 static int cn0_and_tracking_lock_status(oracle_trk* t, const float* P, double coh_integration_time_s)
 {
     const oracle_trk_cfg* c = &t->cfg;
@@ -467,27 +588,198 @@ static int cn0_and_tracking_lock_status(oracle_trk* t, const float* P, double co
     return 1;
 }
 
+/* run_dll_pll (:1092-1160) on the accumulators; the experimental Doppler correction (:1162-1182) is off by default and not restated */
+static void run_dll_pll(oracle_trk* t)
+{
+    const oracle_trk_cfg* c = &t->cfg;
+    const float* VE = t->accu;
+    const float* E = t->accu + 2;
+    const float* P = t->accu + 4;
+    const float* L = t->accu + 6;
+    const float* VL = t->accu + 8;
+    const double T_s = t->current_correlation_time_s;
+    if (t->cloop)
+        t->carr_phase_error_hz = oracle_pll_cloop_two_quadrant_atan(P[0], P[1]) / TWO_PI;
+    else
+        t->carr_phase_error_hz = oracle_pll_four_quadrant_atan(P[0], P[1]) / TWO_PI;
+    if ((t->pull_in && c->enable_fll_pull_in) || c->enable_fll_steady_state)
+        {
+            t->carr_freq_error_hz = oracle_fll_diff_atan(t->P_old[0], t->P_old[1], P[0], P[1], 0, T_s) / TWO_PI;
+            t->P_old[0] = P[0];
+            t->P_old[1] = P[1];
+            if (t->pull_in && c->enable_fll_pull_in)
+                t->carr_error_filt_hz = oracle_carrier_filter_get_carrier_error(&t->cf, (float)t->carr_freq_error_hz, 0.0F, (float)T_s);
+            else
+                t->carr_error_filt_hz = oracle_carrier_filter_get_carrier_error(&t->cf, (float)t->carr_freq_error_hz, (float)t->carr_phase_error_hz, (float)T_s);
+        }
+    else
+        {
+            t->carr_error_filt_hz = oracle_carrier_filter_get_carrier_error(&t->cf, 0, (float)t->carr_phase_error_hz, (float)T_s);
+        }
+    t->carrier_doppler_hz = t->carr_error_filt_hz;
+    if (c->veml)
+        t->code_error_chips = oracle_dll_nc_vemlp_normalized(VE, E, L, VL);
+    else
+        t->code_error_chips = oracle_dll_nc_e_minus_l_normalized(E[0], E[1], L[0], L[1], t->spc, c->slope, c->y_intercept);
+    t->code_error_filt_chips = oracle_loop_filter_apply(&t->lf, (float)t->code_error_chips);
+    t->code_freq_chips = c->code_chip_rate - t->code_error_filt_chips;
+    if (c->carrier_aiding) t->code_freq_chips += t->carrier_doppler_hz * c->code_chip_rate / c->signal_carrier_freq;
+}
+
+/* push_back on boost::circular_buffer<std::pair<double,double>> of capacity cap (pairs stored flat) */
+static void hist_push(double* h, int* size, int cap, double first, double second)
+{
+    if (*size == cap)
+        {
+            memmove(h, h + 2, sizeof(double) * 2 * (size_t)(cap - 1));
+            (*size)--;
+        }
+    h[2 * *size] = first;
+    h[2 * *size + 1] = second;
+    (*size)++;
+}
+
+/* the smoothed rate of a history (:1236-1251, :1268-1283) */
+static double hist_rate(const double* h, unsigned int L)
+{
+    double tmp_cp1 = 0.0, tmp_cp2 = 0.0, tmp_samples = 0.0;
+    for (unsigned int k = 0; k < L; k++)
+        {
+            tmp_cp1 += h[2 * k];
+            tmp_cp2 += h[2 * (L * 2 - k - 1)];
+            tmp_samples += h[2 * (L * 2 - k - 1) + 1];
+        }
+    tmp_cp1 /= (double)L;
+    tmp_cp2 /= (double)L;
+    return (tmp_cp2 - tmp_cp1) / tmp_samples;
+}
+
+/* update_tracking_vars (:1216-1287) */
+static void update_tracking_vars(oracle_trk* t)
+{
+    const oracle_trk_cfg* c = &t->cfg;
+    const int hist_cap = c->high_dyn ? (int)c->smoother_length * 2 : 1;
+    const double T_chip_seconds = 1.0 / t->code_freq_chips;
+    const double T_prn_seconds = T_chip_seconds * (double)c->code_length_chips;
+    const double T_prn_samples = T_prn_seconds * c->fs_in;
+    const double K_blk_samples = T_prn_samples + t->rem_code_phase_samples;
+    t->current_prn_length_samples = (int32_t)floor(K_blk_samples);
+    const double n = (double)t->current_prn_length_samples;
+    t->carrier_phase_step_rad = TWO_PI * t->carrier_doppler_hz / c->fs_in;
+    if (c->high_dyn)
+        {
+            hist_push(t->carr_hist, &t->carr_hist_size, hist_cap, t->carrier_phase_step_rad, n);
+            if (t->carr_hist_size == hist_cap) t->carrier_phase_rate_step_rad = hist_rate(t->carr_hist, c->smoother_length);
+        }
+    t->rem_carr_phase_rad += (float)(t->carrier_phase_step_rad * n + 0.5 * t->carrier_phase_rate_step_rad * n * n);
+    t->rem_carr_phase_rad = fmod(t->rem_carr_phase_rad, TWO_PI);
+    t->acc_carrier_phase_rad -= (t->carrier_phase_step_rad * n + 0.5 * t->carrier_phase_rate_step_rad * n * n);
+    t->code_phase_step_chips = t->code_freq_chips / c->fs_in;
+    if (c->high_dyn)
+        {
+            hist_push(t->code_hist, &t->code_hist_size, hist_cap, t->code_phase_step_chips, n);
+            if (t->code_hist_size == hist_cap) t->code_phase_rate_step_chips = hist_rate(t->code_hist, c->smoother_length);
+        }
+    t->rem_code_phase_samples = K_blk_samples - n;
+    t->rem_code_phase_chips = t->code_freq_chips * t->rem_code_phase_samples / c->fs_in;
+}
+
+/* acquire_secondary (:923-966) */
+static int acquire_secondary(oracle_trk* t)
+{
+    const oracle_trk_cfg* c = &t->cfg;
+    int32_t corr_value = 0;
+    for (uint32_t i = 0; i < c->secondary_code_length; i++)
+        {
+            if (t->circ[2 * i] < 0.0)
+                corr_value += (c->secondary_code_string[i] == '0') ? 1 : -1;
+            else
+                corr_value += (c->secondary_code_string[i] == '0') ? -1 : 1;
+        }
+    if (abs(corr_value) == (int32_t)c->secondary_code_length)
+        {
+            t->pll_180 = corr_value < 0;
+            return 1;
+        }
+    return 0;
+}
+
+/* save_correlation_results (:1290-1400): outs = this epoch's VE,E,P,L,VL; prompt_data = d_Prompt_Data[0] */
+static void save_correlation_results(oracle_trk* t, const float* outs5, const float* prompt_data)
+{
+    const oracle_trk_cfg* c = &t->cfg;
+    const float sign = (c->secondary && c->secondary_code_string[t->current_symbol] != '0') ? -1.0f : 1.0f;
+    for (int k = 0; k < 10; k++)
+        {
+            if (!c->veml && (k < 2 || k >= 8)) continue;
+            if (sign > 0)
+                t->accu[k] += outs5[k];
+            else
+                t->accu[k] -= outs5[k];
+        }
+    if (c->secondary)
+        {
+            t->current_symbol++;
+            t->current_symbol %= (int)c->secondary_code_length;
+        }
+    const float* src = c->track_pilot ? prompt_data : outs5 + 4;
+    if (c->symbols_per_bit > 1)
+        {
+            if (c->data_secondary_code_length > 0)
+                {
+                    if (c->data_secondary_code_string[t->current_data_symbol] == '0')
+                        {
+                            t->P_data_accu[0] += src[0];
+                            t->P_data_accu[1] += src[1];
+                        }
+                    else
+                        {
+                            t->P_data_accu[0] -= src[0];
+                            t->P_data_accu[1] -= src[1];
+                        }
+                    t->current_data_symbol++;
+                    t->current_data_symbol %= (int)c->data_secondary_code_length;
+                }
+            else
+                {
+                    t->P_data_accu[0] += src[0];
+                    t->P_data_accu[1] += src[1];
+                    t->current_data_symbol++;
+                    t->current_data_symbol %= (int)c->symbols_per_bit;
+                }
+        }
+    else
+        {
+            t->P_data_accu[0] = src[0];
+            t->P_data_accu[1] = src[1];
+        }
+    t->cloop = c->track_pilot ? 0 : 1;
+}
+
 int oracle_trk_run(oracle_trk* t, const float* samples_c64, uint64_t stream_start, uint64_t n_samples, int max_epochs, oracle_trk_epoch* out)
 {
     return oracle_trk_run_traced(t, samples_c64, stream_start, n_samples, max_epochs, out, NULL);
 }
 
 /* trace (optional): per epoch {rem_carr_phase_rad, carrier step, rem code phase, code step (both in code samples), first sample
-   of the epoch, 1 if the epoch ran} exactly as handed to the correlator (do_correlation_step, :1064-1089): what an open-loop
-   parity test feeds to the correlator under test. */
+   of the epoch, 1 if the epoch ran, carrier rate step, code rate step (code samples)} exactly as handed to the correlator
+   (do_correlation_step, :1064-1089): what an open-loop parity test feeds to the correlator under test. */
 int oracle_trk_run_traced(oracle_trk* t, const float* samples_c64, uint64_t stream_start, uint64_t n_samples, int max_epochs, oracle_trk_epoch* out,
     double* trace)
 {
     const oracle_trk_cfg* c = &t->cfg;
     const uint64_t stream_end = stream_start + n_samples;
     const float spc = (float)c->code_samples_per_chip;
+    const int ext = c->extend_correlation_symbols;
+    const int extended = ext > 1; /* d_enable_extended_integration */
     int done = 0;
     for (int e = 0; e < max_epochs; e++)
         {
             oracle_trk_epoch* o = &out[e];
             memset(o, 0, sizeof(*o));
-            if (!(t->state == 2 && t->cursor >= stream_start && t->cursor + 2ull * c->vector_length <= stream_end)) continue;
+            if (!(t->state >= 2 && t->cursor >= stream_start && t->cursor + 2ull * c->vector_length <= stream_end)) continue;
             const uint64_t nread = t->cursor;
+            const int state_in = t->state;
             if (t->pull_in && (uint64_t)c->pull_in_time_s < (nread - t->acq_sample_stamp) / (uint64_t)(int)c->fs_in)
                 {
                     t->pull_in = 0;
@@ -495,96 +787,160 @@ int oracle_trk_run_traced(oracle_trk* t, const float* samples_c64, uint64_t stre
                     t->code_lock_fail = 0;
                 }
             /* do_correlation_step */
-            float outs[10];
+            float outs[10], outs5[10], prompt_data[2] = {0.0f, 0.0f};
+            const float a_rem_code = (float)t->rem_code_phase_chips * spc, a_code_step = (float)t->code_phase_step_chips * spc;
+            const float a_code_rate = (float)t->code_phase_rate_step_chips * spc;
             if (trace)
                 {
-                    double* tr = trace + 6 * (size_t)e;
+                    double* tr = trace + 8 * (size_t)e;
                     tr[0] = (double)t->rem_carr_phase_rad;
                     tr[1] = (double)(float)t->carrier_phase_step_rad;
-                    tr[2] = (double)((float)t->rem_code_phase_chips * spc);
-                    tr[3] = (double)((float)t->code_phase_step_chips * spc);
+                    tr[2] = (double)a_rem_code;
+                    tr[3] = (double)a_code_step;
                     tr[4] = (double)nread;
                     tr[5] = 1.0;
+                    tr[6] = (double)(float)t->carrier_phase_rate_step_rad;
+                    tr[7] = (double)a_code_rate;
                 }
             oracle_mc_real(samples_c64 + 2 * (nread - stream_start), (int)c->vector_length, t->code, t->code_len, t->shifts, t->n_taps,
-                t->rem_carr_phase_rad, (float)t->carrier_phase_step_rad, 0.0f, (float)t->rem_code_phase_chips * spc, (float)t->code_phase_step_chips * spc,
-                0.0f * spc, 0, 0, outs);
-            const float *VE = NULL, *VL = NULL, *E, *P, *L;
-            if (c->veml)
+                t->rem_carr_phase_rad, (float)t->carrier_phase_step_rad, (float)t->carrier_phase_rate_step_rad, a_rem_code, a_code_step, a_code_rate,
+                c->high_dyn, 0, outs);
+            if (c->track_pilot && t->data_code)
                 {
-                    VE = outs;
-                    E = outs + 2;
-                    P = outs + 4;
-                    L = outs + 6;
-                    VL = outs + 8;
+                    const float prompt_shift = t->shifts[c->veml ? 2 : 1]; /* d_prompt_data_shift */
+                    oracle_mc_real(samples_c64 + 2 * (nread - stream_start), (int)c->vector_length, t->data_code, t->data_code_len, &prompt_shift, 1,
+                        t->rem_carr_phase_rad, (float)t->carrier_phase_step_rad, (float)t->carrier_phase_rate_step_rad, a_rem_code, a_code_step, a_code_rate,
+                        c->high_dyn, 0, prompt_data);
                 }
-            else
-                {
-                    E = outs;
-                    P = outs + 2;
-                    L = outs + 4;
-                }
+            memset(outs5, 0, sizeof(outs5));
+            memcpy(outs5 + (c->veml ? 0 : 2), outs, sizeof(float) * 2 * (size_t)t->n_taps);
             o->flags = 1u;
-            const int lock_ok = cn0_and_tracking_lock_status(t, P, c->code_period_s);
+            int lock_ok = 1, symbol_out = 0;
+            if (state_in == 2)
+                {
+                    memcpy(t->accu, outs5, sizeof(outs5)); /* d_VE_accu = *d_Very_Early ... (:1849-1856) */
+                    t->spc = c->early_late_space_chips;
+                    if (c->symbol_sync && (uint64_t)c->bit_synchronization_time_limit_s < (nread - t->acq_sample_stamp) / (uint64_t)(int)c->fs_in)
+                        t->carrier_lock_fail = 300000;
+                    lock_ok = cn0_and_tracking_lock_status(t, t->accu + 4, c->code_period_s);
+                    memcpy(o->accu, t->accu, sizeof(t->accu));
+                    if (lock_ok)
+                        {
+                            run_dll_pll(t);
+                            update_tracking_vars(t);
+                            if (c->symbol_sync)
+                                {
+                                    int next_state = 0;
+                                    if (!t->pull_in)
+                                        {
+                                            if (c->secondary || c->symbols_per_bit > 1)
+                                                {
+                                                    const int cap = (int)c->secondary_code_length;
+                                                    if (t->circ_size == cap)
+                                                        {
+                                                            memmove(t->circ, t->circ + 2, sizeof(float) * 2 * (size_t)(cap - 1));
+                                                            t->circ_size--;
+                                                        }
+                                                    t->circ[2 * t->circ_size] = outs5[4];
+                                                    t->circ[2 * t->circ_size + 1] = outs5[5];
+                                                    t->circ_size++;
+                                                    if (t->circ_size == cap) next_state = acquire_secondary(t);
+                                                }
+                                            else
+                                                next_state = 1;
+                                        }
+                                    if (next_state)
+                                        {
+                                            memset(t->accu, 0, sizeof(t->accu));
+                                            t->P_data_accu[0] = t->P_data_accu[1] = 0.0f;
+                                            t->circ_size = 0;
+                                            t->current_symbol = t->current_data_symbol = 0;
+                                            if (extended)
+                                                {
+                                                    t->extend_count = 0;
+                                                    t->current_correlation_time_s = (double)((float)ext * (float)c->code_period_s);
+                                                    t->state = 3;
+                                                    /* set_update_interval + set_noise_bandwidth: new coefficients, the filter memory stays */
+                                                    oracle_loop_filter lf_new;
+                                                    oracle_loop_filter_init(&lf_new, (float)t->current_correlation_time_s, c->dll_bw_narrow_hz, c->dll_filter_order, 0);
+                                                    memcpy(t->lf.in_coef, lf_new.in_coef, sizeof(lf_new.in_coef));
+                                                    memcpy(t->lf.out_coef, lf_new.out_coef, sizeof(lf_new.out_coef));
+                                                    t->lf.n_in = lf_new.n_in;
+                                                    t->lf.n_out = lf_new.n_out;
+                                                    {
+                                                        const float w = t->cf.pll_w, x = t->cf.pll_x;
+                                                        oracle_carrier_filter_set_params(&t->cf, c->fll_bw_hz, c->pll_bw_narrow_hz, c->pll_filter_order);
+                                                        t->cf.pll_w = w;
+                                                        t->cf.pll_x = x;
+                                                    }
+                                                    if (c->veml)
+                                                        {
+                                                            t->shifts[0] = -c->very_early_late_space_narrow_chips * spc;
+                                                            t->shifts[1] = -c->early_late_space_narrow_chips * spc;
+                                                            t->shifts[3] = c->early_late_space_narrow_chips * spc;
+                                                            t->shifts[4] = c->very_early_late_space_narrow_chips * spc;
+                                                        }
+                                                    else
+                                                        {
+                                                            t->shifts[0] = -c->early_late_space_narrow_chips * spc;
+                                                            t->shifts[2] = c->early_late_space_narrow_chips * spc;
+                                                        }
+                                                    t->spc = c->early_late_space_narrow_chips;
+                                                }
+                                            else
+                                                t->state = 4;
+                                        }
+                                }
+                        }
+                }
+            else if (state_in == 3)
+                {
+                    save_correlation_results(t, outs5, prompt_data);
+                    memcpy(o->accu, t->accu, sizeof(t->accu));
+                    update_tracking_vars(t);
+                    if (t->current_data_symbol == 0) symbol_out = 1;
+                    t->extend_count++;
+                    if (t->extend_count == ext - 1)
+                        {
+                            t->extend_count = 0;
+                            t->state = 4;
+                        }
+                }
+            else /* 4 */
+                {
+                    save_correlation_results(t, outs5, prompt_data);
+                    memcpy(o->accu, t->accu, sizeof(t->accu));
+                    lock_ok = cn0_and_tracking_lock_status(t, t->accu + 4, c->code_period_s * (double)ext);
+                    if (lock_ok)
+                        {
+                            run_dll_pll(t);
+                            update_tracking_vars(t);
+                            if (!t->acc_carrier_phase_initialized) /* check_carrier_phase_coherent_initialization (:1184-1190) */
+                                {
+                                    t->acc_carrier_phase_rad = -t->rem_carr_phase_rad;
+                                    t->acc_carrier_phase_initialized = 1;
+                                }
+                            if (t->current_data_symbol == 0) symbol_out = 1;
+                            memset(t->accu, 0, sizeof(t->accu));
+                            if (extended) t->state = 3;
+                        }
+                }
             if (t->pull_in) o->flags |= 2u;
             if (!lock_ok)
                 {
+                    clear_tracking_vars(t);
                     t->state = 0;
-                    t->P_old[0] = t->P_old[1] = 0.0f;
-                    t->carr_phase_error_hz = t->carr_freq_error_hz = t->carr_error_filt_hz = 0.0;
-                    t->code_error_chips = t->code_error_filt_chips = 0.0;
                     o->flags |= 4u;
                 }
-            else
+            if (symbol_out)
                 {
-                    /* run_dll_pll */
-                    const double T_s = c->code_period_s; /* d_current_correlation_time_s */
-                    t->carr_phase_error_hz = oracle_pll_cloop_two_quadrant_atan(P[0], P[1]) / TWO_PI;
-                    if ((t->pull_in && c->enable_fll_pull_in) || c->enable_fll_steady_state)
-                        {
-                            t->carr_freq_error_hz = oracle_fll_diff_atan(t->P_old[0], t->P_old[1], P[0], P[1], 0, T_s) / TWO_PI;
-                            t->P_old[0] = P[0];
-                            t->P_old[1] = P[1];
-                            if (t->pull_in && c->enable_fll_pull_in)
-                                t->carr_error_filt_hz = oracle_carrier_filter_get_carrier_error(&t->cf, (float)t->carr_freq_error_hz, 0.0F, (float)T_s);
-                            else
-                                t->carr_error_filt_hz = oracle_carrier_filter_get_carrier_error(&t->cf, (float)t->carr_freq_error_hz, (float)t->carr_phase_error_hz, (float)T_s);
-                        }
-                    else
-                        {
-                            t->carr_error_filt_hz = oracle_carrier_filter_get_carrier_error(&t->cf, 0, (float)t->carr_phase_error_hz, (float)T_s);
-                        }
-                    t->carrier_doppler_hz = t->carr_error_filt_hz;
-                    if (c->veml)
-                        t->code_error_chips = oracle_dll_nc_vemlp_normalized(VE, E, L, VL);
-                    else
-                        t->code_error_chips = oracle_dll_nc_e_minus_l_normalized(E[0], E[1], L[0], L[1], c->early_late_space_chips, c->slope, c->y_intercept);
-                    t->code_error_filt_chips = oracle_loop_filter_apply(&t->lf, (float)t->code_error_chips);
-                    t->code_freq_chips = c->code_chip_rate - t->code_error_filt_chips;
-                    if (c->carrier_aiding) t->code_freq_chips += t->carrier_doppler_hz * c->code_chip_rate / c->signal_carrier_freq;
-                    /* update_tracking_vars */
-                    const double T_chip_seconds = 1.0 / t->code_freq_chips;
-                    const double T_prn_seconds = T_chip_seconds * (double)c->code_length_chips;
-                    const double T_prn_samples = T_prn_seconds * c->fs_in;
-                    const double K_blk_samples = T_prn_samples + t->rem_code_phase_samples;
-                    t->current_prn_length_samples = (int32_t)floor(K_blk_samples);
-                    t->carrier_phase_step_rad = TWO_PI * t->carrier_doppler_hz / c->fs_in;
-                    const double carrier_phase_rate_step_rad = 0.0;
-                    t->rem_carr_phase_rad += (float)(t->carrier_phase_step_rad * (double)t->current_prn_length_samples +
-                                                     0.5 * carrier_phase_rate_step_rad * (double)t->current_prn_length_samples * (double)t->current_prn_length_samples);
-                    t->rem_carr_phase_rad = fmod(t->rem_carr_phase_rad, TWO_PI);
-                    t->acc_carrier_phase_rad -= (t->carrier_phase_step_rad * (double)t->current_prn_length_samples +
-                                                 0.5 * carrier_phase_rate_step_rad * (double)t->current_prn_length_samples * (double)t->current_prn_length_samples);
-                    t->code_phase_step_chips = t->code_freq_chips / c->fs_in;
-                    t->rem_code_phase_samples = K_blk_samples - (double)t->current_prn_length_samples;
-                    t->rem_code_phase_chips = t->code_freq_chips * t->rem_code_phase_samples / c->fs_in;
+                    o->flags |= 8u;
+                    o->prompt_data[0] = t->P_data_accu[0];
+                    o->prompt_data[1] = t->P_data_accu[1];
+                    t->P_data_accu[0] = t->P_data_accu[1] = 0.0f;
                 }
-            const int base = c->veml ? 0 : 1;
-            for (int k = 0; k < t->n_taps; k++)
-                {
-                    o->corr[2 * (base + k)] = outs[2 * k];
-                    o->corr[2 * (base + k) + 1] = outs[2 * k + 1];
-                }
+            if (t->pll_180) o->flags |= 16u;
+            memcpy(o->corr, outs5, sizeof(outs5));
             o->carrier_doppler_hz = t->carrier_doppler_hz;
             o->code_freq_chips = t->code_freq_chips;
             o->carr_error_hz = t->carr_phase_error_hz;
@@ -598,6 +954,7 @@ int oracle_trk_run_traced(oracle_trk* t, const float* samples_c64, uint64_t stre
             o->evm = t->evm;
             o->sample_counter = nread;
             o->prn_length_samples = t->current_prn_length_samples;
+            o->state = state_in;
             t->cursor += (uint64_t)t->current_prn_length_samples; /* consume_each */
             done++;
         }

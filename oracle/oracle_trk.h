@@ -27,6 +27,14 @@ extern "C"
         int32_t cn0_smoother_samples, carrier_lock_test_smoother_samples;
         uint32_t max_channels;
         int32_t device;
+        /* symbol synchronisation, extended integration, pilot tracking, high dynamics (all 0: the state-2 loop only) */
+        int32_t symbol_sync, secondary;
+        uint32_t secondary_code_length, symbols_per_bit, data_secondary_code_length;
+        int32_t extend_correlation_symbols, track_pilot;
+        float pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_narrow_chips, very_early_late_space_narrow_chips;
+        int32_t high_dyn;
+        uint32_t smoother_length, bit_synchronization_time_limit_s;
+        char secondary_code_string[208], data_secondary_code_string[112];
     } oracle_trk_cfg;
 
     /* same layout as gnss_b200_trk_epoch */
@@ -39,6 +47,10 @@ extern "C"
         uint64_t sample_counter;
         int32_t prn_length_samples;
         uint32_t flags;
+        float accu[10];       /* d_VE_accu .. d_VL_accu as the loop of this epoch saw them */
+        float prompt_data[2]; /* d_P_data_accu handed to the telemetry decoder (flag 8) */
+        int32_t state;        /* d_state the epoch ran in */
+        int32_t reserved;
     } oracle_trk_epoch;
 
     typedef struct
@@ -71,6 +83,8 @@ extern "C"
     float oracle_smoother_smooth(oracle_smoother* s, float raw);
     double oracle_fll_diff_atan(float s1_re, float s1_im, float s2_re, float s2_im, double t1, double t2);
     double oracle_pll_cloop_two_quadrant_atan(float re, float im);
+    double oracle_pll_four_quadrant_atan(float re, float im);
+    float oracle_fast_atan2f(float y, float x);
     double oracle_dll_nc_e_minus_l_normalized(float e_re, float e_im, float l_re, float l_im, float spc, float slope, float y_intercept);
     double oracle_dll_nc_vemlp_normalized(const float* ve, const float* e, const float* l, const float* vl);
     float oracle_cn0_m2m4_estimator(const float* prompt_c64, int length, float coh_integration_time_s);
@@ -80,10 +94,11 @@ extern "C"
     oracle_trk* oracle_trk_create(const oracle_trk_cfg* cfg);
     void oracle_trk_destroy(oracle_trk* t);
     void oracle_trk_set_code(oracle_trk* t, const float* code, int code_len);
+    void oracle_trk_set_data_code(oracle_trk* t, const float* code, int code_len); /* d_data_code (track_pilot) */
     void oracle_trk_start(oracle_trk* t, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t now_sample);
     /* out[max_epochs]; returns the number of epochs that ran */
     int oracle_trk_run(oracle_trk* t, const float* samples_c64, uint64_t stream_start, uint64_t n_samples, int max_epochs, oracle_trk_epoch* out);
-    /* same, and trace[max_epochs][6] = the correlator arguments of every epoch (NULL: no trace) */
+    /* same, and trace[max_epochs][8] = the correlator arguments of every epoch (NULL: no trace) */
     int oracle_trk_run_traced(oracle_trk* t, const float* samples_c64, uint64_t stream_start, uint64_t n_samples, int max_epochs, oracle_trk_epoch* out,
         double* trace);
 

@@ -154,3 +154,92 @@ def test_closed_loop_converges_on_injected_signal(oracle, oracle_mod, system, ve
     period = fs * code_len / t["code_rate"]
     assert np.all(np.abs(np.mod(tail["sample_counter"].astype(np.float64) - tail["rem_code_phase_samples"] * 0 - t["delay"] + period / 2, period) - period / 2) < 2.5)
     trk.close()
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# the symbol machine: secondary-code lock (state 2) -> coherent extension (state 3) -> narrow tracking (state 4), pilot + data
+# ------------------------------------------------------------------------------------------------------------------------
+def pilot_cfg(cfg_cls, kind, fs, carrier, ext, high_dyn=False, max_channels=1, device=0):
+    """Dll_Pll_Conf as the reference's adapters set it for pilot tracking (gps_l5_dll_pll_tracking.cc, galileo_e1_dll_pll_veml_tracking.cc)
+    plus the per-signal constants of the block's constructor (dll_pll_veml_tracking.cc:211-245, :261-286)."""
+    if kind == "gps_l5":
+        chip_rate, code_len, spc, veml = 10.23e6, 10230, 1, 0
+        sec, dsec, spb = synth.SECONDARY["gps_l5q"], synth.SECONDARY["gps_l5i"], 10
+    else:
+        chip_rate, code_len, spc, veml = 1.023e6, 4092, 2, 1
+        sec, dsec, spb = synth.SECONDARY["gal_e1c"], "", 1
+    return cfg_cls(fs_in=fs, code_chip_rate=chip_rate, signal_carrier_freq=carrier, code_period_s=code_len / chip_rate, code_length_chips=code_len,
+                   code_samples_per_chip=spc, vector_length=int(round(fs * code_len / chip_rate)), veml=veml,
+                   early_late_space_chips=0.15 if veml else 0.5, very_early_late_space_chips=0.5, slope=1.0, y_intercept=1.0,
+                   pll_bw_hz=25.0, dll_bw_hz=2.0, fll_bw_hz=20.0, pll_filter_order=3, dll_filter_order=2, enable_fll_pull_in=1,
+                   enable_fll_steady_state=0, carrier_aiding=1, pull_in_time_s=0, cn0_samples=20, cn0_min=25, max_code_lock_fail=50,
+                   max_carrier_lock_fail=5000, carrier_lock_th=0.7, cn0_smoother_alpha=0.002, carrier_lock_test_smoother_alpha=0.002,
+                   cn0_smoother_samples=200, carrier_lock_test_smoother_samples=25, max_channels=max_channels, device=device,
+                   symbol_sync=1, secondary=1, secondary_code_length=len(sec), symbols_per_bit=spb, data_secondary_code_length=len(dsec),
+                   extend_correlation_symbols=ext, track_pilot=1, pll_bw_narrow_hz=20.0, dll_bw_narrow_hz=1.5,
+                   early_late_space_narrow_chips=0.1 if veml else 0.25, very_early_late_space_narrow_chips=0.3,
+                   high_dyn=int(high_dyn), smoother_length=10, bit_synchronization_time_limit_s=70,
+                   secondary_code_string=sec.encode(), data_secondary_code_string=dsec.encode())
+
+
+def pilot_codes(kind, prn):
+    """(d_tracking_code, d_data_code) of start_tracking() for pilot tracking (:670-700)."""
+    return ((synth.tracking_code("gps_l5q", prn), synth.tracking_code("gps_l5i", prn)) if kind == "gps_l5"
+            else (synth.tracking_code("gal_e1c", prn), synth.tracking_code("gal_e1b", prn)))
+
+
+@pytest.mark.parametrize("kind,ext,n_ms", [("gps_l5", 5, 800), ("gal_e1", 4, 1400)])
+def test_symbol_machine_pilot_tracking_with_extension(oracle, oracle_mod, kind, ext, n_ms):
+    fs = 15e6 if kind == "gps_l5" else 4e6
+    iq, t, carrier = synth.tracking_stream_pilot_data(kind, 7, fs, n_ms, seed=21, cn0=50.0, doppler=1230.0, delay=333.4)
+    cfg = pilot_cfg(oracle_mod.TrkCfg, kind, fs, carrier, ext)
+    trk = oracle.trk(cfg)
+    pilot, data = pilot_codes(kind, 7)
+    trk.set_code(pilot)
+    trk.set_data_code(data)
+    # The pull-in transitory ends after pull_in_time_s WHOLE seconds since the acquisition stamp (:1795-1803) and the symbol machine
+    # waits for it (:1888): the stream is placed 1.2 s after the stamp instead of simulating 1.2 s of signal.
+    S0 = int(1.2 * fs)
+    T_prn = fs * cfg.code_period_s
+    trk.start(acq_delay_samples=float(np.fmod(S0 + t["delay"] + 0.15, T_prn)), acq_doppler_hz=t["doppler"] - 10.0, acq_samplestamp=0, now_sample=S0 + 2000)
+    n_ep = int(n_ms / (1e3 * cfg.code_period_s)) - 3
+    ep, done = trk.run(iq, S0, n_ep)
+    ok = ep[ep["flags"] & 1 == 1]
+    assert done >= n_ep - 2 and not (ok["flags"] & 4).any()
+    assert not (ok["flags"] & 2).any()
+    st = ok["state"]
+    first3 = int(np.flatnonzero(st == 3)[0])
+    L = len(synth.SECONDARY["gps_l5q" if kind == "gps_l5" else "gal_e1c"])
+    assert np.all(st[:first3] == 2) and first3 >= L                               # the circular buffer has to fill before the first lock test
+    cyc = st[first3:first3 + 4 * ext]
+    assert list(cyc[:ext]) == [3] * (ext - 1) + [4] and np.array_equal(cyc[:ext], cyc[ext:2 * ext])   # :2021-2025, :2080-2083
+    # state 4 integrates ext secondary-wiped code periods: |P_accu| ~ ext x a single prompt, and the loop runs on it
+    s4 = ok[st == 4][5:]
+    single = np.hypot(ok["corr"][first3:, 4], ok["corr"][first3:, 5]).mean()
+    assert np.hypot(s4["accu"][:, 4], s4["accu"][:, 5]).mean() == pytest.approx(ext * single, rel=0.1)
+    assert abs(np.mean(s4["carrier_doppler_hz"][-20:]) - t["doppler"]) < 2.0
+    # pilot tracking: the four-quadrant discriminator pulls the pilot prompt onto the positive real axis (a Costas loop would accept both)
+    ang = np.arctan2(s4["accu"][-20:, 5], s4["accu"][-20:, 4])
+    assert np.cos(ang).mean() > 0.9
+    # the data component comes out of the slave correlator: one symbol per symbols_per_bit code periods, signs = transmitted symbols
+    sym = ok[(ok["flags"] & 8) != 0]
+    spb = cfg.symbols_per_bit
+    assert np.all(np.diff(np.flatnonzero((ok["flags"] & 8) != 0))[2:] == spb)
+    code_period_samples = fs * cfg.code_period_s
+    k = np.round((sym["sample_counter"].astype(np.float64) - S0 - t["delay"]) / code_period_samples).astype(int)   # code period the symbol ended in
+    want = t["symbols"][(k - t["first_period"] + (t["sec_offset"] if kind == "gps_l5" else 0)) // t["sym_len"]]
+    got = sym["prompt_data"][:, 1] if kind == "gps_l5" else sym["prompt_data"][:, 0]      # L5: data in quadrature to the pilot (d_interchange_iq)
+    sgn = np.sign(got[25:]) * want[25:]                                                    # the loop re-settles after the bandwidth switch
+    assert sgn.size >= 20 and abs(sgn.mean()) == 1.0                                       # all equal up to the global sign convention
+    trk.close()
+
+
+def test_fast_atan2f_restated_from_gnuradio(oracle):
+    """gr::fast_atan2f (pll_four_quadrant_atan, tracking_discriminators.cc:86-89): table + interpolation, documented error < 1e-5 rad."""
+    lib = _own_lib(oracle)
+    lib.oracle_fast_atan2f.restype = C.c_float
+    lib.oracle_fast_atan2f.argtypes = [C.c_float, C.c_float]
+    rng = np.random.default_rng(0)
+    for y, x in rng.standard_normal((2000, 2)):
+        assert abs(lib.oracle_fast_atan2f(y, x) - np.arctan2(np.float32(y), np.float32(x))) < 2e-5
+    assert lib.oracle_fast_atan2f(0.0, 0.0) == 0.0 and lib.oracle_fast_atan2f(1.0, 0.0) == pytest.approx(np.pi / 2, abs=1e-6)

@@ -242,6 +242,57 @@ def tracking_stream(system, prns, fs, n_ms, seed, cn0=45.0, dopplers=None, delay
     return x.astype(np.complex64), truth, carrier
 
 
+SECONDARY = {  # the reference's strings: GPS_L5.h:171-172, Galileo_E1.h:52 ('0' adds, '1' subtracts in save_correlation_results)
+    "gps_l5i": "0000110101", "gps_l5q": "00000100110101001110", "gal_e1c": "0011100000001010110110010",
+}
+
+
+def tracking_stream_pilot_data(kind, prn, fs, n_ms, seed, cn0=48.0, doppler=1500.0, delay=100.3, doppler_rate=0.0):
+    """One satellite with BOTH components, for pilot tracking with a slave data correlator:
+       kind "gps_l5": (L5I * NH10 * data(100 sps) + j * L5Q * NH20) / sqrt(2)            — pilot in quadrature
+       kind "gal_e1": (E1B * data(250 sps) - E1C * secondary25) / sqrt(2), sinBOC(1,1)   — pilot in anti-phase
+    doppler_rate [Hz/s] adds a carrier (and matching code) acceleration for the high-dynamics mode.
+    Returns (iq c64, truth dict with the transmitted symbols and the period index each starts at, carrier_hz)."""
+    data_sys, pilot_sys = {"gps_l5": ("gps_l5i", "gps_l5q"), "gal_e1": ("gal_e1b", "gal_e1c")}[kind]
+    chip_rate, code_len, _ = SYSTEMS[data_sys]
+    carrier = {"gps_l5": 1176.45e6, "gal_e1": 1575.42e6}[kind]
+    rng = np.random.default_rng(seed)
+    n = int(round(fs * 1e-3 * n_ms))
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * np.sqrt(0.5)
+    t = np.arange(n, dtype=np.float64) / fs
+    fd = doppler + doppler_rate * t                                   # instantaneous Doppler
+    carr_phase = 2.0 * np.pi * (doppler * t + 0.5 * doppler_rate * t * t)
+    phase_chips = chip_rate * ((t - delay / fs) + (doppler * t + 0.5 * doppler_rate * t * t) / carrier)
+    idx = np.floor(phase_chips).astype(np.int64)
+    period = np.floor_divide(idx, code_len)
+    p0 = int(period.min())
+    d = chips(data_sys, prn).astype(np.float64)[np.mod(idx, code_len)]
+    q = chips(pilot_sys, prn).astype(np.float64)[np.mod(idx, code_len)]
+    if kind == "gal_e1":
+        boc = np.where(np.mod(phase_chips, 1.0) < 0.5, 1.0, -1.0)
+        d, q = d * boc, q * boc
+    sec_q = np.array([1.0 if ch == "0" else -1.0 for ch in SECONDARY[pilot_sys]])
+    sec_offset = int(rng.integers(0, sec_q.size))                      # the receiver has to find it
+    q = q * sec_q[np.mod(period - p0 + sec_offset, sec_q.size)]
+    if kind == "gps_l5":
+        sec_d = np.array([1.0 if ch == "0" else -1.0 for ch in SECONDARY["gps_l5i"]])
+        sym_len = 10                                                    # code periods per data symbol, aligned with NH10 and NH20
+        d = d * sec_d[np.mod(period - p0 + sec_offset, sec_d.size)]
+        sym_index = np.floor_divide(period - p0 + sec_offset, sym_len)
+    else:
+        sym_len = 1
+        sym_index = period - p0
+    symbols = rng.integers(0, 2, int(sym_index.max()) + 2) * 2 - 1
+    d = d * symbols[sym_index]
+    amp = np.sqrt(10.0 ** (cn0 / 10.0) / fs)
+    ph0 = float(rng.uniform(0, 2 * np.pi))
+    s = (d + 1j * q) if kind == "gps_l5" else (d - q)
+    x = x + amp / np.sqrt(2.0) * s * np.exp(1j * (carr_phase + ph0))
+    truth = dict(kind=kind, prn=prn, doppler=doppler, doppler_rate=doppler_rate, delay=delay, cn0=cn0, symbols=symbols, sym_len=sym_len,
+                 sec_offset=sec_offset, first_period=p0, final_doppler=float(fd[-1]))
+    return x.astype(np.complex64), truth, carrier
+
+
 def tracking_code(system, prn):
     """d_tracking_code as start_tracking() generates it (dll_pll_veml_tracking.cc:663-700): one float per chip, or the
     sinBOC(1,1) replica at 2 samples per chip for Galileo E1 (galileo_e1_code_gen_sinboc11_float)."""
