@@ -127,7 +127,7 @@ TRK_EPOCH_DTYPE = np.dtype([("corr", np.float32, (10,)), ("carrier_doppler_hz", 
                             ("acc_carrier_phase_rad", np.float64), ("cn0_db_hz", np.float64), ("carrier_lock_test", np.float64),
                             ("evm", np.float64), ("sample_counter", np.uint64), ("prn_length_samples", np.int32), ("flags", np.uint32),
                             ("accu", np.float32, (10,)), ("prompt_data", np.float32, (2,)), ("state", np.int32), ("reserved", np.int32)], align=True)
-TRK_VALID, TRK_PULL_IN, TRK_LOSS_OF_LOCK = 1, 2, 4
+TRK_VALID, TRK_PULL_IN, TRK_LOSS_OF_LOCK, TRK_SYMBOL, TRK_PLL_180 = 1, 2, 4, 8, 16
 
 # every symbol include/gnss_b200.h declares (tests check the library exports all of them)
 EXPORTS = [
@@ -145,7 +145,7 @@ EXPORTS = [
     "gnss_b200_mc_correlate_noalloc", "gnss_b200_mc_noalloc_scratch_bytes",
     "gnss_b200_firdes_low_pass", "gnss_b200_resampler_create", "gnss_b200_resampler_destroy", "gnss_b200_resampler_reset",
     "gnss_b200_resampler_work",
-    "gnss_b200_trk_create", "gnss_b200_trk_destroy", "gnss_b200_trk_set_code", "gnss_b200_trk_start", "gnss_b200_trk_run",
+    "gnss_b200_trk_create", "gnss_b200_trk_destroy", "gnss_b200_trk_set_code", "gnss_b200_trk_set_data_code", "gnss_b200_trk_start", "gnss_b200_trk_run",
     "gnss_b200_trk_stream", "gnss_b200_trk_launch_count",
     "gnss_b200_acq_exchange_buffers", "gnss_b200_acq_finalize_gathered_async",
     "gnss_b200_acq_capture_begin", "gnss_b200_acq_capture_end", "gnss_b200_acq_replay_async",
@@ -239,6 +239,7 @@ def lib():
     L.gnss_b200_trk_create.argtypes = [C.POINTER(TrkCfg), C.POINTER(C.c_void_p)]
     L.gnss_b200_trk_destroy.argtypes = [C.c_void_p]
     L.gnss_b200_trk_set_code.argtypes = [C.c_void_p, c_u32, c_u32, _fp]
+    L.gnss_b200_trk_set_data_code.argtypes = [C.c_void_p, c_u32, c_u32, _fp]
     L.gnss_b200_trk_start.argtypes = [C.c_void_p, c_u32, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
     L.gnss_b200_trk_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, c_u32, _u32p, c_u32, C.c_void_p]
     L.gnss_b200_trk_stream.argtypes = [C.c_void_p]
@@ -614,6 +615,10 @@ class TrackingLoopB200:
     def set_code(self, ch, code):
         code = np.ascontiguousarray(code, dtype=np.float32)
         _check(self.L.gnss_b200_trk_set_code(self.h, ch, code.size, _f32p(code)))
+
+    def set_data_code(self, ch, code):
+        code = np.ascontiguousarray(code, dtype=np.float32)
+        _check(self.L.gnss_b200_trk_set_data_code(self.h, ch, code.size, _f32p(code)))
 
     def start(self, ch, acq_delay_samples, acq_doppler_hz, acq_samplestamp, now_sample):
         _check(self.L.gnss_b200_trk_start(self.h, ch, float(acq_delay_samples), float(acq_doppler_hz), int(acq_samplestamp), int(now_sample)))

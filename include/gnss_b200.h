@@ -291,14 +291,17 @@ extern "C"
     /* (f) N1: the dll_pll_veml tracking loop closed on the device          */
     /* ------------------------------------------------------------------ */
 
-    /* Per-epoch loop of dll_pll_veml_tracking::general_work, state 2 (one code period per integration, data
-       component, Costas PLL): do_correlation_step (dll_pll_veml_tracking.cc:1064-1089) ->
+    /* Per-epoch loop of dll_pll_veml_tracking::general_work: do_correlation_step (dll_pll_veml_tracking.cc:1064-1089) ->
        cn0_and_tracking_lock_status (:968-1013) -> run_dll_pll (:1092-1182) -> update_tracking_vars (:1225-1297) ->
        consume_each(d_current_prn_length_samples) (:2118), for many channels at once and for as many epochs as the
        uploaded stream holds, WITHOUT a host round trip between epochs: a loop-update kernel turns the correlator
        outputs of epoch e into the multicorrelator arguments of epoch e+1 in device memory.
-       Not covered (stay in the host block): secondary-code / bit synchronisation (:923-966), extended integration
-       (states 3-4), pilot + data correlator pairs, high-dynamics smoothing, dumps.
+       symbol_sync == 0: state 2 only (one code period per integration, Costas PLL), symbol bookkeeping on the host
+       (host/b200_symbol_sync). symbol_sync == 1: the block's whole symbol machine runs in the loop — secondary-code /
+       bit synchronisation in state 2 (:1888-1925, acquire_secondary :923-966), state 3 coherent extension
+       (:1989-2027), state 4 narrow tracking with the narrow bandwidths and taps (:1945-1975, :2028-2084),
+       save_correlation_results (:1290-1400), the slave data correlator of pilot tracking (:1078-1088) and the
+       high-dynamics rate smoothing (:1232-1284). Not covered: the experimental Doppler correction (:1162-1182), dumps.
        Field names follow Dll_Pll_Conf (dll_pll_conf.h:37-84) and the block's members (dll_pll_veml_tracking.h). */
     typedef struct
     {
@@ -324,6 +327,20 @@ extern "C"
         int32_t cn0_smoother_samples, carrier_lock_test_smoother_samples;  /* smoother initialisation lengths (<= 256) */
         uint32_t max_channels;
         int32_t device;
+        /* symbol synchronisation, extended integration, pilot tracking, high dynamics (all 0: the state-2 loop only) */
+        int32_t symbol_sync;                 /* 1: states 2 -> 3 -> 4 on the device */
+        int32_t secondary;                   /* d_secondary: the tracked component has a secondary code */
+        uint32_t secondary_code_length;      /* d_secondary_code_length (or the preamble length), <= 200 */
+        uint32_t symbols_per_bit;            /* d_symbols_per_bit */
+        uint32_t data_secondary_code_length; /* d_data_secondary_code_length, <= 100 */
+        int32_t extend_correlation_symbols;  /* Dll_Pll_Conf::extend_correlation_symbols (<= 1: no extension) */
+        int32_t track_pilot;                 /* Dll_Pll_Conf::track_pilot: second, 1-tap correlator on the data code */
+        float pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_narrow_chips, very_early_late_space_narrow_chips;
+        int32_t high_dyn;                    /* Dll_Pll_Conf::high_dyn */
+        uint32_t smoother_length;            /* Dll_Pll_Conf::smoother_length (<= 64) */
+        uint32_t bit_synchronization_time_limit_s;
+        char secondary_code_string[208];     /* d_secondary_code_string: '0' adds, anything else subtracts */
+        char data_secondary_code_string[112];
     } gnss_b200_trk_cfg;
 
     /* What one epoch leaves behind per channel: the quantities log_data() dumps (:1403-1530) and the Gnss_Synchro
@@ -340,13 +357,19 @@ extern "C"
         uint64_t sample_counter;      /* absolute index of the first sample correlated in this epoch */
         int32_t prn_length_samples;   /* samples consumed after this epoch (d_current_prn_length_samples) */
         uint32_t flags;               /* GNSS_B200_TRK_* */
+        float accu[10];               /* d_VE_accu .. d_VL_accu as the loop of this epoch saw them */
+        float prompt_data[2];         /* d_P_data_accu handed to the telemetry decoder when GNSS_B200_TRK_SYMBOL is set */
+        int32_t state;                /* d_state the epoch ran in (2, 3 or 4) */
+        int32_t reserved;
     } gnss_b200_trk_epoch;
 
     enum
     {
         GNSS_B200_TRK_VALID = 1,        /* the channel correlated in this epoch */
         GNSS_B200_TRK_PULL_IN = 2,      /* d_pull_in_transitory still set */
-        GNSS_B200_TRK_LOSS_OF_LOCK = 4  /* cn0_and_tracking_lock_status() returned false: channel went to standby */
+        GNSS_B200_TRK_LOSS_OF_LOCK = 4, /* cn0_and_tracking_lock_status() returned false: channel went to standby */
+        GNSS_B200_TRK_SYMBOL = 8,       /* Flag_valid_symbol_output: prompt_data holds a symbol (:1997-2018, :2049-2070) */
+        GNSS_B200_TRK_PLL_180 = 16      /* d_Flag_PLL_180_deg_phase_locked */
     };
 
     typedef struct gnss_b200_trk gnss_b200_trk;
@@ -355,6 +378,8 @@ extern "C"
     GNSS_B200_API int gnss_b200_trk_destroy(gnss_b200_trk* h);
     /* the tracking code of channel `ch` (d_tracking_code: code_samples_per_chip * code_length_chips floats) */
     GNSS_B200_API int gnss_b200_trk_set_code(gnss_b200_trk* h, uint32_t ch, uint32_t code_len, const float* code);
+    /* the data-component code of channel `ch` for pilot tracking (d_data_code, :670-700); same length as the tracking code */
+    GNSS_B200_API int gnss_b200_trk_set_data_code(gnss_b200_trk* h, uint32_t ch, uint32_t code_len, const float* code);
     /* start_tracking() (:640-880) + the state-1 alignment (:1812-1845): `now_sample` is the absolute index of the next
        unread stream sample (nitems_read(0)); the channel's read cursor is moved to the next code-period start. */
     GNSS_B200_API int gnss_b200_trk_start(gnss_b200_trk* h, uint32_t ch, double acq_delay_samples, double acq_doppler_hz,

@@ -210,3 +210,92 @@ def test_open_loop_every_epoch_meets_1e4(b200, oracle, oracle_mod, system, veml)
         err = np.abs(got - w) / scale
         assert err.max() < 1e-4, (system, p, float(err.max()), int(err.argmax()))
         mc.close()
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# the symbol machine on the device: secondary-code lock, state 3 / 4 extended integration, pilot + data pair, high dynamics
+# ------------------------------------------------------------------------------------------------------------------------
+def _pilot_pair(b200, oracle_mod, kind, fs, carrier, ext, n_ch, **kw):
+    from test_oracle_trk import pilot_cfg
+    o = pilot_cfg(oracle_mod.TrkCfg, kind, fs, carrier, ext)
+    for k, v in kw.items():
+        setattr(o, k, v)
+    g = b200.TrkCfg()
+    for name, _ in o._fields_:
+        setattr(g, name, getattr(o, name))
+    g.max_channels = n_ch
+    return g, o
+
+
+def _compare_symbol_machine(gpu, want, n_min, ext):
+    ok = want["flags"] & 1 == 1
+    assert ok.sum() >= n_min
+    assert np.array_equal(gpu["flags"], want["flags"])                     # valid / pull-in / loss / SYMBOL / PLL_180 bits, every epoch
+    assert np.array_equal(gpu["state"], want["state"])                     # the same epochs run in state 2, 3, 4
+    assert np.array_equal(gpu["sample_counter"][ok], want["sample_counter"][ok])
+    assert np.array_equal(gpu["prn_length_samples"][ok], want["prn_length_samples"][ok])
+    scale = np.abs(want["corr"][ok][:, 4] + 1j * want["corr"][ok][:, 5]).mean()
+    d = np.abs(gpu["corr"][ok] - want["corr"][ok]).max(axis=1)
+    # Two closed loops: until the first chip-boundary sample flips between them (see _compare) they agree to ~1e-5 |P|; afterwards the
+    # narrow loops (long memory) keep the two NCO phases a few mrad apart, i.e. a few units on |P| ~ 1700 — the same size as in
+    # _compare, only persistent. Strict bar on the wide-loop epochs before the secondary-code lock, the flip-sized bar afterwards.
+    wide = want["state"][ok] == 2
+    assert np.median(d[wide]) <= 3e-4 * scale
+    assert np.median(d) <= 3e-3 * scale and d.max() <= 24.0
+    da = np.abs(gpu["accu"][ok] - want["accu"][ok]).max(axis=1)            # the accumulators the loop runs on (ext code periods)
+    assert np.median(da) <= 3e-3 * ext * scale and da.max() <= 24.0 * ext
+    sym = (want["flags"] & 8) != 0
+    assert sym.sum() >= 10
+    dp = np.abs(gpu["prompt_data"][sym] - want["prompt_data"][sym]).max(axis=1)
+    assert np.median(dp) <= 3e-3 * scale * ext and dp.max() <= 24.0 * ext
+    big = np.abs(want["prompt_data"][sym]).max(axis=1) > 0.3 * scale
+    k = np.argmax(np.abs(want["prompt_data"][sym][big]), axis=1)
+    assert np.array_equal(np.sign(np.take_along_axis(gpu["prompt_data"][sym][big], k[:, None], 1)), np.sign(np.take_along_axis(want["prompt_data"][sym][big], k[:, None], 1)))
+    assert np.abs(gpu["carrier_doppler_hz"][ok] - want["carrier_doppler_hz"][ok]).max() <= 0.1
+    assert np.median(np.abs(gpu["carrier_doppler_hz"][ok] - want["carrier_doppler_hz"][ok])) <= 1e-2
+    assert np.abs(gpu["code_freq_chips"][ok] - want["code_freq_chips"][ok]).max() <= 0.05
+    assert np.abs(gpu["rem_code_phase_samples"][ok] - want["rem_code_phase_samples"][ok]).max() <= 2e-3
+    assert np.abs(gpu["acc_carrier_phase_rad"][ok] - want["acc_carrier_phase_rad"][ok]).max() <= 1e-2
+    assert np.abs(gpu["cn0_db_hz"][ok] - want["cn0_db_hz"][ok]).max() <= 0.3      # M2M4 on accumulators: sqrt(2 m2^2 - m4) amplifies the mrad-level phase difference
+
+
+@pytest.mark.parametrize("kind,ext,n_ms,high_dyn", [("gps_l5", 5, 500, 0), ("gal_e1", 4, 1000, 0), ("gps_l5", 2, 400, 1)])
+def test_symbol_machine_trajectories_match_oracle(b200, oracle, oracle_mod, kind, ext, n_ms, high_dyn):
+    """Pilot tracking as the reference defaults for Galileo E1 and GPS L5: secondary-code lock on the pilot in state 2, then
+    3,..,3,4 cycles of `ext` secondary-wiped code periods with the narrow bandwidths and taps, four-quadrant PLL, the data
+    component from the slave correlator — device loop against the oracle, epoch by epoch. high_dyn: the rate-aware resampler
+    and rotator with the smoothed carrier / code rates (:1232-1284) on a 300 Hz/s signal."""
+    from test_oracle_trk import pilot_codes
+    fs = 15e6 if kind == "gps_l5" else 4e6
+    rate = 300.0 if high_dyn else 0.0
+    sats = [(7, 1230.0, 333.4), (11, -2210.5, 4001.7)]
+    streams = [synth.tracking_stream_pilot_data(kind, p, fs, n_ms, seed=30 + p, cn0=50.0, doppler=d, delay=dl, doppler_rate=rate) for p, d, dl in sats]
+    iq = (streams[0][0] + streams[1][0]).astype(np.complex64)             # two satellites in one stream (noise adds up: 3 dB less C/N0)
+    carrier = streams[0][2]
+    g, o = _pilot_pair(b200, oracle_mod, kind, fs, carrier, ext, len(sats), high_dyn=high_dyn, smoother_length=5)
+    S0 = int(1.2 * fs)                                                     # the pull-in transitory is over (see tests/test_oracle_trk.py)
+    T_prn = fs * g.code_period_s
+    n_ep = int(n_ms / (1e3 * g.code_period_s)) - 3
+    trk = b200.TrackingLoopB200(g)
+    for c, (p, d, dl) in enumerate(sats):
+        pilot, data = pilot_codes(kind, p)
+        trk.set_code(c, pilot)
+        trk.set_data_code(c, data)
+        trk.start(c, float(np.fmod(S0 + dl + 0.15, T_prn)), d - 10.0, 0, S0 + 2000)
+    got = trk.run(iq, S0, np.arange(len(sats)), n_ep)
+    for c, (p, d, dl) in enumerate(sats):
+        ot = oracle.trk(o)
+        pilot, data = pilot_codes(kind, p)
+        ot.set_code(pilot)
+        ot.set_data_code(data)
+        ot.start(float(np.fmod(S0 + dl + 0.15, T_prn)), d - 10.0, 0, S0 + 2000)
+        want, done = ot.run(iq, S0, n_ep)
+        _compare_symbol_machine(got[:, c], want, n_ep - 3, ext)
+        st = want["state"][want["flags"] & 1 == 1]
+        assert (st == 4).sum() >= 20 and (st == 3).sum() >= 20 * (ext - 1)     # the extended correlator really ran
+        if high_dyn:
+            tail = got[:, c][got[:, c]["flags"] & 1 == 1][-20:]
+            assert tail["carrier_doppler_hz"].mean() - d > 0.5 * rate * n_ms * 1e-3          # climbs with the 300 Hz/s ramp (the reference's loop lags it)
+        ot.close()
+    assert trk.launch_count() == 3 * n_ep + 1                              # tracking taps + data prompt + loop update per epoch
+    trk.close()
