@@ -39,6 +39,7 @@ struct gnss_b200_acq
     gnss_b200_acq_cfg cfg{};
     uint32_t N = 0, consumed = 0, eff = 0, nD = 0, nD_local = 0, row_begin = 0;
     uint32_t code_len = 0, code_off = 0, mag_offset = 0;
+    bool padded = false;  // the transform length is a supported M >= 2 * fft_size - 1 (fft_size has a prime factor the kernels cannot take)
     FftPlan plan;
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;  // last inverse stage of chunk i overlaps the first stage of chunk i+1
@@ -130,6 +131,8 @@ int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
             a.codes_td = h->d_codes_td.as<float2>();
             a.code_len = h->code_len;
             a.code_off = h->code_off;
+            a.code_wrap = h->padded ? 1u : 0u;
+            a.code_scale = h->padded ? (float)((double)h->cfg.fft_size / (double)h->N) : 1.0f;
             a.slots = d_slots;
             a.out_buf = h->d_cbuf.as<float2>();
             a.out_by_slot = 1;
@@ -145,6 +148,8 @@ int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
             a.codes_td = h->d_codes_td.as<float2>();
             a.code_len = h->code_len;
             a.code_off = h->code_off;
+            a.code_wrap = h->padded ? 1u : 0u;
+            a.code_scale = h->padded ? (float)((double)h->cfg.fft_size / (double)h->N) : 1.0f;
             a.y0 = y0;
             a.out_buf = h->d_scratch.as<float2>();
             a.out_y0 = y0;
@@ -670,8 +675,36 @@ int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, 
         const char* why = nullptr;
         if (!make_fft_plan(h->N, kMaxSingleStagePoints, &h->plan, &why))
             {
-                delete h;
-                return fail(GNSS_B200_ERR_UNSUPPORTED, "acq_create: fft_size %u: %s", cfg->fft_size, why ? why : "unsupported");
+                // A length the mixed-radix kernels cannot take (a prime factor > 127; FFTW in the reference takes any d_fft_size,
+                // pcps_acquisition.cc:85-92,114-115). The search needs the CYCLIC correlation of length n = fft_size,
+                //     y[m] = sum_i x[i] conj(c[(i - m) mod n]),  0 <= m < n,
+                // which a cyclic correlation of any length M >= 2n - 1 also produces when the samples are zero-padded to M and the
+                // code buffer holds c at its start AND again at its end (indices i - m < 0 then wrap onto the tail copy): the
+                // engine runs on the smallest M = 2^a 3^b 5^c it has a plan for, searches the first n lags, and scales the code by
+                // n / M so that magnitudes equal those of unnormalised length-n transforms.
+                const bool can_pad = !cfg->bit_transition && cfg->fft_size == cfg->consumed_samples;
+                uint32_t best_m = 0;
+                if (can_pad)
+                    for (uint64_t p2 = 1; p2 <= (1ull << 31); p2 *= 2)
+                        for (uint64_t p3 = p2; p3 <= (1ull << 31); p3 *= 3)
+                            for (uint64_t p5 = p3; p5 <= (1ull << 31); p5 *= 5)
+                                if (p5 >= 2ull * cfg->fft_size - 1 && (best_m == 0 || p5 < best_m))
+                                    {
+                                        FftPlan trial;
+                                        const char* w2 = nullptr;
+                                        if (make_fft_plan((uint32_t)p5, kMaxSingleStagePoints, &trial, &w2)) best_m = (uint32_t)p5;
+                                    }
+                if (!best_m || !make_fft_plan(best_m, kMaxSingleStagePoints, &h->plan, &why))
+                    {
+                        delete h;
+                        return fail(GNSS_B200_ERR_UNSUPPORTED, "acq_create: fft_size %u: %s", cfg->fft_size, why ? why : "unsupported");
+                    }
+                h->padded = true;
+                h->N = best_m;
+                h->eff = cfg->fft_size;
+                h->mag_offset = 0;
+                h->code_len = h->consumed;
+                h->code_off = 0;
             }
         h->center.assign(cfg->max_slots, 0);
         h->bias.assign(cfg->max_slots, 0);

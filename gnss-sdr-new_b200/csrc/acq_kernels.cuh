@@ -80,6 +80,8 @@ struct StageArgs
     const float2* codes_td;  // [transform][code_len]
     uint32_t code_len;
     uint32_t code_off;       // first position of the code inside the padded buffer
+    uint32_t code_wrap;      // != 0: a second copy of the code ends the buffer (cyclic correlation of a shorter length, see acq.cu create_impl)
+    float code_scale;        // factor on the code samples (1 unless code_wrap)
     // ---- LOAD_BUF / LOAD_PRODUCT ----
     const float2* in_buf;    // LOAD_BUF: [transform - in_y0][N]; LOAD_PRODUCT: X [call group][nD_local][N]
     const float2* cbuf;      // code spectra [slot][N]
@@ -196,7 +198,13 @@ __global__ void __launch_bounds__(512) stage_kernel(const StageArgs a)
                 {
                     const uint32_t idx = i / C, c = i - idx * C;
                     const uint32_t pos = idx * st.pos_stride + tile_off + c;
-                    s[i] = (pos >= a.code_off && pos - a.code_off < a.code_len) ? __ldg(code + (pos - a.code_off)) : make_float2(0.f, 0.f);
+                    float2 v = make_float2(0.f, 0.f);
+                    if (pos >= a.code_off && pos - a.code_off < a.code_len)
+                        v = __ldg(code + (pos - a.code_off));
+                    else if (a.code_wrap && pos >= (uint32_t)N - a.code_len)
+                        v = __ldg(code + (pos - ((uint32_t)N - a.code_len)));
+                    if (a.code_wrap) v = make_float2(v.x * a.code_scale, v.y * a.code_scale);
+                    s[i] = v;
                 }
         }
     else if constexpr (LOAD == LOAD_BUF)

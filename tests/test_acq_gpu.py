@@ -127,6 +127,35 @@ def test_dwell_lengths_with_the_prime_31(b200, oracle, name):
     assert det_g == det_o and det_o and det_o <= {t["prn"] for t in truth}
 
 
+@pytest.mark.parametrize("fs,n_dwells", [(5003000, 1), (4146000, 2), (2053000, 1)])
+def test_lengths_with_a_large_prime_factor(b200, oracle, fs, n_dwells):
+    """d_fft_size = fs * 1 ms with a prime factor the mixed-radix kernels do not take (5003 is prime, 4146 = 2 * 3 * 691,
+    2053 is prime): the reference's FFTW plan takes any length (pcps_acquisition.cc:85-92). The engine computes the same cyclic
+    correlation on a padded length (acq.cu, create_impl) — results against the oracle's any-length DFT: statistic, peak, grid,
+    exact cell."""
+    n = fs // 1000
+    prns = [3, 9, 17, 25]
+    sats = [dict(system="gps_l1_ca", prn=3, delay=1234, doppler=1830.0, cn0=47.0), dict(system="gps_l1_ca", prn=17, delay=n - 7, doppler=-3320.0, cn0=45.0)]
+    iq = synth.make_iq(n * n_dwells, fs, sats, seed=fs % 997)
+    codes = np.stack([synth.local_code("gps_l1_ca", p, fs)[:n] for p in prns])
+    geo = dict(fft_size=n, consumed_samples=n, doppler_max=5000, doppler_step=250, fs=fs, samples_per_chip=int(np.ceil(fs / 1.023e6)), samples_per_code=float(n))
+    e = _gpu_engine(b200, geo, len(prns), use_cfar=True, keep_grid=True)
+    e.set_local_codes(np.arange(len(prns)), codes)
+    blocks = [iq[k * n:(k + 1) * n] for k in range(n_dwells)]
+    for blk in blocks:
+        got = e.dwell(blk, np.arange(len(prns)))
+    want, grids = _oracle_search(oracle, geo, codes, blocks, keep=True)
+    thr = oracle.threshold(0.001, n, e.n_doppler)
+    for p in range(len(prns)):
+        _compare(got[p], want[p][-1], thr=thr, strict_idx=False)
+        g = e.read_grid(p)
+        assert g.shape == grids[p].shape and np.abs(g - grids[p]).max() <= RTOL * grids[p].max()
+    for k, p in ((0, 3), (2, 17)):
+        assert got[k]["test_statistic"] > thr and int(got[k]["code_phase"]) == want[k][-1]["code_phase"] and int(got[k]["doppler_hz"]) == want[k][-1]["doppler_hz"]
+    assert got[1]["test_statistic"] < thr and got[3]["test_statistic"] < thr
+    e.close()
+
+
 def test_config2_two_stage_plan(b200, oracle):
     """BASELINE config 2 geometry (Galileo E1, 8 MS/s, 4 ms, N = 32000 -> two-stage FFT), 6 of the 50 PRNs against the oracle."""
     geo, codes, iq, truth = synth.config_scene("C2", n_prn=50)
@@ -292,7 +321,8 @@ def test_row_sharding_merge(b200, oracle):
 
 def test_unsupported_and_state_errors(b200):
     with pytest.raises(b200.B200Error):
-        b200.PcpsAcquisitionB200(2056, 2056, 5000, 250, 2.056e6, 3, 1)  # 257 | 2056: beyond the direct-DFT pass
+        b200.PcpsAcquisitionB200(2 * 2056, 2056, 5000, 250, 2.056e6, 3, 1, bit_transition=True)  # 257 | 4112 and bit_transition: no padded form
+    b200.PcpsAcquisitionB200(2056, 2056, 5000, 250, 2.056e6, 3, 1).close()                       # 257 | 2056 alone: padded correlation
     e = b200.PcpsAcquisitionB200(4000, 4000, 5000, 250, 4e6, 4, 2)
     with pytest.raises(b200.B200Error):
         e.dwell(np.zeros(4000, np.complex64), [0])  # no local code
