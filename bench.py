@@ -65,11 +65,11 @@ def ncu_dram_bytes(path, tag):
         return None
 
 
-def ncu_dram_bytes_r01_multicorr():
-    """dram bytes of one 2048-channel multicorrelator launch from profiles/r01_multicorr_ncu_full_summary.txt (None if absent)."""
+def ncu_dram_bytes_multicorr(name):
+    """dram bytes of one 2048-channel multicorrelator launch from a committed ncu summary under profiles/ (None if absent)."""
     try:
         tot = 0.0
-        for ln in open(os.path.join(ROOT, "profiles", "r01_multicorr_ncu_full_summary.txt")):
+        for ln in open(os.path.join(ROOT, "profiles", name)):
             f = ln.replace(",", " ").split()
             for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                 if key in f:
@@ -386,6 +386,9 @@ def run_ours(args):
     # ------------------------------ weak-signal search (config 3), Doppler rows sharded, grids stay sharded ------------------------------
     weak = bench_weak_signal(b, torch, dist, args, world, rank, local, barrier, max_over_ranks, hbm_peak) if not args.no_weak else None
 
+    # ------------------------------ small grid (config 1): launch-bound, eager launches vs one CUDA-graph replay ------------------------------
+    small = bench_small_grid(b, torch, args, local) if (rank == 0 and world == 1 and args.workload != "C1") else None
+
     # ------------------------------ CPU baseline on rank 0 ------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -402,7 +405,7 @@ def run_ours(args):
                             "host block -> rank 0 (H2D) -> NCCL broadcast -> sharded dwell -> NCCL all-gather of row records -> decision on the device -> records to the host"},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_fp32": roofline_fp32,
             "wall_ms_per_step_incl_flush": wall / args.steps * 1e3, "tracking": trk, "tracking_loop": trk_loop, "cold_start": cold,
-            "weak_signal": weak,
+            "weak_signal": weak, "small_grid": small,
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
@@ -488,7 +491,12 @@ def bench_tracking(b, torch, device, args, world, rank, local, flush_l2, barrier
     barrier()
     sh_s = max_over_ranks((time.perf_counter() - t0) / steps)
     alg_bytes = n_ch * (8.0 * n + 8.0 * T)
-    mc_traffic = ncu_dram_bytes_r01_multicorr()
+    mc_traffic, mc_traffic_file = None, None
+    for cand in ("r02_multicorr_ncu_full_summary.txt", "r01_multicorr_ncu_full_summary.txt"):   # the newest capture of this kernel
+        mc_traffic = ncu_dram_bytes_multicorr(cand)
+        if mc_traffic:
+            mc_traffic_file = cand
+            break
     mc_traffic = mc_traffic * n_ch / 2048.0 if mc_traffic else None
     return {
         "metric": "tracking_channel_ms_per_s", "value": world * n_ch / (dev_ms * 1e-3), "unit": "channel-ms/s", "ms_per_step": dev_ms,
@@ -502,9 +510,9 @@ def bench_tracking(b, torch, device, args, world, rank, local, flush_l2, barrier
         "e2e_independent_streams": {"value": world * e2e_ch / e2e_s, "unit": "channel-ms/s", "channels": e2e_ch, "h2d_bytes_per_step": int(e2e_ch * n * 8),
                                     "d2h_bytes_per_step": int(e2e_ch * T * 8), "ms_per_step": e2e_s * 1e3,
                                     "input_mode": "a separate host sample buffer per channel (PCIe-bound: 240 kB per channel-ms)"},
-        "roofline": {"kernel": "multicorr_kernel", "bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+        "roofline": {"kernel": "multicorr_window_kernel", "bound": "hbm", "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                      "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak, "traffic": mc_traffic,
-                     "traffic_source": "ncu --set full, profiles/r01_multicorr_ncu_full_summary.txt (dram read + write of one 2048-channel launch, scaled to this launch's channels)"
+                     "traffic_source": f"ncu --set full, profiles/{mc_traffic_file} (dram read + write of one 2048-channel launch, scaled to this launch's channels)"
                                        if mc_traffic else "no ncu capture under profiles/",
                      "peak_source": peak_src, "avg_launch_ms": k_ms,
                      "algorithmic_bytes_per_channel_ms": 8.0 * n + 8.0 * T},
@@ -701,6 +709,53 @@ def bench_weak_signal(b, torch, dist, args, world, rank, local, barrier, max_ove
             "config": {"workload": "BASELINE configs[2]: GPS L1 C/A, 4 MS/s, 20 ms coherent x 10 non-coherent dwells, +-10 kHz / 25 Hz (800 rows), 32 PRNs, N = 160 000",
                        "parallelism": "one GPU" if world == 1 else f"800 Doppler rows sharded over {world} GPUs ({chunk} rows x 32 PRNs each); grids stay sharded, "
                                       "row records all-gathered (NCCL) and decided on the device after every dwell"}}
+
+
+def bench_small_grid(b, torch, args, local):
+    """BASELINE config 1 (GPS L1 C/A, 4 MS/s, 1 ms, 40 bins x 32 PRNs = 5.12 M cells): five short kernels per dwell, so the search is
+    bound by launch latency — timed as eager launches and as one CUDA-graph replay (gnss_b200_acq_capture_*), L2 flushed between."""
+    geo, codes, iq, truth = synth.config_scene("C1")
+    n = geo["n_prn"]
+    e = b.PcpsAcquisitionB200(geo["fft_size"], geo["consumed_samples"], geo["doppler_max"], geo["doppler_step"], geo["fs"], geo["samples_per_chip"], n,
+                              use_cfar=True, device=local)
+    slots = np.arange(n, dtype=np.uint32)
+    e.set_local_codes(slots, codes)
+    d_iq = torch.from_numpy(iq.view(np.float32).copy()).cuda()
+    est = torch.cuda.ExternalStream(e.stream())
+    flush = torch.empty(192 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(3):
+        e.dwell_device_async(d_iq.data_ptr(), slots)
+        ref = e.sync(n)
+    l0 = e.launch_count()
+    e.capture_begin()
+    e.dwell_device_async(d_iq.data_ptr(), slots)
+    e.capture_end()
+    per_dwell = e.launch_count() - l0
+
+    def timed(fn):
+        ts = []
+        for _ in range(max(10, args.steps)):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(est)
+            fn()
+            z.record(est)
+            z.synchronize()
+            ts.append(a.elapsed_time(z))
+        return float(np.mean(ts))
+
+    eager = timed(lambda: e.dwell_device_async(d_iq.data_ptr(), slots))
+    graph = timed(e.replay_async)
+    got = e.sync(n)
+    same = bool(np.array_equal(got["test_statistic"], ref["test_statistic"]) and np.array_equal(got["code_phase"], ref["code_phase"]))
+    cells = n * e.n_doppler * geo["fft_size"]
+    out = {"workload": "C1: GPS L1 C/A, 4 MS/s, 1 ms, 40 bins x 32 PRNs", "cells": cells, "kernels_per_dwell": int(per_dwell),
+           "eager_ms_per_dwell": eager, "graph_ms_per_dwell": graph, "cells_per_s_eager": cells / (eager * 1e-3), "cells_per_s_graph": cells / (graph * 1e-3),
+           "replay_equals_eager": same, "l2": "flushed (192 MiB write) before every dwell"}
+    del flush
+    e.close()
+    return out
 
 
 def bench_tracking_loop(b, torch, args, world, rank, local, barrier, max_over_ranks):

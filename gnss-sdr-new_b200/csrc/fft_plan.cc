@@ -183,7 +183,8 @@ bool make_fft_plan(uint32_t N, uint32_t max_single, FftPlan* plan, const char** 
     plan->radices.clear();
     plan->fast = 0;
     std::vector<uint32_t> rad;
-    if (find_fast_plan(N, plan))
+    static const bool single_first = std::getenv("B200_FFT_SINGLE") != nullptr;  // tuning aid: prefer the one-kernel-per-row plan for N <= max_single
+    if (!(single_first && N <= max_single) && find_fast_plan(N, plan))
         {
             const uint32_t M_lo = plan->ra_lo * plan->rb_lo, M_hi = plan->ra_hi * plan->rb_hi;
             plan->fast = 1;

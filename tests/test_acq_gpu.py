@@ -319,6 +319,42 @@ def test_row_sharding_merge(b200, oracle):
             assert m[k] == ref[p][k]
 
 
+def test_a_captured_search_replays_bit_identically(b200):
+    """gnss_b200_acq_capture_begin / _capture_end / _replay_async: the launches of one dwell recorded into a CUDA graph (what a
+    small grid such as C1 is bound by is launch latency). Replays on new samples in the same device buffer equal eager dwells bit
+    for bit; a persistent grid or a running profiler refuse capture."""
+    import torch
+    geo, codes, iq, truth = synth.config_scene("C1", n_dwells=3)
+    n, N = geo["n_prn"], geo["consumed_samples"]
+    e = _gpu_engine(b200, geo, n, use_cfar=True)
+    slots = np.arange(n, dtype=np.uint32)
+    e.set_local_codes(slots, codes)
+    iq = np.ascontiguousarray(iq).reshape(3, N)
+    d_iq = torch.from_numpy(iq[0].view(np.float32).copy()).cuda()
+    e.dwell_device_async(d_iq.data_ptr(), slots)
+    e.sync(n)
+    l0 = e.launch_count()
+    e.capture_begin()
+    e.dwell_device_async(d_iq.data_ptr(), slots)
+    e.capture_end()
+    per_dwell = e.launch_count() - l0
+    for k in range(3):
+        blk = iq[k]
+        want = e.dwell(blk, slots)
+        d_iq.copy_(torch.from_numpy(blk.view(np.float32).copy()))
+        torch.cuda.synchronize()
+        e.replay_async()
+        got = e.sync(n)
+        for f in ("test_statistic", "peak", "code_phase", "doppler_index", "doppler_hz", "input_power"):
+            assert np.array_equal(got[f], want[f]), f
+    assert 3 <= per_dwell <= 6
+    g = _gpu_engine(b200, geo, n, use_cfar=True, keep_grid=True)
+    with pytest.raises(b200.B200Error):
+        g.capture_begin()
+    g.close()
+    e.close()
+
+
 def test_unsupported_and_state_errors(b200):
     with pytest.raises(b200.B200Error):
         b200.PcpsAcquisitionB200(2 * 2056, 2056, 5000, 250, 2.056e6, 3, 1, bit_transition=True)  # 257 | 4112 and bit_transition: no padded form
