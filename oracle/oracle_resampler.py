@@ -4,8 +4,9 @@ The reference builds it from two GNU Radio pieces (gnss_flowgraph.cc:1063-1118):
 gr::filter::firdes::low_pass(1.0, fs, acq_fs / 2.1, acq_fs / 2) and gr::filter::fir_filter_ccf::make(decimation, taps),
 with the decimation of Acq_Conf::ConfigureAutomaticResampler (acq_conf.cc:93-111). GNU Radio is a dependency outside the
 reference tree (any 3.7.3+ per the reference's CMakeLists; not installed here), so this restates the published algorithm
-of gr-filter/lib/firdes.cc and fir_filter.cc; parity of the tap design is pinned on scipy.signal.firwin, an independent
-implementation of the same windowed-sinc design (tests/test_resampler.py). PARITY WITH GNU RADIO ITSELF IS UNPINNED.
+of gr-filter/lib/firdes.cc and fir_filter.cc. The tap design is pinned on the known_taps vector of GNU Radio's own QA
+(qa_firdes.py test_low_pass, quoted in tests/test_resampler.py) and cross-checked against scipy.signal.firwin; the decimating
+FIR (fir_filter_ccf history / phase) has no published vector and stays pinned on numpy's convolution only.
 """
 import numpy as np
 

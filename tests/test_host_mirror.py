@@ -357,6 +357,15 @@ def test_mat_writer_is_read_by_scipy(driver, tmp_path):
     assert m["threshold"].dtype == np.float32 and float(m["threshold"][0, 0]) == 2.5
     assert m["x"].dtype == np.float64 and float(m["x"][0, 0]) == 1.0 / 3.0
     assert np.array_equal(m["odd_length_name_"], np.array([[1, -2, 3, -4, 5]], dtype=np.int32))
+    # the same file through the HDF5-free parser behind tools/acq_dump_reader.py (matio's Mat_Open / Mat_VarRead walk, restated)
+    import acq_dump_reader
+    v = acq_dump_reader.mat_open(str(out))
+    assert v["acq_grid"]["rank"] == 2 and tuple(v["acq_grid"]["dims"]) == (7, 3) and v["acq_grid"]["data_type"] == "f4"
+    assert np.array_equal(v["acq_grid"]["data"], 0.5 * np.arange(21, dtype=np.float32))          # column-major, as Mat_VarRead hands it over
+    assert v["sample_counter"]["data_type"] == "u8" and int(v["sample_counter"]["data"][0]) == 0x123456789ABCDEF
+    assert v["x"]["data_type"] == "f8" and v["PRN"]["data_type"] == "u4" and v["doppler_max"]["data_type"] == "i4"
+    with pytest.raises(acq_dump_reader.MatError):
+        acq_dump_reader.read_binary_acq(str(out), 7, 4)
 
 
 @pytest.mark.gpu
@@ -399,6 +408,18 @@ def test_acquisition_dump_file(driver, oracle, tmp_path, two_steps):
     assert float(m["acq_doppler_hz"][0, 0]) == got["doppler"] and float(m["acq_delay_samples"][0, 0]) == got["delay"]
     assert float(m["test_statistic"][0, 0]) == pytest.approx(got["stat"], rel=1e-6)
     assert m["sample_counter"].dtype == np.uint64 and int(m["sample_counter"][0, 0]) == got["stamp"]
+    # ... and what the reference's own reader takes from the file (Acquisition_Dump_Reader::read_binary_acq, restated in
+    # tools/acq_dump_reader.py over an HDF5-free Level-5 parser: its rank / dims / single-precision checks and its pointer casts)
+    import acq_dump_reader
+    rd = acq_dump_reader.read_binary_acq(str(tmp_path / "dumps" / files[0]), 4000, 40)
+    assert rd["doppler_max"] == geo["doppler_max"] and rd["doppler_step"] == geo["doppler_step"] and rd["PRN"] == strong + 1
+    assert rd["positive_acq"] == int(got["event"] == 1) and rd["num_dwells"] == 1 and rd["sample_counter"] == got["stamp"]
+    assert rd["acq_doppler_hz"] == got["doppler"] and rd["acq_delay_samples"] == got["delay"]
+    assert rd["test_statistic"] == pytest.approx(got["stat"], rel=1e-6) and rd["threshold"] == pytest.approx(got["threshold"], rel=1e-6)
+    k_dop, k_smp = np.unravel_index(np.argmax(rd["mag"]), rd["mag"].shape)
+    assert (k_dop, k_smp) == (w1["doppler_index"], w1["code_phase"])                 # mag[doppler][sample], as the reader's plots index it
+    with pytest.raises(acq_dump_reader.MatError):
+        acq_dump_reader.read_binary_acq(str(tmp_path / "dumps" / files[0]), 4000, 41)  # "dimension matrix error"
     if two_steps:
         w2 = acq.dwell_step2(stream[12000:16000], 4, 125.0, float(w1["doppler_hz"]))
         assert m["acq_grid_narrow"].shape == (4000, 4)

@@ -45,6 +45,23 @@ def test_tap_design_equals_an_independent_windowed_sinc(orx, b200):
         b200.firdes_low_pass(1.0, 4e6, 3e6, 1e6)       # cut-off above fs / 2
 
 
+# known_taps of GNU Radio's own QA for this function (gr-filter/python/filter/qa_firdes.py, test_low_pass:
+# firdes.low_pass(1, 1, 0.4, 0.2, WIN_HAMMING)), as published in the GNU Radio source tree. GNU Radio is not installed here and
+# there is no network to re-fetch the file: the vector is quoted, and both restatements reproduce it to the last printed digit.
+GR_QA_LOW_PASS_1_1_04_02 = (0.0024871660862118006, -4.403502608370943e-18, -0.014456653036177158, 0.0543283149600029, -0.116202212870121,
+                            0.17504146695137024, 0.7976038455963135, 0.17504146695137024, -0.116202212870121, 0.0543283149600029,
+                            -0.014456653036177158, -4.403502608370943e-18, 0.0024871660862118006)
+
+
+def test_tap_design_reproduces_gnuradio_qa_vector(orx, b200):
+    want = np.array(GR_QA_LOW_PASS_1_1_04_02, dtype=np.float32)
+    for taps in (orx.firdes_low_pass(1.0, 1.0, 0.4, 0.2), b200.firdes_low_pass(1.0, 1.0, 0.4, 0.2)):
+        assert taps.dtype == np.float32 and taps.size == 13
+        # GNU Radio's QA compares with assertFloatTuplesAlmostEqual(..., 5); here: the same binary32 values but for the 1e-18 zero crossing
+        assert np.array_equal(np.delete(taps, [1, 11]), np.delete(want, [1, 11]))
+        assert abs(taps[1]) < 1e-9 and abs(taps[11]) < 1e-9
+
+
 @pytest.mark.gpu
 def test_fir_decimator_streams_like_fir_filter_ccf(orx, b200):
     rng = np.random.default_rng(3)
