@@ -149,6 +149,7 @@ EXPORTS = [
     "gnss_b200_trk_stream", "gnss_b200_trk_launch_count",
     "gnss_b200_acq_exchange_buffers", "gnss_b200_acq_finalize_gathered_async",
     "gnss_b200_acq_capture_begin", "gnss_b200_acq_capture_end", "gnss_b200_acq_replay_async",
+    "gnss_b200_acq_peer_setup", "gnss_b200_acq_peer_connect", "gnss_b200_acq_peer_exchange_async",
     "gnss_b200_acq_group_create", "gnss_b200_acq_group_destroy", "gnss_b200_acq_group_num_doppler_bins", "gnss_b200_acq_group_num_shards",
     "gnss_b200_acq_group_set_local_codes", "gnss_b200_acq_group_set_doppler_center", "gnss_b200_acq_group_reset", "gnss_b200_acq_group_dwell",
     "gnss_b200_acq_group_read_grid", "gnss_b200_acq_group_launch_count",
@@ -194,6 +195,9 @@ def lib():
     L.gnss_b200_acq_capture_begin.argtypes = [C.c_void_p]
     L.gnss_b200_acq_capture_end.argtypes = [C.c_void_p]
     L.gnss_b200_acq_replay_async.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_peer_setup.argtypes = [C.c_void_p, c_u32, C.c_void_p, C.POINTER(C.c_void_p)]
+    L.gnss_b200_acq_peer_connect.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
+    L.gnss_b200_acq_peer_exchange_async.argtypes = [C.c_void_p, c_u32]
     L.gnss_b200_acq_group_create.argtypes = [C.POINTER(AcqCfg), c_u32, C.POINTER(c_i32), C.POINTER(C.c_void_p)]
     L.gnss_b200_acq_group_destroy.argtypes = [C.c_void_p]
     L.gnss_b200_acq_group_num_doppler_bins.argtypes = [C.c_void_p]
@@ -371,6 +375,24 @@ class PcpsAcquisitionB200:
 
     def finalize_gathered_async(self, n_slots):
         _check(self.L.gnss_b200_acq_finalize_gathered_async(self.h, int(n_slots)))
+
+    def peer_setup(self, rank):
+        """(64-byte CUDA IPC handle, device pointer) of this shard's peer-exchange region (include/gnss_b200.h)."""
+        hd = (C.c_ubyte * 64)()
+        ptr = C.c_void_p()
+        _check(self.L.gnss_b200_acq_peer_setup(self.h, int(rank), hd, C.byref(ptr)))
+        return bytes(hd), ptr.value
+
+    def peer_connect(self, ipc_handles=None, regions=None):
+        if regions is not None:
+            arr = (C.c_void_p * len(regions))(*regions)
+            _check(self.L.gnss_b200_acq_peer_connect(self.h, None, arr))
+        else:
+            buf = b"".join(ipc_handles)
+            _check(self.L.gnss_b200_acq_peer_connect(self.h, buf, None))
+
+    def peer_exchange_async(self, n_slots):
+        _check(self.L.gnss_b200_acq_peer_exchange_async(self.h, int(n_slots)))
 
     def capture_begin(self):
         _check(self.L.gnss_b200_acq_capture_begin(self.h))

@@ -67,6 +67,11 @@ struct gnss_b200_acq
     // sharded search (gnss_b200_acq_exchange_buffers): what this shard sends / what all shards sent
     DevBuf d_send, d_recv;
     uint32_t xchg_world = 0, xchg_chunk = 0;
+    // record exchange over peer memory (gnss_b200_acq_peer_*)
+    DevBuf d_peer, d_peer_ptrs;
+    PeerLayout peer_layout{};
+    std::vector<void*> peer_opened;  // cudaIpcOpenMemHandle mappings to close
+    bool peer_connected = false;
     // what the last dwell left on the device for gnss_b200_acq_finalize_gathered_async
     FinalizeArgs last_f{};
     // a captured dwell (gnss_b200_acq_capture_*)
@@ -758,6 +763,9 @@ extern "C"
             b->release();
         h->d_send.release();
         h->d_recv.release();
+        for (void* m : h->peer_opened) cudaIpcCloseMemHandle(m);
+        h->d_peer.release();
+        h->d_peer_ptrs.release();
         if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
         if (h->graph) cudaGraphDestroy(h->graph);
         h->h_meta.release();
@@ -994,6 +1002,98 @@ extern "C"
         B200_REQUIRE(h->cfg.use_cfar, GNSS_B200_ERR_UNSUPPORTED, "acq_finalize_gathered_async: only the CFAR statistic can be decided from row records");
         finalize_gathered_kernel<<<n_slots, 32, 0, h->stream>>>(h->last_f, h->d_recv.as<gnss_b200_acq_row>(), h->xchg_world, h->xchg_chunk, n_slots);
         h->launches++;
+        B200_CUDA(cudaGetLastError());
+        B200_CUDA(cudaMemcpyAsync(h->h_results.p, h->d_results.p, sizeof(gnss_b200_acq_result) * n_slots, cudaMemcpyDeviceToHost, h->stream));
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_peer_setup(gnss_b200_acq* h, uint32_t rank, void* ipc_handle_out, void** region_out)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_peer_setup: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_REQUIRE(h->xchg_world, GNSS_B200_ERR_STATE, "acq_peer_setup: call gnss_b200_acq_exchange_buffers first");
+        B200_REQUIRE(rank < h->xchg_world && h->row_begin == rank * h->xchg_chunk, GNSS_B200_ERR_INVALID, "acq_peer_setup: rank %u does not own rows from %u", rank, h->row_begin);
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "the C-ABI passes IPC handles as 64 opaque bytes");
+        PeerLayout& L = h->peer_layout;
+        L.world = h->xchg_world;
+        L.rank = rank;
+        L.flags_off = 256;
+        L.recv_off = (256 + 2 * L.world * 128 + 255) & ~255u;
+        L.per_shard_rows = h->cfg.max_slots * h->xchg_chunk;
+        const size_t bytes = (size_t)L.recv_off + sizeof(gnss_b200_acq_row) * 2ull * L.world * L.per_shard_rows;
+        B200_CUDA(cudaStreamSynchronize(h->stream));
+        B200_CUDA(h->d_peer.reserve(bytes));
+        B200_CUDA(cudaMemset(h->d_peer.p, 0, bytes));
+        B200_CUDA(h->d_peer_ptrs.reserve(sizeof(void*) * L.world));
+        h->peer_connected = false;
+        if (ipc_handle_out)
+            {
+                cudaIpcMemHandle_t hd;
+                B200_CUDA(cudaIpcGetMemHandle(&hd, h->d_peer.p));
+                std::memcpy(ipc_handle_out, &hd, sizeof(hd));
+            }
+        if (region_out) *region_out = h->d_peer.p;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_peer_connect(gnss_b200_acq* h, const void* ipc_handles, void* const* regions)
+    {
+        B200_REQUIRE(h && (ipc_handles || regions), GNSS_B200_ERR_INVALID, "acq_peer_connect: null argument");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_REQUIRE(h->d_peer.p != nullptr, GNSS_B200_ERR_STATE, "acq_peer_connect: call gnss_b200_acq_peer_setup first");
+        const PeerLayout& L = h->peer_layout;
+        std::vector<void*> ptrs(L.world, nullptr);
+        for (uint32_t r = 0; r < L.world; r++)
+            {
+                if (r == L.rank)
+                    ptrs[r] = h->d_peer.p;
+                else if (regions)
+                    {
+                        // same process: the region of another handle, possibly on another device of this process
+                        cudaPointerAttributes at;
+                        B200_CUDA(cudaPointerGetAttributes(&at, regions[r]));
+                        if (at.device != h->cfg.device)
+                            {
+                                int can = 0;
+                                B200_CUDA(cudaDeviceCanAccessPeer(&can, h->cfg.device, at.device));
+                                B200_REQUIRE(can, GNSS_B200_ERR_UNSUPPORTED, "acq_peer_connect: device %d cannot access device %d", h->cfg.device, at.device);
+                                const cudaError_t pe = cudaDeviceEnablePeerAccess(at.device, 0);
+                                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) B200_CUDA(pe);
+                                (void)cudaGetLastError();
+                            }
+                        ptrs[r] = regions[r];
+                    }
+                else
+                    {
+                        cudaIpcMemHandle_t hd;
+                        std::memcpy(&hd, static_cast<const char*>(ipc_handles) + (size_t)r * sizeof(hd), sizeof(hd));
+                        void* m = nullptr;
+                        B200_CUDA(cudaIpcOpenMemHandle(&m, hd, cudaIpcMemLazyEnablePeerAccess));
+                        h->peer_opened.push_back(m);
+                        ptrs[r] = m;
+                    }
+            }
+        B200_CUDA(cudaMemcpy(h->d_peer_ptrs.p, ptrs.data(), sizeof(void*) * L.world, cudaMemcpyHostToDevice));
+        h->peer_connected = true;
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_peer_exchange_async(gnss_b200_acq* h, uint32_t n_slots)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_peer_exchange_async: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_REQUIRE(h->peer_connected, GNSS_B200_ERR_STATE, "acq_peer_exchange_async: call gnss_b200_acq_peer_setup / _peer_connect first");
+        B200_REQUIRE(n_slots == h->last_n_slots && n_slots > 0, GNSS_B200_ERR_INVALID, "acq_peer_exchange_async: n_slots differs from the last dwell");
+        B200_REQUIRE(h->cfg.use_cfar, GNSS_B200_ERR_UNSUPPORTED, "acq_peer_exchange_async: only the CFAR statistic can be decided from row records");
+        const PeerLayout& L = h->peer_layout;
+        uint32_t* epoch = h->d_peer.as<uint32_t>();
+        peer_scatter_kernel<<<L.world, 256, 0, h->stream>>>(h->d_send.as<gnss_b200_acq_row>(), n_slots * h->xchg_chunk, h->d_peer_ptrs.as<char*>(), L, epoch);
+        finalize_peer_kernel<<<n_slots, 32, 0, h->stream>>>(h->last_f, h->d_peer.as<char>(), L, epoch, h->xchg_chunk, n_slots);
+        peer_epoch_bump_kernel<<<1, 1, 0, h->stream>>>(epoch);
+        h->launches += 3;
         B200_CUDA(cudaGetLastError());
         B200_CUDA(cudaMemcpyAsync(h->h_results.p, h->d_results.p, sizeof(gnss_b200_acq_result) * n_slots, cudaMemcpyDeviceToHost, h->stream));
         return GNSS_B200_OK;

@@ -566,6 +566,117 @@ static __global__ void finalize_gathered_kernel(const FinalizeArgs a, const gnss
         }
 }
 
+// ---- record exchange over peer memory (gnss_b200_acq_peer_*): no collective library in the data path --------------------
+// Every shard owns one region [epoch | flags[2][world] (128 B apart) | recv[2][world][per_shard_rows]] that its peers can store
+// into (CUDA IPC or peer access). After its search a shard stores its packed records into EVERY shard's recv[parity][rank] and
+// then raises flag[parity][rank] there (release, system scope); the decision kernel of a shard waits until all `world` flags of
+// the parity carry the current epoch (acquire, system scope) and decides from recv[parity]. Two parities: a shard may be one
+// exchange ahead of a slow peer, never two (its own decision waits for that peer's records of the same epoch).
+struct PeerLayout
+{
+    uint32_t world, rank, flags_off, recv_off, per_shard_rows;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// grid = world CTAs: CTA d delivers this shard's [n_slots][chunk] records to shard d
+static __global__ void peer_scatter_kernel(const gnss_b200_acq_row* send, uint32_t n_rows, char* const* peers, const PeerLayout L, const uint32_t* epoch_ctr)
+{
+    static_assert(sizeof(gnss_b200_acq_row) == 16, "one 16-byte store per record");
+    const uint32_t epoch = *epoch_ctr + 1u, par = epoch & 1u;
+    char* base = peers[blockIdx.x];
+    uint4* dst = reinterpret_cast<uint4*>(base + L.recv_off) + (size_t)(par * L.world + L.rank) * L.per_shard_rows;
+    const uint4* src = reinterpret_cast<const uint4*>(send);
+    for (uint32_t i = threadIdx.x; i < n_rows; i += blockDim.x) dst[i] = src[i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_sys(reinterpret_cast<uint32_t*>(base + L.flags_off + (size_t)(par * L.world + L.rank) * 128u), epoch);
+}
+
+// finalize_gathered_kernel behind the wait for everybody's records; a peer that never delivers (a failed rank) ends the wait after
+// ~2 s with NaN statistics instead of hanging the device
+static __global__ void finalize_peer_kernel(const FinalizeArgs a, const char* own, const PeerLayout L, const uint32_t* epoch_ctr, uint32_t chunk, uint32_t n_slots)
+{
+    const uint32_t epoch = *epoch_ctr + 1u, par = epoch & 1u;
+    const int lane = threadIdx.x;
+    bool ok = true;
+    for (uint32_t r = lane; r < L.world; r += 32)
+        {
+            const uint32_t* flag = reinterpret_cast<const uint32_t*>(own + L.flags_off + (size_t)(par * L.world + r) * 128u);
+            const long long t0 = clock64();
+            while (ld_acquire_sys(flag) != epoch)
+                if (clock64() - t0 > 4000000000ll)
+                    {
+                        ok = false;
+                        break;
+                    }
+        }
+    ok = __all_sync(0xffffffffu, ok);
+    const gnss_b200_acq_row* gathered = reinterpret_cast<const gnss_b200_acq_row*>(own + L.recv_off) + (size_t)par * L.world * L.per_shard_rows;
+    const uint32_t si = blockIdx.x;
+    const uint32_t slot = a.slots[si];
+    gnss_b200_acq_row* rows = a.rows + (size_t)slot * a.nD;
+    float best = 0.f;
+    uint32_t best_k = 0xffffffffu, best_i = 0;
+    for (uint32_t k = lane; k < a.nD; k += 32)
+        {
+            const uint32_t r = k / chunk, j = k - r * chunk;
+            const uint4 raw = __ldcg(reinterpret_cast<const uint4*>(gathered + (size_t)r * L.per_shard_rows + (size_t)si * chunk + j));
+            gnss_b200_acq_row row;
+            memcpy(&row, &raw, sizeof(row));
+            rows[k] = row;
+            if (row.valid && (row.max_val > best || (row.max_val == best && best_k != 0xffffffffu && k < best_k)))
+                {
+                    best = row.max_val;
+                    best_k = k;
+                    best_i = row.max_idx;
+                }
+        }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const uint32_t okk = __shfl_xor_sync(0xffffffffu, best_k, o);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+            if (ob > best || (ob == best && okk < best_k))
+                {
+                    best = ob;
+                    best_k = okk;
+                    best_i = oi;
+                }
+        }
+    __syncwarp();
+    if (lane == 0)
+        {
+            if (best_k == 0xffffffffu)
+                {
+                    best_k = 0;
+                    best_i = 0;
+                }
+            gnss_b200_acq_result res;
+            res.peak = best;
+            res.code_phase = best_i;
+            res.doppler_index = best_k;
+            res.doppler_hz = -a.doppler_max + a.center[si] + (int32_t)a.doppler_step * (int32_t)best_k;  // :535
+            res.dwell_count = a.dwell_after[si];
+            res.second_peak = 0.f;
+            const uint32_t opp = (best_k + a.nD / 2) % a.nD;  // :533
+            const gnss_b200_acq_row ro = rows[opp];
+            const float per = ro.row_sum / (float)(int32_t)a.eff;
+            res.input_power = (ro.valid && ok) ? (float)(((double)per / 2.0) / (double)a.dwell_after[si]) : nanf("");
+            res.test_statistic = best / res.input_power;  // :542
+            a.results[si] = res;
+        }
+}
+
+static __global__ void peer_epoch_bump_kernel(uint32_t* epoch_ctr) { *epoch_ctr += 1u; }
+
 // ---- first_vs_second_peak_statistic (:546-612): second maximum of the best row outside the +-1 chip window ----
 struct SecondPeakArgs
 {

@@ -170,6 +170,22 @@ extern "C"
         uint64_t* bytes_per_shard, uint32_t* rows_per_shard);
     GNSS_B200_API int gnss_b200_acq_finalize_gathered_async(gnss_b200_acq* h, uint32_t n_slots);
 
+    /* The exchange itself over peer memory, fused behind the search — no collective library between the kernels:
+       every shard owns a region (flags + double-buffered [world][max_slots][chunk] records) that its peers can store into;
+       gnss_b200_acq_peer_exchange_async queues, on the handle's stream, (1) a kernel that stores this shard's packed records
+       into EVERY shard's region over NVLink and then raises this shard's flag there (release, system scope), (2) the decision
+       kernel, which waits for all `world` flags of the current exchange (acquire, system scope; ~2 s time-out -> NaN statistics)
+       and decides from the records, (3) the result copy. All of it may sit inside gnss_b200_acq_capture_begin / _end, so a
+       rank's whole step is one graph launch. Every shard must call it once per search, in the same order.
+       Setup, after gnss_b200_acq_exchange_buffers: _peer_setup(rank) allocates the region and returns its CUDA IPC handle (64
+       opaque bytes, for peers in OTHER processes: exchange them with any host-side all-gather) and its device pointer (for
+       handles of the SAME process, also on other devices); _peer_connect takes either all `world` IPC handles or all `world`
+       region pointers (the entry of the own rank is ignored). One shard per GPU: shards that share a GPU could wait on each
+       other's unscheduled kernels. */
+    GNSS_B200_API int gnss_b200_acq_peer_setup(gnss_b200_acq* h, uint32_t rank, void* ipc_handle_out /* 64 bytes or NULL */, void** region_out);
+    GNSS_B200_API int gnss_b200_acq_peer_connect(gnss_b200_acq* h, const void* ipc_handles /* [world][64] or NULL */, void* const* regions /* [world] or NULL */);
+    GNSS_B200_API int gnss_b200_acq_peer_exchange_async(gnss_b200_acq* h, uint32_t n_slots);
+
     /* The same inside ONE process that drives several GPUs (the reference receiver is one process): a group owns one engine
        per listed device, splits the Doppler rows of every slot over them (Doppler-major: no forward transform is computed
        twice and every device carries an equal share of every PRN), broadcasts each sample block host -> devices[0] -> the

@@ -80,3 +80,56 @@ def test_one_search_over_two_devices(two_devices, scene, n_prn):
             assert got.tobytes() == want.tobytes(), devices
         grp.close()
     one.close()
+
+
+@pytest.mark.parametrize("scene,n_prn", [("C2", 8), ("C1", 6)])
+def test_record_exchange_over_peer_memory(two_devices, scene, n_prn):
+    """gnss_b200_acq_peer_*: two shards of one search on the two GPUs store their row records straight into each other's
+    region over NVLink and raise a flag; each decision kernel waits for both flags. No collective, no host hop — and the whole
+    step of a shard (search + exchange + decision) replays from one CUDA graph. Records on BOTH shards bit-identical to one
+    engine's, over several searches (the regions are double-buffered by exchange parity)."""
+    import torch
+    b200 = two_devices
+    geo, codes, iq, _ = synth.config_scene(scene, n_prn=n_prn, n_dwells=4)
+    N = geo["consumed_samples"]
+    iq = np.ascontiguousarray(iq).reshape(4, N)
+    slots = np.arange(n_prn, dtype=np.uint32)
+    one = _gpu_engine(b200, geo, n_prn, use_cfar=True)
+    one.set_local_codes(slots, codes[:n_prn])
+    nD = one.n_doppler
+    chunk = (nD + 1) // 2
+    shards, regions, bufs = [], [], []
+    for r in range(2):
+        e = _gpu_engine(b200, geo, n_prn, use_cfar=True, device=r, row_begin=r * chunk, row_end=min(nD, (r + 1) * chunk))
+        e.set_local_codes(slots, codes[:n_prn])
+        e.exchange_buffers(2)
+        _, ptr = e.peer_setup(r)
+        shards.append(e)
+        regions.append(ptr)
+        bufs.append(torch.empty(2 * N, dtype=torch.float32, device=f"cuda:{r}"))
+    for e in shards:
+        e.peer_connect(regions=regions)
+    for k in range(4):
+        want = one.dwell(iq[k], slots)
+        for r in range(2):
+            bufs[r].copy_(torch.from_numpy(iq[k].view(np.float32).copy()))
+        torch.cuda.synchronize(0)
+        torch.cuda.synchronize(1)
+        if k == 2:     # from the third search on: one graph per shard
+            for r, e in enumerate(shards):
+                e.capture_begin()
+                e.dwell_device_async(bufs[r].data_ptr(), slots)
+                e.peer_exchange_async(n_prn)
+                e.capture_end()
+        for r, e in enumerate(shards):
+            if k >= 2:
+                e.replay_async()
+            else:
+                e.dwell_device_async(bufs[r].data_ptr(), slots)
+                e.peer_exchange_async(n_prn)
+        for e in shards:
+            got = e.sync(n_prn)
+            assert got.tobytes() == want.tobytes(), (k, scene)
+    for e in shards:
+        e.close()
+    one.close()
