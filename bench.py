@@ -162,7 +162,30 @@ def run_reference(args):
     print(json.dumps(line))
 
 
-def workload_config(name, geo, n_doppler, world=1):
+def connect_peers(eng, dist, world, rank):
+    """CUDA IPC handles of every rank's exchange region, gathered on the host once; False when this box refuses peer mappings."""
+    ok = True
+    try:
+        hd, _ = eng.peer_setup(rank)
+    except Exception as ex:   # noqa: BLE001
+        hd, ok = b"", False
+        sys.stderr.write(f"bench.py: peer exchange unavailable on rank {rank}: {ex}\n")
+    handles = [None] * world
+    dist.all_gather_object(handles, hd)
+    if ok and all(len(h) == 64 for h in handles):
+        try:
+            eng.peer_connect(ipc_handles=handles)
+        except Exception as ex:   # noqa: BLE001
+            ok = False
+            sys.stderr.write(f"bench.py: peer exchange unavailable on rank {rank}: {ex}\n")
+    else:
+        ok = False
+    flags = [None] * world
+    dist.all_gather_object(flags, ok)
+    return all(flags)
+
+
+def workload_config(name, geo, n_doppler, world=1, exchange="nccl"):
     desc = {"C2": "BASELINE configs[1]: Galileo E1b PCPS acquisition, 4 ms code, 8 MS/s, +-5 kHz / 125 Hz, 50 PRNs",
             "C1": "BASELINE configs[0]: GPS L1 C/A PCPS acquisition, 1 ms, 4 MS/s, +-5 kHz / 250 Hz, 32 PRNs"}.get(name, name)
     return {"workload": desc, "fft_size": geo["fft_size"], "n_doppler_bins": n_doppler, "n_prn": geo["n_prn"],
@@ -170,7 +193,9 @@ def workload_config(name, geo, n_doppler, world=1):
             "l2_policy": "L2 flushed (256 MiB write) between timed iterations",
             "parallelism": "one GPU" if world == 1 else
                            f"ONE search, its {n_doppler} Doppler rows sharded over {world} GPUs ({-(-n_doppler // world)} rows x all PRNs each, no forward FFT computed twice); "
-                           "row records all-gathered device-to-device (NCCL), decision on every device; a shard's dwell replayed as one CUDA graph"}
+                           + ("row records stored into every rank's region over peer memory (NVLink stores + system-scope flags, no collective), decision on "
+                              "every device; a rank's whole step (search + exchange + decision) replayed as ONE CUDA graph" if exchange == "peer" else
+                              "row records all-gathered device-to-device (NCCL), decision on every device; a shard's dwell replayed as one CUDA graph")}
 
 
 # ----------------------------------------------------------------------------------------------
@@ -247,9 +272,17 @@ def run_ours(args):
         assert ch == chunk
         send_t = torch.as_tensor(RawCuda(ds, n_prn * chunk * 16), device=torch.device("cuda", local))
         recv_t = torch.as_tensor(RawCuda(dr, world * n_prn * chunk * 16), device=torch.device("cuda", local))
+    peer = world > 1 and args.exchange == "peer"
+    if peer:
+        peer = connect_peers(eng, dist, world, rank)
+    align_t = recv_t[:4].view(torch.float32) if world > 1 else None   # engine-owned memory (nothing torch-owned lives on the engine's stream)
 
     def exchange_and_decide():
-        """rows of all shards -> every rank (NCCL all-gather between the engines' device buffers), decision on the device"""
+        """rows of all shards -> every rank, decision on the device: peer-memory stores + flags (no collective), or an NCCL all-gather
+        between the engines' device buffers"""
+        if peer:
+            eng.peer_exchange_async(n_prn)
+            return
         with torch.cuda.stream(est):
             dist.all_gather_into_tensor(recv_t, send_t)
         eng.finalize_gathered_async(n_prn)
@@ -286,9 +319,13 @@ def run_ours(args):
     if use_graph:
         eng.capture_begin()
         eng.dwell_device_async(d_iq.data_ptr(), slots)
+        if peer:
+            eng.peer_exchange_async(n_prn)     # the exchange and the decision are kernels too: the rank's whole step is ONE graph
         eng.capture_end()
+        barrier()
         eng.replay_async()
-        exchange_and_decide()
+        if not peer:
+            exchange_and_decide()
         if eng.sync(n_prn).tobytes() != res.tobytes():
             raise RuntimeError("bench.py: the replayed dwell differs from the recorded one")
 
@@ -304,12 +341,17 @@ def run_ours(args):
     for i in range(args.steps):
         flush_l2()
         barrier()
+        if world > 1:
+            # the host barrier releases the ranks tens of microseconds apart; a 4-byte all-reduce queued on the engine's stream right
+            # before the start event aligns the ranks ON THE DEVICE, so the timed region holds the search and its exchange, not that skew
+            with torch.cuda.stream(est):
+                dist.all_reduce(align_t)
         ev[i][0].record(est)
         if use_graph:
             eng.replay_async()
         else:
             eng.dwell_device_async(d_iq.data_ptr(), slots)
-        if world > 1:
+        if world > 1 and not (use_graph and peer):
             exchange_and_decide()
         ev[i][1].record(est)
         res = eng.sync(n_prn)
@@ -399,10 +441,11 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args.workload, geo, nD, world),
+            "config": workload_config(args.workload, geo, nD, world, "peer" if peer else "nccl"),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(iq.nbytes), "d2h_bytes_per_step": int(n_prn * 32), "ms_per_step": e2e_s * 1e3,
                     "path": "gnss_b200_acq_dwell (host block in, records out)" if world == 1 else
-                            "host block -> rank 0 (H2D) -> NCCL broadcast -> sharded dwell -> NCCL all-gather of row records -> decision on the device -> records to the host"},
+                            "host block -> rank 0 (H2D) -> NCCL broadcast -> sharded dwell -> row records to every rank (" + ("peer memory" if peer else "NCCL all-gather") +
+                            ") -> decision on the device -> records to the host"},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_fp32": roofline_fp32,
             "wall_ms_per_step_incl_flush": wall / args.steps * 1e3, "tracking": trk, "tracking_loop": trk_loop, "cold_start": cold,
             "weak_signal": weak, "small_grid": small,
@@ -412,7 +455,7 @@ def run_ours(args):
         print(json.dumps(line))
         sys.stdout.flush()
     # orderly teardown: the tensors that alias the engine's exchange buffers, then the engine, then the process group
-    send_t = recv_t = None
+    send_t = recv_t = align_t = None
     eng.close()
     torch.cuda.synchronize()
     if world > 1:
@@ -554,7 +597,8 @@ def bench_cold_start(b, torch, dist, args, world, rank, local, barrier, max_over
             ds, dr, _, ch = e.exchange_buffers(world)
             send_t = torch.as_tensor(RawCuda(ds, n * ch * 16), device=dev)
             recv_t = torch.as_tensor(RawCuda(dr, world * n * ch * 16), device=dev)
-        engines.append(dict(name=k, geo=geo, e=e, n=n, slots=slots, est=torch.cuda.ExternalStream(e.stream(), device=dev), send=send_t, recv=recv_t, graph=False))
+        pe = world > 1 and args.exchange == "peer" and connect_peers(e, dist, world, rank)
+        engines.append(dict(name=k, geo=geo, e=e, n=n, slots=slots, est=torch.cuda.ExternalStream(e.stream(), device=dev), send=send_t, recv=recv_t, graph=False, peer=pe))
         total_cells += n * nD * e.eff
 
     def search():
@@ -564,11 +608,15 @@ def bench_cold_start(b, torch, dist, args, world, rank, local, barrier, max_over
         for g in engines:
             g["est"].wait_stream(cur)
             if g["graph"]:
-                g["e"].replay_async()
+                g["e"].replay_async()          # with the peer exchange: search + record exchange + decision in this one graph
             else:
                 g["e"].dwell_device_async(d_iq.data_ptr(), g["slots"])
+                if g["peer"]:
+                    g["e"].peer_exchange_async(g["n"])
         if world > 1:
             for g in engines:
+                if g["peer"]:
+                    continue
                 with torch.cuda.stream(g["est"]):
                     dist.all_gather_into_tensor(g["recv"], g["send"])
                 g["e"].finalize_gathered_async(g["n"])
@@ -584,6 +632,8 @@ def bench_cold_start(b, torch, dist, args, world, rank, local, barrier, max_over
     for g in engines:   # every engine's dwell as one graph launch
         g["e"].capture_begin()
         g["e"].dwell_device_async(d_iq.data_ptr(), g["slots"])
+        if g["peer"]:
+            g["e"].peer_exchange_async(g["n"])
         g["e"].capture_end()
         g["graph"] = True
     search()
@@ -629,7 +679,9 @@ def bench_cold_start(b, torch, dist, args, world, rank, local, barrier, max_over
             "satellites_checked": want, "gpu_launches_per_search_this_rank": launches / steps,
             "config": {"workload": "BASELINE configs[3]: GPS L1 C/A (32) + Galileo E1b (36) + BeiDou B1I (63) at 25 MS/s, +-5 kHz / 250 Hz, 1 dwell",
                        "parallelism": f"Doppler-major over {world} GPU(s): {-(-40 // world)} of 40 rows x all 131 PRNs per GPU; sample block H2D on rank 0 + NCCL broadcast, "
-                                      "row records all-gathered device-to-device (NCCL), decision on the device, one CUDA graph per constellation — all inside the timed region",
+                                      + ("row records stored into every rank over peer memory (flags, no collective) and decided on the device inside ONE CUDA graph per constellation"
+                                         if all(g["peer"] for g in engines) and world > 1 else
+                                         "row records all-gathered device-to-device (NCCL), decision on the device, one CUDA graph per constellation") + " — all inside the timed region",
                        "h2d_bytes": int(iq.nbytes), "note": "north_star target: < 1 ms on 8 GPUs"}}
 
 
@@ -918,6 +970,8 @@ def main():
     ap.add_argument("--workload", default="C2", choices=["C1", "C2"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-weak", action="store_true", help="skip the config-3 (weak-signal, persistent grid) leg")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: row records over peer memory (stores + flags fused behind the search, gnss_b200_acq_peer_*) or an NCCL all-gather")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: file descriptor 1 is pointed at stderr for everything native code prints there
     # (NCCL's version banner at any NCCL_DEBUG level), Python's own sys.stdout keeps the real one

@@ -78,6 +78,7 @@ struct gnss_b200_acq
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t graph_exec = nullptr;
     bool capturing = false;
+    uint64_t graph_kernels = 0;  // kernel nodes of the captured graph: what one replay launches
 };
 
 namespace
@@ -340,6 +341,9 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
             fa.X = h->d_xbuf.as<float2>();
             fa.nb = pl.stage[1].blocks;
             fa.C = pl.stage[0].C;
+            // A shard of a split search transforms only a few rows: narrower column tiles until the launch fills the machine
+            // (10 rows of N = 32 000: 0.048 -> 0.034 ms for the two forward kernels; a full grid keeps the plan's tile)
+            while (fa.C % 2 == 0 && fa.C > 2 && (uint64_t)n_fwd * (fa.M_lo / fa.C) < (uint64_t)kNumSMs) fa.C /= 2;
             const uint32_t pitch = (pl.ra_lo % 2 == 0) ? pl.ra_lo + 1 : pl.ra_lo;
             const size_t smem_lo = ((size_t)fa.nb * pitch * pl.rb_lo + fa.M_lo) * sizeof(float2);
             const size_t smem_hi = ((size_t)fa.M_hi * fa.C + fa.M_hi) * sizeof(float2);
@@ -1127,6 +1131,16 @@ extern "C"
         h->graph = g;
         h->graph_exec = nullptr;
         B200_CUDA(cudaGraphInstantiate(&h->graph_exec, h->graph, 0));
+        size_t n_nodes = 0;
+        B200_CUDA(cudaGraphGetNodes(h->graph, nullptr, &n_nodes));
+        std::vector<cudaGraphNode_t> nodes(n_nodes);
+        if (n_nodes) B200_CUDA(cudaGraphGetNodes(h->graph, nodes.data(), &n_nodes));
+        h->graph_kernels = 0;
+        for (cudaGraphNode_t nd : nodes)
+            {
+                cudaGraphNodeType ty;
+                if (cudaGraphNodeGetType(nd, &ty) == cudaSuccess && ty == cudaGraphNodeTypeKernel) h->graph_kernels++;
+            }
         return GNSS_B200_OK;
     }
 
@@ -1137,7 +1151,7 @@ extern "C"
         B200_CUDA(cudaSetDevice(h->cfg.device));
         B200_REQUIRE(h->graph_exec, GNSS_B200_ERR_STATE, "acq_replay_async: nothing captured");
         B200_CUDA(cudaGraphLaunch(h->graph_exec, h->stream));
-        h->launches++;
+        h->launches += h->graph_kernels;  // the kernels the replay runs (one graph launch on the host)
         return GNSS_B200_OK;
     }
 
