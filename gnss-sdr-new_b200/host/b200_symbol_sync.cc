@@ -31,40 +31,20 @@ void B200_Symbol_Sync::reset()
 
 
 // :923-966
+// acquire_secondary (:923-966): the signs of the buffered prompts against the expected symbols ('0' = +, anything else = -).
+// A prompt at exactly 0 counts as positive. All agree -> locked; all disagree -> locked half a cycle off.
 bool B200_Symbol_Sync::acquire_secondary()
 {
-    int32_t corr_value = 0;
+    int32_t agree = 0;
     for (uint32_t i = 0; i < d_secondary_code_length; i++)
         {
-            if (d_Prompt_circular_buffer[i].real() < 0.0)  // symbols clipping
-                {
-                    if (d_secondary_code_string[i] == '0')
-                        {
-                            corr_value++;
-                        }
-                    else
-                        {
-                            corr_value--;
-                        }
-                }
-            else
-                {
-                    if (d_secondary_code_string[i] == '0')
-                        {
-                            corr_value--;
-                        }
-                    else
-                        {
-                            corr_value++;
-                        }
-                }
+            const bool prompt_negative = d_Prompt_circular_buffer[i].real() < 0.0F;
+            const bool symbol_negative = d_secondary_code_string[i] == '0';  // the reference counts a NEGATIVE prompt on '0' as agreement
+            agree += (prompt_negative == symbol_negative) ? 1 : -1;
         }
-    if (std::abs(corr_value) == static_cast<int32_t>(d_secondary_code_length))
-        {
-            d_Flag_PLL_180_deg_phase_locked = corr_value < 0;
-            return true;
-        }
-    return false;
+    if (std::abs(agree) != static_cast<int32_t>(d_secondary_code_length)) return false;
+    d_Flag_PLL_180_deg_phase_locked = agree < 0;
+    return true;
 }
 
 
@@ -117,25 +97,11 @@ bool B200_Symbol_Sync::push(const gnss_b200_trk_epoch& e, Symbol* out)
         }
     if (d_symbols_per_bit > 1)
         {
-            if (d_data_secondary_code_length > 0)
-                {
-                    if (d_data_secondary_code_string[d_current_data_symbol] == '0')
-                        {
-                            d_P_data_accu += prompt;
-                        }
-                    else
-                        {
-                            d_P_data_accu -= prompt;
-                        }
-                    d_current_data_symbol++;
-                    d_current_data_symbol %= d_data_secondary_code_length;
-                }
-            else
-                {
-                    d_P_data_accu += prompt;
-                    d_current_data_symbol++;
-                    d_current_data_symbol %= d_symbols_per_bit;
-                }
+            // per-bit accumulation, with the data secondary code wiped off where the signal has one
+            const bool wipe = d_data_secondary_code_length > 0;
+            const bool minus = wipe && d_data_secondary_code_string[d_current_data_symbol] != '0';
+            d_P_data_accu = minus ? d_P_data_accu - prompt : d_P_data_accu + prompt;
+            d_current_data_symbol = (d_current_data_symbol + 1) % (wipe ? d_data_secondary_code_length : d_symbols_per_bit);
         }
     else
         {
