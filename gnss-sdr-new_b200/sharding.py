@@ -1,6 +1,8 @@
 """Multi-GPU partition of one acquisition search and of a tracking epoch.
 
-One process per GPU (torchrun). The units are independent:
+One process per GPU (torchrun). The units are independent. The engines themselves split ONE search Doppler-major (partition_doppler_major,
+pack_rows, unpack_gathered below restate that layout for the gloo tests; on the device it is gnss_b200_acq_exchange_buffers with the
+peer-memory or NCCL exchange). The PRN-major helpers are the general (slot, row) form:
 
 * acquisition: a unit is a (PRN slot, Doppler row). Partition PRN-major (rank g owns slots g, g+G, ...); when there
   are fewer slots than ranks, the Doppler rows of a slot are split over `G // n_slots` ranks (config 3: 800 rows per
@@ -35,6 +37,48 @@ def partition_search(n_slots: int, n_doppler: int, world: int):
             r1 = (n_doppler * (j + 1)) // per
             plan[s * per + j].append((s, r0, r1))
     return plan
+
+
+def partition_doppler_major(n_doppler: int, world: int):
+    """The split the engines themselves use for ONE search over `world` shards (gnss_b200_acq_exchange_buffers,
+    gnss_b200_acq_group_*): shard r owns rows [r * chunk, min(n_doppler, (r + 1) * chunk)) of EVERY slot, chunk = ceil(n_doppler /
+    world) — no forward transform is computed twice and every shard carries an equal share of every PRN.
+    -> (chunk, [(row_begin, row_end) per rank]); trailing ranks may own nothing."""
+    if world < 1 or n_doppler < 1:
+        raise ValueError("partition_doppler_major: bad arguments")
+    chunk = -(-n_doppler // world)
+    return chunk, [(min(n_doppler, r * chunk), min(n_doppler, (r + 1) * chunk)) for r in range(world)]
+
+
+def pack_rows(rows: np.ndarray, row_begin: int, row_end: int, chunk: int) -> np.ndarray:
+    """What pack_rows_kernel leaves in d_send: this shard's rows of every slot as [n_slots][chunk], padded with invalid records."""
+    out = np.zeros((rows.shape[0], chunk), dtype=rows.dtype)
+    out[:, :row_end - row_begin] = rows[:, row_begin:row_end]
+    return out
+
+
+def unpack_gathered(gathered: np.ndarray, n_doppler: int) -> np.ndarray:
+    """[world][n_slots][chunk] (what d_recv / the peer regions hold) -> [n_slots][n_doppler], the table finalize_gathered_kernel decides on."""
+    world, n_slots, chunk = gathered.shape
+    return np.ascontiguousarray(np.transpose(gathered, (1, 0, 2)).reshape(n_slots, world * chunk)[:, :n_doppler])
+
+
+def gather_rows_doppler_major(local_rows: np.ndarray, n_doppler: int, group=None) -> np.ndarray:
+    """All-gather of the packed records of a Doppler-major split (the host form of the device exchange): every rank passes its
+    full-size [n_slots][n_doppler] table with only its own rows valid and gets the complete table back."""
+    import torch
+    dist = _dist()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    chunk, parts = partition_doppler_major(n_doppler, world)
+    mine = pack_rows(np.ascontiguousarray(local_rows), parts[rank][0], parts[rank][1], chunk)
+    send = torch.from_numpy(mine.view(np.uint8).reshape(-1).copy())
+    recv = torch.empty(world * send.numel(), dtype=torch.uint8)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    gathered = recv.numpy().view(local_rows.dtype).reshape(world, local_rows.shape[0], chunk)
+    merged = unpack_gathered(gathered, n_doppler)
+    if not merged["valid"].all():
+        raise RuntimeError("gather_rows_doppler_major: no rank delivered some row")
+    return merged
 
 
 def partition_channels(n_channels: int, world: int):

@@ -42,6 +42,14 @@ def main():
         if merged is not None:
             for s in range(n_slots):
                 res[s] = b.finalize_rows(merged[s], int(z["eff"]), int(z["doppler_max"]), int(z["doppler_step"]), 0, 1)
+        # the same search split Doppler-major (the engines' own split: gnss_b200_acq_exchange_buffers / _group / _peer)
+        chunk, parts = sh.partition_doppler_major(n_doppler, world)
+        mine = np.zeros_like(full)
+        mine[:, parts[rank][0]:parts[rank][1]] = full[:, parts[rank][0]:parts[rank][1]]
+        merged_dm = sh.gather_rows_doppler_major(mine, n_doppler)
+        res_dm = np.zeros(n_slots, dtype=b.ACQ_RESULT_DTYPE)
+        for s in range(n_slots):
+            res_dm[s] = b.finalize_rows(merged_dm[s], int(z["eff"]), int(z["doppler_max"]), int(z["doppler_step"]), 0, 1)
         # sample block broadcast and channel gather
         blk = z["samples"] if rank == 0 else np.zeros_like(z["samples"])
         blk = sh.broadcast_samples(blk)
@@ -49,7 +57,7 @@ def main():
         cb, ce = sh.partition_channels(n_ch, world)[rank]
         ch_out = sh.gather_channels(z["ch_out"][cb:ce], n_ch)
         np.savez(os.path.join(work, f"out{rank}.npz"), res=res.view(np.uint8), err=np.array(err), samples=blk, ch_out=ch_out,
-                 owned=np.array([len(plan[rank])]))
+                 owned=np.array([len(plan[rank])]), res_dm=res_dm.view(np.uint8), rows_dm=np.array([parts[rank][1] - parts[rank][0]]))
     finally:
         dist.destroy_process_group()
 

@@ -91,6 +91,11 @@ def test_sharded_search_equals_single_process(b200, scene, world):
     # every rank reached the same answer bit for bit
     for o in outs[1:]:
         assert o["res"].tobytes() == outs[0]["res"].tobytes()
+    # the Doppler-major split of the same search (what the engines exchange on the device): the same decision on every rank
+    for o in outs:
+        assert o["res_dm"].tobytes() == outs[0]["res"].tobytes()
+    chunk = -(-scene["nd"] // world)
+    assert [int(o["rows_dm"][0]) for o in outs] == [max(0, min(scene["nd"], (r + 1) * chunk) - min(scene["nd"], r * chunk)) for r in range(world)]
     if world == 8:  # 3 slots on 8 ranks: rows of a slot are split over 2 ranks, 2 ranks idle
         assert sorted(int(o["owned"][0]) for o in outs) == [0, 0, 1, 1, 1, 1, 1, 1]
 
