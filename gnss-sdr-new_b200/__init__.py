@@ -136,7 +136,7 @@ EXPORTS = [
     "gnss_b200_acq_set_local_code", "gnss_b200_acq_set_local_codes", "gnss_b200_acq_set_doppler_center",
     "gnss_b200_acq_reset", "gnss_b200_acq_dwell", "gnss_b200_acq_dwell_device_async", "gnss_b200_acq_sync",
     "gnss_b200_acq_read_grid", "gnss_b200_acq_read_rows", "gnss_b200_acq_finalize_rows", "gnss_b200_acq_threshold",
-    "gnss_b200_acq_stream", "gnss_b200_acq_launch_count", "gnss_b200_mc_create", "gnss_b200_mc_destroy",
+    "gnss_b200_acq_stream", "gnss_b200_acq_launch_count", "gnss_b200_acq_transform_length", "gnss_b200_mc_create", "gnss_b200_mc_destroy",
     "gnss_b200_mc_set_code", "gnss_b200_mc_set_stream", "gnss_b200_mc_correlate_batch",
     "gnss_b200_mc_correlate_device_async", "gnss_b200_mc_sync", "gnss_b200_mc_chip_indices", "gnss_b200_mc_stream",
     "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan",
@@ -220,6 +220,8 @@ def lib():
     L.gnss_b200_acq_stream.restype = C.c_void_p
     L.gnss_b200_acq_launch_count.argtypes = [C.c_void_p]
     L.gnss_b200_acq_launch_count.restype = C.c_uint64
+    L.gnss_b200_acq_transform_length.argtypes = [C.c_void_p]
+    L.gnss_b200_acq_transform_length.restype = C.c_uint32
     L.gnss_b200_host_register.argtypes = [C.c_void_p, C.c_size_t]
     L.gnss_b200_host_unregister.argtypes = [C.c_void_p]
     L.gnss_b200_mc_create.argtypes = [c_u32, c_u32, c_u32, c_i32, C.POINTER(C.c_void_p)]
@@ -425,6 +427,11 @@ class PcpsAcquisitionB200:
 
     def launch_count(self):
         return int(self.L.gnss_b200_acq_launch_count(self.h))
+
+    @property
+    def transform_length(self):
+        """fft_size, or the padded length the engine searches on (gnss_b200_acq_transform_length)."""
+        return int(self.L.gnss_b200_acq_transform_length(self.h))
 
 
 class PcpsAcquisitionGroupB200:

@@ -641,6 +641,28 @@ extern "C"
 
 namespace
 {
+// Relative cost per transform point of a plan, measured on B200 (profiles/r02_padded_lengths.txt): the "fast" four-radix plans run
+// at ~1.4e11 points/s, single-stage codelet plans at about half of that, generic two-stage plans and plans with a direct-DFT
+// pass over a large prime (31 for the sample rates that are multiples of 1.023 MHz) at 0.36-0.42e11.
+double plan_cost_per_point(const b200::FftPlan& plan)
+{
+    if (plan.fast) return 1.0;
+    uint32_t rmax = 0;
+    for (uint32_t r : plan.radices) rmax = std::max(rmax, r);
+    if (rmax >= 31) return 3.5;
+    return plan.n_stages == 2 ? 3.3 : 2.2;
+}
+
+// A supported length whose plan needs a direct-DFT pass can be searched faster in the padded form (create_impl) on a longer
+// length that has a fast plan. B200_FFT_PAD=1/0 forces the choice (tuning aid, tests).
+bool consider_padded(const b200::FftPlan& plan)
+{
+    if (const char* e = getenv("B200_FFT_PAD")) return e[0] == '1';
+    for (uint32_t r : plan.radices)
+        if (r >= 31) return true;
+    return false;
+}
+
 int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, gnss_b200_acq** out)
     {
         B200_REQUIRE(cfg && out, GNSS_B200_ERR_INVALID, "acq_create: null argument");
@@ -682,38 +704,54 @@ int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, 
         h->code_off = h->N - h->code_len;
         if (!cfg->bit_transition && h->N == h->consumed) h->code_off = 0;
         const char* why = nullptr;
-        if (!make_fft_plan(h->N, kMaxSingleStagePoints, &h->plan, &why))
+        const bool have_plan = make_fft_plan(h->N, kMaxSingleStagePoints, &h->plan, &why);
+        if (!have_plan || consider_padded(h->plan))
             {
                 // A length the mixed-radix kernels cannot take (a prime factor > 127; FFTW in the reference takes any d_fft_size,
-                // pcps_acquisition.cc:85-92,114-115). The search needs the CYCLIC correlation of length n = fft_size,
+                // pcps_acquisition.cc:85-92,114-115) or take only slowly. The search needs the CYCLIC correlation of length
+                // n = fft_size,
                 //     y[m] = sum_i x[i] conj(c[(i - m) mod n]),  0 <= m < n,
                 // which a cyclic correlation of any length M >= 2n - 1 also produces when the samples are zero-padded to M and the
                 // code buffer holds c at its start AND again at its end (indices i - m < 0 then wrap onto the tail copy): the
-                // engine runs on the smallest M = 2^a 3^b 5^c it has a plan for, searches the first n lags, and scales the code by
-                // n / M so that magnitudes equal those of unnormalised length-n transforms.
+                // engine runs on the cheapest M = 2^a 3^b 5^c it has a plan for (points x cost per point of the plan), searches
+                // the first n lags, and scales the code by n / M so that magnitudes equal those of unnormalised length-n transforms.
                 const bool can_pad = !cfg->bit_transition && cfg->fft_size == cfg->consumed_samples;
+                const bool forced = getenv("B200_FFT_PAD") != nullptr;
                 uint32_t best_m = 0;
+                double best_cost = have_plan && !forced ? 0.9 * (double)h->N * plan_cost_per_point(h->plan) : 1e300;
+                const uint64_t m_min = 2ull * cfg->fft_size - 1, m_max = std::min<uint64_t>(4 * m_min, 1ull << 31);
                 if (can_pad)
-                    for (uint64_t p2 = 1; p2 <= (1ull << 31); p2 *= 2)
-                        for (uint64_t p3 = p2; p3 <= (1ull << 31); p3 *= 3)
-                            for (uint64_t p5 = p3; p5 <= (1ull << 31); p5 *= 5)
-                                if (p5 >= 2ull * cfg->fft_size - 1 && (best_m == 0 || p5 < best_m))
+                    for (uint64_t p2 = 1; p2 <= m_max; p2 *= 2)
+                        for (uint64_t p3 = p2; p3 <= m_max; p3 *= 3)
+                            for (uint64_t p5 = p3; p5 <= m_max; p5 *= 5)
+                                if (p5 >= m_min)
                                     {
                                         FftPlan trial;
                                         const char* w2 = nullptr;
-                                        if (make_fft_plan((uint32_t)p5, kMaxSingleStagePoints, &trial, &w2)) best_m = (uint32_t)p5;
+                                        if (!make_fft_plan((uint32_t)p5, kMaxSingleStagePoints, &trial, &w2)) continue;
+                                        const double cost = (double)p5 * plan_cost_per_point(trial);
+                                        if (cost < best_cost || (cost == best_cost && p5 < best_m))
+                                            {
+                                                best_cost = cost;
+                                                best_m = (uint32_t)p5;
+                                            }
                                     }
-                if (!best_m || !make_fft_plan(best_m, kMaxSingleStagePoints, &h->plan, &why))
+                FftPlan padded_plan;
+                if (best_m && make_fft_plan(best_m, kMaxSingleStagePoints, &padded_plan, &why))
+                    {
+                        h->plan = padded_plan;
+                        h->padded = true;
+                        h->N = best_m;
+                        h->eff = cfg->fft_size;
+                        h->mag_offset = 0;
+                        h->code_len = h->consumed;
+                        h->code_off = 0;
+                    }
+                else if (!have_plan)
                     {
                         delete h;
                         return fail(GNSS_B200_ERR_UNSUPPORTED, "acq_create: fft_size %u: %s", cfg->fft_size, why ? why : "unsupported");
                     }
-                h->padded = true;
-                h->N = best_m;
-                h->eff = cfg->fft_size;
-                h->mag_offset = 0;
-                h->code_len = h->consumed;
-                h->code_off = 0;
             }
         h->center.assign(cfg->max_slots, 0);
         h->bias.assign(cfg->max_slots, 0);
@@ -1157,4 +1195,5 @@ extern "C"
 
     void* gnss_b200_acq_stream(gnss_b200_acq* h) { return h ? (void*)h->stream : nullptr; }
     uint64_t gnss_b200_acq_launch_count(const gnss_b200_acq* h) { return h ? h->launches : 0; }
+    uint32_t gnss_b200_acq_transform_length(const gnss_b200_acq* h) { return h ? h->N : 0; }
 }

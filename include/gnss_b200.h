@@ -242,6 +242,12 @@ extern "C"
     GNSS_B200_API void* gnss_b200_acq_stream(gnss_b200_acq* h);
     GNSS_B200_API uint64_t gnss_b200_acq_launch_count(const gnss_b200_acq* h);
 
+    /* Length of the transforms the handle runs: fft_size, or the longer 2^a 3^b 5^c length of the padded cyclic correlation
+       the engine chose because fft_size has a prime factor its codelets do not cover (> 127) or cover only by a slow direct
+       pass (31 ... 127). The reference's FFTW plan takes any d_fft_size (pcps_acquisition.cc:85-92,114-115); results, indices
+       and magnitudes are those of the fft_size-point search either way. */
+    GNSS_B200_API uint32_t gnss_b200_acq_transform_length(const gnss_b200_acq* h);
+
     /* ------------------------------------------------------------------ */
     /* (b) tracking multicorrelator                                        */
     /* ------------------------------------------------------------------ */

@@ -105,15 +105,27 @@ def test_config1_all_prns(b200, oracle):
     assert same >= 30
 
 
-@pytest.mark.parametrize("name", ["F4092", "F16368", "F65472"])
-def test_dwell_lengths_with_the_prime_31(b200, oracle, name):
+# transform length the engine picks for these dwell lengths (gnss_b200_acq_transform_length): the padded form on a length with a
+# fast plan where that is cheaper than a direct-DFT pass over the 31
+PADDED_LENGTH = {"F2046": 4096, "F4092": 8192, "F8184": 16384, "F12276": 25000, "F16368": 32768, "F32736": 65536, "F65472": 160000}
+
+
+@pytest.mark.parametrize("form", ["chosen", "direct"])
+@pytest.mark.parametrize("name", ["F4092", "F16368", "F65472", "F12276"])
+def test_dwell_lengths_with_the_prime_31(b200, oracle, name, form, monkeypatch):
     """Sample rates that are multiples of 1.023 MHz (4.092, 16.368 MS/s front ends): N = 4092 = 4*3*11*31, 16 368 and
-    65 472 (two stages). The reference's FFT takes any length; here the 31 runs as a direct-DFT pass. Every PRN against the
-    oracle, injected satellites found at their cells."""
+    65 472 (two stages). The reference's FFT takes any length; here the 31 runs as a direct-DFT pass ("direct") or, by default,
+    the search runs as a padded cyclic correlation on a longer length with a fast plan ("chosen"). Every PRN
+    against the oracle in both forms, injected satellites found at their cells."""
     geo, codes, iq, truth = synth.config_scene(name)
     n = geo["n_prn"]
     assert geo["fft_size"] % 31 == 0
+    if form == "direct":
+        monkeypatch.setenv("B200_FFT_PAD", "0")
+    else:
+        monkeypatch.delenv("B200_FFT_PAD", raising=False)
     e = _gpu_engine(b200, geo, n, use_cfar=True, keep_grid=True)
+    assert e.transform_length == (geo["fft_size"] if form == "direct" else PADDED_LENGTH[name])
     e.set_local_codes(np.arange(n), codes)
     got = e.dwell(iq, np.arange(n))
     want, grids = _oracle_search(oracle, geo, codes, [iq], keep=True)
@@ -125,6 +137,28 @@ def test_dwell_lengths_with_the_prime_31(b200, oracle, name):
     det_g = {p + 1 for p in range(n) if got[p]["test_statistic"] > thr}
     det_o = {p + 1 for p in range(n) if want[p][0]["test_statistic"] > thr}
     assert det_g == det_o and det_o and det_o <= {t["prn"] for t in truth}
+    e.close()
+
+
+def test_transform_length_choice(b200, monkeypatch):
+    """Codelet lengths are searched as they are; lengths with the prime 31 on the cheapest padded length; a forced choice
+    (B200_FFT_PAD) is honoured; layouts the padded form cannot take (zero-padded / bit-transition dwells) stay direct."""
+    monkeypatch.delenv("B200_FFT_PAD", raising=False)
+    def length(n, consumed=None, **kw):
+        e = b200.PcpsAcquisitionB200(n, consumed or n, 5000, 250, n * 1000.0, 4, 1, **kw)
+        m = e.transform_length
+        e.close()
+        return m
+    for n in (4000, 8000, 16000, 25000, 32000, 100000, 160000, 7 * 11 * 13 * 4):
+        assert length(n) == n
+    for name, m in PADDED_LENGTH.items():
+        assert length(synth.CONFIGS[name]["fs"] // 1000 * (4 if synth.CONFIGS[name]["system"] == "gal_e1b" else 1)) == m
+    assert length(8184, consumed=4092) == 8184
+    assert length(4092, bit_transition=True) == 4092
+    monkeypatch.setenv("B200_FFT_PAD", "1")
+    assert length(4000) == 8000
+    monkeypatch.setenv("B200_FFT_PAD", "0")
+    assert length(4092) == 4092
 
 
 @pytest.mark.parametrize("fs,n_dwells", [(5003000, 1), (4146000, 2), (2053000, 1)])

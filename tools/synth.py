@@ -176,6 +176,14 @@ CONFIGS = {
                    present=[2, 5], cn0=(46, 52), seed=8),
     "F65472": dict(system="gal_e1b", fs=16368000, sampled_ms=4, doppler_max=1000, doppler_step=250, n_prn=4,
                    present=[1, 4], cn0=(42, 50), seed=9),
+    "F2046": dict(system="gps_l1_ca", fs=2046000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=8,
+                  present=[1, 3, 7], cn0=(46, 52), seed=10),
+    "F8184": dict(system="gps_l1_ca", fs=8184000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=8,
+                  present=[1, 3, 7], cn0=(46, 52), seed=11),
+    "F12276": dict(system="gps_l1_ca", fs=12276000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=8,
+                   present=[1, 3, 7], cn0=(46, 52), seed=12),
+    "F32736": dict(system="gal_e1b", fs=8184000, sampled_ms=4, doppler_max=2000, doppler_step=250, n_prn=4,
+                   present=[1, 4], cn0=(42, 50), seed=13),
     "C4_bds": dict(system="bds_b1i", fs=25000000, sampled_ms=1, doppler_max=5000, doppler_step=250, n_prn=63,
                    present=[1, 6, 9, 14, 19, 27, 33, 40, 52, 60], cn0=(38, 50), seed=6),
 }
