@@ -72,6 +72,7 @@ struct gnss_b200_acq
     PeerLayout peer_layout{};
     std::vector<void*> peer_opened;  // cudaIpcOpenMemHandle mappings to close
     bool peer_connected = false;
+    bool tail_deferred = false;  // peer-connected shard: the last dwell left its per-tile records for peer_exchange_async (shard_tail_kernel)
     // what the last dwell left on the device for gnss_b200_acq_finalize_gathered_async
     FinalizeArgs last_f{};
     // a captured dwell (gnss_b200_acq_capture_*)
@@ -527,10 +528,13 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     if (rc) return rc;
 
     // ---- decision ----
+    // A peer-connected shard decides nothing on its own: its records go to every shard in gnss_b200_acq_peer_exchange_async, which
+    // folds the per-tile records itself (shard_tail_kernel) - no merge / decision / pack launches here.
+    const bool defer_tail = h->peer_connected && h->cfg.use_cfar && !h->step2 && !h->prof.on;
     FinalizeArgs f;
     f.partials = h->d_partials.as<RowPartial>();
     f.tiles = tiles_last;
-    if (tiles_last > 8)
+    if (tiles_last > 8 && !defer_tail)
         {
             // one record per warp of the row-resident kernel: fold them per row first (one warp per row)
             B200_CUDA(h->d_partials2.reserve(sizeof(RowPartial) * (size_t)std::max<size_t>(n_rows, (size_t)n_slots * std::max(tiles_last, tiles_plan))));
@@ -558,12 +562,18 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
     f.rows = h->d_rows.as<gnss_b200_acq_row>();
     f.results = h->d_results.as<gnss_b200_acq_result>();
     f.best_k_local = h->d_bestk.as<uint32_t>();
+    h->last_f = f;
+    h->tail_deferred = defer_tail;
+    if (defer_tail)
+        {
+            h->last_n_slots = n_slots;
+            return GNSS_B200_OK;
+        }
     h->prof.begin(CAT_DECIDE, h->stream);
     finalize_kernel<<<n_slots, 32, 0, h->stream>>>(f);
     h->prof.end(h->stream);
     h->launches++;
     B200_CUDA(cudaGetLastError());
-    h->last_f = f;
     if (h->xchg_world)
         {
             // sharded search: this shard's rows of the call's slots, contiguous, ready to be sent
@@ -903,6 +913,7 @@ extern "C"
         B200_CUDA(cudaStreamSynchronize(h->stream));
         if (results)
             {
+                B200_REQUIRE(!h->tail_deferred, GNSS_B200_ERR_STATE, "acq_sync: a peer-connected shard decides in gnss_b200_acq_peer_exchange_async; call it after the dwell");
                 B200_REQUIRE(n_slots == h->last_n_slots, GNSS_B200_ERR_INVALID, "acq_sync: n_slots differs from the last dwell");
                 std::memcpy(results, h->h_results.p, sizeof(gnss_b200_acq_result) * n_slots);
             }
@@ -1042,6 +1053,7 @@ extern "C"
         B200_REQUIRE(h->xchg_world, GNSS_B200_ERR_STATE, "acq_finalize_gathered_async: call gnss_b200_acq_exchange_buffers first");
         B200_REQUIRE(n_slots == h->last_n_slots && n_slots > 0, GNSS_B200_ERR_INVALID, "acq_finalize_gathered_async: n_slots differs from the last dwell");
         B200_REQUIRE(h->cfg.use_cfar, GNSS_B200_ERR_UNSUPPORTED, "acq_finalize_gathered_async: only the CFAR statistic can be decided from row records");
+        B200_REQUIRE(!h->tail_deferred, GNSS_B200_ERR_STATE, "acq_finalize_gathered_async: this shard is peer-connected; its records travel by gnss_b200_acq_peer_exchange_async");
         finalize_gathered_kernel<<<n_slots, 32, 0, h->stream>>>(h->last_f, h->d_recv.as<gnss_b200_acq_row>(), h->xchg_world, h->xchg_chunk, n_slots);
         h->launches++;
         B200_CUDA(cudaGetLastError());
@@ -1132,10 +1144,22 @@ extern "C"
         B200_REQUIRE(h->cfg.use_cfar, GNSS_B200_ERR_UNSUPPORTED, "acq_peer_exchange_async: only the CFAR statistic can be decided from row records");
         const PeerLayout& L = h->peer_layout;
         uint32_t* epoch = h->d_peer.as<uint32_t>();
-        peer_scatter_kernel<<<L.world, 256, 0, h->stream>>>(h->d_send.as<gnss_b200_acq_row>(), n_slots * h->xchg_chunk, h->d_peer_ptrs.as<char*>(), L, epoch);
-        finalize_peer_kernel<<<n_slots, 32, 0, h->stream>>>(h->last_f, h->d_peer.as<char>(), L, epoch, h->xchg_chunk, n_slots);
-        peer_epoch_bump_kernel<<<1, 1, 0, h->stream>>>(epoch);
-        h->launches += 3;
+        if (h->tail_deferred)
+            {
+                // two launches: records folded and delivered, then the decision (which also advances the epoch)
+                shard_tail_kernel<<<n_slots, 256, 0, h->stream>>>(h->last_f, h->d_peer_ptrs.as<char*>(), L, epoch, h->xchg_chunk, epoch + 16);
+                finalize_peer_kernel<<<n_slots, 32, 0, h->stream>>>(h->last_f, h->d_peer.as<char>(), L, epoch, h->xchg_chunk, n_slots, epoch + 32);
+                h->launches += 2;
+                h->tail_deferred = false;
+            }
+        else
+            {
+                // the dwell ran before the peers were connected (or under the per-kernel profiler): its packed records are in d_send
+                peer_scatter_kernel<<<L.world, 256, 0, h->stream>>>(h->d_send.as<gnss_b200_acq_row>(), n_slots * h->xchg_chunk, h->d_peer_ptrs.as<char*>(), L, epoch);
+                finalize_peer_kernel<<<n_slots, 32, 0, h->stream>>>(h->last_f, h->d_peer.as<char>(), L, epoch, h->xchg_chunk, n_slots, nullptr);
+                peer_epoch_bump_kernel<<<1, 1, 0, h->stream>>>(epoch);
+                h->launches += 3;
+            }
         B200_CUDA(cudaGetLastError());
         B200_CUDA(cudaMemcpyAsync(h->h_results.p, h->d_results.p, sizeof(gnss_b200_acq_result) * n_slots, cudaMemcpyDeviceToHost, h->stream));
         return GNSS_B200_OK;

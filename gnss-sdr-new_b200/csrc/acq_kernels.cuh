@@ -601,7 +601,8 @@ static __global__ void peer_scatter_kernel(const gnss_b200_acq_row* send, uint32
 
 // finalize_gathered_kernel behind the wait for everybody's records; a peer that never delivers (a failed rank) ends the wait after
 // ~2 s with NaN statistics instead of hanging the device
-static __global__ void finalize_peer_kernel(const FinalizeArgs a, const char* own, const PeerLayout L, const uint32_t* epoch_ctr, uint32_t chunk, uint32_t n_slots)
+// bump_ticket != nullptr: the last CTA to finish advances the epoch counter itself (no peer_epoch_bump_kernel behind this one)
+static __global__ void finalize_peer_kernel(const FinalizeArgs a, const char* own, const PeerLayout L, uint32_t* epoch_ctr, uint32_t chunk, uint32_t n_slots, uint32_t* bump_ticket)
 {
     const uint32_t epoch = *epoch_ctr + 1u, par = epoch & 1u;
     const int lane = threadIdx.x;
@@ -672,10 +673,106 @@ static __global__ void finalize_peer_kernel(const FinalizeArgs a, const char* ow
             res.input_power = (ro.valid && ok) ? (float)(((double)per / 2.0) / (double)a.dwell_after[si]) : nanf("");
             res.test_statistic = best / res.input_power;  // :542
             a.results[si] = res;
+            if (bump_ticket)
+                {
+                    // every CTA read the epoch before it got here; the last one through moves it on
+                    __threadfence();
+                    if (atomicAdd(bump_ticket, 1u) == gridDim.x - 1u)
+                        {
+                            *bump_ticket = 0u;
+                            *epoch_ctr = epoch;
+                        }
+                }
         }
 }
 
 static __global__ void peer_epoch_bump_kernel(uint32_t* epoch_ctr) { *epoch_ctr += 1u; }
+
+// The tail of a peer-connected shard's search in ONE kernel (instead of merge_partials + finalize + pack_rows + peer_scatter): CTA
+// si folds the per-tile records of its slot's rows (the arithmetic of merge_partials_kernel / finalize_kernel, so the records
+// are bit-identical to theirs), stores them straight into EVERY shard's recv[parity][rank] and, when the last CTA of the grid is
+// through, raises this shard's flag in every region. `ticket` (own region, offset 64) counts finished CTAs and is left at 0.
+static __global__ void shard_tail_kernel(const FinalizeArgs a, char* const* peers, const PeerLayout L, const uint32_t* epoch_ctr, uint32_t chunk, uint32_t* ticket)
+{
+    const uint32_t epoch = *epoch_ctr + 1u, par = epoch & 1u;
+    const uint32_t si = blockIdx.x, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    for (uint32_t j = warp; j < chunk; j += n_warps)
+        {
+            gnss_b200_acq_row r;
+            r.max_val = 0.f;
+            r.max_idx = 0;
+            r.row_sum = 0.f;
+            r.valid = 0;
+            if (j < a.nD_local)
+                {
+                    const RowPartial* p = a.partials + ((size_t)si * a.nD_local + j) * a.tiles;
+                    float m, s;
+                    uint32_t mi;
+                    if (a.tiles > 8)
+                        {
+                            m = -1.f, s = 0.f, mi = 0xffffffffu;
+                            for (uint32_t t = lane; t < a.tiles; t += 32)
+                                {
+                                    const RowPartial q = p[t];
+                                    s += q.sum;
+                                    if (q.max_val > m || (q.max_val == m && q.max_idx < mi))
+                                        {
+                                            m = q.max_val;
+                                            mi = q.max_idx;
+                                        }
+                                }
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1)
+                                {
+                                    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+                                    const uint32_t oi = __shfl_xor_sync(0xffffffffu, mi, o);
+                                    s += __shfl_xor_sync(0xffffffffu, s, o);
+                                    if (om > m || (om == m && oi < mi))
+                                        {
+                                            m = om;
+                                            mi = oi;
+                                        }
+                                }
+                        }
+                    else
+                        {
+                            m = p[0].max_val, s = p[0].sum, mi = p[0].max_idx;
+                            for (uint32_t t = 1; t < a.tiles; t++)
+                                {
+                                    s += p[t].sum;
+                                    if (p[t].max_val > m || (p[t].max_val == m && p[t].max_idx < mi))
+                                        {
+                                            m = p[t].max_val;
+                                            mi = p[t].max_idx;
+                                        }
+                                }
+                        }
+                    r.max_val = m;
+                    r.max_idx = mi;
+                    r.row_sum = s;
+                    r.valid = 1;
+                }
+            uint4 raw;
+            memcpy(&raw, &r, sizeof(raw));
+            for (uint32_t d = lane; d < L.world; d += 32)
+                {
+                    uint4* dst = reinterpret_cast<uint4*>(peers[d] + L.recv_off) + (size_t)(par * L.world + L.rank) * L.per_shard_rows;
+                    dst[(size_t)si * chunk + j] = raw;
+                }
+        }
+    __threadfence_system();
+    __syncthreads();
+    __shared__ uint32_t s_last;
+    if (threadIdx.x == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1u) ? 1u : 0u;
+    __syncthreads();
+    if (s_last)
+        {
+            __threadfence_system();
+            if (threadIdx.x == 0) *ticket = 0u;
+            for (uint32_t d = threadIdx.x; d < L.world; d += blockDim.x)
+                st_release_sys(reinterpret_cast<uint32_t*>(peers[d] + L.flags_off + (size_t)(par * L.world + L.rank) * 128u), epoch);
+        }
+}
 
 // ---- first_vs_second_peak_statistic (:546-612): second maximum of the best row outside the +-1 chip window ----
 struct SecondPeakArgs

@@ -172,11 +172,14 @@ extern "C"
 
     /* The exchange itself over peer memory, fused behind the search — no collective library between the kernels:
        every shard owns a region (flags + double-buffered [world][max_slots][chunk] records) that its peers can store into;
-       gnss_b200_acq_peer_exchange_async queues, on the handle's stream, (1) a kernel that stores this shard's packed records
-       into EVERY shard's region over NVLink and then raises this shard's flag there (release, system scope), (2) the decision
-       kernel, which waits for all `world` flags of the current exchange (acquire, system scope; ~2 s time-out -> NaN statistics)
-       and decides from the records, (3) the result copy. All of it may sit inside gnss_b200_acq_capture_begin / _end, so a
-       rank's whole step is one graph launch. Every shard must call it once per search, in the same order.
+       gnss_b200_acq_peer_exchange_async queues, on the handle's stream, (1) a kernel that folds this shard's per-tile records
+       into row records, stores them into EVERY shard's region over NVLink and then raises this shard's flag there (release,
+       system scope), (2) the decision kernel, which waits for all `world` flags of the current exchange (acquire, system
+       scope; ~2 s time-out -> NaN statistics) and decides from the records, (3) the result copy. All of it may sit inside
+       gnss_b200_acq_capture_begin / _end, so a rank's whole step is one graph launch. Every shard must call it once per
+       search, in the same order. Once connected, a dwell leaves the shard-local merge / decision / pack launches out (their
+       work is kernel (1)): the search's results exist only after this call, and gnss_b200_acq_sync asked for results before
+       it returns GNSS_B200_ERR_STATE.
        Setup, after gnss_b200_acq_exchange_buffers: _peer_setup(rank) allocates the region and returns its CUDA IPC handle (64
        opaque bytes, for peers in OTHER processes: exchange them with any host-side all-gather) and its device pointer (for
        handles of the SAME process, also on other devices); _peer_connect takes either all `world` IPC handles or all `world`

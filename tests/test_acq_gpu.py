@@ -140,6 +140,48 @@ def test_dwell_lengths_with_the_prime_31(b200, oracle, name, form, monkeypatch):
     e.close()
 
 
+@pytest.mark.parametrize("scene,n_prn", [("C2", 6), ("C1", 8), ("F4092", 4)])
+def test_peer_exchange_with_a_single_shard(b200, scene, n_prn):
+    """gnss_b200_acq_peer_* with world = 1 on one GPU: the fused tail of a connected shard (per-tile records folded, delivered
+    and decided by two kernels instead of the merge / decision / pack launches) gives the records of a plain engine bit for
+    bit, eagerly and from a captured graph. The two-GPU form is tests/test_two_devices_gpu.py."""
+    import torch
+    geo, codes, iq, _ = synth.config_scene(scene, n_prn=n_prn, n_dwells=3)
+    N = geo["consumed_samples"]
+    iq = np.ascontiguousarray(iq).reshape(3, N)
+    slots = np.arange(n_prn, dtype=np.uint32)
+    one = _gpu_engine(b200, geo, n_prn, use_cfar=True)
+    one.set_local_codes(slots, codes[:n_prn])
+    e = _gpu_engine(b200, geo, n_prn, use_cfar=True)
+    e.set_local_codes(slots, codes[:n_prn])
+    e.exchange_buffers(1)
+    _, ptr = e.peer_setup(0)
+    e.peer_connect(regions=[ptr])
+    buf = torch.empty(2 * N, dtype=torch.float32, device="cuda")
+    for k in range(3):
+        want = one.dwell(iq[k], slots)
+        buf.copy_(torch.from_numpy(iq[k].view(np.float32).copy()))
+        torch.cuda.synchronize()
+        if k == 1:
+            e.capture_begin()
+            e.dwell_device_async(buf.data_ptr(), slots)
+            e.peer_exchange_async(n_prn)
+            e.capture_end()
+        if k >= 1:
+            e.replay_async()
+        else:
+            e.dwell_device_async(buf.data_ptr(), slots)
+            with pytest.raises(b200.B200Error):
+                e.sync(n_prn)
+            e.peer_exchange_async(n_prn)
+        got = e.sync(n_prn)
+        assert got.tobytes() == want.tobytes(), (scene, k)
+        for p in (0, n_prn - 1):
+            assert e.read_rows(p).tobytes() == one.read_rows(p).tobytes()
+    e.close()
+    one.close()
+
+
 def test_transform_length_choice(b200, monkeypatch):
     """Codelet lengths are searched as they are; lengths with the prime 31 on the cheapest padded length; a forced choice
     (B200_FFT_PAD) is honoured; layouts the padded form cannot take (zero-padded / bit-transition dwells) stay direct."""

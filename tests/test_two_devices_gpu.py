@@ -126,6 +126,9 @@ def test_record_exchange_over_peer_memory(two_devices, scene, n_prn):
                 e.replay_async()
             else:
                 e.dwell_device_async(bufs[r].data_ptr(), slots)
+                if k == 0:       # a connected shard has no results of its own before the exchange
+                    with pytest.raises(b200.B200Error):
+                        e.sync(n_prn)
                 e.peer_exchange_async(n_prn)
         for e in shards:
             got = e.sync(n_prn)
