@@ -182,6 +182,79 @@ def test_peer_exchange_with_a_single_shard(b200, scene, n_prn):
     one.close()
 
 
+def test_padded_form_with_the_other_engine_features(b200, oracle, monkeypatch):
+    """The padded search (4.092 MS/s: 4092 lags on an 8192-point transform) under everything else a handle can be asked for:
+    the first-vs-second-peak statistic with and without a kept grid, cshort samples with shifted Doppler centres, a narrow
+    second-step grid, and a split into row shards — each against the oracle's 4092-point search."""
+    monkeypatch.delenv("B200_FFT_PAD", raising=False)
+    geo, codes, iq, truth = synth.config_scene("F4092", n_prn=4)
+    slots = np.arange(4)
+    present = {t["prn"] for t in truth}
+    want, _ = _oracle_search(oracle, geo, codes, [iq], use_cfar=False)
+    for keep in (False, True):
+        e = _gpu_engine(b200, geo, 4, use_cfar=False, keep_grid=keep)
+        assert e.transform_length == 8192
+        e.set_local_codes(slots, codes)
+        got = e.dwell(iq, slots)
+        for p in range(4):
+            _compare(got[p], want[p][0], strict_idx=(p + 1) in present)
+            assert got[p]["second_peak"] == pytest.approx(want[p][0]["second_peak"], rel=RTOL)
+        e.close()
+    # cshort items, Doppler centres
+    iqs = synth.to_cshort(iq, scale=64.0)
+    centers = [0, 750, -1125, 250]
+    e = _gpu_engine(b200, geo, 4, use_cfar=True)
+    e.set_local_codes(slots, codes)
+    for p, c in enumerate(centers):
+        e.set_doppler_center(p, c)
+    got = e.dwell(iqs, slots)
+    want, _ = _oracle_search(oracle, geo, codes, [iqs], centers=centers)
+    for p in range(4):
+        _compare(got[p], want[p][0], strict_idx=(p == 0))
+    e.close()
+    # second step around the coarse Doppler
+    e1 = _gpu_engine(b200, geo, 4, use_cfar=True)
+    e2 = _gpu_engine(b200, geo, 4, use_cfar=True, step2=(4, 125.0))
+    assert e2.transform_length == 8192
+    e1.set_local_codes(slots, codes)
+    e2.set_local_codes(slots, codes)
+    r1 = e1.dwell(iq, slots)
+    for p in range(4):
+        e2.set_step2_center(p, float(r1[p]["doppler_hz"]), r1[p]["input_power"])
+    r2 = e2.dwell(iq, slots)
+    for p in range(4):
+        a = oracle.acq(fft_size=geo["fft_size"], consumed_samples=geo["consumed_samples"], doppler_max=geo["doppler_max"],
+                       doppler_step=geo["doppler_step"], fs=geo["fs"], samples_per_chip=geo["samples_per_chip"],
+                       samples_per_code=geo["samples_per_code"], use_cfar=True)
+        a.set_local_code(codes[p])
+        a.reset()
+        w1 = a.dwell(iq)
+        w2 = a.dwell_step2(iq, 4, 125.0, float(w1["doppler_hz"]))
+        a.close()
+        if int(r1[p]["doppler_hz"]) != w1["doppler_hz"]:
+            continue
+        assert r2[p]["peak"] == pytest.approx(w2["peak"], rel=RTOL) and r2[p]["test_statistic"] == pytest.approx(w2["test_statistic"], rel=RTOL)
+        if (p + 1) in present:
+            assert int(r2[p]["code_phase"]) == w2["code_phase"] and int(r2[p]["doppler_hz"]) == w2["doppler_hz"]
+    e2.close()
+    # three row shards merged on the host == the unsharded handle, bit for bit
+    nD = e1.n_doppler
+    cuts = [0, 13, 27, nD]
+    rows = np.zeros((4, nD), dtype=b200.ACQ_ROW_DTYPE)
+    for r0, r1_ in zip(cuts[:-1], cuts[1:]):
+        sh = _gpu_engine(b200, geo, 4, use_cfar=True, row_begin=r0, row_end=r1_)
+        sh.set_local_codes(slots, codes)
+        sh.dwell(iq, slots)
+        for p in range(4):
+            rows[p, r0:r1_] = sh.read_rows(p)[r0:r1_]
+        sh.close()
+    for p in range(4):
+        assert rows[p].tobytes() == e1.read_rows(p).tobytes()
+        m = b200.finalize_rows(rows[p], geo["fft_size"], geo["doppler_max"], geo["doppler_step"], 0, 1)
+        assert m["test_statistic"] == r1[p]["test_statistic"] and m["code_phase"] == r1[p]["code_phase"] and m["doppler_hz"] == r1[p]["doppler_hz"]
+    e1.close()
+
+
 def test_transform_length_choice(b200, monkeypatch):
     """Codelet lengths are searched as they are; lengths with the prime 31 on the cheapest padded length; a forced choice
     (B200_FFT_PAD) is honoured; layouts the padded form cannot take (zero-padded / bit-transition dwells) stay direct."""
