@@ -138,7 +138,7 @@ int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
             a.codes_td = h->d_codes_td.as<float2>();
             a.code_len = h->code_len;
             a.code_off = h->code_off;
-            a.code_wrap = h->padded ? 1u : 0u;
+            a.code_wrap = h->padded ? h->cfg.fft_size : 0u;
             a.code_scale = h->padded ? (float)((double)h->cfg.fft_size / (double)h->N) : 1.0f;
             a.slots = d_slots;
             a.out_buf = h->d_cbuf.as<float2>();
@@ -155,7 +155,7 @@ int run_code_forward(gnss_b200_acq* h, uint32_t n, const uint32_t* d_slots)
             a.codes_td = h->d_codes_td.as<float2>();
             a.code_len = h->code_len;
             a.code_off = h->code_off;
-            a.code_wrap = h->padded ? 1u : 0u;
+            a.code_wrap = h->padded ? h->cfg.fft_size : 0u;
             a.code_scale = h->padded ? (float)((double)h->cfg.fft_size / (double)h->N) : 1.0f;
             a.y0 = y0;
             a.out_buf = h->d_scratch.as<float2>();
@@ -588,7 +588,7 @@ int enqueue_dwell(gnss_b200_acq* h, const void* d_samples, int is_cshort, uint32
             SecondPeakArgs sp;
             sp.nD_local = h->nD_local;
             sp.eff = h->eff;
-            sp.N = h->N;
+            sp.N = h->cfg.fft_size;  // the window wraps at d_fft_size (:580-591), not at a padded transform length
             sp.samples_per_chip = h->cfg.samples_per_chip;
             sp.slots = d_slots;
             sp.best_k_local = h->d_bestk.as<uint32_t>();
@@ -719,17 +719,19 @@ int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, 
             {
                 // A length the mixed-radix kernels cannot take (a prime factor > 127; FFTW in the reference takes any d_fft_size,
                 // pcps_acquisition.cc:85-92,114-115) or take only slowly. The search needs the CYCLIC correlation of length
-                // n = fft_size,
-                //     y[m] = sum_i x[i] conj(c[(i - m) mod n]),  0 <= m < n,
-                // which a cyclic correlation of any length M >= 2n - 1 also produces when the samples are zero-padded to M and the
-                // code buffer holds c at its start AND again at its end (indices i - m < 0 then wrap onto the tail copy): the
-                // engine runs on the cheapest M = 2^a 3^b 5^c it has a plan for (points x cost per point of the plan), searches
-                // the first n lags, and scales the code by n / M so that magnitudes equal those of unnormalised length-n transforms.
-                const bool can_pad = !cfg->bit_transition && cfg->fft_size == cfg->consumed_samples;
+                // n = fft_size of the (zero-padded) block x, nonzero on [0, consumed), with the zero-padded code c:
+                //     y[m] = sum_i x[i] conj(c[(i - m) mod n]),  0 <= m < n.
+                // i - m runs over [-(n - 1), consumed - 1]: a cyclic correlation of any length M >= n + consumed - 1 produces the
+                // same y when the samples are zero-padded to M and the code buffer holds c[0 .. consumed) at its start and
+                // c[1 .. n) at its END (negative i - m wrap onto that tail) - for every layout of set_local_code (:176-209): full
+                // (2n - 1), zero-padded double length (1.5n - 1), bit transition. The engine runs on the cheapest
+                // M = 2^a 3^b 5^c it has a plan for (points x cost per point of the plan), searches the lags the layout keeps, and
+                // scales the code by n / M so that magnitudes equal those of unnormalised length-n transforms.
+                const bool can_pad = true;
                 const bool forced = getenv("B200_FFT_PAD") != nullptr;
                 uint32_t best_m = 0;
                 double best_cost = have_plan && !forced ? 0.9 * (double)h->N * plan_cost_per_point(h->plan) : 1e300;
-                const uint64_t m_min = 2ull * cfg->fft_size - 1, m_max = std::min<uint64_t>(4 * m_min, 1ull << 31);
+                const uint64_t m_min = (uint64_t)cfg->fft_size + cfg->consumed_samples - 1, m_max = std::min<uint64_t>(4 * m_min, 1ull << 31);
                 if (can_pad)
                     for (uint64_t p2 = 1; p2 <= m_max; p2 *= 2)
                         for (uint64_t p3 = p2; p3 <= m_max; p3 *= 3)
@@ -751,11 +753,7 @@ int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, 
                     {
                         h->plan = padded_plan;
                         h->padded = true;
-                        h->N = best_m;
-                        h->eff = cfg->fft_size;
-                        h->mag_offset = 0;
-                        h->code_len = h->consumed;
-                        h->code_off = 0;
+                        h->N = best_m;  // eff, mag_offset, code_len, code_off stay those of the fft_size-point layout
                     }
                 else if (!have_plan)
                     {

@@ -80,7 +80,7 @@ struct StageArgs
     const float2* codes_td;  // [transform][code_len]
     uint32_t code_len;
     uint32_t code_off;       // first position of the code inside the padded buffer
-    uint32_t code_wrap;      // != 0: a second copy of the code ends the buffer (cyclic correlation of a shorter length, see acq.cu create_impl)
+    uint32_t code_wrap;      // != 0: the code's period (fft_size) inside a longer padded transform; its tail copy ends the buffer (acq.cu create_impl)
     float code_scale;        // factor on the code samples (1 unless code_wrap)
     // ---- LOAD_BUF / LOAD_PRODUCT ----
     const float2* in_buf;    // LOAD_BUF: [transform - in_y0][N]; LOAD_PRODUCT: X [call group][nD_local][N]
@@ -199,10 +199,18 @@ __global__ void __launch_bounds__(512) stage_kernel(const StageArgs a)
                     const uint32_t idx = i / C, c = i - idx * C;
                     const uint32_t pos = idx * st.pos_stride + tile_off + c;
                     float2 v = make_float2(0.f, 0.f);
-                    if (pos >= a.code_off && pos - a.code_off < a.code_len)
-                        v = __ldg(code + (pos - a.code_off));
-                    else if (a.code_wrap && pos >= (uint32_t)N - a.code_len)
-                        v = __ldg(code + (pos - ((uint32_t)N - a.code_len)));
+                    // index into the code's own period: the position itself, or in the padded form (period code_wrap < N) the
+                    // first `consumed` positions directly and the last code_wrap - 1 positions wrapped onto 1 .. code_wrap - 1
+                    uint32_t j = pos;
+                    if (a.code_wrap)
+                        {
+                            j = 0xffffffffu;
+                            if (pos < a.consumed)
+                                j = pos;
+                            else if (pos + a.code_wrap > (uint32_t)N)
+                                j = pos + a.code_wrap - (uint32_t)N;
+                        }
+                    if (j != 0xffffffffu && j >= a.code_off && j - a.code_off < a.code_len) v = __ldg(code + (j - a.code_off));
                     if (a.code_wrap) v = make_float2(v.x * a.code_scale, v.y * a.code_scale);
                     s[i] = v;
                 }

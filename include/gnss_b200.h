@@ -44,7 +44,7 @@ extern "C"
         GNSS_B200_OK = 0,
         GNSS_B200_ERR_INVALID = -1,     /* bad argument */
         GNSS_B200_ERR_CUDA = -2,        /* CUDA runtime error (message in last_error) */
-        GNSS_B200_ERR_UNSUPPORTED = -3, /* e.g. FFT length with an unsupported prime factor */
+        GNSS_B200_ERR_UNSUPPORTED = -3, /* e.g. a statistic that cannot be decided from row records */
         GNSS_B200_ERR_NO_DEVICE = -4,   /* no CUDA device: the engine has no CPU path */
         GNSS_B200_ERR_STATE = -5        /* call order violated (e.g. dwell before set_local_code) */
     } gnss_b200_status;
@@ -65,7 +65,7 @@ extern "C"
        sample stream and one search geometry (one Acq_Conf, acq_conf.h:33-82). */
     typedef struct
     {
-        uint32_t fft_size;         /* d_fft_size (:85-92) — any length whose prime factors are <= 127 (register codelets up to 13) */
+        uint32_t fft_size;         /* d_fft_size (:85-92) — any length (see gnss_b200_acq_transform_length for lengths with a prime factor >= 31) */
         uint32_t consumed_samples; /* d_consumed_samples (:71) */
         uint32_t bit_transition;   /* Acq_Conf::bit_transition_flag */
         int32_t doppler_max;       /* Acq_Conf::doppler_max [Hz] */

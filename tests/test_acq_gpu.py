@@ -257,7 +257,7 @@ def test_padded_form_with_the_other_engine_features(b200, oracle, monkeypatch):
 
 def test_transform_length_choice(b200, monkeypatch):
     """Codelet lengths are searched as they are; lengths with the prime 31 on the cheapest padded length; a forced choice
-    (B200_FFT_PAD) is honoured; layouts the padded form cannot take (zero-padded / bit-transition dwells) stay direct."""
+    (B200_FFT_PAD) is honoured; zero-padded and bit-transition dwells take the padded form as well."""
     monkeypatch.delenv("B200_FFT_PAD", raising=False)
     def length(n, consumed=None, **kw):
         e = b200.PcpsAcquisitionB200(n, consumed or n, 5000, 250, n * 1000.0, 4, 1, **kw)
@@ -268,8 +268,8 @@ def test_transform_length_choice(b200, monkeypatch):
         assert length(n) == n
     for name, m in PADDED_LENGTH.items():
         assert length(synth.CONFIGS[name]["fs"] // 1000 * (4 if synth.CONFIGS[name]["system"] == "gal_e1b" else 1)) == m
-    assert length(8184, consumed=4092) == 8184
-    assert length(4092, bit_transition=True) == 4092
+    assert length(8184, consumed=4092) == 12500      # zero-padded double-length dwell: M >= fft_size + consumed - 1
+    assert length(4092, bit_transition=True) == 8192
     monkeypatch.setenv("B200_FFT_PAD", "1")
     assert length(4000) == 8000
     monkeypatch.setenv("B200_FFT_PAD", "0")
@@ -358,29 +358,44 @@ def test_first_vs_second_without_grid(b200, oracle):
         assert got[p]["second_peak"] == pytest.approx(want[p][0]["second_peak"], rel=RTOL)
 
 
-def test_zero_padded_long_coherent_and_bit_transition(b200, oracle):
-    """sampled_ms != ms_per_code doubles the FFT and zero-pads (:85-92,:200-204); bit_transition keeps the upper half (:188-193,:671)."""
-    fs = 4000000
+@pytest.mark.parametrize("fs,form,lengths", [(4000000, "own", (16000, 8000)), (4092000, "chosen", (25000, 16384)), (4092000, "direct", (16368, 8184)),
+                                            (2056000, "chosen", (12500, 10000))])
+def test_zero_padded_long_coherent_and_bit_transition(b200, oracle, monkeypatch, fs, form, lengths):
+    """sampled_ms != ms_per_code doubles the FFT and zero-pads (:85-92,:200-204); bit_transition keeps the upper half
+    (:188-193,:671). At 4 MS/s on the lengths' own plans; at 4.092 MS/s (prime 31) both as a padded correlation on a fast-plan
+    length and with the direct-DFT pass; at 2.056 MS/s (4112 = 2^4 * 257: no plan of its own) padded only."""
+    if form == "direct":
+        monkeypatch.setenv("B200_FFT_PAD", "0")
+    else:
+        monkeypatch.delenv("B200_FFT_PAD", raising=False)
+    n = fs // 1000
+    spc = int(np.ceil(fs / 1.023e6))
     truth = [dict(system="gps_l1_ca", prn=5, delay=1234, doppler=1130.0, cn0=42.0)]
-    # 2 ms coherent: consumed 8000, N = 16000
-    iq = synth.make_iq(8000, fs, truth, seed=91)
-    geo = dict(fft_size=16000, consumed_samples=8000, doppler_max=5000, doppler_step=250, fs=fs, samples_per_chip=4, samples_per_code=4000.0)
+    # 2 ms coherent: consumed 2n, N = 4n
+    iq = synth.make_iq(2 * n, fs, truth, seed=91)
+    geo = dict(fft_size=4 * n, consumed_samples=2 * n, doppler_max=5000, doppler_step=250, fs=fs, samples_per_chip=spc, samples_per_code=float(n))
     codes = np.stack([synth.adapter_code("gps_l1_ca", p, fs, 2) for p in (5, 6)])
-    e = _gpu_engine(b200, geo, 2, use_cfar=True)
+    e = _gpu_engine(b200, geo, 2, use_cfar=True, keep_grid=True)
+    assert e.transform_length == lengths[0]
     e.set_local_codes([0, 1], codes)
     got = e.dwell(iq, [0, 1])
-    want, _ = _oracle_search(oracle, geo, codes, [iq])
+    want, grids = _oracle_search(oracle, geo, codes, [iq], keep=True)
     _compare(got[0], want[0][0])
     _compare(got[1], want[1][0], strict_idx=False)
-    assert int(got[0]["code_phase"]) % 4000 == 1234
-    # bit transition: consumed = N = 8000, effective 4000
-    geo = dict(fft_size=8000, consumed_samples=8000, doppler_max=5000, doppler_step=250, fs=fs, samples_per_chip=4, samples_per_code=4000.0)
-    e = _gpu_engine(b200, geo, 2, use_cfar=True, bit_transition=True, keep_grid=True)
-    e.set_local_codes([0, 1], codes)
-    got = e.dwell(iq, [0, 1])
-    want, grids = _oracle_search(oracle, geo, codes, [iq], bit_transition=True, keep=True)
-    _compare(got[0], want[0][0])
+    assert int(got[0]["code_phase"]) % n == 1234
     assert np.abs(e.read_grid(0) - grids[0]).max() <= 2e-5 * grids[0].max()
+    e.close()
+    # bit transition: consumed = N = 2n, effective n; both statistics
+    geo = dict(fft_size=2 * n, consumed_samples=2 * n, doppler_max=5000, doppler_step=250, fs=fs, samples_per_chip=spc, samples_per_code=float(n))
+    for use_cfar in (True, False):
+        e = _gpu_engine(b200, geo, 2, use_cfar=use_cfar, bit_transition=True, keep_grid=True)
+        assert e.transform_length == lengths[1]
+        e.set_local_codes([0, 1], codes)
+        got = e.dwell(iq, [0, 1])
+        want, grids = _oracle_search(oracle, geo, codes, [iq], use_cfar=use_cfar, bit_transition=True, keep=True)
+        _compare(got[0], want[0][0])
+        assert np.abs(e.read_grid(0) - grids[0]).max() <= 2e-5 * grids[0].max()
+        e.close()
 
 
 def test_cshort_input_and_doppler_center(b200, oracle):
@@ -505,9 +520,9 @@ def test_a_captured_search_replays_bit_identically(b200):
 
 
 def test_unsupported_and_state_errors(b200):
-    with pytest.raises(b200.B200Error):
-        b200.PcpsAcquisitionB200(2 * 2056, 2056, 5000, 250, 2.056e6, 3, 1, bit_transition=True)  # 257 | 4112 and bit_transition: no padded form
-    b200.PcpsAcquisitionB200(2056, 2056, 5000, 250, 2.056e6, 3, 1).close()                       # 257 | 2056 alone: padded correlation
+    for kw in (dict(), dict(bit_transition=True)):                                               # 257 | 2056: padded correlation, every layout
+        b200.PcpsAcquisitionB200(2 * 2056, 2056, 5000, 250, 2.056e6, 3, 1, **kw).close()
+    b200.PcpsAcquisitionB200(2056, 2056, 5000, 250, 2.056e6, 3, 1).close()
     e = b200.PcpsAcquisitionB200(4000, 4000, 5000, 250, 4e6, 4, 2)
     with pytest.raises(b200.B200Error):
         e.dwell(np.zeros(4000, np.complex64), [0])  # no local code
