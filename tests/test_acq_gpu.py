@@ -200,6 +200,19 @@ def test_padded_form_with_the_other_engine_features(b200, oracle, monkeypatch):
             _compare(got[p], want[p][0], strict_idx=(p + 1) in present)
             assert got[p]["second_peak"] == pytest.approx(want[p][0]["second_peak"], rel=RTOL)
         e.close()
+    # peaks in the first / last samples of the code period: the exclusion window wraps at d_fft_size (:580-591), not at 8192
+    n = geo["fft_size"]
+    edge = [dict(system="gps_l1_ca", prn=1, delay=1, doppler=730.0, cn0=50.0), dict(system="gps_l1_ca", prn=3, delay=n - 2, doppler=-2210.0, cn0=50.0)]
+    iq_edge = synth.make_iq(n, geo["fs"], edge, seed=5)
+    want_e, _ = _oracle_search(oracle, geo, codes, [iq_edge], use_cfar=False)
+    e = _gpu_engine(b200, geo, 4, use_cfar=False)
+    e.set_local_codes(slots, codes)
+    got = e.dwell(iq_edge, slots)
+    assert int(got[0]["code_phase"]) == 1 and int(got[2]["code_phase"]) == n - 2
+    for p in (0, 2):
+        _compare(got[p], want_e[p][0])
+        assert got[p]["second_peak"] == pytest.approx(want_e[p][0]["second_peak"], rel=RTOL)
+    e.close()
     # cshort items, Doppler centres
     iqs = synth.to_cshort(iq, scale=64.0)
     centers = [0, 750, -1125, 250]
