@@ -8,8 +8,9 @@ namespace cl
 {
 namespace
 {
-// B200_ACQ_CLUSTER: 0 = never use the row-resident kernel (two-kernel path), 1 = the variant that stages X_k by TMA bulk copies;
-// unset / anything else = the default variant (operands in registers). Read once per process (tuning aid, like B200_NO_FIXED).
+// B200_ACQ_CLUSTER: 0 = never use the row-resident kernel (two-kernel path), 1 = the variant that stages X_k by TMA bulk copies,
+// 2 = operands in registers with the half-warp-per-column upper stage; unset / anything else = the default variant (operands in
+// registers, grouped upper stage). Read once per process (tuning aid, like B200_NO_FIXED).
 int env_variant()
 {
     static const int v = [] {
@@ -67,8 +68,9 @@ cudaError_t launch_mode(int mode, uint32_t n_rows, cudaStream_t st, const FastAr
 
 // N = 32 000 = (8 x 8) x (25 x 20) (BASELINE configs[1], Galileo E1 at 8 MS/s): a row is 256 kB = the shared memory of an SM pair.
 // 8 x 8 lower blocks: 4 blocks = 32 pencils per warp in both lower passes; 16 warps x 2 columns of the 32 a CTA owns.
-using G32k_r = GeoW<8, 8, 25, 20, 2, 512, 0>;   // operands in registers, no staging (default)
-using G32k_w = GeoW<8, 8, 25, 20, 2, 512, 2>;   // X_k tiles by TMA bulk copies, two-stage ring
+using G32k_g = GeoW<8, 8, 25, 20, 2, 512, 0, 1, 4>;  // operands in registers, grouped upper stage (default)
+using G32k_r = GeoW<8, 8, 25, 20, 2, 512, 0>;        // operands in registers, one upper-stage column per half-warp (B200_ACQ_CLUSTER=2)
+using G32k_w = GeoW<8, 8, 25, 20, 2, 512, 2>;        // X_k tiles by TMA bulk copies, two-stage ring (B200_ACQ_CLUSTER=1)
 }  // namespace
 
 bool cluster_preferred_plan(uint32_t N, uint32_t* ra_lo, uint32_t* rb_lo, uint32_t* ra_hi, uint32_t* rb_hi)
@@ -92,7 +94,11 @@ uint32_t cluster_tiles(uint32_t ra_lo, uint32_t rb_lo, uint32_t ra_hi, uint32_t 
 cudaError_t launch_inv_cluster(uint32_t ra_lo, uint32_t rb_lo, uint32_t ra_hi, uint32_t rb_hi, int mode, uint32_t n_rows, cudaStream_t st, const FastArgs& a)
 {
     if (ra_lo == 8 && rb_lo == 8 && ra_hi == 25 && rb_hi == 20)
-        return env_variant() == 1 ? launch_mode<G32k_w>(mode, n_rows, st, a) : launch_mode<G32k_r>(mode, n_rows, st, a);
+        {
+            if (env_variant() == 1) return launch_mode<G32k_w>(mode, n_rows, st, a);
+            if (env_variant() == 2) return launch_mode<G32k_r>(mode, n_rows, st, a);
+            return launch_mode<G32k_g>(mode, n_rows, st, a);
+        }
     return cudaErrorInvalidValue;
 }
 

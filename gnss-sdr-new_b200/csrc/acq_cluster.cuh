@@ -98,9 +98,14 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 // STAGES_ = 0: no operand staging at all — both operands are loaded straight from L2 into registers one tile ahead (each element is
 // used exactly once, so staging only costs shared-memory bandwidth, which ncu shows to be this kernel's scarcest resource); the
 // one "stage" left is the warps' transpose buffer between pass A and pass B.
-template <int RA_, int RB_, int RAH_, int RBH_, int CS_, int THREADS_, int STAGES_, int CTAS_PER_SM_ = 1>
+// UG_ = 0: upper stage with one column per half-warp (20 and 25 pencils on 16 lanes: 45 of 64 lane slots used). UG_ = 4: groups of
+// four warps own eight columns and deal their 8 x 20 + 8 x 25 pencils out in half-warp tiles of (2 pencils x 8 columns): three
+// rounds per warp instead of four, 360 of 384 lane slots used; one named barrier of 128 threads between the two passes; row
+// pitch CW + 8, for which those tiles - and the lower stage's stores - are bank-conflict-free.
+template <int RA_, int RB_, int RAH_, int RBH_, int CS_, int THREADS_, int STAGES_, int CTAS_PER_SM_ = 1, int UG_ = 0>
 struct GeoW
 {
+    static constexpr int UG = UG_;
     static constexpr int RA = RA_, RB = RB_, RAH = RAH_, RBH = RBH_, CS = CS_, THREADS = THREADS_, CTAS_PER_SM = CTAS_PER_SM_;
     static constexpr bool kTma = STAGES_ > 0;
     static constexpr int kStages = STAGES_ > 0 ? STAGES_ : 1;
@@ -108,7 +113,7 @@ struct GeoW
     static constexpr int NW = THREADS / 32;
     static constexpr int CW = M_LO / CS;      // upper-stage columns owned by one CTA
     static constexpr int CPW = CW / NW;       // ... by one warp
-    static constexpr int UP = CW + 1;         // U row pitch (odd)
+    static constexpr int UP = UG_ ? CW + 8 : CW + 1;  // U row pitch (odd, or 8 mod 16 for the grouped upper stage)
     static constexpr int BPC = M_HI / CS;     // lower-stage blocks transformed by one CTA
     static constexpr int GB = 32 / RB;        // blocks per warp and tile
     static constexpr int TB = NW * GB;        // blocks per tile
@@ -122,6 +127,7 @@ struct GeoW
     static_assert(32 % RB == 0 && (GB * RA) % 32 == 0, "a warp's blocks fill whole 32-lane rounds in both lower passes");
     static_assert(CW % NW == 0 && CW % RA == 0, "columns per warp / pass-B pencils per column range");
     static_assert(RA == 8 && RB == 8, "the pass-A swizzle below is derived for 8 x 8 blocks");
+    static_assert(UG_ == 0 || (UG_ == 4 && CW / (THREADS_ / 32) == 2 && CW % 16 == 0 && RBH_ % 2 == 0 && (THREADS_ / 32) % 4 == 0), "grouped upper stage: 4 warps x 2 columns, pitch 8 mod 16");
     static_assert((BPC * RB * 8) % 16 == 0 && ((BPC % TB) * RB * 8) % 16 == 0 && (TP * 8) % 16 == 0, "bulk copies need 16-byte granularity");
     static constexpr size_t smem_bytes = (size_t)(U_ELEMS + kStages * TILE + M_HI) * sizeof(float2) + kStages * (sizeof(uint64_t) + sizeof(uint32_t)) + 16;
 };
@@ -326,60 +332,130 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
                 __syncthreads();
 
             // ================= upper stage: warp-local, CPW columns of U in place =================
-            // lanes: half-warp h works on column (h % CPW) of the warp, lanes of a half-warp on 16 consecutive pencils of that
-            // column: with the odd row pitch every 64-bit access of both strided passes is conflict-free
-            static_assert(CPW == 2, "lane map of the upper stage: one column per half-warp");
-            float2* Uw = U + w * CPW + (lane >> 4);
-            const uint32_t l16 = lane & 15u;
-#pragma unroll 1
-            for (uint32_t ub = l16; ub < (uint32_t)RBH && !(dbg & 4u); ub += 16)
-                {
-                    float2 v[RAH];
-                    float2* col = Uw + (size_t)RAH * ub * UP;
-#pragma unroll
-                    for (int u = 0; u < RAH; u++) v[u] = col[u * UP];
-                    fft::Dft<RAH, true>::run(v);
-#pragma unroll
-                    for (int q = 0; q < RAH; q++) col[q * UP] = fft::cmul(v[q], tw_hi[ub * RAH + q]);
-                }
-            __syncwarp();
             float best = -1.f, sum = 0.f;
             uint32_t best_pos = 0xffffffffu;
-#pragma unroll 1
-            for (uint32_t aa = l16; aa < (uint32_t)RAH && !(dbg & 32u); aa += 16)
+            if constexpr (G::UG == 0)
                 {
-                    float2 v[RBH];
-                    float2* col = Uw + (size_t)aa * UP;
+                // lanes: half-warp h works on column (h % CPW) of the warp, lanes of a half-warp on 16 consecutive pencils of that
+                // column: with the odd row pitch every 64-bit access of both strided passes is conflict-free
+                static_assert(CPW == 2, "lane map of the upper stage: one column per half-warp");
+                float2* Uw = U + w * CPW + (lane >> 4);
+                const uint32_t l16 = lane & 15u;
+#pragma unroll 1
+                for (uint32_t ub = l16; ub < (uint32_t)RBH && !(dbg & 4u); ub += 16)
+                    {
+                        float2 v[RAH];
+                        float2* col = Uw + (size_t)RAH * ub * UP;
 #pragma unroll
-                    for (int u = 0; u < RBH; u++) v[u] = col[(size_t)RAH * u * UP];
-                    fft::Dft<RBH, true>::run(v);
-                    if (MODE == 1)
+                        for (int u = 0; u < RAH; u++) v[u] = col[u * UP];
+                        fft::Dft<RAH, true>::run(v);
+#pragma unroll
+                        for (int q = 0; q < RAH; q++) col[q * UP] = fft::cmul(v[q], tw_hi[ub * RAH + q]);
+                    }
+                __syncwarp();
+#pragma unroll 1
+                for (uint32_t aa = l16; aa < (uint32_t)RAH && !(dbg & 32u); aa += 16)
+                    {
+                        float2 v[RBH];
+                        float2* col = Uw + (size_t)aa * UP;
+#pragma unroll
+                        for (int u = 0; u < RBH; u++) v[u] = col[(size_t)RAH * u * UP];
+                        fft::Dft<RBH, true>::run(v);
+                        if (MODE == 1)
+                            {
+                                // persistent grid: park |.|^2 in the slots just consumed; the coalesced read-modify-write follows below
+#pragma unroll
+                                for (int b = 0; b < RBH; b++) col[(size_t)RAH * b * UP].x = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                            }
+                        else
+                            {
+                                const uint32_t pos0 = aa * M_LO + rank * CW + w * CPW + (lane >> 4);
+                                float pbest = -1.f;
+                                uint32_t pb = 0;
+#pragma unroll
+                                for (int b = 0; b < RBH; b++)
+                                    {
+                                        const float gm = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                                        sum += gm;
+                                        const bool gt = gm > pbest;
+                                        pbest = gt ? gm : pbest;
+                                        pb = gt ? (uint32_t)b : pb;
+                                    }
+                                const uint32_t ppos = pos0 + pb * (RAH * M_LO);
+                                if (pbest > best || (pbest == best && ppos < best_pos))
+                                    {
+                                        best = pbest;
+                                        best_pos = ppos;
+                                    }
+                            }
+                    }
+                }
+            else
+                {
+                    // Groups of UG warps own UG * CPW = 8 columns. Half-warp tiles of (2 consecutive pencils x 8 columns): with the
+                    // pitch 8 mod 16 every 64-bit access of both strided passes is conflict-free. Pass 1 has RBH / 2 = 10 tiles,
+                    // pass 2 (RAH + 1) / 2 = 13 (the last one half full); they are dealt to the group's 8 half-warps so that every
+                    // warp runs three rounds, and the role of a warp rotates with the group so that the one warp with two radix-RAH
+                    // rounds sits on a different scheduler in each group.
+                    constexpr uint32_t kHw = 2 * G::UG, GC = G::UG * CPW;
+                    static_assert(GC == 8, "tile = 2 pencils x 8 columns");
+                    const uint32_t grp = w / G::UG, role = (w + grp) % G::UG;
+                    const uint32_t hw = role * 2 + (lane >> 4), c8 = lane & 7u, sub = (lane >> 3) & 1u;
+                    float2* Ug = U + grp * GC + c8;
+#pragma unroll 1
+                    for (uint32_t j = hw; j < (uint32_t)RBH / 2 && !(dbg & 4u); j += kHw)
                         {
-                            // persistent grid: park |.|^2 in the slots just consumed; the coalesced read-modify-write follows below
+                            const uint32_t ub = 2 * j + sub;
+                            float2 v[RAH];
+                            float2* col = Ug + (size_t)RAH * ub * UP;
 #pragma unroll
-                            for (int b = 0; b < RBH; b++) col[(size_t)RAH * b * UP].x = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                            for (int u = 0; u < RAH; u++) v[u] = col[u * UP];
+                            fft::Dft<RAH, true>::run(v);
+#pragma unroll
+                            for (int q = 0; q < RAH; q++) col[q * UP] = fft::cmul(v[q], tw_hi[ub * RAH + q]);
                         }
-                    else
+                    __syncwarp();
+                    asm volatile("bar.sync %0, %1;" ::"r"(1u + grp), "n"(G::UG * 32) : "memory");  // the group's columns are through pass 1
+#pragma unroll 1
+                    for (uint32_t j = (hw + kHw - 2) % kHw; j < (uint32_t)(RAH + 1) / 2 && !(dbg & 32u); j += kHw)
                         {
-                            const uint32_t pos0 = aa * M_LO + rank * CW + w * CPW + (lane >> 4);
-                            float pbest = -1.f;
-                            uint32_t pb = 0;
+                            const uint32_t aa = 2 * j + sub;
+                            if (aa < (uint32_t)RAH)
+                                {
+                                    float2 v[RBH];
+                                    float2* col = Ug + (size_t)aa * UP;
 #pragma unroll
-                            for (int b = 0; b < RBH; b++)
-                                {
-                                    const float gm = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
-                                    sum += gm;
-                                    const bool gt = gm > pbest;
-                                    pbest = gt ? gm : pbest;
-                                    pb = gt ? (uint32_t)b : pb;
-                                }
-                            const uint32_t ppos = pos0 + pb * (RAH * M_LO);
-                            if (pbest > best || (pbest == best && ppos < best_pos))
-                                {
-                                    best = pbest;
-                                    best_pos = ppos;
+                                    for (int u = 0; u < RBH; u++) v[u] = col[(size_t)RAH * u * UP];
+                                    fft::Dft<RBH, true>::run(v);
+                                    if (MODE == 1)
+                                        {
+#pragma unroll
+                                            for (int b = 0; b < RBH; b++) col[(size_t)RAH * b * UP].x = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                                        }
+                                    else
+                                        {
+                                            const uint32_t pos0 = aa * M_LO + rank * CW + grp * GC + c8;
+                                            float pbest = -1.f;
+                                            uint32_t pb = 0;
+#pragma unroll
+                                            for (int b = 0; b < RBH; b++)
+                                                {
+                                                    const float gm = v[b].x * v[b].x + v[b].y * v[b].y;  // :674
+                                                    sum += gm;
+                                                    const bool gt = gm > pbest;
+                                                    pbest = gt ? gm : pbest;
+                                                    pb = gt ? (uint32_t)b : pb;
+                                                }
+                                            const uint32_t ppos = pos0 + pb * (RAH * M_LO);
+                                            if (pbest > best || (pbest == best && ppos < best_pos))
+                                                {
+                                                    best = pbest;
+                                                    best_pos = ppos;
+                                                }
+                                        }
                                 }
                         }
+                    __syncwarp();
                 }
             if (MODE == 1)
                 {

@@ -60,7 +60,8 @@ VARIANTS = {
     "ref": dict(B200_ACQ_CLUSTER="0"),                                   # two-kernel path, its own plan
     "ref_sameplan": dict(B200_ACQ_CLUSTER="0", B200_FFT_PLAN="8,8,25,20"),  # two-kernel path on the row-resident kernel's plan
     "cl_tma": dict(B200_ACQ_CLUSTER="1"),
-    "cl": dict(),
+    "cl_halfwarp": dict(B200_ACQ_CLUSTER="2"),                           # registers, one upper-stage column per half-warp
+    "cl": dict(),                                                        # default: registers, grouped upper stage
 }
 REC = np.dtype([("test_statistic", np.float32), ("peak", np.float32), ("input_power", np.float32), ("second_peak", np.float32),
                 ("code_phase", np.uint32), ("doppler_index", np.uint32), ("doppler_hz", np.int32), ("dwell_count", np.uint32)])
