@@ -52,6 +52,15 @@ __device__ __forceinline__ void st_cluster(uint32_t addr, float2 v)
 }
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// arrival that publishes nothing (the warp only READ the buffer the barrier guards): no fence in front of it
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
+// operand loads: read-only path, not kept in L1 (each element is used once; L1 is left to the few spilled registers)
+__device__ __forceinline__ float2 ldg_stream(const float2* p)
+{
+    float2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+    return v;
+}
 
 // ---- mbarrier + bulk copy (TMA, 1-D) ----
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
@@ -184,19 +193,25 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
     const uint32_t total_tiles = my_rows * NT;
 
     // operand rows of the row the tile counter is in, and of the one after it (resolved once per row, not once per tile)
-    const float2 *rowX[2] = {nullptr, nullptr}, *rowC[2] = {nullptr, nullptr};
+    // (32-bit row numbers in two pairs of scalars selected by the row's parity: a dynamically indexed array would live in local
+    // memory, and four 64-bit pointers cost registers this kernel does not have)
+    uint32_t rowX0 = 0, rowX1 = 0, rowC0 = 0, rowC1 = 0;
     auto resolve_row = [&](uint32_t r, int slot) {
         if (r >= my_rows) return;
         const uint32_t y = a.y0 + cluster_id + r * n_clusters;
         uint32_t si, kk;
         fast_row_of(a, y, si, kk);
-        rowX[slot] = a.X + ((size_t)a.slot_group[si] * a.nD_local + kk) * N + rank * BPC * RB;
-        rowC[slot] = a.Cs + (size_t)a.slots[si] * N + rank * BPC * RB;
+        const uint32_t xr = a.slot_group[si] * a.nD_local + kk, cr = a.slots[si];
+        if (slot)
+            rowX1 = xr, rowC1 = cr;
+        else
+            rowX0 = xr, rowC0 = cr;
     };
     auto operands = [&](uint32_t g, const float2*& X, const float2*& Cp) {
-        const uint32_t slot = (g / NT) & 1u, col0 = (g % NT) * TB * RB;
-        X = rowX[slot] + col0;
-        Cp = rowC[slot] + col0;
+        const bool odd = (g / NT) & 1u;
+        const uint32_t col0 = rank * BPC * RB + (g % NT) * TB * RB;
+        X = a.X + (size_t)(odd ? rowX1 : rowX0) * N + col0;
+        Cp = a.Cs + (size_t)(odd ? rowC1 : rowC0) * N + col0;
     };
     resolve_row(0, 0);
     resolve_row(1, 1);
@@ -222,11 +237,11 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
                 const float2 *X, *Cp;
                 operands(g, X, Cp);
 #pragma unroll
-                for (int u = 0; u < RA; u++) cn[u] = __ldg(Cp + (size_t)u * SEG + w * 32 + lane);
+                for (int u = 0; u < RA; u++) cn[u] = ldg_stream(Cp + (size_t)u * SEG + w * 32 + lane);
                 if (!kTma)
                     {
 #pragma unroll
-                        for (int u = 0; u < RA; u++) xn[kTma ? 0 : u] = __ldg(X + (size_t)u * SEG + w * 32 + lane);
+                        for (int u = 0; u < RA; u++) xn[kTma ? 0 : u] = ldg_stream(X + (size_t)u * SEG + w * 32 + lane);
                     }
             }
     };
@@ -248,6 +263,8 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
                 {
                     float2* xt = xs + (kTma ? (g % S) * TILE : 0) + w * 32;  // this warp's 32-column window
                     const uint32_t nblk = tile_blocks(g);
+                    static_assert(GB * RA == 32, "one pass-B pencil per lane and tile");
+                    const uint32_t bl_b = w * GB + lane / RA, aa_b = lane % RA;  // this lane's pass-B pencil: block of the tile, column
                     if (kTma && (!(dbg & 2u) || g < (uint32_t)S)) mbar_wait(&full[g % S], (g / S) & 1u);
                     // ---- pass A: product, radix-RA IDFT, inner twiddle; stored swizzled (column ^ (q >= RA/2)) ----
                     {
@@ -264,19 +281,15 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
                         if (act)
                             {
 #pragma unroll
-                                for (int q = 0; q < RA; q++) xt[q * TP + (lane ^ (uint32_t)(q >= RA / 2))] = fft::cmul(x[q], twl[q]);
+                                for (int q = 0; q < RA; q++) xt[q * TP + (lane ^ (uint32_t)(q >= RA / 2))] = q ? fft::cmul(x[q], twl[q]) : x[q];  // twl[0] = 1
                             }
                     }
                     __syncwarp();
                     if (t == 0 && r > 0 && CS > 1 && !(dbg & 64u)) cluster_wait();  // every CTA is done READING its U of the previous row
                     // ---- pass B: radix-RB IDFT, inter-stage twiddle, to the owner of each column ----
-#pragma unroll 1
-                    for (uint32_t pp = lane; pp < (uint32_t)(GB * RA) && !(dbg & 16u); pp += 32)
+                    if (bl_b < nblk && !(dbg & 16u))
                         {
-                            const uint32_t bl_l = pp / RA, aa = pp - bl_l * RA;
-                            const uint32_t bl = w * GB + bl_l;
-                            if (bl >= nblk) continue;
-                            const uint32_t gblk = rank * BPC + t * TB + bl;
+                            const uint32_t bl_l = lane / RA, aa = aa_b, gblk = rank * BPC + t * TB + bl_b;
                             const uint32_t ubh = gblk / RAH, uah = gblk - ubh * RAH;
                             const uint32_t k1 = uah * RBH + ubh;  // upper-stage frequency index of this block
                             const float2 wb = __ldg(a.W + (size_t)k1 * aa);
@@ -479,7 +492,7 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
                                     }
                             }
                 }
-            if (CS > 1 && r + 1 < my_rows && !(dbg & 64u)) cluster_arrive();  // this warp is done reading U
+            if (CS > 1 && r + 1 < my_rows && !(dbg & 64u)) cluster_arrive_relaxed();  // this warp is done reading U (nothing to publish)
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1)
                 {
