@@ -398,10 +398,14 @@ def run_ours(args):
     row_resident = prof_cnt[1] == 0 and geo["fft_size"] == 32000   # the row-resident inverse kernel ran (no "first stage -> scratch" launches)
     traffic, traffic_src = None, "no ncu capture of this kernel variant under profiles/"
     if row_resident and dom == 2:
-        per_dwell = ncu_dram_bytes("r02_cluster_ncu_summary.txt", "v4")   # one launch = 4000 rows
+        tag = "v6"                                                        # the newest capture of this kernel; one launch = 4000 rows
+        per_dwell = ncu_dram_bytes("r02_cluster_ncu_summary.txt", tag)
+        if per_dwell is None:
+            tag = "v4"
+            per_dwell = ncu_dram_bytes("r02_cluster_ncu_summary.txt", tag)
         if per_dwell is not None:
             traffic = per_dwell * (n_prn * eng.n_doppler_local) / 4000.0
-            traffic_src = "ncu --set full, profiles/r02_cluster_ncu_summary.txt (v4: dram read + write of one 4000-row launch, scaled to the rows of this launch)"
+            traffic_src = f"ncu --set full, profiles/r02_cluster_ncu_summary.txt ({tag}: dram read + write of one 4000-row launch, scaled to the rows of this launch)"
     roofline = {"kernel": names[dom] + (" (row-resident: cluster + DSMEM)" if row_resident and dom == 2 else ""), "bound": "hbm", "achieved": achieved_gbs,
                 "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": peak_src,
