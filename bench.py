@@ -191,7 +191,7 @@ def workload_config(name, geo, n_doppler, world=1, exchange="nccl"):
     return {"workload": desc, "fft_size": geo["fft_size"], "n_doppler_bins": n_doppler, "n_prn": geo["n_prn"],
             "cells_per_step": geo["n_prn"] * n_doppler * geo["fft_size"],
             "l2_policy": "L2 flushed (256 MiB write) between timed iterations",
-            "parallelism": "one GPU" if world == 1 else
+            "parallelism": "one GPU; the search's five launches replayed as ONE CUDA graph (gnss_b200_acq_capture_*), per-kernel times taken eagerly afterwards" if world == 1 else
                            f"ONE search, its {n_doppler} Doppler rows sharded over {world} GPUs ({-(-n_doppler // world)} rows x all PRNs each, no forward FFT computed twice); "
                            + ("row records stored into every rank's region over peer memory (NVLink stores + system-scope flags, no collective), decision on "
                               "every device; a rank's whole step (search + exchange + decision) replayed as ONE CUDA graph" if exchange == "peer" else
@@ -315,7 +315,7 @@ def run_ours(args):
     want = {t["prn"] for t in truth if t["cn0"] > 41.0}
     if not want <= found:
         raise RuntimeError(f"bench.py: search is wrong, strong PRNs {sorted(want - found)} not detected")
-    use_graph = world > 1   # a shard's dwell is short: its launches go out as one CUDA graph (gnss_b200_acq_capture_*)
+    use_graph = True   # the search's launches go out as one CUDA graph (gnss_b200_acq_capture_*); per-kernel times are taken afterwards, eagerly
     if use_graph:
         eng.capture_begin()
         eng.dwell_device_async(d_iq.data_ptr(), slots)
@@ -324,7 +324,7 @@ def run_ours(args):
         eng.capture_end()
         barrier()
         eng.replay_async()
-        if not peer:
+        if world > 1 and not peer:
             exchange_and_decide()
         if eng.sync(n_prn).tobytes() != res.tobytes():
             raise RuntimeError("bench.py: the replayed dwell differs from the recorded one")
@@ -341,9 +341,12 @@ def run_ours(args):
     for i in range(args.steps):
         flush_l2()
         barrier()
-        if world > 1:
-            # the host barrier releases the ranks tens of microseconds apart; a 4-byte all-reduce queued on the engine's stream right
-            # before the start event aligns the ranks ON THE DEVICE, so the timed region holds the search and its exchange, not that skew
+        if world > 1 and peer:
+            # the host barrier releases the ranks tens of microseconds apart, and so does a collective; the engine's own rendezvous
+            # kernel (flags in every rank's region) right before the start event aligns the ranks ON THE DEVICE to within a store
+            # latency, so the timed region holds the search and its exchange, not that skew
+            eng.peer_barrier_async()
+        elif world > 1:
             with torch.cuda.stream(est):
                 dist.all_reduce(align_t)
         ev[i][0].record(est)

@@ -149,7 +149,7 @@ EXPORTS = [
     "gnss_b200_trk_stream", "gnss_b200_trk_launch_count",
     "gnss_b200_acq_exchange_buffers", "gnss_b200_acq_finalize_gathered_async",
     "gnss_b200_acq_capture_begin", "gnss_b200_acq_capture_end", "gnss_b200_acq_replay_async",
-    "gnss_b200_acq_peer_setup", "gnss_b200_acq_peer_connect", "gnss_b200_acq_peer_exchange_async",
+    "gnss_b200_acq_peer_setup", "gnss_b200_acq_peer_connect", "gnss_b200_acq_peer_exchange_async", "gnss_b200_acq_peer_barrier_async",
     "gnss_b200_acq_group_create", "gnss_b200_acq_group_destroy", "gnss_b200_acq_group_num_doppler_bins", "gnss_b200_acq_group_num_shards",
     "gnss_b200_acq_group_set_local_codes", "gnss_b200_acq_group_set_doppler_center", "gnss_b200_acq_group_reset", "gnss_b200_acq_group_dwell",
     "gnss_b200_acq_group_read_grid", "gnss_b200_acq_group_launch_count",
@@ -198,6 +198,7 @@ def lib():
     L.gnss_b200_acq_peer_setup.argtypes = [C.c_void_p, c_u32, C.c_void_p, C.POINTER(C.c_void_p)]
     L.gnss_b200_acq_peer_connect.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
     L.gnss_b200_acq_peer_exchange_async.argtypes = [C.c_void_p, c_u32]
+    L.gnss_b200_acq_peer_barrier_async.argtypes = [C.c_void_p]
     L.gnss_b200_acq_group_create.argtypes = [C.POINTER(AcqCfg), c_u32, C.POINTER(c_i32), C.POINTER(C.c_void_p)]
     L.gnss_b200_acq_group_destroy.argtypes = [C.c_void_p]
     L.gnss_b200_acq_group_num_doppler_bins.argtypes = [C.c_void_p]
@@ -395,6 +396,10 @@ class PcpsAcquisitionB200:
 
     def peer_exchange_async(self, n_slots):
         _check(self.L.gnss_b200_acq_peer_exchange_async(self.h, int(n_slots)))
+
+    def peer_barrier_async(self):
+        """device-side rendezvous of all connected shards on the engine's stream (gnss_b200_acq_peer_barrier_async)"""
+        _check(self.L.gnss_b200_acq_peer_barrier_async(self.h))
 
     def capture_begin(self):
         _check(self.L.gnss_b200_acq_capture_begin(self.h))

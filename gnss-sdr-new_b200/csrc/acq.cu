@@ -1071,7 +1071,8 @@ extern "C"
         L.world = h->xchg_world;
         L.rank = rank;
         L.flags_off = 256;
-        L.recv_off = (256 + 2 * L.world * 128 + 255) & ~255u;
+        L.bar_off = 256 + 2 * L.world * 128;
+        L.recv_off = (L.bar_off + L.world * 128 + 255) & ~255u;
         L.per_shard_rows = h->cfg.max_slots * h->xchg_chunk;
         const size_t bytes = (size_t)L.recv_off + sizeof(gnss_b200_acq_row) * 2ull * L.world * L.per_shard_rows;
         B200_CUDA(cudaStreamSynchronize(h->stream));
@@ -1160,6 +1161,18 @@ extern "C"
             }
         B200_CUDA(cudaGetLastError());
         B200_CUDA(cudaMemcpyAsync(h->h_results.p, h->d_results.p, sizeof(gnss_b200_acq_result) * n_slots, cudaMemcpyDeviceToHost, h->stream));
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_acq_peer_barrier_async(gnss_b200_acq* h)
+    {
+        B200_REQUIRE(h, GNSS_B200_ERR_INVALID, "acq_peer_barrier_async: null handle");
+        std::lock_guard<std::mutex> lk(h->mu);
+        B200_CUDA(cudaSetDevice(h->cfg.device));
+        B200_REQUIRE(h->peer_connected, GNSS_B200_ERR_STATE, "acq_peer_barrier_async: call gnss_b200_acq_peer_setup / _peer_connect first");
+        peer_barrier_kernel<<<1, 32, 0, h->stream>>>(h->d_peer_ptrs.as<char*>(), h->d_peer.as<char>(), h->peer_layout, h->d_peer.as<uint32_t>() + 48);
+        h->launches++;
+        B200_CUDA(cudaGetLastError());
         return GNSS_B200_OK;
     }
 

@@ -583,6 +583,7 @@ static __global__ void finalize_gathered_kernel(const FinalizeArgs a, const gnss
 struct PeerLayout
 {
     uint32_t world, rank, flags_off, recv_off, per_shard_rows;
+    uint32_t bar_off;  // [world] rendezvous counters (128 B apart), written by the peers (peer_barrier_kernel)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
@@ -695,6 +696,25 @@ static __global__ void finalize_peer_kernel(const FinalizeArgs a, const char* ow
 }
 
 static __global__ void peer_epoch_bump_kernel(uint32_t* epoch_ctr) { *epoch_ctr += 1u; }
+
+// Rendezvous of all shards ON THE DEVICE (one warp): every shard stores its next rendezvous number into EVERY region and waits
+// until all `world` counters of its own region have reached it. Shards leave within an NVLink store latency of each other -
+// what a time-critical caller (or a benchmark) puts in front of a search so that it starts on all GPUs together; ~2 s time-out.
+static __global__ void peer_barrier_kernel(char* const* peers, char* own, const PeerLayout L, uint32_t* ctr)
+{
+    const uint32_t lane = threadIdx.x;
+    const uint32_t n = *ctr + 1u;
+    __syncwarp();
+    if (lane == 0) *ctr = n;
+    for (uint32_t d = lane; d < L.world; d += 32) st_release_sys(reinterpret_cast<uint32_t*>(peers[d] + L.bar_off + (size_t)L.rank * 128u), n);
+    for (uint32_t r = lane; r < L.world; r += 32)
+        {
+            const uint32_t* flag = reinterpret_cast<const uint32_t*>(own + L.bar_off + (size_t)r * 128u);
+            const long long t0 = clock64();
+            while ((int32_t)(ld_acquire_sys(flag) - n) < 0)
+                if (clock64() - t0 > 4000000000ll) break;
+        }
+}
 
 // The tail of a peer-connected shard's search in ONE kernel (instead of merge_partials + finalize + pack_rows + peer_scatter): CTA
 // si folds the per-tile records of its slot's rows (the arithmetic of merge_partials_kernel / finalize_kernel, so the records

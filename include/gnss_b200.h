@@ -188,6 +188,11 @@ extern "C"
     GNSS_B200_API int gnss_b200_acq_peer_setup(gnss_b200_acq* h, uint32_t rank, void* ipc_handle_out /* 64 bytes or NULL */, void** region_out);
     GNSS_B200_API int gnss_b200_acq_peer_connect(gnss_b200_acq* h, const void* ipc_handles /* [world][64] or NULL */, void* const* regions /* [world] or NULL */);
     GNSS_B200_API int gnss_b200_acq_peer_exchange_async(gnss_b200_acq* h, uint32_t n_slots);
+    /* Rendezvous of all connected shards on the device, queued on the handle's stream: a one-warp kernel that announces itself in
+       every region and waits for all `world` shards (~2 s time-out). Shards leave it within an NVLink store latency of each
+       other - put it in front of a search that has to start on all GPUs together (a collective's ranks finish tens of
+       microseconds apart). Every shard must call it, in the same order relative to its exchanges. */
+    GNSS_B200_API int gnss_b200_acq_peer_barrier_async(gnss_b200_acq* h);
 
     /* The same inside ONE process that drives several GPUs (the reference receiver is one process): a group owns one engine
        per listed device, splits the Doppler rows of every slot over them (Doppler-major: no forward transform is computed

@@ -167,6 +167,7 @@ def test_peer_exchange_with_a_single_shard(b200, scene, n_prn):
             e.dwell_device_async(buf.data_ptr(), slots)
             e.peer_exchange_async(n_prn)
             e.capture_end()
+        e.peer_barrier_async()
         if k >= 1:
             e.replay_async()
         else:

@@ -121,6 +121,8 @@ def test_record_exchange_over_peer_memory(two_devices, scene, n_prn):
                 e.dwell_device_async(bufs[r].data_ptr(), slots)
                 e.peer_exchange_async(n_prn)
                 e.capture_end()
+        for e in shards:
+            e.peer_barrier_async()           # device-side rendezvous of the two shards in front of the search
         for r, e in enumerate(shards):
             if k >= 2:
                 e.replay_async()
