@@ -14,17 +14,20 @@
 //                 then |.|^2, the optional persistent-grid accumulation, and per-warp {max, first argmax, sum} records;
 //   cluster barrier (split: arrive after the upper stage, wait before the next row's first remote store).
 //
-// Both stages are WARP-LOCAL: a warp owns whole lower blocks and whole upper columns, so the transposes inside a stage need
-// __syncwarp only and there is no CTA-wide barrier in a records-only search. Operands: either straight from L2 into registers
+// The lower stage is WARP-LOCAL: a warp owns whole blocks, so its transpose needs __syncwarp only. The upper stage is warp-local too
+// with one column per half-warp (GeoW<..., UG = 0>), or - the default, UG = 4 - runs in groups of four warps that deal the pencils of
+// their eight columns out so that every lane has work (one 128-thread named barrier between its two passes); there is no CTA-wide
+// barrier in a records-only search. Operands: either straight from L2 into registers
 // one tile ahead (default: every element is used exactly once, and ncu shows shared-memory bandwidth to be this kernel's
 // scarcest resource), or the X_k tiles by bulk copies (TMA, mbarrier ring) with C* in registers (B200_ACQ_CLUSTER=1).
 //
 // The arithmetic (codelets, twiddle tables, operation order) is exactly that of the two-kernel path on the same FFT plan, so grids
 // are bit-identical to it and records differ only in the summation order of the row sum. DRAM traffic per C2 dwell drops from
-// 2.05 GB to 33 MB (profiles/r02_cluster_ncu_summary.txt). What was measured on the way (profiles/r02_cluster_experiments.md):
+// 2.05 GB to 34 MB (profiles/r02_cluster_ncu_summary.txt). What was measured on the way (profiles/r02_cluster_experiments.md):
 // CTA-barrier versions with TMA rings (0.91-1.08 ms), a 4-CTA cluster with two CTAs per SM, and a warp-specialised version with
 // the two stages pipelined over a double-buffered U and remote mbarrier arrivals (1.09 ms: the kernel is issue-bound, overlap
-// buys nothing) — all bit-identical, all slower than this one (0.75 ms, two-kernel path 0.83 ms).
+// buys nothing) — all bit-identical, all slower than this one (0.63 ms with the grouped upper stage, 0.75 ms without; two-kernel
+// path 0.83 ms).
 #pragma once
 #include "acq_fast.cuh"
 #include <cooperative_groups.h>
