@@ -141,7 +141,10 @@ struct GeoW
     static_assert(RA == 8 && RB == 8, "the pass-A swizzle below is derived for 8 x 8 blocks");
     static_assert(UG_ == 0 || (UG_ == 4 && CW / (THREADS_ / 32) == 2 && CW % 16 == 0 && RBH_ % 2 == 0 && (THREADS_ / 32) % 4 == 0), "grouped upper stage: 4 warps x 2 columns, pitch 8 mod 16");
     static_assert((BPC * RB * 8) % 16 == 0 && ((BPC % TB) * RB * 8) % 16 == 0 && (TP * 8) % 16 == 0, "bulk copies need 16-byte granularity");
-    static constexpr size_t smem_bytes = (size_t)(U_ELEMS + kStages * TILE + M_HI) * sizeof(float2) + kStages * (sizeof(uint64_t) + sizeof(uint32_t)) + 16;
+    static constexpr int kRowTab = 256;       // rows of one cluster whose operand row numbers are looked up once, at kernel start
+    static constexpr int TWL = RB * (RA + 1); // lower-stage inner twiddles [ub][q], pitch RA + 1: the 8 rows a warp reads lie in distinct banks
+    static constexpr size_t smem_bytes = (size_t)(U_ELEMS + kStages * TILE + M_HI + TWL) * sizeof(float2) + kRowTab * 2 * sizeof(uint32_t) +
+                                         kStages * (sizeof(uint64_t) + sizeof(uint32_t)) + 16;
 };
 
 template <class G, int MODE>
@@ -155,7 +158,9 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
     float2* U = reinterpret_cast<float2*>(smem_raw);   // [M_HI][UP]: this CTA's columns of the row between the stages
     float2* xs = U + G::U_ELEMS;                       // [S][RA][TP]: X_k tiles (kTma) / the warps' transpose windows
     float2* tw_hi = xs + S * TILE;                     // conj W_Mhi^(q*ub), [ub][q]
-    uint64_t* full = reinterpret_cast<uint64_t*>(tw_hi + M_HI);  // [S] "tile landed"
+    float2* twl_s = tw_hi + M_HI;                      // conj W_Mlo^(q*ub), [ub][RA + 1]
+    uint32_t* rowtab = reinterpret_cast<uint32_t*>(twl_s + G::TWL);  // [kRowTab][2]: X row, C* row of this cluster's r-th row
+    uint64_t* full = reinterpret_cast<uint64_t*>(rowtab + 2 * G::kRowTab);  // [S] "tile landed"
     uint32_t* done = reinterpret_cast<uint32_t*>(full + S);      // [S] warps that have finished with the stage's tile
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, w = tid >> 5;
@@ -181,43 +186,44 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
 #pragma unroll
     for (int d = 0; d < CS; d++) u_base[d] = CS > 1 ? map_rank(smem_u32(U), d) : smem_u32(U);
     // pass-A pencil of this lane inside its warp's window: block w*GB + lane / RB of the tile, ub = lane % RB — the same for every
-    // tile, so its inner twiddles conj W_Mlo^(q*ub) stay in registers for the whole kernel
+    // tile. Its inner twiddles conj W_Mlo^(q*ub) are read from a small shared table: held in registers they were spilled (the
+    // kernel runs at its 128-register limit) and came back from local memory with a long-scoreboard stall every tile.
     const uint32_t ub_a = lane % RB, bl_a = w * GB + lane / RB;
-    float2 twl[RA];
-#pragma unroll
-    for (int q = 0; q < RA; q++)
+    for (uint32_t i = tid; i < (uint32_t)(RA * RB); i += kT)
         {
-            const float2 t = __ldg(a.W + (size_t)q * ub_a * (N / M_LO));
-            twl[q] = make_float2(t.x, -t.y);
+            const uint32_t ub = i / RA, q = i - ub * RA;
+            const float2 t = __ldg(a.W + (size_t)q * ub * (N / M_LO));
+            twl_s[ub * (RA + 1) + q] = make_float2(t.x, -t.y);
         }
-    __syncthreads();
+    const float2* twl = twl_s + ub_a * (RA + 1);
 
     const uint32_t my_rows = cluster_id < n_rows ? (n_rows - cluster_id + n_clusters - 1) / n_clusters : 0;
     const uint32_t total_tiles = my_rows * NT;
 
-    // operand rows of the row the tile counter is in, and of the one after it (resolved once per row, not once per tile)
-    // (32-bit row numbers in two pairs of scalars selected by the row's parity: a dynamically indexed array would live in local
-    // memory, and four 64-bit pointers cost registers this kernel does not have)
-    uint32_t rowX0 = 0, rowX1 = 0, rowC0 = 0, rowC1 = 0;
-    auto resolve_row = [&](uint32_t r, int slot) {
-        if (r >= my_rows) return;
+    // operand rows (X_k row, C* row) of this cluster's rows: looked up once, here, by as many threads as there are rows - inside
+    // the row loop the two dependent global loads per row (slot -> group / code slot) were a long-scoreboard stall per row
+    auto row_numbers = [&](uint32_t r, uint32_t& xr, uint32_t& cr) {
         const uint32_t y = a.y0 + cluster_id + r * n_clusters;
         uint32_t si, kk;
         fast_row_of(a, y, si, kk);
-        const uint32_t xr = a.slot_group[si] * a.nD_local + kk, cr = a.slots[si];
-        if (slot)
-            rowX1 = xr, rowC1 = cr;
-        else
-            rowX0 = xr, rowC0 = cr;
+        xr = a.slot_group[si] * a.nD_local + kk;
+        cr = a.slots[si];
     };
+    for (uint32_t r = tid; r < my_rows && r < (uint32_t)G::kRowTab; r += kT) row_numbers(r, rowtab[2 * r], rowtab[2 * r + 1]);
+    __syncthreads();
     auto operands = [&](uint32_t g, const float2*& X, const float2*& Cp) {
-        const bool odd = (g / NT) & 1u;
-        const uint32_t col0 = rank * BPC * RB + (g % NT) * TB * RB;
-        X = a.X + (size_t)(odd ? rowX1 : rowX0) * N + col0;
-        Cp = a.Cs + (size_t)(odd ? rowC1 : rowC0) * N + col0;
+        const uint32_t r = g / NT, col0 = rank * BPC * RB + (g - r * NT) * TB * RB;
+        uint32_t xr, cr;
+        if (r < (uint32_t)G::kRowTab)
+            {
+                const uint2 rc = *reinterpret_cast<const uint2*>(rowtab + 2 * r);
+                xr = rc.x, cr = rc.y;
+            }
+        else
+            row_numbers(r, xr, cr);
+        X = a.X + (size_t)xr * N + col0;
+        Cp = a.Cs + (size_t)cr * N + col0;
     };
-    resolve_row(0, 0);
-    resolve_row(1, 1);
     auto tile_blocks = [&](uint32_t g) -> uint32_t {  // the last tile of a row share may be partial
         const uint32_t t = g % NT;
         return (t + 1) * TB <= (uint32_t)BPC ? (uint32_t)TB : (uint32_t)BPC - t * TB;
@@ -258,7 +264,6 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
             const uint32_t y = a.y0 + cluster_id + r * n_clusters;
             uint32_t si, kk;
             fast_row_of(a, y, si, kk);
-            if (r > 0) resolve_row(r + 1, (r + 1) & 1);  // row r - 1's slot is free: its last tile was loaded before this row began
 
             // ================= lower stage: warp-local, tile after tile =================
 #pragma unroll 1
