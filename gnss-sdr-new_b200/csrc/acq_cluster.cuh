@@ -273,6 +273,16 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
                     const uint32_t nblk = tile_blocks(g);
                     static_assert(GB * RA == 32, "one pass-B pencil per lane and tile");
                     const uint32_t bl_b = w * GB + lane / RA, aa_b = lane % RA;  // this lane's pass-B pencil: block of the tile, column
+                    // its inter-stage twiddles: asked for here, used after pass A
+                    float2 wb = make_float2(1.f, 0.f), ws = make_float2(1.f, 0.f);
+                    if (bl_b < nblk)
+                        {
+                            const uint32_t gblk = rank * BPC + t * TB + bl_b;
+                            const uint32_t ubh = gblk / RAH, uah = gblk - ubh * RAH;
+                            const uint32_t k1 = uah * RBH + ubh;  // upper-stage frequency index of this block
+                            wb = __ldg(a.W + (size_t)k1 * aa_b);
+                            ws = __ldg(a.W + (size_t)k1 * RA);
+                        }
                     if (kTma && (!(dbg & 2u) || g < (uint32_t)S)) mbar_wait(&full[g % S], (g / S) & 1u);
                     // ---- pass A: product, radix-RA IDFT, inner twiddle; stored swizzled (column ^ (q >= RA/2)) ----
                     {
@@ -298,10 +308,6 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
                     if (bl_b < nblk && !(dbg & 16u))
                         {
                             const uint32_t bl_l = lane / RA, aa = aa_b, gblk = rank * BPC + t * TB + bl_b;
-                            const uint32_t ubh = gblk / RAH, uah = gblk - ubh * RAH;
-                            const uint32_t k1 = uah * RBH + ubh;  // upper-stage frequency index of this block
-                            const float2 wb = __ldg(a.W + (size_t)k1 * aa);
-                            const float2 ws = __ldg(a.W + (size_t)k1 * RA);
                             float2 v[RB];
                             const uint32_t swz = aa >= RA / 2;
 #pragma unroll
