@@ -49,13 +49,22 @@ cudaError_t launch_one(uint32_t n_rows, cudaStream_t st, const FastArgs& a)
             if (slot >= 0) n_clusters_cached[slot].store(n_clusters, std::memory_order_relaxed);
             if (std::getenv("B200_CL_VERBOSE")) fprintf(stderr, "inv_cluster CS=%d threads=%d smem=%zu: %d co-resident clusters\n", G::CS, G::THREADS, (size_t)G::smem_bytes, n_clusters);
         }
-    const uint32_t use = std::min<uint32_t>((uint32_t)n_clusters, n_rows);
-    cfg.gridDim = dim3(use * G::CS);
     static const uint32_t dbg = [] {
         const char* e = std::getenv("B200_CL_DBG");  // timing experiments only (results are wrong with any bit set)
         return e ? (uint32_t)std::atoi(e) : 0u;
     }();
-    return cudaLaunchKernelEx(&cfg, kernel, a, n_rows, dbg);
+    // a cluster looks the operand rows of at most kRowTab rows up at its start: larger searches go out in several launches
+    const uint32_t per_launch = (uint32_t)n_clusters * (uint32_t)G::kRowTab;
+    FastArgs part = a;
+    for (uint32_t y0 = 0; y0 < n_rows; y0 += per_launch)
+        {
+            const uint32_t cnt = std::min(per_launch, n_rows - y0);
+            part.y0 = a.y0 + y0;
+            cfg.gridDim = dim3(std::min<uint32_t>((uint32_t)n_clusters, cnt) * G::CS);
+            const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, part, cnt, dbg);
+            if (e != cudaSuccess) return e;
+        }
+    return cudaSuccess;
 }
 
 template <class G>

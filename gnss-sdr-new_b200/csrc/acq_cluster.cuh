@@ -211,18 +211,11 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
     };
     for (uint32_t r = tid; r < my_rows && r < (uint32_t)G::kRowTab; r += kT) row_numbers(r, rowtab[2 * r], rowtab[2 * r + 1]);
     __syncthreads();
-    auto operands = [&](uint32_t g, const float2*& X, const float2*& Cp) {
+    auto operands = [&](uint32_t g, const float2*& X, const float2*& Cp) {  // (the launcher never gives a cluster more than kRowTab rows)
         const uint32_t r = g / NT, col0 = rank * BPC * RB + (g - r * NT) * TB * RB;
-        uint32_t xr, cr;
-        if (r < (uint32_t)G::kRowTab)
-            {
-                const uint2 rc = *reinterpret_cast<const uint2*>(rowtab + 2 * r);
-                xr = rc.x, cr = rc.y;
-            }
-        else
-            row_numbers(r, xr, cr);
-        X = a.X + (size_t)xr * N + col0;
-        Cp = a.Cs + (size_t)cr * N + col0;
+        const uint2 rc = *reinterpret_cast<const uint2*>(rowtab + 2 * r);
+        X = a.X + (size_t)rc.x * N + col0;
+        Cp = a.Cs + (size_t)rc.y * N + col0;
     };
     auto tile_blocks = [&](uint32_t g) -> uint32_t {  // the last tile of a row share may be partial
         const uint32_t t = g % NT;

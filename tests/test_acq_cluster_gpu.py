@@ -41,6 +41,13 @@ f = b.PcpsAcquisitionB200(geo["fft_size"], geo["consumed_samples"], geo["doppler
 f.set_local_codes(np.arange(4), codes[:4])
 out["rec_2nd"] = f.dwell(iq, np.arange(4))
 f.close()
+# 50 PRNs x 400 Doppler rows (25 Hz step) = 20 000 rows: more than one launch of the row-resident kernel (74 clusters x 256 rows each)
+geo50, codes50, iq50, _ = synth.config_scene("C2", n_prn=50)
+m = b.PcpsAcquisitionB200(geo50["fft_size"], geo50["consumed_samples"], geo50["doppler_max"], 25, geo50["fs"], geo50["samples_per_chip"], 50, use_cfar=True)
+assert m.n_doppler == 400
+m.set_local_codes(np.arange(50), codes50)
+out["rec_many"] = m.dwell(iq50, np.arange(50))
+m.close()
 np.savez(sys.argv[2], **out)
 """
 
@@ -52,14 +59,14 @@ def _run(tmp_path, tag, env):
     return np.load(path)
 
 
-@pytest.mark.parametrize("variant", ["default", "tma"])
+@pytest.mark.parametrize("variant", ["default", "tma", "halfwarp"])
 def test_row_resident_inverse_equals_two_kernel_path(tmp_path, variant):
     ref = _run(tmp_path, "ref", dict(B200_ACQ_CLUSTER="0", B200_FFT_PLAN="8,8,25,20"))
-    got = _run(tmp_path, variant, {} if variant == "default" else dict(B200_ACQ_CLUSTER="1"))
+    got = _run(tmp_path, variant, {"default": {}, "tma": dict(B200_ACQ_CLUSTER="1"), "halfwarp": dict(B200_ACQ_CLUSTER="2")}[variant])
     assert int(ref["first_stage_launches"][0]) == 2 and int(got["first_stage_launches"][0]) == 0   # the path under test really ran
     for k in ("grid0", "grid2"):
         assert np.array_equal(got[k], ref[k]), k                        # same arithmetic in the same order
-    for k in ("rec", "rec_subset", "rec_grid", "rec_2nd"):
+    for k in ("rec", "rec_subset", "rec_grid", "rec_2nd", "rec_many"):
         a, c = ref[k], got[k]
         for f in ("peak", "code_phase", "doppler_index", "doppler_hz", "dwell_count", "second_peak"):
             assert np.array_equal(a[f], c[f]), (k, f)
