@@ -401,11 +401,11 @@ def run_ours(args):
     row_resident = prof_cnt[1] == 0 and geo["fft_size"] == 32000   # the row-resident inverse kernel ran (no "first stage -> scratch" launches)
     traffic, traffic_src = None, "no ncu capture of this kernel variant under profiles/"
     if row_resident and dom == 2:
-        tag = "v6"                                                        # the newest capture of this kernel; one launch = 4000 rows
-        per_dwell = ncu_dram_bytes("r02_cluster_ncu_summary.txt", tag)
-        if per_dwell is None:
-            tag = "v4"
+        per_dwell = None
+        for tag in ("v7", "v6", "v4"):                                    # the newest capture of this kernel; one launch = 4000 rows
             per_dwell = ncu_dram_bytes("r02_cluster_ncu_summary.txt", tag)
+            if per_dwell is not None:
+                break
         if per_dwell is not None:
             traffic = per_dwell * (n_prn * eng.n_doppler_local) / 4000.0
             traffic_src = f"ncu --set full, profiles/r02_cluster_ncu_summary.txt ({tag}: dram read + write of one 4000-row launch, scaled to the rows of this launch)"
