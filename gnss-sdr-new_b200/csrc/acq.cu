@@ -73,6 +73,7 @@ struct gnss_b200_acq
     std::vector<void*> peer_opened;  // cudaIpcOpenMemHandle mappings to close
     bool peer_connected = false;
     bool tail_deferred = false;  // peer-connected shard: the last dwell left its per-tile records for peer_exchange_async (shard_tail_kernel)
+    bool graph_leaves_tail = false;  // tail_deferred as the captured sequence left it: a replay puts the handle into the same state
     // what the last dwell left on the device for gnss_b200_acq_finalize_gathered_async
     FinalizeArgs last_f{};
     // a captured dwell (gnss_b200_acq_capture_*)
@@ -1203,6 +1204,7 @@ extern "C"
         if (h->graph) cudaGraphDestroy(h->graph);
         h->graph = g;
         h->graph_exec = nullptr;
+        h->graph_leaves_tail = h->tail_deferred;
         B200_CUDA(cudaGraphInstantiate(&h->graph_exec, h->graph, 0));
         size_t n_nodes = 0;
         B200_CUDA(cudaGraphGetNodes(h->graph, nullptr, &n_nodes));
@@ -1224,6 +1226,7 @@ extern "C"
         B200_CUDA(cudaSetDevice(h->cfg.device));
         B200_REQUIRE(h->graph_exec, GNSS_B200_ERR_STATE, "acq_replay_async: nothing captured");
         B200_CUDA(cudaGraphLaunch(h->graph_exec, h->stream));
+        h->tail_deferred = h->graph_leaves_tail;  // e.g. a captured dwell of a connected shard whose exchange is queued eagerly afterwards
         h->launches += h->graph_kernels;  // the kernels the replay runs (one graph launch on the host)
         return GNSS_B200_OK;
     }

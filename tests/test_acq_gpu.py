@@ -179,6 +179,14 @@ def test_peer_exchange_with_a_single_shard(b200, scene, n_prn):
         assert got.tobytes() == want.tobytes(), (scene, k)
         for p in (0, n_prn - 1):
             assert e.read_rows(p).tobytes() == one.read_rows(p).tobytes()
+    # a graph that holds the dwell only, the exchange queued eagerly behind every replay
+    e.capture_begin()
+    e.dwell_device_async(buf.data_ptr(), slots)
+    e.capture_end()
+    for _ in range(2):
+        e.replay_async()
+        e.peer_exchange_async(n_prn)
+        assert e.sync(n_prn).tobytes() == want.tobytes()
     e.close()
     one.close()
 
