@@ -186,8 +186,9 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
 #pragma unroll
     for (int d = 0; d < CS; d++) u_base[d] = CS > 1 ? map_rank(smem_u32(U), d) : smem_u32(U);
     // pass-A pencil of this lane inside its warp's window: block w*GB + lane / RB of the tile, ub = lane % RB — the same for every
-    // tile. Its inner twiddles conj W_Mlo^(q*ub) are read from a small shared table: held in registers they were spilled (the
-    // kernel runs at its 128-register limit) and came back from local memory with a long-scoreboard stall every tile.
+    // tile. Its inner twiddles conj W_Mlo^(q*ub): the first kTwReg stay in registers, the others are read from a small shared
+    // table at their use - all seven in registers were spilled (the kernel runs at its 128-register limit) and came back from local
+    // memory with a long-scoreboard stall every tile; five (one with a persistent grid) is what fits without a spill.
     const uint32_t ub_a = lane % RB, bl_a = w * GB + lane / RB;
     for (uint32_t i = tid; i < (uint32_t)(RA * RB); i += kT)
         {
@@ -196,6 +197,14 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
             twl_s[ub * (RA + 1) + q] = make_float2(t.x, -t.y);
         }
     const float2* twl = twl_s + ub_a * (RA + 1);
+    constexpr int kTwReg = MODE == 1 ? 1 : 5;  // (the persistent-grid form has fewer registers to spare)
+    float2 twr[kTwReg + 1];
+#pragma unroll
+    for (int q = 1; q <= kTwReg; q++)
+        {
+            const float2 t = __ldg(a.W + (size_t)q * ub_a * (N / M_LO));
+            twr[q] = make_float2(t.x, -t.y);
+        }
 
     const uint32_t my_rows = cluster_id < n_rows ? (n_rows - cluster_id + n_clusters - 1) / n_clusters : 0;
     const uint32_t total_tiles = my_rows * NT;
@@ -292,7 +301,7 @@ __global__ void __launch_bounds__(G::THREADS, G::CTAS_PER_SM) inv_cluster_wl_ker
                         if (act)
                             {
 #pragma unroll
-                                for (int q = 0; q < RA; q++) xt[q * TP + (lane ^ (uint32_t)(q >= RA / 2))] = q ? fft::cmul(x[q], twl[q]) : x[q];  // twl[0] = 1
+                                for (int q = 0; q < RA; q++) xt[q * TP + (lane ^ (uint32_t)(q >= RA / 2))] = q ? fft::cmul(x[q], q <= kTwReg ? twr[q <= kTwReg ? q : 0] : twl[q]) : x[q];  // twl[0] = 1
                             }
                     }
                     __syncwarp();
