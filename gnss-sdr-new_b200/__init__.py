@@ -139,7 +139,7 @@ EXPORTS = [
     "gnss_b200_acq_stream", "gnss_b200_acq_launch_count", "gnss_b200_acq_transform_length", "gnss_b200_mc_create", "gnss_b200_mc_destroy",
     "gnss_b200_mc_set_code", "gnss_b200_mc_set_stream", "gnss_b200_mc_correlate_batch",
     "gnss_b200_mc_correlate_device_async", "gnss_b200_mc_sync", "gnss_b200_mc_chip_indices", "gnss_b200_mc_stream",
-    "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan",
+    "gnss_b200_mc_launch_count", "gnss_b200_debug_wipeoff_phase", "gnss_b200_debug_fft_plan", "gnss_b200_debug_transform_length",
     "gnss_b200_acq_profile", "gnss_b200_mc_profile", "gnss_b200_debug_fp32_peak",
     "gnss_b200_acq_create_step2", "gnss_b200_acq_set_step2_center",
     "gnss_b200_mc_correlate_noalloc", "gnss_b200_mc_noalloc_scratch_bytes",
@@ -240,6 +240,7 @@ def lib():
     L.gnss_b200_mc_launch_count.restype = C.c_uint64
     L.gnss_b200_debug_wipeoff_phase.argtypes = [c_i32, C.c_double, c_u32, _fp, _u32p]
     L.gnss_b200_debug_fft_plan.argtypes = [c_u32, _u32p, _u32p, _u32p, _u32p]
+    L.gnss_b200_debug_transform_length.argtypes = [c_u32, c_u32, _u32p]
     L.gnss_b200_acq_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]
     L.gnss_b200_mc_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_int]
     L.gnss_b200_debug_fp32_peak.argtypes = [c_i32, C.POINTER(C.c_double)]
@@ -507,6 +508,13 @@ def finalize_rows(rows, effective_size, doppler_max, doppler_step, doppler_cente
 
 def acq_threshold(pfa, effective_size, n_doppler, max_dwells=1, bit_transition=False):
     return float(lib().gnss_b200_acq_threshold(pfa, effective_size, n_doppler, max_dwells, int(bit_transition)))
+
+
+def debug_transform_length(fft_size, consumed_samples=None):
+    """transform length the engine searches `fft_size` lags on (no device needed)"""
+    m = c_u32(0)
+    _check(lib().gnss_b200_debug_transform_length(int(fft_size), int(consumed_samples or fft_size), C.byref(m)))
+    return int(m.value)
 
 
 def debug_wipeoff_phase(doppler_hz, fs, n):

@@ -674,6 +674,53 @@ bool consider_padded(const b200::FftPlan& plan)
     return false;
 }
 
+// The transform the engine runs for a search of `fft_size` lags over `consumed` samples: the length's own plan, or the padded form.
+//
+// A length the mixed-radix kernels cannot take (a prime factor > 127; FFTW in the reference takes any d_fft_size,
+// pcps_acquisition.cc:85-92,114-115) or take only slowly. The search needs the CYCLIC correlation of length n = fft_size of the
+// (zero-padded) block x, nonzero on [0, consumed), with the zero-padded code c:
+//     y[m] = sum_i x[i] conj(c[(i - m) mod n]),  0 <= m < n.
+// i - m runs over [-(n - 1), consumed - 1]: a cyclic correlation of any length M >= n + consumed - 1 produces the same y when the
+// samples are zero-padded to M and the code buffer holds c[0 .. consumed) at its start and c[1 .. n) at its END (negative i - m
+// wrap onto that tail) - for every layout of set_local_code (:176-209): full (2n - 1), zero-padded double length (1.5n - 1), bit
+// transition. The engine runs on the cheapest M = 2^a 3^b 5^c it has a plan for (points x cost per point of the plan), searches the
+// lags the layout keeps, and scales the code by n / M so that magnitudes equal those of unnormalised length-n transforms.
+bool choose_transform(uint32_t fft_size, uint32_t consumed, b200::FftPlan* plan, uint32_t* length, const char** why)
+{
+    using b200::FftPlan;
+    using b200::make_fft_plan;
+    const bool have_plan = make_fft_plan(fft_size, kMaxSingleStagePoints, plan, why);
+    *length = fft_size;
+    if (have_plan && !consider_padded(*plan)) return true;
+    const bool forced = getenv("B200_FFT_PAD") != nullptr;
+    uint32_t best_m = 0;
+    double best_cost = have_plan && !forced ? 0.9 * (double)fft_size * plan_cost_per_point(*plan) : 1e300;
+    const uint64_t m_min = (uint64_t)fft_size + consumed - 1, m_max = std::min<uint64_t>(4 * m_min, 1ull << 31);
+    for (uint64_t p2 = 1; p2 <= m_max; p2 *= 2)
+        for (uint64_t p3 = p2; p3 <= m_max; p3 *= 3)
+            for (uint64_t p5 = p3; p5 <= m_max; p5 *= 5)
+                if (p5 >= m_min)
+                    {
+                        FftPlan trial;
+                        const char* w2 = nullptr;
+                        if (!make_fft_plan((uint32_t)p5, kMaxSingleStagePoints, &trial, &w2)) continue;
+                        const double cost = (double)p5 * plan_cost_per_point(trial);
+                        if (cost < best_cost || (cost == best_cost && p5 < best_m))
+                            {
+                                best_cost = cost;
+                                best_m = (uint32_t)p5;
+                            }
+                    }
+    FftPlan padded_plan;
+    if (best_m && make_fft_plan(best_m, kMaxSingleStagePoints, &padded_plan, why))
+        {
+            *plan = padded_plan;
+            *length = best_m;
+            return true;
+        }
+    return have_plan;
+}
+
 int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, gnss_b200_acq** out)
     {
         B200_REQUIRE(cfg && out, GNSS_B200_ERR_INVALID, "acq_create: null argument");
@@ -715,53 +762,14 @@ int create_impl(const gnss_b200_acq_cfg* cfg, uint32_t n_step2, float step2_hz, 
         h->code_off = h->N - h->code_len;
         if (!cfg->bit_transition && h->N == h->consumed) h->code_off = 0;
         const char* why = nullptr;
-        const bool have_plan = make_fft_plan(h->N, kMaxSingleStagePoints, &h->plan, &why);
-        if (!have_plan || consider_padded(h->plan))
+        uint32_t transform_len = 0;
+        if (!choose_transform(cfg->fft_size, cfg->consumed_samples, &h->plan, &transform_len, &why))
             {
-                // A length the mixed-radix kernels cannot take (a prime factor > 127; FFTW in the reference takes any d_fft_size,
-                // pcps_acquisition.cc:85-92,114-115) or take only slowly. The search needs the CYCLIC correlation of length
-                // n = fft_size of the (zero-padded) block x, nonzero on [0, consumed), with the zero-padded code c:
-                //     y[m] = sum_i x[i] conj(c[(i - m) mod n]),  0 <= m < n.
-                // i - m runs over [-(n - 1), consumed - 1]: a cyclic correlation of any length M >= n + consumed - 1 produces the
-                // same y when the samples are zero-padded to M and the code buffer holds c[0 .. consumed) at its start and
-                // c[1 .. n) at its END (negative i - m wrap onto that tail) - for every layout of set_local_code (:176-209): full
-                // (2n - 1), zero-padded double length (1.5n - 1), bit transition. The engine runs on the cheapest
-                // M = 2^a 3^b 5^c it has a plan for (points x cost per point of the plan), searches the lags the layout keeps, and
-                // scales the code by n / M so that magnitudes equal those of unnormalised length-n transforms.
-                const bool can_pad = true;
-                const bool forced = getenv("B200_FFT_PAD") != nullptr;
-                uint32_t best_m = 0;
-                double best_cost = have_plan && !forced ? 0.9 * (double)h->N * plan_cost_per_point(h->plan) : 1e300;
-                const uint64_t m_min = (uint64_t)cfg->fft_size + cfg->consumed_samples - 1, m_max = std::min<uint64_t>(4 * m_min, 1ull << 31);
-                if (can_pad)
-                    for (uint64_t p2 = 1; p2 <= m_max; p2 *= 2)
-                        for (uint64_t p3 = p2; p3 <= m_max; p3 *= 3)
-                            for (uint64_t p5 = p3; p5 <= m_max; p5 *= 5)
-                                if (p5 >= m_min)
-                                    {
-                                        FftPlan trial;
-                                        const char* w2 = nullptr;
-                                        if (!make_fft_plan((uint32_t)p5, kMaxSingleStagePoints, &trial, &w2)) continue;
-                                        const double cost = (double)p5 * plan_cost_per_point(trial);
-                                        if (cost < best_cost || (cost == best_cost && p5 < best_m))
-                                            {
-                                                best_cost = cost;
-                                                best_m = (uint32_t)p5;
-                                            }
-                                    }
-                FftPlan padded_plan;
-                if (best_m && make_fft_plan(best_m, kMaxSingleStagePoints, &padded_plan, &why))
-                    {
-                        h->plan = padded_plan;
-                        h->padded = true;
-                        h->N = best_m;  // eff, mag_offset, code_len, code_off stay those of the fft_size-point layout
-                    }
-                else if (!have_plan)
-                    {
-                        delete h;
-                        return fail(GNSS_B200_ERR_UNSUPPORTED, "acq_create: fft_size %u: %s", cfg->fft_size, why ? why : "unsupported");
-                    }
+                delete h;
+                return fail(GNSS_B200_ERR_UNSUPPORTED, "acq_create: fft_size %u: %s", cfg->fft_size, why ? why : "unsupported");
             }
+        h->padded = transform_len != cfg->fft_size;
+        h->N = transform_len;  // eff, mag_offset, code_len, code_off stay those of the fft_size-point layout
         h->center.assign(cfg->max_slots, 0);
         h->bias.assign(cfg->max_slots, 0);
         h->has_code.assign(cfg->max_slots, 0);
@@ -1000,6 +1008,15 @@ extern "C"
                 const std::vector<uint32_t> p = fft_plan_permutation(plan);
                 std::memcpy(perm, p.data(), sizeof(uint32_t) * n);
             }
+        return GNSS_B200_OK;
+    }
+
+    int gnss_b200_debug_transform_length(uint32_t fft_size, uint32_t consumed_samples, uint32_t* length)
+    {
+        B200_REQUIRE(length && fft_size >= 2 && consumed_samples >= 1 && consumed_samples <= fft_size, GNSS_B200_ERR_INVALID, "debug_transform_length: bad arguments");
+        FftPlan plan;
+        const char* why = nullptr;
+        if (!choose_transform(fft_size, consumed_samples, &plan, length, &why)) return fail(GNSS_B200_ERR_UNSUPPORTED, "fft_size %u: %s", fft_size, why ? why : "unsupported");
         return GNSS_B200_OK;
     }
 

@@ -496,6 +496,9 @@ extern "C"
        denominator for the FP32 roofline of the acquisition kernels, which no driver-written file provides. */
     GNSS_B200_API int gnss_b200_debug_fp32_peak(int32_t device, double* tflops);
     GNSS_B200_API int gnss_b200_debug_fft_plan(uint32_t n, uint32_t* n_stages, uint32_t* radices, uint32_t* n_radices, uint32_t* perm);
+    /* The transform length gnss_b200_acq_create would choose for this search (gnss_b200_acq_transform_length of the handle);
+       needs no device. */
+    GNSS_B200_API int gnss_b200_debug_transform_length(uint32_t fft_size, uint32_t consumed_samples, uint32_t* length);
 
 #ifdef __cplusplus
 }

@@ -156,3 +156,27 @@ def test_acq_geometry_matches_reference_configurations(b200):
     assert (g["fft_size"], g["consumed_samples"]) == (160000, 80000)
     g = b200.acq_geometry(4e6, 1.023e6, 1, 1, bit_transition=True)
     assert (g["fft_size"], g["effective_size"]) == (8000, 4000)
+
+
+def test_transform_length_choice_needs_no_device(b200, monkeypatch):
+    """gnss_b200_debug_transform_length = the choice gnss_b200_acq_create makes: codelet lengths as they are,
+    lengths with a prime factor >= 31 as a padded correlation on the cheapest 2^a 3^b 5^c length >= fft_size + consumed - 1 (by
+    points x cost per point of the plan kind), in every code layout; B200_FFT_PAD forces the choice."""
+    monkeypatch.delenv("B200_FFT_PAD", raising=False)
+    L = b200.debug_transform_length
+    for n in (4000, 8000, 16000, 25000, 32000, 100000, 160000, 7 * 11 * 13 * 4, 17 * 1000):
+        assert L(n) == n
+    want = {2046: 4096, 4092: 8192, 8184: 16384, 12276: 25000, 16368: 32768, 32736: 65536, 65472: 160000,   # the prime 31
+            5003: 10240, 4146: 10000, 2053: 5000}                                                           # primes above 127
+    for n, m in want.items():
+        assert L(n) == m, n
+        assert m >= 2 * n - 1
+    # zero-padded double-length dwell (consumed = fft_size / 2): M >= 1.5 fft_size - 1; bit transition: consumed = fft_size
+    assert L(16368, 8184) == 25000 and L(8184, 4092) == 12500 and L(8224, 4112) == 12500 and L(4112, 4112) == 10000
+    monkeypatch.setenv("B200_FFT_PAD", "0")
+    assert L(4092) == 4092 and L(65472) == 65472
+    assert L(5003) == 10240                       # no plan of its own: padded whatever the switch says
+    monkeypatch.setenv("B200_FFT_PAD", "1")
+    assert L(4000) == 8000
+    with pytest.raises(b200.B200Error):
+        L(4000, 4001)
